@@ -1,0 +1,54 @@
+"""Pins the oracle (oracle/model.py, oracle/neighbors.py) against fixtures produced by the unmodified
+reference (oracle/make_golden.py).  CPU only."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import GOLDEN, SMALL, load_npz, tt
+from oracle import model as om
+from oracle import neighbors as onb
+
+# the reference's own comparison tolerance for model goldens (torch.testing.assert_allclose fp32 defaults,
+# tests/test_model.py:184-188): rtol 1.3e-6, atol 1e-5
+RTOL, ATOL = 1.3e-6, 1e-5
+
+
+@pytest.mark.parametrize("name", SMALL + ["small_tensornet_periodic.npz"])
+def test_oracle_matches_reference_small_models(name):
+    g = load_npz(name)
+    box = tt(g["box"]) if "box" in g else None
+    y, f = om.energy_forces(g["sd"], g["hparams"], tt(g["z"]), tt(g["pos"]), tt(g["batch"]), box=box)
+    torch.testing.assert_close(y, tt(g["y"]), rtol=1e-5, atol=2e-5)
+    torch.testing.assert_close(f, tt(g["forces"]), rtol=1e-4, atol=2e-5)
+
+
+@pytest.mark.parametrize("i", range(8))
+def test_oracle_neighbors_match_reference_cpu_op(i):
+    g = load_npz("neighbors_%d.npz" % i)
+    box = g["box"] if g["box"].size else None
+    nb, dl, ds = onb.neighbor_pairs(g["pos"], g["batch"], box, 0.0, float(g["cutoff"]), loop=bool(g["loop"]),
+                                    include_transpose=bool(g["transpose"]), d2_rule=False)
+    assert nb.shape[1] == int(g["count"][0]) == g["neighbors"].shape[1]
+    a = onb.canonical_order(nb, dl, ds)
+    b = onb.canonical_order(g["neighbors"], g["deltas"], g["distances"])
+    assert np.array_equal(a[0], b[0])                       # pair set bit-exact after sorting
+    np.testing.assert_allclose(a[1], b[1], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(a[2], b[2], rtol=1e-5, atol=1e-6)
+
+
+def test_neighbor_backward_restatement_matches_autograd():
+    rng = np.random.RandomState(0)
+    pos = rng.randn(30, 3) * 1.5
+    nb, dl, ds = onb.neighbor_pairs(pos, None, None, 0.0, 2.5, loop=True)
+    gd, gw = rng.randn(*dl.shape), rng.randn(*ds.shape)
+    p = torch.tensor(pos, requires_grad=True)
+    i, j = torch.from_numpy(nb[0].astype("int64")), torch.from_numpy(nb[1].astype("int64"))
+    v = p[i] - p[j]
+    nz = torch.from_numpy(ds != 0)
+    w = v[nz].norm(dim=1)
+    loss = (v[nz] * torch.from_numpy(gd)[nz]).sum() + (w * torch.from_numpy(gw)[nz]).sum()
+    loss.backward()
+    np.testing.assert_allclose(onb.neighbor_backward(nb, dl, ds, gd, gw, 30), p.grad.numpy(), atol=1e-10)
