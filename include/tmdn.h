@@ -1,0 +1,166 @@
+/* tmdn.h -- C ABI of the B200-native TorchMD-NET energy+force hot path (libtmdn.so).
+ *
+ * Plain pointers and sizes only; no torch types.  Every pointer marked "device" is a CUDA device
+ * pointer on the current device; `stream` is a cudaStream_t.  No entry point allocates, frees or
+ * synchronises: the caller passes a workspace (size from the matching *_workspace_bytes), so every
+ * call is CUDA-graph capturable.  All entry points return TMDN_OK (0) or an error code and never
+ * throw; tmdn_last_error() gives the message of the last failure on the calling thread.
+ *
+ * Reference interfaces replaced (paths relative to the reference repository):
+ *   tmdn_neighbors_*            torch op torchmdnet_neighbors::get_neighbor_pairs
+ *                               schema  torchmdnet/neighbors/neighbors.cpp:3-5
+ *                               brute   torchmdnet/neighbors/neighbors_cuda_brute.cuh:61-101
+ *                               shared  torchmdnet/neighbors/neighbors_cuda_shared.cuh:71-106
+ *                               cell    torchmdnet/neighbors/neighbors_cuda_cell.cuh:338-378
+ *   tmdn_neighbors_backward_*   NeighborAutograd::backward, torchmdnet/neighbors/neighbors_cuda.cu:43-71
+ *   tmdn_is_stream_capturing    torch_extension::is_stream_capturing, torchmdnet/models/utils.py:533-555
+ *   tmdn_csr_from_pairs         (new) CSR-by-target view of the pair list consumed by the model kernels
+ *   tmdn_tensornet_*            TensorNet.forward + Scalar head + TorchMD_Net force path:
+ *                               torchmdnet/models/tensornet.py:200-234,287-326,376-410,
+ *                               torchmdnet/models/output_modules.py:27-43,76-77,
+ *                               torchmdnet/models/model.py:232-300 (autograd.grad replaced by
+ *                               hand-written adjoint kernels)
+ *   tmdn_et_*                   TorchMD_ET.forward + EquivariantScalar head + force path:
+ *                               torchmdnet/models/torchmd_et.py:154-187,272-347,
+ *                               torchmdnet/models/utils.py:73-108,496-522,
+ *                               torchmdnet/models/output_modules.py:111-115
+ */
+#ifndef TMDN_H
+#define TMDN_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TMDN_VERSION 100
+#define TMDN_MAX_LAYERS 16
+
+typedef void* tmdn_stream_t; /* cudaStream_t */
+
+enum tmdn_status {
+    TMDN_OK = 0,
+    TMDN_EINVAL = 1,      /* bad argument (shape, null pointer, unsupported size) */
+    TMDN_ECUDA = 2,       /* a CUDA runtime call / kernel launch failed */
+    TMDN_EWORKSPACE = 3,  /* workspace too small */
+    TMDN_EUNSUPPORTED = 4 /* valid request this build does not implement */
+};
+
+enum tmdn_strategy { TMDN_BRUTE = 0, TMDN_SHARED = 1, TMDN_CELL = 2 };
+enum tmdn_rbf { TMDN_RBF_EXPNORM = 0, TMDN_RBF_GAUSS = 1 };
+enum tmdn_act { TMDN_ACT_SILU = 0, TMDN_ACT_TANH = 1, TMDN_ACT_SIGMOID = 2, TMDN_ACT_SSP = 3 };
+enum tmdn_filter_mode {
+    TMDN_FILTER_EXACT = 0, /* per-edge filter MLP evaluated exactly (fp32 FFMA GEMM chain), [E,*] in the workspace */
+    TMDN_FILTER_TABLE = 1  /* cubic Hermite table in d (host-built in fp64), evaluated inside the edge kernels */
+};
+
+int tmdn_version(void);
+const char* tmdn_last_error(void);
+
+/* 1 if `stream` is being captured into a CUDA graph, 0 if not, <0 on error. */
+int tmdn_is_stream_capturing(tmdn_stream_t stream);
+
+/* ---------------------------------------------------------------- neighbor list
+ * Semantics = the reference CUDA op: all pairs of atoms of the same batch with
+ * cutoff_lower^2 <= d^2 < cutoff_upper^2; delta = pos[i]-pos[j] (minimum image if use_periodic:
+ * triclinic round() z->y->x for brute/shared, rectangular floor(x/L+0.5) for cell); emitted as (i,j), i>j,
+ * plus (j,i) with -delta if include_transpose, plus (i,i,0,0) if loop.  Order is unspecified.
+ * Outputs are sized max_pairs: slots beyond the number found hold neighbors=-1, deltas=0,
+ * distances=0.  *num_found (device int32) receives the number FOUND, which may exceed max_pairs (the
+ * excess is dropped).  `box` is 9 host doubles, rows a,b,c (ignored unless use_periodic, except that
+ * the cell strategy always needs a diagonal box for binning).
+ */
+size_t tmdn_neighbors_workspace_bytes(int strategy, int64_t n_atoms, const double box[9], double cutoff_upper,
+                                      int elem_bytes);
+int tmdn_neighbors_f32(int strategy, const float* pos, const int64_t* batch, int64_t n_atoms, const double box[9],
+                       int use_periodic, double cutoff_lower, double cutoff_upper, int loop, int include_transpose,
+                       int64_t max_pairs, int32_t* neighbors, float* deltas, float* distances, int32_t* num_found,
+                       void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
+int tmdn_neighbors_f64(int strategy, const double* pos, const int64_t* batch, int64_t n_atoms, const double box[9],
+                       int use_periodic, double cutoff_lower, double cutoff_upper, int loop, int include_transpose,
+                       int64_t max_pairs, int32_t* neighbors, double* deltas, double* distances, int32_t* num_found,
+                       void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
+/* grad_pos[n_atoms,3] = sum_e (+g_e at neighbors[0][e], -g_e at neighbors[1][e]),
+ * g_e = grad_deltas[e] + deltas[e]/distances[e]*grad_distances[e], rows with distances==0 skipped.
+ * grad_pos is overwritten.  Either grad pointer may be NULL (treated as zero). */
+int tmdn_neighbors_backward_f32(const int32_t* neighbors, const float* deltas, const float* distances,
+                                const float* grad_deltas, const float* grad_distances, int64_t max_pairs,
+                                int64_t n_atoms, float* grad_pos, tmdn_stream_t stream);
+int tmdn_neighbors_backward_f64(const int32_t* neighbors, const double* deltas, const double* distances,
+                                const double* grad_deltas, const double* grad_distances, int64_t max_pairs,
+                                int64_t n_atoms, double* grad_pos, tmdn_stream_t stream);
+
+/* ---------------------------------------------------------------- CSR view of the pair list (fp32)
+ * Rows = target atoms (neighbors[target_row][e]), columns = the other atom, sorted by column inside each
+ * row so that every segmented reduction downstream is deterministic.  geom[e] = (ux,uy,uz,d) with
+ * u = (pos_target - pos_source)/d  (0 for self loops).  num_found/max_pairs as produced by tmdn_neighbors_*.
+ * row_ptr has n_atoms+1 entries.  If the list overflowed (found > max_pairs) only the stored pairs are used.
+ */
+size_t tmdn_csr_workspace_bytes(int64_t n_atoms, int64_t max_pairs);
+int tmdn_csr_from_pairs(const int32_t* neighbors, const float* deltas, const float* distances,
+                        const int32_t* num_found, int64_t max_pairs, int64_t n_atoms, int target_row,
+                        int32_t* row_ptr, int32_t* col, float* geom /* [max_pairs,4] */, void* workspace,
+                        size_t workspace_bytes, tmdn_stream_t stream);
+
+/* ---------------------------------------------------------------- TensorNet energy + forces (fp32)
+ * All weight pointers are device fp32 arrays prepared once by the host side (layouts below; H = hidden,
+ * K = num_rbf).  "T" suffix = transposed copy used by the backward kernels.
+ */
+typedef struct tmdn_filter_set {
+    /* EXACT mode: MLP K -> n1 [-> n2 -> n3], weights [out,in] row-major (+ transposed copies unused: the
+     * filter derivative is propagated forward as a tangent).  n_layers = 1 (embedding) or 3 (interaction);
+     * the last layer's rows are ordered g*H+h (g = I/A/S group).  final_act: activation after the last layer. */
+    int32_t n_layers, final_act;
+    int32_t dims[4]; /* K, n1, n2, n3 */
+    const float* w[3];
+    const float* b[3];
+    /* TABLE mode: [n_int][3][H] float4 cubic coefficients of f(d)*C(d) on a uniform grid over [0, cutoff_upper] */
+    const float* table;
+    int32_t n_int;
+    int32_t pad_;
+} tmdn_filter_set;
+
+typedef struct tmdn_tensornet_model {
+    int32_t hidden, num_rbf, num_layers, max_z;
+    int32_t rbf_type, activation, so3, filter_mode;
+    float cutoff_lower, cutoff_upper, mean, std;
+    const float* rbf_p0; /* expnorm: means[K]; gauss: offset[K] */
+    const float* rbf_p1; /* expnorm: betas[K]; gauss: coeff broadcast to [K] */
+    const float* P;      /* [max_z,H]  emb @ emb2.weight[:, :H]^T + emb2.bias   (tensornet.py:310-312) */
+    const float* Q;      /* [max_z,H]  emb @ emb2.weight[:, H:]^T */
+    tmdn_filter_set emb_filter;                  /* distance_proj1..3 stacked -> [3H] */
+    const float* emb_mix[3];  const float* emb_mixT[3];   /* tensor_embedding.linears_tensor.k  [H,H] */
+    const float* emb_ln_w;    const float* emb_ln_b;      /* init_norm */
+    const float* emb_w1;      const float* emb_b1;  const float* emb_w1T;   /* linears_scalar.0 [2H,H] */
+    const float* emb_w2;      const float* emb_b2;  const float* emb_w2T;   /* linears_scalar.1 [3H,2H], rows g*H+h */
+    tmdn_filter_set layer_filter[TMDN_MAX_LAYERS];        /* layers.l.linears_scalar.0-2 */
+    const float* layer_mix[TMDN_MAX_LAYERS][6];           /* layers.l.linears_tensor.0-5 [H,H] */
+    const float* layer_mixT[TMDN_MAX_LAYERS][6];
+    const float* out_ln_w;    const float* out_ln_b;      /* out_norm [3H] */
+    const float* out_w;       const float* out_b;   const float* out_wT;    /* linear [H,3H] */
+    const float* head_w1;     const float* head_b1; const float* head_w1T;  /* output_network.0 [H/2,H] */
+    const float* head_w2;     const float* head_b2;                         /* output_network.2 [1,H/2] */
+} tmdn_tensornet_model;
+
+size_t tmdn_tensornet_workspace_bytes(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,
+                                      int64_t n_mol);
+/* One energy(+force) evaluation.  z,batch int64 device [n_atoms] (batch sorted non-decreasing, values in
+ * [0,n_mol)); pos fp32 device [n_atoms,3]; energy fp32 device [n_mol]; forces fp32 device [n_atoms,3] or NULL
+ * (forward only).  Neighbors are searched with `strategy` under box/use_periodic; max_edges is the pair
+ * capacity INCLUDING self loops (reference: max_num_neighbors * n_atoms, models/utils.py:234-236).
+ * status (device int32[4]): [0] edges found, [1] 1 if found > max_edges (result then invalid), [2..3] reserved.
+ */
+int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const int64_t* z, const float* pos,
+                                 const int64_t* batch, int64_t n_atoms, int64_t n_mol, const double box[9],
+                                 int use_periodic, int strategy, int64_t max_edges, float* energy, float* forces,
+                                 int32_t* status, void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
+/* Debug/inspection: byte offset and size of a named intermediate inside the workspace (names as in
+ * oracle/staged_tensornet.py: "row_ptr","col","geom","ias","nh","fias","X0","Y0","M0","tauh0","X1",...,"e_atom","Dias","gpos"). */
+int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,
+                                    int64_t n_mol, const char* name, size_t* offset, size_t* bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TMDN_H */

@@ -1,0 +1,105 @@
+// common.cuh -- shared host/device helpers for libtmdn (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <stdarg.h>
+#include "../../include/tmdn.h"
+
+// ------------------------------------------------------------------ error plumbing (never throws)
+void tmdn_set_error(const char* fmt, ...);
+
+#define TMDN_CHECK_ARG(cond, ...)                 \
+    do {                                          \
+        if (!(cond)) {                            \
+            tmdn_set_error(__VA_ARGS__);          \
+            return TMDN_EINVAL;                   \
+        }                                         \
+    } while (0)
+
+#define TMDN_CUDA(call)                                                                         \
+    do {                                                                                        \
+        cudaError_t err__ = (call);                                                             \
+        if (err__ != cudaSuccess) {                                                             \
+            tmdn_set_error("%s failed at %s:%d: %s", #call, __FILE__, __LINE__,                 \
+                           cudaGetErrorString(err__));                                          \
+            return TMDN_ECUDA;                                                                  \
+        }                                                                                       \
+    } while (0)
+
+#define TMDN_LAUNCH_CHECK()                                                                     \
+    do {                                                                                        \
+        cudaError_t err__ = cudaPeekAtLastError();                                              \
+        if (err__ != cudaSuccess) {                                                             \
+            tmdn_set_error("kernel launch failed at %s:%d: %s", __FILE__, __LINE__,             \
+                           cudaGetErrorString(err__));                                          \
+            return TMDN_ECUDA;                                                                  \
+        }                                                                                       \
+    } while (0)
+
+#define TMDN_TRY(call)                 \
+    do {                               \
+        int rc__ = (call);             \
+        if (rc__ != TMDN_OK) return rc__; \
+    } while (0)
+
+static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// Bump allocator over the caller's workspace.
+struct Arena {
+    char* base;
+    size_t cap, off;
+    bool ok;
+    Arena(void* b, size_t c) : base((char*)b), cap(c), off(0), ok(true) {}
+    template <typename T> T* get(size_t n) {
+        size_t bytes = align_up(n * sizeof(T));
+        size_t o = off;
+        off += bytes;
+        if (base && off > cap) ok = false;
+        return base ? (T*)(base + o) : (T*)nullptr;
+    }
+};
+
+// ------------------------------------------------------------------ device helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ int warp_incl_scan_i(int v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+
+// Activations (models/utils.py act_class_mapping) and their derivatives.
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+__device__ __forceinline__ float act_apply(int act, float x) {
+    switch (act) {
+        case TMDN_ACT_SILU: return x * sigmoidf_(x);
+        case TMDN_ACT_TANH: return tanhf(x);
+        case TMDN_ACT_SIGMOID: return sigmoidf_(x);
+        default: {  // shifted softplus, F.softplus threshold 20
+            float sp = x > 20.0f ? x : log1pf(expf(x));
+            return sp - 0.69314718055994530942f;
+        }
+    }
+}
+__device__ __forceinline__ float act_grad(int act, float x) {
+    switch (act) {
+        case TMDN_ACT_SILU: { float s = sigmoidf_(x); return s * (1.0f + x * (1.0f - s)); }
+        case TMDN_ACT_TANH: { float y = tanhf(x); return 1.0f - y * y; }
+        case TMDN_ACT_SIGMOID: { float s = sigmoidf_(x); return s * (1.0f - s); }
+        default: return sigmoidf_(x);
+    }
+}

@@ -1,0 +1,551 @@
+// neighbors.cu -- neighbor-pair search for sm_100a: tiled brute force (batch-aware) and cell list.
+//
+// Replaces torchmdnet/neighbors/neighbors_cuda_{brute,shared,cell}.cuh of the reference (same pair set,
+// same padded outputs, same found-count semantics; see include/tmdn.h).  Design differences:
+//   * brute/shared: one CTA per 128 target atoms streams 128-atom source tiles through shared memory and
+//     skips every tile whose batch-id range cannot overlap its own, so a batch of small molecules costs
+//     O(N * molecule size) instead of N^2/2 tests; no N < 32768 limit.
+//   * cell: counting sort into cells (integer atomics + scan, no radix sort), then ONE CTA per cell stages the
+//     27-cell neighbourhood in shared memory and emits the cell's pairs.
+//   * in both, pairs are appended with one global atomicAdd per (CTA, tile): hits are counted, block-scanned,
+//     a contiguous range is reserved, and the range is filled -- instead of one contended atomic per pair.
+//   * arithmetic is written with explicit round-to-nearest mul/add/sub (no FMA contraction) so deltas and
+//     distances are bit-identical to the CPU restatement in oracle/neighbors.py.
+#include "common.cuh"
+#include "scan.cuh"
+
+namespace {
+
+constexpr int NB_THREADS = 128;
+
+template <typename T> struct Box3 { T m[3][3]; };
+
+__device__ __forceinline__ float rn_mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double rn_mul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float rn_add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double rn_add(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float rn_sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ double rn_sub(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ float rn_div(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ double rn_div(double a, double b) { return __ddiv_rn(a, b); }
+__device__ __forceinline__ float sqrt_rn(float a) { return __fsqrt_rn(a); }
+__device__ __forceinline__ double sqrt_rn(double a) { return __dsqrt_rn(a); }
+__device__ __forceinline__ float round_(float a) { return roundf(a); }
+__device__ __forceinline__ double round_(double a) { return round(a); }
+__device__ __forceinline__ float floor_(float a) { return floorf(a); }
+__device__ __forceinline__ double floor_(double a) { return floor(a); }
+
+// neighbors/common.cuh:180-194 (triclinic minimum image, z -> y -> x)
+template <typename T> __device__ __forceinline__ void min_image_tric(T& dx, T& dy, T& dz, const Box3<T>& b) {
+    T s = round_(rn_div(dz, b.m[2][2]));
+    dx = rn_sub(dx, rn_mul(s, b.m[2][0]));
+    dy = rn_sub(dy, rn_mul(s, b.m[2][1]));
+    dz = rn_sub(dz, rn_mul(s, b.m[2][2]));
+    s = round_(rn_div(dy, b.m[1][1]));
+    dx = rn_sub(dx, rn_mul(s, b.m[1][0]));
+    dy = rn_sub(dy, rn_mul(s, b.m[1][1]));
+    dz = rn_sub(dz, rn_mul(s, b.m[1][2]));
+    s = round_(rn_div(dx, b.m[0][0]));
+    dx = rn_sub(dx, rn_mul(s, b.m[0][0]));
+    dy = rn_sub(dy, rn_mul(s, b.m[0][1]));
+    dz = rn_sub(dz, rn_mul(s, b.m[0][2]));
+}
+// neighbors/common.cuh:142-148 (rectangular minimum image)
+template <typename T> __device__ __forceinline__ T min_image_rect1(T d, T L) {
+    return rn_sub(d, rn_mul(floor_(rn_add(rn_div(d, L), T(0.5))), L));
+}
+template <typename T> __device__ __forceinline__ T dist2(T dx, T dy, T dz) {
+    return rn_add(rn_add(rn_mul(dx, dx), rn_mul(dy, dy)), rn_mul(dz, dz));
+}
+
+template <typename T> struct PairOut {
+    int32_t* nbr;   // [2, max_pairs]
+    T* deltas;      // [max_pairs, 3]
+    T* dist;        // [max_pairs]
+    int32_t* counter;
+    long long max_pairs;
+};
+
+template <typename T>
+__device__ __forceinline__ void write_pair(const PairOut<T>& o, long long slot, int a, int b, T dx, T dy, T dz, T d) {
+    if (slot < o.max_pairs) {
+        o.nbr[slot] = a;
+        o.nbr[o.max_pairs + slot] = b;
+        o.deltas[3 * slot + 0] = dx;
+        o.deltas[3 * slot + 1] = dy;
+        o.deltas[3 * slot + 2] = dz;
+        o.dist[slot] = d;
+    }
+}
+
+// Block-wide exclusive scan of one int per thread (NB_THREADS threads); returns the thread's offset and the total.
+__device__ __forceinline__ int block_excl_scan(int v, int& total, int* s_warp /* [NB_THREADS/32 + 1] */) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int incl = warp_incl_scan_i(v, lane);
+    __syncthreads();  // protect s_warp reuse
+    if (lane == 31) s_warp[w] = incl;
+    __syncthreads();
+    int woff = 0, tot = 0;
+#pragma unroll
+    for (int k = 0; k < NB_THREADS / 32; ++k) {
+        int x = s_warp[k];
+        if (k < w) woff += x;
+        tot += x;
+    }
+    total = tot;
+    return woff + incl - v;
+}
+
+// ------------------------------------------------------------------ batch range of every 128-atom tile
+__global__ void __launch_bounds__(NB_THREADS) tile_batch_range_kernel(const int64_t* __restrict__ batch, int n,
+                                                                      long long* __restrict__ tile_mm) {
+    __shared__ long long s_min[NB_THREADS / 32], s_max[NB_THREADS / 32];
+    const int i = blockIdx.x * NB_THREADS + threadIdx.x;
+    long long lo = LLONG_MAX, hi = LLONG_MIN;
+    if (i < n) lo = hi = batch[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        long long a = __shfl_xor_sync(0xffffffffu, lo, o), b = __shfl_xor_sync(0xffffffffu, hi, o);
+        lo = a < lo ? a : lo;
+        hi = b > hi ? b : hi;
+    }
+    if ((threadIdx.x & 31) == 0) { s_min[threadIdx.x >> 5] = lo; s_max[threadIdx.x >> 5] = hi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < NB_THREADS / 32; ++k) {
+            lo = s_min[k] < lo ? s_min[k] : lo;
+            hi = s_max[k] > hi ? s_max[k] : hi;
+        }
+        tile_mm[2 * blockIdx.x] = lo;
+        tile_mm[2 * blockIdx.x + 1] = hi;
+    }
+}
+
+// ------------------------------------------------------------------ tiled brute force
+template <typename T>
+__global__ void __launch_bounds__(NB_THREADS)
+nbr_brute_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, int n, Box3<T> box, int periodic, T lo2,
+                 T hi2, int loop, int transpose, PairOut<T> out, const long long* __restrict__ tile_mm) {
+    __shared__ T sx[NB_THREADS], sy[NB_THREADS], sz[NB_THREADS];
+    __shared__ long long sb[NB_THREADS];
+    __shared__ int s_warp[NB_THREADS / 32 + 1];
+    __shared__ int s_base;
+    const int t = threadIdx.x;
+    const int i = blockIdx.x * NB_THREADS + t;
+    const bool vi = i < n;
+    T xi = 0, yi = 0, zi = 0;
+    long long bi = 0;
+    if (vi) {
+        xi = pos[3 * (size_t)i];
+        yi = pos[3 * (size_t)i + 1];
+        zi = pos[3 * (size_t)i + 2];
+        bi = batch[i];
+    }
+    const long long bmin = tile_mm[2 * blockIdx.x], bmax = tile_mm[2 * blockIdx.x + 1];
+    const int per_hit = transpose ? 2 : 1;
+    for (int jt = 0; jt <= (int)blockIdx.x; ++jt) {
+        if (tile_mm[2 * jt + 1] < bmin || tile_mm[2 * jt] > bmax) continue;  // block-uniform
+        __syncthreads();
+        const int j0 = jt * NB_THREADS;
+        const int nj = min(NB_THREADS, n - j0);
+        if (t < nj) {
+            sx[t] = pos[3 * (size_t)(j0 + t)];
+            sy[t] = pos[3 * (size_t)(j0 + t) + 1];
+            sz[t] = pos[3 * (size_t)(j0 + t) + 2];
+            sb[t] = batch[j0 + t];
+        }
+        __syncthreads();
+        const int jend = vi ? min(nj, i - j0) : 0;  // only j < i
+        int cnt = 0;
+        for (int jj = 0; jj < jend; ++jj) {
+            if (sb[jj] != bi) continue;
+            T dx = rn_sub(xi, sx[jj]), dy = rn_sub(yi, sy[jj]), dz = rn_sub(zi, sz[jj]);
+            if (periodic) min_image_tric(dx, dy, dz, box);
+            const T d2 = dist2(dx, dy, dz);
+            cnt += (d2 < hi2 && d2 >= lo2) ? 1 : 0;
+        }
+        const int self = (loop && vi && jt == (int)blockIdx.x) ? 1 : 0;
+        const int items = cnt * per_hit + self;
+        int total;
+        const int off = block_excl_scan(items, total, s_warp);
+        if (total == 0) continue;  // block-uniform
+        if (t == 0) s_base = atomicAdd(out.counter, total);
+        __syncthreads();
+        long long slot = (long long)s_base + off;
+        for (int jj = 0; jj < jend; ++jj) {
+            if (sb[jj] != bi) continue;
+            T dx = rn_sub(xi, sx[jj]), dy = rn_sub(yi, sy[jj]), dz = rn_sub(zi, sz[jj]);
+            if (periodic) min_image_tric(dx, dy, dz, box);
+            const T d2 = dist2(dx, dy, dz);
+            if (d2 < hi2 && d2 >= lo2) {
+                const T d = sqrt_rn(d2);
+                write_pair(out, slot++, i, j0 + jj, dx, dy, dz, d);
+                if (transpose) write_pair(out, slot++, j0 + jj, i, -dx, -dy, -dz, d);
+            }
+        }
+        if (self) write_pair(out, slot, i, i, T(0), T(0), T(0), T(0));
+    }
+}
+
+// slots in [min(found, max_pairs), max_pairs) get the reference's padding values (common.cuh:70-76)
+template <typename T> __global__ void pad_fill_kernel(PairOut<T> out) {
+    const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= out.max_pairs) return;
+    const long long found = *out.counter;
+    if (s < found) return;
+    out.nbr[s] = -1;
+    out.nbr[out.max_pairs + s] = -1;
+    out.deltas[3 * s] = T(0);
+    out.deltas[3 * s + 1] = T(0);
+    out.deltas[3 * s + 2] = T(0);
+    out.dist[s] = T(0);
+}
+
+// ------------------------------------------------------------------ cell list
+template <typename T> struct CellGrid {
+    int n[3];       // cells per dimension (cell edge L/n >= cutoff*(1+1e-4))
+    int lo[3], hi[3];  // neighbour offsets to visit per dimension (unique cells only)
+    T L[3];
+    int ncells;
+};
+template <typename T> struct SortedAtom { T x, y, z; int idx; };
+
+template <typename T> __device__ __forceinline__ int cell_coord(T p, T L, int n) {
+    const T w = rn_sub(p, rn_mul(floor_(rn_add(rn_div(p, L), T(0.5))), L));  // wrapped to [-L/2, L/2)
+    int c = (int)floor_((w / L + T(0.5)) * T(n));
+    return c < 0 ? 0 : (c >= n ? n - 1 : c);
+}
+
+template <typename T>
+__global__ void cell_assign_kernel(const T* __restrict__ pos, int n, CellGrid<T> g, int* __restrict__ cell_cnt,
+                                   int* __restrict__ cell_of, int* __restrict__ slot_of) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int cx = cell_coord(pos[3 * (size_t)i], g.L[0], g.n[0]);
+    const int cy = cell_coord(pos[3 * (size_t)i + 1], g.L[1], g.n[1]);
+    const int cz = cell_coord(pos[3 * (size_t)i + 2], g.L[2], g.n[2]);
+    const int c = cx + g.n[0] * (cy + g.n[1] * cz);
+    cell_of[i] = c;
+    slot_of[i] = atomicAdd(&cell_cnt[c], 1);
+}
+
+template <typename T>
+__global__ void cell_scatter_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, int n,
+                                    const int* __restrict__ cell_start, const int* __restrict__ cell_of,
+                                    const int* __restrict__ slot_of, SortedAtom<T>* __restrict__ spos,
+                                    long long* __restrict__ sbatch) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int p = cell_start[cell_of[i]] + slot_of[i];
+    SortedAtom<T> a;
+    a.x = pos[3 * (size_t)i];
+    a.y = pos[3 * (size_t)i + 1];
+    a.z = pos[3 * (size_t)i + 2];
+    a.idx = i;
+    spos[p] = a;
+    sbatch[p] = batch[i];
+}
+
+constexpr int CELL_CAND = 1024;   // candidates staged per chunk
+constexpr int CELL_GROUP = 128;   // centre atoms processed per group
+
+template <typename T>
+__device__ __forceinline__ bool cell_hit(T xa, T ya, T za, long long ba, int ga, int ia, T xq, T yq, T zq, long long bq,
+                                         int gq, int iq, const CellGrid<T>& g, int periodic, T lo2, T hi2, int loop,
+                                         int transpose, T& dx, T& dy, T& dz, T& d2) {
+    if (gq == ga) {  // the atom itself: self loop regardless of the cutoffs (neighbors_cuda_cell.cuh:300-301)
+        dx = dy = dz = d2 = T(0);
+        return loop != 0;
+    }
+    if (bq != ba) return false;
+    if (!transpose && ia < iq) return false;  // half list keeps (larger index, smaller index)
+    dx = rn_sub(xa, xq);
+    dy = rn_sub(ya, yq);
+    dz = rn_sub(za, zq);
+    if (periodic) {
+        dx = min_image_rect1(dx, g.L[0]);
+        dy = min_image_rect1(dy, g.L[1]);
+        dz = min_image_rect1(dz, g.L[2]);
+    }
+    d2 = dist2(dx, dy, dz);
+    return d2 < hi2 && d2 >= lo2;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(NB_THREADS)
+cell_traverse_kernel(const SortedAtom<T>* __restrict__ spos, const long long* __restrict__ sbatch,
+                     const int* __restrict__ cell_start, CellGrid<T> g, int periodic, T lo2, T hi2, int loop,
+                     int transpose, PairOut<T> out) {
+    __shared__ T cx[CELL_CAND], cy[CELL_CAND], cz[CELL_CAND];
+    __shared__ long long cb[CELL_CAND];
+    __shared__ int cidx[CELL_CAND], cgl[CELL_CAND];
+    __shared__ int nb_start[27], nb_pref[28];
+    __shared__ int s_cnt[CELL_GROUP];
+    __shared__ int s_warp[NB_THREADS / 32 + 1];
+    __shared__ int s_base;
+    const int cell = blockIdx.x;
+    const int cs = cell_start[cell], ce = cell_start[cell + 1];
+    if (cs == ce) return;  // empty cell (block-uniform)
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int ccx = cell % g.n[0], ccy = (cell / g.n[0]) % g.n[1], ccz = cell / (g.n[0] * g.n[1]);
+    if (t == 0) {
+        int k = 0, run = 0;
+        for (int oz = g.lo[2]; oz <= g.hi[2]; ++oz)
+            for (int oy = g.lo[1]; oy <= g.hi[1]; ++oy)
+                for (int ox = g.lo[0]; ox <= g.hi[0]; ++ox) {
+                    const int x = (ccx + ox + g.n[0]) % g.n[0], y = (ccy + oy + g.n[1]) % g.n[1],
+                              z = (ccz + oz + g.n[2]) % g.n[2];
+                    const int c = x + g.n[0] * (y + g.n[1] * z);
+                    nb_start[k] = cell_start[c];
+                    nb_pref[k] = run;
+                    run += cell_start[c + 1] - cell_start[c];
+                    ++k;
+                }
+        for (; k < 27; ++k) { nb_start[k] = 0; nb_pref[k] = run; }
+        nb_pref[27] = run;
+    }
+    __syncthreads();
+    const int ncand = nb_pref[27];
+    for (int g0 = cs; g0 < ce; g0 += CELL_GROUP) {
+        const int gn = min(CELL_GROUP, ce - g0);
+        for (int k0 = 0; k0 < ncand; k0 += CELL_CAND) {
+            const int kn = min(CELL_CAND, ncand - k0);
+            __syncthreads();
+            for (int k = t; k < kn; k += NB_THREADS) {
+                const int kk = k0 + k;
+                int c = 0;
+                while (c < 26 && nb_pref[c + 1] <= kk) ++c;
+                const int gi = nb_start[c] + (kk - nb_pref[c]);
+                const SortedAtom<T> a = spos[gi];
+                cx[k] = a.x; cy[k] = a.y; cz[k] = a.z; cidx[k] = a.idx; cgl[k] = gi;
+                cb[k] = sbatch[gi];
+            }
+            for (int k = t; k < CELL_GROUP; k += NB_THREADS) s_cnt[k] = 0;
+            __syncthreads();
+            // count
+            for (int al = w; al < gn; al += NB_THREADS / 32) {
+                const int ga = g0 + al;
+                const SortedAtom<T> a = spos[ga];
+                const long long ba = sbatch[ga];
+                int cnt = 0;
+                for (int k = lane; k < kn; k += 32) {
+                    T dx, dy, dz, d2;
+                    cnt += cell_hit(a.x, a.y, a.z, ba, ga, a.idx, cx[k], cy[k], cz[k], cb[k], cgl[k], cidx[k], g,
+                                    periodic, lo2, hi2, loop, transpose, dx, dy, dz, d2) ? 1 : 0;
+                }
+                cnt = warp_sum_i(cnt);
+                if (lane == 0) s_cnt[al] = cnt;
+            }
+            __syncthreads();
+            int total;
+            const int mine = (t < CELL_GROUP) ? s_cnt[t] : 0;   // CELL_GROUP == NB_THREADS
+            const int off = block_excl_scan(mine, total, s_warp);
+            if (total == 0) continue;  // block-uniform
+            __syncthreads();
+            s_cnt[t] = off;
+            if (t == 0) s_base = atomicAdd(out.counter, total);
+            __syncthreads();
+            // fill
+            for (int al = w; al < gn; al += NB_THREADS / 32) {
+                const int ga = g0 + al;
+                const SortedAtom<T> a = spos[ga];
+                const long long ba = sbatch[ga];
+                long long slot = (long long)s_base + s_cnt[al];
+                for (int kb = 0; kb < kn; kb += 32) {
+                    const int k = kb + lane;
+                    T dx = 0, dy = 0, dz = 0, d2 = 0;
+                    bool hit = false;
+                    if (k < kn)
+                        hit = cell_hit(a.x, a.y, a.z, ba, ga, a.idx, cx[k], cy[k], cz[k], cb[k], cgl[k], cidx[k], g,
+                                       periodic, lo2, hi2, loop, transpose, dx, dy, dz, d2);
+                    const unsigned m = __ballot_sync(0xffffffffu, hit);
+                    if (hit) write_pair(out, slot + __popc(m & ((1u << lane) - 1u)), a.idx, cidx[k], dx, dy, dz, sqrt_rn(d2));
+                    slot += __popc(m);
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ backward (neighbors_cuda.cu:43-71)
+template <typename T>
+__global__ void nbr_backward_kernel(const int32_t* __restrict__ nbr, const T* __restrict__ deltas,
+                                    const T* __restrict__ dist, const T* __restrict__ gdel, const T* __restrict__ gdist,
+                                    long long max_pairs, T* __restrict__ gpos) {
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= max_pairs) return;
+    const T d = dist[e];
+    const int i = nbr[e], j = nbr[max_pairs + e];
+    if (d == T(0) || i < 0) return;
+    T g[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        T v = gdel ? gdel[3 * e + k] : T(0);
+        if (gdist) v += deltas[3 * e + k] / d * gdist[e];
+        g[k] = v;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        atomicAdd(&gpos[3 * (size_t)i + k], g[k]);
+        atomicAdd(&gpos[3 * (size_t)j + k], -g[k]);
+    }
+}
+
+template <typename T> bool make_grid(const double box[9], double cutoff, CellGrid<T>& g) {
+    long long nc = 1;
+    for (int k = 0; k < 3; ++k) {
+        const double L = box[4 * k];
+        int n = (int)(L / (cutoff * (1.0 + 1e-4)));
+        if (n < 1) n = 1;
+        if (n > 1024) return false;  // neighbors_cuda_cell.cuh:23-25
+        g.n[k] = n;
+        g.L[k] = (T)L;
+        if (n == 1) { g.lo[k] = 0; g.hi[k] = 0; }
+        else if (n == 2) { g.lo[k] = 0; g.hi[k] = 1; }
+        else { g.lo[k] = -1; g.hi[k] = 1; }
+        nc *= n;
+    }
+    g.ncells = (int)nc;
+    return true;
+}
+
+struct CellWs {
+    int *cell_cnt, *cell_start, *cell_of, *slot_of, *scan_tmp;
+    void* spos;
+    long long* sbatch;
+};
+template <typename T> void carve_cell(Arena& a, int64_t n, int ncells, CellWs& w) {
+    w.cell_cnt = a.get<int>(ncells + 1);
+    w.cell_start = a.get<int>(ncells + 1);
+    w.cell_of = a.get<int>(n);
+    w.slot_of = a.get<int>(n);
+    w.scan_tmp = a.get<int>(tmdn_scan_tmp_ints(ncells + 1));
+    w.spos = a.get<SortedAtom<T>>(n);
+    w.sbatch = a.get<long long>(n);
+}
+
+template <typename T>
+int neighbors_impl(int strategy, const T* pos, const int64_t* batch, int64_t n_atoms, const double box[9],
+                   int use_periodic, double cutoff_lower, double cutoff_upper, int loop, int include_transpose,
+                   int64_t max_pairs, int32_t* neighbors, T* deltas, T* distances, int32_t* num_found, void* workspace,
+                   size_t workspace_bytes, cudaStream_t stream) {
+    TMDN_CHECK_ARG(pos && batch && neighbors && deltas && distances && num_found, "neighbors: null pointer argument");
+    TMDN_CHECK_ARG(n_atoms > 0, "Expected the 1nd dimension size of \"positions\" to be more than 0");
+    TMDN_CHECK_ARG(n_atoms < (1LL << 31) - 256, "neighbors: too many atoms");
+    TMDN_CHECK_ARG(max_pairs > 0, "Expected \"max_num_neighbors\" to be positive");
+    TMDN_CHECK_ARG(max_pairs < (1LL << 31), "neighbors: max_num_pairs must fit int32");
+    TMDN_CHECK_ARG(cutoff_upper > 0, "Expected \"cutoff\" to be positive");
+    TMDN_CHECK_ARG(strategy == TMDN_BRUTE || strategy == TMDN_SHARED || strategy == TMDN_CELL, "Unknown kernel name");
+    TMDN_CHECK_ARG(!(use_periodic || strategy == TMDN_CELL) || box, "neighbors: box required");
+    const int n = (int)n_atoms;
+    PairOut<T> out{neighbors, deltas, distances, num_found, (long long)max_pairs};
+    const T lo = (T)cutoff_lower, hi = (T)cutoff_upper;
+    const T lo2 = lo * lo, hi2 = hi * hi;
+    TMDN_CUDA(cudaMemsetAsync(num_found, 0, sizeof(int32_t), stream));
+    Arena arena(workspace, workspace_bytes);
+    if (strategy == TMDN_CELL) {
+        TMDN_CHECK_ARG(box[1] == 0 && box[2] == 0 && box[3] == 0 && box[5] == 0 && box[6] == 0 && box[7] == 0,
+                       "Expected \"box_size\" to be diagonal");
+        TMDN_CHECK_ARG(box[0] > 0 && box[4] > 0 && box[8] > 0, "neighbors: box lengths must be positive");
+        CellGrid<T> g;
+        TMDN_CHECK_ARG(make_grid<T>(box, cutoff_upper, g), "Too many cells in one dimension. Maximum is 1024");
+        CellWs w;
+        carve_cell<T>(arena, n_atoms, g.ncells, w);
+        if (!arena.ok || !workspace) {
+            tmdn_set_error("neighbors(cell): workspace too small (%zu < %zu)", workspace_bytes, arena.off);
+            return TMDN_EWORKSPACE;
+        }
+        TMDN_CUDA(cudaMemsetAsync(w.cell_cnt, 0, sizeof(int) * (g.ncells + 1), stream));
+        const int blocks = (int)cdiv(n, 256);
+        cell_assign_kernel<T><<<blocks, 256, 0, stream>>>(pos, n, g, w.cell_cnt, w.cell_of, w.slot_of);
+        TMDN_LAUNCH_CHECK();
+        TMDN_TRY(tmdn_scan_exclusive_i32(w.cell_cnt, w.cell_start, g.ncells, w.scan_tmp, stream));
+        cell_scatter_kernel<T><<<blocks, 256, 0, stream>>>(pos, batch, n, w.cell_start, w.cell_of, w.slot_of,
+                                                           (SortedAtom<T>*)w.spos, w.sbatch);
+        TMDN_LAUNCH_CHECK();
+        cell_traverse_kernel<T><<<g.ncells, NB_THREADS, 0, stream>>>((const SortedAtom<T>*)w.spos, w.sbatch, w.cell_start,
+                                                                     g, use_periodic, lo2, hi2, loop, include_transpose,
+                                                                     out);
+        TMDN_LAUNCH_CHECK();
+    } else {
+        Box3<T> b;
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) b.m[r][c] = (use_periodic && box) ? (T)box[3 * r + c] : T(0);
+        const int ntiles = (int)cdiv(n, NB_THREADS);
+        long long* tile_mm = arena.get<long long>(2 * (size_t)ntiles);
+        if (!arena.ok || !workspace) {
+            tmdn_set_error("neighbors(brute): workspace too small (%zu < %zu)", workspace_bytes, arena.off);
+            return TMDN_EWORKSPACE;
+        }
+        tile_batch_range_kernel<<<ntiles, NB_THREADS, 0, stream>>>(batch, n, tile_mm);
+        TMDN_LAUNCH_CHECK();
+        nbr_brute_kernel<T><<<ntiles, NB_THREADS, 0, stream>>>(pos, batch, n, b, use_periodic, lo2, hi2, loop,
+                                                               include_transpose, out, tile_mm);
+        TMDN_LAUNCH_CHECK();
+    }
+    pad_fill_kernel<T><<<(unsigned)cdiv(max_pairs, 256), 256, 0, stream>>>(out);
+    TMDN_LAUNCH_CHECK();
+    return TMDN_OK;
+}
+
+template <typename T>
+int backward_impl(const int32_t* neighbors, const T* deltas, const T* distances, const T* grad_deltas,
+                  const T* grad_distances, int64_t max_pairs, int64_t n_atoms, T* grad_pos, cudaStream_t stream) {
+    TMDN_CHECK_ARG(neighbors && deltas && distances && grad_pos, "neighbors_backward: null pointer argument");
+    TMDN_CHECK_ARG(n_atoms > 0 && max_pairs >= 0, "neighbors_backward: bad sizes");
+    TMDN_CUDA(cudaMemsetAsync(grad_pos, 0, sizeof(T) * 3 * (size_t)n_atoms, stream));
+    if (max_pairs == 0 || (!grad_deltas && !grad_distances)) return TMDN_OK;
+    nbr_backward_kernel<T><<<(unsigned)cdiv(max_pairs, 256), 256, 0, stream>>>(
+        neighbors, deltas, distances, grad_deltas, grad_distances, (long long)max_pairs, grad_pos);
+    TMDN_LAUNCH_CHECK();
+    return TMDN_OK;
+}
+
+}  // namespace
+
+extern "C" size_t tmdn_neighbors_workspace_bytes(int strategy, int64_t n_atoms, const double box[9],
+                                                 double cutoff_upper, int elem_bytes) {
+    Arena a(nullptr, 0);
+    if (strategy == TMDN_CELL) {
+        if (!box || cutoff_upper <= 0) return 0;
+        CellGrid<double> g;
+        if (!make_grid<double>(box, cutoff_upper, g)) return 0;
+        CellWs w;
+        if (elem_bytes == 8) carve_cell<double>(a, n_atoms, g.ncells, w);
+        else carve_cell<float>(a, n_atoms, g.ncells, w);
+    } else {
+        a.get<long long>(2 * (size_t)cdiv(n_atoms, NB_THREADS));
+    }
+    return a.off + 256;
+}
+
+extern "C" int tmdn_neighbors_f32(int strategy, const float* pos, const int64_t* batch, int64_t n_atoms,
+                                  const double box[9], int use_periodic, double cutoff_lower, double cutoff_upper,
+                                  int loop, int include_transpose, int64_t max_pairs, int32_t* neighbors, float* deltas,
+                                  float* distances, int32_t* num_found, void* workspace, size_t workspace_bytes,
+                                  tmdn_stream_t stream) {
+    return neighbors_impl<float>(strategy, pos, batch, n_atoms, box, use_periodic, cutoff_lower, cutoff_upper, loop,
+                                 include_transpose, max_pairs, neighbors, deltas, distances, num_found, workspace,
+                                 workspace_bytes, (cudaStream_t)stream);
+}
+extern "C" int tmdn_neighbors_f64(int strategy, const double* pos, const int64_t* batch, int64_t n_atoms,
+                                  const double box[9], int use_periodic, double cutoff_lower, double cutoff_upper,
+                                  int loop, int include_transpose, int64_t max_pairs, int32_t* neighbors,
+                                  double* deltas, double* distances, int32_t* num_found, void* workspace,
+                                  size_t workspace_bytes, tmdn_stream_t stream) {
+    return neighbors_impl<double>(strategy, pos, batch, n_atoms, box, use_periodic, cutoff_lower, cutoff_upper, loop,
+                                  include_transpose, max_pairs, neighbors, deltas, distances, num_found, workspace,
+                                  workspace_bytes, (cudaStream_t)stream);
+}
+extern "C" int tmdn_neighbors_backward_f32(const int32_t* neighbors, const float* deltas, const float* distances,
+                                           const float* grad_deltas, const float* grad_distances, int64_t max_pairs,
+                                           int64_t n_atoms, float* grad_pos, tmdn_stream_t stream) {
+    return backward_impl<float>(neighbors, deltas, distances, grad_deltas, grad_distances, max_pairs, n_atoms, grad_pos,
+                                (cudaStream_t)stream);
+}
+extern "C" int tmdn_neighbors_backward_f64(const int32_t* neighbors, const double* deltas, const double* distances,
+                                           const double* grad_deltas, const double* grad_distances, int64_t max_pairs,
+                                           int64_t n_atoms, double* grad_pos, tmdn_stream_t stream) {
+    return backward_impl<double>(neighbors, deltas, distances, grad_deltas, grad_distances, max_pairs, n_atoms,
+                                 grad_pos, (cudaStream_t)stream);
+}

@@ -1,0 +1,121 @@
+// scan.cu -- exclusive prefix sum over int32 (cell offsets, CSR row pointers) + error-message storage.
+#include "common.cuh"
+#include "scan.cuh"
+
+static thread_local char g_err[512] = "";
+
+void tmdn_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* tmdn_last_error(void) { return g_err; }
+extern "C" int tmdn_version(void) { return TMDN_VERSION; }
+
+extern "C" int tmdn_is_stream_capturing(tmdn_stream_t stream) {
+    cudaStreamCaptureStatus st;
+    cudaError_t err = cudaStreamIsCapturing((cudaStream_t)stream, &st);
+    if (err != cudaSuccess) {
+        tmdn_set_error("cudaStreamIsCapturing: %s", cudaGetErrorString(err));
+        return -1;
+    }
+    return st == cudaStreamCaptureStatusActive ? 1 : 0;
+}
+
+namespace {
+constexpr int SCAN_THREADS = 1024;
+constexpr int SCAN_ITEMS = 4;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+// out[i] = sum_{k<i} in[k] within the tile (+ optional carry added later); tile total -> sums[blockIdx.x].
+// Elements with index >= n_in read as 0; outputs are written for index < n_out.
+__global__ void __launch_bounds__(SCAN_THREADS) scan_tile_kernel(const int* in, int* out,
+                                                                 int64_t n_in, int64_t n_out, int* __restrict__ sums) {
+    __shared__ int s_warp[32];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)t * SCAN_ITEMS;
+    int v[SCAN_ITEMS];
+    int tot = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        int64_t i = base + k;
+        v[k] = (i < n_in) ? in[i] : 0;
+        tot += v[k];
+    }
+    int incl = warp_incl_scan_i(tot, lane);
+    if (lane == 31) s_warp[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+        int x = s_warp[lane];
+        int xi = warp_incl_scan_i(x, lane);
+        s_warp[lane] = xi - x;  // exclusive warp offsets
+        if (lane == 31 && sums) sums[blockIdx.x] = xi;
+    }
+    __syncthreads();
+    int run = s_warp[w] + incl - tot;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        int64_t i = base + k;
+        if (i < n_out) out[i] = run;
+        run += v[k];
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_add_kernel(int* __restrict__ out, int64_t n_out,
+                                                                const int* __restrict__ carry) {
+    const int c = carry[blockIdx.x];
+    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        int64_t i = base + k;
+        if (i < n_out) out[i] += c;
+    }
+}
+}  // namespace
+
+size_t tmdn_scan_tmp_ints(int64_t n_out) {
+    size_t total = 0;
+    int64_t n = n_out;
+    while (n > SCAN_TILE) {
+        n = cdiv(n, SCAN_TILE);
+        total += align_up((size_t)n * sizeof(int)) / sizeof(int);
+    }
+    return total + 64;
+}
+
+// out[0..n_in] (n_in+1 entries) = exclusive scan of in[0..n_in); out[n_in] = total.  in may alias out.
+int tmdn_scan_exclusive_i32(const int* in, int* out, int64_t n_in, int* tmp, cudaStream_t stream) {
+    const int64_t n_out = n_in + 1;
+    const int64_t nb = cdiv(n_out, SCAN_TILE);
+    if (nb == 1) {
+        scan_tile_kernel<<<1, SCAN_THREADS, 0, stream>>>(in, out, n_in, n_out, nullptr);
+        TMDN_LAUNCH_CHECK();
+        return TMDN_OK;
+    }
+    int* sums = tmp;
+    int* next_tmp = tmp + align_up((size_t)nb * sizeof(int)) / sizeof(int);
+    scan_tile_kernel<<<(unsigned)nb, SCAN_THREADS, 0, stream>>>(in, out, n_in, n_out, sums);
+    TMDN_LAUNCH_CHECK();
+    // exclusive scan of the tile totals, in place (only nb entries are needed)
+    {
+        const int64_t nb2 = cdiv(nb, SCAN_TILE);
+        if (nb2 == 1) {
+            scan_tile_kernel<<<1, SCAN_THREADS, 0, stream>>>(sums, sums, nb, nb, nullptr);
+            TMDN_LAUNCH_CHECK();
+        } else {
+            int* sums2 = next_tmp;
+            scan_tile_kernel<<<(unsigned)nb2, SCAN_THREADS, 0, stream>>>(sums, sums, nb, nb, sums2);
+            TMDN_LAUNCH_CHECK();
+            TMDN_CHECK_ARG(nb2 <= SCAN_TILE, "scan: too many elements (%lld)", (long long)n_in);
+            scan_tile_kernel<<<1, SCAN_THREADS, 0, stream>>>(sums2, sums2, nb2, nb2, nullptr);
+            TMDN_LAUNCH_CHECK();
+            scan_add_kernel<<<(unsigned)nb2, SCAN_THREADS, 0, stream>>>(sums, nb, sums2);
+            TMDN_LAUNCH_CHECK();
+        }
+    }
+    scan_add_kernel<<<(unsigned)nb, SCAN_THREADS, 0, stream>>>(out, n_out, sums);
+    TMDN_LAUNCH_CHECK();
+    return TMDN_OK;
+}

@@ -1,0 +1,992 @@
+// tensornet.cu -- TensorNet energy + analytic forces for sm_100a (fp32).
+//
+// Replaces TensorNet.forward / TensorEmbedding / Interaction (torchmdnet/models/tensornet.py:200-410), the
+// Scalar head + reduce (output_modules.py:27-43,76-77) and the autograd force path of TorchMD_Net.forward
+// (models/model.py:286-298) of the reference.  The stage list, buffer names and every adjoint formula are the
+// ones of oracle/staged_tensornet.py, which is checked against torch.autograd on the CPU.
+//
+// Data layout in HBM: node tensors are [N, 9, H] fp32 in irreducible components (tensor3.cuh); a thread owns
+// one (atom, channel) pair, so all loads/stores of a warp are 128-byte coalesced rows and no per-edge tensor
+// ([E,H,3,3] in the reference) ever exists.  Edges are CSR by target atom, sorted by source; every sum over
+// neighbours is an in-order loop in registers (deterministic, no float atomics).  Because the edge set is
+// symmetric, the backward pass of a message-passing stage is evaluated inside the SAME row structure: row i
+// gathers the adjoints of its neighbours and also accumulates both directions' contribution to dE/dpos_i.
+#include "common.cuh"
+#include "gemm.cuh"
+#include "tensor3.cuh"
+#include "scan.cuh"
+#include <vector>
+#include <string>
+
+namespace {
+
+// ------------------------------------------------------------------ filters f_g(d) (g = I, A, S), f*C(d) and d/dd
+struct FilterView {
+    const float* F;     // [E,3,H]   (exact mode, CSR edge order)
+    const float* dF;    // [E,3,H]
+    const float4* tab;  // [n_int,3,H] cubic coefficients (table mode)
+    float inv_h;
+    int n_int;
+};
+
+template <bool TAB>
+__device__ __forceinline__ void filter_val(const FilterView& fv, size_t e, float d, int H, int h, float f[3]) {
+    if (TAB) {
+        float s = d * fv.inv_h;
+        int k = (int)s;
+        k = k > fv.n_int - 1 ? fv.n_int - 1 : k;
+        s -= (float)k;
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+            const float4 c = __ldg(&fv.tab[((size_t)k * 3 + g) * H + h]);
+            f[g] = c.x + s * (c.y + s * (c.z + s * c.w));
+        }
+    } else {
+#pragma unroll
+        for (int g = 0; g < 3; ++g) f[g] = fv.F[(e * 3 + g) * H + h];
+    }
+}
+template <bool TAB>
+__device__ __forceinline__ void filter_val_grad(const FilterView& fv, size_t e, float d, int H, int h, float f[3],
+                                                float df[3]) {
+    if (TAB) {
+        float s = d * fv.inv_h;
+        int k = (int)s;
+        k = k > fv.n_int - 1 ? fv.n_int - 1 : k;
+        s -= (float)k;
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+            const float4 c = __ldg(&fv.tab[((size_t)k * 3 + g) * H + h]);
+            f[g] = c.x + s * (c.y + s * (c.z + s * c.w));
+            df[g] = (c.y + s * (2.0f * c.z + 3.0f * s * c.w)) * fv.inv_h;
+        }
+    } else {
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+            f[g] = fv.F[(e * 3 + g) * H + h];
+            df[g] = fv.dF[(e * 3 + g) * H + h];
+        }
+    }
+}
+
+__device__ __forceinline__ void cutoff_fn(float d, float lo, float hi, float& c, float& dc) {
+    const float PI = 3.14159265358979323846f;
+    if (lo > 0.f) {  // models/utils.py:369-385
+        const float arg = PI * (2.0f * (d - lo) / (hi - lo) + 1.0f);
+        const float m = (d < hi && d > lo) ? 1.0f : 0.0f;
+        c = 0.5f * (cosf(arg) + 1.0f) * m;
+        dc = -0.5f * sinf(arg) * (2.0f * PI / (hi - lo)) * m;
+    } else {         // models/utils.py:386-390
+        const float m = d < hi ? 1.0f : 0.0f;
+        c = 0.5f * (cosf(d * PI / hi) + 1.0f) * m;
+        dc = -0.5f * sinf(d * PI / hi) * (PI / hi) * m;
+    }
+}
+
+// ------------------------------------------------------------------ small device utilities
+__device__ __forceinline__ void ld9(const float* __restrict__ p, size_t i, int H, int h, float x[9]) {
+    const float* q = p + i * 9 * H + h;
+#pragma unroll
+    for (int c = 0; c < 9; ++c) x[c] = q[(size_t)c * H];
+}
+__device__ __forceinline__ void st9(float* __restrict__ p, size_t i, int H, int h, const float x[9]) {
+    float* q = p + i * 9 * H + h;
+#pragma unroll
+    for (int c = 0; c < 9; ++c) q[(size_t)c * H] = x[c];
+}
+
+// Sum over the channels of one atom row.  Block = (H, APB); every thread of the block must call.
+template <int NV> __device__ __forceinline__ void row_reduce(float (&v)[NV], float* s_red) {
+    const int lane = threadIdx.x & 31, wr = threadIdx.x >> 5, nw = blockDim.x >> 5, a = threadIdx.y;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) v[k] = warp_sum(v[k]);
+    __syncthreads();
+    if (lane == 0)
+#pragma unroll
+        for (int k = 0; k < NV; ++k) s_red[(a * nw + wr) * NV + k] = v[k];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        float s = 0.f;
+        for (int w = 0; w < nw; ++w) s += s_red[(a * nw + w) * NV + k];
+        v[k] = s;
+    }
+}
+
+__global__ void tn_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ z32, int n, int max_z,
+                               const int32_t* __restrict__ num_found, long long max_edges, int32_t* __restrict__ status) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        const int f = *num_found;
+        status[0] = f;
+        status[1] = f > max_edges ? 1 : 0;
+    }
+    if (i >= n) return;
+    long long v = z[i];
+    if (v < 0 || v >= max_z) {
+        status[2] = 1;
+        v = 0;
+    }
+    z32[i] = (int)v;
+}
+
+// ------------------------------------------------------------------ exact-mode filter MLP helpers
+// R[e,k] = rbf_k(d_e), dR = d/dd  (models/utils.py:298-300, 339-344); rows e >= E are zero-filled.
+__global__ void tn_rbf_kernel(const float4* __restrict__ geom, const int* __restrict__ row_ptr, int n_atoms,
+                              long long e_cap, int K, int rbf_type, float lo, float hi, const float* __restrict__ p0,
+                              const float* __restrict__ p1, float* __restrict__ R, float* __restrict__ dR) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= e_cap * K) return;
+    const long long e = idx / K;
+    const int k = (int)(idx % K);
+    float r = 0.f, dr = 0.f;
+    if (e < row_ptr[n_atoms]) {
+        const float d = geom[e].w;
+        if (rbf_type == TMDN_RBF_EXPNORM) {
+            const float alpha = 5.0f / (hi - lo);
+            float c0, dc0;
+            cutoff_fn(d, 0.f, hi, c0, dc0);
+            const float u = expf(alpha * (lo - d));
+            const float mu = p0[k], beta = p1[k];
+            const float g = expf(-beta * (u - mu) * (u - mu));
+            r = c0 * g;
+            dr = dc0 * g + c0 * g * (2.0f * alpha) * beta * u * (u - mu);
+        } else {
+            const float off = p0[k], coeff = p1[k];
+            const float g = expf(coeff * (d - off) * (d - off));
+            r = g;
+            dr = 2.0f * coeff * (d - off) * g;
+        }
+    }
+    R[idx] = r;
+    dR[idx] = dr;
+}
+// F = a*C(d), dF = t*C(d) + a*C'(d)    (in place on a/t)
+__global__ void tn_filter_finalize_kernel(const float4* __restrict__ geom, long long e_cap, int n3, float lo, float hi,
+                                          float* __restrict__ a, float* __restrict__ t) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= e_cap * n3) return;
+    const long long e = idx / n3;
+    float c, dc;
+    cutoff_fn(geom[e].w, lo, hi, c, dc);
+    const float av = a[idx], tv = t[idx];
+    a[idx] = av * c;
+    t[idx] = tv * c + av * dc;
+}
+
+// ------------------------------------------------------------------ E1: embedding edge kernel (+ init LayerNorm)
+// ias_c[i,h] = sum_{e in row i} (P[z_i]+Q[z_j])[h] * W_g(c)(d_e)[h] * geom_c(u_e)      (tensornet.py:295-315)
+// nh = LayerNorm_H(||I+A+S||^2)                                                     (tensornet.py:316)
+template <bool TAB>
+__global__ void tn_embed_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                                  const float4* __restrict__ geom, const int* __restrict__ z32,
+                                  const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv, int N,
+                                  int H, float* __restrict__ ias, const float* __restrict__ ln_w,
+                                  const float* __restrict__ ln_b, float* __restrict__ nh) {
+    __shared__ float s_red[64];
+    const int h = threadIdx.x;
+    const int i = blockIdx.x * blockDim.y + threadIdx.y;
+    const bool valid = i < N;
+    float acc[9];
+#pragma unroll
+    for (int c = 0; c < 9; ++c) acc[c] = 0.f;
+    if (valid) {
+        const float pz = Pz[(size_t)z32[i] * H + h];
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0; e < r1; ++e) {
+            const int j = col[e];
+            const float4 g = geom[e];
+            float f[3];
+            filter_val<TAB>(fv, (size_t)e, g.w, H, h, f);
+            const float zv = pz + Qz[(size_t)z32[j] * H + h];
+            const float w1 = zv * f[0], w2 = zv * f[1], w3 = zv * f[2];
+            const float n2 = (g.x * g.x + g.y * g.y + g.z * g.z) * (1.0f / 3.0f);
+            acc[0] += w1;
+            acc[1] += w2 * g.x; acc[2] += w2 * g.y; acc[3] += w2 * g.z;
+            acc[4] += w3 * (g.x * g.x - n2);
+            acc[5] += w3 * (g.y * g.y - n2);
+            acc[6] += w3 * (g.x * g.y);
+            acc[7] += w3 * (g.x * g.z);
+            acc[8] += w3 * (g.y * g.z);
+        }
+        st9(ias, (size_t)i, H, h, acc);
+    }
+    const float q = t3_q(acc);
+    float s[1] = {q};
+    row_reduce<1>(s, s_red);
+    const float mean = s[0] / (float)H;
+    float v[1] = {(q - mean) * (q - mean)};
+    row_reduce<1>(v, s_red);
+    const float rstd = rsqrtf(v[0] / (float)H + 1e-5f);
+    if (valid) nh[(size_t)i * H + h] = (q - mean) * rstd * ln_w[h] + ln_b[h];
+}
+
+// ------------------------------------------------------------------ per-(atom,channel) elementwise stages
+__global__ void tn_normalize_fwd(const float* __restrict__ X, float* __restrict__ Xh, long long total, int H) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / H;
+    const int h = (int)(idx % H);
+    float x[9], xh[9];
+    ld9(X, i, H, h, x);
+    t3_normalize(x, xh);
+    st9(Xh, i, H, h, xh);
+}
+__global__ void tn_normalize_bwd(const float* __restrict__ X, float* __restrict__ dX, long long total, int H) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / H;
+    const int h = (int)(idx % H);
+    float x[9], dxh[9], dx[9];
+    ld9(X, i, H, h, x);
+    ld9(dX, i, H, h, dxh);
+    t3_normalize_bwd(x, dxh, dx);
+    st9(dX, i, H, h, dx);
+}
+// Xn = Xh + dX + (dX)^2 ; optionally also the next layer's normalised input   (tensornet.py:409, :385)
+__global__ void tn_update_fwd(const float* Xh, const float* __restrict__ dX, float* __restrict__ Xn,
+                              float* Xh_next, long long total, int H) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / H;
+    const int h = (int)(idx % H);
+    float xh[9], d[9], sq[9], xn[9];
+    ld9(Xh, i, H, h, xh);
+    ld9(dX, i, H, h, d);
+    t3_square(d, sq);
+#pragma unroll
+    for (int c = 0; c < 9; ++c) xn[c] = xh[c] + d[c] + sq[c];
+    st9(Xn, i, H, h, xn);
+    if (Xh_next) {
+        float nx[9];
+        t3_normalize(xn, nx);
+        st9(Xh_next, i, H, h, nx);
+    }
+}
+// ddX = dXn + adjoint of the square term
+__global__ void tn_update_bwd(const float* __restrict__ dXn, const float* __restrict__ dX, float* __restrict__ ddX,
+                              long long total, int H) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / H;
+    const int h = (int)(idx % H);
+    float g[9], d[9], dd[9];
+    ld9(dXn, i, H, h, g);
+    ld9(dX, i, H, h, d);
+    t3_square_bwd(d, g, dd);
+#pragma unroll
+    for (int c = 0; c < 9; ++c) dd[c] += g[c];
+    st9(ddX, i, H, h, dd);
+}
+// recompute tau = product(M,Y); dtau from dtauh; then dM -> dMout, dY(direct) -> dtauh buffer (in place)
+__global__ void tn_prod_bwd(const float* __restrict__ Y, const float* __restrict__ M, float* __restrict__ dtauh_dY,
+                            float* __restrict__ dMout, long long total, int H, int so3) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / H;
+    const int h = (int)(idx % H);
+    float y[9], m[9], tau[9], dth[9], dtau[9], dm[9], dy[9];
+    ld9(Y, i, H, h, y);
+    ld9(M, i, H, h, m);
+    ld9(dtauh_dY, i, H, h, dth);
+    t3_product(m, y, so3 != 0, tau);
+    t3_normalize_bwd(tau, dth, dtau);
+    t3_product_bwd(m, y, so3 != 0, dtau, dm, dy);
+    st9(dMout, i, H, h, dm);
+    st9(dtauh_dY, i, H, h, dy);
+}
+
+// ------------------------------------------------------------------ E2: interaction message passing (+ product)
+// M_c[i,h] = sum_{e in row i} f_g(c)(d_e)[h] * Y_c[j,h]  ;  tauh = normalise(decompose(M Y + Y M))   (tensornet.py:392-405)
+template <bool TAB>
+__global__ void tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                           const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H,
+                           int so3, float* __restrict__ M, float* __restrict__ tauh) {
+    const int h = threadIdx.x;
+    const int i = blockIdx.x * blockDim.y + threadIdx.y;
+    if (i >= N) return;
+    float m[9];
+#pragma unroll
+    for (int c = 0; c < 9; ++c) m[c] = 0.f;
+    const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+    for (int e = r0; e < r1; ++e) {
+        const int j = col[e];
+        const float d = geom[e].w;
+        float f[3], y[9];
+        filter_val<TAB>(fv, (size_t)e, d, H, h, f);
+        ld9(Y, (size_t)j, H, h, y);
+        m[0] += f[0] * y[0];
+        m[1] += f[1] * y[1]; m[2] += f[1] * y[2]; m[3] += f[1] * y[3];
+        m[4] += f[2] * y[4]; m[5] += f[2] * y[5]; m[6] += f[2] * y[6]; m[7] += f[2] * y[7]; m[8] += f[2] * y[8];
+    }
+    st9(M, (size_t)i, H, h, m);
+    float yi[9], tau[9], th[9];
+    ld9(Y, (size_t)i, H, h, yi);
+    t3_product(m, yi, so3 != 0, tau);
+    t3_normalize(tau, th);
+    st9(tauh, (size_t)i, H, h, th);
+}
+
+// E3: adjoint of the message passing, evaluated in row i of the symmetric edge set:
+//   dY_i += sum_e f_e * dM_j
+//   dE/dpos_i += u_e * sum_{h,c} f'_g(c)(d_e)[h] * (dM_c[i,h] Y_c[j,h] + dM_c[j,h] Y_c[i,h])
+template <bool TAB>
+__global__ void tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                           const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
+                           const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
+                           int H) {
+    __shared__ float s_red[128];
+    const int h = threadIdx.x;
+    const int i = blockIdx.x * blockDim.y + threadIdx.y;
+    const bool valid = i < N;
+    float gp[3] = {0.f, 0.f, 0.f};
+    if (valid) {
+        float yi[9], dmi[9], acc[9];
+        ld9(Y, (size_t)i, H, h, yi);
+        ld9(dM, (size_t)i, H, h, dmi);
+        ld9(dY, (size_t)i, H, h, acc);
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0; e < r1; ++e) {
+            const int j = col[e];
+            const float4 g = geom[e];
+            float f[3], df[3], yj[9], dmj[9];
+            filter_val_grad<TAB>(fv, (size_t)e, g.w, H, h, f, df);
+            ld9(Y, (size_t)j, H, h, yj);
+            ld9(dM, (size_t)j, H, h, dmj);
+            acc[0] += f[0] * dmj[0];
+            acc[1] += f[1] * dmj[1]; acc[2] += f[1] * dmj[2]; acc[3] += f[1] * dmj[3];
+            acc[4] += f[2] * dmj[4]; acc[5] += f[2] * dmj[5]; acc[6] += f[2] * dmj[6];
+            acc[7] += f[2] * dmj[7]; acc[8] += f[2] * dmj[8];
+            const float s0 = dmi[0] * yj[0] + dmj[0] * yi[0];
+            float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+            for (int c = 1; c < 4; ++c) s1 += dmi[c] * yj[c] + dmj[c] * yi[c];
+#pragma unroll
+            for (int c = 4; c < 9; ++c) s2 += dmi[c] * yj[c] + dmj[c] * yi[c];
+            const float ge = df[0] * s0 + df[1] * s1 + df[2] * s2;
+            gp[0] += g.x * ge; gp[1] += g.y * ge; gp[2] += g.z * ge;
+        }
+        st9(dY, (size_t)i, H, h, acc);
+    }
+    row_reduce<3>(gp, s_red);
+    if (valid && h == 0) {
+        gpos[3 * (size_t)i] += gp[0];
+        gpos[3 * (size_t)i + 1] += gp[1];
+        gpos[3 * (size_t)i + 2] += gp[2];
+    }
+}
+
+// ------------------------------------------------------------------ output norm / head
+// x = [||I||^2, ||A||^2, ||S||^2] -> LayerNorm(3H)      (tensornet.py:230-232)
+__global__ void tn_out_norm_fwd(const float* __restrict__ X, const float* __restrict__ ln_w,
+                                const float* __restrict__ ln_b, float* __restrict__ xl, float* __restrict__ stat,
+                                int N, int H) {
+    __shared__ float s_red[64];
+    const int h = threadIdx.x;
+    const int i = blockIdx.x * blockDim.y + threadIdx.y;
+    const bool valid = i < N;
+    float q[3] = {0.f, 0.f, 0.f};
+    if (valid) {
+        float x[9];
+        ld9(X, (size_t)i, H, h, x);
+        t3_qparts(x, q[0], q[1], q[2]);
+    }
+    float s[1] = {q[0] + q[1] + q[2]};
+    row_reduce<1>(s, s_red);
+    const float mean = s[0] / (3.0f * H);
+    float v[1] = {(q[0] - mean) * (q[0] - mean) + (q[1] - mean) * (q[1] - mean) + (q[2] - mean) * (q[2] - mean)};
+    row_reduce<1>(v, s_red);
+    const float rstd = rsqrtf(v[0] / (3.0f * H) + 1e-5f);
+    if (valid) {
+#pragma unroll
+        for (int g = 0; g < 3; ++g)
+            xl[(size_t)i * 3 * H + g * H + h] = (q[g] - mean) * rstd * ln_w[g * H + h] + ln_b[g * H + h];
+        if (h == 0) { stat[2 * (size_t)i] = mean; stat[2 * (size_t)i + 1] = rstd; }
+    }
+}
+__global__ void tn_out_norm_bwd(const float* __restrict__ X, const float* __restrict__ ln_w,
+                                const float* __restrict__ stat, const float* __restrict__ dxl,
+                                float* __restrict__ dXa, int N, int H) {
+    __shared__ float s_red[64];
+    const int h = threadIdx.x;
+    const int i = blockIdx.x * blockDim.y + threadIdx.y;
+    const bool valid = i < N;
+    float x[9], q[3] = {0.f, 0.f, 0.f}, xh[3] = {0.f, 0.f, 0.f}, dg[3] = {0.f, 0.f, 0.f};
+    float mean = 0.f, rstd = 0.f;
+#pragma unroll
+    for (int c = 0; c < 9; ++c) x[c] = 0.f;
+    if (valid) {
+        ld9(X, (size_t)i, H, h, x);
+        t3_qparts(x, q[0], q[1], q[2]);
+        mean = stat[2 * (size_t)i];
+        rstd = stat[2 * (size_t)i + 1];
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+            xh[g] = (q[g] - mean) * rstd;
+            dg[g] = dxl[(size_t)i * 3 * H + g * H + h] * ln_w[g * H + h];
+        }
+    }
+    float r[2] = {dg[0] + dg[1] + dg[2], dg[0] * xh[0] + dg[1] * xh[1] + dg[2] * xh[2]};
+    row_reduce<2>(r, s_red);
+    if (!valid) return;
+    const float m1 = r[0] / (3.0f * H), m2 = r[1] / (3.0f * H);
+    float dq[3];
+#pragma unroll
+    for (int g = 0; g < 3; ++g) dq[g] = (dg[g] - m1 - xh[g] * m2) * rstd;
+    float gq[9], out[9];
+    t3_qgrad(x, gq);
+    out[0] = gq[0] * dq[0];
+#pragma unroll
+    for (int c = 1; c < 4; ++c) out[c] = gq[c] * dq[1];
+#pragma unroll
+    for (int c = 4; c < 9; ++c) out[c] = gq[c] * dq[2];
+    st9(dXa, (size_t)i, H, h, out);
+}
+// e_i = (w2 . a4_i + b2) * std      (output_modules.py:76-77, model.py:262-263); one warp per atom
+__global__ void tn_head_energy(const float* __restrict__ a4, const float* __restrict__ w2,
+                               const float* __restrict__ b2, float stdv, float* __restrict__ e_atom, int N, int Hh) {
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (i >= N) return;
+    float s = 0.f;
+    for (int k = lane; k < Hh; k += 32) s += a4[(size_t)i * Hh + k] * w2[k];
+    s = warp_sum(s);
+    if (lane == 0) e_atom[i] = (s + b2[0]) * stdv;
+}
+// y[m] = sum_{i: batch[i]==m} e_i + mean  (batch sorted); one CTA per molecule, fixed-order tree => deterministic
+__global__ void __launch_bounds__(128) tn_mol_reduce(const float* __restrict__ e_atom, const int64_t* __restrict__ batch,
+                                                     int N, float mean, float* __restrict__ energy) {
+    __shared__ float s_part[128];
+    const long long m = blockIdx.x;
+    int lo = 0, hi = N;  // first index with batch >= m
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m) lo = mid + 1; else hi = mid; }
+    const int a = lo;
+    hi = N;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m + 1) lo = mid + 1; else hi = mid; }
+    const int b = lo;
+    float s = 0.f;
+    for (int i = a + threadIdx.x; i < b; i += 128) s += e_atom[i];
+    s_part[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 64; o > 0; o >>= 1) {
+        if (threadIdx.x < o) s_part[threadIdx.x] += s_part[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) energy[m] = s_part[0] + mean;
+}
+// d4[i,n] = std * w2[n] * act'(h4[i,n])
+__global__ void tn_head_seed_bwd(const float* __restrict__ h4, const float* __restrict__ w2, float stdv, int act,
+                                 float* __restrict__ d4, long long total, int Hh) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    d4[idx] = stdv * w2[idx % Hh] * act_grad(act, h4[idx]);
+}
+
+// ------------------------------------------------------------------ embedding backward (node part)
+// X0_c = fias_g(c) * iasm_c :  dh2[g*H+h] = (sum_{c in g} dX_c iasm_c) * act'(h2) ;  diasm_c = dX_c * fias_g  (in place)
+__global__ void tn_embed_scale_bwd(float* __restrict__ dXa, const float* __restrict__ iasm,
+                                   const float* __restrict__ fias, const float* __restrict__ h2, int act,
+                                   float* __restrict__ dh2, long long total, int H) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / H;
+    const int h = (int)(idx % H);
+    float dx[9], im[9], f[3];
+    ld9(dXa, i, H, h, dx);
+    ld9(iasm, i, H, h, im);
+#pragma unroll
+    for (int g = 0; g < 3; ++g) f[g] = fias[i * 3 * H + g * H + h];
+    float s0 = dx[0] * im[0], s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int c = 1; c < 4; ++c) s1 += dx[c] * im[c];
+#pragma unroll
+    for (int c = 4; c < 9; ++c) s2 += dx[c] * im[c];
+    dh2[i * 3 * H + h] = s0 * act_grad(act, h2[i * 3 * H + h]);
+    dh2[i * 3 * H + H + h] = s1 * act_grad(act, h2[i * 3 * H + H + h]);
+    dh2[i * 3 * H + 2 * H + h] = s2 * act_grad(act, h2[i * 3 * H + 2 * H + h]);
+    dx[0] *= f[0];
+#pragma unroll
+    for (int c = 1; c < 4; ++c) dx[c] *= f[1];
+#pragma unroll
+    for (int c = 4; c < 9; ++c) dx[c] *= f[2];
+    st9(dXa, i, H, h, dx);
+}
+// Dias_c += LayerNorm^T(dnh)[h] * dq/dias_c
+__global__ void tn_embed_norm_bwd(const float* __restrict__ ias, const float* __restrict__ ln_w,
+                                  const float* __restrict__ dnh, float* __restrict__ Dias, int N, int H) {
+    __shared__ float s_red[64];
+    const int h = threadIdx.x;
+    const int i = blockIdx.x * blockDim.y + threadIdx.y;
+    const bool valid = i < N;
+    float x[9];
+#pragma unroll
+    for (int c = 0; c < 9; ++c) x[c] = 0.f;
+    if (valid) ld9(ias, (size_t)i, H, h, x);
+    const float q = t3_q(x);
+    float s[1] = {q};
+    row_reduce<1>(s, s_red);
+    const float mean = s[0] / (float)H;
+    float v[1] = {(q - mean) * (q - mean)};
+    row_reduce<1>(v, s_red);
+    const float rstd = rsqrtf(v[0] / (float)H + 1e-5f);
+    const float xh = (q - mean) * rstd;
+    const float dg = valid ? dnh[(size_t)i * H + h] * ln_w[h] : 0.f;
+    float r[2] = {dg, dg * xh};
+    row_reduce<2>(r, s_red);
+    if (!valid) return;
+    const float dq = (dg - r[0] / (float)H - xh * r[1] / (float)H) * rstd;
+    float gq[9], d[9];
+    t3_qgrad(x, gq);
+    ld9(Dias, (size_t)i, H, h, d);
+#pragma unroll
+    for (int c = 0; c < 9; ++c) d[c] += dq * gq[c];
+    st9(Dias, (size_t)i, H, h, d);
+}
+
+// E4: adjoint of the embedding edge kernel w.r.t. positions, both directions of every edge inside row i.
+//   forces[i] = -(gpos[i] + sum_e [ u (gd_e + gd_e') + perp(gu_e) - perp(gu_e') ])
+template <bool TAB>
+__global__ void tn_embed_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                                  const float4* __restrict__ geom, const int* __restrict__ z32,
+                                  const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv,
+                                  const float* __restrict__ Dias, const float* __restrict__ gpos,
+                                  float* __restrict__ forces, int N, int H) {
+    __shared__ float s_red[128];
+    const int h = threadIdx.x;
+    const int i = blockIdx.x * blockDim.y + threadIdx.y;
+    const bool valid = i < N;
+    float gp[3] = {0.f, 0.f, 0.f};
+    if (valid) {
+        float di[9];
+        ld9(Dias, (size_t)i, H, h, di);
+        const int zi = z32[i];
+        const float pzi = Pz[(size_t)zi * H + h], qzi = Qz[(size_t)zi * H + h];
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0; e < r1; ++e) {
+            const int j = col[e];
+            if (j == i) continue;  // self loop: d = 0, u = 0, no position dependence
+            const float4 g = geom[e];
+            float f[3], df[3], dj[9];
+            filter_val_grad<TAB>(fv, (size_t)e, g.w, H, h, f, df);
+            ld9(Dias, (size_t)j, H, h, dj);
+            const int zj = z32[j];
+            const float ze = pzi + Qz[(size_t)zj * H + h];        // Z of edge (i <- j)
+            const float zr = Pz[(size_t)zj * H + h] + qzi;        // Z of the reverse edge (j <- i)
+            const float ux = g.x, uy = g.y, uz = g.z;
+            const float n2 = (ux * ux + uy * uy + uz * uz) * (1.0f / 3.0f);
+            const float g4 = ux * ux - n2, g5 = uy * uy - n2, g6 = ux * uy, g7 = ux * uz, g8 = uy * uz;
+            // a_c = Dias_c[i]*Z_e ; r_c = Dias_c[j]*Z_r ; geom of the reverse edge: odd components flip sign
+            float a[9], r[9];
+#pragma unroll
+            for (int c = 0; c < 9; ++c) { a[c] = di[c] * ze; r[c] = dj[c] * zr; }
+            const float gd = df[0] * (a[0] + r[0]) +
+                             df[1] * ((a[1] - r[1]) * ux + (a[2] - r[2]) * uy + (a[3] - r[3]) * uz) +
+                             df[2] * ((a[4] + r[4]) * g4 + (a[5] + r[5]) * g5 + (a[6] + r[6]) * g6 +
+                                      (a[7] + r[7]) * g7 + (a[8] + r[8]) * g8);
+            // dL/du of edge e minus dL/du' of the reverse edge (d geom_c/du is even for c=1..3, odd for c=4..8):
+            //   gu_e - gu_r  with gu_r evaluated at u' = -u  ==  sum_c (a_c*f - r_c*f*sign_c) dgeom_c(u)
+            float w[9];
+#pragma unroll
+            for (int c = 1; c < 4; ++c) w[c] = (a[c] - r[c]) * f[1];
+#pragma unroll
+            for (int c = 4; c < 9; ++c) w[c] = (a[c] + r[c]) * f[2];
+            const float tw = 2.0f / 3.0f;
+            const float gx = w[1] + w[4] * (2.0f * ux - tw * ux) - w[5] * tw * ux + w[6] * uy + w[7] * uz;
+            const float gy = w[2] - w[4] * tw * uy + w[5] * (2.0f * uy - tw * uy) + w[6] * ux + w[8] * uz;
+            const float gz = w[3] - (w[4] + w[5]) * tw * uz + w[7] * ux + w[8] * uy;
+            const float dot = gx * ux + gy * uy + gz * uz;
+            const float inv_d = 1.0f / g.w;
+            gp[0] += ux * gd + (gx - dot * ux) * inv_d;
+            gp[1] += uy * gd + (gy - dot * uy) * inv_d;
+            gp[2] += uz * gd + (gz - dot * uz) * inv_d;
+        }
+    }
+    row_reduce<3>(gp, s_red);
+    if (valid && h == 0) {
+        forces[3 * (size_t)i] = -(gpos[3 * (size_t)i] + gp[0]);
+        forces[3 * (size_t)i + 1] = -(gpos[3 * (size_t)i + 1] + gp[1]);
+        forces[3 * (size_t)i + 2] = -(gpos[3 * (size_t)i + 2] + gp[2]);
+    }
+}
+
+// ------------------------------------------------------------------ workspace
+struct TnWs {
+    // graph
+    int32_t *nbr, *num_found, *row_ptr, *col;
+    float *deltas, *dist, *geom;
+    int* z32;
+    void *nbr_ws, *csr_ws;
+    size_t nbr_ws_bytes, csr_ws_bytes;
+    // exact-mode filters
+    float *R, *dR, *fh[3], *fa[3], *ft[3];
+    float *F[TMDN_MAX_LAYERS + 1], *dF[TMDN_MAX_LAYERS + 1];
+    // forward node buffers
+    float *ias, *iasm, *nh, *h1, *a1, *h2, *fias, *X[TMDN_MAX_LAYERS + 1], *Xh, *Y[TMDN_MAX_LAYERS],
+        *M[TMDN_MAX_LAYERS], *tauh, *dX[TMDN_MAX_LAYERS], *xl, *stat, *h3, *a3, *h4, *a4, *e_atom;
+    // backward
+    float *dXa, *dB, *dC, *d4, *d3, *dxl, *dh2, *dh1, *dnh, *gpos;
+};
+struct WsEntry { std::string name; size_t off, bytes; };
+
+template <typename T> T* carve(Arena& a, std::vector<WsEntry>* names, const char* name, size_t n) {
+    const size_t o = a.off;
+    T* p = a.get<T>(n);
+    if (names) names->push_back({name, o, n * sizeof(T)});
+    return p;
+}
+
+int carve_tn(Arena& a, const tmdn_tensornet_model* m, int64_t N, int64_t P, int64_t n_mol, TnWs& w,
+             std::vector<WsEntry>* names, const double* box, int strategy, double cutoff) {
+    const size_t H = m->hidden, K = m->num_rbf, L = m->num_layers;
+    const size_t n = (size_t)N, nh9 = n * 9 * H;
+    char buf[32];
+    w.nbr = carve<int32_t>(a, names, "nbr", 2 * (size_t)P);
+    w.deltas = carve<float>(a, names, "deltas", 3 * (size_t)P);
+    w.dist = carve<float>(a, names, "dist", (size_t)P);
+    w.num_found = carve<int32_t>(a, names, "num_found", 4);
+    w.row_ptr = carve<int32_t>(a, names, "row_ptr", n + 1);
+    w.col = carve<int32_t>(a, names, "col", (size_t)P);
+    w.geom = carve<float>(a, names, "geom", 4 * (size_t)P);
+    w.z32 = carve<int>(a, names, "z32", n);
+    double dummy_box[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    w.nbr_ws_bytes = tmdn_neighbors_workspace_bytes(strategy, N, box ? box : dummy_box, cutoff, 4);
+    if (strategy == TMDN_CELL && w.nbr_ws_bytes == 0) return TMDN_EINVAL;
+    w.nbr_ws = carve<char>(a, names, "nbr_ws", w.nbr_ws_bytes);
+    w.csr_ws_bytes = tmdn_csr_workspace_bytes(N, P);
+    w.csr_ws = carve<char>(a, names, "csr_ws", w.csr_ws_bytes);
+    if (m->filter_mode == TMDN_FILTER_EXACT) {
+        const size_t e = (size_t)P;
+        w.R = carve<float>(a, names, "R", e * K);
+        w.dR = carve<float>(a, names, "dR", e * K);
+        const size_t dims[3] = {H, 2 * H, 3 * H};
+        for (int k = 0; k < 2; ++k) {
+            snprintf(buf, sizeof buf, "fh%d", k); w.fh[k] = carve<float>(a, names, buf, e * dims[k]);
+            snprintf(buf, sizeof buf, "fa%d", k); w.fa[k] = carve<float>(a, names, buf, e * dims[k]);
+            snprintf(buf, sizeof buf, "ft%d", k); w.ft[k] = carve<float>(a, names, buf, e * dims[k]);
+        }
+        w.fh[2] = carve<float>(a, names, "fh2", e * 3 * H);
+        for (size_t s = 0; s <= L; ++s) {
+            snprintf(buf, sizeof buf, "F%zu", s); w.F[s] = carve<float>(a, names, buf, e * 3 * H);
+            snprintf(buf, sizeof buf, "dF%zu", s); w.dF[s] = carve<float>(a, names, buf, e * 3 * H);
+        }
+    }
+    w.ias = carve<float>(a, names, "ias", nh9);
+    w.iasm = carve<float>(a, names, "iasm", nh9);
+    w.nh = carve<float>(a, names, "nh", n * H);
+    w.h1 = carve<float>(a, names, "h1", n * 2 * H);
+    w.a1 = carve<float>(a, names, "a1", n * 2 * H);
+    w.h2 = carve<float>(a, names, "h2", n * 3 * H);
+    w.fias = carve<float>(a, names, "fias", n * 3 * H);
+    for (size_t l = 0; l <= L; ++l) { snprintf(buf, sizeof buf, "X%zu", l); w.X[l] = carve<float>(a, names, buf, nh9); }
+    w.Xh = carve<float>(a, names, "Xh", nh9);
+    for (size_t l = 0; l < L; ++l) {
+        snprintf(buf, sizeof buf, "Y%zu", l); w.Y[l] = carve<float>(a, names, buf, nh9);
+        snprintf(buf, sizeof buf, "M%zu", l); w.M[l] = carve<float>(a, names, buf, nh9);
+        snprintf(buf, sizeof buf, "dX%zu", l); w.dX[l] = carve<float>(a, names, buf, nh9);
+    }
+    w.tauh = carve<float>(a, names, "tauh", nh9);
+    w.xl = carve<float>(a, names, "xl", n * 3 * H);
+    w.stat = carve<float>(a, names, "stat", n * 2);
+    w.h3 = carve<float>(a, names, "h3", n * H);
+    w.a3 = carve<float>(a, names, "a3", n * H);
+    w.h4 = carve<float>(a, names, "h4", n * (H / 2));
+    w.a4 = carve<float>(a, names, "a4", n * (H / 2));
+    w.e_atom = carve<float>(a, names, "e_atom", n);
+    w.dXa = carve<float>(a, names, "dXa", nh9);
+    w.dB = carve<float>(a, names, "Dias", nh9);   // last content: dE/d ias (staged name "Dias")
+    w.dC = carve<float>(a, names, "dC", nh9);
+    w.d4 = carve<float>(a, names, "d4", n * (H / 2));
+    w.d3 = carve<float>(a, names, "d3", n * H);
+    w.dxl = carve<float>(a, names, "dxl", n * 3 * H);
+    w.dh2 = carve<float>(a, names, "dh2", n * 3 * H);
+    w.dh1 = carve<float>(a, names, "dh1", n * 2 * H);
+    w.dnh = carve<float>(a, names, "dnh", n * H);
+    w.gpos = carve<float>(a, names, "gpos", n * 3);
+    (void)n_mol;
+    return TMDN_OK;
+}
+
+int check_model(const tmdn_tensornet_model* m) {
+    TMDN_CHECK_ARG(m, "tensornet: null model");
+    TMDN_CHECK_ARG(m->hidden >= 32 && m->hidden <= 1024 && m->hidden % 32 == 0,
+                   "tensornet: hidden_channels must be a multiple of 32 in [32,1024] (got %d)", m->hidden);
+    TMDN_CHECK_ARG(m->num_layers >= 0 && m->num_layers <= TMDN_MAX_LAYERS, "tensornet: num_layers out of range");
+    TMDN_CHECK_ARG(m->num_rbf > 0 && m->max_z > 0, "tensornet: bad num_rbf/max_z");
+    TMDN_CHECK_ARG(m->cutoff_upper > m->cutoff_lower && m->cutoff_lower >= 0, "tensornet: bad cutoffs");
+    TMDN_CHECK_ARG(m->filter_mode == TMDN_FILTER_EXACT || m->filter_mode == TMDN_FILTER_TABLE,
+                   "tensornet: bad filter_mode");
+    if (m->filter_mode == TMDN_FILTER_TABLE) {
+        TMDN_CHECK_ARG(m->emb_filter.table && m->emb_filter.n_int > 0, "tensornet: missing embedding filter table");
+        for (int l = 0; l < m->num_layers; ++l)
+            TMDN_CHECK_ARG(m->layer_filter[l].table && m->layer_filter[l].n_int > 0,
+                           "tensornet: missing filter table of layer %d", l);
+    }
+    return TMDN_OK;
+}
+
+// grouped channel mix over the rows of an [N,9,H] tensor: problem g uses weight Wg[g] on components of group g
+GemmBatch mix_batch(const float* A, float* C, const float* const Wg[3], int N, int H) {
+    GemmBatch b;
+    memset(&b, 0, sizeof(b));
+    const int gs[3] = {1, 3, 5}, c0[3] = {0, 1, 4};
+    for (int g = 0; g < 3; ++g) {
+        GemmP p = gemm_desc(A, H, Wg[g], nullptr, C, H, N * gs[g], H, H);
+        p.gs = gs[g]; p.c0 = c0[g]; p.rpa = 9; p.g = g;
+        b.p[g] = p;
+    }
+    b.n = 3;
+    return b;
+}
+
+// exact-mode evaluation of one filter set on all (capacity) edges -> F, dF [E,3,H]
+int eval_filter_exact(const tmdn_tensornet_model* m, const tmdn_filter_set& fs, const TnWs& w, int64_t N, int64_t P,
+                      float* F, float* dF, cudaStream_t stream) {
+    const int K = m->num_rbf;
+    const float* a = w.R;
+    const float* t = w.dR;
+    for (int k = 0; k < fs.n_layers; ++k) {
+        const int in = fs.dims[k], out = fs.dims[k + 1];
+        const bool last = k == fs.n_layers - 1;
+        const bool has_act = !last || fs.final_act;
+        float* ha = last ? F : w.fa[k];
+        float* tt = last ? dF : w.ft[k];
+        if (has_act) {
+            GemmP p = gemm_desc(a, in, fs.w[k], fs.b[k], ha, out, (int)P, out, in);
+            p.C2 = w.fh[k]; p.act = m->activation;
+            TMDN_TRY(gemm1(EPI_ACT, p, stream));
+            GemmP q = gemm_desc(t, in, fs.w[k], nullptr, tt, out, (int)P, out, in);
+            q.aux = w.fh[k]; q.ldaux = out; q.act = m->activation;
+            TMDN_TRY(gemm1(EPI_MULGRAD, q, stream));
+        } else {
+            GemmP p = gemm_desc(a, in, fs.w[k], fs.b[k], ha, out, (int)P, out, in);
+            TMDN_TRY(gemm1(EPI_NONE, p, stream));
+            GemmP q = gemm_desc(t, in, fs.w[k], nullptr, tt, out, (int)P, out, in);
+            TMDN_TRY(gemm1(EPI_NONE, q, stream));
+        }
+        a = ha;
+        t = tt;
+    }
+    (void)K; (void)N;
+    const long long tot = (long long)P * fs.dims[fs.n_layers];
+    tn_filter_finalize_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>((const float4*)w.geom, (long long)P,
+                                                                            fs.dims[fs.n_layers], m->cutoff_lower,
+                                                                            m->cutoff_upper, F, dF);
+    TMDN_LAUNCH_CHECK();
+    return TMDN_OK;
+}
+
+FilterView make_view(const tmdn_tensornet_model* m, const tmdn_filter_set& fs, const float* F, const float* dF) {
+    FilterView v;
+    v.F = F; v.dF = dF;
+    v.tab = (const float4*)fs.table;
+    v.n_int = fs.n_int;
+    v.inv_h = fs.n_int > 0 ? (float)((double)fs.n_int / (double)m->cutoff_upper) : 0.f;
+    return v;
+}
+
+}  // namespace
+
+extern "C" size_t tmdn_tensornet_workspace_bytes(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,
+                                                 int64_t n_mol) {
+    if (check_model(m) != TMDN_OK || n_atoms <= 0 || max_edges <= 0) return 0;
+    Arena a(nullptr, 0);
+    TnWs w;
+    // the cell strategy needs box-dependent scratch; size for the worst case of both strategies with a box of
+    // up to 2^22 cells (callers pass the same box at run time; see tmdn_tensornet_energy_forces)
+    carve_tn(a, m, n_atoms, max_edges, n_mol, w, nullptr, nullptr, TMDN_BRUTE, m->cutoff_upper);
+    const size_t cell_extra = (size_t)n_atoms * 40 + ((size_t)1 << 22) * 12 + 4096;
+    return a.off + cell_extra + 256;
+}
+
+extern "C" int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,
+                                               int64_t n_mol, const char* name, size_t* offset, size_t* bytes) {
+    TMDN_TRY(check_model(m));
+    TMDN_CHECK_ARG(name && offset && bytes, "lookup: null argument");
+    Arena a(nullptr, 0);
+    TnWs w;
+    std::vector<WsEntry> names;
+    carve_tn(a, m, n_atoms, max_edges, n_mol, w, &names, nullptr, TMDN_BRUTE, m->cutoff_upper);
+    for (const auto& e : names)
+        if (e.name == name) {
+            *offset = e.off;
+            *bytes = e.bytes;
+            return TMDN_OK;
+        }
+    tmdn_set_error("lookup: unknown buffer '%s'", name);
+    return TMDN_EINVAL;
+}
+
+extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const int64_t* z, const float* pos,
+                                            const int64_t* batch, int64_t n_atoms, int64_t n_mol, const double box[9],
+                                            int use_periodic, int strategy, int64_t max_edges, float* energy,
+                                            float* forces, int32_t* status, void* workspace, size_t workspace_bytes,
+                                            tmdn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    TMDN_TRY(check_model(m));
+    TMDN_CHECK_ARG(z && pos && batch && energy && status && workspace, "tensornet: null pointer argument");
+    TMDN_CHECK_ARG(n_atoms > 0 && n_mol > 0 && max_edges > 0, "tensornet: bad sizes");
+    TMDN_CHECK_ARG((long long)n_atoms * 9 * m->hidden < (1LL << 40), "tensornet: system too large");
+    TMDN_CHECK_ARG(max_edges < (1LL << 31) && n_atoms < (1LL << 31) / 16, "tensornet: sizes exceed int32 indexing");
+    const int N = (int)n_atoms, H = m->hidden, L = m->num_layers, act = m->activation;
+    const bool tab = m->filter_mode == TMDN_FILTER_TABLE;
+    const int64_t P = max_edges;
+
+    // The brute-strategy layout is a prefix of every layout (cell scratch lives in the tail reserve).
+    Arena arena(workspace, workspace_bytes);
+    TnWs w;
+    TMDN_TRY(carve_tn(arena, m, n_atoms, P, n_mol, w, nullptr, nullptr, TMDN_BRUTE, m->cutoff_upper));
+    void* nbr_ws = w.nbr_ws;
+    size_t nbr_ws_bytes = w.nbr_ws_bytes;
+    if (strategy == TMDN_CELL) {
+        TMDN_CHECK_ARG(box, "tensornet: the cell strategy needs a box");
+        nbr_ws_bytes = tmdn_neighbors_workspace_bytes(TMDN_CELL, n_atoms, box, m->cutoff_upper, 4);
+        TMDN_CHECK_ARG(nbr_ws_bytes > 0, "tensornet: bad box for the cell strategy");
+        nbr_ws = arena.get<char>(nbr_ws_bytes);
+    }
+    if (!arena.ok) {
+        tmdn_set_error("tensornet: workspace too small (%zu < %zu)", workspace_bytes, arena.off);
+        return TMDN_EWORKSPACE;
+    }
+
+    // ---- graph: pairs (incl. transposes and self loops) -> CSR by target = row 0 (tensornet.py:313-315)
+    TMDN_TRY(tmdn_neighbors_f32(strategy, pos, batch, n_atoms, box, use_periodic, m->cutoff_lower, m->cutoff_upper, 1, 1,
+                                P, w.nbr, w.deltas, w.dist, w.num_found, nbr_ws, nbr_ws_bytes, stream_));
+    TMDN_TRY(tmdn_csr_from_pairs(w.nbr, w.deltas, w.dist, w.num_found, P, n_atoms, 0, w.row_ptr, w.col, w.geom,
+                                 w.csr_ws, w.csr_ws_bytes, stream_));
+    TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
+    tn_prep_kernel<<<(unsigned)cdiv(N, 256), 256, 0, stream>>>(z, w.z32, N, m->max_z, w.num_found, (long long)P, status);
+    TMDN_LAUNCH_CHECK();
+
+    const float4* geom = (const float4*)w.geom;
+    const int apb = H >= 128 ? 1 : 128 / H;
+    const dim3 rblock(H, apb);
+    const unsigned rgrid = (unsigned)cdiv(N, apb);
+    const long long NH = (long long)N * H;
+    const unsigned egrid = (unsigned)cdiv(NH, 256);
+
+    // ---- filters (exact mode): rbf once, then one MLP chain per filter set
+    FilterView fv_emb, fv_layer[TMDN_MAX_LAYERS];
+    if (!tab) {
+        const long long tot = (long long)P * m->num_rbf;
+        tn_rbf_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(geom, w.row_ptr, N, (long long)P, m->num_rbf,
+                                                                    m->rbf_type, m->cutoff_lower, m->cutoff_upper,
+                                                                    m->rbf_p0, m->rbf_p1, w.R, w.dR);
+        TMDN_LAUNCH_CHECK();
+        TMDN_TRY(eval_filter_exact(m, m->emb_filter, w, n_atoms, P, w.F[0], w.dF[0], stream));
+        for (int l = 0; l < L; ++l)
+            TMDN_TRY(eval_filter_exact(m, m->layer_filter[l], w, n_atoms, P, w.F[l + 1], w.dF[l + 1], stream));
+    }
+    fv_emb = make_view(m, m->emb_filter, w.F[0], w.dF[0]);
+    for (int l = 0; l < L; ++l) fv_layer[l] = make_view(m, m->layer_filter[l], w.F[l + 1], w.dF[l + 1]);
+
+    // ---- E1 + embedding node stage
+    if (tab)
+        tn_embed_edge_fwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H,
+                                                              w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+    else
+        tn_embed_edge_fwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H,
+                                                               w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+    TMDN_LAUNCH_CHECK();
+    {
+        GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
+        p.C2 = w.h1; p.act = act;
+        TMDN_TRY(gemm1(EPI_ACT, p, stream));
+        GemmP q = gemm_desc(w.a1, 2 * H, m->emb_w2, m->emb_b2, w.fias, 3 * H, N, 3 * H, 2 * H);
+        q.C2 = w.h2; q.act = act;
+        TMDN_TRY(gemm1(EPI_ACT, q, stream));
+        GemmBatch b = mix_batch(w.ias, w.X[0], m->emb_mix, N, H);
+        for (int g = 0; g < 3; ++g) { b.p[g].C2 = w.iasm; b.p[g].aux = w.fias; }
+        TMDN_TRY(gemm_launch(EPI_SCALE3, b, stream));
+    }
+    // ---- interaction layers
+    if (L > 0) {
+        tn_normalize_fwd<<<egrid, 256, 0, stream>>>(w.X[0], w.Xh, NH, H);
+        TMDN_LAUNCH_CHECK();
+    }
+    for (int l = 0; l < L; ++l) {
+        TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.Xh, w.Y[l], m->layer_mix[l], N, H), stream));
+        if (tab)
+            tn_msg_fwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N, H, m->so3,
+                                                           w.M[l], w.tauh);
+        else
+            tn_msg_fwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N, H, m->so3,
+                                                            w.M[l], w.tauh);
+        TMDN_LAUNCH_CHECK();
+        TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
+        // Xh is both input (residual) and, for the next layer, output: safe because each thread reads its own
+        // (atom, channel) column before writing it.
+        tn_update_fwd<<<egrid, 256, 0, stream>>>(w.Xh, w.dX[l], w.X[l + 1], l + 1 < L ? w.Xh : nullptr, NH, H);
+        TMDN_LAUNCH_CHECK();
+    }
+    // ---- output norm, linear, head, reduce
+    tn_out_norm_fwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, m->out_ln_b, w.xl, w.stat, N, H);
+    TMDN_LAUNCH_CHECK();
+    {
+        GemmP p = gemm_desc(w.xl, 3 * H, m->out_w, m->out_b, w.a3, H, N, H, 3 * H);
+        p.C2 = w.h3; p.act = act;
+        TMDN_TRY(gemm1(EPI_ACT, p, stream));
+        GemmP q = gemm_desc(w.a3, H, m->head_w1, m->head_b1, w.a4, H / 2, N, H / 2, H);
+        q.C2 = w.h4; q.act = act;
+        TMDN_TRY(gemm1(EPI_ACT, q, stream));
+    }
+    tn_head_energy<<<(unsigned)cdiv(N, 4), 128, 0, stream>>>(w.a4, m->head_w2, m->head_b2, m->std, w.e_atom, N, H / 2);
+    TMDN_LAUNCH_CHECK();
+    tn_mol_reduce<<<(unsigned)n_mol, 128, 0, stream>>>(w.e_atom, batch, N, m->mean, energy);
+    TMDN_LAUNCH_CHECK();
+    if (!forces) return TMDN_OK;
+
+    // ================================================================= backward (dE_total/dpos)
+    TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
+    {
+        const long long tot = (long long)N * (H / 2);
+        tn_head_seed_bwd<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(w.h4, m->head_w2, m->std, act, w.d4, tot, H / 2);
+        TMDN_LAUNCH_CHECK();
+        GemmP p = gemm_desc(w.d4, H / 2, m->head_w1T, nullptr, w.d3, H, N, H, H / 2);
+        p.aux = w.h3; p.ldaux = H; p.act = act;
+        TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
+        GemmP q = gemm_desc(w.d3, H, m->out_wT, nullptr, w.dxl, 3 * H, N, 3 * H, H);
+        TMDN_TRY(gemm1(EPI_NONE, q, stream));
+    }
+    tn_out_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
+    TMDN_LAUNCH_CHECK();
+    for (int l = L - 1; l >= 0; --l) {
+        tn_update_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.dX[l], w.dB, NH, H);
+        TMDN_LAUNCH_CHECK();
+        TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.dB, w.dC, m->layer_mixT[l] + 3, N, H), stream));
+        tn_prod_bwd<<<egrid, 256, 0, stream>>>(w.Y[l], w.M[l], w.dC, w.dB, NH, H, m->so3);
+        TMDN_LAUNCH_CHECK();
+        if (tab)
+            tn_msg_bwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
+                                                           w.gpos, N, H);
+        else
+            tn_msg_bwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
+                                                            w.gpos, N, H);
+        TMDN_LAUNCH_CHECK();
+        GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
+        for (int g = 0; g < 3; ++g) b.p[g].accumulate = 1;
+        TMDN_TRY(gemm_launch(EPI_NONE, b, stream));
+        tn_normalize_bwd<<<egrid, 256, 0, stream>>>(w.X[l], w.dXa, NH, H);
+        TMDN_LAUNCH_CHECK();
+    }
+    // embedding node stage backward
+    tn_embed_scale_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.iasm, w.fias, w.h2, act, w.dh2, NH, H);
+    TMDN_LAUNCH_CHECK();
+    {
+        GemmP p = gemm_desc(w.dh2, 3 * H, m->emb_w2T, nullptr, w.dh1, 2 * H, N, 2 * H, 3 * H);
+        p.aux = w.h1; p.ldaux = 2 * H; p.act = act;
+        TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
+        GemmP q = gemm_desc(w.dh1, 2 * H, m->emb_w1T, nullptr, w.dnh, H, N, H, 2 * H);
+        TMDN_TRY(gemm1(EPI_NONE, q, stream));
+        TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.dXa, w.dB, m->emb_mixT, N, H), stream));
+    }
+    tn_embed_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.ias, m->emb_ln_w, w.dnh, w.dB, N, H);
+    TMDN_LAUNCH_CHECK();
+    if (tab)
+        tn_embed_edge_bwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
+                                                              w.gpos, forces, N, H);
+    else
+        tn_embed_edge_bwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
+                                                               w.gpos, forces, N, H);
+    TMDN_LAUNCH_CHECK();
+    return TMDN_OK;
+}

@@ -1,0 +1,362 @@
+// torch_shim.cpp -- thin torch C++ extension over the C ABI of libtmdn.so (include/tmdn.h).
+//
+// Registers, with the reference's namespace / name / schema (torchmdnet/neighbors/neighbors.cpp:3-5):
+//     torchmdnet_neighbors::get_neighbor_pairs            (AutogradCUDA; CPU tensors are refused: no CPU fallback)
+// the reference's stream-capture probe as a compiled op (torchmdnet/models/utils.py:533-555):
+//     torch_extension::is_stream_capturing
+// and the fused model entry points:
+//     torchmdnet_b200::csr_from_pairs, ::tensornet_create, ::tensornet_energy_forces, ::tensornet_debug_lookup
+// Nothing here computes: tensors are validated, outputs/workspaces are taken from the caching allocator, and the
+// C ABI is called on the current stream.
+#include <ATen/ATen.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+#include <torch/autograd.h>
+#include <torch/library.h>
+
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/tmdn.h"
+
+using at::Tensor;
+using torch::autograd::AutogradContext;
+using torch::autograd::tensor_list;
+
+namespace {
+
+#define TMDN_CALL(expr)                                                              \
+    do {                                                                             \
+        int rc__ = (expr);                                                           \
+        TORCH_CHECK(rc__ == TMDN_OK, tmdn_last_error(), " (tmdn status ", rc__, ")"); \
+    } while (0)
+
+tmdn_stream_t cur_stream() { return (tmdn_stream_t)c10::cuda::getCurrentCUDAStream().stream(); }
+
+int strategy_id(const std::string& s) {
+    if (s == "brute") return TMDN_BRUTE;
+    if (s == "shared") return TMDN_SHARED;
+    if (s == "cell") return TMDN_CELL;
+    throw std::runtime_error("Unknown kernel name");  // neighbors_cuda.cu:17
+}
+
+// box_vectors: CPU tensor [3,3] (or empty when not periodic) -> 9 host doubles. Returns false if absent.
+bool read_box(const Tensor& box, double out[9]) {
+    if (!box.defined() || box.numel() == 0) return false;
+    TORCH_CHECK(box.device().is_cpu(), "Expected \"box_vectors\" to be on CPU");
+    TORCH_CHECK(box.dim() == 2 && box.size(0) == 3 && box.size(1) == 3, "Expected \"box_vectors\" to have shape (3, 3)");
+    const Tensor b = box.to(at::kDouble).contiguous();
+    const double* p = b.data_ptr<double>();
+    for (int i = 0; i < 9; ++i) out[i] = p[i];
+    return true;
+}
+
+void check_input(const Tensor& positions, const Tensor& batch) {  // neighbors/common.cuh:118-131
+    TORCH_CHECK(positions.is_cuda(),
+                "torchmdnet_neighbors::get_neighbor_pairs: this build runs on CUDA (sm_100a) only; got a ",
+                positions.device().type(), " tensor and there is no CPU fallback");
+    TORCH_CHECK(positions.dim() == 2, "Expected \"positions\" to have two dimensions");
+    TORCH_CHECK(positions.size(0) > 0, "Expected the 1nd dimension size of \"positions\" to be more than 0");
+    TORCH_CHECK(positions.size(1) == 3, "Expected the 2nd dimension size of \"positions\" to be 3");
+    TORCH_CHECK(positions.is_contiguous(), "Expected \"positions\" to be contiguous");
+    TORCH_CHECK(batch.dim() == 1, "Expected \"batch\" to have one dimension");
+    TORCH_CHECK(batch.size(0) == positions.size(0),
+                "Expected the 1st dimension size of \"batch\" to be the same as the 1st dimension size of \"positions\"");
+    TORCH_CHECK(batch.is_contiguous(), "Expected \"batch\" to be contiguous");
+    TORCH_CHECK(batch.dtype() == at::kLong, "Expected \"batch\" to be of type torch::kLong");
+    TORCH_CHECK(batch.device() == positions.device(), "Expected \"batch\" on the device of \"positions\"");
+    TORCH_CHECK(positions.scalar_type() == at::kFloat || positions.scalar_type() == at::kDouble,
+                "Expected \"positions\" to be float32 or float64");
+}
+
+std::vector<Tensor> neighbors_forward(const std::string& strategy, const Tensor& positions, const Tensor& batch,
+                                      const Tensor& box_vectors, bool use_periodic, double lo, double hi,
+                                      int64_t max_pairs, bool loop, bool include_transpose) {
+    check_input(positions, batch);
+    TORCH_CHECK(max_pairs > 0, "Expected \"max_num_neighbors\" to be positive");
+    TORCH_CHECK(hi > 0, "Expected \"cutoff\" to be positive");
+    const int sid = strategy_id(strategy);
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    TORCH_CHECK(have_box || !(use_periodic || sid == TMDN_CELL), "Expected \"box_vectors\" to have two dimensions");
+    const c10::cuda::CUDAGuard guard(positions.device());
+    const int64_t n = positions.size(0);
+    const auto opts = positions.options();
+    Tensor neighbors = at::empty({2, max_pairs}, opts.dtype(at::kInt));
+    Tensor deltas = at::empty({max_pairs, 3}, opts);
+    Tensor distances = at::empty({max_pairs}, opts);
+    Tensor num = at::empty({1}, opts.dtype(at::kInt));
+    const bool f64 = positions.scalar_type() == at::kDouble;
+    const size_t ws_bytes = tmdn_neighbors_workspace_bytes(sid, n, have_box ? box : nullptr, hi, f64 ? 8 : 4);
+    TORCH_CHECK(ws_bytes > 0, sid == TMDN_CELL ? "Too many cells in one dimension. Maximum is 1024" : "workspace");
+    Tensor ws = at::empty({(int64_t)ws_bytes}, opts.dtype(at::kByte));
+    if (f64)
+        TMDN_CALL(tmdn_neighbors_f64(sid, positions.data_ptr<double>(), batch.data_ptr<int64_t>(), n,
+                                     have_box ? box : nullptr, use_periodic, lo, hi, loop, include_transpose, max_pairs,
+                                     neighbors.data_ptr<int32_t>(), deltas.data_ptr<double>(),
+                                     distances.data_ptr<double>(), num.data_ptr<int32_t>(), ws.data_ptr(), ws_bytes,
+                                     cur_stream()));
+    else
+        TMDN_CALL(tmdn_neighbors_f32(sid, positions.data_ptr<float>(), batch.data_ptr<int64_t>(), n,
+                                     have_box ? box : nullptr, use_periodic, lo, hi, loop, include_transpose, max_pairs,
+                                     neighbors.data_ptr<int32_t>(), deltas.data_ptr<float>(),
+                                     distances.data_ptr<float>(), num.data_ptr<int32_t>(), ws.data_ptr(), ws_bytes,
+                                     cur_stream()));
+    return {neighbors, deltas, distances, num};
+}
+
+// dL/dpos from dL/d(deltas), dL/d(distances).  First-order use (inference, forces) runs the CUDA kernel; when the
+// backward itself must be differentiable (create_graph=True, training on forces) it is composed of ATen ops.
+Tensor neighbors_backward(const Tensor& neighbors, const Tensor& deltas, const Tensor& distances, Tensor grad_deltas,
+                          Tensor grad_distances, int64_t num_atoms) {
+    const c10::cuda::CUDAGuard guard(deltas.device());
+    if (at::GradMode::is_enabled()) {
+        const Tensor keep = (distances != 0).to(deltas.dtype());
+        const Tensor safe_d = distances + (1 - keep);
+        Tensor g = at::zeros_like(deltas);
+        if (grad_deltas.defined()) g = g + grad_deltas * keep.unsqueeze(1);
+        if (grad_distances.defined()) g = g + deltas / safe_d.unsqueeze(1) * (grad_distances * keep).unsqueeze(1);
+        const Tensor idx = neighbors.to(at::kLong).clamp_min(0);
+        Tensor gp = at::zeros({num_atoms, 3}, deltas.options());
+        gp = gp.index_add(0, idx[0], g).index_add(0, idx[1], -g);
+        return gp;
+    }
+    Tensor gp = at::empty({num_atoms, 3}, deltas.options());
+    const int64_t P = distances.size(0);
+    if (grad_deltas.defined()) grad_deltas = grad_deltas.contiguous();
+    if (grad_distances.defined()) grad_distances = grad_distances.contiguous();
+    if (deltas.scalar_type() == at::kDouble)
+        TMDN_CALL(tmdn_neighbors_backward_f64(neighbors.data_ptr<int32_t>(), deltas.data_ptr<double>(),
+                                              distances.data_ptr<double>(),
+                                              grad_deltas.defined() ? grad_deltas.data_ptr<double>() : nullptr,
+                                              grad_distances.defined() ? grad_distances.data_ptr<double>() : nullptr, P,
+                                              num_atoms, gp.data_ptr<double>(), cur_stream()));
+    else
+        TMDN_CALL(tmdn_neighbors_backward_f32(neighbors.data_ptr<int32_t>(), deltas.data_ptr<float>(),
+                                              distances.data_ptr<float>(),
+                                              grad_deltas.defined() ? grad_deltas.data_ptr<float>() : nullptr,
+                                              grad_distances.defined() ? grad_distances.data_ptr<float>() : nullptr, P,
+                                              num_atoms, gp.data_ptr<float>(), cur_stream()));
+    return gp;
+}
+
+class NeighborFn : public torch::autograd::Function<NeighborFn> {
+public:
+    static tensor_list forward(AutogradContext* ctx, const std::string& strategy, const Tensor& positions,
+                               const Tensor& batch, const Tensor& box_vectors, bool use_periodic, double lo, double hi,
+                               int64_t max_pairs, bool loop, bool include_transpose) {
+        auto out = neighbors_forward(strategy, positions, batch, box_vectors, use_periodic, lo, hi, max_pairs, loop,
+                                     include_transpose);
+        ctx->save_for_backward({out[0], out[1], out[2]});
+        ctx->saved_data["num_atoms"] = positions.size(0);
+        ctx->mark_non_differentiable({out[0], out[3]});
+        return out;
+    }
+    static tensor_list backward(AutogradContext* ctx, tensor_list grads) {
+        const auto saved = ctx->get_saved_variables();
+        const int64_t n = ctx->saved_data["num_atoms"].toInt();
+        Tensor gp = neighbors_backward(saved[0], saved[1], saved[2], grads[1], grads[2], n);
+        Tensor none;
+        return {none, gp, none, none, none, none, none, none, none, none};
+    }
+};
+
+std::tuple<Tensor, Tensor, Tensor, Tensor> get_neighbor_pairs_autograd(
+    const std::string& strategy, const Tensor& positions, const Tensor& batch, const Tensor& box_vectors,
+    bool use_periodic, const at::Scalar& cutoff_lower, const at::Scalar& cutoff_upper, const at::Scalar& max_num_pairs,
+    bool loop, bool include_transpose) {
+    auto r = NeighborFn::apply(strategy, positions, batch, box_vectors, use_periodic, cutoff_lower.toDouble(),
+                               cutoff_upper.toDouble(), max_num_pairs.toLong(), loop, include_transpose);
+    return std::make_tuple(r[0], r[1], r[2], r[3]);
+}
+
+std::tuple<Tensor, Tensor, Tensor, Tensor> get_neighbor_pairs_cpu(const std::string&, const Tensor& positions,
+                                                                  const Tensor&, const Tensor&, bool, const at::Scalar&,
+                                                                  const at::Scalar&, const at::Scalar&, bool, bool) {
+    TORCH_CHECK(false, "torchmdnet_neighbors::get_neighbor_pairs: this build runs on CUDA (sm_100a) only; got a ",
+                positions.device().type(), " tensor and there is no CPU fallback");
+    return {};
+}
+
+bool is_stream_capturing() {
+    const int r = tmdn_is_stream_capturing(cur_stream());
+    TORCH_CHECK(r >= 0, tmdn_last_error());
+    return r == 1;
+}
+
+std::tuple<Tensor, Tensor, Tensor> csr_from_pairs(const Tensor& neighbors, const Tensor& deltas,
+                                                  const Tensor& distances, const Tensor& num_found, int64_t n_atoms,
+                                                  int64_t target_row) {
+    TORCH_CHECK(neighbors.is_cuda() && neighbors.scalar_type() == at::kInt && neighbors.is_contiguous(),
+                "csr_from_pairs: neighbors must be a contiguous CUDA int32 tensor");
+    TORCH_CHECK(deltas.scalar_type() == at::kFloat && distances.scalar_type() == at::kFloat,
+                "csr_from_pairs: fp32 only");
+    const c10::cuda::CUDAGuard guard(neighbors.device());
+    const int64_t P = neighbors.size(1);
+    const auto opts = neighbors.options();
+    Tensor row_ptr = at::empty({n_atoms + 1}, opts);
+    Tensor col = at::full({P}, -1, opts);
+    Tensor geom = at::zeros({P, 4}, deltas.options());
+    const size_t ws_bytes = tmdn_csr_workspace_bytes(n_atoms, P);
+    Tensor ws = at::empty({(int64_t)ws_bytes}, opts.dtype(at::kByte));
+    TMDN_CALL(tmdn_csr_from_pairs(neighbors.data_ptr<int32_t>(), deltas.contiguous().data_ptr<float>(),
+                                  distances.contiguous().data_ptr<float>(), num_found.data_ptr<int32_t>(), P, n_atoms,
+                                  (int)target_row, row_ptr.data_ptr<int32_t>(), col.data_ptr<int32_t>(),
+                                  geom.data_ptr<float>(), ws.data_ptr(), ws_bytes, cur_stream()));
+    return std::make_tuple(row_ptr, col, geom);
+}
+
+// ------------------------------------------------------------------ TensorNet model handles
+struct TnHandle {
+    tmdn_tensornet_model m;
+    std::vector<Tensor> keep;  // keeps the packed weights alive
+};
+std::mutex g_mu;
+std::unordered_map<int64_t, std::shared_ptr<TnHandle>> g_tn;
+int64_t g_next = 1;
+
+const float* fptr(const Tensor& t) {
+    if (!t.defined() || t.numel() == 0) return nullptr;
+    TORCH_CHECK(t.is_cuda() && t.scalar_type() == at::kFloat && t.is_contiguous(),
+                "tensornet_create: weights must be contiguous CUDA float32 tensors");
+    return t.data_ptr<float>();
+}
+
+// Weight order (must match torchmdnet/models/tensornet.py::_pack):
+//   rbf_p0 rbf_p1 P Q | emb_filter: w b table | emb_mix x3 emb_mixT x3 | emb_ln_w emb_ln_b
+//   emb_w1 emb_b1 emb_w1T emb_w2 emb_b2 emb_w2T | out_ln_w out_ln_b out_w out_b out_wT
+//   head_w1 head_b1 head_w1T head_w2 head_b2 | per layer: w0 b0 w1 b1 w2 b2 table mix x6 mixT x6
+// iparams: hidden num_rbf num_layers max_z rbf_type activation so3 filter_mode n_int ; fparams: lo hi mean std
+int64_t tensornet_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::vector<double> fp) {
+    TORCH_CHECK(ip.size() == 9 && fp.size() == 4, "tensornet_create: bad parameter vectors");
+    auto h = std::make_shared<TnHandle>();
+    tmdn_tensornet_model& m = h->m;
+    memset(&m, 0, sizeof(m));
+    m.hidden = (int32_t)ip[0]; m.num_rbf = (int32_t)ip[1]; m.num_layers = (int32_t)ip[2]; m.max_z = (int32_t)ip[3];
+    m.rbf_type = (int32_t)ip[4]; m.activation = (int32_t)ip[5]; m.so3 = (int32_t)ip[6]; m.filter_mode = (int32_t)ip[7];
+    const int32_t n_int = (int32_t)ip[8];
+    m.cutoff_lower = (float)fp[0]; m.cutoff_upper = (float)fp[1]; m.mean = (float)fp[2]; m.std = (float)fp[3];
+    TORCH_CHECK(m.num_layers >= 0 && m.num_layers <= TMDN_MAX_LAYERS, "tensornet_create: too many layers");
+    const size_t expect = 31 + 19 * (size_t)m.num_layers;
+    TORCH_CHECK(w.size() == expect, "tensornet_create: expected ", expect, " weight tensors, got ", w.size());
+    const int H = m.hidden, K = m.num_rbf;
+    size_t k = 0;
+    auto next = [&]() -> const float* { return fptr(w[k++]); };
+    m.rbf_p0 = next(); m.rbf_p1 = next(); m.P = next(); m.Q = next();
+    m.emb_filter.n_layers = 1; m.emb_filter.final_act = 0;
+    m.emb_filter.dims[0] = K; m.emb_filter.dims[1] = 3 * H;
+    m.emb_filter.w[0] = next(); m.emb_filter.b[0] = next(); m.emb_filter.table = next(); m.emb_filter.n_int = n_int;
+    for (int g = 0; g < 3; ++g) m.emb_mix[g] = next();
+    for (int g = 0; g < 3; ++g) m.emb_mixT[g] = next();
+    m.emb_ln_w = next(); m.emb_ln_b = next();
+    m.emb_w1 = next(); m.emb_b1 = next(); m.emb_w1T = next();
+    m.emb_w2 = next(); m.emb_b2 = next(); m.emb_w2T = next();
+    m.out_ln_w = next(); m.out_ln_b = next(); m.out_w = next(); m.out_b = next(); m.out_wT = next();
+    m.head_w1 = next(); m.head_b1 = next(); m.head_w1T = next(); m.head_w2 = next(); m.head_b2 = next();
+    for (int l = 0; l < m.num_layers; ++l) {
+        tmdn_filter_set& f = m.layer_filter[l];
+        f.n_layers = 3; f.final_act = 1;
+        f.dims[0] = K; f.dims[1] = H; f.dims[2] = 2 * H; f.dims[3] = 3 * H;
+        for (int j = 0; j < 3; ++j) { f.w[j] = next(); f.b[j] = next(); }
+        f.table = next(); f.n_int = n_int;
+        for (int j = 0; j < 6; ++j) m.layer_mix[l][j] = next();
+        for (int j = 0; j < 6; ++j) m.layer_mixT[l][j] = next();
+    }
+    h->keep = std::move(w);
+    std::lock_guard<std::mutex> lock(g_mu);
+    const int64_t id = g_next++;
+    g_tn[id] = h;
+    return id;
+}
+
+void tensornet_destroy(int64_t id) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    g_tn.erase(id);
+}
+
+std::shared_ptr<TnHandle> tn_get(int64_t id) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    auto it = g_tn.find(id);
+    TORCH_CHECK(it != g_tn.end(), "tensornet: unknown model handle ", id);
+    return it->second;
+}
+
+// -> (energy[n_mol,1], forces[n_atoms,3] (empty if !compute_forces), status int32[4], workspace uint8)
+std::tuple<Tensor, Tensor, Tensor, Tensor> tensornet_energy_forces(int64_t handle, const Tensor& z, const Tensor& pos,
+                                                                   const Tensor& batch, const Tensor& box_vectors,
+                                                                   bool use_periodic, const std::string& strategy,
+                                                                   int64_t max_edges, int64_t n_mol,
+                                                                   bool compute_forces,
+                                                                   const c10::optional<Tensor>& workspace) {
+    auto h = tn_get(handle);
+    TORCH_CHECK(pos.is_cuda(), "tensornet_energy_forces: CUDA tensors required (sm_100a build, no CPU fallback)");
+    TORCH_CHECK(pos.scalar_type() == at::kFloat && pos.dim() == 2 && pos.size(1) == 3 && pos.is_contiguous(),
+                "tensornet_energy_forces: pos must be a contiguous float32 [N,3] tensor");
+    TORCH_CHECK(z.scalar_type() == at::kLong && z.dim() == 1 && z.is_contiguous() && z.size(0) == pos.size(0),
+                "tensornet_energy_forces: z must be a contiguous int64 [N] tensor");
+    TORCH_CHECK(batch.scalar_type() == at::kLong && batch.dim() == 1 && batch.is_contiguous() &&
+                    batch.size(0) == pos.size(0),
+                "tensornet_energy_forces: batch must be a contiguous int64 [N] tensor");
+    TORCH_CHECK(z.device() == pos.device() && batch.device() == pos.device(), "tensornet_energy_forces: device mismatch");
+    const c10::cuda::CUDAGuard guard(pos.device());
+    const int64_t n = pos.size(0);
+    const int sid = strategy_id(strategy);
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    TORCH_CHECK(have_box || !(use_periodic || sid == TMDN_CELL), "tensornet_energy_forces: box required");
+    const size_t need = tmdn_tensornet_workspace_bytes(&h->m, n, max_edges, n_mol);
+    TORCH_CHECK(need > 0, "tensornet_energy_forces: ", tmdn_last_error());
+    Tensor ws;
+    if (workspace.has_value() && workspace->defined() && (size_t)workspace->numel() >= need && workspace->is_cuda() &&
+        workspace->scalar_type() == at::kByte)
+        ws = *workspace;
+    else
+        ws = at::empty({(int64_t)need}, pos.options().dtype(at::kByte));
+    Tensor energy = at::empty({n_mol, 1}, pos.options());
+    Tensor forces = compute_forces ? at::empty({n, 3}, pos.options()) : at::empty({0, 3}, pos.options());
+    Tensor status = at::empty({4}, pos.options().dtype(at::kInt));
+    TMDN_CALL(tmdn_tensornet_energy_forces(&h->m, z.data_ptr<int64_t>(), pos.data_ptr<float>(),
+                                           batch.data_ptr<int64_t>(), n, n_mol, have_box ? box : nullptr, use_periodic,
+                                           sid, max_edges, energy.data_ptr<float>(),
+                                           compute_forces ? forces.data_ptr<float>() : nullptr,
+                                           status.data_ptr<int32_t>(), ws.data_ptr(), (size_t)ws.numel(), cur_stream()));
+    return std::make_tuple(energy, forces, status, ws);
+}
+
+// -> [offset, bytes] of a named intermediate inside the workspace
+std::vector<int64_t> tensornet_debug_lookup(int64_t handle, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                            const std::string& name) {
+    auto h = tn_get(handle);
+    size_t off = 0, bytes = 0;
+    TMDN_CALL(tmdn_tensornet_workspace_lookup(&h->m, n_atoms, max_edges, n_mol, name.c_str(), &off, &bytes));
+    return {(int64_t)off, (int64_t)bytes};
+}
+
+}  // namespace
+
+TORCH_LIBRARY(torchmdnet_neighbors, m) {
+    m.def("get_neighbor_pairs(str strategy, Tensor positions, Tensor batch, Tensor box_vectors, bool use_periodic, "
+          "Scalar cutoff_lower, Scalar cutoff_upper, Scalar max_num_pairs, bool loop, bool include_transpose) -> "
+          "(Tensor neighbors, Tensor distances, Tensor distance_vecs, Tensor num_pairs)");
+}
+TORCH_LIBRARY_IMPL(torchmdnet_neighbors, AutogradCUDA, m) { m.impl("get_neighbor_pairs", get_neighbor_pairs_autograd); }
+TORCH_LIBRARY_IMPL(torchmdnet_neighbors, CPU, m) { m.impl("get_neighbor_pairs", get_neighbor_pairs_cpu); }
+
+TORCH_LIBRARY(torch_extension, m) { m.def("is_stream_capturing() -> bool", is_stream_capturing); }
+
+TORCH_LIBRARY(torchmdnet_b200, m) {
+    m.def("csr_from_pairs(Tensor neighbors, Tensor deltas, Tensor distances, Tensor num_found, int n_atoms, "
+          "int target_row) -> (Tensor, Tensor, Tensor)",
+          csr_from_pairs);
+    m.def("tensornet_create(Tensor[] weights, int[] iparams, float[] fparams) -> int", tensornet_create);
+    m.def("tensornet_destroy(int handle) -> ()", tensornet_destroy);
+    m.def("tensornet_energy_forces(int handle, Tensor z, Tensor pos, Tensor batch, Tensor box_vectors, "
+          "bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces, Tensor? workspace) -> "
+          "(Tensor, Tensor, Tensor, Tensor)",
+          tensornet_energy_forces);
+    m.def("tensornet_debug_lookup(int handle, int n_atoms, int max_edges, int n_mol, str name) -> int[]",
+          tensornet_debug_lookup);
+}
