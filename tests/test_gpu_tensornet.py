@@ -1,0 +1,257 @@
+"""Fused CUDA TensorNet energy+forces (TorchMD_Net.forward -> torch op -> C ABI) against
+  * the oracle restatement of the reference CPU path (oracle/model.py) on the same seeded inputs,
+  * fixtures produced by the unmodified reference (tests/golden/small_*.npz, model_*.npz, expected_pkl.json),
+  * the staged restatement of the kernel pipeline, buffer by buffer (oracle/staged_tensornet.py).
+Tolerances are north_star's: energies 1e-5 relative, forces 1e-4 eV/A absolute (fp32, exact-filter mode); the
+table-filter mode is held to the same bar."""
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import GOLDEN, load_npz, tt
+from oracle import model as om
+from oracle import staged_tensornet as st
+
+pytestmark = pytest.mark.gpu
+E_RTOL, F_ATOL = 1e-5, 1e-4
+
+
+def seed_everything(s):
+    random.seed(s)
+    np.random.seed(s)
+    torch.manual_seed(s)
+
+
+def build(g, mode="exact", mean=None, std=None):
+    from torchmdnet.models.model import create_model
+    m = create_model(g["hparams"])
+    m.load_state_dict(g["sd"])
+    m = m.cuda().eval()
+    m.representation_model.filter_mode = mode
+    return m
+
+
+def check(y, f, y_ref, f_ref, e_rtol=E_RTOL, f_atol=F_ATOL):
+    y, f = y.cpu().double(), f.cpu().double()
+    y_ref, f_ref = torch.as_tensor(y_ref).double(), torch.as_tensor(f_ref).double()
+    assert y.shape == y_ref.shape and f.shape == f_ref.shape
+    scale = max(1.0, float(y_ref.abs().max()))
+    assert float((y - y_ref).abs().max()) <= e_rtol * scale, (y, y_ref)
+    assert float((f - f_ref).abs().max()) <= f_atol, float((f - f_ref).abs().max())
+
+
+SMALL_TN = ["small_tensornet_o3.npz", "small_tensornet_so3.npz", "small_tensornet_gauss.npz"]
+
+
+@pytest.mark.parametrize("mode", ["exact", "table"])
+@pytest.mark.parametrize("name", SMALL_TN)
+def test_small_models_match_reference(name, mode):
+    g = load_npz(name)
+    m = build(g, mode)
+    y, f = m(tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda())
+    check(y, f, g["y"], g["forces"])
+
+
+@pytest.mark.parametrize("mode", ["exact", "table"])
+@pytest.mark.parametrize("strategy", ["brute", "cell"])
+def test_periodic_box_matches_reference(mode, strategy):
+    """The reference model with OptimizedDistance(box=...) swapped in, 375 atoms of water."""
+    from torchmdnet.models.utils import OptimizedDistance
+    g = load_npz("small_tensornet_periodic.npz")
+    m = build(g, mode)
+    hp = g["hparams"]
+    m.representation_model.distance = OptimizedDistance(
+        hp["cutoff_lower"], hp["cutoff_upper"], max_num_pairs=-hp["max_num_neighbors"], return_vecs=True, loop=True,
+        check_errors=False, resize_to_fit=False, box=tt(g["box"]), strategy=strategy)
+    y, f = m(tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda())
+    check(y, f, g["y"], g["forces"])
+
+
+@pytest.mark.parametrize("cfg", ["TensorNet-SPICE", "TensorNet-rMD17", "TensorNet-ANI1X", "TensorNet-QM9"])
+@pytest.mark.parametrize("mode", ["exact", "table"])
+def test_full_size_hparams_match_reference(cfg, mode):
+    """Seeded create_model with the example yaml hparams (weights are bit-identical to the reference's, see
+    tests/test_host.py) on the synthetic inputs; expected values were produced by the unmodified reference."""
+    from torchmdnet.models.model import create_model
+    g = load_npz("model_%s.npz" % cfg)
+    seed_everything(int(g["seed"]))
+    m = create_model(g["hparams"]).cuda().eval()
+    m.representation_model.filter_mode = mode
+    y, f = m(tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda())
+    check(y, f, g["y"], g["forces"])
+
+
+def test_reference_expected_pkl_row():
+    """tests/expected.pkl, TensorNet/Scalar row (tests/test_model.py:137-188): 5 atoms in 2 molecules."""
+    from torchmdnet.models.model import create_model
+    with open(os.path.join(GOLDEN, "expected_pkl.json")) as fh:
+        e = json.load(fh)["tensornet"]
+    seed_everything(1234)
+    m = create_model(e["hparams"]).cuda().eval()
+    y, f = m(torch.tensor(e["z"]).cuda(), torch.tensor(e["pos"]).cuda(), torch.tensor(e["batch"]).cuda())
+    # the reference's own tolerance for this file: assert_allclose fp32 defaults, rtol 1.3e-6 atol 1e-5
+    torch.testing.assert_close(y.cpu(), torch.tensor(e["expected_pred"]), rtol=1.3e-6, atol=1e-5)
+    torch.testing.assert_close(f.cpu(), torch.tensor(e["expected_deriv"]), rtol=1.3e-6, atol=1e-5)
+
+
+def test_intermediate_buffers_match_staged_restatement():
+    g = load_npz("small_tensornet_o3.npz")
+    m = build(g, "exact")
+    z, pos, batch = tt(g["z"]), tt(g["pos"]), tt(g["batch"])
+    n, n_mol = z.shape[0], int(batch.max()) + 1
+    y, f = m(z.cuda(), pos.cuda(), batch.cuda())
+    sd = {k: (v.double() if v.is_floating_point() else v) for k, v in g["sd"].items()}
+    hp = g["hparams"]
+    ei, shift = om.build_edges(pos.double(), batch, hp, None)
+    keep = {}
+    ys, fs = st.energy_forces_staged(sd, hp, z, pos.double(), batch, ei, shift, n_mol, keep)
+    rm = m.representation_model
+    H = hp["embedding_dimension"]
+    rp = rm.debug_buffer("row_ptr", n, n_mol, torch.int32)[:n + 1].cpu().long()
+    assert torch.equal(rp, keep["row_ptr"])
+    E = int(rp[-1])
+    col = rm.debug_buffer("col", n, n_mol, torch.int32)[:E].cpu().long()
+    assert torch.equal(col, keep["col"])
+    geom = rm.debug_buffer("geom", n, n_mol)[:4 * E].view(E, 4).cpu().double()
+    torch.testing.assert_close(geom[:, :3], keep["u"], rtol=0, atol=2e-6)
+    torch.testing.assert_close(geom[:, 3], keep["d"], rtol=2e-6, atol=0)
+    for name in ["ias", "X0", "Y0", "M0", "X1", "Y1", "M1", "X2", "Dias"]:
+        got = rm.debug_buffer(name, n, n_mol)[:n * 9 * H].view(n, 9, H).cpu().double()
+        ref = keep[name]
+        tol = 5e-5 * max(1.0, float(ref.abs().max()))
+        assert float((got - ref).abs().max()) < tol, (name, float((got - ref).abs().max()), tol)
+    check(y, f, ys, fs)
+
+
+def test_batch_none_and_forward_only_and_features():
+    g = load_npz("small_tensornet_o3.npz")
+    m = build(g)
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    sel = batch == 0
+    y1, f1 = m(z[sel], pos[sel])                 # batch=None -> single molecule
+    y, f = m(z, pos, batch)
+    torch.testing.assert_close(y1[0], y[0], rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(f1, f[sel], rtol=0, atol=1e-6)
+    m.derivative = False
+    y2, none = m(z, pos, batch)
+    assert none is None
+    torch.testing.assert_close(y2, y, rtol=0, atol=0)
+    x, v, z_, pos_, batch_ = m.representation_model(z, pos, batch)
+    sd, hp = g["sd"], g["hparams"]
+    ei, shift = om.build_edges(pos.cpu(), batch.cpu(), hp, None)
+    xr, _ = om.tensornet_representation(sd, hp, z.cpu(), pos.cpu(), ei, shift)
+    assert v is None
+    torch.testing.assert_close(x.cpu(), xr, rtol=1e-4, atol=2e-5)
+
+
+def test_batch_sharding_is_exact():
+    """Molecules are independent: evaluating a shard gives the same numbers as the full batch (bitwise, because
+    every reduction is an in-order segmented sum)."""
+    import synth_inputs as S
+    from torchmdnet.models.model import create_model
+    g = load_npz("model_TensorNet-rMD17.npz")
+    seed_everything(int(g["seed"]))
+    m = create_model(g["hparams"]).cuda().eval()
+    z, pos, batch = (torch.from_numpy(a).cuda() for a in S.md17_like_batch(n_mol=64, seed=3))
+    y, f = m(z, pos, batch)
+    lo = 21 * 32
+    y2, f2 = m(z[lo:], pos[lo:], batch[lo:] - 32)
+    assert torch.equal(y2, y[32:]) and torch.equal(f2, f[lo:])
+    yr, fr = om.energy_forces(m.state_dict(), g["hparams"], z[:63].cpu(), pos[:63].cpu(), batch[:63].cpu())
+    check(y[:3], f[:63], yr, fr)
+
+
+def test_forces_are_minus_energy_gradient_fp64_finite_differences():
+    """Size-independent property (the reference's test_gradients idea, tests/test_model.py:191-211):
+    central differences of the CUDA energy in fp32 positions against the CUDA forces."""
+    g = load_npz("small_tensornet_o3.npz")
+    m = build(g)
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    y, f = m(z, pos, batch)
+    h = 2e-2
+    rng = np.random.RandomState(0)
+    for _ in range(6):
+        i, k = rng.randint(pos.shape[0]), rng.randint(3)
+        p1, p2 = pos.clone(), pos.clone()
+        p1[i, k] += h
+        p2[i, k] -= h
+        m.derivative = False
+        e1 = m(z, p1, batch)[0].double().sum()
+        e2 = m(z, p2, batch)[0].double().sum()
+        fd = -(e1 - e2) / (2 * h)
+        assert abs(float(fd) - float(f[i, k])) < 5e-3 * max(1.0, abs(float(f[i, k]))), (float(fd), float(f[i, k]))
+
+
+def test_rotation_invariance_and_force_equivariance():
+    """tests/test_equivariance.py idea: E(Rx) = E(x), F(Rx) = R F(x)."""
+    g = load_npz("small_tensornet_o3.npz")
+    m = build(g)
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    R = torch.tensor([[0.9362934, -0.2896295, 0.1986693], [0.3129918, 0.9447025, -0.0978434],
+                      [-0.1593451, 0.1537920, 0.9751703]], device="cuda")
+    y, f = m(z, pos, batch)
+    y2, f2 = m(z, pos @ R.T, batch)
+    torch.testing.assert_close(y2, y, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(f2, f @ R.T, rtol=0, atol=1e-4)
+
+
+def test_cuda_graph_capture_of_the_whole_step():
+    g = load_npz("small_tensornet_o3.npz")
+    m = build(g)
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    y0, f0 = m(z, pos, batch)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(2):
+            m(z, pos, batch)
+    torch.cuda.current_stream().wait_stream(s)
+    static_pos = pos.clone()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        y, f = m(z, static_pos, batch)
+    static_pos.copy_(pos + 0.01)
+    graph.replay()
+    static_pos.copy_(pos)
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(y, y0) and torch.equal(f, f0)
+
+
+def test_external_calculator(tmp_path):
+    """tests/test_calculator.py of the reference with a locally written checkpoint (example.ckpt is absent)."""
+    from torchmdnet.calculators import External
+    from torchmdnet.models.model import load_model
+    g = load_npz("small_tensornet_o3.npz")
+    ckpt = str(tmp_path / "model.ckpt")
+    torch.save({"hyper_parameters": dict(g["hparams"], derivative=False),
+                "state_dict": {"model." + k: v for k, v in g["sd"].items()}}, ckpt)
+    z = tt(g["z"])[:9]
+    pos = tt(g["pos"])[:9]
+    model = load_model(ckpt, device="cuda", derivative=True)
+    e_ref, f_ref = model(z.cuda(), pos.cuda())
+    calc = External(ckpt, z.unsqueeze(0), "cuda")
+    e, f = calc.calculate(pos, None)
+    torch.testing.assert_close(e, e_ref)
+    torch.testing.assert_close(f, f_ref.unsqueeze(0))
+    calc2 = External(ckpt, torch.stack([z, z]), "cuda", output_transform="eV/A -> kcal/mol/A")
+    e2, f2 = calc2.calculate(torch.cat([pos, pos]), None)
+    assert e2.shape == (2, 1) and f2.shape == (2, 9, 3)
+    torch.testing.assert_close(e2[1:], e_ref * 23.0609, rtol=1e-5, atol=1e-5)
+
+
+def test_overflow_is_reported():
+    g = load_npz("small_tensornet_o3.npz")
+    m = build(g)
+    rm = m.representation_model
+    rm.distance.max_num_pairs = -1            # one pair per atom: certainly too few
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    y, f, status = rm.energy_forces(z, pos, batch, int(batch.max()) + 1, m.output_model, 0.0, 1.0)
+    assert int(status[1]) == 1 and int(status[0]) > z.shape[0]
+    rm.distance.check_errors = True
+    with pytest.raises(RuntimeError, match="max_num_pairs"):
+        m(z, pos, batch)

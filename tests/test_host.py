@@ -1,0 +1,148 @@
+"""Host-side logic that needs no GPU: seed-for-seed parameter initialisation against the reference
+(checksums recorded by oracle/make_golden.py), state_dict compatibility, C-ABI exports, loud failure on CPU."""
+import ctypes
+import json
+import os
+import random
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT
+from helpers import GOLDEN, load_npz, tt
+
+CONFIGS = ["TensorNet-SPICE", "TensorNet-rMD17", "TensorNet-ANI1X", "TensorNet-QM9", "ET-QM9", "ET-MD17"]
+
+
+def seed_everything(s):
+    random.seed(s)
+    np.random.seed(s)
+    torch.manual_seed(s)
+
+
+@pytest.mark.parametrize("cfg", CONFIGS)
+def test_seeded_init_matches_reference(cfg):
+    from torchmdnet.models.model import create_model
+    g = load_npz("model_%s.npz" % cfg)
+    seed_everything(int(g["seed"]))
+    sd = create_model(g["hparams"]).state_dict()
+    cs = g["checksums"]
+    assert list(sd) == list(cs)          # same keys, same order as the reference's state_dict
+    for k, v in sd.items():
+        assert float(v.double().sum()) == pytest.approx(cs[k][0], abs=1e-9), k
+        assert float(v.double().abs().sum()) == pytest.approx(cs[k][1], abs=1e-9), k
+
+
+@pytest.mark.parametrize("name", ["small_tensornet_o3.npz", "small_et_both.npz", "small_et_keys_nonbr.npz"])
+def test_reference_state_dict_loads_strictly(name):
+    from torchmdnet.models.model import create_model
+    g = load_npz(name)
+    m = create_model(g["hparams"])
+    m.load_state_dict(g["sd"], strict=True)
+
+
+def test_expected_pkl_recipe_init(tmp_path):
+    """The reference's own golden recipe (tests/test_model.py:137-188): seed 1234 then create_model."""
+    from torchmdnet.models.model import create_model
+    with open(os.path.join(GOLDEN, "expected_pkl.json")) as f:
+        exp = json.load(f)
+    for key in ("tensornet", "equivariant-transformer"):
+        e = exp[key]
+        seed_everything(1234)
+        sd = create_model(e["hparams"]).state_dict()
+        for k, v in sd.items():
+            assert float(v.double().sum()) == pytest.approx(e["checksums"][k][0], abs=1e-9), k
+
+
+def _declared_symbols():
+    with open(os.path.join(ROOT, "include", "tmdn.h")) as f:
+        src = re.sub(r"/\*.*?\*/", "", f.read(), flags=re.S)
+    return sorted(set(re.findall(r"\b(tmdn_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_cabi_exports_every_declared_symbol():
+    from torchmdnet import _native
+    lib = _native.cabi()
+    names = _declared_symbols()
+    assert "tmdn_neighbors_f32" in names and "tmdn_tensornet_energy_forces" in names
+    for n in names:
+        assert hasattr(lib, n), "libtmdn.so does not export %s" % n
+    lib.tmdn_version.restype = ctypes.c_int
+    assert lib.tmdn_version() == 100
+    lib.tmdn_neighbors_workspace_bytes.restype = ctypes.c_size_t
+    lib.tmdn_neighbors_workspace_bytes.argtypes = [ctypes.c_int, ctypes.c_int64, ctypes.c_void_p, ctypes.c_double,
+                                                   ctypes.c_int]
+    assert lib.tmdn_neighbors_workspace_bytes(0, 1000, None, 5.0, 4) > 0
+
+
+def test_cabi_rejects_bad_arguments_without_a_gpu():
+    from torchmdnet import _native
+    lib = _native.cabi()
+    lib.tmdn_last_error.restype = ctypes.c_char_p
+    rc = lib.tmdn_neighbors_f32(0, None, None, ctypes.c_int64(0), None, 0, ctypes.c_double(0), ctypes.c_double(5),
+                                0, 1, ctypes.c_int64(10), None, None, None, None, None, ctypes.c_size_t(0), None)
+    assert rc == 1 and b"null pointer" in lib.tmdn_last_error()
+
+
+def test_cpu_tensors_fail_loudly():
+    from torchmdnet.models.model import create_model
+    from torchmdnet.models.utils import OptimizedDistance
+    with pytest.raises(RuntimeError, match="CUDA"):
+        OptimizedDistance(0.0, 5.0)(torch.randn(10, 3))
+    g = load_npz("small_tensornet_o3.npz")
+    m = create_model(g["hparams"])
+    m.load_state_dict(g["sd"])
+    with pytest.raises(RuntimeError, match="CUDA"):
+        m(tt(g["z"]), tt(g["pos"]), tt(g["batch"]))
+
+
+def test_unsupported_configurations_are_refused():
+    from torchmdnet.models.model import create_model
+    hp = dict(load_npz("small_tensornet_o3.npz")["hparams"])
+    with pytest.raises(NotImplementedError):
+        create_model(dict(hp, model="graph-network"))
+    with pytest.raises(NotImplementedError):
+        create_model(dict(hp, output_model="DipoleMoment"))
+    with pytest.raises(ValueError):
+        create_model(dict(hp, model="nope"))
+
+
+def test_rbf_modules_match_oracle():
+    from oracle import model as om
+    from torchmdnet.models.utils import CosineCutoff, ExpNormalSmearing, GaussianSmearing
+    d = torch.linspace(0, 6, 50)
+    e = ExpNormalSmearing(0.0, 5.0, 16, trainable=False)
+    torch.testing.assert_close(e(d), om.expnorm_rbf(d, e.means, e.betas, 0.0, 5.0))
+    gs = GaussianSmearing(0.0, 5.0, 16, trainable=False)
+    torch.testing.assert_close(gs(d), om.gauss_rbf(d, gs.offset, gs.coeff))
+    torch.testing.assert_close(CosineCutoff(0.0, 5.0)(d), om.cosine_cutoff(d, 0.0, 5.0))
+    torch.testing.assert_close(CosineCutoff(1.0, 5.0)(d), om.cosine_cutoff(d, 1.0, 5.0))
+    # decay outside the cutoffs, as tests/test_rbfs.py:6-30 of the reference
+    assert float(e(torch.tensor([5.5])).abs().max()) == 0.0
+
+
+def test_filter_table_interpolates_filter():
+    """The Hermite table the host builds for filter_mode='table' reproduces the filter MLP to ~1e-7."""
+    from torchmdnet.models.model import create_model
+    from torchmdnet.models.tensornet import filter_table, hermite_coefficients
+    g = load_npz("small_tensornet_o3.npz")
+    m = create_model(g["hparams"]).double()
+    m.load_state_dict({k: v.double() if v.is_floating_point() else v for k, v in g["sd"].items()})
+    rm = m.representation_model
+    hi = float(rm.cutoff_upper)
+    ls = rm.layers[0].linears_scalar
+    layers = [(l.weight.detach(), l.bias.detach()) for l in ls]
+    p0, p1 = rm.distance_expansion.means, rm.distance_expansion.betas
+    n_int = 4096
+    grid = torch.linspace(0, hi, n_int + 1, dtype=torch.float64)
+    f, df = filter_table(grid, "expnorm", p0, p1, 0.0, hi, layers, "silu", True)
+    c = hermite_coefficients(f, df, hi / n_int)
+    d = torch.rand(2000, dtype=torch.float64) * hi * 0.999
+    k = (d / (hi / n_int)).long().clamp(max=n_int - 1)
+    s = (d / (hi / n_int) - k)[:, None]
+    ck = c[k]
+    approx = ck[..., 0] + s * (ck[..., 1] + s * (ck[..., 2] + s * ck[..., 3]))
+    exact, _ = filter_table(d, "expnorm", p0, p1, 0.0, hi, layers, "silu", True)
+    assert float((approx - exact).abs().max()) < 2e-7 * max(1.0, float(exact.abs().max()))

@@ -1,0 +1,130 @@
+"""``create_model`` / ``load_model`` / ``TorchMD_Net`` with the reference's signatures
+(torchmdnet/models/model.py:15-300) over the fused CUDA energy+force pipeline.
+
+``TorchMD_Net.forward(z, pos, batch=None, q=None, s=None, extra_args=None) -> (y, neg_dy | None)`` performs ONE
+native call: neighbour search, representation, head, per-molecule reduction, ``* std + mean`` and -- when
+``derivative`` -- the hand-written backward kernels that give ``neg_dy = -dy/dpos`` (the reference replays the
+graph with ``torch.autograd.grad(create_graph=True)``, model.py:286-298).  The returned tensors carry no
+autograd graph: training through forces (double backward) is outside this build and is
+refused rather than silently approximated.
+"""
+import re
+import warnings
+from typing import Dict, Optional, Tuple
+
+import torch
+from torch import Tensor, nn
+
+from . import output_modules
+from .utils import dtype_mapping
+
+
+def create_model(args, prior_model=None, mean=None, std=None):
+    """Build a model from the flat hparam dict the reference reads (model.py:28-116)."""
+    dtype = dtype_mapping[args["precision"]]
+    shared_args = dict(hidden_channels=args["embedding_dimension"], num_layers=args["num_layers"],
+                       num_rbf=args["num_rbf"], rbf_type=args["rbf_type"], trainable_rbf=args["trainable_rbf"],
+                       activation=args["activation"], cutoff_lower=args["cutoff_lower"],
+                       cutoff_upper=args["cutoff_upper"], max_z=args["max_z"],
+                       max_num_neighbors=args["max_num_neighbors"], dtype=dtype)
+    if args["model"] == "equivariant-transformer":
+        from .torchmd_et import TorchMD_ET
+        is_equivariant = True
+        representation_model = TorchMD_ET(attn_activation=args["attn_activation"], num_heads=args["num_heads"],
+                                          distance_influence=args["distance_influence"],
+                                          neighbor_embedding=args["neighbor_embedding"], **shared_args)
+    elif args["model"] == "tensornet":
+        from .tensornet import TensorNet
+        is_equivariant = False          # TensorNet always takes the plain Scalar head (model.py:79-80)
+        representation_model = TensorNet(equivariance_invariance_group=args["equivariance_invariance_group"],
+                                         **shared_args)
+    elif args["model"] in ("graph-network", "transformer"):
+        raise NotImplementedError('architecture "%s" is outside the accelerated energy+force path of this build '
+                                  "(equivariant-transformer and tensornet only)" % args["model"])
+    else:
+        raise ValueError(f'Unknown architecture: {args["model"]}')
+    if args.get("atom_filter", -1) > -1:
+        if args["derivative"]:
+            raise ValueError("Derivative and atom filter can't be used together")
+        raise NotImplementedError("AtomFilter is outside the accelerated energy+force path of this build")
+    if args.get("prior_model") or prior_model is not None:
+        raise NotImplementedError("prior models are outside the accelerated energy+force path of this build")
+    if args["output_model"] != "Scalar":
+        raise NotImplementedError('output_model "%s": only the Scalar energy head is built' % args["output_model"])
+    if args.get("reduce_op", "add") not in ("add", "sum"):
+        raise NotImplementedError('reduce_op "%s": only add/sum is built' % args["reduce_op"])
+    output_prefix = "Equivariant" if is_equivariant else ""
+    output_model = getattr(output_modules, output_prefix + args["output_model"])(
+        args["embedding_dimension"], activation=args["activation"], reduce_op=args["reduce_op"], dtype=dtype)
+    return TorchMD_Net(representation_model, output_model, prior_model=None, mean=mean, std=std,
+                       derivative=args["derivative"], dtype=dtype)
+
+
+def load_model(filepath, args=None, device="cpu", **kwargs):
+    """Rebuild a model from a Lightning checkpoint (``hyper_parameters`` + ``state_dict`` with a ``model.``
+    prefix), model.py:121-143."""
+    ckpt = torch.load(filepath, map_location="cpu", weights_only=False)
+    if args is None:
+        args = ckpt["hyper_parameters"]
+    for key, value in kwargs.items():
+        if key not in args:
+            warnings.warn(f"Unknown hyperparameter: {key}={value}")
+        args[key] = value
+    model = create_model(args)
+    state_dict = {re.sub(r"^model\.", "", k): v for k, v in ckpt["state_dict"].items()}
+    model.load_state_dict(state_dict)
+    return model.to(device)
+
+
+class TorchMD_Net(nn.Module):
+    """Representation model + energy head + (fused) force evaluation (model.py:180-300)."""
+
+    def __init__(self, representation_model, output_model, prior_model=None, mean=None, std=None,
+                 derivative=False, dtype=torch.float32):
+        super().__init__()
+        self.representation_model = representation_model.to(dtype=dtype)
+        self.output_model = output_model.to(dtype=dtype)
+        if prior_model is not None:
+            raise NotImplementedError("prior models are outside the accelerated energy+force path of this build")
+        self.prior_model = None
+        self.derivative = derivative
+        mean = torch.scalar_tensor(0) if mean is None else mean
+        self.register_buffer("mean", mean.to(dtype=dtype))
+        std = torch.scalar_tensor(1) if std is None else std
+        self.register_buffer("std", std.to(dtype=dtype))
+        self._scale = None          # (mean, std) as host floats, cached per buffer version (one sync, once)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        self.representation_model.reset_parameters()
+        self.output_model.reset_parameters()
+
+    def _mean_std(self):
+        key = (self.mean.data_ptr(), self.mean._version, self.std.data_ptr(), self.std._version)
+        if self._scale is None or self._scale[0] != key:
+            self._scale = (key, float(self.mean), float(self.std))
+        return self._scale[1], self._scale[2]
+
+    def forward(self, z: Tensor, pos: Tensor, batch: Optional[Tensor] = None, q: Optional[Tensor] = None,
+                s: Optional[Tensor] = None, extra_args: Optional[Dict[str, Tensor]] = None
+                ) -> Tuple[Tensor, Optional[Tensor]]:
+        assert z.dim() == 1 and z.dtype == torch.long
+        if batch is None:
+            batch = torch.zeros_like(z)
+            n_mol = 1
+        else:
+            n_mol = self._num_molecules(batch)
+        mean, std = self._mean_std()
+        y, neg_dy, _ = self.representation_model.energy_forces(z, pos, batch, n_mol, self.output_model, mean, std,
+                                                                compute_forces=self.derivative)
+        return y, (neg_dy if self.derivative else None)
+
+    def _num_molecules(self, batch):
+        """``batch.max()+1`` (output_modules.py:33); cached while capturing a CUDA graph, as the reference."""
+        from .utils import check_stream_capturing
+        om = self.output_model
+        if batch.is_cuda and check_stream_capturing():
+            assert om.dim_size > 0, "Warming up is needed before capturing the model into a CUDA graph"
+            return om.dim_size
+        om.dim_size = int(batch.max().item() + 1)
+        return om.dim_size

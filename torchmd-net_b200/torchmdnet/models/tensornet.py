@@ -1,0 +1,323 @@
+"""TensorNet (reference: torchmdnet/models/tensornet.py) as a parameter tree + weight packer for the fused
+CUDA energy/force pipeline of libtmdn (csrc/tensornet.cu).
+
+The module tree reproduces the reference's parameter names, shapes and RNG consumption order
+(tensornet.py:104-198, 236-286, 335-375), so ``state_dict``s are interchangeable and a seeded ``create_model``
+gives bit-identical initial weights.  No layer has a PyTorch ``forward``: ``pack_weights`` rearranges the
+parameters once per weight version into the layouts the kernels read and ``TensorNet.energy_forces`` runs
+neighbour search, embedding, interactions, head and the analytic backward in one C-ABI call.
+
+Two deliberate differences from the reference's *CUDA* behaviour (both documented in DESIGN.md):
+  * the unpadded edge semantics of the reference CPU path are implemented -- the static-shape padding
+    artefact of tensornet.py:215-221 (spurious self-loop messages on atom 0) is not reproduced;
+  * matmuls are exact fp32 (the reference flips TF32 on process-wide at import, tensornet.py:13-14).
+"""
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor, nn
+
+from .. import _native
+from .utils import (ACT_ID, RBF_ID, CosineCutoff, OptimizedDistance, _fused_only, act_class_mapping,
+                    rbf_class_mapping)
+
+__all__ = ["TensorNet"]
+
+FILTER_EXACT, FILTER_TABLE = 0, 1
+
+
+class TensorEmbedding(nn.Module):
+    """Parameters of tensornet.py:236-286."""
+
+    def __init__(self, hidden_channels, num_rbf, activation, cutoff_lower, cutoff_upper, trainable_rbf=False,
+                 max_z=128, dtype=torch.float32):
+        super().__init__()
+        H = hidden_channels
+        self.hidden_channels = H
+        self.distance_proj1 = nn.Linear(num_rbf, H, dtype=dtype)
+        self.distance_proj2 = nn.Linear(num_rbf, H, dtype=dtype)
+        self.distance_proj3 = nn.Linear(num_rbf, H, dtype=dtype)
+        self.cutoff = CosineCutoff(cutoff_lower, cutoff_upper)
+        self.max_z = max_z
+        self.emb = nn.Embedding(max_z, H, dtype=dtype)
+        self.emb2 = nn.Linear(2 * H, H, dtype=dtype)
+        self.act = activation()
+        # the reference builds these three without dtype= (tensornet.py:261-264); TorchMD_Net casts afterwards
+        self.linears_tensor = nn.ModuleList([nn.Linear(H, H, bias=False) for _ in range(3)])
+        self.linears_scalar = nn.ModuleList([nn.Linear(H, 2 * H, bias=True, dtype=dtype),
+                                             nn.Linear(2 * H, 3 * H, bias=True, dtype=dtype)])
+        self.init_norm = nn.LayerNorm(H, dtype=dtype)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        for m in (self.distance_proj1, self.distance_proj2, self.distance_proj3, self.emb, self.emb2,
+                  *self.linears_tensor, *self.linears_scalar, self.init_norm):
+            m.reset_parameters()
+
+    forward = _fused_only
+
+
+class Interaction(nn.Module):
+    """Parameters of tensornet.py:335-375."""
+
+    def __init__(self, num_rbf, hidden_channels, activation, cutoff_lower, cutoff_upper,
+                 equivariance_invariance_group, dtype=torch.float32):
+        super().__init__()
+        H = hidden_channels
+        self.num_rbf = num_rbf
+        self.hidden_channels = H
+        self.cutoff = CosineCutoff(cutoff_lower, cutoff_upper)
+        self.linears_scalar = nn.ModuleList([nn.Linear(num_rbf, H, bias=True, dtype=dtype),
+                                             nn.Linear(H, 2 * H, bias=True, dtype=dtype),
+                                             nn.Linear(2 * H, 3 * H, bias=True, dtype=dtype)])
+        self.linears_tensor = nn.ModuleList([nn.Linear(H, H, bias=False) for _ in range(6)])
+        self.act = activation()
+        self.equivariance_invariance_group = equivariance_invariance_group
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        for m in (*self.linears_scalar, *self.linears_tensor):
+            m.reset_parameters()
+
+    forward = _fused_only
+
+
+# ------------------------------------------------------------------------------------------------ fp64 helpers
+def _act_and_grad(name, x):
+    if name == "silu":
+        s = torch.sigmoid(x)
+        return x * s, s * (1 + x * (1 - s))
+    if name == "tanh":
+        y = torch.tanh(x)
+        return y, 1 - y * y
+    if name == "sigmoid":
+        s = torch.sigmoid(x)
+        return s, s * (1 - s)
+    if name == "ssp":
+        return torch.nn.functional.softplus(x) - 0.6931471805599453, torch.sigmoid(x)
+    raise ValueError(name)
+
+
+def _cutoff_and_grad(d, lo, hi):
+    pi = 3.141592653589793
+    if lo > 0:
+        arg = pi * (2 * (d - lo) / (hi - lo) + 1.0)
+        m = ((d < hi) & (d > lo)).to(d.dtype)
+        return 0.5 * (torch.cos(arg) + 1) * m, -0.5 * torch.sin(arg) * (2 * pi / (hi - lo)) * m
+    m = (d < hi).to(d.dtype)
+    return 0.5 * (torch.cos(d * pi / hi) + 1) * m, -0.5 * torch.sin(d * pi / hi) * (pi / hi) * m
+
+
+def filter_table(d, rbf_type, p0, p1, lo, hi, layers, act, final_act):
+    """f(d) = [act o] Lin_n(... act(Lin_1(rbf(d)))) * C(d) and df/dd at the points ``d`` (all in d.dtype;
+    called in fp64 on the device).  ``layers`` = [(W[out,in], b[out]), ...].  Reference functions:
+    models/utils.py:298-300, 339-344, 368-390; tensornet.py:295-304, 381-382."""
+    dd = d.unsqueeze(-1)
+    if rbf_type == "expnorm":
+        alpha = 5.0 / (hi - lo)
+        c0, dc0 = _cutoff_and_grad(dd, 0.0, hi)
+        u = torch.exp(alpha * (lo - dd))
+        g = torch.exp(-p1 * (u - p0) ** 2)
+        h, t = c0 * g, dc0 * g + c0 * g * (2 * alpha) * p1 * u * (u - p0)
+    else:
+        g = torch.exp(p1 * (dd - p0) ** 2)
+        h, t = g, 2 * p1 * (dd - p0) * g
+    for k, (W, b) in enumerate(layers):
+        h = h @ W.t() + b
+        t = t @ W.t()
+        if k < len(layers) - 1 or final_act:
+            h, gact = _act_and_grad(act, h)
+            t = t * gact
+    c, dc = _cutoff_and_grad(d, lo, hi)
+    return h * c[:, None], t * c[:, None] + h * dc[:, None]
+
+
+def hermite_coefficients(f, df, h):
+    """Cubic Hermite coefficients per interval: value(s) = c0 + s(c1 + s(c2 + s c3)), s in [0,1).
+    f, df: [n_int+1, C] -> [n_int, C, 4]."""
+    f0, f1, d0, d1 = f[:-1], f[1:], df[:-1] * h, df[1:] * h
+    return torch.stack([f0, d0, 3 * (f1 - f0) - 2 * d0 - d1, 2 * (f0 - f1) + d0 + d1], -1)
+
+
+class TensorNet(nn.Module):
+    """Drop-in for ``torchmdnet.models.tensornet.TensorNet`` (tensornet.py:70-234): same constructor, same
+    parameters.  ``filter_mode``: "exact" evaluates the per-edge filter MLPs with fp32 GEMMs, "table"
+    evaluates them from a cubic Hermite table in d built in fp64 from the weights (``table_intervals``)."""
+
+    def __init__(self, hidden_channels=128, num_layers=2, num_rbf=32, rbf_type="expnorm", trainable_rbf=False,
+                 activation="silu", cutoff_lower=0, cutoff_upper=4.5, max_num_neighbors=64, max_z=128,
+                 equivariance_invariance_group="O(3)", static_shapes=True, dtype=torch.float32):
+        super().__init__()
+        assert rbf_type in rbf_class_mapping, f'Unknown RBF type "{rbf_type}".'
+        assert activation in act_class_mapping, f'Unknown activation function "{activation}".'
+        assert equivariance_invariance_group in ["O(3)", "SO(3)"], \
+            f'Unknown group "{equivariance_invariance_group}". Choose O(3) or SO(3).'
+        self.hidden_channels = hidden_channels
+        self.equivariance_invariance_group = equivariance_invariance_group
+        self.num_layers = num_layers
+        self.num_rbf = num_rbf
+        self.rbf_type = rbf_type
+        self.activation = activation
+        self.cutoff_lower = cutoff_lower
+        self.cutoff_upper = cutoff_upper
+        self.max_z = max_z
+        self.max_num_neighbors = max_num_neighbors
+        act_class = act_class_mapping[activation]
+        self.distance_expansion = rbf_class_mapping[rbf_type](cutoff_lower, cutoff_upper, num_rbf, trainable_rbf)
+        self.tensor_embedding = TensorEmbedding(hidden_channels, num_rbf, act_class, cutoff_lower, cutoff_upper,
+                                                trainable_rbf, max_z, dtype)
+        self.layers = nn.ModuleList([Interaction(num_rbf, hidden_channels, act_class, cutoff_lower, cutoff_upper,
+                                                 equivariance_invariance_group, dtype)
+                                     for _ in range(num_layers)])
+        self.linear = nn.Linear(3 * hidden_channels, hidden_channels, dtype=dtype)
+        self.out_norm = nn.LayerNorm(3 * hidden_channels, dtype=dtype)
+        self.act = act_class()
+        self.static_shapes = static_shapes
+        # kept for API compatibility (callers swap in a periodic OptimizedDistance by attribute);
+        # the fused op reads cutoffs / box / strategy / capacity from it on every call.
+        self.distance = OptimizedDistance(cutoff_lower, cutoff_upper, max_num_pairs=-max_num_neighbors,
+                                          return_vecs=True, loop=True, check_errors=False,
+                                          resize_to_fit=not static_shapes, long_edge_index=True)
+        self.filter_mode = "exact"
+        self.table_intervals = 4096
+        self._handle = None
+        self._pack_key = None
+        self._workspace = None
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        self.tensor_embedding.reset_parameters()
+        for layer in self.layers:
+            layer.reset_parameters()
+        self.linear.reset_parameters()
+        self.out_norm.reset_parameters()
+
+    # -------------------------------------------------------------------------------------------- packing
+    def pack_weights(self, head: Optional[nn.Module], mean: float, std: float):
+        """-> (weights list in the order csrc/torch_shim.cpp::tensornet_create expects, iparams, fparams)."""
+        dev = self.linear.weight.device
+        H, K = self.hidden_channels, self.num_rbf
+        f32 = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()   # noqa: E731
+        f64 = lambda t: t.detach().to(device=dev, dtype=torch.float64)                 # noqa: E731
+        tr = lambda t: f32(t.detach().t())                                             # noqa: E731
+        te = self.tensor_embedding
+        table = self.filter_mode == "table"
+        n_int = int(self.table_intervals) if table else 0
+        empty = torch.empty(0, device=dev, dtype=torch.float32)
+        lo, hi = float(self.cutoff_lower), float(self.cutoff_upper)
+
+        if self.rbf_type == "expnorm":
+            p0, p1 = self.distance_expansion.means, self.distance_expansion.betas
+        else:
+            p0 = self.distance_expansion.offset
+            p1 = self.distance_expansion.coeff.expand(K)
+        grid = torch.linspace(0.0, hi, n_int + 1, device=dev, dtype=torch.float64) if table else None
+
+        def make_table(layers, final_act):
+            if not table:
+                return empty
+            f, df = filter_table(grid, self.rbf_type, f64(p0), f64(p1), lo, hi,
+                                 [(f64(w), f64(b)) for w, b in layers], self.activation, final_act)
+            return f32(hermite_coefficients(f, df, hi / n_int).view(n_int, 3, H, 4))
+
+        # Z_ij = emb2([emb(z_i) | emb(z_j)]) = P[z_i] + Q[z_j]      (tensornet.py:310-312)
+        emb, w2, b2 = f64(te.emb.weight), f64(te.emb2.weight), f64(te.emb2.bias)
+        P, Q = emb @ w2[:, :H].t() + b2, emb @ w2[:, H:].t()
+        # reference filter rows are h*3+g (reshape(-1,H,3), tensornet.py:325,383); kernels want g*H+h
+        perm = torch.arange(3 * H, device=dev).view(H, 3).t().reshape(-1)
+        ew = torch.cat([te.distance_proj1.weight, te.distance_proj2.weight, te.distance_proj3.weight]).detach()
+        eb = torch.cat([te.distance_proj1.bias, te.distance_proj2.bias, te.distance_proj3.bias]).detach()
+        w = [f32(p0), f32(p1), f32(P), f32(Q), f32(ew), f32(eb), make_table([(ew, eb)], False)]
+        w += [f32(l.weight) for l in te.linears_tensor] + [tr(l.weight) for l in te.linears_tensor]
+        w += [f32(te.init_norm.weight), f32(te.init_norm.bias)]
+        s0, s1 = te.linears_scalar
+        w += [f32(s0.weight), f32(s0.bias), tr(s0.weight),
+              f32(s1.weight[perm]), f32(s1.bias[perm]), tr(s1.weight[perm])]
+        w += [f32(self.out_norm.weight), f32(self.out_norm.bias), f32(self.linear.weight), f32(self.linear.bias),
+              tr(self.linear.weight)]
+        if head is not None:
+            h0, h2 = head.output_network[0], head.output_network[2]
+            w += [f32(h0.weight), f32(h0.bias), tr(h0.weight), f32(h2.weight), f32(h2.bias)]
+        else:   # features-only use: a zero head
+            w += [torch.zeros(H // 2, H, device=dev), torch.zeros(H // 2, device=dev),
+                  torch.zeros(H, H // 2, device=dev), torch.zeros(1, H // 2, device=dev), torch.zeros(1, device=dev)]
+        for layer in self.layers:
+            ls = layer.linears_scalar
+            flt = [(ls[0].weight.detach(), ls[0].bias.detach()), (ls[1].weight.detach(), ls[1].bias.detach()),
+                   (ls[2].weight.detach()[perm], ls[2].bias.detach()[perm])]
+            for wk, bk in flt:
+                w += [f32(wk), f32(bk)]
+            w.append(make_table(flt, True))
+            w += [f32(l.weight) for l in layer.linears_tensor] + [tr(l.weight) for l in layer.linears_tensor]
+        iparams = [H, K, self.num_layers, self.max_z, RBF_ID[self.rbf_type], ACT_ID[self.activation],
+                   int(self.equivariance_invariance_group == "SO(3)"), FILTER_TABLE if table else FILTER_EXACT,
+                   n_int]
+        fparams = [lo, hi, float(mean), float(std)]
+        return w, iparams, fparams
+
+    def _tensors_for_key(self, head):
+        mods = [self] if head is None else [self, head]
+        for m in mods:
+            yield from m.parameters()
+            yield from m.buffers()
+
+    def native_handle(self, head: Optional[nn.Module] = None, mean: float = 0.0, std: float = 1.0) -> int:
+        """Handle of the packed model inside the shim; repacked when any weight changed."""
+        _native.load()
+        key = (tuple((t.data_ptr(), t._version, t.device) for t in self._tensors_for_key(head)),
+               self.filter_mode, self.table_intervals, float(mean), float(std))
+        if key != self._pack_key:
+            p = self.linear.weight
+            _native.require_cuda(p, "TensorNet")
+            if p.dtype != torch.float32:
+                raise NotImplementedError("TensorNet kernels are fp32 (precision: 32); got %s" % p.dtype)
+            if self._handle is not None:
+                torch.ops.torchmdnet_b200.tensornet_destroy(self._handle)
+            w, ip, fp = self.pack_weights(head, mean, std)
+            self._handle = torch.ops.torchmdnet_b200.tensornet_create(w, ip, fp)
+            self._pack_key = key
+        return self._handle
+
+    def __del__(self):
+        try:
+            if self._handle is not None:
+                torch.ops.torchmdnet_b200.tensornet_destroy(self._handle)
+        except Exception:
+            pass
+
+    # -------------------------------------------------------------------------------------------- running
+    def energy_forces(self, z: Tensor, pos: Tensor, batch: Tensor, n_mol: int, head: Optional[nn.Module],
+                      mean: float, std: float, compute_forces: bool = True) -> Tuple[Tensor, Tensor, Tensor]:
+        """One fused evaluation: -> (y[n_mol,1], forces[N,3] (empty if not compute_forces), status int32[4]).
+        status[0] = edges found (incl. self loops), status[1] = 1 if they exceeded the capacity
+        max_num_neighbors*N (models/utils.py:234-236), status[2] = 1 if some z was outside [0,max_z)."""
+        handle = self.native_handle(head, mean, std)
+        _native.require_cuda(pos, "TensorNet")
+        if pos.dtype != torch.float32:
+            raise NotImplementedError("TensorNet kernels are fp32; got positions of dtype %s" % pos.dtype)
+        dist = self.distance
+        n = pos.shape[0]
+        max_edges = dist.max_num_pairs if dist.max_num_pairs > 0 else -dist.max_num_pairs * n
+        y, f, status, ws = torch.ops.torchmdnet_b200.tensornet_energy_forces(
+            handle, z.contiguous(), pos.detach().contiguous(), batch.contiguous(), dist.box, dist.use_periodic,
+            dist.strategy, max_edges, n_mol, compute_forces, self._workspace)
+        self._workspace = ws
+        if dist.check_errors and int(status[1]) != 0:
+            raise RuntimeError("Found num_pairs({}) > max_num_pairs({})".format(int(status[0]), max_edges))
+        return y, f, status
+
+    def debug_buffer(self, name: str, n_atoms: int, n_mol: int, dtype=torch.float32) -> Tensor:
+        """Flat view of a named intermediate of the LAST call (names as in oracle/staged_tensornet.py)."""
+        dist = self.distance
+        max_edges = dist.max_num_pairs if dist.max_num_pairs > 0 else -dist.max_num_pairs * n_atoms
+        off, nbytes = torch.ops.torchmdnet_b200.tensornet_debug_lookup(self._handle, n_atoms, max_edges, n_mol, name)
+        return self._workspace[off:off + nbytes].view(dtype)
+
+    def forward(self, z: Tensor, pos: Tensor, batch: Tensor, q: Optional[Tensor] = None,
+                s: Optional[Tensor] = None):
+        """Representation only (tensornet.py:200-234): -> (x[N,H], None, z, pos, batch).  Runs the fused forward
+        with a zero head and returns the activations of the final Linear+act."""
+        n_mol = int(batch.max()) + 1
+        self.energy_forces(z, pos, batch, n_mol, None, 0.0, 1.0, compute_forces=False)
+        x = self.debug_buffer("a3", pos.shape[0], n_mol).view(pos.shape[0], self.hidden_channels).clone()
+        return x, None, z, pos, batch
