@@ -1,0 +1,400 @@
+#!/usr/bin/env python
+"""bench.py -- atom-steps/s (energy + forces) of the B200-native TorchMD-NET hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload chignolin|md17|water] [--filter table|exact]
+    python bench.py --impl reference ...      # the reference algorithm's CPU restatement on the host cores
+
+One "step" = one energy+force evaluation (neighbour search included) of the workload on one GPU:
+  chignolin (default; BASELINE.json configs[1]): TensorNet, TensorNet-SPICE hparams, one 166-atom system, fresh
+            positions every step (MD-step variant);
+  md17      (configs[2]): TensorNet-rMD17 hparams, 8192 21-atom molecules per GPU;
+  water     (configs[3], single-GPU slice): TensorNet-ANI1X hparams, periodic water box, cell-list neighbours.
+With --gpus N > 1 (torchrun, one rank per GPU) every rank evaluates its own shard / replica with no collective in
+the step (molecules and replicas are independent): weak scaling, value = N * atoms / max-over-ranks step time.
+
+Timing: W >= 3 warm-up steps; L2 is flushed (a 512 MiB write) before every timed step, outside the timed span;
+each step is bracketed by CUDA events on the launching stream; ms_per_step = sum of the K spans / K, max over
+ranks.  `value` runs the whole step as one CUDA graph with inputs resident in HBM; `e2e` goes through the public
+calculators.External.calculate() with pinned HOST positions in and host energy+forces out, copies timed.
+"""
+import argparse
+import json
+import os
+import random
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "torchmd-net_b200"))
+import synth_inputs as S  # noqa: E402
+
+METRIC = "atom-steps/sec (energy+forces) TensorNet/ET at 1/2/4/8 B200; neighbor-list ms"
+UNIT = "atom-steps/s"
+
+HP_BASE = dict(model="tensornet", precision=32, trainable_rbf=False, activation="silu", cutoff_lower=0.0,
+               max_z=128, rbf_type="expnorm", equivariance_invariance_group="O(3)", derivative=True, atom_filter=-1,
+               prior_model=None, output_model="Scalar", reduce_op="add", num_layers=2, embedding_dimension=128)
+# hparams of the reference's example yamls (examples/TensorNet-SPICE.yaml, TensorNet-rMD17.yaml, TensorNet-ANI1X.yaml)
+HPARAMS = {
+    "chignolin": dict(HP_BASE, num_rbf=64, cutoff_upper=10.0, max_num_neighbors=128),
+    "md17": dict(HP_BASE, num_rbf=32, cutoff_upper=4.5, max_num_neighbors=32),
+    "water": dict(HP_BASE, num_rbf=32, cutoff_upper=4.5, max_num_neighbors=128),
+}
+WORKLOAD_DESC = {
+    "chignolin": "TensorNet-SPICE hparams, 166-atom chignolin-size molecule, single-system MD energy+force step",
+    "md17": "TensorNet-rMD17 hparams, 8192 synthetic 21-atom molecules per GPU, batched energy+forces",
+    "water": "TensorNet-ANI1X hparams, periodic water box, cell-list neighbours, energy+forces",
+}
+
+
+def seed_everything(s):
+    random.seed(s)
+    np.random.seed(s)
+    torch.manual_seed(s)
+
+
+def make_inputs(workload, rank, args):
+    """-> z, pos0, batch, box (numpy).  Rank r draws its own seeded shard/replica."""
+    if workload == "chignolin":
+        z, pos, batch = S.chignolin_like(seed=2 + 1000 * rank)
+        return z, pos, batch, None
+    if workload == "md17":
+        z, pos, batch = S.md17_like_batch(n_mol=args.molecules, seed=3 + 1000 * rank)
+        return z, pos, batch, None
+    z, pos, batch, box = S.water_box(args.water_side, seed=4 + 1000 * rank)
+    return z, pos, batch, box
+
+
+def step_positions(pos0, n, seed):
+    """Fresh positions per step: N(0, 0.05 A) displacements of the base geometry (cfg 2 MD variant)."""
+    return [S.md_step_noise(pos0, i, seed=seed) for i in range(n)]
+
+
+# ------------------------------------------------------------------------------------------- clocks sampler
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 <= t <= t1] or [r for _, r in self.rows[-3:]]
+        sm = sorted(float(r[0]) for r in rows if r and r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        mx = [float(r[1]) for r in rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(rows)}
+
+
+# ------------------------------------------------------------------------------------------- CPU (reference) arm
+def cpu_reference_steps(workload, hp, args, steps, warmup):
+    """Times oracle/model.py (the CPU restatement of the reference's PyTorch path, pinned to the reference's
+    goldens) on all host threads.  -> (atom-steps/s, cores, sample description)."""
+    from oracle import model as om
+    from torchmdnet.models.model import create_model
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    seed_everything(1234)
+    sd = {k: v.clone() for k, v in create_model(hp).state_dict().items()}
+    if workload == "chignolin":
+        z, pos0, batch, box = make_inputs(workload, 0, args)
+        sample = "the full 166-atom step"
+    elif workload == "md17":
+        z, pos0, batch = S.md17_like_batch(n_mol=64, seed=3)
+        box = None
+        sample = "64 of the 8192 molecules per step (the reference CPU op is O(N^2) over the whole batch)"
+    else:
+        z, pos0, batch, box = S.water_box(8, seed=4)
+        sample = "a 1536-atom periodic box (8^3 waters) per step"
+    tz, tb = torch.from_numpy(z), torch.from_numpy(batch)
+    tbox = None if box is None else torch.from_numpy(box)
+    poss = step_positions(pos0, steps + warmup, 2)
+    times = []
+    for i, p in enumerate(poss):
+        t0 = time.perf_counter()
+        om.energy_forces(sd, hp, tz, torch.from_numpy(p), tb, box=tbox)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    per = sum(times) / len(times)
+    return z.shape[0] / per, cores, "%s, %d timed step(s) after %d warm-up, %.3f s/step" % (sample, steps, warmup, per), per
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    hp = HPARAMS[args.workload]
+    steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
+    v, cores, sample, per = cpu_reference_steps(args.workload, hp, args, steps, warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warmup, "ms_per_step": per * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD_DESC[args.workload], "device": "host CPU, %d threads" % cores},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------- roofline
+def algorithmic_bytes(family, N, E, H, L):
+    """Per-LAUNCH algorithmic HBM bytes of a kernel family (SURVEY 8d per-unit figures)."""
+    node = 36 * H * N                       # one [N,9,H] fp32 tensor
+    table = {
+        "tn_msg_fwd": 2 * node + 8 * E,     # read Y, write M; per edge: i32 column + f32 distance
+        "tn_msg_bwd": 4 * node + 16 * E,    # read Y, dM, dY; write dY (backward = 2x forward)
+        "tn_embed_edge_fwd": node + 20 * E,
+        "tn_embed_edge_bwd": node + 20 * E + 12 * N,
+        "neighbors": 20 * N + 24 * E,
+        "csr": 2 * 24 * E,
+    }
+    return table.get(family, 2 * node)
+
+
+def profile_families(run_step, steps):
+    torch.ops.torchmdnet_b200.profile_enable(True)
+    for i in range(steps):
+        run_step(i)
+    torch.cuda.synchronize()
+    rep = torch.ops.torchmdnet_b200.profile_report()
+    torch.ops.torchmdnet_b200.profile_enable(False)
+    fam = {}
+    for ln in rep.strip().splitlines():
+        name, cnt, ms = ln.split()
+        fam[name] = (int(cnt), float(ms))
+    return fam
+
+
+# ------------------------------------------------------------------------------------------- main arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="chignolin", choices=list(HPARAMS))
+    ap.add_argument("--filter", default="table", choices=["table", "exact"])
+    ap.add_argument("--molecules", type=int, default=8192)
+    ap.add_argument("--water-side", type=int, default=32)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    args.warmup = max(args.warmup, 3)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node %d" % args.gpus
+
+    from torchmdnet import _native
+    from torchmdnet.calculators import External
+    from torchmdnet.models.model import create_model
+    from torchmdnet.models.utils import OptimizedDistance
+    _native.load()
+
+    hp = HPARAMS[args.workload]
+    seed_everything(1234)
+    model = create_model(hp).to(dev).eval()
+    rm = model.representation_model
+    rm.filter_mode = args.filter
+    z_np, pos0, batch_np, box = make_inputs(args.workload, rank, args)
+    if box is not None:
+        rm.distance = OptimizedDistance(hp["cutoff_lower"], hp["cutoff_upper"], max_num_pairs=-hp["max_num_neighbors"],
+                                        return_vecs=True, loop=True, check_errors=False, resize_to_fit=False,
+                                        box=torch.from_numpy(box), strategy="cell")
+    N = z_np.shape[0]
+    n_mol = int(batch_np.max()) + 1
+    K, W = args.steps, args.warmup
+    n_pos = min(K + W, 64)                                   # distinct position sets, cycled
+    poss_np = step_positions(pos0, n_pos, 2 + rank)
+    z, batch = torch.from_numpy(z_np).to(dev), torch.from_numpy(batch_np).to(dev)
+    poss = torch.stack([torch.from_numpy(p) for p in poss_np]).to(dev)       # resident in HBM
+    static_pos = poss[0].clone()
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)           # > 126 MB L2
+
+    def eager_step(i):
+        static_pos.copy_(poss[i % n_pos])
+        return model(z, static_pos, batch)
+
+    # launches per step (the library counts every kernel it launches)
+    eager_step(0)
+    torch.cuda.synchronize()
+    c0 = torch.ops.torchmdnet_b200.launch_count()
+    y, f = eager_step(1)
+    torch.cuda.synchronize()
+    launches_per_step = torch.ops.torchmdnet_b200.launch_count() - c0
+    status = rm.energy_forces(z, static_pos, batch, n_mol, model.output_model, *model._mean_std())[2].cpu()
+    E = int(status[0])
+    assert int(status[1]) == 0, "pair capacity exceeded: %d edges" % E
+
+    # whole step as one CUDA graph
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for i in range(3):
+            model(z, static_pos, batch)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        gy, gf = model(z, static_pos, batch)
+
+    def graph_step(i):
+        static_pos.copy_(poss[i % n_pos])
+        graph.replay()
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(W):
+        graph_step(i)
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    barrier()
+    t_begin = time.perf_counter()
+    for i in range(K):
+        flush.zero_()                                   # L2 flush, outside the timed span
+        ev[i][0].record()
+        graph_step(W + i)
+        ev[i][1].record()
+    barrier()
+    t_end = time.perf_counter()
+    clocks = sampler.stop(t_begin, t_end) if sampler else None
+    total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    total_ms = float(t)
+    ms_per_step = total_ms / K
+    value = world * N / (ms_per_step * 1e-3)
+
+    # ---- e2e: public API, host buffers in and out, copies inside the timed span
+    tmp = tempfile.mkdtemp()
+    ckpt = os.path.join(tmp, "bench.ckpt")
+    torch.save({"hyper_parameters": dict(hp), "state_dict": {"model." + k: v.cpu() for k, v in
+                                                              model.state_dict().items()}}, ckpt)
+    if n_mol == 1 or N % n_mol == 0:
+        emb = torch.from_numpy(z_np).view(n_mol, N // n_mol)
+    else:
+        emb = torch.from_numpy(z_np).view(1, N)
+    calc = External(ckpt, emb, dev)
+    calc.model.representation_model.filter_mode = args.filter
+    if box is not None:
+        calc.model.representation_model.distance = rm.distance
+    if emb.shape[0] != n_mol:
+        calc.batch = batch
+        calc._n_mol = n_mol
+    host_pos = [torch.from_numpy(p).pin_memory() for p in poss_np]
+    h_e = torch.empty(n_mol, 1).pin_memory()
+    h_f = torch.empty(N, 3).pin_memory()
+    Ke = K
+
+    def e2e_step(i):
+        e, frc = calc.calculate(host_pos[i % n_pos], None)
+        h_e.copy_(e, non_blocking=True)
+        h_f.copy_(frc.view(N, 3), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for i in range(W):
+        e2e_step(i)
+    barrier()
+    e2e_t = 0.0
+    for i in range(Ke):
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e2e_step(W + i)
+        e2e_t += time.perf_counter() - t0
+    barrier()
+    t = torch.tensor([e2e_t], device=dev, dtype=torch.float64)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    e2e_value = world * N / (float(t) / Ke)
+    # the e2e result must be the product's result
+    assert torch.allclose(h_f, calc.calculate(host_pos[(W + Ke - 1) % n_pos], None)[1].view(N, 3).cpu())
+
+    if rank != 0:
+        return
+    # ---- per-kernel-family device times (separate eager pass, events inside the library) -> roofline
+    fam = profile_families(eager_step, min(K, 20))
+    n_prof = min(K, 20)
+    step_ms_prof = sum(ms for _, ms in fam.values()) / n_prof
+    top = max(fam, key=lambda k: fam[k][1])
+    # the roofline is quoted for the neighbour-aggregation kernels north_star names; the table shows all
+    agg = [k for k in ("tn_msg_bwd", "tn_msg_fwd") if k in fam]
+    dom = max(agg, key=lambda k: fam[k][1]) if agg else top
+    cnt, ms = fam[dom]
+    H, L = hp["embedding_dimension"], hp["num_layers"]
+    bytes_per_launch = algorithmic_bytes(dom, N, E, H, L)
+    achieved = bytes_per_launch / (ms / cnt * 1e-3) / 1e9
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        with open(peaks_path) as fh:
+            peak, peak_src = float(json.load(fh)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
+    else:
+        peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_us": ms / cnt * 1e3,
+                "share_of_step": ms / n_prof / step_ms_prof,
+                "note": "time of the kernel = CUDA events inside the library over %d eager steps" % n_prof}
+    families = {k: {"launches_per_step": c / n_prof, "us_per_step": m / n_prof * 1e3} for k, (c, m) in
+                sorted(fam.items(), key=lambda kv: -kv[1][1])}
+
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        v, cores, sample, _ = cpu_reference_steps(args.workload, hp, args, 3, 1)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD_DESC[args.workload], "atoms_per_gpu": N, "molecules_per_gpu": n_mol,
+                       "edges_per_gpu": E, "filter_mode": args.filter, "neighbor_strategy": rm.distance.strategy,
+                       "l2": "flushed (512 MiB write) before every timed step",
+                       "step": "one CUDA graph replay: neighbour list + CSR + forward + analytic backward",
+                       "parallelism": "independent replicas/shards per GPU, no collective in the step"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": N * 12,
+                    "d2h_bytes_per_step": N * 12 + n_mol * 4, "api": "torchmdnet.calculators.External.calculate"},
+            "gpu_launches": int(launches_per_step) * K, "launches_per_step": int(launches_per_step),
+            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "kernel_families": families,
+            "energy_checksum": float(gy.double().sum())}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -61,6 +61,15 @@ const char* tmdn_last_error(void);
 /* 1 if `stream` is being captured into a CUDA graph, 0 if not, <0 on error. */
 int tmdn_is_stream_capturing(tmdn_stream_t stream);
 
+/* Measurement hooks (new; no reference counterpart).  tmdn_launch_count: kernels launched by this library since
+ * load (process-wide).  tmdn_profile_enable(1) makes every entry point bracket each kernel family with a CUDA
+ * event pair on the caller's stream (skipped while the stream is being captured); tmdn_profile_report
+ * synchronises those events and writes one line "family launches total_ms" per family into buf;
+ * tmdn_profile_enable(0|1) also clears what was recorded. */
+long long tmdn_launch_count(void);
+int tmdn_profile_enable(int on);
+int tmdn_profile_report(char* buf, size_t buf_bytes);
+
 /* ---------------------------------------------------------------- neighbor list
  * Semantics = the reference CUDA op: all pairs of atoms of the same batch with
  * cutoff_lower^2 <= d^2 < cutoff_upper^2; delta = pos[i]-pos[j] (minimum image if use_periodic:

@@ -11,12 +11,13 @@ from oracle import neighbors as onb
 pytestmark = pytest.mark.gpu
 
 
-def run_op(strategy, pos, batch, box, lo, hi, max_pairs, loop, transpose):
+def run_op(strategy, pos, batch, box, lo, hi, max_pairs, loop, transpose, periodic=None):
     from torchmdnet.neighbors import get_neighbor_pairs_kernel
     dev = "cuda"
     tb = torch.empty(0, 0) if box is None else torch.from_numpy(np.asarray(box)).to(torch.from_numpy(pos).dtype)
     nb, dl, ds, cnt = get_neighbor_pairs_kernel(strategy, torch.from_numpy(pos).to(dev),
-                                                torch.from_numpy(batch).to(dev), tb, box is not None, lo, hi,
+                                                torch.from_numpy(batch).to(dev), tb,
+                                                (box is not None) if periodic is None else periodic, lo, hi,
                                                 max_pairs, loop, transpose)
     torch.cuda.synchronize()
     return nb.cpu().numpy(), dl.cpu().numpy(), ds.cpu().numpy(), int(cnt.item())
@@ -93,7 +94,8 @@ def test_sweep_against_oracle(strategy, dtype):
             ref = onb.neighbor_pairs(pos, batch, None if box is None else box.astype(dtype), 0.0, cutoff, loop,
                                      transpose, d2_rule=True, rect=rect)
         n_ref = ref[0].shape[1]
-        nb, dl, ds, cnt = run_op(strategy, pos, batch, obox, 0.0, cutoff, max(n_ref, 1), loop, transpose)
+        nb, dl, ds, cnt = run_op(strategy, pos, batch, obox, 0.0, cutoff, max(n_ref, 1), loop, transpose,
+                                 periodic=periodic)
         assert cnt == n_ref, (n_batches, cutoff, loop, transpose, boxkind)
         a = onb.canonical_order(nb, dl, ds)
         b = onb.canonical_order(*ref)

@@ -9,6 +9,16 @@
 
 // ------------------------------------------------------------------ error plumbing (never throws)
 void tmdn_set_error(const char* fmt, ...);
+// every kernel launch of the library goes through TMDN_LAUNCH_CHECK, which also counts it (tmdn_launch_count)
+void tmdn_note_launch();
+// Optional per-kernel-family device timing (tmdn_profile_*): a KTimer brackets the launches issued in its scope
+// with a CUDA event pair on `stream` when profiling is enabled and the stream is not being captured.
+struct KTimer {
+    KTimer(const char* name, cudaStream_t stream);
+    ~KTimer();
+    int slot;
+    cudaStream_t stream;
+};
 
 #define TMDN_CHECK_ARG(cond, ...)                 \
     do {                                          \
@@ -31,6 +41,7 @@ void tmdn_set_error(const char* fmt, ...);
 #define TMDN_LAUNCH_CHECK()                                                                     \
     do {                                                                                        \
         cudaError_t err__ = cudaPeekAtLastError();                                              \
+        tmdn_note_launch();                                                                     \
         if (err__ != cudaSuccess) {                                                             \
             tmdn_set_error("kernel launch failed at %s:%d: %s", __FILE__, __LINE__,             \
                            cudaGetErrorString(err__));                                          \

@@ -136,7 +136,8 @@ static inline GemmP gemm_desc(const float* A, int lda, const float* W, const flo
     return p;
 }
 
-static inline int gemm_launch(int epi, const GemmBatch& b, cudaStream_t stream) {
+static inline int gemm_launch(int epi, const GemmBatch& b, cudaStream_t stream, const char* tag = "node_gemm") {
+    KTimer ktimer__(tag, stream);
     int maxM = 0, maxN = 0;
     for (int i = 0; i < b.n; ++i) {
         if (b.p[i].M > maxM) maxM = b.p[i].M;
@@ -155,10 +156,10 @@ static inline int gemm_launch(int epi, const GemmBatch& b, cudaStream_t stream) 
     return TMDN_OK;
 }
 
-static inline int gemm1(int epi, const GemmP& p, cudaStream_t stream) {
+static inline int gemm1(int epi, const GemmP& p, cudaStream_t stream, const char* tag = "node_gemm") {
     GemmBatch b;
     memset(&b, 0, sizeof(b));
     b.p[0] = p;
     b.n = 1;
-    return gemm_launch(epi, b, stream);
+    return gemm_launch(epi, b, stream, tag);
 }

@@ -24,6 +24,72 @@ extern "C" int tmdn_is_stream_capturing(tmdn_stream_t stream) {
     return st == cudaStreamCaptureStatusActive ? 1 : 0;
 }
 
+// ------------------------------------------------------------------ launch counter + per-kernel timing
+#include <atomic>
+#include <mutex>
+#include <vector>
+#include <map>
+#include <string>
+static std::atomic<long long> g_launches{0};
+void tmdn_note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+extern "C" long long tmdn_launch_count(void) { return g_launches.load(); }
+
+namespace {
+struct TimedSpan { std::string name; cudaEvent_t e0, e1; };
+std::mutex g_prof_mu;
+std::atomic<int> g_prof_on{0};
+std::vector<TimedSpan> g_spans;
+}  // namespace
+
+KTimer::KTimer(const char* name, cudaStream_t s) : slot(-1), stream(s) {
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess || st != cudaStreamCaptureStatusNone) return;
+    TimedSpan sp;
+    sp.name = name;
+    if (cudaEventCreate(&sp.e0) != cudaSuccess) return;
+    if (cudaEventCreate(&sp.e1) != cudaSuccess) { cudaEventDestroy(sp.e0); return; }
+    cudaEventRecord(sp.e0, s);
+    std::lock_guard<std::mutex> lock(g_prof_mu);
+    g_spans.push_back(sp);
+    slot = (int)g_spans.size() - 1;
+}
+KTimer::~KTimer() {
+    if (slot < 0) return;
+    std::lock_guard<std::mutex> lock(g_prof_mu);
+    if (slot < (int)g_spans.size()) cudaEventRecord(g_spans[slot].e1, stream);
+}
+
+extern "C" int tmdn_profile_enable(int on) {
+    std::lock_guard<std::mutex> lock(g_prof_mu);
+    for (auto& sp : g_spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
+    g_spans.clear();
+    g_prof_on.store(on ? 1 : 0);
+    return TMDN_OK;
+}
+// Writes "name count total_ms\n" per kernel family (sorted by name) into buf; synchronises the recorded events.
+extern "C" int tmdn_profile_report(char* buf, size_t buf_bytes) {
+    TMDN_CHECK_ARG(buf && buf_bytes > 0, "profile_report: null buffer");
+    std::lock_guard<std::mutex> lock(g_prof_mu);
+    std::map<std::string, std::pair<long long, double>> agg;
+    for (auto& sp : g_spans) {
+        float ms = 0.f;
+        TMDN_CUDA(cudaEventSynchronize(sp.e1));
+        TMDN_CUDA(cudaEventElapsedTime(&ms, sp.e0, sp.e1));
+        auto& a = agg[sp.name];
+        a.first += 1;
+        a.second += ms;
+    }
+    size_t off = 0;
+    buf[0] = 0;
+    for (auto& kv : agg) {
+        int n = snprintf(buf + off, buf_bytes - off, "%s %lld %.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+        if (n < 0 || (size_t)n >= buf_bytes - off) break;
+        off += (size_t)n;
+    }
+    return TMDN_OK;
+}
+
 namespace {
 constexpr int SCAN_THREADS = 1024;
 constexpr int SCAN_ITEMS = 4;

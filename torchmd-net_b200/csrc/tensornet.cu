@@ -753,25 +753,28 @@ int eval_filter_exact(const tmdn_tensornet_model* m, const tmdn_filter_set& fs, 
         if (has_act) {
             GemmP p = gemm_desc(a, in, fs.w[k], fs.b[k], ha, out, (int)P, out, in);
             p.C2 = w.fh[k]; p.act = m->activation;
-            TMDN_TRY(gemm1(EPI_ACT, p, stream));
+            TMDN_TRY(gemm1(EPI_ACT, p, stream, "filter_gemm"));
             GemmP q = gemm_desc(t, in, fs.w[k], nullptr, tt, out, (int)P, out, in);
             q.aux = w.fh[k]; q.ldaux = out; q.act = m->activation;
-            TMDN_TRY(gemm1(EPI_MULGRAD, q, stream));
+            TMDN_TRY(gemm1(EPI_MULGRAD, q, stream, "filter_gemm"));
         } else {
             GemmP p = gemm_desc(a, in, fs.w[k], fs.b[k], ha, out, (int)P, out, in);
-            TMDN_TRY(gemm1(EPI_NONE, p, stream));
+            TMDN_TRY(gemm1(EPI_NONE, p, stream, "filter_gemm"));
             GemmP q = gemm_desc(t, in, fs.w[k], nullptr, tt, out, (int)P, out, in);
-            TMDN_TRY(gemm1(EPI_NONE, q, stream));
+            TMDN_TRY(gemm1(EPI_NONE, q, stream, "filter_gemm"));
         }
         a = ha;
         t = tt;
     }
     (void)K; (void)N;
     const long long tot = (long long)P * fs.dims[fs.n_layers];
-    tn_filter_finalize_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>((const float4*)w.geom, (long long)P,
-                                                                            fs.dims[fs.n_layers], m->cutoff_lower,
-                                                                            m->cutoff_upper, F, dF);
-    TMDN_LAUNCH_CHECK();
+    {
+        KTimer ktimer__("tn_filter_finalize_kernel", stream);
+        tn_filter_finalize_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>((const float4*)w.geom, (long long)P,
+                                                                                fs.dims[fs.n_layers], m->cutoff_lower,
+                                                                                m->cutoff_upper, F, dF);
+        TMDN_LAUNCH_CHECK();
+    }
     return TMDN_OK;
 }
 
@@ -849,13 +852,22 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
     }
 
     // ---- graph: pairs (incl. transposes and self loops) -> CSR by target = row 0 (tensornet.py:313-315)
-    TMDN_TRY(tmdn_neighbors_f32(strategy, pos, batch, n_atoms, box, use_periodic, m->cutoff_lower, m->cutoff_upper, 1, 1,
-                                P, w.nbr, w.deltas, w.dist, w.num_found, nbr_ws, nbr_ws_bytes, stream_));
-    TMDN_TRY(tmdn_csr_from_pairs(w.nbr, w.deltas, w.dist, w.num_found, P, n_atoms, 0, w.row_ptr, w.col, w.geom,
-                                 w.csr_ws, w.csr_ws_bytes, stream_));
+    {
+        KTimer ktimer__("neighbors", stream);
+        TMDN_TRY(tmdn_neighbors_f32(strategy, pos, batch, n_atoms, box, use_periodic, m->cutoff_lower, m->cutoff_upper,
+                                    1, 1, P, w.nbr, w.deltas, w.dist, w.num_found, nbr_ws, nbr_ws_bytes, stream_));
+    }
+    {
+        KTimer ktimer__("csr", stream);
+        TMDN_TRY(tmdn_csr_from_pairs(w.nbr, w.deltas, w.dist, w.num_found, P, n_atoms, 0, w.row_ptr, w.col, w.geom,
+                                     w.csr_ws, w.csr_ws_bytes, stream_));
+    }
     TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
-    tn_prep_kernel<<<(unsigned)cdiv(N, 256), 256, 0, stream>>>(z, w.z32, N, m->max_z, w.num_found, (long long)P, status);
-    TMDN_LAUNCH_CHECK();
+    {
+        KTimer ktimer__("tn_prep_kernel", stream);
+        tn_prep_kernel<<<(unsigned)cdiv(N, 256), 256, 0, stream>>>(z, w.z32, N, m->max_z, w.num_found, (long long)P, status);
+        TMDN_LAUNCH_CHECK();
+    }
 
     const float4* geom = (const float4*)w.geom;
     const int apb = H >= 128 ? 1 : 128 / H;
@@ -868,10 +880,13 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
     FilterView fv_emb, fv_layer[TMDN_MAX_LAYERS];
     if (!tab) {
         const long long tot = (long long)P * m->num_rbf;
-        tn_rbf_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(geom, w.row_ptr, N, (long long)P, m->num_rbf,
-                                                                    m->rbf_type, m->cutoff_lower, m->cutoff_upper,
-                                                                    m->rbf_p0, m->rbf_p1, w.R, w.dR);
-        TMDN_LAUNCH_CHECK();
+        {
+            KTimer ktimer__("tn_rbf_kernel", stream);
+            tn_rbf_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(geom, w.row_ptr, N, (long long)P, m->num_rbf,
+                                                                        m->rbf_type, m->cutoff_lower, m->cutoff_upper,
+                                                                        m->rbf_p0, m->rbf_p1, w.R, w.dR);
+            TMDN_LAUNCH_CHECK();
+        }
         TMDN_TRY(eval_filter_exact(m, m->emb_filter, w, n_atoms, P, w.F[0], w.dF[0], stream));
         for (int l = 0; l < L; ++l)
             TMDN_TRY(eval_filter_exact(m, m->layer_filter[l], w, n_atoms, P, w.F[l + 1], w.dF[l + 1], stream));
@@ -880,13 +895,16 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
     for (int l = 0; l < L; ++l) fv_layer[l] = make_view(m, m->layer_filter[l], w.F[l + 1], w.dF[l + 1]);
 
     // ---- E1 + embedding node stage
-    if (tab)
-        tn_embed_edge_fwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H,
-                                                              w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
-    else
-        tn_embed_edge_fwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H,
-                                                               w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
-    TMDN_LAUNCH_CHECK();
+    {
+        KTimer ktimer__("tn_embed_edge_fwd", stream);
+        if (tab)
+            tn_embed_edge_fwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H,
+                                                                  w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+        else
+            tn_embed_edge_fwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H,
+                                                                   w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+        TMDN_LAUNCH_CHECK();
+    }
     {
         GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
         p.C2 = w.h1; p.act = act;
@@ -900,27 +918,39 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
     }
     // ---- interaction layers
     if (L > 0) {
-        tn_normalize_fwd<<<egrid, 256, 0, stream>>>(w.X[0], w.Xh, NH, H);
-        TMDN_LAUNCH_CHECK();
+        {
+            KTimer ktimer__("tn_normalize_fwd", stream);
+            tn_normalize_fwd<<<egrid, 256, 0, stream>>>(w.X[0], w.Xh, NH, H);
+            TMDN_LAUNCH_CHECK();
+        }
     }
     for (int l = 0; l < L; ++l) {
         TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.Xh, w.Y[l], m->layer_mix[l], N, H), stream));
-        if (tab)
-            tn_msg_fwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N, H, m->so3,
-                                                           w.M[l], w.tauh);
-        else
-            tn_msg_fwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N, H, m->so3,
-                                                            w.M[l], w.tauh);
-        TMDN_LAUNCH_CHECK();
+        {
+            KTimer ktimer__("tn_msg_fwd", stream);
+            if (tab)
+                tn_msg_fwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N, H, m->so3,
+                                                               w.M[l], w.tauh);
+            else
+                tn_msg_fwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N, H, m->so3,
+                                                                w.M[l], w.tauh);
+            TMDN_LAUNCH_CHECK();
+        }
         TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
         // Xh is both input (residual) and, for the next layer, output: safe because each thread reads its own
         // (atom, channel) column before writing it.
-        tn_update_fwd<<<egrid, 256, 0, stream>>>(w.Xh, w.dX[l], w.X[l + 1], l + 1 < L ? w.Xh : nullptr, NH, H);
-        TMDN_LAUNCH_CHECK();
+        {
+            KTimer ktimer__("tn_update_fwd", stream);
+            tn_update_fwd<<<egrid, 256, 0, stream>>>(w.Xh, w.dX[l], w.X[l + 1], l + 1 < L ? w.Xh : nullptr, NH, H);
+            TMDN_LAUNCH_CHECK();
+        }
     }
     // ---- output norm, linear, head, reduce
-    tn_out_norm_fwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, m->out_ln_b, w.xl, w.stat, N, H);
-    TMDN_LAUNCH_CHECK();
+    {
+        KTimer ktimer__("tn_out_norm_fwd", stream);
+        tn_out_norm_fwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, m->out_ln_b, w.xl, w.stat, N, H);
+        TMDN_LAUNCH_CHECK();
+    }
     {
         GemmP p = gemm_desc(w.xl, 3 * H, m->out_w, m->out_b, w.a3, H, N, H, 3 * H);
         p.C2 = w.h3; p.act = act;
@@ -929,48 +959,75 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
         q.C2 = w.h4; q.act = act;
         TMDN_TRY(gemm1(EPI_ACT, q, stream));
     }
-    tn_head_energy<<<(unsigned)cdiv(N, 4), 128, 0, stream>>>(w.a4, m->head_w2, m->head_b2, m->std, w.e_atom, N, H / 2);
-    TMDN_LAUNCH_CHECK();
-    tn_mol_reduce<<<(unsigned)n_mol, 128, 0, stream>>>(w.e_atom, batch, N, m->mean, energy);
-    TMDN_LAUNCH_CHECK();
+    {
+        KTimer ktimer__("tn_head_energy", stream);
+        tn_head_energy<<<(unsigned)cdiv(N, 4), 128, 0, stream>>>(w.a4, m->head_w2, m->head_b2, m->std, w.e_atom, N, H / 2);
+        TMDN_LAUNCH_CHECK();
+    }
+    {
+        KTimer ktimer__("tn_mol_reduce", stream);
+        tn_mol_reduce<<<(unsigned)n_mol, 128, 0, stream>>>(w.e_atom, batch, N, m->mean, energy);
+        TMDN_LAUNCH_CHECK();
+    }
     if (!forces) return TMDN_OK;
 
     // ================================================================= backward (dE_total/dpos)
     TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
     {
         const long long tot = (long long)N * (H / 2);
-        tn_head_seed_bwd<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(w.h4, m->head_w2, m->std, act, w.d4, tot, H / 2);
-        TMDN_LAUNCH_CHECK();
+        {
+            KTimer ktimer__("tn_head_seed_bwd", stream);
+            tn_head_seed_bwd<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(w.h4, m->head_w2, m->std, act, w.d4, tot, H / 2);
+            TMDN_LAUNCH_CHECK();
+        }
         GemmP p = gemm_desc(w.d4, H / 2, m->head_w1T, nullptr, w.d3, H, N, H, H / 2);
         p.aux = w.h3; p.ldaux = H; p.act = act;
         TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
         GemmP q = gemm_desc(w.d3, H, m->out_wT, nullptr, w.dxl, 3 * H, N, 3 * H, H);
         TMDN_TRY(gemm1(EPI_NONE, q, stream));
     }
-    tn_out_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
-    TMDN_LAUNCH_CHECK();
+    {
+        KTimer ktimer__("tn_out_norm_bwd", stream);
+        tn_out_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
+        TMDN_LAUNCH_CHECK();
+    }
     for (int l = L - 1; l >= 0; --l) {
-        tn_update_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.dX[l], w.dB, NH, H);
-        TMDN_LAUNCH_CHECK();
+        {
+            KTimer ktimer__("tn_update_bwd", stream);
+            tn_update_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.dX[l], w.dB, NH, H);
+            TMDN_LAUNCH_CHECK();
+        }
         TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.dB, w.dC, m->layer_mixT[l] + 3, N, H), stream));
-        tn_prod_bwd<<<egrid, 256, 0, stream>>>(w.Y[l], w.M[l], w.dC, w.dB, NH, H, m->so3);
-        TMDN_LAUNCH_CHECK();
-        if (tab)
-            tn_msg_bwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
-                                                           w.gpos, N, H);
-        else
-            tn_msg_bwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
-                                                            w.gpos, N, H);
-        TMDN_LAUNCH_CHECK();
+        {
+            KTimer ktimer__("tn_prod_bwd", stream);
+            tn_prod_bwd<<<egrid, 256, 0, stream>>>(w.Y[l], w.M[l], w.dC, w.dB, NH, H, m->so3);
+            TMDN_LAUNCH_CHECK();
+        }
+        {
+            KTimer ktimer__("tn_msg_bwd", stream);
+            if (tab)
+                tn_msg_bwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
+                                                               w.gpos, N, H);
+            else
+                tn_msg_bwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
+                                                                w.gpos, N, H);
+            TMDN_LAUNCH_CHECK();
+        }
         GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
         for (int g = 0; g < 3; ++g) b.p[g].accumulate = 1;
         TMDN_TRY(gemm_launch(EPI_NONE, b, stream));
-        tn_normalize_bwd<<<egrid, 256, 0, stream>>>(w.X[l], w.dXa, NH, H);
-        TMDN_LAUNCH_CHECK();
+        {
+            KTimer ktimer__("tn_normalize_bwd", stream);
+            tn_normalize_bwd<<<egrid, 256, 0, stream>>>(w.X[l], w.dXa, NH, H);
+            TMDN_LAUNCH_CHECK();
+        }
     }
     // embedding node stage backward
-    tn_embed_scale_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.iasm, w.fias, w.h2, act, w.dh2, NH, H);
-    TMDN_LAUNCH_CHECK();
+    {
+        KTimer ktimer__("tn_embed_scale_bwd", stream);
+        tn_embed_scale_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.iasm, w.fias, w.h2, act, w.dh2, NH, H);
+        TMDN_LAUNCH_CHECK();
+    }
     {
         GemmP p = gemm_desc(w.dh2, 3 * H, m->emb_w2T, nullptr, w.dh1, 2 * H, N, 2 * H, 3 * H);
         p.aux = w.h1; p.ldaux = 2 * H; p.act = act;
@@ -979,14 +1036,20 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
         TMDN_TRY(gemm1(EPI_NONE, q, stream));
         TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.dXa, w.dB, m->emb_mixT, N, H), stream));
     }
-    tn_embed_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.ias, m->emb_ln_w, w.dnh, w.dB, N, H);
-    TMDN_LAUNCH_CHECK();
-    if (tab)
-        tn_embed_edge_bwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
-                                                              w.gpos, forces, N, H);
-    else
-        tn_embed_edge_bwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
-                                                               w.gpos, forces, N, H);
-    TMDN_LAUNCH_CHECK();
+    {
+        KTimer ktimer__("tn_embed_norm_bwd", stream);
+        tn_embed_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.ias, m->emb_ln_w, w.dnh, w.dB, N, H);
+        TMDN_LAUNCH_CHECK();
+    }
+    {
+        KTimer ktimer__("tn_embed_edge_bwd", stream);
+        if (tab)
+            tn_embed_edge_bwd<true><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
+                                                                  w.gpos, forces, N, H);
+        else
+            tn_embed_edge_bwd<false><<<rgrid, rblock, 0, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
+                                                                   w.gpos, forces, N, H);
+        TMDN_LAUNCH_CHECK();
+    }
     return TMDN_OK;
 }

@@ -335,6 +335,14 @@ std::vector<int64_t> tensornet_debug_lookup(int64_t handle, int64_t n_atoms, int
     return {(int64_t)off, (int64_t)bytes};
 }
 
+int64_t launch_count() { return (int64_t)tmdn_launch_count(); }
+void profile_enable(bool on) { TMDN_CALL(tmdn_profile_enable(on ? 1 : 0)); }
+std::string profile_report() {
+    std::vector<char> buf(1 << 16);
+    TMDN_CALL(tmdn_profile_report(buf.data(), buf.size()));
+    return std::string(buf.data());
+}
+
 }  // namespace
 
 TORCH_LIBRARY(torchmdnet_neighbors, m) {
@@ -357,6 +365,9 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
           "bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces, Tensor? workspace) -> "
           "(Tensor, Tensor, Tensor, Tensor)",
           tensornet_energy_forces);
+    m.def("launch_count() -> int", launch_count);
+    m.def("profile_enable(bool on) -> ()", profile_enable);
+    m.def("profile_report() -> str", profile_report);
     m.def("tensornet_debug_lookup(int handle, int n_atoms, int max_edges, int n_mol, str name) -> int[]",
           tensornet_debug_lookup);
 }

@@ -1,7 +1,9 @@
 """``External`` -- the adapter MD engines (TorchMD / OpenMM) call, torchmdnet/calculators.py:21-56.
 
 Same constructor and ``calculate(pos, box)`` contract; the model it drives is the fused CUDA pipeline, so
-``device`` must be a CUDA device.  As in the reference, ``box`` is accepted and ignored (calculators.py:50-56);
+``device`` must be a CUDA device.  Because the atom types and the number of replicas are fixed at construction,
+the whole step (neighbour list, forward, analytic backward) is captured once into a CUDA graph after two eager
+warm-up calls and replayed afterwards (``use_cuda_graph=False`` keeps eager launches).  As in the reference, ``box`` is accepted and ignored (calculators.py:50-56);
 periodic evaluation is selected on the model (``model.representation_model.distance = OptimizedDistance(...,
 box=...)``).
 """
@@ -18,7 +20,7 @@ tranforms = {
 
 
 class External:
-    def __init__(self, netfile, embeddings, device="cpu", output_transform=None):
+    def __init__(self, netfile, embeddings, device="cpu", output_transform=None, use_cuda_graph=True):
         self.model = load_model(netfile, device=device, derivative=True)
         self.device = device
         self.n_atoms = embeddings.size(1)
@@ -28,6 +30,11 @@ class External:
         # the number of replicas is fixed: tell the head so that no step needs a batch.max() sync
         self.model.output_model.dim_size = int(embeddings.size(0))
         self._n_mol = int(embeddings.size(0))
+        self.use_cuda_graph = use_cuda_graph
+        self._calls = 0
+        self._graph = None
+        self._static_pos = None
+        self._static_out = None
         if not output_transform:
             self.output_transformer = lambda energy, forces: (energy, forces)
         elif output_transform in tranforms:
@@ -35,10 +42,31 @@ class External:
         else:
             self.output_transformer = eval(output_transform)
 
-    def calculate(self, pos, box):
-        pos = pos.to(self.device).type(torch.float32).reshape(-1, 3)
+    def _evaluate(self, pos):
         m = self.model
         mean, std = m._mean_std()
         energy, forces, _ = m.representation_model.energy_forces(self.embeddings, pos, self.batch, self._n_mol,
                                                                  m.output_model, mean, std, compute_forces=True)
+        return energy, forces
+
+    def invalidate_graph(self):
+        """Call after changing the model (weights, filter mode, distance module) to re-capture."""
+        self._graph, self._calls = None, 0
+
+    def calculate(self, pos, box):
+        self._calls += 1
+        if not self.use_cuda_graph or self._calls <= 2:
+            pos = pos.to(self.device, non_blocking=True).type(torch.float32).reshape(-1, 3)
+            energy, forces = self._evaluate(pos)
+        else:
+            if self._graph is None:
+                self._static_pos = torch.empty(self.embeddings.numel(), 3, device=self.device)
+                self._static_pos.copy_(pos.reshape(-1, 3))
+                torch.cuda.synchronize()
+                self._graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self._graph):
+                    self._static_out = self._evaluate(self._static_pos)
+            self._static_pos.copy_(pos.reshape(-1, 3), non_blocking=True)     # H2D (or D2D) + dtype cast
+            self._graph.replay()
+            energy, forces = (t.clone() for t in self._static_out)
         return self.output_transformer(energy.detach(), forces.reshape(-1, self.n_atoms, 3).detach())
