@@ -165,7 +165,7 @@ def test_brute_and_cell_agree_at_scale():
     rkey = v[1].astype(np.int64) * pos.shape[0] + v[0]
     assert np.array_equal(np.sort(key), np.sort(rkey))            # symmetric
     assert np.unique(key).size == key.size                          # no duplicates
-    assert ds_c[:cnt_c].max() < 5.0 and ds_c[:cnt_c].min() > 0
+    assert ds_c[:cnt_c].max() <= 5.0 and ds_c[:cnt_c].min() > 0   # d^2 < 25 may round to d == 5.0f
     # a 20k-atom slab of targets against the tiled brute kernel restricted through batch ids is not possible
     # (different batch ids change the pair set), so compare full brute at 100k atoms instead
     pos2, box2 = S.uniform_gas(100000, seed=8)
