@@ -1,0 +1,285 @@
+// csr_direct.cu -- neighbour search straight into the CSR-by-target edge structure the model kernels consume.
+//
+// The reference materialises a padded pair list (neighbors/common.cuh:64-116) that its models then index with
+// gathers and atomics.  The fused models here never need that list: one warp per target atom walks its candidate
+// sources (its molecule's index range for brute, the 27 neighbouring cells for cell), counts the hits with
+// ballot/popc, a scan turns counts into row pointers, and a second identical walk writes (col, geom) in place.
+// No atomics on the output, no sort, and the edge order inside a row is a pure function of the positions
+// (ascending source index for brute; cell-traversal order with cells internally sorted by index for cell), so
+// every downstream segmented sum is bit-reproducible.  Same pair set and same rounding as tmdn_neighbors_f32.
+#include "common.cuh"
+#include "nbr_common.cuh"
+#include "scan.cuh"
+
+namespace {
+using namespace nbr;
+
+constexpr int CD_WARPS = 8;  // warps (target atoms) per CTA
+
+struct EdgeOut {
+    const int* row_ptr;  // null in the counting pass
+    int* row_cnt;        // counting pass output
+    int32_t* col;
+    float4* geom;
+    long long cap;
+};
+
+// first index in [0,n) with batch[idx] >= v (batch sorted ascending)
+__device__ __forceinline__ int lower_bound_batch(const int64_t* __restrict__ batch, int n, long long v) {
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (batch[mid] < v) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+template <bool FILL>
+__device__ __forceinline__ void emit(bool hit, int lane, int j, float dx, float dy, float dz, float d2, int& run,
+                                     long long base, const EdgeOut& o) {
+    const unsigned m = __ballot_sync(0xffffffffu, hit);
+    if (FILL && hit) {
+        const long long slot = base + run + __popc(m & ((1u << lane) - 1u));
+        if (slot < o.cap) {
+            float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (d2 > 0.f) {
+                const float d = __fsqrt_rn(d2);
+                const float inv = 1.0f / d;
+                g = make_float4(dx * inv, dy * inv, dz * inv, d);
+            }
+            o.col[slot] = j;
+            o.geom[slot] = g;
+        }
+    }
+    run += __popc(m);
+}
+
+// ------------------------------------------------------------------ brute: sources = the target's own molecule
+template <bool FILL>
+__global__ void __launch_bounds__(CD_WARPS * 32)
+csr_brute_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int n, Box3<float> box, int periodic,
+                 float lo2, float hi2, EdgeOut out) {
+    const int i = blockIdx.x * CD_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const long long bi = batch[i];
+    const int m0 = lower_bound_batch(batch, n, bi), m1 = lower_bound_batch(batch, n, bi + 1);
+    const float xi = pos[3 * (size_t)i], yi = pos[3 * (size_t)i + 1], zi = pos[3 * (size_t)i + 2];
+    const long long base = FILL ? out.row_ptr[i] : 0;
+    int run = 0;
+    for (int j0 = m0; j0 < m1; j0 += 32) {
+        const int j = j0 + lane;
+        bool hit = false;
+        float dx = 0.f, dy = 0.f, dz = 0.f, d2 = 0.f;
+        if (j < m1) {
+            if (j == i) {
+                hit = true;  // self loop (loop=True in both models)
+            } else {
+                dx = rn_sub(xi, pos[3 * (size_t)j]);
+                dy = rn_sub(yi, pos[3 * (size_t)j + 1]);
+                dz = rn_sub(zi, pos[3 * (size_t)j + 2]);
+                if (periodic) min_image_tric(dx, dy, dz, box);
+                d2 = dist2(dx, dy, dz);
+                hit = d2 < hi2 && d2 >= lo2;
+            }
+        }
+        emit<FILL>(hit, lane, j, dx, dy, dz, d2, run, base, out);
+    }
+    if (!FILL && lane == 0) out.row_cnt[i] = run;
+}
+
+// ------------------------------------------------------------------ cell list
+// cells are filled by atomics (arbitrary order); re-rank every cell by atom index so traversal order is deterministic
+__global__ void cell_rank_kernel(const SortedAtom<float>* __restrict__ tmp, const long long* __restrict__ tmp_batch,
+                                 const int* __restrict__ cell_start, const int* __restrict__ cell_of,
+                                 const int* __restrict__ slot_of, int n, SortedAtom<float>* __restrict__ spos,
+                                 long long* __restrict__ sbatch) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int c = cell_of[i];
+    const int cs = cell_start[c], ce = cell_start[c + 1];
+    int rank = 0;
+    for (int k = cs; k < ce; ++k) rank += tmp[k].idx < i ? 1 : 0;
+    const int src = cs + slot_of[i];
+    spos[cs + rank] = tmp[src];
+    sbatch[cs + rank] = tmp_batch[src];
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(CD_WARPS * 32)
+csr_cell_kernel(const SortedAtom<float>* __restrict__ spos, const long long* __restrict__ sbatch,
+                const int* __restrict__ cell_start, CellGrid<float> g, int n, int periodic, float lo2, float hi2,
+                EdgeOut out) {
+    const int a = blockIdx.x * CD_WARPS + (threadIdx.x >> 5);  // position in the cell-sorted order
+    const int lane = threadIdx.x & 31;
+    if (a >= n) return;
+    const SortedAtom<float> me = spos[a];
+    const long long ba = sbatch[a];
+    // recompute the cell of `a` exactly as cell_assign_kernel did
+    const int cx = cell_coord(me.x, g.L[0], g.n[0]), cy = cell_coord(me.y, g.L[1], g.n[1]),
+              cz = cell_coord(me.z, g.L[2], g.n[2]);
+    const long long base = FILL ? out.row_ptr[me.idx] : 0;
+    int run = 0;
+    for (int oz = g.lo[2]; oz <= g.hi[2]; ++oz) {
+        const int z = (cz + oz + g.n[2]) % g.n[2];
+        for (int oy = g.lo[1]; oy <= g.hi[1]; ++oy) {
+            const int y = (cy + oy + g.n[1]) % g.n[1];
+            const int row0 = g.n[0] * (y + g.n[1] * z);
+            // the x-neighbourhood of a row of cells is one contiguous range of the sorted array, or two when it wraps
+            int xr[2][2];
+            int nr = 1;
+            if (g.n[0] <= 3) {
+                xr[0][0] = 0; xr[0][1] = g.n[0] - 1;         // lo..hi covers every cell of the row
+            } else if (cx == 0) {
+                xr[0][0] = 0; xr[0][1] = 1; xr[1][0] = g.n[0] - 1; xr[1][1] = g.n[0] - 1; nr = 2;
+            } else if (cx == g.n[0] - 1) {
+                xr[0][0] = 0; xr[0][1] = 0; xr[1][0] = cx - 1; xr[1][1] = cx; nr = 2;
+            } else {
+                xr[0][0] = cx - 1; xr[0][1] = cx + 1;
+            }
+            for (int r = 0; r < nr; ++r) {
+                const int ks = cell_start[row0 + xr[r][0]], ke = cell_start[row0 + xr[r][1] + 1];
+                for (int k0 = ks; k0 < ke; k0 += 32) {
+                    const int k = k0 + lane;
+                    bool hit = false;
+                    float dx = 0.f, dy = 0.f, dz = 0.f, d2 = 0.f;
+                    int j = -1;
+                    if (k < ke) {
+                        const SortedAtom<float> q = spos[k];
+                        j = q.idx;
+                        if (k == a) {
+                            hit = true;
+                        } else if (sbatch[k] == ba) {
+                            dx = rn_sub(me.x, q.x);
+                            dy = rn_sub(me.y, q.y);
+                            dz = rn_sub(me.z, q.z);
+                            if (periodic) {
+                                dx = min_image_rect1(dx, g.L[0]);
+                                dy = min_image_rect1(dy, g.L[1]);
+                                dz = min_image_rect1(dz, g.L[2]);
+                            }
+                            d2 = dist2(dx, dy, dz);
+                            hit = d2 < hi2 && d2 >= lo2;
+                        }
+                    }
+                    emit<FILL>(hit, lane, j, dx, dy, dz, d2, run, base, out);
+                }
+            }
+        }
+    }
+    if (!FILL && lane == 0) out.row_cnt[me.idx] = run;
+}
+
+// num_found = edges found; row pointers are clamped to the capacity so that an overflowing list is truncated
+// (rows past the capacity become empty) instead of read out of bounds by the model kernels
+__global__ void csr_finish_kernel(int* __restrict__ row_ptr, int n, long long cap, int32_t* __restrict__ num_found) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n) return;
+    const int v = row_ptr[i];
+    if (i == n) *num_found = v;
+    if (v > cap) row_ptr[i] = (int)cap;
+}
+
+struct DirectWs {
+    int *row_cnt, *scan_tmp;
+    // cell only
+    int *cell_cnt, *cell_start, *cell_of, *slot_of, *cell_scan_tmp;
+    SortedAtom<float>*tmp, *spos;
+    long long *tmp_batch, *sbatch;
+};
+void carve_direct(Arena& a, int strategy, int64_t n, int ncells, DirectWs& w) {
+    w.row_cnt = a.get<int>(n + 1);
+    w.scan_tmp = a.get<int>(tmdn_scan_tmp_ints(n + 1));
+    if (strategy == TMDN_CELL) {
+        w.cell_cnt = a.get<int>(ncells + 1);
+        w.cell_start = a.get<int>(ncells + 1);
+        w.cell_of = a.get<int>(n);
+        w.slot_of = a.get<int>(n);
+        w.cell_scan_tmp = a.get<int>(tmdn_scan_tmp_ints(ncells + 1));
+        w.tmp = a.get<SortedAtom<float>>(n);
+        w.spos = a.get<SortedAtom<float>>(n);
+        w.tmp_batch = a.get<long long>(n);
+        w.sbatch = a.get<long long>(n);
+    }
+}
+}  // namespace
+
+extern "C" size_t tmdn_csr_build_workspace_bytes(int strategy, int64_t n_atoms, const double box[9],
+                                                 double cutoff_upper) {
+    Arena a(nullptr, 0);
+    DirectWs w;
+    int ncells = 0;
+    if (strategy == TMDN_CELL) {
+        CellGrid<float> g;
+        if (!box || cutoff_upper <= 0 || !make_grid<float>(box, cutoff_upper, g)) return 0;
+        ncells = g.ncells;
+    }
+    carve_direct(a, strategy, n_atoms, ncells, w);
+    return a.off + 256;
+}
+
+extern "C" int tmdn_csr_build_f32(int strategy, const float* pos, const int64_t* batch, int64_t n_atoms,
+                                  const double box[9], int use_periodic, double cutoff_lower, double cutoff_upper,
+                                  int64_t max_edges, int32_t* row_ptr, int32_t* col, float* geom, int32_t* num_found,
+                                  void* workspace, size_t workspace_bytes, tmdn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    TMDN_CHECK_ARG(pos && batch && row_ptr && col && geom && num_found, "csr_build: null pointer argument");
+    TMDN_CHECK_ARG(n_atoms > 0 && n_atoms < (1LL << 31) - 256, "csr_build: bad atom count");
+    TMDN_CHECK_ARG(max_edges > 0 && max_edges < (1LL << 31), "csr_build: max_edges must be positive and fit int32");
+    TMDN_CHECK_ARG(cutoff_upper > 0, "Expected \"cutoff\" to be positive");
+    TMDN_CHECK_ARG(strategy == TMDN_BRUTE || strategy == TMDN_SHARED || strategy == TMDN_CELL, "Unknown kernel name");
+    TMDN_CHECK_ARG(!(use_periodic || strategy == TMDN_CELL) || box, "csr_build: box required");
+    const int n = (int)n_atoms;
+    const float lo = (float)cutoff_lower, hi = (float)cutoff_upper;
+    const float lo2 = lo * lo, hi2 = hi * hi;
+    Arena arena(workspace, workspace_bytes);
+    DirectWs w;
+    CellGrid<float> g;
+    memset(&g, 0, sizeof(g));
+    if (strategy == TMDN_CELL) {
+        TMDN_CHECK_ARG(box[1] == 0 && box[2] == 0 && box[3] == 0 && box[5] == 0 && box[6] == 0 && box[7] == 0,
+                       "Expected \"box_size\" to be diagonal");
+        TMDN_CHECK_ARG(box[0] > 0 && box[4] > 0 && box[8] > 0, "csr_build: box lengths must be positive");
+        TMDN_CHECK_ARG(make_grid<float>(box, cutoff_upper, g), "Too many cells in one dimension. Maximum is 1024");
+    }
+    carve_direct(arena, strategy, n_atoms, g.ncells, w);
+    if (!arena.ok || !workspace) {
+        tmdn_set_error("csr_build: workspace too small (%zu < %zu)", workspace_bytes, arena.off);
+        return TMDN_EWORKSPACE;
+    }
+    EdgeOut cnt{nullptr, w.row_cnt, col, (float4*)geom, (long long)max_edges};
+    EdgeOut fill{row_ptr, nullptr, col, (float4*)geom, (long long)max_edges};
+    const unsigned wgrid = (unsigned)cdiv(n, CD_WARPS);
+    if (strategy == TMDN_CELL) {
+        TMDN_CUDA(cudaMemsetAsync(w.cell_cnt, 0, sizeof(int) * (g.ncells + 1), stream));
+        const int blocks = (int)cdiv(n, 256);
+        cell_assign_kernel<float><<<blocks, 256, 0, stream>>>(pos, n, g, w.cell_cnt, w.cell_of, w.slot_of);
+        TMDN_LAUNCH_CHECK();
+        TMDN_TRY(tmdn_scan_exclusive_i32(w.cell_cnt, w.cell_start, g.ncells, w.cell_scan_tmp, stream));
+        cell_scatter_kernel<float><<<blocks, 256, 0, stream>>>(pos, batch, n, w.cell_start, w.cell_of, w.slot_of, w.tmp,
+                                                               w.tmp_batch);
+        TMDN_LAUNCH_CHECK();
+        cell_rank_kernel<<<blocks, 256, 0, stream>>>(w.tmp, w.tmp_batch, w.cell_start, w.cell_of, w.slot_of, n, w.spos,
+                                                     w.sbatch);
+        TMDN_LAUNCH_CHECK();
+        csr_cell_kernel<false><<<wgrid, CD_WARPS * 32, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g, n, use_periodic,
+                                                                    lo2, hi2, cnt);
+        TMDN_LAUNCH_CHECK();
+        TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));
+        csr_cell_kernel<true><<<wgrid, CD_WARPS * 32, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g, n, use_periodic,
+                                                                   lo2, hi2, fill);
+        TMDN_LAUNCH_CHECK();
+    } else {
+        Box3<float> b;
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) b.m[r][c] = (use_periodic && box) ? (float)box[3 * r + c] : 0.f;
+        csr_brute_kernel<false><<<wgrid, CD_WARPS * 32, 0, stream>>>(pos, batch, n, b, use_periodic, lo2, hi2, cnt);
+        TMDN_LAUNCH_CHECK();
+        TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));
+        csr_brute_kernel<true><<<wgrid, CD_WARPS * 32, 0, stream>>>(pos, batch, n, b, use_periodic, lo2, hi2, fill);
+        TMDN_LAUNCH_CHECK();
+    }
+    csr_finish_kernel<<<(unsigned)cdiv(n + 1, 256), 256, 0, stream>>>(row_ptr, n, (long long)max_edges, num_found);
+    TMDN_LAUNCH_CHECK();
+    return TMDN_OK;
+}

@@ -612,11 +612,11 @@ __global__ void tn_embed_edge_bwd(const int* __restrict__ row_ptr, const int* __
 // ------------------------------------------------------------------ workspace
 struct TnWs {
     // graph
-    int32_t *nbr, *num_found, *row_ptr, *col;
-    float *deltas, *dist, *geom;
+    int32_t *num_found, *row_ptr, *col;
+    float* geom;
     int* z32;
-    void *nbr_ws, *csr_ws;
-    size_t nbr_ws_bytes, csr_ws_bytes;
+    void* graph_ws;
+    size_t graph_ws_bytes;
     // exact-mode filters
     float *R, *dR, *fh[3], *fa[3], *ft[3];
     float *F[TMDN_MAX_LAYERS + 1], *dF[TMDN_MAX_LAYERS + 1];
@@ -640,20 +640,17 @@ int carve_tn(Arena& a, const tmdn_tensornet_model* m, int64_t N, int64_t P, int6
     const size_t H = m->hidden, K = m->num_rbf, L = m->num_layers;
     const size_t n = (size_t)N, nh9 = n * 9 * H;
     char buf[32];
-    w.nbr = carve<int32_t>(a, names, "nbr", 2 * (size_t)P);
-    w.deltas = carve<float>(a, names, "deltas", 3 * (size_t)P);
-    w.dist = carve<float>(a, names, "dist", (size_t)P);
     w.num_found = carve<int32_t>(a, names, "num_found", 4);
     w.row_ptr = carve<int32_t>(a, names, "row_ptr", n + 1);
     w.col = carve<int32_t>(a, names, "col", (size_t)P);
     w.geom = carve<float>(a, names, "geom", 4 * (size_t)P);
     w.z32 = carve<int>(a, names, "z32", n);
-    double dummy_box[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
-    w.nbr_ws_bytes = tmdn_neighbors_workspace_bytes(strategy, N, box ? box : dummy_box, cutoff, 4);
-    if (strategy == TMDN_CELL && w.nbr_ws_bytes == 0) return TMDN_EINVAL;
-    w.nbr_ws = carve<char>(a, names, "nbr_ws", w.nbr_ws_bytes);
-    w.csr_ws_bytes = tmdn_csr_workspace_bytes(N, P);
-    w.csr_ws = carve<char>(a, names, "csr_ws", w.csr_ws_bytes);
+    w.graph_ws_bytes = tmdn_csr_build_workspace_bytes(strategy, N, box, cutoff);
+    if (w.graph_ws_bytes == 0) {
+        tmdn_set_error("tensornet: bad box for the cell strategy");
+        return TMDN_EINVAL;
+    }
+    w.graph_ws = carve<char>(a, names, "graph_ws", w.graph_ws_bytes);
     if (m->filter_mode == TMDN_FILTER_EXACT) {
         const size_t e = (size_t)P;
         w.R = carve<float>(a, names, "R", e * K);
@@ -790,25 +787,23 @@ FilterView make_view(const tmdn_tensornet_model* m, const tmdn_filter_set& fs, c
 }  // namespace
 
 extern "C" size_t tmdn_tensornet_workspace_bytes(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,
-                                                 int64_t n_mol) {
+                                                 int64_t n_mol, int strategy, const double box[9]) {
     if (check_model(m) != TMDN_OK || n_atoms <= 0 || max_edges <= 0) return 0;
     Arena a(nullptr, 0);
     TnWs w;
-    // the cell strategy needs box-dependent scratch; size for the worst case of both strategies with a box of
-    // up to 2^22 cells (callers pass the same box at run time; see tmdn_tensornet_energy_forces)
-    carve_tn(a, m, n_atoms, max_edges, n_mol, w, nullptr, nullptr, TMDN_BRUTE, m->cutoff_upper);
-    const size_t cell_extra = (size_t)n_atoms * 40 + ((size_t)1 << 22) * 12 + 4096;
-    return a.off + cell_extra + 256;
+    if (carve_tn(a, m, n_atoms, max_edges, n_mol, w, nullptr, box, strategy, m->cutoff_upper) != TMDN_OK) return 0;
+    return a.off + 256;
 }
 
 extern "C" int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,
-                                               int64_t n_mol, const char* name, size_t* offset, size_t* bytes) {
+                                               int64_t n_mol, int strategy, const double box[9], const char* name,
+                                               size_t* offset, size_t* bytes) {
     TMDN_TRY(check_model(m));
     TMDN_CHECK_ARG(name && offset && bytes, "lookup: null argument");
     Arena a(nullptr, 0);
     TnWs w;
     std::vector<WsEntry> names;
-    carve_tn(a, m, n_atoms, max_edges, n_mol, w, &names, nullptr, TMDN_BRUTE, m->cutoff_upper);
+    TMDN_TRY(carve_tn(a, m, n_atoms, max_edges, n_mol, w, &names, box, strategy, m->cutoff_upper));
     for (const auto& e : names)
         if (e.name == name) {
             *offset = e.off;
@@ -834,33 +829,21 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
     const bool tab = m->filter_mode == TMDN_FILTER_TABLE;
     const int64_t P = max_edges;
 
-    // The brute-strategy layout is a prefix of every layout (cell scratch lives in the tail reserve).
+    TMDN_CHECK_ARG(strategy != TMDN_CELL || box, "tensornet: the cell strategy needs a box");
     Arena arena(workspace, workspace_bytes);
     TnWs w;
-    TMDN_TRY(carve_tn(arena, m, n_atoms, P, n_mol, w, nullptr, nullptr, TMDN_BRUTE, m->cutoff_upper));
-    void* nbr_ws = w.nbr_ws;
-    size_t nbr_ws_bytes = w.nbr_ws_bytes;
-    if (strategy == TMDN_CELL) {
-        TMDN_CHECK_ARG(box, "tensornet: the cell strategy needs a box");
-        nbr_ws_bytes = tmdn_neighbors_workspace_bytes(TMDN_CELL, n_atoms, box, m->cutoff_upper, 4);
-        TMDN_CHECK_ARG(nbr_ws_bytes > 0, "tensornet: bad box for the cell strategy");
-        nbr_ws = arena.get<char>(nbr_ws_bytes);
-    }
+    TMDN_TRY(carve_tn(arena, m, n_atoms, P, n_mol, w, nullptr, box, strategy, m->cutoff_upper));
     if (!arena.ok) {
         tmdn_set_error("tensornet: workspace too small (%zu < %zu)", workspace_bytes, arena.off);
         return TMDN_EWORKSPACE;
     }
 
-    // ---- graph: pairs (incl. transposes and self loops) -> CSR by target = row 0 (tensornet.py:313-315)
+    // ---- graph: neighbour search straight into CSR by target (= row 0 of the reference's pair list,
+    //      tensornet.py:313-315), self loops included
     {
-        KTimer ktimer__("neighbors", stream);
-        TMDN_TRY(tmdn_neighbors_f32(strategy, pos, batch, n_atoms, box, use_periodic, m->cutoff_lower, m->cutoff_upper,
-                                    1, 1, P, w.nbr, w.deltas, w.dist, w.num_found, nbr_ws, nbr_ws_bytes, stream_));
-    }
-    {
-        KTimer ktimer__("csr", stream);
-        TMDN_TRY(tmdn_csr_from_pairs(w.nbr, w.deltas, w.dist, w.num_found, P, n_atoms, 0, w.row_ptr, w.col, w.geom,
-                                     w.csr_ws, w.csr_ws_bytes, stream_));
+        KTimer ktimer__("neighbors_csr", stream);
+        TMDN_TRY(tmdn_csr_build_f32(strategy, pos, batch, n_atoms, box, use_periodic, m->cutoff_lower, m->cutoff_upper,
+                                    P, w.row_ptr, w.col, w.geom, w.num_found, w.graph_ws, w.graph_ws_bytes, stream_));
     }
     TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
     {
