@@ -112,6 +112,19 @@ int tmdn_csr_from_pairs(const int32_t* neighbors, const float* deltas, const flo
                         int32_t* row_ptr, int32_t* col, float* geom /* [max_pairs,4] */, void* workspace,
                         size_t workspace_bytes, tmdn_stream_t stream);
 
+/* Direct build (new): the same pair set as tmdn_neighbors_f32(loop=1, include_transpose=1), emitted straight as
+ * CSR rows (target atom -> sources) without materialising the reference's pair list.  `batch` must be sorted
+ * ascending (molecules contiguous); brute/shared search each atom's own molecule, cell searches the 27 cells
+ * around it (diagonal box).  Row order: ascending source index (brute) / cell-traversal order with cells
+ * internally sorted by atom index (cell) -- a pure function of the input, so downstream sums are reproducible.
+ * *num_found = edges found; if it exceeds max_edges the structure is truncated (row_ptr clamped to max_edges).
+ */
+size_t tmdn_csr_build_workspace_bytes(int strategy, int64_t n_atoms, const double box[9], double cutoff_upper);
+int tmdn_csr_build_f32(int strategy, const float* pos, const int64_t* batch, int64_t n_atoms, const double box[9],
+                       int use_periodic, double cutoff_lower, double cutoff_upper, int64_t max_edges,
+                       int32_t* row_ptr, int32_t* col, float* geom /* [max_edges,4] */, int32_t* num_found,
+                       void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
+
 /* ---------------------------------------------------------------- TensorNet energy + forces (fp32)
  * All weight pointers are device fp32 arrays prepared once by the host side (layouts below; H = hidden,
  * K = num_rbf).  "T" suffix = transposed copy used by the backward kernels.
@@ -153,7 +166,7 @@ typedef struct tmdn_tensornet_model {
 } tmdn_tensornet_model;
 
 size_t tmdn_tensornet_workspace_bytes(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,
-                                      int64_t n_mol);
+                                      int64_t n_mol, int strategy, const double box[9] /* cell strategy only */);
 /* One energy(+force) evaluation.  z,batch int64 device [n_atoms] (batch sorted non-decreasing, values in
  * [0,n_mol)); pos fp32 device [n_atoms,3]; energy fp32 device [n_mol]; forces fp32 device [n_atoms,3] or NULL
  * (forward only).  Neighbors are searched with `strategy` under box/use_periodic; max_edges is the pair
@@ -167,7 +180,8 @@ int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const int64_t* z
 /* Debug/inspection: byte offset and size of a named intermediate inside the workspace (names as in
  * oracle/staged_tensornet.py: "row_ptr","col","geom","ias","nh","fias","X0","Y0","M0","tauh0","X1",...,"e_atom","Dias","gpos"). */
 int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,
-                                    int64_t n_mol, const char* name, size_t* offset, size_t* bytes);
+                                    int64_t n_mol, int strategy, const double box[9], const char* name,
+                                    size_t* offset, size_t* bytes);
 
 #ifdef __cplusplus
 }

@@ -236,3 +236,68 @@ def test_cuda_graph_capture_of_the_op():
     a = onb.canonical_order(ei.cpu().numpy().astype(np.int32), ev.cpu().numpy(), ew.cpu().numpy())
     b = onb.canonical_order(*ref)
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2])
+
+
+def _csr_reference(pos, batch, box, hi, rect):
+    nb, dl, ds = onb.neighbor_pairs(pos, batch, box, 0.0, hi, loop=True, include_transpose=True, rect=rect)
+    order = np.lexsort((nb[1], nb[0]))
+    return nb[:, order], dl[order], ds[order]
+
+
+@pytest.mark.parametrize("case", ["molecules", "single", "periodic_tric", "periodic_rect_cell", "open_cell"])
+def test_direct_csr_build_matches_oracle(case):
+    """tmdn_csr_build_f32 (the fused models' graph builder): same pair set as the reference op with loop=True and
+    include_transpose=True, rows contiguous, geom = (unit vector target-source, distance)."""
+    from torchmdnet import _native
+    _native.load()
+    rng = np.random.RandomState(21)
+    strategy, box, periodic = "brute", None, False
+    if case == "molecules":
+        sizes = rng.randint(1, 40, 50)
+        batch = np.repeat(np.arange(50, dtype=np.int64), sizes)
+        pos = (rng.rand(batch.size, 3) * 6).astype(np.float32)
+    elif case == "single":
+        pos = (rng.rand(700, 3) * 12).astype(np.float32)
+        batch = np.zeros(700, dtype=np.int64)
+    elif case == "periodic_tric":
+        pos = (rng.rand(500, 3) * 24 - 12).astype(np.float32)
+        batch = np.zeros(500, dtype=np.int64)
+        box, periodic = np.array([[12.0, 0, 0], [1.2, 12.0, 0], [3.6, 2.4, 12.0]], dtype=np.float32), True
+    else:
+        pos = (rng.rand(3000, 3) * 30 - 15).astype(np.float32)
+        batch = np.sort(rng.randint(0, 2, 3000)).astype(np.int64)
+        strategy = "cell"
+        box = np.diag([30.0, 30.0, 30.0]).astype(np.float32)
+        periodic = case == "periodic_rect_cell"
+    hi = 3.0
+    ref_nb, ref_dl, ref_ds = _csr_reference(pos, batch, box if periodic else None, hi, rect=(strategy == "cell"))
+    E = ref_nb.shape[1]
+    tb = torch.empty(0, 0) if box is None else torch.from_numpy(box)
+    rp, col, geom, num = torch.ops.torchmdnet_b200.csr_build(strategy, torch.from_numpy(pos).cuda(),
+                                                             torch.from_numpy(batch).cuda(), tb, periodic, 0.0, hi,
+                                                             E + 13)
+    assert int(num) == E
+    rp, col, geom = rp.cpu().numpy(), col.cpu().numpy()[:E], geom.cpu().numpy()[:E]
+    n = pos.shape[0]
+    assert rp[0] == 0 and rp[-1] == E
+    assert np.array_equal(np.diff(rp), np.bincount(ref_nb[0], minlength=n))
+    tgt = np.repeat(np.arange(n), np.diff(rp))
+    if strategy == "brute":
+        assert np.array_equal(col, ref_nb[1])           # ascending source index inside every row
+    order = np.lexsort((col, tgt))
+    assert np.array_equal(col[order], ref_nb[1])
+    g = geom[order]
+    assert np.array_equal(g[:, 3], ref_ds)               # same rounding sequence -> identical distances
+    nz = ref_ds > 0
+    np.testing.assert_allclose(g[nz, :3], ref_dl[nz] / ref_ds[nz, None], rtol=0, atol=3e-7)
+    assert (g[~nz] == 0).all()
+    # determinism: a second build gives the identical structure (cells are internally re-ranked by atom index)
+    rp2, col2, geom2, _ = torch.ops.torchmdnet_b200.csr_build(strategy, torch.from_numpy(pos).cuda(),
+                                                              torch.from_numpy(batch).cuda(), tb, periodic, 0.0, hi,
+                                                              E + 13)
+    assert torch.equal(col2.cpu()[:E], torch.from_numpy(col)) and torch.equal(geom2.cpu()[:E], torch.from_numpy(geom))
+    # overflow: the structure is truncated, the count is not
+    rp3, col3, geom3, num3 = torch.ops.torchmdnet_b200.csr_build(strategy, torch.from_numpy(pos).cuda(),
+                                                                 torch.from_numpy(batch).cuda(), tb, periodic, 0.0,
+                                                                 hi, E // 2)
+    assert int(num3) == E and int(rp3.max()) == E // 2

@@ -209,6 +209,33 @@ std::tuple<Tensor, Tensor, Tensor> csr_from_pairs(const Tensor& neighbors, const
     return std::make_tuple(row_ptr, col, geom);
 }
 
+// -> (row_ptr int32[N+1], col int32[max_edges], geom float32[max_edges,4], num_found int32[1])
+std::tuple<Tensor, Tensor, Tensor, Tensor> csr_build(const std::string& strategy, const Tensor& positions,
+                                                     const Tensor& batch, const Tensor& box_vectors, bool use_periodic,
+                                                     double lo, double hi, int64_t max_edges) {
+    check_input(positions, batch);
+    TORCH_CHECK(positions.scalar_type() == at::kFloat, "csr_build: fp32 positions only");
+    const int sid = strategy_id(strategy);
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    TORCH_CHECK(have_box || !(use_periodic || sid == TMDN_CELL), "csr_build: box required");
+    const c10::cuda::CUDAGuard guard(positions.device());
+    const int64_t n = positions.size(0);
+    const auto iopts = positions.options().dtype(at::kInt);
+    Tensor row_ptr = at::empty({n + 1}, iopts);
+    Tensor col = at::full({max_edges}, -1, iopts);
+    Tensor geom = at::zeros({max_edges, 4}, positions.options());
+    Tensor num = at::empty({1}, iopts);
+    const size_t ws_bytes = tmdn_csr_build_workspace_bytes(sid, n, have_box ? box : nullptr, hi);
+    TORCH_CHECK(ws_bytes > 0, "csr_build: bad box for the cell strategy");
+    Tensor ws = at::empty({(int64_t)ws_bytes}, positions.options().dtype(at::kByte));
+    TMDN_CALL(tmdn_csr_build_f32(sid, positions.data_ptr<float>(), batch.data_ptr<int64_t>(), n,
+                                 have_box ? box : nullptr, use_periodic, lo, hi, max_edges, row_ptr.data_ptr<int32_t>(),
+                                 col.data_ptr<int32_t>(), geom.data_ptr<float>(), num.data_ptr<int32_t>(),
+                                 ws.data_ptr(), ws_bytes, cur_stream()));
+    return std::make_tuple(row_ptr, col, geom, num);
+}
+
 // ------------------------------------------------------------------ TensorNet model handles
 struct TnHandle {
     tmdn_tensornet_model m;
@@ -307,7 +334,7 @@ std::tuple<Tensor, Tensor, Tensor, Tensor> tensornet_energy_forces(int64_t handl
     double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     const bool have_box = read_box(box_vectors, box);
     TORCH_CHECK(have_box || !(use_periodic || sid == TMDN_CELL), "tensornet_energy_forces: box required");
-    const size_t need = tmdn_tensornet_workspace_bytes(&h->m, n, max_edges, n_mol);
+    const size_t need = tmdn_tensornet_workspace_bytes(&h->m, n, max_edges, n_mol, sid, have_box ? box : nullptr);
     TORCH_CHECK(need > 0, "tensornet_energy_forces: ", tmdn_last_error());
     Tensor ws;
     if (workspace.has_value() && workspace->defined() && (size_t)workspace->numel() >= need && workspace->is_cuda() &&
@@ -328,10 +355,14 @@ std::tuple<Tensor, Tensor, Tensor, Tensor> tensornet_energy_forces(int64_t handl
 
 // -> [offset, bytes] of a named intermediate inside the workspace
 std::vector<int64_t> tensornet_debug_lookup(int64_t handle, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                            const std::string& strategy, const Tensor& box_vectors,
                                             const std::string& name) {
     auto h = tn_get(handle);
     size_t off = 0, bytes = 0;
-    TMDN_CALL(tmdn_tensornet_workspace_lookup(&h->m, n_atoms, max_edges, n_mol, name.c_str(), &off, &bytes));
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    TMDN_CALL(tmdn_tensornet_workspace_lookup(&h->m, n_atoms, max_edges, n_mol, strategy_id(strategy),
+                                              have_box ? box : nullptr, name.c_str(), &off, &bytes));
     return {(int64_t)off, (int64_t)bytes};
 }
 
@@ -368,6 +399,10 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
     m.def("launch_count() -> int", launch_count);
     m.def("profile_enable(bool on) -> ()", profile_enable);
     m.def("profile_report() -> str", profile_report);
-    m.def("tensornet_debug_lookup(int handle, int n_atoms, int max_edges, int n_mol, str name) -> int[]",
+    m.def("csr_build(str strategy, Tensor positions, Tensor batch, Tensor box_vectors, bool use_periodic, "
+          "float cutoff_lower, float cutoff_upper, int max_edges) -> (Tensor, Tensor, Tensor, Tensor)",
+          csr_build);
+    m.def("tensornet_debug_lookup(int handle, int n_atoms, int max_edges, int n_mol, str strategy, Tensor box_vectors, "
+          "str name) -> int[]",
           tensornet_debug_lookup);
 }

@@ -310,7 +310,8 @@ class TensorNet(nn.Module):
         """Flat view of a named intermediate of the LAST call (names as in oracle/staged_tensornet.py)."""
         dist = self.distance
         max_edges = dist.max_num_pairs if dist.max_num_pairs > 0 else -dist.max_num_pairs * n_atoms
-        off, nbytes = torch.ops.torchmdnet_b200.tensornet_debug_lookup(self._handle, n_atoms, max_edges, n_mol, name)
+        off, nbytes = torch.ops.torchmdnet_b200.tensornet_debug_lookup(self._handle, n_atoms, max_edges, n_mol,
+                                                                       dist.strategy, dist.box, name)
         return self._workspace[off:off + nbytes].view(dtype)
 
     def forward(self, z: Tensor, pos: Tensor, batch: Tensor, q: Optional[Tensor] = None,
