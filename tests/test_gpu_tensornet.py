@@ -153,8 +153,9 @@ def test_batch_none_and_forward_only_and_features():
 
 
 def test_batch_sharding_is_exact():
-    """Molecules are independent: evaluating a shard gives the same numbers as the full batch (bitwise, because
-    every reduction is an in-order segmented sum)."""
+    """Molecules are independent: evaluating a shard gives the same numbers as the full batch (to fp32 rounding:
+    the number of edge slices per row, hence the summation order, depends on the launch size) and the same
+    call repeated is bitwise reproducible (no float atomics anywhere)."""
     import synth_inputs as S
     from torchmdnet.models.model import create_model
     g = load_npz("model_TensorNet-rMD17.npz")
@@ -164,7 +165,10 @@ def test_batch_sharding_is_exact():
     y, f = m(z, pos, batch)
     lo = 21 * 32
     y2, f2 = m(z[lo:], pos[lo:], batch[lo:] - 32)
-    assert torch.equal(y2, y[32:]) and torch.equal(f2, f[lo:])
+    torch.testing.assert_close(y2, y[32:], rtol=2e-6, atol=2e-6)
+    torch.testing.assert_close(f2, f[lo:], rtol=0, atol=5e-6)
+    y3, f3 = m(z, pos, batch)
+    assert torch.equal(y3, y) and torch.equal(f3, f)
     sd = {k: v.cpu() for k, v in m.state_dict().items()}
     yr, fr = om.energy_forces(sd, g["hparams"], z[:63].cpu(), pos[:63].cpu(), batch[:63].cpu())
     check(y[:3], f[:63], yr, fr)

@@ -155,8 +155,8 @@ template <int NV> __device__ __forceinline__ void atom_reduce(float (&v)[NV], fl
 struct EdgeLaunch { dim3 block; unsigned grid; size_t smem; };
 // s_red (<= 32 warps x 3 values per atom) lives at the start of dynamic shared memory, slice partials after it
 constexpr int EDGE_RED_FLOATS = 128;
-static EdgeLaunch edge_launch(int N, int H) {
-    int smax = 1024 / H;
+static EdgeLaunch edge_launch(int N, int H, int max_threads) {
+    int smax = max_threads / H;
     if (smax < 1) smax = 1;
     const long long target = 148LL * 2048;
     int S = 1;
@@ -235,7 +235,7 @@ __global__ void tn_filter_finalize_kernel(const float4* __restrict__ geom, long 
 // ias_c[i,h] = sum_{e in row i} (P[z_i]+Q[z_j])[h] * W_g(c)(d_e)[h] * geom_c(u_e)      (tensornet.py:295-315)
 // nh = LayerNorm_H(||I+A+S||^2)                                                     (tensornet.py:316)
 template <bool TAB>
-__global__ void tn_embed_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+__global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                                   const float4* __restrict__ geom, const int* __restrict__ z32,
                                   const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv, int N,
                                   int H, float* __restrict__ ias, const float* __restrict__ ln_w,
@@ -360,7 +360,7 @@ __global__ void tn_prod_bwd(const float* __restrict__ Y, const float* __restrict
 // ------------------------------------------------------------------ E2: interaction message passing (+ product)
 // M_c[i,h] = sum_{e in row i} f_g(c)(d_e)[h] * Y_c[j,h]  ;  tauh = normalise(decompose(M Y + Y M))   (tensornet.py:392-405)
 template <bool TAB>
-__global__ void tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+__global__ void __launch_bounds__(1024) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H,
                            int so3, float* __restrict__ M, float* __restrict__ tauh) {
     extern __shared__ float smem[];
@@ -398,7 +398,7 @@ __global__ void tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restric
 //   dY_i += sum_e f_e * dM_j
 //   dE/dpos_i += u_e * sum_{h,c} f'_g(c)(d_e)[h] * (dM_c[i,h] Y_c[j,h] + dM_c[j,h] Y_c[i,h])
 template <bool TAB>
-__global__ void tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+__global__ void __launch_bounds__(512) tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
                            const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
                            int H) {
@@ -619,7 +619,7 @@ __global__ void tn_embed_norm_bwd(const float* __restrict__ ias, const float* __
 // E4: adjoint of the embedding edge kernel w.r.t. positions, both directions of every edge inside row i.
 //   forces[i] = -(gpos[i] + sum_e [ u (gd_e + gd_e') + perp(gu_e) - perp(gu_e') ])
 template <bool TAB>
-__global__ void tn_embed_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+__global__ void __launch_bounds__(512) tn_embed_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                                   const float4* __restrict__ geom, const int* __restrict__ z32,
                                   const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv,
                                   const float* __restrict__ Dias, const float* __restrict__ gpos,
@@ -929,7 +929,8 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
     const float4* geom = (const float4*)w.geom;
     const int apb = H >= 128 ? 1 : 128 / H;
     const dim3 rblock(H, apb);
-    const EdgeLaunch el = edge_launch(N, H);
+    const EdgeLaunch el = edge_launch(N, H, 1024);    // forward edge kernels: <= 64 registers/thread
+    const EdgeLaunch elb = edge_launch(N, H, 512);    // backward edge kernels: <= 128 registers/thread
     const unsigned rgrid = (unsigned)cdiv(N, apb);
     const long long NH = (long long)N * H;
     const unsigned egrid = (unsigned)cdiv(NH, 256);
@@ -1064,10 +1065,10 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
         {
             KTimer ktimer__("tn_msg_bwd", stream);
             if (tab)
-                tn_msg_bwd<true><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
+                tn_msg_bwd<true><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
                                                                w.gpos, N, H);
             else
-                tn_msg_bwd<false><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
+                tn_msg_bwd<false><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
                                                                 w.gpos, N, H);
             TMDN_LAUNCH_CHECK();
         }
@@ -1102,10 +1103,10 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
     {
         KTimer ktimer__("tn_embed_edge_bwd", stream);
         if (tab)
-            tn_embed_edge_bwd<true><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
+            tn_embed_edge_bwd<true><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
                                                                   w.gpos, forces, N, H);
         else
-            tn_embed_edge_bwd<false><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
+            tn_embed_edge_bwd<false><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
                                                                    w.gpos, forces, N, H);
         TMDN_LAUNCH_CHECK();
     }
