@@ -183,6 +183,56 @@ int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_ato
                                     int64_t n_mol, int strategy, const double box[9], const char* name,
                                     size_t* offset, size_t* bytes);
 
+/* ---------------------------------------------------------------- Equivariant Transformer energy + forces (fp32)
+ * TorchMD_ET.forward + NeighborEmbedding + EquivariantMultiHeadAttention + EquivariantScalar head + force path
+ * (torchmdnet/models/torchmd_et.py:154-187,272-347; models/utils.py:73-108,496-522; models/output_modules.py:111-115).
+ * Weights are device fp32 arrays prepared once by the host side.  "T" = transposed copy for the backward GEMMs.
+ * v_proj / dv_proj rows are re-ordered part-major (row p*H + head*hd + c <- reference row head*3hd + p*hd + c).
+ * The distance filters are univariate in d and are passed as cubic Hermite tables built in fp64:
+ *   layer table [n_int][4][H] float4 : act(dk_proj(rbf(d))), act(dv_proj(rbf(d))) parts 0..2 (NO cutoff factor;
+ *                                      a missing filter (distance_influence) is the constant 1)
+ *   ne_table    [n_int][H]    float4 : distance_proj(rbf(d)) * C(d)      (models/utils.py:98-99)
+ * head_dim = hidden/num_heads must be a power of two <= 32.
+ */
+typedef struct tmdn_et_layer {
+    const float *ln_w, *ln_b;
+    const float *qkv_w, *qkv_b, *qkv_wT;   /* [5H,H] = q | k | v(part-major), [5H], [H,5H] */
+    const float *vp_w, *vp_wT;             /* vec_proj [3H,H], [H,3H] */
+    const float *o_w, *o_b, *o_wT;         /* o_proj [3H,H], [3H], [H,3H] */
+    const float* table;
+} tmdn_et_layer;
+
+typedef struct tmdn_et_gated {              /* GatedEquivariantBlock: hin -> out, intermediate = hin */
+    int32_t hin, out;
+    const float *w1, *w1T;                  /* vec1_proj [hin,hin] */
+    const float *w2, *w2T;                  /* vec2_proj [out,hin], [hin,out] */
+    const float *u0_w, *u0_b, *u0_wT;       /* update_net.0 [hin,2hin], [hin], [2hin,hin] */
+    const float *u2_w, *u2_b, *u2_wT;       /* update_net.2 [2out,hin], [2out], [hin,2out] */
+} tmdn_et_gated;
+
+typedef struct tmdn_et_model {
+    int32_t hidden, num_layers, num_heads, max_z;
+    int32_t activation, attn_activation, has_neighbor_embedding, n_int;
+    float cutoff_lower, cutoff_upper, mean, std;
+    const float* emb;                       /* embedding [max_z,H] */
+    const float *ne_emb, *ne_table;         /* neighbor_embedding.embedding [max_z,H], filter table */
+    const float *ne_comb_w, *ne_comb_b;     /* combine [H,2H], [H] */
+    const float* ne_comb_w2T;               /* (combine.weight[:, H:])^T  [H,H]: adjoint w.r.t. the neighbour half */
+    tmdn_et_layer layer[TMDN_MAX_LAYERS];
+    const float *out_ln_w, *out_ln_b;
+    tmdn_et_gated head[2];
+} tmdn_et_model;
+
+size_t tmdn_et_workspace_bytes(const tmdn_et_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                               int strategy, const double box[9]);
+/* Same contract as tmdn_tensornet_energy_forces. */
+int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, const float* pos, const int64_t* batch,
+                          int64_t n_atoms, int64_t n_mol, const double box[9], int use_periodic, int strategy,
+                          int64_t max_edges, float* energy, float* forces, int32_t* status, void* workspace,
+                          size_t workspace_bytes, tmdn_stream_t stream);
+int tmdn_et_workspace_lookup(const tmdn_et_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol, int strategy,
+                             const double box[9], const char* name, size_t* offset, size_t* bytes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,746 @@
+// et.cu -- Equivariant Transformer energy + analytic forces for sm_100a (fp32).
+//
+// Replaces TorchMD_ET.forward / NeighborEmbedding / EquivariantMultiHeadAttention (torchmdnet/models/torchmd_et.py:
+// 154-187, 272-347; models/utils.py:73-108), the EquivariantScalar head (models/utils.py:496-522,
+// output_modules.py:111-115), the reduce (output_modules.py:27-43) and the autograd force path of TorchMD_Net.forward
+// (models/model.py:286-298).  Stage list, buffer names and adjoint formulas are those of oracle/staged_et.py, which is
+// checked against torch.autograd on the CPU in fp64.
+//
+// Layout: x [N,H]; vec [N,3,H]; q|k|v in one [N,5H] buffer with v part-major [3][H]; a thread owns one (atom,
+// channel); per-head sums are segmented warp shuffles over head_dim consecutive lanes.  Edges are CSR by target;
+// the edge set is symmetric, so row i also evaluates the reverse edge of every entry and collects the source-side
+// adjoints (k_i, v_i, vec_i) -- no transposed graph, no float atomics, bit-reproducible.
+// The per-edge [E,H], [E,3H], [E,3,H] message tensors of the reference never exist.
+#include "common.cuh"
+#include "gemm.cuh"
+#include "edge_common.cuh"
+#include "scan.cuh"
+#include <string>
+#include <vector>
+
+namespace {
+
+struct Tab {
+    const float4* t;
+    float inv_h;
+    int n_int;
+};
+// NF filters per interval: value and d/dd from the same cubic
+template <int NF>
+__device__ __forceinline__ void tab_eval(const Tab& tb, float d, int H, int h, float (&f)[NF], float (&df)[NF]) {
+    float s = d * tb.inv_h;
+    int k = (int)s;
+    k = k > tb.n_int - 1 ? tb.n_int - 1 : k;
+    s -= (float)k;
+#pragma unroll
+    for (int g = 0; g < NF; ++g) {
+        const float4 c = __ldg(&tb.t[((size_t)k * NF + g) * H + h]);
+        f[g] = c.x + s * (c.y + s * (c.z + s * c.w));
+        df[g] = (c.y + s * (2.0f * c.z + 3.0f * s * c.w)) * tb.inv_h;
+    }
+}
+// sum over the hd consecutive lanes of a head (hd power of two <= 32); result in every lane of the segment
+__device__ __forceinline__ float seg_sum(float v, int hd) {
+    for (int o = hd >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void et_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ z32, int n, int max_z,
+                               const int32_t* __restrict__ num_found, long long max_edges, int32_t* __restrict__ status) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        const int f = *num_found;
+        status[0] = f;
+        status[1] = f > max_edges ? 1 : 0;
+    }
+    if (i >= n) return;
+    long long v = z[i];
+    if (v < 0 || v >= max_z) {
+        status[2] = 1;
+        v = 0;
+    }
+    z32[i] = (int)v;
+}
+
+// ------------------------------------------------------------------ embedding (+ neighbour embedding edge sum)
+// out[i, 0:H] = emb[z_i];  if NE: out[i, H:2H] = sum_{e in row i, j != i} ne_emb[z_j] * fne(d_e)   (models/utils.py:92-103)
+template <bool NE>
+__global__ void __launch_bounds__(1024)
+et_embed_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom,
+             const int* __restrict__ z32, const float* __restrict__ emb, const float* __restrict__ ne_emb, Tab tb, int N,
+             int H, float* __restrict__ out, int ldo) {
+    extern __shared__ float smem[];
+    float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
+    const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    float acc[1] = {0.f};
+    if (NE && valid) {
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0 + sl; e < r1; e += S) {
+            const int j = col[e];
+            if (j == i) continue;
+            float f[1], df[1];
+            tab_eval<1>(tb, geom[e].w, H, h, f, df);
+            acc[0] += ne_emb[(size_t)z32[j] * H + h] * f[0];
+        }
+    }
+    if (NE) slice_reduce<1>(acc, s_part, H);
+    if (!valid || sl != 0) return;
+    out[(size_t)i * ldo + h] = emb[(size_t)z32[i] * H + h];
+    if (NE) out[(size_t)i * ldo + H + h] = acc[0];
+}
+
+// ------------------------------------------------------------------ LayerNorm over H (block = (H,1,A))
+__global__ void et_ln_fwd(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                          float* __restrict__ y, int ldy, float* __restrict__ stat, int N, int H) {
+    __shared__ float s_red[EDGE_RED_FLOATS * 4];
+    const int h = threadIdx.x;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    const float v = valid ? x[(size_t)i * H + h] : 0.f;
+    float s[1] = {v};
+    atom_reduce<1>(s, s_red);
+    const float mean = s[0] / (float)H;
+    float q[1] = {(v - mean) * (v - mean)};
+    atom_reduce<1>(q, s_red);
+    const float rstd = rsqrtf(q[0] / (float)H + 1e-5f);
+    if (!valid) return;
+    y[(size_t)i * ldy + h] = (v - mean) * rstd * w[h] + b[h];
+    if (h == 0) { stat[2 * (size_t)i] = mean; stat[2 * (size_t)i + 1] = rstd; }
+}
+// gx (+)= LN^T(gy): gy has row stride ldg
+__global__ void et_ln_bwd(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ stat,
+                          const float* __restrict__ gy, int ldg, float* __restrict__ gx, int accumulate, int N, int H) {
+    __shared__ float s_red[EDGE_RED_FLOATS * 4];
+    const int h = threadIdx.x;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    float xh = 0.f, dg = 0.f, rstd = 0.f;
+    if (valid) {
+        const float mean = stat[2 * (size_t)i];
+        rstd = stat[2 * (size_t)i + 1];
+        xh = (x[(size_t)i * H + h] - mean) * rstd;
+        dg = gy[(size_t)i * ldg + h] * w[h];
+    }
+    float r[2] = {dg, dg * xh};
+    atom_reduce<2>(r, s_red);
+    if (!valid) return;
+    const float v = (dg - r[0] / (float)H - xh * r[1] / (float)H) * rstd;
+    const size_t o = (size_t)i * H + h;
+    gx[o] = accumulate ? gx[o] + v : v;
+}
+
+// ------------------------------------------------------------------ attention edge kernel (torchmd_et.py:314-347)
+// xa[i] = sum_e v0_j dv0 * attn_e ;  va[i] = sum_e vec_j (v1_j dv1) + (v2_j dv2) dhat_e,  dhat = -u
+// attn_e(head) = attn_act(sum_{c in head} q_i k_j dk) * C(d_e)
+__global__ void __launch_bounds__(1024)
+et_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
+            float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
+            int N, int H, float* __restrict__ xa, float* __restrict__ va) {
+    extern __shared__ float smem[];
+    float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
+    const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    const int H5 = 5 * H;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    if (valid) {
+        const float qi = qkv[(size_t)i * H5 + h];
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0 + sl; e < r1; e += S) {
+            const int j = col[e];
+            const float4 g = geom[e];
+            float f[4], df[4], c, dc;
+            tab_eval<4>(tb, g.w, H, h, f, df);
+            cutoff_fn(g.w, lo, hi, c, dc);
+            const float* pj = qkv + (size_t)j * H5 + h;
+            const float kj = pj[H], v0 = pj[2 * H], v1 = pj[3 * H], v2 = pj[4 * H];
+            const float* vj = vec + (size_t)j * 3 * H + h;
+            const float s = seg_sum(qi * kj * f[0], hd);
+            const float attn = act_apply(attn_act, s) * c;
+            acc[0] += v0 * f[1] * attn;
+            const float a1 = v1 * f[2], a2 = v2 * f[3];
+            acc[1] += vj[0] * a1 - a2 * g.x;
+            acc[2] += vj[H] * a1 - a2 * g.y;
+            acc[3] += vj[2 * H] * a1 - a2 * g.z;
+        }
+    }
+    slice_reduce<4>(acc, s_part, H);
+    if (!valid || sl != 0) return;
+    xa[(size_t)i * H + h] = acc[0];
+    float* o = va + (size_t)i * 3 * H + h;
+    o[0] = acc[1]; o[H] = acc[2]; o[2 * H] = acc[3];
+}
+
+// x' = x + (sum_xyz vec1 vec2) o2 + o3 ;  vec' = vec + vec3 o1 + va        (torchmd_et.py:278-312, 181-184)
+__global__ void et_update_fwd(const float* __restrict__ x, const float* __restrict__ vec, const float* __restrict__ vp,
+                              const float* __restrict__ o, const float* __restrict__ va, float* __restrict__ xn,
+                              float* __restrict__ vecn, long long total, int H) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / H;
+    const int h = (int)(idx % H);
+    const float* p = vp + i * 9 * H + h;     // [3 xyz][3H]
+    const float o1 = o[i * 3 * H + h], o2 = o[i * 3 * H + H + h], o3 = o[i * 3 * H + 2 * H + h];
+    float dot = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float v1 = p[(size_t)c * 3 * H], v2 = p[(size_t)c * 3 * H + H], v3 = p[(size_t)c * 3 * H + 2 * H];
+        dot += v1 * v2;
+        const size_t k = (i * 3 + c) * H + h;
+        vecn[k] = vec[k] + v3 * o1 + va[k];
+    }
+    xn[idx] = x[idx] + dot * o2 + o3;
+}
+
+// ------------------------------------------------------------------ gated equivariant block pieces (models/utils.py:496-522)
+// cat[i, hin + c] = || vb[i,:,c] ||
+__global__ void et_gate_norm_fwd(const float* __restrict__ vb, float* __restrict__ cat, long long total, int hin) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / hin;
+    const int c = (int)(idx % hin);
+    const float* p = vb + i * 3 * hin + c;
+    const float a = p[0], b = p[hin], d = p[2 * hin];
+    cat[i * 2 * hin + hin + c] = sqrtf(a * a + b * b + d * d);
+}
+// block with scalar activation: xo = act(h2[:, :out]) -> xout (row stride ldx); vo = h2[:, out:] * vec2
+__global__ void et_gate_out_fwd(const float* __restrict__ h2, const float* __restrict__ vec2, int act,
+                                float* __restrict__ xout, int ldx, float* __restrict__ vo, long long total, int out) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / out;
+    const int c = (int)(idx % out);
+    xout[i * ldx + c] = act_apply(act, h2[i * 2 * out + c]);
+    const float gate = h2[i * 2 * out + out + c];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) vo[(i * 3 + k) * out + c] = gate * vec2[(i * 3 + k) * out + c];
+}
+// e_i = (w . a_i + b) * std ; one warp per atom
+__global__ void et_head_energy(const float* __restrict__ a, const float* __restrict__ w, const float* __restrict__ b,
+                               float stdv, float* __restrict__ e_atom, int N, int K) {
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (i >= N) return;
+    float s = 0.f;
+    for (int k = lane; k < K; k += 32) s += a[(size_t)i * K + k] * w[k];
+    s = warp_sum(s);
+    if (lane == 0) e_atom[i] = (s + b[0]) * stdv;
+}
+__global__ void __launch_bounds__(128) et_mol_reduce(const float* __restrict__ e_atom, const int64_t* __restrict__ batch,
+                                                     int N, float mean, float* __restrict__ energy) {
+    __shared__ float s_part[128];
+    const long long m = blockIdx.x;
+    int lo = 0, hi = N;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m) lo = mid + 1; else hi = mid; }
+    const int a = lo;
+    hi = N;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m + 1) lo = mid + 1; else hi = mid; }
+    const int b = lo;
+    float s = 0.f;
+    for (int i = a + threadIdx.x; i < b; i += 128) s += e_atom[i];
+    s_part[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 64; o > 0; o >>= 1) {
+        if (threadIdx.x < o) s_part[threadIdx.x] += s_part[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) energy[m] = s_part[0] + mean;
+}
+
+// ================================================================== backward kernels
+// d[i,n] = std * w[n] * act'(h0[i,n])      (seed of dE/d(update_net.0 output) of the last gated block)
+__global__ void et_head_seed_bwd(const float* __restrict__ h0, const float* __restrict__ w, float stdv, int act,
+                                 float* __restrict__ d, long long total, int K) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    d[idx] = stdv * w[idx % K] * act_grad(act, h0[idx]);
+}
+// g_vb[i,:,c] = g_cat[i,hin+c] * vb[i,:,c] / ||vb[i,:,c]||   (0 where the norm is 0: models/utils.py:499-512)
+__global__ void et_gate_norm_bwd(const float* __restrict__ vb, const float* __restrict__ cat,
+                                 const float* __restrict__ g_cat, float* __restrict__ g_vb, long long total, int hin) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / hin;
+    const int c = (int)(idx % hin);
+    const float nrm = cat[i * 2 * hin + hin + c];
+    const float s = nrm > 0.f ? g_cat[i * 2 * hin + hin + c] / nrm : 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) g_vb[(i * 3 + k) * hin + c] = s * vb[(i * 3 + k) * hin + c];
+}
+// adjoint of et_gate_out_fwd: g_h2 = [g_xo * act'(h2_x) | sum_xyz g_vo vec2] ; g_vec2 = g_vo * gate
+__global__ void et_gate_out_bwd(const float* __restrict__ h2, const float* __restrict__ vec2, int act,
+                                const float* __restrict__ g_xo, int ldx, const float* __restrict__ g_vo,
+                                float* __restrict__ g_h2, float* __restrict__ g_vec2, long long total, int out) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / out;
+    const int c = (int)(idx % out);
+    g_h2[i * 2 * out + c] = g_xo[i * ldx + c] * act_grad(act, h2[i * 2 * out + c]);
+    const float gate = h2[i * 2 * out + out + c];
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const size_t o = (i * 3 + k) * out + c;
+        const float gv = g_vo[o];
+        s += gv * vec2[o];
+        g_vec2[o] = gv * gate;
+    }
+    g_h2[i * 2 * out + out + c] = s;
+}
+// adjoint of et_update_fwd: g_o = [sum_xyz g_vec vec3 | g_x vec_dot | g_x] ; g_vp = [g_x o2 vec2 | g_x o2 vec1 | g_vec o1]
+// g_vec_new = g_vec (residual path; the vec_proj^T and edge terms are added afterwards)
+__global__ void et_update_bwd(const float* __restrict__ g_x, const float* __restrict__ g_vec,
+                              const float* __restrict__ vp, const float* __restrict__ o, float* __restrict__ g_o,
+                              float* __restrict__ g_vp, float* __restrict__ g_vec_new, long long total, int H) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / H;
+    const int h = (int)(idx % H);
+    const float gx = g_x[idx];
+    const float o1 = o[i * 3 * H + h], o2 = o[i * 3 * H + H + h];
+    const float* p = vp + i * 9 * H + h;
+    float* gp = g_vp + i * 9 * H + h;
+    float dot = 0.f, go1 = 0.f;
+    const float gd = gx * o2;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float v1 = p[(size_t)c * 3 * H], v2 = p[(size_t)c * 3 * H + H], v3 = p[(size_t)c * 3 * H + 2 * H];
+        const size_t k = (i * 3 + c) * H + h;
+        const float gv = g_vec[k];
+        dot += v1 * v2;
+        go1 += gv * v3;
+        gp[(size_t)c * 3 * H] = gd * v2;
+        gp[(size_t)c * 3 * H + H] = gd * v1;
+        gp[(size_t)c * 3 * H + 2 * H] = gv * o1;
+        g_vec_new[k] = gv;
+    }
+    g_o[i * 3 * H + h] = go1;
+    g_o[i * 3 * H + H + h] = gx * dot;
+    g_o[i * 3 * H + 2 * H + h] = gx;
+}
+
+// Adjoint of et_edge_fwd evaluated in row i for both directions of every entry (i, j):
+//   A: edge (i <- j): g_q_i, and -G_A on pos_i          B: reverse edge (j <- i): g_k_i, g_v_i, g_vec_i, +G_B on pos_i
+//   G = g_d dhat + (g_dhat - (g_dhat.dhat) dhat)/d  is linear in (g_d, g_dhat), so every channel accumulates its share
+__global__ void __launch_bounds__(512)
+et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
+            float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
+            const float* __restrict__ g_xa, const float* __restrict__ g_va, int N, int H, float* __restrict__ g_qkv,
+            float* __restrict__ g_vec_new, float* __restrict__ gpos) {
+    extern __shared__ float smem[];
+    float* s_red = smem;
+    float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
+    const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    const int H5 = 5 * H;
+    const float inv_hd = 1.0f / (float)hd;
+    float acc[8];   // g_q, g_k, g_v0, g_v1, g_v2, g_vec xyz
+#pragma unroll
+    for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+    float gp[3] = {0.f, 0.f, 0.f};
+    if (valid) {
+        const float* pi = qkv + (size_t)i * H5 + h;
+        const float qi = pi[0], ki = pi[H], vi0 = pi[2 * H], vi1 = pi[3 * H], vi2 = pi[4 * H];
+        const float* vci = vec + (size_t)i * 3 * H + h;
+        const float vix = vci[0], viy = vci[H], viz = vci[2 * H];
+        const float gxi = g_xa[(size_t)i * H + h];
+        const float* gvi = g_va + (size_t)i * 3 * H + h;
+        const float gvix = gvi[0], gviy = gvi[H], gviz = gvi[2 * H];
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0 + sl; e < r1; e += S) {
+            const int j = col[e];
+            const float4 g = geom[e];
+            const float hx = -g.x, hy = -g.y, hz = -g.z;   // dhat of direction A; direction B uses +u
+            float f[4], df[4], c, dc;
+            tab_eval<4>(tb, g.w, H, h, f, df);
+            cutoff_fn(g.w, lo, hi, c, dc);
+            const float* pj = qkv + (size_t)j * H5 + h;
+            const float qj = pj[0], kj = pj[H], vj0 = pj[2 * H], vj1 = pj[3 * H], vj2 = pj[4 * H];
+            const float* vcj = vec + (size_t)j * 3 * H + h;
+            const float vjx = vcj[0], vjy = vcj[H], vjz = vcj[2 * H];
+            const float gxj = g_xa[(size_t)j * H + h];
+            const float* gvj = g_va + (size_t)j * 3 * H + h;
+            const float gvjx = gvj[0], gvjy = gvj[H], gvjz = gvj[2 * H];
+            // ---- A
+            const float sA = seg_sum(qi * kj * f[0], hd);
+            const float aA = act_apply(attn_act, sA), attnA = aA * c;
+            const float gattA = seg_sum(gxi * vj0 * f[1], hd);
+            const float gsA = gattA * act_grad(attn_act, sA) * c;
+            acc[0] += gsA * kj * f[0];
+            const float gv1A = gvix * vjx + gviy * vjy + gviz * vjz;
+            const float gv2A = gvix * hx + gviy * hy + gviz * hz;
+            const float gdA = gsA * qi * kj * df[0] + gxi * attnA * vj0 * df[1] + gv1A * vj1 * df[2] +
+                              gv2A * vj2 * df[3] + gattA * aA * inv_hd * dc;
+            const float v2A = vj2 * f[3];
+            const float ghxA = gvix * v2A, ghyA = gviy * v2A, ghzA = gviz * v2A;
+            // ---- B (roles swapped, dhat' = +u)
+            const float sB = seg_sum(qj * ki * f[0], hd);
+            const float aB = act_apply(attn_act, sB), attnB = aB * c;
+            const float gattB = seg_sum(gxj * vi0 * f[1], hd);
+            const float gsB = gattB * act_grad(attn_act, sB) * c;
+            acc[1] += gsB * qj * f[0];
+            const float gv1B = gvjx * vix + gvjy * viy + gvjz * viz;
+            const float gv2B = gvjx * g.x + gvjy * g.y + gvjz * g.z;
+            acc[2] += gxj * attnB * f[1];
+            acc[3] += gv1B * f[2];
+            acc[4] += gv2B * f[3];
+            const float s1B = vi1 * f[2];
+            acc[5] += gvjx * s1B; acc[6] += gvjy * s1B; acc[7] += gvjz * s1B;
+            if (j != i) {   // the self loop has d = 0 and no position dependence
+                const float gdB = gsB * qj * ki * df[0] + gxj * attnB * vi0 * df[1] + gv1B * vi1 * df[2] +
+                                  gv2B * vi2 * df[3] + gattB * aB * inv_hd * dc;
+                const float v2B = vi2 * f[3];
+                const float ghxB = gvjx * v2B, ghyB = gvjy * v2B, ghzB = gvjz * v2B;
+                const float inv_d = 1.0f / g.w;
+                const float dotA = ghxA * hx + ghyA * hy + ghzA * hz;
+                const float dotB = ghxB * g.x + ghyB * g.y + ghzB * g.z;
+                // -G_A + G_B
+                gp[0] += -(gdA * hx + (ghxA - dotA * hx) * inv_d) + (gdB * g.x + (ghxB - dotB * g.x) * inv_d);
+                gp[1] += -(gdA * hy + (ghyA - dotA * hy) * inv_d) + (gdB * g.y + (ghyB - dotB * g.y) * inv_d);
+                gp[2] += -(gdA * hz + (ghzA - dotA * hz) * inv_d) + (gdB * g.z + (ghzB - dotB * g.z) * inv_d);
+            }
+        }
+    }
+    slice_reduce<8>(acc, s_part, H);
+    if (valid && sl == 0) {
+        float* o = g_qkv + (size_t)i * H5 + h;
+        o[0] = acc[0]; o[H] = acc[1]; o[2 * H] = acc[2]; o[3 * H] = acc[3]; o[4 * H] = acc[4];
+        float* gv = g_vec_new + (size_t)i * 3 * H + h;
+        gv[0] += acc[5]; gv[H] += acc[6]; gv[2 * H] += acc[7];
+    }
+    atom_reduce<3>(gp, s_red);
+    if (valid && h == 0 && sl == 0) {
+        gpos[3 * (size_t)i] += gp[0];
+        gpos[3 * (size_t)i + 1] += gp[1];
+        gpos[3 * (size_t)i + 2] += gp[2];
+    }
+}
+
+// neighbour-embedding adjoint + force write-out: forces[i] = -(gpos[i] + sum_e u_e * g_d(e)),
+// g_d(e) = sum_h (g_xn_i ne_emb[z_j] + g_xn_j ne_emb[z_i]) fne'(d_e)       (both directions of the entry; dhat = -u)
+template <bool NE>
+__global__ void __launch_bounds__(512)
+et_final_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom,
+             const int* __restrict__ z32, const float* __restrict__ ne_emb, Tab tb, const float* __restrict__ g_xn,
+             const float* __restrict__ gpos, float* __restrict__ forces, int N, int H) {
+    extern __shared__ float smem[];
+    float* s_red = smem;
+    const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    float gp[3] = {0.f, 0.f, 0.f};
+    if (NE && valid) {
+        const float gi = g_xn[(size_t)i * H + h], ei = ne_emb[(size_t)z32[i] * H + h];
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0 + sl; e < r1; e += S) {
+            const int j = col[e];
+            if (j == i) continue;
+            const float4 g = geom[e];
+            float f[1], df[1];
+            tab_eval<1>(tb, g.w, H, h, f, df);
+            const float gd = (gi * ne_emb[(size_t)z32[j] * H + h] + g_xn[(size_t)j * H + h] * ei) * df[0];
+            gp[0] += g.x * gd; gp[1] += g.y * gd; gp[2] += g.z * gd;
+        }
+    }
+    atom_reduce<3>(gp, s_red);
+    if (valid && h == 0 && sl == 0) {
+        forces[3 * (size_t)i] = -(gpos[3 * (size_t)i] + gp[0]);
+        forces[3 * (size_t)i + 1] = -(gpos[3 * (size_t)i + 1] + gp[1]);
+        forces[3 * (size_t)i + 2] = -(gpos[3 * (size_t)i + 2] + gp[2]);
+    }
+}
+
+// ================================================================== workspace
+struct EtWs {
+    int32_t *num_found, *row_ptr, *col;
+    float* geom;
+    int* z32;
+    void* graph_ws;
+    size_t graph_ws_bytes;
+    float *cat0, *X[TMDN_MAX_LAYERS + 1], *VEC[TMDN_MAX_LAYERS + 1], *stat[TMDN_MAX_LAYERS + 1], *xl,
+        *QKV[TMDN_MAX_LAYERS], *VP[TMDN_MAX_LAYERS], *O[TMDN_MAX_LAYERS], *xa, *va;
+    // head
+    float *cat1, *vb1, *vec2_1, *h0_1, *a0_1, *h2_1, *v1, *cat2, *vb2, *h0_2, *a0_2, *e_atom;
+    // backward
+    float *d_a0_2, *g_cat2, *g_vb2, *g_v1, *g_h2, *g_vec2, *g_h0, *g_cat1, *g_vb, *g_x, *g_vecA, *g_vecB, *g_o, *g_vp,
+        *g_xa, *g_qkv, *g_xl, *g_xn, *gpos;
+};
+struct EtEntry { std::string name; size_t off, bytes; };
+template <typename T> T* ecarve(Arena& a, std::vector<EtEntry>* names, const char* name, size_t n) {
+    const size_t o = a.off;
+    T* p = a.get<T>(n);
+    if (names) names->push_back({name, o, n * sizeof(T)});
+    return p;
+}
+
+int carve_et(Arena& a, const tmdn_et_model* m, int64_t N, int64_t P, EtWs& w, std::vector<EtEntry>* names,
+             const double* box, int strategy) {
+    const size_t H = m->hidden, L = m->num_layers, n = (size_t)N, H2 = H / 2;
+    char buf[32];
+    w.num_found = ecarve<int32_t>(a, names, "num_found", 4);
+    w.row_ptr = ecarve<int32_t>(a, names, "row_ptr", n + 1);
+    w.col = ecarve<int32_t>(a, names, "col", (size_t)P);
+    w.geom = ecarve<float>(a, names, "geom", 4 * (size_t)P);
+    w.z32 = ecarve<int>(a, names, "z32", n);
+    w.graph_ws_bytes = tmdn_csr_build_workspace_bytes(strategy, N, box, m->cutoff_upper);
+    if (w.graph_ws_bytes == 0) {
+        tmdn_set_error("et: bad box for the cell strategy");
+        return TMDN_EINVAL;
+    }
+    w.graph_ws = ecarve<char>(a, names, "graph_ws", w.graph_ws_bytes);
+    w.cat0 = ecarve<float>(a, names, "cat0", n * 2 * H);
+    for (size_t l = 0; l <= L; ++l) {
+        snprintf(buf, sizeof buf, "x%zu", l); w.X[l] = ecarve<float>(a, names, buf, n * H);
+        snprintf(buf, sizeof buf, "vec%zu", l); w.VEC[l] = ecarve<float>(a, names, buf, n * 3 * H);
+        snprintf(buf, sizeof buf, "stat%zu", l); w.stat[l] = ecarve<float>(a, names, buf, n * 2);
+    }
+    w.xl = ecarve<float>(a, names, "xl", n * H);
+    for (size_t l = 0; l < L; ++l) {
+        snprintf(buf, sizeof buf, "qkv%zu", l); w.QKV[l] = ecarve<float>(a, names, buf, n * 5 * H);
+        snprintf(buf, sizeof buf, "vp%zu", l); w.VP[l] = ecarve<float>(a, names, buf, n * 9 * H);
+        snprintf(buf, sizeof buf, "o%zu", l); w.O[l] = ecarve<float>(a, names, buf, n * 3 * H);
+    }
+    w.xa = ecarve<float>(a, names, "xa", n * H);
+    w.va = ecarve<float>(a, names, "va", n * 3 * H);
+    w.cat1 = ecarve<float>(a, names, "cat1", n * 2 * H);
+    w.vb1 = ecarve<float>(a, names, "vb1", n * 3 * H);
+    w.vec2_1 = ecarve<float>(a, names, "vec2_1", n * 3 * H2);
+    w.h0_1 = ecarve<float>(a, names, "h0_1", n * H);
+    w.a0_1 = ecarve<float>(a, names, "a0_1", n * H);
+    w.h2_1 = ecarve<float>(a, names, "h2_1", n * H);
+    w.v1 = ecarve<float>(a, names, "v1", n * 3 * H2);
+    w.cat2 = ecarve<float>(a, names, "cat2", n * H);
+    w.vb2 = ecarve<float>(a, names, "vb2", n * 3 * H2);
+    w.h0_2 = ecarve<float>(a, names, "h0_2", n * H2);
+    w.a0_2 = ecarve<float>(a, names, "a0_2", n * H2);
+    w.e_atom = ecarve<float>(a, names, "e_atom", n);
+    w.d_a0_2 = ecarve<float>(a, names, "d_a0_2", n * H2);
+    w.g_cat2 = ecarve<float>(a, names, "g_cat2", n * H);
+    w.g_vb2 = ecarve<float>(a, names, "g_vb2", n * 3 * H2);
+    w.g_v1 = ecarve<float>(a, names, "g_v1", n * 3 * H2);
+    w.g_h2 = ecarve<float>(a, names, "g_h2", n * H);
+    w.g_vec2 = ecarve<float>(a, names, "g_vec2", n * 3 * H2);
+    w.g_h0 = ecarve<float>(a, names, "g_h0", n * H);
+    w.g_cat1 = ecarve<float>(a, names, "g_cat1", n * 2 * H);
+    w.g_vb = ecarve<float>(a, names, "g_vb", n * 3 * H);
+    w.g_x = ecarve<float>(a, names, "g_x", n * H);
+    w.g_vecA = ecarve<float>(a, names, "g_vecA", n * 3 * H);
+    w.g_vecB = ecarve<float>(a, names, "g_vecB", n * 3 * H);
+    w.g_o = ecarve<float>(a, names, "g_o", n * 3 * H);
+    w.g_vp = ecarve<float>(a, names, "g_vp", n * 9 * H);
+    w.g_xa = ecarve<float>(a, names, "g_xa", n * H);
+    w.g_qkv = ecarve<float>(a, names, "g_qkv", n * 5 * H);
+    w.g_xl = ecarve<float>(a, names, "g_xl", n * H);
+    w.g_xn = ecarve<float>(a, names, "g_xn", n * H);
+    w.gpos = ecarve<float>(a, names, "gpos", n * 3);
+    return TMDN_OK;
+}
+
+int check_et(const tmdn_et_model* m) {
+    TMDN_CHECK_ARG(m, "et: null model");
+    TMDN_CHECK_ARG(m->hidden >= 32 && m->hidden <= 1024 && m->hidden % 32 == 0,
+                   "et: hidden_channels must be a multiple of 32 in [32,1024] (got %d)", m->hidden);
+    TMDN_CHECK_ARG(m->num_layers >= 0 && m->num_layers <= TMDN_MAX_LAYERS, "et: num_layers out of range");
+    TMDN_CHECK_ARG(m->num_heads > 0 && m->hidden % m->num_heads == 0, "et: hidden must be divisible by num_heads");
+    const int hd = m->hidden / m->num_heads;
+    TMDN_CHECK_ARG(hd <= 32 && (hd & (hd - 1)) == 0, "et: head_dim must be a power of two <= 32 (got %d)", hd);
+    TMDN_CHECK_ARG(m->max_z > 0 && m->n_int > 0, "et: bad max_z / table size");
+    TMDN_CHECK_ARG(m->cutoff_upper > m->cutoff_lower && m->cutoff_lower >= 0, "et: bad cutoffs");
+    TMDN_CHECK_ARG(m->emb && m->out_ln_w && m->out_ln_b, "et: missing weights");
+    for (int l = 0; l < m->num_layers; ++l) TMDN_CHECK_ARG(m->layer[l].table, "et: missing filter table of layer %d", l);
+    if (m->has_neighbor_embedding) TMDN_CHECK_ARG(m->ne_emb && m->ne_table && m->ne_comb_w, "et: missing NE weights");
+    return TMDN_OK;
+}
+}  // namespace
+
+extern "C" size_t tmdn_et_workspace_bytes(const tmdn_et_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                          int strategy, const double box[9]) {
+    (void)n_mol;
+    if (check_et(m) != TMDN_OK || n_atoms <= 0 || max_edges <= 0) return 0;
+    Arena a(nullptr, 0);
+    EtWs w;
+    if (carve_et(a, m, n_atoms, max_edges, w, nullptr, box, strategy) != TMDN_OK) return 0;
+    return a.off + 256;
+}
+
+extern "C" int tmdn_et_workspace_lookup(const tmdn_et_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                        int strategy, const double box[9], const char* name, size_t* offset,
+                                        size_t* bytes) {
+    (void)n_mol;
+    TMDN_TRY(check_et(m));
+    TMDN_CHECK_ARG(name && offset && bytes, "lookup: null argument");
+    Arena a(nullptr, 0);
+    EtWs w;
+    std::vector<EtEntry> names;
+    TMDN_TRY(carve_et(a, m, n_atoms, max_edges, w, &names, box, strategy));
+    for (const auto& e : names)
+        if (e.name == name) {
+            *offset = e.off;
+            *bytes = e.bytes;
+            return TMDN_OK;
+        }
+    tmdn_set_error("lookup: unknown buffer '%s'", name);
+    return TMDN_EINVAL;
+}
+
+#define ET_K(name, ...)                      \
+    do {                                     \
+        KTimer ktimer__(name, stream);       \
+        __VA_ARGS__;                         \
+        TMDN_LAUNCH_CHECK();                 \
+    } while (0)
+
+extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, const float* pos, const int64_t* batch,
+                                     int64_t n_atoms, int64_t n_mol, const double box[9], int use_periodic,
+                                     int strategy, int64_t max_edges, float* energy, float* forces, int32_t* status,
+                                     void* workspace, size_t workspace_bytes, tmdn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    TMDN_TRY(check_et(m));
+    TMDN_CHECK_ARG(z && pos && batch && energy && status && workspace, "et: null pointer argument");
+    TMDN_CHECK_ARG(n_atoms > 0 && n_mol > 0 && max_edges > 0, "et: bad sizes");
+    TMDN_CHECK_ARG(max_edges < (1LL << 31) && n_atoms < (1LL << 31) / 16, "et: sizes exceed int32 indexing");
+    TMDN_CHECK_ARG(strategy != TMDN_CELL || box, "et: the cell strategy needs a box");
+    const int N = (int)n_atoms, H = m->hidden, L = m->num_layers, act = m->activation, H2 = H / 2;
+    const int hd = H / m->num_heads;
+    const int64_t P = max_edges;
+    const float lo = m->cutoff_lower, hi = m->cutoff_upper;
+    Arena arena(workspace, workspace_bytes);
+    EtWs w;
+    TMDN_TRY(carve_et(arena, m, n_atoms, P, w, nullptr, box, strategy));
+    if (!arena.ok) {
+        tmdn_set_error("et: workspace too small (%zu < %zu)", workspace_bytes, arena.off);
+        return TMDN_EWORKSPACE;
+    }
+    {
+        KTimer ktimer__("neighbors_csr", stream);
+        TMDN_TRY(tmdn_csr_build_f32(strategy, pos, batch, n_atoms, box, use_periodic, lo, hi, P, w.row_ptr, w.col, w.geom,
+                                    w.num_found, w.graph_ws, w.graph_ws_bytes, stream_));
+    }
+    TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
+    ET_K("et_prep", et_prep_kernel<<<(unsigned)cdiv(N, 256), 256, 0, stream>>>(z, w.z32, N, m->max_z, w.num_found,
+                                                                                (long long)P, status));
+    const float4* geom = (const float4*)w.geom;
+    const float inv_h = (float)((double)m->n_int / (double)hi);
+    const Tab ne_tab{(const float4*)m->ne_table, inv_h, m->n_int};
+    const EdgeLaunch e1 = edge_launch(N, H, 1024, 1), e4 = edge_launch(N, H, 1024, 4), e8 = edge_launch(N, H, 512, 8);
+    const int apb = H >= 128 ? 1 : 128 / H;
+    const dim3 lblock(H, 1, apb);
+    const unsigned lgrid = (unsigned)cdiv(N, apb);
+    const long long NH = (long long)N * H;
+    const unsigned egrid = (unsigned)cdiv(NH, 256);
+    const unsigned hgrid = (unsigned)cdiv((long long)N * H2, 256);
+
+    // ---- embedding (+ neighbour embedding)
+    if (m->has_neighbor_embedding) {
+        ET_K("et_embed_fwd", et_embed_fwd<true><<<e1.grid, e1.block, e1.smem, stream>>>(
+                                 w.row_ptr, w.col, geom, w.z32, m->emb, m->ne_emb, ne_tab, N, H, w.cat0, 2 * H));
+        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.cat0, 2 * H, m->ne_comb_w, m->ne_comb_b, w.X[0], H, N, H, 2 * H), stream));
+    } else {
+        ET_K("et_embed_fwd", et_embed_fwd<false><<<e1.grid, e1.block, e1.smem, stream>>>(
+                                 w.row_ptr, w.col, geom, w.z32, m->emb, nullptr, ne_tab, N, H, w.X[0], H));
+    }
+    TMDN_CUDA(cudaMemsetAsync(w.VEC[0], 0, sizeof(float) * 3 * (size_t)NH, stream));
+    // ---- attention layers
+    for (int l = 0; l < L; ++l) {
+        const tmdn_et_layer& ly = m->layer[l];
+        const Tab tb{(const float4*)ly.table, inv_h, m->n_int};
+        ET_K("et_ln_fwd", et_ln_fwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, ly.ln_b, w.xl, H, w.stat[l], N, H));
+        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.xl, H, ly.qkv_w, ly.qkv_b, w.QKV[l], 5 * H, N, 5 * H, H), stream));
+        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.VEC[l], H, ly.vp_w, nullptr, w.VP[l], 3 * H, 3 * N, 3 * H, H), stream));
+        ET_K("et_edge_fwd", et_edge_fwd<<<e4.grid, e4.block, e4.smem, stream>>>(
+                                w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], N, H, w.xa,
+                                w.va));
+        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.xa, H, ly.o_w, ly.o_b, w.O[l], 3 * H, N, 3 * H, H), stream));
+        ET_K("et_update_fwd", et_update_fwd<<<egrid, 256, 0, stream>>>(w.X[l], w.VEC[l], w.VP[l], w.O[l], w.va,
+                                                                       w.X[l + 1], w.VEC[l + 1], NH, H));
+    }
+    // ---- out_norm written straight into the first half of cat1 = [xo | vec1]
+    ET_K("et_ln_fwd", et_ln_fwd<<<lgrid, lblock, 0, stream>>>(w.X[L], m->out_ln_w, m->out_ln_b, w.cat1, 2 * H, w.stat[L],
+                                                              N, H));
+    // ---- gated block 1: H -> H/2 (scalar activation)
+    const tmdn_et_gated& g1 = m->head[0];
+    const tmdn_et_gated& g2 = m->head[1];
+    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.VEC[L], H, g1.w1, nullptr, w.vb1, H, 3 * N, H, H), stream));
+    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.VEC[L], H, g1.w2, nullptr, w.vec2_1, H2, 3 * N, H2, H), stream));
+    ET_K("et_gate_norm_fwd", et_gate_norm_fwd<<<egrid, 256, 0, stream>>>(w.vb1, w.cat1, NH, H));
+    {
+        GemmP p = gemm_desc(w.cat1, 2 * H, g1.u0_w, g1.u0_b, w.a0_1, H, N, H, 2 * H);
+        p.C2 = w.h0_1; p.act = act;
+        TMDN_TRY(gemm1(EPI_ACT, p, stream));
+        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.a0_1, H, g1.u2_w, g1.u2_b, w.h2_1, H, N, H, H), stream));
+    }
+    ET_K("et_gate_out_fwd", et_gate_out_fwd<<<hgrid, 256, 0, stream>>>(w.h2_1, w.vec2_1, act, w.cat2, H, w.v1,
+                                                                       (long long)N * H2, H2));
+    // ---- gated block 2: H/2 -> 1 (its vector output does not reach the energy)
+    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.v1, H2, g2.w1, nullptr, w.vb2, H2, 3 * N, H2, H2), stream));
+    ET_K("et_gate_norm_fwd", et_gate_norm_fwd<<<hgrid, 256, 0, stream>>>(w.vb2, w.cat2, (long long)N * H2, H2));
+    {
+        GemmP p = gemm_desc(w.cat2, H, g2.u0_w, g2.u0_b, w.a0_2, H2, N, H2, H);
+        p.C2 = w.h0_2; p.act = act;
+        TMDN_TRY(gemm1(EPI_ACT, p, stream));
+    }
+    ET_K("et_head_energy", et_head_energy<<<(unsigned)cdiv(N, 4), 128, 0, stream>>>(w.a0_2, g2.u2_w, g2.u2_b, m->std,
+                                                                                   w.e_atom, N, H2));
+    ET_K("et_mol_reduce", et_mol_reduce<<<(unsigned)n_mol, 128, 0, stream>>>(w.e_atom, batch, N, m->mean, energy));
+    if (!forces) return TMDN_OK;
+
+    // ================================================================= backward
+    TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
+    // block 2
+    ET_K("et_head_seed_bwd", et_head_seed_bwd<<<hgrid, 256, 0, stream>>>(w.h0_2, g2.u2_w, m->std, act, w.d_a0_2,
+                                                                         (long long)N * H2, H2));
+    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.d_a0_2, H2, g2.u0_wT, nullptr, w.g_cat2, H, N, H, H2), stream));
+    ET_K("et_gate_norm_bwd", et_gate_norm_bwd<<<hgrid, 256, 0, stream>>>(w.vb2, w.cat2, w.g_cat2, w.g_vb2,
+                                                                         (long long)N * H2, H2));
+    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_vb2, H2, g2.w1T, nullptr, w.g_v1, H2, 3 * N, H2, H2), stream));
+    // block 1
+    ET_K("et_gate_out_bwd", et_gate_out_bwd<<<hgrid, 256, 0, stream>>>(w.h2_1, w.vec2_1, act, w.g_cat2, H, w.g_v1, w.g_h2,
+                                                                       w.g_vec2, (long long)N * H2, H2));
+    {
+        GemmP p = gemm_desc(w.g_h2, H, g1.u2_wT, nullptr, w.g_h0, H, N, H, H);
+        p.aux = w.h0_1; p.ldaux = H; p.act = act;
+        TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
+        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_h0, H, g1.u0_wT, nullptr, w.g_cat1, 2 * H, N, 2 * H, H), stream));
+    }
+    ET_K("et_gate_norm_bwd", et_gate_norm_bwd<<<egrid, 256, 0, stream>>>(w.vb1, w.cat1, w.g_cat1, w.g_vb, NH, H));
+    float* g_vec = w.g_vecA;
+    float* g_vec_new = w.g_vecB;
+    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_vb, H, g1.w1T, nullptr, g_vec, H, 3 * N, H, H), stream));
+    {
+        GemmP p = gemm_desc(w.g_vec2, H2, g1.w2T, nullptr, g_vec, H, 3 * N, H, H2);
+        p.accumulate = 1;
+        TMDN_TRY(gemm1(EPI_NONE, p, stream));
+    }
+    ET_K("et_ln_bwd", et_ln_bwd<<<lgrid, lblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat[L], w.g_cat1, 2 * H, w.g_x, 0, N,
+                                                              H));
+    for (int l = L - 1; l >= 0; --l) {
+        const tmdn_et_layer& ly = m->layer[l];
+        const Tab tb{(const float4*)ly.table, inv_h, m->n_int};
+        ET_K("et_update_bwd", et_update_bwd<<<egrid, 256, 0, stream>>>(w.g_x, g_vec, w.VP[l], w.O[l], w.g_o, w.g_vp,
+                                                                       g_vec_new, NH, H));
+        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_o, 3 * H, ly.o_wT, nullptr, w.g_xa, H, N, H, 3 * H), stream));
+        {
+            GemmP p = gemm_desc(w.g_vp, 3 * H, ly.vp_wT, nullptr, g_vec_new, H, 3 * N, H, 3 * H);
+            p.accumulate = 1;
+            TMDN_TRY(gemm1(EPI_NONE, p, stream));
+        }
+        ET_K("et_edge_bwd", et_edge_bwd<<<e8.grid, e8.block, e8.smem, stream>>>(
+                                w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], w.g_xa,
+                                g_vec, N, H, w.g_qkv, g_vec_new, w.gpos));
+        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_qkv, 5 * H, ly.qkv_wT, nullptr, w.g_xl, H, N, H, 5 * H), stream));
+        ET_K("et_ln_bwd", et_ln_bwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, w.stat[l], w.g_xl, H, w.g_x, 1, N, H));
+        float* t = g_vec; g_vec = g_vec_new; g_vec_new = t;
+    }
+    if (m->has_neighbor_embedding) {
+        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_x, H, m->ne_comb_w2T, nullptr, w.g_xn, H, N, H, H), stream));
+        ET_K("et_final_bwd", et_final_bwd<true><<<e8.grid, e8.block, e8.smem, stream>>>(
+                                 w.row_ptr, w.col, geom, w.z32, m->ne_emb, ne_tab, w.g_xn, w.gpos, forces, N, H));
+    } else {
+        ET_K("et_final_bwd", et_final_bwd<false><<<e8.grid, e8.block, e8.smem, stream>>>(
+                                 w.row_ptr, w.col, geom, w.z32, nullptr, ne_tab, nullptr, w.gpos, forces, N, H));
+    }
+    return TMDN_OK;
+}

@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include "gemm.cuh"
 #include "tensor3.cuh"
+#include "edge_common.cuh"
 #include "scan.cuh"
 #include <vector>
 #include <string>
@@ -69,20 +70,6 @@ __device__ __forceinline__ void filter_val_grad(const FilterView& fv, size_t e, 
     }
 }
 
-__device__ __forceinline__ void cutoff_fn(float d, float lo, float hi, float& c, float& dc) {
-    const float PI = 3.14159265358979323846f;
-    if (lo > 0.f) {  // models/utils.py:369-385
-        const float arg = PI * (2.0f * (d - lo) / (hi - lo) + 1.0f);
-        const float m = (d < hi && d > lo) ? 1.0f : 0.0f;
-        c = 0.5f * (cosf(arg) + 1.0f) * m;
-        dc = -0.5f * sinf(arg) * (2.0f * PI / (hi - lo)) * m;
-    } else {         // models/utils.py:386-390
-        const float m = d < hi ? 1.0f : 0.0f;
-        c = 0.5f * (cosf(d * PI / hi) + 1.0f) * m;
-        dc = -0.5f * sinf(d * PI / hi) * (PI / hi) * m;
-    }
-}
-
 // ------------------------------------------------------------------ small device utilities
 __device__ __forceinline__ void ld9(const float* __restrict__ p, size_t i, int H, int h, float x[9]) {
     const float* q = p + i * 9 * H + h;
@@ -111,63 +98,6 @@ template <int NV> __device__ __forceinline__ void row_reduce(float (&v)[NV], flo
         for (int w = 0; w < nw; ++w) s += s_red[(a * nw + w) * NV + k];
         v[k] = s;
     }
-}
-
-// ---- edge kernels: block = (H channels, S edge slices, A atoms).  Slice s of an atom's thread group walks the
-// edges r0+s, r0+s+S, ... of the row; partial sums are combined through shared memory in slice order, so the
-// result depends only on (row content, S) and stays bit-reproducible.  S > 1 shortens the serial gather chain of
-// small systems (166 atoms: 8 slices -> 15 dependent iterations instead of 120).
-__device__ __forceinline__ void slice_reduce9(float (&v)[9], float* s_part, int H) {
-    const int S = blockDim.y;
-    if (S == 1) return;
-    const int h = threadIdx.x, sl = threadIdx.y, a = threadIdx.z;
-    __syncthreads();
-#pragma unroll
-    for (int c = 0; c < 9; ++c) s_part[(((size_t)a * S + sl) * 9 + c) * H + h] = v[c];
-    __syncthreads();
-    if (sl == 0) {
-#pragma unroll
-        for (int c = 0; c < 9; ++c) {
-            float t = 0.f;
-            for (int q = 0; q < S; ++q) t += s_part[(((size_t)a * S + q) * 9 + c) * H + h];
-            v[c] = t;
-        }
-    }
-}
-// Sum over all threads of one atom's group (channels x slices).  Every thread of the block must call.
-template <int NV> __device__ __forceinline__ void atom_reduce(float (&v)[NV], float* s_red) {
-    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
-    const int lane = tid & 31, wr = tid >> 5, nw = (blockDim.x * blockDim.y) >> 5, a = threadIdx.z;
-#pragma unroll
-    for (int k = 0; k < NV; ++k) v[k] = warp_sum(v[k]);
-    __syncthreads();
-    if (lane == 0)
-#pragma unroll
-        for (int k = 0; k < NV; ++k) s_red[(a * nw + wr) * NV + k] = v[k];
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-        float t = 0.f;
-        for (int w = 0; w < nw; ++w) t += s_red[(a * nw + w) * NV + k];
-        v[k] = t;
-    }
-}
-struct EdgeLaunch { dim3 block; unsigned grid; size_t smem; };
-// s_red (<= 32 warps x 3 values per atom) lives at the start of dynamic shared memory, slice partials after it
-constexpr int EDGE_RED_FLOATS = 128;
-static EdgeLaunch edge_launch(int N, int H, int max_threads) {
-    int smax = max_threads / H;
-    if (smax < 1) smax = 1;
-    const long long target = 148LL * 2048;
-    int S = 1;
-    while (S < smax && (long long)N * H * S < target) S *= 2;
-    int A = 128 / (H * S);
-    if (A < 1) A = 1;
-    EdgeLaunch l;
-    l.block = dim3((unsigned)H, (unsigned)S, (unsigned)A);
-    l.grid = (unsigned)cdiv(N, A);
-    l.smem = sizeof(float) * ((size_t)EDGE_RED_FLOATS * A + (S > 1 ? (size_t)A * S * 9 * H : 0));
-    return l;
 }
 
 __global__ void tn_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ z32, int n, int max_z,
@@ -269,7 +199,7 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict_
             acc[8] += w3 * (g.y * g.z);
         }
     }
-    slice_reduce9(acc, s_part, H);
+    slice_reduce<9>(acc, s_part, H);
     const bool lead = sl == 0;
     if (valid && lead) st9(ias, (size_t)i, H, h, acc);
     const float q = lead ? t3_q(acc) : 0.f;
@@ -384,7 +314,7 @@ __global__ void __launch_bounds__(1024) tn_msg_fwd(const int* __restrict__ row_p
             m[4] += f[2] * y[4]; m[5] += f[2] * y[5]; m[6] += f[2] * y[6]; m[7] += f[2] * y[7]; m[8] += f[2] * y[8];
         }
     }
-    slice_reduce9(m, s_part, H);
+    slice_reduce<9>(m, s_part, H);
     if (!valid || sl != 0) return;
     st9(M, (size_t)i, H, h, m);
     float yi[9], tau[9], th[9];
@@ -439,7 +369,7 @@ __global__ void __launch_bounds__(512) tn_msg_bwd(const int* __restrict__ row_pt
             gp[0] += g.x * ge; gp[1] += g.y * ge; gp[2] += g.z * ge;
         }
     }
-    slice_reduce9(acc, s_part, H);
+    slice_reduce<9>(acc, s_part, H);
     if (valid && sl == 0) st9(dY, (size_t)i, H, h, acc);
     atom_reduce<3>(gp, s_red);
     if (valid && h == 0 && sl == 0) {

@@ -366,6 +366,113 @@ std::vector<int64_t> tensornet_debug_lookup(int64_t handle, int64_t n_atoms, int
     return {(int64_t)off, (int64_t)bytes};
 }
 
+// ------------------------------------------------------------------ Equivariant Transformer model handles
+struct EtHandle {
+    tmdn_et_model m;
+    std::vector<Tensor> keep;
+};
+std::unordered_map<int64_t, std::shared_ptr<EtHandle>> g_et;
+
+// Weight order (must match torchmdnet/models/torchmd_et.py::pack_weights):
+//   emb ne_emb ne_table ne_comb_w ne_comb_b ne_comb_w2T out_ln_w out_ln_b
+//   head block x2: w1 w1T w2 w2T u0_w u0_b u0_wT u2_w u2_b u2_wT
+//   per layer: ln_w ln_b qkv_w qkv_b qkv_wT vp_w vp_wT o_w o_b o_wT table
+// iparams: hidden num_layers num_heads max_z activation attn_activation has_ne n_int ; fparams: lo hi mean std
+int64_t et_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::vector<double> fp) {
+    TORCH_CHECK(ip.size() == 8 && fp.size() == 4, "et_create: bad parameter vectors");
+    auto h = std::make_shared<EtHandle>();
+    tmdn_et_model& m = h->m;
+    memset(&m, 0, sizeof(m));
+    m.hidden = (int32_t)ip[0]; m.num_layers = (int32_t)ip[1]; m.num_heads = (int32_t)ip[2]; m.max_z = (int32_t)ip[3];
+    m.activation = (int32_t)ip[4]; m.attn_activation = (int32_t)ip[5]; m.has_neighbor_embedding = (int32_t)ip[6];
+    m.n_int = (int32_t)ip[7];
+    m.cutoff_lower = (float)fp[0]; m.cutoff_upper = (float)fp[1]; m.mean = (float)fp[2]; m.std = (float)fp[3];
+    TORCH_CHECK(m.num_layers >= 0 && m.num_layers <= TMDN_MAX_LAYERS, "et_create: too many layers");
+    const size_t expect = 28 + 11 * (size_t)m.num_layers;
+    TORCH_CHECK(w.size() == expect, "et_create: expected ", expect, " weight tensors, got ", w.size());
+    size_t k = 0;
+    auto next = [&]() -> const float* { return fptr(w[k++]); };
+    m.emb = next(); m.ne_emb = next(); m.ne_table = next(); m.ne_comb_w = next(); m.ne_comb_b = next();
+    m.ne_comb_w2T = next(); m.out_ln_w = next(); m.out_ln_b = next();
+    for (int b = 0; b < 2; ++b) {
+        tmdn_et_gated& g = m.head[b];
+        g.hin = b == 0 ? m.hidden : m.hidden / 2;
+        g.out = b == 0 ? m.hidden / 2 : 1;
+        g.w1 = next(); g.w1T = next(); g.w2 = next(); g.w2T = next();
+        g.u0_w = next(); g.u0_b = next(); g.u0_wT = next(); g.u2_w = next(); g.u2_b = next(); g.u2_wT = next();
+    }
+    for (int l = 0; l < m.num_layers; ++l) {
+        tmdn_et_layer& y = m.layer[l];
+        y.ln_w = next(); y.ln_b = next(); y.qkv_w = next(); y.qkv_b = next(); y.qkv_wT = next();
+        y.vp_w = next(); y.vp_wT = next(); y.o_w = next(); y.o_b = next(); y.o_wT = next(); y.table = next();
+    }
+    h->keep = std::move(w);
+    std::lock_guard<std::mutex> lock(g_mu);
+    const int64_t id = g_next++;
+    g_et[id] = h;
+    return id;
+}
+void et_destroy(int64_t id) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    g_et.erase(id);
+}
+std::shared_ptr<EtHandle> et_get(int64_t id) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    auto it = g_et.find(id);
+    TORCH_CHECK(it != g_et.end(), "et: unknown model handle ", id);
+    return it->second;
+}
+
+std::tuple<Tensor, Tensor, Tensor, Tensor> et_energy_forces(int64_t handle, const Tensor& z, const Tensor& pos,
+                                                            const Tensor& batch, const Tensor& box_vectors,
+                                                            bool use_periodic, const std::string& strategy,
+                                                            int64_t max_edges, int64_t n_mol, bool compute_forces,
+                                                            const c10::optional<Tensor>& workspace) {
+    auto h = et_get(handle);
+    TORCH_CHECK(pos.is_cuda(), "et_energy_forces: CUDA tensors required (sm_100a build, no CPU fallback)");
+    TORCH_CHECK(pos.scalar_type() == at::kFloat && pos.dim() == 2 && pos.size(1) == 3 && pos.is_contiguous(),
+                "et_energy_forces: pos must be a contiguous float32 [N,3] tensor");
+    TORCH_CHECK(z.scalar_type() == at::kLong && z.dim() == 1 && z.is_contiguous() && z.size(0) == pos.size(0),
+                "et_energy_forces: z must be a contiguous int64 [N] tensor");
+    TORCH_CHECK(batch.scalar_type() == at::kLong && batch.dim() == 1 && batch.is_contiguous() &&
+                    batch.size(0) == pos.size(0),
+                "et_energy_forces: batch must be a contiguous int64 [N] tensor");
+    TORCH_CHECK(z.device() == pos.device() && batch.device() == pos.device(), "et_energy_forces: device mismatch");
+    const c10::cuda::CUDAGuard guard(pos.device());
+    const int64_t n = pos.size(0);
+    const int sid = strategy_id(strategy);
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    TORCH_CHECK(have_box || !(use_periodic || sid == TMDN_CELL), "et_energy_forces: box required");
+    const size_t need = tmdn_et_workspace_bytes(&h->m, n, max_edges, n_mol, sid, have_box ? box : nullptr);
+    TORCH_CHECK(need > 0, "et_energy_forces: ", tmdn_last_error());
+    Tensor ws;
+    if (workspace.has_value() && workspace->defined() && (size_t)workspace->numel() >= need && workspace->is_cuda() &&
+        workspace->scalar_type() == at::kByte)
+        ws = *workspace;
+    else
+        ws = at::empty({(int64_t)need}, pos.options().dtype(at::kByte));
+    Tensor energy = at::empty({n_mol, 1}, pos.options());
+    Tensor forces = compute_forces ? at::empty({n, 3}, pos.options()) : at::empty({0, 3}, pos.options());
+    Tensor status = at::empty({4}, pos.options().dtype(at::kInt));
+    TMDN_CALL(tmdn_et_energy_forces(&h->m, z.data_ptr<int64_t>(), pos.data_ptr<float>(), batch.data_ptr<int64_t>(), n,
+                                    n_mol, have_box ? box : nullptr, use_periodic, sid, max_edges,
+                                    energy.data_ptr<float>(), compute_forces ? forces.data_ptr<float>() : nullptr,
+                                    status.data_ptr<int32_t>(), ws.data_ptr(), (size_t)ws.numel(), cur_stream()));
+    return std::make_tuple(energy, forces, status, ws);
+}
+
+std::vector<int64_t> et_debug_lookup(int64_t handle, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                     const std::string& strategy, const Tensor& box_vectors, const std::string& name) {
+    auto h = et_get(handle);
+    size_t off = 0, bytes = 0;
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    TMDN_CALL(tmdn_et_workspace_lookup(&h->m, n_atoms, max_edges, n_mol, strategy_id(strategy),
+                                       have_box ? box : nullptr, name.c_str(), &off, &bytes));
+    return {(int64_t)off, (int64_t)bytes};
+}
+
 int64_t launch_count() { return (int64_t)tmdn_launch_count(); }
 void profile_enable(bool on) { TMDN_CALL(tmdn_profile_enable(on ? 1 : 0)); }
 std::string profile_report() {
@@ -396,6 +503,15 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
           "bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces, Tensor? workspace) -> "
           "(Tensor, Tensor, Tensor, Tensor)",
           tensornet_energy_forces);
+    m.def("et_create(Tensor[] weights, int[] iparams, float[] fparams) -> int", et_create);
+    m.def("et_destroy(int handle) -> ()", et_destroy);
+    m.def("et_energy_forces(int handle, Tensor z, Tensor pos, Tensor batch, Tensor box_vectors, "
+          "bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces, Tensor? workspace) -> "
+          "(Tensor, Tensor, Tensor, Tensor)",
+          et_energy_forces);
+    m.def("et_debug_lookup(int handle, int n_atoms, int max_edges, int n_mol, str strategy, Tensor box_vectors, "
+          "str name) -> int[]",
+          et_debug_lookup);
     m.def("launch_count() -> int", launch_count);
     m.def("profile_enable(bool on) -> ()", profile_enable);
     m.def("profile_report() -> str", profile_report);

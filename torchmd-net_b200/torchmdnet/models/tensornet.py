@@ -17,7 +17,7 @@ from typing import Optional, Tuple
 import torch
 from torch import Tensor, nn
 
-from .. import _native
+from ._fused import FusedRepresentation
 from .utils import (ACT_ID, RBF_ID, CosineCutoff, OptimizedDistance, _fused_only, act_class_mapping,
                     rbf_class_mapping)
 
@@ -108,7 +108,7 @@ def _cutoff_and_grad(d, lo, hi):
     return 0.5 * (torch.cos(d * pi / hi) + 1) * m, -0.5 * torch.sin(d * pi / hi) * (pi / hi) * m
 
 
-def filter_table(d, rbf_type, p0, p1, lo, hi, layers, act, final_act):
+def filter_table(d, rbf_type, p0, p1, lo, hi, layers, act, final_act, cutoff=True):
     """f(d) = [act o] Lin_n(... act(Lin_1(rbf(d)))) * C(d) and df/dd at the points ``d`` (all in d.dtype;
     called in fp64 on the device).  ``layers`` = [(W[out,in], b[out]), ...].  Reference functions:
     models/utils.py:298-300, 339-344, 368-390; tensornet.py:295-304, 381-382."""
@@ -128,6 +128,8 @@ def filter_table(d, rbf_type, p0, p1, lo, hi, layers, act, final_act):
         if k < len(layers) - 1 or final_act:
             h, gact = _act_and_grad(act, h)
             t = t * gact
+    if not cutoff:
+        return h, t
     c, dc = _cutoff_and_grad(d, lo, hi)
     return h * c[:, None], t * c[:, None] + h * dc[:, None]
 
@@ -139,10 +141,12 @@ def hermite_coefficients(f, df, h):
     return torch.stack([f0, d0, 3 * (f1 - f0) - 2 * d0 - d1, 2 * (f0 - f1) + d0 + d1], -1)
 
 
-class TensorNet(nn.Module):
+class TensorNet(FusedRepresentation):
     """Drop-in for ``torchmdnet.models.tensornet.TensorNet`` (tensornet.py:70-234): same constructor, same
     parameters.  ``filter_mode``: "exact" evaluates the per-edge filter MLPs with fp32 GEMMs, "table"
     evaluates them from a cubic Hermite table in d built in fp64 from the weights (``table_intervals``)."""
+    _op = "tensornet"
+    _kernel_name = "TensorNet"
 
     def __init__(self, hidden_channels=128, num_layers=2, num_rbf=32, rbf_type="expnorm", trainable_rbf=False,
                  activation="silu", cutoff_lower=0, cutoff_upper=4.5, max_num_neighbors=64, max_z=128,
@@ -178,11 +182,8 @@ class TensorNet(nn.Module):
         self.distance = OptimizedDistance(cutoff_lower, cutoff_upper, max_num_pairs=-max_num_neighbors,
                                           return_vecs=True, loop=True, check_errors=False,
                                           resize_to_fit=not static_shapes, long_edge_index=True)
+        self._init_fused()
         self.filter_mode = "exact"
-        self.table_intervals = 4096
-        self._handle = None
-        self._pack_key = None
-        self._workspace = None
         self.reset_parameters()
 
     def reset_parameters(self):
@@ -255,64 +256,8 @@ class TensorNet(nn.Module):
         fparams = [lo, hi, float(mean), float(std)]
         return w, iparams, fparams
 
-    def _tensors_for_key(self, head):
-        mods = [self] if head is None else [self, head]
-        for m in mods:
-            yield from m.parameters()
-            yield from m.buffers()
-
-    def native_handle(self, head: Optional[nn.Module] = None, mean: float = 0.0, std: float = 1.0) -> int:
-        """Handle of the packed model inside the shim; repacked when any weight changed."""
-        _native.load()
-        key = (tuple((t.data_ptr(), t._version, t.device) for t in self._tensors_for_key(head)),
-               self.filter_mode, self.table_intervals, float(mean), float(std))
-        if key != self._pack_key:
-            p = self.linear.weight
-            _native.require_cuda(p, "TensorNet")
-            if p.dtype != torch.float32:
-                raise NotImplementedError("TensorNet kernels are fp32 (precision: 32); got %s" % p.dtype)
-            if self._handle is not None:
-                torch.ops.torchmdnet_b200.tensornet_destroy(self._handle)
-            w, ip, fp = self.pack_weights(head, mean, std)
-            self._handle = torch.ops.torchmdnet_b200.tensornet_create(w, ip, fp)
-            self._pack_key = key
-        return self._handle
-
-    def __del__(self):
-        try:
-            if self._handle is not None:
-                torch.ops.torchmdnet_b200.tensornet_destroy(self._handle)
-        except Exception:
-            pass
-
-    # -------------------------------------------------------------------------------------------- running
-    def energy_forces(self, z: Tensor, pos: Tensor, batch: Tensor, n_mol: int, head: Optional[nn.Module],
-                      mean: float, std: float, compute_forces: bool = True) -> Tuple[Tensor, Tensor, Tensor]:
-        """One fused evaluation: -> (y[n_mol,1], forces[N,3] (empty if not compute_forces), status int32[4]).
-        status[0] = edges found (incl. self loops), status[1] = 1 if they exceeded the capacity
-        max_num_neighbors*N (models/utils.py:234-236), status[2] = 1 if some z was outside [0,max_z)."""
-        handle = self.native_handle(head, mean, std)
-        _native.require_cuda(pos, "TensorNet")
-        if pos.dtype != torch.float32:
-            raise NotImplementedError("TensorNet kernels are fp32; got positions of dtype %s" % pos.dtype)
-        dist = self.distance
-        n = pos.shape[0]
-        max_edges = dist.max_num_pairs if dist.max_num_pairs > 0 else -dist.max_num_pairs * n
-        y, f, status, ws = torch.ops.torchmdnet_b200.tensornet_energy_forces(
-            handle, z.contiguous(), pos.detach().contiguous(), batch.contiguous(), dist.box, dist.use_periodic,
-            dist.strategy, max_edges, n_mol, compute_forces, self._workspace)
-        self._workspace = ws
-        if dist.check_errors and int(status[1]) != 0:
-            raise RuntimeError("Found num_pairs({}) > max_num_pairs({})".format(int(status[0]), max_edges))
-        return y, f, status
-
-    def debug_buffer(self, name: str, n_atoms: int, n_mol: int, dtype=torch.float32) -> Tensor:
-        """Flat view of a named intermediate of the LAST call (names as in oracle/staged_tensornet.py)."""
-        dist = self.distance
-        max_edges = dist.max_num_pairs if dist.max_num_pairs > 0 else -dist.max_num_pairs * n_atoms
-        off, nbytes = torch.ops.torchmdnet_b200.tensornet_debug_lookup(self._handle, n_atoms, max_edges, n_mol,
-                                                                       dist.strategy, dist.box, name)
-        return self._workspace[off:off + nbytes].view(dtype)
+    def _extra_key(self):
+        return (self.filter_mode,)
 
     def forward(self, z: Tensor, pos: Tensor, batch: Tensor, q: Optional[Tensor] = None,
                 s: Optional[Tensor] = None):

@@ -6,7 +6,9 @@ from typing import Optional
 import torch
 from torch import Tensor, nn
 
-from .utils import (CosineCutoff, NeighborEmbedding, OptimizedDistance, _fused_only, _xavier_zero_bias,
+from ._fused import FusedRepresentation
+from .tensornet import filter_table, hermite_coefficients
+from .utils import (ACT_ID, CosineCutoff, NeighborEmbedding, OptimizedDistance, _fused_only, _xavier_zero_bias,
                     act_class_mapping, rbf_class_mapping)
 
 __all__ = ["TorchMD_ET"]
@@ -54,8 +56,13 @@ class EquivariantMultiHeadAttention(nn.Module):
     forward = _fused_only
 
 
-class TorchMD_ET(nn.Module):
-    """Drop-in constructor for ``torchmdnet.models.torchmd_et.TorchMD_ET`` (torchmd_et.py:55-152)."""
+class TorchMD_ET(FusedRepresentation):
+    """Drop-in for ``torchmdnet.models.torchmd_et.TorchMD_ET`` (torchmd_et.py:55-152): same constructor, same
+    parameters; evaluated by the fused kernels of csrc/et.cu.  The distance filters (dk_proj, dv_proj, the
+    neighbour-embedding distance_proj) are univariate in d and are evaluated from cubic Hermite tables built in fp64
+    from the weights (``table_intervals`` intervals over [0, cutoff_upper])."""
+    _op = "et"
+    _kernel_name = "TorchMD_ET"
 
     def __init__(self, hidden_channels=128, num_layers=6, num_rbf=50, rbf_type="expnorm", trainable_rbf=True,
                  activation="silu", attn_activation="silu", neighbor_embedding=True, num_heads=8,
@@ -92,6 +99,7 @@ class TorchMD_ET(nn.Module):
                                           attn_activation, cutoff_lower, cutoff_upper, dtype)
             for _ in range(num_layers)])
         self.out_norm = nn.LayerNorm(hidden_channels, dtype=dtype)
+        self._init_fused()
         self.reset_parameters()
 
     def reset_parameters(self):
@@ -103,8 +111,67 @@ class TorchMD_ET(nn.Module):
             attn.reset_parameters()
         self.out_norm.reset_parameters()
 
-    forward = _fused_only
+    # -------------------------------------------------------------------------------------------- packing
+    def pack_weights(self, head: Optional[nn.Module], mean: float, std: float):
+        """-> (weights in the order csrc/torch_shim.cpp::et_create expects, iparams, fparams)."""
+        if head is None:
+            raise NotImplementedError("TorchMD_ET is evaluated together with its EquivariantScalar head")
+        dev = self.embedding.weight.device
+        H, nh, K = self.hidden_channels, self.num_heads, self.num_rbf
+        hd = H // nh
+        f32 = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()   # noqa: E731
+        f64 = lambda t: t.detach().to(device=dev, dtype=torch.float64)                 # noqa: E731
+        tr = lambda t: f32(t.detach().t())                                             # noqa: E731
+        lo, hi = float(self.cutoff_lower), float(self.cutoff_upper)
+        n_int = int(self.table_intervals)
+        if self.rbf_type == "expnorm":
+            p0, p1 = f64(self.distance_expansion.means), f64(self.distance_expansion.betas)
+        else:
+            p0, p1 = f64(self.distance_expansion.offset), f64(self.distance_expansion.coeff).expand(K)
+        grid = torch.linspace(0.0, hi, n_int + 1, device=dev, dtype=torch.float64)
+        step = hi / n_int
 
-    def energy_forces(self, *a, **k):
-        raise NotImplementedError("the fused Equivariant Transformer kernels (csrc/et.cu) are not built yet; "
-                                  "there is no PyTorch or CPU fallback")
+        def table(lin, act, n_out, cutoff):
+            """[n_int, n_out, 4] Hermite coefficients of [act o] lin(rbf(d)) [* C(d)]; the constant 1 if lin is None"""
+            if lin is None:
+                c = torch.zeros(n_int, n_out, 4, device=dev, dtype=torch.float64)
+                c[..., 0] = 1.0
+                return c
+            f, df = filter_table(grid, self.rbf_type, p0, p1, lo, hi, [(f64(lin[0]), f64(lin[1]))],
+                                 act, act is not None, cutoff=cutoff)
+            return hermite_coefficients(f, df, step)
+
+        # part-major row order of v / dv: row p*H + head*hd + c <- reference row head*3hd + p*hd + c
+        perm = torch.arange(3 * H, device=dev).view(nh, 3, hd).permute(1, 0, 2).reshape(-1)
+        empty = torch.empty(0, device=dev, dtype=torch.float32)
+        ne = self.neighbor_embedding
+        w = [f32(self.embedding.weight)]
+        if ne is not None:
+            ne_tab = table((ne.distance_proj.weight, ne.distance_proj.bias), None, H, True)
+            w += [f32(ne.embedding.weight), f32(ne_tab), f32(ne.combine.weight), f32(ne.combine.bias),
+                  tr(ne.combine.weight[:, H:])]
+        else:
+            w += [empty] * 5
+        w += [f32(self.out_norm.weight), f32(self.out_norm.bias)]
+        for blk in head.output_network:
+            u0, u2 = blk.update_net[0], blk.update_net[2]
+            w += [f32(blk.vec1_proj.weight), tr(blk.vec1_proj.weight), f32(blk.vec2_proj.weight),
+                  tr(blk.vec2_proj.weight), f32(u0.weight), f32(u0.bias), tr(u0.weight), f32(u2.weight), f32(u2.bias),
+                  tr(u2.weight)]
+        for ly in self.attention_layers:
+            qkv_w = torch.cat([ly.q_proj.weight, ly.k_proj.weight, ly.v_proj.weight[perm]]).detach()
+            qkv_b = torch.cat([ly.q_proj.bias, ly.k_proj.bias, ly.v_proj.bias[perm]]).detach()
+            dk = None if ly.dk_proj is None else (ly.dk_proj.weight, ly.dk_proj.bias)
+            dv = None if ly.dv_proj is None else (ly.dv_proj.weight[perm], ly.dv_proj.bias[perm])
+            tab = torch.cat([table(dk, self.activation, H, False), table(dv, self.activation, 3 * H, False)], 1)
+            w += [f32(ly.layernorm.weight), f32(ly.layernorm.bias), f32(qkv_w), f32(qkv_b), tr(qkv_w),
+                  f32(ly.vec_proj.weight), tr(ly.vec_proj.weight), f32(ly.o_proj.weight), f32(ly.o_proj.bias),
+                  tr(ly.o_proj.weight), f32(tab.view(n_int, 4, H, 4))]
+        iparams = [H, self.num_layers, nh, self.max_z, ACT_ID[self.activation], ACT_ID[self.attn_activation],
+                   int(ne is not None), n_int]
+        return w, iparams, [lo, hi, float(mean), float(std)]
+
+    def forward(self, z: Tensor, pos: Tensor, batch: Tensor, q: Optional[Tensor] = None,
+                s: Optional[Tensor] = None):
+        raise RuntimeError("TorchMD_ET is evaluated inside the fused CUDA energy+force kernels through "
+                           "TorchMD_Net.forward (no standalone representation output, no CPU path)")
