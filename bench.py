@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- atom-steps/s (energy + forces) of the B200-native TorchMD-NET hot path.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload chignolin|md17|water] [--filter table|exact]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload chignolin|md17|water|qm9-et|md17-et] [--filter table|exact]
     python bench.py --impl reference ...      # the reference algorithm's CPU restatement on the host cores
 
 One "step" = one energy+force evaluation (neighbour search included) of the workload on one GPU:
@@ -47,7 +47,16 @@ HPARAMS = {
     "md17": dict(HP_BASE, num_rbf=32, cutoff_upper=4.5, max_num_neighbors=32),
     "water": dict(HP_BASE, num_rbf=32, cutoff_upper=4.5, max_num_neighbors=128),
 }
+HP_ET = dict(model="equivariant-transformer", precision=32, trainable_rbf=False, activation="silu",
+             attn_activation="silu", cutoff_lower=0.0, cutoff_upper=5.0, max_z=100, rbf_type="expnorm",
+             neighbor_embedding=True, distance_influence="both", derivative=True, atom_filter=-1, prior_model=None,
+             output_model="Scalar", reduce_op="add", num_heads=8)
+# examples/ET-QM9.yaml and examples/ET-MD17.yaml
+HPARAMS["qm9-et"] = dict(HP_ET, embedding_dimension=256, num_layers=8, num_rbf=64, max_num_neighbors=64)
+HPARAMS["md17-et"] = dict(HP_ET, embedding_dimension=128, num_layers=6, num_rbf=32, max_num_neighbors=32)
 WORKLOAD_DESC = {
+    "qm9-et": "ET-QM9 hparams, 128 synthetic QM9-size molecules (3-29 atoms) per GPU, batched energy+forces",
+    "md17-et": "ET-MD17 hparams, 8192 synthetic 21-atom molecules per GPU, batched energy+forces",
     "chignolin": "TensorNet-SPICE hparams, 166-atom chignolin-size molecule, single-system MD energy+force step",
     "md17": "TensorNet-rMD17 hparams, 8192 synthetic 21-atom molecules per GPU, batched energy+forces",
     "water": "TensorNet-ANI1X hparams, periodic water box, cell-list neighbours, energy+forces",
@@ -65,8 +74,11 @@ def make_inputs(workload, rank, args):
     if workload == "chignolin":
         z, pos, batch = S.chignolin_like(seed=2 + 1000 * rank)
         return z, pos, batch, None
-    if workload == "md17":
+    if workload in ("md17", "md17-et"):
         z, pos, batch = S.md17_like_batch(n_mol=args.molecules, seed=3 + 1000 * rank)
+        return z, pos, batch, None
+    if workload == "qm9-et":
+        z, pos, batch = S.qm9_like_batch(n_mol=128, seed=1 + 1000 * rank)
         return z, pos, batch, None
     z, pos, batch, box = S.water_box(args.water_side, seed=4 + 1000 * rank)
     return z, pos, batch, box
@@ -121,10 +133,10 @@ def cpu_reference_steps(workload, hp, args, steps, warmup):
     torch.set_num_threads(cores)
     seed_everything(1234)
     sd = {k: v.clone() for k, v in create_model(hp).state_dict().items()}
-    if workload == "chignolin":
+    if workload in ("chignolin", "qm9-et"):
         z, pos0, batch, box = make_inputs(workload, 0, args)
-        sample = "the full 166-atom step"
-    elif workload == "md17":
+        sample = "the full %d-atom step" % z.shape[0]
+    elif workload in ("md17", "md17-et"):
         z, pos0, batch = S.md17_like_batch(n_mol=64, seed=3)
         box = None
         sample = "64 of the 8192 molecules per step (the reference CPU op is O(N^2) over the whole batch)"
@@ -170,8 +182,9 @@ def algorithmic_bytes(family, N, E, H, L):
         "tn_msg_bwd": 4 * node + 16 * E,    # read Y, dM, dY; write dY (backward = 2x forward)
         "tn_embed_edge_fwd": node + 20 * E,
         "tn_embed_edge_bwd": node + 20 * E + 12 * N,
-        "neighbors": 20 * N + 24 * E,
-        "csr": 2 * 24 * E,
+        "neighbors_csr": 16 * N + 20 * E,
+        "et_edge_fwd": 48 * H * N + 20 * E,     # read q,k,v,vec once, write xa,va; CSR (SURVEY 8d B_et)
+        "et_edge_bwd": 96 * H * N + 40 * E,     # backward = 2x forward
     }
     return table.get(family, 2 * node)
 
@@ -229,7 +242,10 @@ def main():
     seed_everything(1234)
     model = create_model(hp).to(dev).eval()
     rm = model.representation_model
-    rm.filter_mode = args.filter
+    if hp["model"] == "tensornet":
+        rm.filter_mode = args.filter
+    else:
+        args.filter = "table"
     z_np, pos0, batch_np, box = make_inputs(args.workload, rank, args)
     if box is not None:
         rm.distance = OptimizedDistance(hp["cutoff_lower"], hp["cutoff_upper"], max_num_pairs=-hp["max_num_neighbors"],
@@ -307,12 +323,11 @@ def main():
     ckpt = os.path.join(tmp, "bench.ckpt")
     torch.save({"hyper_parameters": dict(hp), "state_dict": {"model." + k: v.cpu() for k, v in
                                                               model.state_dict().items()}}, ckpt)
-    if n_mol == 1 or N % n_mol == 0:
-        emb = torch.from_numpy(z_np).view(n_mol, N // n_mol)
-    else:
-        emb = torch.from_numpy(z_np).view(1, N)
+    equal_sizes = n_mol == 1 or (N % n_mol == 0 and bool((np.bincount(batch_np) == N // n_mol).all()))
+    emb = torch.from_numpy(z_np).view(n_mol, N // n_mol) if equal_sizes else torch.from_numpy(z_np).view(1, N)
     calc = External(ckpt, emb, dev)
-    calc.model.representation_model.filter_mode = args.filter
+    if hp["model"] == "tensornet":
+        calc.model.representation_model.filter_mode = args.filter
     if box is not None:
         calc.model.representation_model.distance = rm.distance
     if emb.shape[0] != n_mol:
@@ -355,7 +370,7 @@ def main():
     step_ms_prof = sum(ms for _, ms in fam.values()) / n_prof
     top = max(fam, key=lambda k: fam[k][1])
     # the roofline is quoted for the neighbour-aggregation kernels north_star names; the table shows all
-    agg = [k for k in ("tn_msg_bwd", "tn_msg_fwd") if k in fam]
+    agg = [k for k in ("tn_msg_bwd", "tn_msg_fwd", "et_edge_bwd", "et_edge_fwd") if k in fam]
     dom = max(agg, key=lambda k: fam[k][1]) if agg else top
     cnt, ms = fam[dom]
     H, L = hp["embedding_dimension"], hp["num_layers"]
