@@ -125,6 +125,13 @@ int tmdn_csr_build_f32(int strategy, const float* pos, const int64_t* batch, int
                        int32_t* row_ptr, int32_t* col, float* geom /* [max_edges,4] */, int32_t* num_found,
                        void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
 
+/* Rows only for the first n_rows atoms (the atoms a rank owns); atoms [n_rows, n_atoms) are ghosts that appear as
+ * sources only.  row_ptr still has n_atoms+1 entries (ghost rows empty). */
+int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int64_t* batch, int64_t n_atoms, int64_t n_rows,
+                            const double box[9], int use_periodic, double cutoff_lower, double cutoff_upper,
+                            int64_t max_edges, int32_t* row_ptr, int32_t* col, float* geom, int32_t* num_found,
+                            void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
+
 /* ---------------------------------------------------------------- TensorNet energy + forces (fp32)
  * All weight pointers are device fp32 arrays prepared once by the host side (layouts below; H = hidden,
  * K = num_rbf).  "T" suffix = transposed copy used by the backward kernels.
@@ -177,6 +184,22 @@ int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const int64_t* z
                                  const int64_t* batch, int64_t n_atoms, int64_t n_mol, const double box[9],
                                  int use_periodic, int strategy, int64_t max_edges, float* energy, float* forces,
                                  int32_t* status, void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
+/* The same evaluation cut at its halo points, for spatially decomposed runs (one rank owns the first n_rows atoms of
+ * its local arrays, the remaining n_atoms - n_rows are ghosts owned by other ranks).  Call order:
+ *   EMBED, [exchange "Y0"], LAYER_FWD(0), [exchange "Y1"], ..., LAYER_FWD(L-1), HEAD, [exchange "Dias"],
+ *   LAYER_BWD(L-1), [exchange "Dias"], ..., LAYER_BWD(0), [exchange "Dias"], FINAL
+ * where an exchange copies the rows of the named workspace buffer ([n_atoms,9,H] fp32) from their owners into the
+ * ghost rows.  energy receives the sum over the OWNED atoms only (+ mean); forces has n_rows rows.
+ * tmdn_tensornet_energy_forces == all stages in sequence with n_rows = n_atoms. */
+enum tmdn_tn_stage { TMDN_TN_EMBED = 0, TMDN_TN_LAYER_FWD = 1, TMDN_TN_HEAD = 2, TMDN_TN_LAYER_BWD = 3, TMDN_TN_FINAL = 4 };
+int tmdn_tensornet_stage(const tmdn_tensornet_model* m, int stage, int layer, const int64_t* z, const float* pos,
+                         const int64_t* batch, int64_t n_atoms, int64_t n_rows, int64_t n_mol, const double box[9],
+                         int use_periodic, int strategy, int64_t max_edges, float* energy, float* forces,
+                         int32_t* status, void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
+/* Halo pack: out[r, :] = src[idx[r], :] for r < n_rows (rows of row_floats fp32).  The receive side writes straight into
+ * the ghost rows (the contiguous tail of the local arrays), so there is no unpack. */
+int tmdn_halo_pack_f32(const float* src, const int32_t* idx, int64_t n_rows, int64_t row_floats, float* out,
+                       tmdn_stream_t stream);
 /* Debug/inspection: byte offset and size of a named intermediate inside the workspace (names as in
  * oracle/staged_tensornet.py: "row_ptr","col","geom","ias","nh","fias","X0","Y0","M0","tauh0","X1",...,"e_atom","Dias","gpos"). */
 int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,

@@ -57,11 +57,11 @@ __device__ __forceinline__ void emit(bool hit, int lane, int j, float dx, float 
 // ------------------------------------------------------------------ brute: sources = the target's own molecule
 template <bool FILL>
 __global__ void __launch_bounds__(CD_WARPS * 32)
-csr_brute_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int n, Box3<float> box, int periodic,
-                 float lo2, float hi2, EdgeOut out) {
+csr_brute_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int n, int n_rows, Box3<float> box,
+                 int periodic, float lo2, float hi2, EdgeOut out) {
     const int i = blockIdx.x * CD_WARPS + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (i >= n) return;
+    if (i >= n_rows) return;
     const long long bi = batch[i];
     const int m0 = lower_bound_batch(batch, n, bi), m1 = lower_bound_batch(batch, n, bi + 1);
     const float xi = pos[3 * (size_t)i], yi = pos[3 * (size_t)i + 1], zi = pos[3 * (size_t)i + 2];
@@ -108,12 +108,13 @@ __global__ void cell_rank_kernel(const SortedAtom<float>* __restrict__ tmp, cons
 template <bool FILL>
 __global__ void __launch_bounds__(CD_WARPS * 32)
 csr_cell_kernel(const SortedAtom<float>* __restrict__ spos, const long long* __restrict__ sbatch,
-                const int* __restrict__ cell_start, CellGrid<float> g, int n, int periodic, float lo2, float hi2,
-                EdgeOut out) {
+                const int* __restrict__ cell_start, CellGrid<float> g, int n, int n_rows, int periodic, float lo2,
+                float hi2, EdgeOut out) {
     const int a = blockIdx.x * CD_WARPS + (threadIdx.x >> 5);  // position in the cell-sorted order
     const int lane = threadIdx.x & 31;
     if (a >= n) return;
     const SortedAtom<float> me = spos[a];
+    if (me.idx >= n_rows) return;                              // ghost atom: a source only, no row
     const long long ba = sbatch[a];
     // recompute the cell of `a` exactly as cell_assign_kernel did
     const int cx = cell_coord(me.x, g.L[0], g.n[0]), cy = cell_coord(me.y, g.L[1], g.n[1]),
@@ -222,7 +223,17 @@ extern "C" int tmdn_csr_build_f32(int strategy, const float* pos, const int64_t*
                                   const double box[9], int use_periodic, double cutoff_lower, double cutoff_upper,
                                   int64_t max_edges, int32_t* row_ptr, int32_t* col, float* geom, int32_t* num_found,
                                   void* workspace, size_t workspace_bytes, tmdn_stream_t stream_) {
+    return tmdn_csr_build_rows_f32(strategy, pos, batch, n_atoms, n_atoms, box, use_periodic, cutoff_lower, cutoff_upper,
+                                   max_edges, row_ptr, col, geom, num_found, workspace, workspace_bytes, stream_);
+}
+
+extern "C" int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int64_t* batch, int64_t n_atoms,
+                                       int64_t n_rows, const double box[9], int use_periodic, double cutoff_lower,
+                                       double cutoff_upper, int64_t max_edges, int32_t* row_ptr, int32_t* col,
+                                       float* geom, int32_t* num_found, void* workspace, size_t workspace_bytes,
+                                       tmdn_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
+    TMDN_CHECK_ARG(n_rows > 0 && n_rows <= n_atoms, "csr_build: n_rows must be in [1, n_atoms]");
     TMDN_CHECK_ARG(pos && batch && row_ptr && col && geom && num_found, "csr_build: null pointer argument");
     TMDN_CHECK_ARG(n_atoms > 0 && n_atoms < (1LL << 31) - 256, "csr_build: bad atom count");
     TMDN_CHECK_ARG(max_edges > 0 && max_edges < (1LL << 31), "csr_build: max_edges must be positive and fit int32");
@@ -249,7 +260,9 @@ extern "C" int tmdn_csr_build_f32(int strategy, const float* pos, const int64_t*
     }
     EdgeOut cnt{nullptr, w.row_cnt, col, (float4*)geom, (long long)max_edges};
     EdgeOut fill{row_ptr, nullptr, col, (float4*)geom, (long long)max_edges};
-    const unsigned wgrid = (unsigned)cdiv(n, CD_WARPS);
+    const int nr = (int)n_rows;
+    const unsigned wgrid = (unsigned)cdiv(n, CD_WARPS), rgrid = (unsigned)cdiv(nr, CD_WARPS);
+    if (nr < n) TMDN_CUDA(cudaMemsetAsync(w.row_cnt, 0, sizeof(int) * ((size_t)n + 1), stream));
     if (strategy == TMDN_CELL) {
         TMDN_CUDA(cudaMemsetAsync(w.cell_cnt, 0, sizeof(int) * (g.ncells + 1), stream));
         const int blocks = (int)cdiv(n, 256);
@@ -262,21 +275,21 @@ extern "C" int tmdn_csr_build_f32(int strategy, const float* pos, const int64_t*
         cell_rank_kernel<<<blocks, 256, 0, stream>>>(w.tmp, w.tmp_batch, w.cell_start, w.cell_of, w.slot_of, n, w.spos,
                                                      w.sbatch);
         TMDN_LAUNCH_CHECK();
-        csr_cell_kernel<false><<<wgrid, CD_WARPS * 32, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g, n, use_periodic,
-                                                                    lo2, hi2, cnt);
+        csr_cell_kernel<false><<<wgrid, CD_WARPS * 32, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g, n, nr,
+                                                                    use_periodic, lo2, hi2, cnt);
         TMDN_LAUNCH_CHECK();
         TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));
-        csr_cell_kernel<true><<<wgrid, CD_WARPS * 32, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g, n, use_periodic,
-                                                                   lo2, hi2, fill);
+        csr_cell_kernel<true><<<wgrid, CD_WARPS * 32, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g, n, nr,
+                                                                   use_periodic, lo2, hi2, fill);
         TMDN_LAUNCH_CHECK();
     } else {
         Box3<float> b;
         for (int r = 0; r < 3; ++r)
             for (int c = 0; c < 3; ++c) b.m[r][c] = (use_periodic && box) ? (float)box[3 * r + c] : 0.f;
-        csr_brute_kernel<false><<<wgrid, CD_WARPS * 32, 0, stream>>>(pos, batch, n, b, use_periodic, lo2, hi2, cnt);
+        csr_brute_kernel<false><<<rgrid, CD_WARPS * 32, 0, stream>>>(pos, batch, n, nr, b, use_periodic, lo2, hi2, cnt);
         TMDN_LAUNCH_CHECK();
         TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));
-        csr_brute_kernel<true><<<wgrid, CD_WARPS * 32, 0, stream>>>(pos, batch, n, b, use_periodic, lo2, hi2, fill);
+        csr_brute_kernel<true><<<rgrid, CD_WARPS * 32, 0, stream>>>(pos, batch, n, nr, b, use_periodic, lo2, hi2, fill);
         TMDN_LAUNCH_CHECK();
     }
     csr_finish_kernel<<<(unsigned)cdiv(n + 1, 256), 256, 0, stream>>>(row_ptr, n, (long long)max_edges, num_found);

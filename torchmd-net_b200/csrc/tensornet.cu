@@ -818,169 +818,49 @@ extern "C" int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, in
     return TMDN_EINVAL;
 }
 
-extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const int64_t* z, const float* pos,
-                                            const int64_t* batch, int64_t n_atoms, int64_t n_mol, const double box[9],
-                                            int use_periodic, int strategy, int64_t max_edges, float* energy,
-                                            float* forces, int32_t* status, void* workspace, size_t workspace_bytes,
-                                            tmdn_stream_t stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    TMDN_TRY(check_model(m));
-    TMDN_CHECK_ARG(z && pos && batch && energy && status && workspace, "tensornet: null pointer argument");
-    TMDN_CHECK_ARG(n_atoms > 0 && n_mol > 0 && max_edges > 0, "tensornet: bad sizes");
-    TMDN_CHECK_ARG((long long)n_atoms * 9 * m->hidden < (1LL << 40), "tensornet: system too large");
-    TMDN_CHECK_ARG(max_edges < (1LL << 31) && n_atoms < (1LL << 31) / 16, "tensornet: sizes exceed int32 indexing");
-    const int N = (int)n_atoms, H = m->hidden, L = m->num_layers, act = m->activation;
-    const bool tab = m->filter_mode == TMDN_FILTER_TABLE;
-    const int64_t P = max_edges;
-
-    TMDN_CHECK_ARG(strategy != TMDN_CELL || box, "tensornet: the cell strategy needs a box");
-    Arena arena(workspace, workspace_bytes);
+namespace {
+// One evaluation = the stage sequence below.  Halo points (the only places where a spatially decomposed run needs
+// data of atoms it does not own; owner -> ghost copies of node rows, see torchmdnet/distributed.py):
+//   after EMBED        : Y0            after LAYER_FWD(l) : Y{l+1}
+//   after HEAD         : Dias (= dM of layer L-1, or dE/d(ias) if there are no layers)
+//   after LAYER_BWD(l) : Dias (= dM of layer l-1, or dE/d(ias) for l = 0)
+// Rows (targets) are the first n_rows atoms; the remaining n_atoms - n_rows atoms are ghosts that only appear as
+// sources.  Because the edge set is symmetric every adjoint is gathered, never scattered, so the backward pass needs
+// the same owner -> ghost direction as the forward pass and forces of owned atoms are complete locally.
+struct TnRun {
+    const tmdn_tensornet_model* m;
+    const int64_t* z; const float* pos; const int64_t* batch;
+    int64_t n_atoms, n_rows, n_mol, P;
+    const double* box; int use_periodic, strategy;
+    float* energy; float* forces; int32_t* status;
+    cudaStream_t stream;
     TnWs w;
-    TMDN_TRY(carve_tn(arena, m, n_atoms, P, n_mol, w, nullptr, box, strategy, m->cutoff_upper));
-    if (!arena.ok) {
-        tmdn_set_error("tensornet: workspace too small (%zu < %zu)", workspace_bytes, arena.off);
-        return TMDN_EWORKSPACE;
-    }
-
-    // ---- graph: neighbour search straight into CSR by target (= row 0 of the reference's pair list,
-    //      tensornet.py:313-315), self loops included
-    {
-        KTimer ktimer__("neighbors_csr", stream);
-        TMDN_TRY(tmdn_csr_build_f32(strategy, pos, batch, n_atoms, box, use_periodic, m->cutoff_lower, m->cutoff_upper,
-                                    P, w.row_ptr, w.col, w.geom, w.num_found, w.graph_ws, w.graph_ws_bytes, stream_));
-    }
-    TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
-    {
-        KTimer ktimer__("tn_prep_kernel", stream);
-        tn_prep_kernel<<<(unsigned)cdiv(N, 256), 256, 0, stream>>>(z, w.z32, N, m->max_z, w.num_found, (long long)P, status);
-        TMDN_LAUNCH_CHECK();
-    }
-
-    const float4* geom = (const float4*)w.geom;
-    const int apb = H >= 128 ? 1 : 128 / H;
-    const dim3 rblock(H, apb);
-    const EdgeLaunch el = edge_launch(N, H, 1024);    // forward edge kernels: <= 64 registers/thread
-    const EdgeLaunch elb = edge_launch(N, H, 512);    // backward edge kernels: <= 128 registers/thread
-    const unsigned rgrid = (unsigned)cdiv(N, apb);
-    const long long NH = (long long)N * H;
-    const unsigned egrid = (unsigned)cdiv(NH, 256);
-
-    // ---- filters (exact mode): rbf once, then one MLP chain per filter set
     FilterView fv_emb, fv_layer[TMDN_MAX_LAYERS];
-    if (!tab) {
-        const long long tot = (long long)P * m->num_rbf;
-        {
-            KTimer ktimer__("tn_rbf_kernel", stream);
-            tn_rbf_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(geom, w.row_ptr, N, (long long)P, m->num_rbf,
-                                                                        m->rbf_type, m->cutoff_lower, m->cutoff_upper,
-                                                                        m->rbf_p0, m->rbf_p1, w.R, w.dR);
-            TMDN_LAUNCH_CHECK();
-        }
-        TMDN_TRY(eval_filter_exact(m, m->emb_filter, w, n_atoms, P, w.F[0], w.dF[0], stream));
-        for (int l = 0; l < L; ++l)
-            TMDN_TRY(eval_filter_exact(m, m->layer_filter[l], w, n_atoms, P, w.F[l + 1], w.dF[l + 1], stream));
-    }
-    fv_emb = make_view(m, m->emb_filter, w.F[0], w.dF[0]);
-    for (int l = 0; l < L; ++l) fv_layer[l] = make_view(m, m->layer_filter[l], w.F[l + 1], w.dF[l + 1]);
 
-    // ---- E1 + embedding node stage
-    {
-        KTimer ktimer__("tn_embed_edge_fwd", stream);
-        if (tab)
-            tn_embed_edge_fwd<true><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H,
-                                                                  w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
-        else
-            tn_embed_edge_fwd<false><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H,
-                                                                   w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
-        TMDN_LAUNCH_CHECK();
-    }
-    {
-        GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
-        p.C2 = w.h1; p.act = act;
-        TMDN_TRY(gemm1(EPI_ACT, p, stream));
-        GemmP q = gemm_desc(w.a1, 2 * H, m->emb_w2, m->emb_b2, w.fias, 3 * H, N, 3 * H, 2 * H);
-        q.C2 = w.h2; q.act = act;
-        TMDN_TRY(gemm1(EPI_ACT, q, stream));
-        GemmBatch b = mix_batch(w.ias, w.X[0], m->emb_mix, N, H);
-        for (int g = 0; g < 3; ++g) { b.p[g].C2 = w.iasm; b.p[g].aux = w.fias; }
-        TMDN_TRY(gemm_launch(EPI_SCALE3, b, stream));
-    }
-    // ---- interaction layers
-    if (L > 0) {
-        {
-            KTimer ktimer__("tn_normalize_fwd", stream);
-            tn_normalize_fwd<<<egrid, 256, 0, stream>>>(w.X[0], w.Xh, NH, H);
-            TMDN_LAUNCH_CHECK();
+    int init(void* workspace, size_t workspace_bytes) {
+        TMDN_TRY(check_model(m));
+        TMDN_CHECK_ARG(z && pos && batch && status && workspace, "tensornet: null pointer argument");
+        TMDN_CHECK_ARG(n_atoms > 0 && n_mol > 0 && P > 0, "tensornet: bad sizes");
+        TMDN_CHECK_ARG(n_rows > 0 && n_rows <= n_atoms, "tensornet: n_rows must be in [1, n_atoms]");
+        TMDN_CHECK_ARG((long long)n_atoms * 9 * m->hidden < (1LL << 40), "tensornet: system too large");
+        TMDN_CHECK_ARG(P < (1LL << 31) && n_atoms < (1LL << 31) / 16, "tensornet: sizes exceed int32 indexing");
+        TMDN_CHECK_ARG(strategy != TMDN_CELL || box, "tensornet: the cell strategy needs a box");
+        Arena arena(workspace, workspace_bytes);
+        TMDN_TRY(carve_tn(arena, m, n_atoms, P, n_mol, w, nullptr, box, strategy, m->cutoff_upper));
+        if (!arena.ok) {
+            tmdn_set_error("tensornet: workspace too small (%zu < %zu)", workspace_bytes, arena.off);
+            return TMDN_EWORKSPACE;
         }
+        fv_emb = make_view(m, m->emb_filter, w.F[0], w.dF[0]);
+        for (int l = 0; l < m->num_layers; ++l) fv_layer[l] = make_view(m, m->layer_filter[l], w.F[l + 1], w.dF[l + 1]);
+        return TMDN_OK;
     }
-    for (int l = 0; l < L; ++l) {
-        TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.Xh, w.Y[l], m->layer_mix[l], N, H), stream));
-        {
-            KTimer ktimer__("tn_msg_fwd", stream);
-            if (tab)
-                tn_msg_fwd<true><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N, H, m->so3,
-                                                               w.M[l], w.tauh);
-            else
-                tn_msg_fwd<false><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N, H, m->so3,
-                                                                w.M[l], w.tauh);
-            TMDN_LAUNCH_CHECK();
-        }
-        TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
-        // Xh is both input (residual) and, for the next layer, output: safe because each thread reads its own
-        // (atom, channel) column before writing it.
-        {
-            KTimer ktimer__("tn_update_fwd", stream);
-            tn_update_fwd<<<egrid, 256, 0, stream>>>(w.Xh, w.dX[l], w.X[l + 1], l + 1 < L ? w.Xh : nullptr, NH, H);
-            TMDN_LAUNCH_CHECK();
-        }
-    }
-    // ---- output norm, linear, head, reduce
-    {
-        KTimer ktimer__("tn_out_norm_fwd", stream);
-        tn_out_norm_fwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, m->out_ln_b, w.xl, w.stat, N, H);
-        TMDN_LAUNCH_CHECK();
-    }
-    {
-        GemmP p = gemm_desc(w.xl, 3 * H, m->out_w, m->out_b, w.a3, H, N, H, 3 * H);
-        p.C2 = w.h3; p.act = act;
-        TMDN_TRY(gemm1(EPI_ACT, p, stream));
-        GemmP q = gemm_desc(w.a3, H, m->head_w1, m->head_b1, w.a4, H / 2, N, H / 2, H);
-        q.C2 = w.h4; q.act = act;
-        TMDN_TRY(gemm1(EPI_ACT, q, stream));
-    }
-    {
-        KTimer ktimer__("tn_head_energy", stream);
-        tn_head_energy<<<(unsigned)cdiv(N, 4), 128, 0, stream>>>(w.a4, m->head_w2, m->head_b2, m->std, w.e_atom, N, H / 2);
-        TMDN_LAUNCH_CHECK();
-    }
-    {
-        KTimer ktimer__("tn_mol_reduce", stream);
-        tn_mol_reduce<<<(unsigned)n_mol, 128, 0, stream>>>(w.e_atom, batch, N, m->mean, energy);
-        TMDN_LAUNCH_CHECK();
-    }
-    if (!forces) return TMDN_OK;
 
-    // ================================================================= backward (dE_total/dpos)
-    TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
-    {
-        const long long tot = (long long)N * (H / 2);
-        {
-            KTimer ktimer__("tn_head_seed_bwd", stream);
-            tn_head_seed_bwd<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(w.h4, m->head_w2, m->std, act, w.d4, tot, H / 2);
-            TMDN_LAUNCH_CHECK();
-        }
-        GemmP p = gemm_desc(w.d4, H / 2, m->head_w1T, nullptr, w.d3, H, N, H, H / 2);
-        p.aux = w.h3; p.ldaux = H; p.act = act;
-        TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
-        GemmP q = gemm_desc(w.d3, H, m->out_wT, nullptr, w.dxl, 3 * H, N, 3 * H, H);
-        TMDN_TRY(gemm1(EPI_NONE, q, stream));
-    }
-    {
-        KTimer ktimer__("tn_out_norm_bwd", stream);
-        tn_out_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
-        TMDN_LAUNCH_CHECK();
-    }
-    for (int l = L - 1; l >= 0; --l) {
+    // adjoint of X_{l+1} = Xh + dX + dX^2 and of the (M, Y) product: dXa -> dB (= dM_l), dC (= direct dY_l)
+    int pre_bwd(int l) {
+        const int N = (int)n_rows, H = m->hidden;
+        const long long NH = (long long)N * H;
+        const unsigned egrid = (unsigned)cdiv(NH, 256);
         {
             KTimer ktimer__("tn_update_bwd", stream);
             tn_update_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.dX[l], w.dB, NH, H);
@@ -992,53 +872,238 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
             tn_prod_bwd<<<egrid, 256, 0, stream>>>(w.Y[l], w.M[l], w.dC, w.dB, NH, H, m->so3);
             TMDN_LAUNCH_CHECK();
         }
+        return TMDN_OK;
+    }
+    // adjoint of the embedding node stage: dXa -> dB (= dE/d ias, "Dias")
+    int embed_node_bwd() {
+        const int N = (int)n_rows, H = m->hidden, act = m->activation;
+        const long long NH = (long long)N * H;
+        const unsigned egrid = (unsigned)cdiv(NH, 256);
+        const int apb = H >= 128 ? 1 : 128 / H;
         {
-            KTimer ktimer__("tn_msg_bwd", stream);
-            if (tab)
-                tn_msg_bwd<true><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
-                                                               w.gpos, N, H);
-            else
-                tn_msg_bwd<false><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], w.dB, w.dC,
-                                                                w.gpos, N, H);
+            KTimer ktimer__("tn_embed_scale_bwd", stream);
+            tn_embed_scale_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.iasm, w.fias, w.h2, act, w.dh2, NH, H);
             TMDN_LAUNCH_CHECK();
         }
-        GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
-        for (int g = 0; g < 3; ++g) b.p[g].accumulate = 1;
-        TMDN_TRY(gemm_launch(EPI_NONE, b, stream));
-        {
-            KTimer ktimer__("tn_normalize_bwd", stream);
-            tn_normalize_bwd<<<egrid, 256, 0, stream>>>(w.X[l], w.dXa, NH, H);
-            TMDN_LAUNCH_CHECK();
-        }
-    }
-    // embedding node stage backward
-    {
-        KTimer ktimer__("tn_embed_scale_bwd", stream);
-        tn_embed_scale_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.iasm, w.fias, w.h2, act, w.dh2, NH, H);
-        TMDN_LAUNCH_CHECK();
-    }
-    {
         GemmP p = gemm_desc(w.dh2, 3 * H, m->emb_w2T, nullptr, w.dh1, 2 * H, N, 2 * H, 3 * H);
         p.aux = w.h1; p.ldaux = 2 * H; p.act = act;
         TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
         GemmP q = gemm_desc(w.dh1, 2 * H, m->emb_w1T, nullptr, w.dnh, H, N, H, 2 * H);
         TMDN_TRY(gemm1(EPI_NONE, q, stream));
         TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.dXa, w.dB, m->emb_mixT, N, H), stream));
+        {
+            KTimer ktimer__("tn_embed_norm_bwd", stream);
+            tn_embed_norm_bwd<<<(unsigned)cdiv(N, apb), dim3(H, apb), 0, stream>>>(w.ias, m->emb_ln_w, w.dnh, w.dB, N, H);
+            TMDN_LAUNCH_CHECK();
+        }
+        return TMDN_OK;
     }
-    {
-        KTimer ktimer__("tn_embed_norm_bwd", stream);
-        tn_embed_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.ias, m->emb_ln_w, w.dnh, w.dB, N, H);
-        TMDN_LAUNCH_CHECK();
+
+    int stage(int s, int l) {
+        const int N = (int)n_rows, NT = (int)n_atoms, H = m->hidden, L = m->num_layers, act = m->activation;
+        const bool tab = m->filter_mode == TMDN_FILTER_TABLE;
+        const float4* geom = (const float4*)w.geom;
+        const int apb = H >= 128 ? 1 : 128 / H;
+        const dim3 rblock(H, apb);
+        const EdgeLaunch el = edge_launch(N, H, 1024);    // forward edge kernels: <= 64 registers/thread
+        const EdgeLaunch elb = edge_launch(N, H, 512);    // backward edge kernels: <= 128 registers/thread
+        const unsigned rgrid = (unsigned)cdiv(N, apb);
+        const long long NH = (long long)N * H;
+        const unsigned egrid = (unsigned)cdiv(NH, 256);
+        TMDN_CHECK_ARG(s >= TMDN_TN_EMBED && s <= TMDN_TN_FINAL, "tensornet: bad stage %d", s);
+        TMDN_CHECK_ARG((s != TMDN_TN_LAYER_FWD && s != TMDN_TN_LAYER_BWD) || (l >= 0 && l < L), "tensornet: bad layer %d", l);
+
+        if (s == TMDN_TN_EMBED) {
+            // graph: neighbour search straight into CSR by target (= row 0 of the reference's pair list,
+            // tensornet.py:313-315), self loops included
+            {
+                KTimer ktimer__("neighbors_csr", stream);
+                TMDN_TRY(tmdn_csr_build_rows_f32(strategy, pos, batch, n_atoms, n_rows, box, use_periodic, m->cutoff_lower,
+                                                 m->cutoff_upper, P, w.row_ptr, w.col, w.geom, w.num_found, w.graph_ws,
+                                                 w.graph_ws_bytes, (tmdn_stream_t)stream));
+            }
+            TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
+            {
+                KTimer ktimer__("tn_prep_kernel", stream);
+                tn_prep_kernel<<<(unsigned)cdiv(NT, 256), 256, 0, stream>>>(z, w.z32, NT, m->max_z, w.num_found,
+                                                                            (long long)P, status);
+                TMDN_LAUNCH_CHECK();
+            }
+            if (!tab) {  // exact filters: rbf once, then one MLP chain per filter set
+                const long long tot = (long long)P * m->num_rbf;
+                {
+                    KTimer ktimer__("tn_rbf_kernel", stream);
+                    tn_rbf_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(geom, w.row_ptr, N, (long long)P,
+                                                                                m->num_rbf, m->rbf_type, m->cutoff_lower,
+                                                                                m->cutoff_upper, m->rbf_p0, m->rbf_p1,
+                                                                                w.R, w.dR);
+                    TMDN_LAUNCH_CHECK();
+                }
+                TMDN_TRY(eval_filter_exact(m, m->emb_filter, w, n_atoms, P, w.F[0], w.dF[0], stream));
+                for (int k = 0; k < L; ++k)
+                    TMDN_TRY(eval_filter_exact(m, m->layer_filter[k], w, n_atoms, P, w.F[k + 1], w.dF[k + 1], stream));
+            }
+            {
+                KTimer ktimer__("tn_embed_edge_fwd", stream);
+                if (tab)
+                    tn_embed_edge_fwd<true><<<el.grid, el.block, el.smem, stream>>>(
+                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+                else
+                    tn_embed_edge_fwd<false><<<el.grid, el.block, el.smem, stream>>>(
+                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+                TMDN_LAUNCH_CHECK();
+            }
+            GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
+            p.C2 = w.h1; p.act = act;
+            TMDN_TRY(gemm1(EPI_ACT, p, stream));
+            GemmP q = gemm_desc(w.a1, 2 * H, m->emb_w2, m->emb_b2, w.fias, 3 * H, N, 3 * H, 2 * H);
+            q.C2 = w.h2; q.act = act;
+            TMDN_TRY(gemm1(EPI_ACT, q, stream));
+            GemmBatch b = mix_batch(w.ias, w.X[0], m->emb_mix, N, H);
+            for (int g = 0; g < 3; ++g) { b.p[g].C2 = w.iasm; b.p[g].aux = w.fias; }
+            TMDN_TRY(gemm_launch(EPI_SCALE3, b, stream));
+            if (L > 0) {
+                {
+                    KTimer ktimer__("tn_normalize_fwd", stream);
+                    tn_normalize_fwd<<<egrid, 256, 0, stream>>>(w.X[0], w.Xh, NH, H);
+                    TMDN_LAUNCH_CHECK();
+                }
+                TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.Xh, w.Y[0], m->layer_mix[0], N, H), stream));
+            }
+            return TMDN_OK;
+        }
+        if (s == TMDN_TN_LAYER_FWD) {
+            {
+                KTimer ktimer__("tn_msg_fwd", stream);
+                if (tab)
+                    tn_msg_fwd<true><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
+                                                                             H, m->so3, w.M[l], w.tauh);
+                else
+                    tn_msg_fwd<false><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
+                                                                              H, m->so3, w.M[l], w.tauh);
+                TMDN_LAUNCH_CHECK();
+            }
+            TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
+            // Xh is both input (residual) and, for the next layer, output: safe because each thread reads its own
+            // (atom, channel) column before writing it.
+            {
+                KTimer ktimer__("tn_update_fwd", stream);
+                tn_update_fwd<<<egrid, 256, 0, stream>>>(w.Xh, w.dX[l], w.X[l + 1], l + 1 < L ? w.Xh : nullptr, NH, H);
+                TMDN_LAUNCH_CHECK();
+            }
+            if (l + 1 < L) TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.Xh, w.Y[l + 1], m->layer_mix[l + 1], N, H), stream));
+            return TMDN_OK;
+        }
+        if (s == TMDN_TN_HEAD) {
+            TMDN_CHECK_ARG(energy, "tensornet: null energy pointer");
+            {
+                KTimer ktimer__("tn_out_norm_fwd", stream);
+                tn_out_norm_fwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, m->out_ln_b, w.xl, w.stat, N, H);
+                TMDN_LAUNCH_CHECK();
+            }
+            {
+                GemmP p = gemm_desc(w.xl, 3 * H, m->out_w, m->out_b, w.a3, H, N, H, 3 * H);
+                p.C2 = w.h3; p.act = act;
+                TMDN_TRY(gemm1(EPI_ACT, p, stream));
+                GemmP q = gemm_desc(w.a3, H, m->head_w1, m->head_b1, w.a4, H / 2, N, H / 2, H);
+                q.C2 = w.h4; q.act = act;
+                TMDN_TRY(gemm1(EPI_ACT, q, stream));
+            }
+            {
+                KTimer ktimer__("tn_head_energy", stream);
+                tn_head_energy<<<(unsigned)cdiv(N, 4), 128, 0, stream>>>(w.a4, m->head_w2, m->head_b2, m->std, w.e_atom, N,
+                                                                         H / 2);
+                TMDN_LAUNCH_CHECK();
+            }
+            {
+                KTimer ktimer__("tn_mol_reduce", stream);
+                tn_mol_reduce<<<(unsigned)n_mol, 128, 0, stream>>>(w.e_atom, batch, N, m->mean, energy);
+                TMDN_LAUNCH_CHECK();
+            }
+            if (!forces) return TMDN_OK;
+            TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
+            const long long tot = (long long)N * (H / 2);
+            {
+                KTimer ktimer__("tn_head_seed_bwd", stream);
+                tn_head_seed_bwd<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(w.h4, m->head_w2, m->std, act, w.d4, tot,
+                                                                               H / 2);
+                TMDN_LAUNCH_CHECK();
+            }
+            GemmP p = gemm_desc(w.d4, H / 2, m->head_w1T, nullptr, w.d3, H, N, H, H / 2);
+            p.aux = w.h3; p.ldaux = H; p.act = act;
+            TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
+            GemmP q = gemm_desc(w.d3, H, m->out_wT, nullptr, w.dxl, 3 * H, N, 3 * H, H);
+            TMDN_TRY(gemm1(EPI_NONE, q, stream));
+            {
+                KTimer ktimer__("tn_out_norm_bwd", stream);
+                tn_out_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
+                TMDN_LAUNCH_CHECK();
+            }
+            return L > 0 ? pre_bwd(L - 1) : embed_node_bwd();
+        }
+        if (s == TMDN_TN_LAYER_BWD) {
+            {
+                KTimer ktimer__("tn_msg_bwd", stream);
+                if (tab)
+                    tn_msg_bwd<true><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
+                                                                                w.dB, w.dC, w.gpos, N, H);
+                else
+                    tn_msg_bwd<false><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
+                                                                                 w.dB, w.dC, w.gpos, N, H);
+                TMDN_LAUNCH_CHECK();
+            }
+            GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
+            for (int g = 0; g < 3; ++g) b.p[g].accumulate = 1;
+            TMDN_TRY(gemm_launch(EPI_NONE, b, stream));
+            {
+                KTimer ktimer__("tn_normalize_bwd", stream);
+                tn_normalize_bwd<<<egrid, 256, 0, stream>>>(w.X[l], w.dXa, NH, H);
+                TMDN_LAUNCH_CHECK();
+            }
+            return l > 0 ? pre_bwd(l - 1) : embed_node_bwd();
+        }
+        // TMDN_TN_FINAL
+        TMDN_CHECK_ARG(forces, "tensornet: null forces pointer");
+        {
+            KTimer ktimer__("tn_embed_edge_bwd", stream);
+            if (tab)
+                tn_embed_edge_bwd<true><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
+                                                                                   fv_emb, w.dB, w.gpos, forces, N, H);
+            else
+                tn_embed_edge_bwd<false><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
+                                                                                    fv_emb, w.dB, w.gpos, forces, N, H);
+            TMDN_LAUNCH_CHECK();
+        }
+        return TMDN_OK;
     }
-    {
-        KTimer ktimer__("tn_embed_edge_bwd", stream);
-        if (tab)
-            tn_embed_edge_bwd<true><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
-                                                                  w.gpos, forces, N, H);
-        else
-            tn_embed_edge_bwd<false><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, w.dB,
-                                                                   w.gpos, forces, N, H);
-        TMDN_LAUNCH_CHECK();
-    }
-    return TMDN_OK;
+};
+}  // namespace
+
+extern "C" int tmdn_tensornet_stage(const tmdn_tensornet_model* m, int stage, int layer, const int64_t* z,
+                                    const float* pos, const int64_t* batch, int64_t n_atoms, int64_t n_rows,
+                                    int64_t n_mol, const double box[9], int use_periodic, int strategy,
+                                    int64_t max_edges, float* energy, float* forces, int32_t* status, void* workspace,
+                                    size_t workspace_bytes, tmdn_stream_t stream_) {
+    TnRun r{m, z, pos, batch, n_atoms, n_rows, n_mol, max_edges, box, use_periodic, strategy, energy, forces, status,
+            (cudaStream_t)stream_};
+    TMDN_TRY(r.init(workspace, workspace_bytes));
+    return r.stage(stage, layer);
+}
+
+extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const int64_t* z, const float* pos,
+                                            const int64_t* batch, int64_t n_atoms, int64_t n_mol, const double box[9],
+                                            int use_periodic, int strategy, int64_t max_edges, float* energy,
+                                            float* forces, int32_t* status, void* workspace, size_t workspace_bytes,
+                                            tmdn_stream_t stream_) {
+    TMDN_CHECK_ARG(energy, "tensornet: null pointer argument");
+    TnRun r{m, z, pos, batch, n_atoms, n_atoms, n_mol, max_edges, box, use_periodic, strategy, energy, forces, status,
+            (cudaStream_t)stream_};
+    TMDN_TRY(r.init(workspace, workspace_bytes));
+    const int L = m->num_layers;
+    TMDN_TRY(r.stage(TMDN_TN_EMBED, 0));
+    for (int l = 0; l < L; ++l) TMDN_TRY(r.stage(TMDN_TN_LAYER_FWD, l));
+    TMDN_TRY(r.stage(TMDN_TN_HEAD, 0));
+    if (!forces) return TMDN_OK;
+    for (int l = L - 1; l >= 0; --l) TMDN_TRY(r.stage(TMDN_TN_LAYER_BWD, l));
+    return r.stage(TMDN_TN_FINAL, 0);
 }

@@ -473,6 +473,57 @@ std::vector<int64_t> et_debug_lookup(int64_t handle, int64_t n_atoms, int64_t ma
     return {(int64_t)off, (int64_t)bytes};
 }
 
+// ------------------------------------------------------------------ staged evaluation (spatial decomposition)
+int64_t tensornet_workspace_bytes(int64_t handle, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                  const std::string& strategy, const Tensor& box_vectors) {
+    auto h = tn_get(handle);
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    const size_t need = tmdn_tensornet_workspace_bytes(&h->m, n_atoms, max_edges, n_mol, strategy_id(strategy),
+                                                       have_box ? box : nullptr);
+    TORCH_CHECK(need > 0, "tensornet_workspace_bytes: ", tmdn_last_error());
+    return (int64_t)need;
+}
+
+// One stage of the evaluation (include/tmdn.h: tmdn_tensornet_stage) on caller-owned outputs and workspace.
+void tensornet_stage(int64_t handle, int64_t stage, int64_t layer, const Tensor& z, const Tensor& pos, const Tensor& batch,
+                     int64_t n_rows, const Tensor& box_vectors, bool use_periodic, const std::string& strategy,
+                     int64_t max_edges, int64_t n_mol, Tensor energy, Tensor forces, Tensor status, Tensor workspace) {
+    auto h = tn_get(handle);
+    TORCH_CHECK(pos.is_cuda() && pos.scalar_type() == at::kFloat && pos.is_contiguous() && pos.dim() == 2 &&
+                    pos.size(1) == 3, "tensornet_stage: pos must be a contiguous CUDA float32 [N,3] tensor");
+    TORCH_CHECK(z.scalar_type() == at::kLong && z.is_contiguous() && z.size(0) == pos.size(0) &&
+                    batch.scalar_type() == at::kLong && batch.is_contiguous() && batch.size(0) == pos.size(0),
+                "tensornet_stage: z / batch must be contiguous int64 [N] tensors");
+    TORCH_CHECK(energy.is_cuda() && energy.scalar_type() == at::kFloat && energy.numel() >= n_mol &&
+                    status.scalar_type() == at::kInt && status.numel() >= 4 && workspace.scalar_type() == at::kByte,
+                "tensornet_stage: bad output tensors");
+    TORCH_CHECK(!forces.defined() || forces.numel() == 0 ||
+                    (forces.scalar_type() == at::kFloat && forces.is_contiguous() && forces.numel() >= 3 * n_rows),
+                "tensornet_stage: forces must be a contiguous float32 [n_rows,3] tensor");
+    const c10::cuda::CUDAGuard guard(pos.device());
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    float* fptr_ = (forces.defined() && forces.numel() > 0) ? forces.data_ptr<float>() : nullptr;
+    TMDN_CALL(tmdn_tensornet_stage(&h->m, (int)stage, (int)layer, z.data_ptr<int64_t>(), pos.data_ptr<float>(),
+                                   batch.data_ptr<int64_t>(), pos.size(0), n_rows, n_mol, have_box ? box : nullptr,
+                                   use_periodic, strategy_id(strategy), max_edges, energy.data_ptr<float>(), fptr_,
+                                   status.data_ptr<int32_t>(), workspace.data_ptr(), (size_t)workspace.numel(),
+                                   cur_stream()));
+}
+
+// out[r,:] = src[idx[r],:]
+Tensor halo_pack(const Tensor& src, const Tensor& idx) {
+    TORCH_CHECK(src.is_cuda() && src.scalar_type() == at::kFloat && src.is_contiguous() && src.dim() == 2,
+                "halo_pack: src must be a contiguous CUDA float32 [n,row] tensor");
+    TORCH_CHECK(idx.is_cuda() && idx.scalar_type() == at::kInt && idx.is_contiguous(), "halo_pack: idx must be int32");
+    const c10::cuda::CUDAGuard guard(src.device());
+    Tensor out = at::empty({idx.numel(), src.size(1)}, src.options());
+    TMDN_CALL(tmdn_halo_pack_f32(src.data_ptr<float>(), idx.data_ptr<int32_t>(), idx.numel(), src.size(1),
+                                 out.data_ptr<float>(), cur_stream()));
+    return out;
+}
+
 int64_t launch_count() { return (int64_t)tmdn_launch_count(); }
 void profile_enable(bool on) { TMDN_CALL(tmdn_profile_enable(on ? 1 : 0)); }
 std::string profile_report() {
@@ -512,6 +563,12 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
     m.def("et_debug_lookup(int handle, int n_atoms, int max_edges, int n_mol, str strategy, Tensor box_vectors, "
           "str name) -> int[]",
           et_debug_lookup);
+    m.def("tensornet_workspace_bytes(int handle, int n_atoms, int max_edges, int n_mol, str strategy, "
+          "Tensor box_vectors) -> int", tensornet_workspace_bytes);
+    m.def("tensornet_stage(int handle, int stage, int layer, Tensor z, Tensor pos, Tensor batch, int n_rows, "
+          "Tensor box_vectors, bool use_periodic, str strategy, int max_edges, int n_mol, Tensor(a!) energy, "
+          "Tensor(b!) forces, Tensor(c!) status, Tensor(d!) workspace) -> ()", tensornet_stage);
+    m.def("halo_pack(Tensor src, Tensor idx) -> Tensor", halo_pack);
     m.def("launch_count() -> int", launch_count);
     m.def("profile_enable(bool on) -> ()", profile_enable);
     m.def("profile_report() -> str", profile_report);
