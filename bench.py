@@ -80,7 +80,7 @@ def make_inputs(workload, rank, args):
     if workload == "qm9-et":
         z, pos, batch = S.qm9_like_batch(n_mol=128, seed=1 + 1000 * rank)
         return z, pos, batch, None
-    z, pos, batch, box = S.water_box(args.water_side, seed=4 + 1000 * rank)
+    z, pos, batch, box = S.water_box(args.water_side, seed=4 + 1000 * rank, order=args.water_order)
     return z, pos, batch, box
 
 
@@ -298,6 +298,8 @@ def main():
     ap.add_argument("--filter", default="table", choices=["table", "exact"])
     ap.add_argument("--molecules", type=int, default=8192)
     ap.add_argument("--water-side", type=int, default=32)
+    ap.add_argument("--water-order", default="raster", choices=["raster", "morton", "shuffle"],
+                    help="index order of the synthetic water molecules (raster = lattice order)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

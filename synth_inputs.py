@@ -64,7 +64,7 @@ def md17_like_batch(n_mol=8192, seed=3):
     return z, pos, batch
 
 
-def water_box(n_side, seed=4, density=0.1):
+def water_box(n_side, seed=4, density=0.1, order="raster"):
     """cfg 4: n_side^3 water-like triplets (O + 2 H at 0.96 A, random orientation) on a jittered lattice in
     a periodic cubic box at `density` atoms/A^3.  n_side=70 -> 1 029 000 atoms (L = 217.5 A);
     n_side=19 -> 20 577 atoms (L = 59.0 A) is the CPU-parity size.  Returns (z, pos, batch, box[3,3])."""
@@ -75,6 +75,15 @@ def water_box(n_side, seed=4, density=0.1):
     g = np.arange(n_side)
     O = (np.stack(np.meshgrid(g, g, g, indexing="ij"), -1).reshape(-1, 3) + 0.5) * a
     O = O + rng.uniform(-0.15, 0.15, O.shape) * a
+    if order == "morton":      # molecules along a Z-order curve (spatially local atom indices)
+        gi = np.stack(np.meshgrid(g, g, g, indexing="ij"), -1).reshape(-1, 3).astype(np.uint64)
+        key = np.zeros(nmol, dtype=np.uint64)
+        for b in range(10):
+            for ax in range(3):
+                key |= ((gi[:, ax] >> np.uint64(b)) & np.uint64(1)) << np.uint64(3 * b + ax)
+        O = O[np.argsort(key, kind="stable")]
+    elif order == "shuffle":   # worst case: no relation between index and position
+        O = O[rng.permutation(nmol)]
     def unit(v):
         return v / np.linalg.norm(v, axis=1, keepdims=True)
     h1 = unit(rng.normal(size=(nmol, 3)))

@@ -5,10 +5,10 @@
 // sources (its molecule's index range for brute, the 27 neighbouring cells for cell), counts the hits with
 // ballot/popc, a scan turns counts into row pointers, and a second identical walk writes (col, geom) in place.
 // No atomics on the output, no sort, and the edge order inside a row is a pure function of the positions
-// (ascending source index for brute; cell-traversal order with cells internally sorted by index for cell), so
+// (ascending source index for brute; cell-traversal order of nbr_cell_tile.cuh with cells internally sorted by index for cell), so
 // every downstream segmented sum is bit-reproducible.  Same pair set and same rounding as tmdn_neighbors_f32.
 #include "common.cuh"
-#include "nbr_common.cuh"
+#include "nbr_cell_tile.cuh"
 #include "scan.cuh"
 
 namespace {
@@ -105,72 +105,6 @@ __global__ void cell_rank_kernel(const SortedAtom<float>* __restrict__ tmp, cons
     sbatch[cs + rank] = tmp_batch[src];
 }
 
-template <bool FILL>
-__global__ void __launch_bounds__(CD_WARPS * 32)
-csr_cell_kernel(const SortedAtom<float>* __restrict__ spos, const long long* __restrict__ sbatch,
-                const int* __restrict__ cell_start, CellGrid<float> g, int n, int n_rows, int periodic, float lo2,
-                float hi2, EdgeOut out) {
-    const int a = blockIdx.x * CD_WARPS + (threadIdx.x >> 5);  // position in the cell-sorted order
-    const int lane = threadIdx.x & 31;
-    if (a >= n) return;
-    const SortedAtom<float> me = spos[a];
-    if (me.idx >= n_rows) return;                              // ghost atom: a source only, no row
-    const long long ba = sbatch[a];
-    // recompute the cell of `a` exactly as cell_assign_kernel did
-    const int cx = cell_coord(me.x, g.L[0], g.n[0]), cy = cell_coord(me.y, g.L[1], g.n[1]),
-              cz = cell_coord(me.z, g.L[2], g.n[2]);
-    const long long base = FILL ? out.row_ptr[me.idx] : 0;
-    int run = 0;
-    for (int oz = g.lo[2]; oz <= g.hi[2]; ++oz) {
-        const int z = (cz + oz + g.n[2]) % g.n[2];
-        for (int oy = g.lo[1]; oy <= g.hi[1]; ++oy) {
-            const int y = (cy + oy + g.n[1]) % g.n[1];
-            const int row0 = g.n[0] * (y + g.n[1] * z);
-            // the x-neighbourhood of a row of cells is one contiguous range of the sorted array, or two when it wraps
-            int xr[2][2];
-            int nr = 1;
-            if (g.n[0] <= 3) {
-                xr[0][0] = 0; xr[0][1] = g.n[0] - 1;         // lo..hi covers every cell of the row
-            } else if (cx == 0) {
-                xr[0][0] = 0; xr[0][1] = 1; xr[1][0] = g.n[0] - 1; xr[1][1] = g.n[0] - 1; nr = 2;
-            } else if (cx == g.n[0] - 1) {
-                xr[0][0] = 0; xr[0][1] = 0; xr[1][0] = cx - 1; xr[1][1] = cx; nr = 2;
-            } else {
-                xr[0][0] = cx - 1; xr[0][1] = cx + 1;
-            }
-            for (int r = 0; r < nr; ++r) {
-                const int ks = cell_start[row0 + xr[r][0]], ke = cell_start[row0 + xr[r][1] + 1];
-                for (int k0 = ks; k0 < ke; k0 += 32) {
-                    const int k = k0 + lane;
-                    bool hit = false;
-                    float dx = 0.f, dy = 0.f, dz = 0.f, d2 = 0.f;
-                    int j = -1;
-                    if (k < ke) {
-                        const SortedAtom<float> q = spos[k];
-                        j = q.idx;
-                        if (k == a) {
-                            hit = true;
-                        } else if (sbatch[k] == ba) {
-                            dx = rn_sub(me.x, q.x);
-                            dy = rn_sub(me.y, q.y);
-                            dz = rn_sub(me.z, q.z);
-                            if (periodic) {
-                                dx = min_image_rect1(dx, g.L[0]);
-                                dy = min_image_rect1(dy, g.L[1]);
-                                dz = min_image_rect1(dz, g.L[2]);
-                            }
-                            d2 = dist2(dx, dy, dz);
-                            hit = d2 < hi2 && d2 >= lo2;
-                        }
-                    }
-                    emit<FILL>(hit, lane, j, dx, dy, dz, d2, run, base, out);
-                }
-            }
-        }
-    }
-    if (!FILL && lane == 0) out.row_cnt[me.idx] = run;
-}
-
 // num_found = edges found; row pointers are clamped to the capacity so that an overflowing list is truncated
 // (rows past the capacity become empty) instead of read out of bounds by the model kernels
 __global__ void csr_finish_kernel(int* __restrict__ row_ptr, int n, long long cap, int32_t* __restrict__ num_found) {
@@ -261,7 +195,7 @@ extern "C" int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int
     EdgeOut cnt{nullptr, w.row_cnt, col, (float4*)geom, (long long)max_edges};
     EdgeOut fill{row_ptr, nullptr, col, (float4*)geom, (long long)max_edges};
     const int nr = (int)n_rows;
-    const unsigned wgrid = (unsigned)cdiv(n, CD_WARPS), rgrid = (unsigned)cdiv(nr, CD_WARPS);
+    const unsigned rgrid = (unsigned)cdiv(nr, CD_WARPS);
     if (nr < n) TMDN_CUDA(cudaMemsetAsync(w.row_cnt, 0, sizeof(int) * ((size_t)n + 1), stream));
     if (strategy == TMDN_CELL) {
         TMDN_CUDA(cudaMemsetAsync(w.cell_cnt, 0, sizeof(int) * (g.ncells + 1), stream));
@@ -275,12 +209,15 @@ extern "C" int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int
         cell_rank_kernel<<<blocks, 256, 0, stream>>>(w.tmp, w.tmp_batch, w.cell_start, w.cell_of, w.slot_of, n, w.spos,
                                                      w.sbatch);
         TMDN_LAUNCH_CHECK();
-        csr_cell_kernel<false><<<wgrid, CD_WARPS * 32, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g, n, nr,
-                                                                    use_periodic, lo2, hi2, cnt);
+        CellTileOut<float> to{};
+        to.row_cnt = w.row_cnt; to.row_ptr = row_ptr; to.col = col; to.geom = (float4*)geom;
+        to.cap = (long long)max_edges; to.n_rows = nr;
+        cell_tile_kernel<float, CT_CSR_COUNT><<<g.ncells, CT_THREADS, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g,
+                                                                                  use_periodic, lo2, hi2, to);
         TMDN_LAUNCH_CHECK();
         TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));
-        csr_cell_kernel<true><<<wgrid, CD_WARPS * 32, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g, n, nr,
-                                                                   use_periodic, lo2, hi2, fill);
+        cell_tile_kernel<float, CT_CSR_FILL><<<g.ncells, CT_THREADS, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g,
+                                                                                 use_periodic, lo2, hi2, to);
         TMDN_LAUNCH_CHECK();
     } else {
         Box3<float> b;

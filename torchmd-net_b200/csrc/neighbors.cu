@@ -12,7 +12,7 @@
 //   * arithmetic is written with explicit round-to-nearest mul/add/sub (no FMA contraction) so deltas and
 //     distances are bit-identical to the CPU restatement in oracle/neighbors.py.
 #include "common.cuh"
-#include "nbr_common.cuh"
+#include "nbr_cell_tile.cuh"
 #include "scan.cuh"
 
 namespace {
@@ -161,127 +161,8 @@ template <typename T> __global__ void pad_fill_kernel(PairOut<T> out) {
     out.dist[s] = T(0);
 }
 
-// ------------------------------------------------------------------ cell list (binning: nbr_common.cuh)
-constexpr int CELL_CAND = 1024;   // candidates staged per chunk
-constexpr int CELL_GROUP = 128;   // centre atoms processed per group
-
-template <typename T>
-__device__ __forceinline__ bool cell_hit(T xa, T ya, T za, long long ba, int ga, int ia, T xq, T yq, T zq, long long bq,
-                                         int gq, int iq, const CellGrid<T>& g, int periodic, T lo2, T hi2, int loop,
-                                         int transpose, T& dx, T& dy, T& dz, T& d2) {
-    if (gq == ga) {  // the atom itself: self loop regardless of the cutoffs (neighbors_cuda_cell.cuh:300-301)
-        dx = dy = dz = d2 = T(0);
-        return loop != 0;
-    }
-    if (bq != ba) return false;
-    if (!transpose && ia < iq) return false;  // half list keeps (larger index, smaller index)
-    dx = rn_sub(xa, xq);
-    dy = rn_sub(ya, yq);
-    dz = rn_sub(za, zq);
-    if (periodic) {
-        dx = min_image_rect1(dx, g.L[0]);
-        dy = min_image_rect1(dy, g.L[1]);
-        dz = min_image_rect1(dz, g.L[2]);
-    }
-    d2 = dist2(dx, dy, dz);
-    return d2 < hi2 && d2 >= lo2;
-}
-
-template <typename T>
-__global__ void __launch_bounds__(NB_THREADS)
-cell_traverse_kernel(const SortedAtom<T>* __restrict__ spos, const long long* __restrict__ sbatch,
-                     const int* __restrict__ cell_start, CellGrid<T> g, int periodic, T lo2, T hi2, int loop,
-                     int transpose, PairOut<T> out) {
-    __shared__ T cx[CELL_CAND], cy[CELL_CAND], cz[CELL_CAND];
-    __shared__ long long cb[CELL_CAND];
-    __shared__ int cidx[CELL_CAND], cgl[CELL_CAND];
-    __shared__ int nb_start[27], nb_pref[28];
-    __shared__ int s_cnt[CELL_GROUP];
-    __shared__ int s_warp[NB_THREADS / 32 + 1];
-    __shared__ int s_base;
-    const int cell = blockIdx.x;
-    const int cs = cell_start[cell], ce = cell_start[cell + 1];
-    if (cs == ce) return;  // empty cell (block-uniform)
-    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
-    const int ccx = cell % g.n[0], ccy = (cell / g.n[0]) % g.n[1], ccz = cell / (g.n[0] * g.n[1]);
-    if (t == 0) {
-        int k = 0, run = 0;
-        for (int oz = g.lo[2]; oz <= g.hi[2]; ++oz)
-            for (int oy = g.lo[1]; oy <= g.hi[1]; ++oy)
-                for (int ox = g.lo[0]; ox <= g.hi[0]; ++ox) {
-                    const int x = (ccx + ox + g.n[0]) % g.n[0], y = (ccy + oy + g.n[1]) % g.n[1],
-                              z = (ccz + oz + g.n[2]) % g.n[2];
-                    const int c = x + g.n[0] * (y + g.n[1] * z);
-                    nb_start[k] = cell_start[c];
-                    nb_pref[k] = run;
-                    run += cell_start[c + 1] - cell_start[c];
-                    ++k;
-                }
-        for (; k < 27; ++k) { nb_start[k] = 0; nb_pref[k] = run; }
-        nb_pref[27] = run;
-    }
-    __syncthreads();
-    const int ncand = nb_pref[27];
-    for (int g0 = cs; g0 < ce; g0 += CELL_GROUP) {
-        const int gn = min(CELL_GROUP, ce - g0);
-        for (int k0 = 0; k0 < ncand; k0 += CELL_CAND) {
-            const int kn = min(CELL_CAND, ncand - k0);
-            __syncthreads();
-            for (int k = t; k < kn; k += NB_THREADS) {
-                const int kk = k0 + k;
-                int c = 0;
-                while (c < 26 && nb_pref[c + 1] <= kk) ++c;
-                const int gi = nb_start[c] + (kk - nb_pref[c]);
-                const SortedAtom<T> a = spos[gi];
-                cx[k] = a.x; cy[k] = a.y; cz[k] = a.z; cidx[k] = a.idx; cgl[k] = gi;
-                cb[k] = sbatch[gi];
-            }
-            for (int k = t; k < CELL_GROUP; k += NB_THREADS) s_cnt[k] = 0;
-            __syncthreads();
-            // count
-            for (int al = w; al < gn; al += NB_THREADS / 32) {
-                const int ga = g0 + al;
-                const SortedAtom<T> a = spos[ga];
-                const long long ba = sbatch[ga];
-                int cnt = 0;
-                for (int k = lane; k < kn; k += 32) {
-                    T dx, dy, dz, d2;
-                    cnt += cell_hit(a.x, a.y, a.z, ba, ga, a.idx, cx[k], cy[k], cz[k], cb[k], cgl[k], cidx[k], g,
-                                    periodic, lo2, hi2, loop, transpose, dx, dy, dz, d2) ? 1 : 0;
-                }
-                cnt = warp_sum_i(cnt);
-                if (lane == 0) s_cnt[al] = cnt;
-            }
-            __syncthreads();
-            int total;
-            const int mine = (t < CELL_GROUP) ? s_cnt[t] : 0;   // CELL_GROUP == NB_THREADS
-            const int off = block_excl_scan(mine, total, s_warp);
-            if (total == 0) continue;  // block-uniform
-            __syncthreads();
-            s_cnt[t] = off;
-            if (t == 0) s_base = atomicAdd(out.counter, total);
-            __syncthreads();
-            // fill
-            for (int al = w; al < gn; al += NB_THREADS / 32) {
-                const int ga = g0 + al;
-                const SortedAtom<T> a = spos[ga];
-                const long long ba = sbatch[ga];
-                long long slot = (long long)s_base + s_cnt[al];
-                for (int kb = 0; kb < kn; kb += 32) {
-                    const int k = kb + lane;
-                    T dx = 0, dy = 0, dz = 0, d2 = 0;
-                    bool hit = false;
-                    if (k < kn)
-                        hit = cell_hit(a.x, a.y, a.z, ba, ga, a.idx, cx[k], cy[k], cz[k], cb[k], cgl[k], cidx[k], g,
-                                       periodic, lo2, hi2, loop, transpose, dx, dy, dz, d2);
-                    const unsigned m = __ballot_sync(0xffffffffu, hit);
-                    if (hit) write_pair(out, slot + __popc(m & ((1u << lane) - 1u)), a.idx, cidx[k], dx, dy, dz, sqrt_rn(d2));
-                    slot += __popc(m);
-                }
-            }
-        }
-    }
-}
+// ------------------------------------------------------------------ cell list: binning in nbr_common.cuh, traversal in
+// nbr_cell_tile.cuh (one CTA per cell, shared-memory candidate tile, hit lists, one atomic per centre group)
 
 // ------------------------------------------------------------------ backward (neighbors_cuda.cu:43-71)
 template <typename T>
@@ -361,9 +242,11 @@ int neighbors_impl(int strategy, const T* pos, const int64_t* batch, int64_t n_a
         cell_scatter_kernel<T><<<blocks, 256, 0, stream>>>(pos, batch, n, w.cell_start, w.cell_of, w.slot_of,
                                                            (SortedAtom<T>*)w.spos, w.sbatch);
         TMDN_LAUNCH_CHECK();
-        cell_traverse_kernel<T><<<g.ncells, NB_THREADS, 0, stream>>>((const SortedAtom<T>*)w.spos, w.sbatch, w.cell_start,
-                                                                     g, use_periodic, lo2, hi2, loop, include_transpose,
-                                                                     out);
+        CellTileOut<T> to{};
+        to.nbr = neighbors; to.deltas = deltas; to.dist = distances; to.counter = num_found;
+        to.max_pairs = (long long)max_pairs; to.loop = loop; to.transpose = include_transpose;
+        cell_tile_kernel<T, CT_PAIRS><<<g.ncells, CT_THREADS, 0, stream>>>((const SortedAtom<T>*)w.spos, w.sbatch,
+                                                                          w.cell_start, g, use_periodic, lo2, hi2, to);
         TMDN_LAUNCH_CHECK();
     } else {
         Box3<T> b;
