@@ -200,6 +200,12 @@ int tmdn_tensornet_stage(const tmdn_tensornet_model* m, int stage, int layer, co
  * the ghost rows (the contiguous tail of the local arrays), so there is no unpack. */
 int tmdn_halo_pack_f32(const float* src, const int32_t* idx, int64_t n_rows, int64_t row_floats, float* out,
                        tmdn_stream_t stream);
+/* Grouped channel mix of TensorNet (tensornet.py:273-284, 386-408: linears_tensor on the I | A | S parts):
+ *   y[a, c, :] (+)= x[a, c, :] * w[g(c)]^T,   x, y [n_atoms,9,H] fp32, w [3,H,H] (g = 0 for c = 0, 1 for c = 1..3, 2 for
+ *   c = 4..8).  H = 128 runs on the tcgen05 tensor cores with the three-product tf32 split (fp32-level accuracy);
+ * other widths on the fp32 FFMA kernel.  This is the operator the model path calls for every mix; exported for tests. */
+int tmdn_channel_mix_f32(const float* x, const float* w, float* y, int64_t n_atoms, int H, int accumulate,
+                         tmdn_stream_t stream);
 /* Debug/inspection: byte offset and size of a named intermediate inside the workspace (names as in
  * oracle/staged_tensornet.py: "row_ptr","col","geom","ias","nh","fias","X0","Y0","M0","tauh0","X1",...,"e_atom","Dias","gpos"). */
 int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,

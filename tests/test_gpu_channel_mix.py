@@ -1,0 +1,53 @@
+"""Grouped channel mix (tensornet.py:273-284, 386-408 linears_tensor) through the C ABI: tcgen05 path (H = 128,
+three-product tf32 split) and FFMA path (other widths) against an fp64 einsum."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+GROUP = [0, 1, 1, 1, 2, 2, 2, 2, 2]
+
+
+def reference(x, w):
+    xd, wd = x.double().cpu(), w.double().cpu()
+    return torch.stack([xd[:, c] @ wd[GROUP[c]].T for c in range(9)], 1)
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from torchmdnet import _native
+    _native.load()
+    return torch.ops.torchmdnet_b200
+
+
+@pytest.mark.parametrize("n", [1, 7, 25, 42, 43, 128, 166, 1000, 20011])
+@pytest.mark.parametrize("H", [128, 64])
+def test_channel_mix_matches_fp64(ops, n, H):
+    g = torch.Generator().manual_seed(n * 7 + H)
+    x = (torch.randn(n, 9, H, generator=g) * torch.logspace(-2, 1, 9).view(1, 9, 1)).cuda()
+    w = (torch.randn(3, H, H, generator=g) / H ** 0.5).cuda()
+    y = ops.channel_mix(x, w, None, False)
+    ref = reference(x, w)
+    bound = torch.stack([x.double().cpu()[:, c].abs() @ w.double().cpu()[GROUP[c]].abs().T for c in range(9)], 1)
+    err = (y.double().cpu() - ref).abs()
+    # fp32-level accuracy: 2e-6 of sum_k |x_k w_k| (fp32 FFMA itself is ~1e-6 of that bound at K = 128)
+    assert (err <= 2e-6 * bound + 1e-30).all(), float((err / (bound + 1e-30)).max())
+
+
+def test_channel_mix_accumulates(ops):
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(333, 9, 128, generator=g).cuda()
+    w = (torch.randn(3, 128, 128, generator=g) / 128 ** 0.5).cuda()
+    y0 = torch.randn(333, 9, 128, generator=g).cuda()
+    y = ops.channel_mix(x, w, y0.clone(), True)
+    ref = reference(x, w) + y0.double().cpu()
+    assert torch.allclose(y.double().cpu(), ref, rtol=0, atol=2e-5)
+
+
+def test_channel_mix_is_repeatable(ops):
+    g = torch.Generator().manual_seed(6)
+    x = torch.randn(5000, 9, 128, generator=g).cuda()
+    w = (torch.randn(3, 128, 128, generator=g) / 128 ** 0.5).cuda()
+    a = ops.channel_mix(x, w, None, False)
+    b = ops.channel_mix(x, w, None, False)
+    assert torch.equal(a, b)

@@ -196,7 +196,7 @@ extern "C" int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int
     EdgeOut fill{row_ptr, nullptr, col, (float4*)geom, (long long)max_edges};
     const int nr = (int)n_rows;
     const unsigned rgrid = (unsigned)cdiv(nr, CD_WARPS);
-    if (nr < n) TMDN_CUDA(cudaMemsetAsync(w.row_cnt, 0, sizeof(int) * ((size_t)n + 1), stream));
+    if (nr < n || strategy == TMDN_CELL) TMDN_CUDA(cudaMemsetAsync(w.row_cnt, 0, sizeof(int) * ((size_t)n + 1), stream));
     if (strategy == TMDN_CELL) {
         TMDN_CUDA(cudaMemsetAsync(w.cell_cnt, 0, sizeof(int) * (g.ncells + 1), stream));
         const int blocks = (int)cdiv(n, 256);
@@ -216,6 +216,7 @@ extern "C" int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int
                                                                                   use_periodic, lo2, hi2, to);
         TMDN_LAUNCH_CHECK();
         TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));
+        TMDN_CUDA(cudaMemsetAsync(w.row_cnt, 0, sizeof(int) * ((size_t)n + 1), stream));   // now the fill cursor
         cell_tile_kernel<float, CT_CSR_FILL><<<g.ncells, CT_THREADS, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g,
                                                                                  use_periodic, lo2, hi2, to);
         TMDN_LAUNCH_CHECK();

@@ -7,7 +7,7 @@
 // x-neighbours of a cell row are adjacent); their atoms are staged once in shared memory.  A warp owns a centre atom:
 //   pass 1  lanes test 32 candidates at a time from shared memory, `ballot` compacts the hits into a per-centre
 //           list of candidate slots (uint16) -- no output yet, ~20 instructions per test;
-//   reserve (pair list only) block scan of the per-centre counts, ONE global atomicAdd per (CTA, centre group);
+//   reserve (pair list only) warp scan of the per-centre counts, ONE global atomicAdd per (chunk, centre group);
 //   pass 2  dense loop over the hit list: recompute the delta with the same rounding, sqrt, coalesced stores.
 // The pair list tests each unordered pair once (original index i > j) and writes both directions; the CSR builder
 // tests all candidates of a row (rows must be complete).  The rectangular minimum image of the reference,
@@ -79,28 +79,22 @@ cell_tile_kernel(const SortedAtom<T>* __restrict__ spos, const long long* __rest
     const int ncand = r_pref[18];
     const int nchunks = (ncand + CT_CAND - 1) / CT_CAND;
     const int per_hit = (MODE == CT_PAIRS && out.transpose) ? 2 : 1;
-    for (int g0 = cs; g0 < ce; g0 += CT_GROUP) {
-        const int gn = min(CT_GROUP, ce - g0);
-        int run[CT_GROUP / CT_WARPS];                        // CSR fill: per-centre running offset across chunks
-#pragma unroll
-        for (int q = 0; q < CT_GROUP / CT_WARPS; ++q) run[q] = 0;
-        for (int ch = 0; ch < nchunks; ++ch) {
-            const int k0 = ch * CT_CAND, kn = min(CT_CAND, ncand - k0);
-            if (nchunks > 1 || g0 == cs) {                   // stage the candidates (once when they fit one chunk)
-                __syncthreads();
-                for (int r = w; r < 18; r += CT_WARPS) {
-                    const int p0 = r_pref[r], len = r_pref[r + 1] - p0, st = r_start[r];
-                    for (int k = lane; k < len; k += 32) {
-                        const int kk = p0 + k - k0;
-                        if (kk >= 0 && kk < CT_CAND) {
-                            const SortedAtom<T> a = spos[st + k];
-                            cx[kk] = a.x; cy[kk] = a.y; cz[kk] = a.z; cidx[kk] = a.idx;
-                            cb[kk] = sbatch[st + k];
-                        }
-                    }
-                }
+    for (int ch = 0; ch < nchunks; ++ch) {
+        const int k0 = ch * CT_CAND, kn = min(CT_CAND, ncand - k0);
+        // ---- stage the candidates of this chunk: a warp per range, coalesced
+        for (int r = w; r < 18; r += CT_WARPS) {
+            const int p0 = r_pref[r], len = r_pref[r + 1] - p0, st = r_start[r];
+            const int kb = max(0, k0 - p0), ke = min(len, k0 + CT_CAND - p0);   // part of the range in this chunk
+            for (int k = kb + lane; k < ke; k += 32) {
+                const int kk = p0 + k - k0;
+                const SortedAtom<T> a = spos[st + k];
+                cx[kk] = a.x; cy[kk] = a.y; cz[kk] = a.z; cidx[kk] = a.idx;
+                cb[kk] = sbatch[st + k];
             }
-            __syncthreads();
+        }
+        __syncthreads();
+        for (int g0 = cs; g0 < ce; g0 += CT_GROUP) {
+            const int gn = min(CT_GROUP, ce - g0);
             // ---- pass 1: hit lists
 #pragma unroll
             for (int q = 0; q < CT_GROUP / CT_WARPS; ++q) {
@@ -136,7 +130,7 @@ cell_tile_kernel(const SortedAtom<T>* __restrict__ spos, const long long* __rest
                 if (lane == 0) s_cnt[al] = cnt;
             }
             __syncthreads();
-            // ---- reserve
+            // ---- reserve output slots: one global atomic per (chunk, centre group)
             if (MODE == CT_PAIRS) {
                 if (w == 0) {
                     int items = 0;
@@ -155,13 +149,19 @@ cell_tile_kernel(const SortedAtom<T>* __restrict__ spos, const long long* __rest
                 if (al >= gn) continue;
                 const int cnt = s_cnt[al];
                 const SortedAtom<T> a = spos[g0 + al];
-                if (MODE == CT_CSR_COUNT) {
-                    if (lane == 0 && a.idx < out.n_rows) run[q] += cnt;
-                    continue;
+                long long base = 0;
+                if (MODE == CT_PAIRS) {
+                    base = (long long)s_base + s_off[al];
+                } else {
+                    // the row's running length across chunks lives in row_cnt (zeroed by the host before each
+                    // pass); only this warp touches the entry
+                    if (a.idx >= out.n_rows || cnt == 0) continue;
+                    int run = 0;
+                    if (lane == 0) { run = out.row_cnt[a.idx]; out.row_cnt[a.idx] = run + cnt; }
+                    if (MODE == CT_CSR_COUNT) continue;
+                    run = __shfl_sync(0xffffffffu, run, 0);
+                    base = (long long)out.row_ptr[a.idx] + run;
                 }
-                long long base;
-                if (MODE == CT_PAIRS) base = (long long)s_base + s_off[al];
-                else base = (a.idx < out.n_rows) ? (long long)out.row_ptr[a.idx] + run[q] : 0;
                 for (int hb = 0; hb < cnt; hb += 32) {
                     const int hI = hb + lane;
                     if (hI < cnt) {
@@ -207,18 +207,8 @@ cell_tile_kernel(const SortedAtom<T>* __restrict__ spos, const long long* __rest
                         out.dist[slot] = T(0);
                     }
                 }
-                if (MODE == CT_CSR_FILL) run[q] += cnt;
             }
-            __syncthreads();
-        }
-        if (MODE == CT_CSR_COUNT) {                          // publish the row lengths
-#pragma unroll
-            for (int q = 0; q < CT_GROUP / CT_WARPS; ++q) {
-                const int al = w + q * CT_WARPS;
-                if (al >= gn || lane != 0) continue;
-                const int idx = spos[g0 + al].idx;
-                if (idx < out.n_rows) out.row_cnt[idx] = run[q];
-            }
+            __syncthreads();                                 // hit lists and counters are reused by the next group
         }
     }
 }

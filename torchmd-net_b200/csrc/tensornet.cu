@@ -13,6 +13,7 @@
 // gathers the adjoints of its neighbours and also accumulates both directions' contribution to dE/dpos_i.
 #include "common.cuh"
 #include "gemm.cuh"
+#include "tc_mix.cuh"
 #include "tensor3.cuh"
 #include "edge_common.cuh"
 #include "scan.cuh"
@@ -739,6 +740,13 @@ GemmBatch mix_batch(const float* A, float* C, const float* const Wg[3], int N, i
     return b;
 }
 
+// tensor cores for H = 128 (tc_mix.cuh); TMDN_TC_MIX=0 keeps the FFMA kernel (A/B measurements)
+int mix_launch(int epi, const GemmBatch& b, cudaStream_t stream) {
+    static const int use_tc = [] { const char* e = getenv("TMDN_TC_MIX"); return e ? atoi(e) : 1; }();
+    if (use_tc && (epi == EPI_NONE || epi == EPI_SCALE3) && tcmix::supported(b)) return tcmix::launch(epi, b, stream);
+    return gemm_launch(epi, b, stream);
+}
+
 // exact-mode evaluation of one filter set on all (capacity) edges -> F, dF [E,3,H]
 int eval_filter_exact(const tmdn_tensornet_model* m, const tmdn_filter_set& fs, const TnWs& w, int64_t N, int64_t P,
                       float* F, float* dF, cudaStream_t stream) {
@@ -866,7 +874,7 @@ struct TnRun {
             tn_update_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.dX[l], w.dB, NH, H);
             TMDN_LAUNCH_CHECK();
         }
-        TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.dB, w.dC, m->layer_mixT[l] + 3, N, H), stream));
+        TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.dB, w.dC, m->layer_mixT[l] + 3, N, H), stream));
         {
             KTimer ktimer__("tn_prod_bwd", stream);
             tn_prod_bwd<<<egrid, 256, 0, stream>>>(w.Y[l], w.M[l], w.dC, w.dB, NH, H, m->so3);
@@ -890,7 +898,7 @@ struct TnRun {
         TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
         GemmP q = gemm_desc(w.dh1, 2 * H, m->emb_w1T, nullptr, w.dnh, H, N, H, 2 * H);
         TMDN_TRY(gemm1(EPI_NONE, q, stream));
-        TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.dXa, w.dB, m->emb_mixT, N, H), stream));
+        TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.dXa, w.dB, m->emb_mixT, N, H), stream));
         {
             KTimer ktimer__("tn_embed_norm_bwd", stream);
             tn_embed_norm_bwd<<<(unsigned)cdiv(N, apb), dim3(H, apb), 0, stream>>>(w.ias, m->emb_ln_w, w.dnh, w.dB, N, H);
@@ -961,14 +969,14 @@ struct TnRun {
             TMDN_TRY(gemm1(EPI_ACT, q, stream));
             GemmBatch b = mix_batch(w.ias, w.X[0], m->emb_mix, N, H);
             for (int g = 0; g < 3; ++g) { b.p[g].C2 = w.iasm; b.p[g].aux = w.fias; }
-            TMDN_TRY(gemm_launch(EPI_SCALE3, b, stream));
+            TMDN_TRY(mix_launch(EPI_SCALE3, b, stream));
             if (L > 0) {
                 {
                     KTimer ktimer__("tn_normalize_fwd", stream);
                     tn_normalize_fwd<<<egrid, 256, 0, stream>>>(w.X[0], w.Xh, NH, H);
                     TMDN_LAUNCH_CHECK();
                 }
-                TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.Xh, w.Y[0], m->layer_mix[0], N, H), stream));
+                TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.Xh, w.Y[0], m->layer_mix[0], N, H), stream));
             }
             return TMDN_OK;
         }
@@ -983,7 +991,7 @@ struct TnRun {
                                                                               H, m->so3, w.M[l], w.tauh);
                 TMDN_LAUNCH_CHECK();
             }
-            TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
+            TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
             // Xh is both input (residual) and, for the next layer, output: safe because each thread reads its own
             // (atom, channel) column before writing it.
             {
@@ -991,7 +999,7 @@ struct TnRun {
                 tn_update_fwd<<<egrid, 256, 0, stream>>>(w.Xh, w.dX[l], w.X[l + 1], l + 1 < L ? w.Xh : nullptr, NH, H);
                 TMDN_LAUNCH_CHECK();
             }
-            if (l + 1 < L) TMDN_TRY(gemm_launch(EPI_NONE, mix_batch(w.Xh, w.Y[l + 1], m->layer_mix[l + 1], N, H), stream));
+            if (l + 1 < L) TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.Xh, w.Y[l + 1], m->layer_mix[l + 1], N, H), stream));
             return TMDN_OK;
         }
         if (s == TMDN_TN_HEAD) {
@@ -1054,7 +1062,7 @@ struct TnRun {
             }
             GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
             for (int g = 0; g < 3; ++g) b.p[g].accumulate = 1;
-            TMDN_TRY(gemm_launch(EPI_NONE, b, stream));
+            TMDN_TRY(mix_launch(EPI_NONE, b, stream));
             {
                 KTimer ktimer__("tn_normalize_bwd", stream);
                 tn_normalize_bwd<<<egrid, 256, 0, stream>>>(w.X[l], w.dXa, NH, H);
@@ -1106,4 +1114,16 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
     if (!forces) return TMDN_OK;
     for (int l = L - 1; l >= 0; --l) TMDN_TRY(r.stage(TMDN_TN_LAYER_BWD, l));
     return r.stage(TMDN_TN_FINAL, 0);
+}
+
+extern "C" int tmdn_channel_mix_f32(const float* x, const float* w, float* y, int64_t n_atoms, int H, int accumulate,
+                                    tmdn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    TMDN_CHECK_ARG(x && w && y, "channel_mix: null pointer argument");
+    TMDN_CHECK_ARG(n_atoms > 0 && n_atoms * 9 < (1LL << 31), "channel_mix: bad atom count");
+    TMDN_CHECK_ARG(H > 0 && H % 4 == 0, "channel_mix: H must be a positive multiple of 4");
+    const float* Wg[3] = {w, w + (size_t)H * H, w + 2 * (size_t)H * H};
+    GemmBatch b = mix_batch(x, y, Wg, (int)n_atoms, H);
+    for (int g = 0; g < 3; ++g) b.p[g].accumulate = accumulate;
+    return mix_launch(EPI_NONE, b, stream);
 }

@@ -524,6 +524,23 @@ Tensor halo_pack(const Tensor& src, const Tensor& idx) {
     return out;
 }
 
+// y[a,c,:] (+)= x[a,c,:] * w[g(c)]^T  (grouped channel mix of TensorNet)
+Tensor channel_mix(const Tensor& x, const Tensor& w, const c10::optional<Tensor>& y_, bool accumulate) {
+    TORCH_CHECK(x.is_cuda() && x.scalar_type() == at::kFloat && x.is_contiguous() && x.dim() == 3 && x.size(1) == 9,
+                "channel_mix: x must be a contiguous CUDA float32 [n,9,H] tensor");
+    const int64_t H = x.size(2);
+    TORCH_CHECK(w.is_cuda() && w.scalar_type() == at::kFloat && w.is_contiguous() && w.dim() == 3 && w.size(0) == 3 &&
+                    w.size(1) == H && w.size(2) == H,
+                "channel_mix: w must be a contiguous CUDA float32 [3,H,H] tensor");
+    const c10::cuda::CUDAGuard guard(x.device());
+    Tensor y = y_.has_value() ? *y_ : at::zeros_like(x);
+    TORCH_CHECK(y.is_cuda() && y.scalar_type() == at::kFloat && y.is_contiguous() && y.sizes() == x.sizes(),
+                "channel_mix: y must match x");
+    TMDN_CALL(tmdn_channel_mix_f32(x.data_ptr<float>(), w.data_ptr<float>(), y.data_ptr<float>(), x.size(0), (int)H,
+                                   accumulate ? 1 : 0, cur_stream()));
+    return y;
+}
+
 int64_t launch_count() { return (int64_t)tmdn_launch_count(); }
 void profile_enable(bool on) { TMDN_CALL(tmdn_profile_enable(on ? 1 : 0)); }
 std::string profile_report() {
@@ -569,6 +586,7 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
           "Tensor box_vectors, bool use_periodic, str strategy, int max_edges, int n_mol, Tensor(a!) energy, "
           "Tensor(b!) forces, Tensor(c!) status, Tensor(d!) workspace) -> ()", tensornet_stage);
     m.def("halo_pack(Tensor src, Tensor idx) -> Tensor", halo_pack);
+    m.def("channel_mix(Tensor x, Tensor w, Tensor? y, bool accumulate) -> Tensor", channel_mix);
     m.def("launch_count() -> int", launch_count);
     m.def("profile_enable(bool on) -> ()", profile_enable);
     m.def("profile_report() -> str", profile_report);
