@@ -10,11 +10,12 @@
 //
 // One persistent CTA per SM works on 128-row tiles of one component group (a tile = na atoms x gs components:
 // 128x1, 42x3 or 25x5 rows, fetched as ONE 3-D TMA box from the [N,9,H] tensor, so no permuted copy of X exists):
-//   warp 0       TMA producer: W once (4 K-chunks of 32), then X chunks [rows, 32] into a 3-stage ring (SWIZZLE_128B)
+//   warp 0       TMA producer: W once (4 K-chunks of 32), then X chunks [rows, 32] into a 2-stage ring (SWIZZLE_128B)
 //   warps 8-11   split: round the landed chunk to tf32 in place, write the low part beside it, fence to the async proxy
 //   warp 1       one thread issues 3 x 4 tcgen05.mma (M128 N128 K8) per chunk; tcgen05.commit frees the ring slot
 //   warps 4-7    epilogue: tcgen05.ld the 128x128 accumulator (double buffered in TMEM, 2 x 128 columns), apply the
-//                fused scale / accumulate, store rows through the same (atom, component) map
+//                fused scale, stage 32-column slabs in shared memory and TMA-store (or reduce-add) them through
+//                the same 3-D box
 // Per tile the tensor pipe needs ~1.7 us and HBM (64 KB in, 64 KB out) ~2.9 us, so the kernel is bound by HBM.
 #pragma once
 #include <cuda.h>
@@ -28,10 +29,11 @@ namespace tcmix {
 constexpr int TILE = 128;            // rows per tile = MMA M; also N and K (= hidden channels)
 constexpr int KC = 32;               // K floats per chunk: one 128-byte swizzle row
 constexpr int NCHUNK = TILE / KC;    // 4
-constexpr int STAGES = 3;
+constexpr int STAGES = 2;           // X ring (raw/hi + lo per stage)
+constexpr int CSTAGES = 2;          // output staging buffers [128 rows x 32 columns]
 constexpr int CHUNK_FLOATS = TILE * KC;          // 4096 floats = 16 KB
 constexpr int THREADS = 384;
-constexpr int SMEM_BYTES = (2 * NCHUNK + 2 * STAGES) * CHUNK_FLOATS * 4 + 256 + 1024;
+constexpr int SMEM_BYTES = (2 * NCHUNK + 2 * STAGES + CSTAGES) * CHUNK_FLOATS * 4 + 256 + 1024;
 constexpr int TMEM_COLS = 256;
 
 struct Problem {
@@ -45,6 +47,9 @@ struct Params {
     int cta_off[4];
     int n_atoms;
     int epi, accumulate;
+};
+struct Maps {
+    CUtensorMap x[3], w[3], c[3], c2[3];   // per component group: input box, weight, output box, second output
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -84,6 +89,21 @@ __device__ __forceinline__ void tma_3d(void* dst, const CUtensorMap* map, int x,
         "l"(map), "r"(x), "r"(y), "r"(z), "r"(s32(bar))
         : "memory");
 }
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* src, int x, int y, int z, bool add) {
+    if (add)
+        asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
+                     "r"(s32(src)), "r"(x), "r"(y), "r"(z)
+                     : "memory");
+    else
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
+                     "r"(s32(src)), "r"(x), "r"(y), "r"(z)
+                     : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N> __device__ __forceinline__ void tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -133,23 +153,21 @@ __device__ __forceinline__ void split_inplace(float4* hi, float4* lo, int idx) {
     const float4 v = hi[idx];
     float4 h, l;
     h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
-    l.x = tf32_rna(v.x - h.x); l.y = tf32_rna(v.y - h.y); l.z = tf32_rna(v.z - h.z); l.w = tf32_rna(v.w - h.w);
+    l.x = v.x - h.x; l.y = v.y - h.y; l.z = v.z - h.z; l.w = v.w - h.w;   // exact; the MMA reads its top 19 bits
     hi[idx] = h;
     lo[idx] = l;
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
-tc_mix_kernel(const __grid_constant__ CUtensorMap mA0, const __grid_constant__ CUtensorMap mA1,
-              const __grid_constant__ CUtensorMap mA2, const __grid_constant__ CUtensorMap mW0,
-              const __grid_constant__ CUtensorMap mW1, const __grid_constant__ CUtensorMap mW2,
-              const __grid_constant__ Params P) {
+tc_mix_kernel(const __grid_constant__ Maps M, const __grid_constant__ Params P) {
     extern __shared__ unsigned char tc_smem_raw[];
     unsigned char* sm = tc_smem_raw + ((1024u - (s32(tc_smem_raw) & 1023u)) & 1023u);   // SWIZZLE_128B: 1024-byte base
     float* Bhi = reinterpret_cast<float*>(sm);
     float* Blo = Bhi + NCHUNK * CHUNK_FLOATS;
     float* Ahi = Blo + NCHUNK * CHUNK_FLOATS;
     float* Alo = Ahi + STAGES * CHUNK_FLOATS;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(Alo + STAGES * CHUNK_FLOATS);
+    float* Cst = Alo + STAGES * CHUNK_FLOATS;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(Cst + CSTAGES * CHUNK_FLOATS);
     uint64_t* full_raw = bars;            // [STAGES] TMA -> split
     uint64_t* lo_ready = bars + 3;        // [STAGES] split -> MMA
     uint64_t* empty = bars + 6;           // [STAGES] MMA -> TMA
@@ -164,8 +182,8 @@ tc_mix_kernel(const __grid_constant__ CUtensorMap mA0, const __grid_constant__ C
     while (pi < 2 && (int)blockIdx.x >= P.cta_off[pi + 1]) ++pi;
     const int rank = blockIdx.x - P.cta_off[pi], nctas = P.cta_off[pi + 1] - P.cta_off[pi];
     const Problem pr = P.p[pi];
-    const CUtensorMap* mA = pi == 0 ? &mA0 : (pi == 1 ? &mA1 : &mA2);
-    const CUtensorMap* mW = pi == 0 ? &mW0 : (pi == 1 ? &mW1 : &mW2);
+    const CUtensorMap* mA = &M.x[pi];
+    const CUtensorMap* mW = &M.w[pi];
     const int my_tiles = rank < pr.tiles ? (pr.tiles - rank + nctas - 1) / nctas : 0;
 
     if (threadIdx.x == 0) {
@@ -233,42 +251,56 @@ tc_mix_kernel(const __grid_constant__ CUtensorMap mA0, const __grid_constant__ C
             }
         }
     } else if (warp >= 4 && warp < 8) {
-        // ================= epilogue: warp w reads TMEM lanes 32 (w % 4) ..
+        // ================= epilogue: warp w reads TMEM lanes 32 (w % 4) ..; thread = one row of the tile.  A 32-column
+        // slab goes registers -> swizzled staging buffer -> ONE TMA store (or reduce-add) through the same
+        // (channel, component, atom) box as the input, so global memory sees whole 128-byte row segments.
         const int row = (warp - 4) * 32 + lane;
-        const int H = TILE;
+        const bool issuer = threadIdx.x == 128;
+        const CUtensorMap* mC = &M.c[pi];
+        const CUtensorMap* mC2 = &M.c2[pi];
+        const bool scale = P.epi == EPI_SCALE3;
+        int sb = 0;
+        auto stage_out = [&](const float (&v)[32], const CUtensorMap* map, int col0, int atom0, bool add) {
+            if (issuer) tma_store_wait_read<CSTAGES - 1>();   // the store that last read this buffer is done with it
+            epi_barrier();
+            float* buf = Cst + sb * CHUNK_FLOATS + row * KC;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(buf + ((j ^ (row & 7)) << 2)) =
+                    make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            fence_async_smem();
+            epi_barrier();
+            if (issuer) tma_store_3d(map, Cst + sb * CHUNK_FLOATS, col0, pr.c0, atom0, add);
+            sb ^= 1;
+        };
         for (int t = 0; t < my_tiles; ++t) {
             const int b = t & 1;
             mbar_wait(&tmem_full[b], (t >> 1) & 1);
             tc_fence_after();
-            const int atom = (rank + t * nctas) * pr.na + row / pr.gs;
+            const int atom0 = (rank + t * nctas) * pr.na;
+            const int atom = atom0 + row / pr.gs;
             const bool valid = row < pr.gs * pr.na && atom < P.n_atoms;
-            const size_t prow = (size_t)atom * 9 + pr.c0 + row % pr.gs;
-            float* crow = pr.C + prow * H;
 #pragma unroll 1
             for (int cb = 0; cb < TILE / 32; ++cb) {
                 float v[32];
                 tc_ld32(tmem + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)(b * TILE + cb * 32), v);
-                if (valid) {
+                if (scale) {
+                    if (pr.C2) stage_out(v, mC2, cb * 32, atom0, false);
+                    if (valid) {
+                        const float4* sc = reinterpret_cast<const float4*>(pr.aux + ((size_t)atom * 3 + pr.g) * TILE + cb * 32);
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        const int n = cb * 32 + j;
-                        float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                        if (P.epi == EPI_SCALE3) {
-                            if (pr.C2) *reinterpret_cast<float4*>(pr.C2 + prow * H + n) = o;
-                            const float4 sc = *reinterpret_cast<const float4*>(pr.aux + ((size_t)atom * 3 + pr.g) * H + n);
-                            o.x *= sc.x; o.y *= sc.y; o.z *= sc.z; o.w *= sc.w;
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 q = sc[j];
+                            v[4 * j] *= q.x; v[4 * j + 1] *= q.y; v[4 * j + 2] *= q.z; v[4 * j + 3] *= q.w;
                         }
-                        if (P.accumulate) {
-                            const float4 old = *reinterpret_cast<const float4*>(crow + n);
-                            o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
-                        }
-                        *reinterpret_cast<float4*>(crow + n) = o;
                     }
                 }
+                stage_out(v, mC, cb * 32, atom0, P.accumulate != 0);
             }
             tc_fence_before();
             mbar_arrive(&tmem_empty[b]);
         }
+        if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     } else if (warp >= 8) {
         // ================= split warps
         const int tid = threadIdx.x - 256;
@@ -351,7 +383,8 @@ static inline int launch(int epi, const GemmBatch& b, cudaStream_t stream) {
     if (n_atoms <= 0) return TMDN_OK;
     Params P;
     memset(&P, 0, sizeof(P));
-    CUtensorMap mA[3], mW[3];
+    Maps M;
+    memset(&M, 0, sizeof(M));
     long long total_tiles = 0;
     for (int g = 0; g < 3; ++g) {
         const GemmP& p = b.p[g];
@@ -361,7 +394,10 @@ static inline int launch(int epi, const GemmBatch& b, cudaStream_t stream) {
         q.na = TILE / p.gs;
         q.tiles = (int)cdiv(n_atoms, q.na);
         total_tiles += q.tiles;
-        if (!make_map_x(&mA[g], p.A, n_atoms, TILE, p.gs, q.na) || !make_map_w(&mW[g], p.W, TILE)) {
+        bool ok = make_map_x(&M.x[g], p.A, n_atoms, TILE, p.gs, q.na) && make_map_w(&M.w[g], p.W, TILE) &&
+                  make_map_x(&M.c[g], p.C, n_atoms, TILE, p.gs, q.na);
+        if (ok && epi == EPI_SCALE3 && p.C2) ok = make_map_x(&M.c2[g], p.C2, n_atoms, TILE, p.gs, q.na);
+        if (!ok) {
             tmdn_set_error("tc_mix: cuTensorMapEncodeTiled failed");
             return TMDN_EINVAL;
         }
@@ -381,7 +417,7 @@ static inline int launch(int epi, const GemmBatch& b, cudaStream_t stream) {
     P.n_atoms = n_atoms;
     P.epi = epi;
     P.accumulate = b.p[0].accumulate;
-    tc_mix_kernel<<<(unsigned)used, THREADS, SMEM_BYTES, stream>>>(mA[0], mA[1], mA[2], mW[0], mW[1], mW[2], P);
+    tc_mix_kernel<<<(unsigned)used, THREADS, SMEM_BYTES, stream>>>(M, P);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }
