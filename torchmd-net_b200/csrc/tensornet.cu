@@ -288,10 +288,59 @@ __global__ void tn_prod_bwd(const float* __restrict__ Y, const float* __restrict
     st9(dtauh_dY, i, H, h, dy);
 }
 
+// NB = edges whose loads are issued together (independent register sets): the kernel is bound by the latency of the
+// gathers, and the compiler does not overlap the loads of consecutive iterations on its own.
+template <bool TAB> struct FilterRaw { float4 c[3]; float s; };
+template <> struct FilterRaw<false> { float f[3], df[3]; };
+template <bool TAB>
+__device__ __forceinline__ void filter_load(const FilterView& fv, size_t e, float d, int H, int h, FilterRaw<TAB>& r) {
+    if constexpr (TAB) {
+        float s = d * fv.inv_h;
+        int k = (int)s;
+        k = k > fv.n_int - 1 ? fv.n_int - 1 : k;
+        r.s = s - (float)k;
+#pragma unroll
+        for (int g = 0; g < 3; ++g) r.c[g] = __ldg(&fv.tab[((size_t)k * 3 + g) * H + h]);
+    } else {
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+            r.f[g] = fv.F[(e * 3 + g) * H + h];
+            r.df[g] = fv.dF[(e * 3 + g) * H + h];
+        }
+    }
+}
+template <bool TAB> __device__ __forceinline__ void filter_eval_val(const FilterRaw<TAB>& r, float f[3]) {
+    if constexpr (TAB) {
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+            const float4 c = r.c[g];
+            f[g] = c.x + r.s * (c.y + r.s * (c.z + r.s * c.w));
+        }
+    } else {
+#pragma unroll
+        for (int g = 0; g < 3; ++g) f[g] = r.f[g];
+    }
+}
+template <bool TAB>
+__device__ __forceinline__ void filter_eval(const FilterView& fv, const FilterRaw<TAB>& r, float f[3], float df[3]) {
+    if constexpr (TAB) {
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+            const float4 c = r.c[g];
+            f[g] = c.x + r.s * (c.y + r.s * (c.z + r.s * c.w));
+            df[g] = (c.y + r.s * (2.0f * c.z + 3.0f * r.s * c.w)) * fv.inv_h;
+        }
+    } else {
+#pragma unroll
+        for (int g = 0; g < 3; ++g) { f[g] = r.f[g]; df[g] = r.df[g]; }
+    }
+}
+
 // ------------------------------------------------------------------ E2: interaction message passing (+ product)
 // M_c[i,h] = sum_{e in row i} f_g(c)(d_e)[h] * Y_c[j,h]  ;  tauh = normalise(decompose(M Y + Y M))   (tensornet.py:392-405)
-template <bool TAB>
-__global__ void __launch_bounds__(1024) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+constexpr int MSG_FWD_THREADS = 1024;   // 64 registers, one edge per batch: at 98k atoms this runs at 83 % of L2 throughput
+template <bool TAB, int NB = 1>
+__global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H,
                            int so3, float* __restrict__ M, float* __restrict__ tauh) {
     extern __shared__ float smem[];
@@ -304,15 +353,29 @@ __global__ void __launch_bounds__(1024) tn_msg_fwd(const int* __restrict__ row_p
     for (int c = 0; c < 9; ++c) m[c] = 0.f;
     if (valid) {
         const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        for (int e = r0 + sl; e < r1; e += S) {
-            const int j = col[e];
-            const float d = geom[e].w;
-            float f[3], y[9];
-            filter_val<TAB>(fv, (size_t)e, d, H, h, f);
-            ld9(Y, (size_t)j, H, h, y);
-            m[0] += f[0] * y[0];
-            m[1] += f[1] * y[1]; m[2] += f[1] * y[2]; m[3] += f[1] * y[3];
-            m[4] += f[2] * y[4]; m[5] += f[2] * y[5]; m[6] += f[2] * y[6]; m[7] += f[2] * y[7]; m[8] += f[2] * y[8];
+        for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
+            FilterRaw<TAB> fr[NB];
+            float y[NB][9];
+            bool on[NB];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {           // all loads of the batch first
+                const int e = e0 + b * S;
+                on[b] = e < r1;
+                const int ee = on[b] ? e : e0;
+                const int j = col[ee];
+                filter_load<TAB>(fv, (size_t)ee, geom[ee].w, H, h, fr[b]);
+                ld9(Y, (size_t)j, H, h, y[b]);
+            }
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                if (!on[b]) continue;
+                float f[3];
+                filter_eval_val<TAB>(fr[b], f);
+                m[0] += f[0] * y[b][0];
+                m[1] += f[1] * y[b][1]; m[2] += f[1] * y[b][2]; m[3] += f[1] * y[b][3];
+                m[4] += f[2] * y[b][4]; m[5] += f[2] * y[b][5]; m[6] += f[2] * y[b][6]; m[7] += f[2] * y[b][7];
+                m[8] += f[2] * y[b][8];
+            }
         }
     }
     slice_reduce<9>(m, s_part, H);
@@ -328,8 +391,9 @@ __global__ void __launch_bounds__(1024) tn_msg_fwd(const int* __restrict__ row_p
 // E3: adjoint of the message passing, evaluated in row i of the symmetric edge set:
 //   dY_i += sum_e f_e * dM_j
 //   dE/dpos_i += u_e * sum_{h,c} f'_g(c)(d_e)[h] * (dM_c[i,h] Y_c[j,h] + dM_c[j,h] Y_c[i,h])
-template <bool TAB>
-__global__ void __launch_bounds__(512) tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+constexpr int MSG_BWD_THREADS = 256;   // 128 registers: two edges' gathers (60 loads) in flight per thread
+template <bool TAB, int NB = 2>
+__global__ void __launch_bounds__(MSG_BWD_THREADS) tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
                            const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
                            int H) {
@@ -349,25 +413,40 @@ __global__ void __launch_bounds__(512) tn_msg_bwd(const int* __restrict__ row_pt
         ld9(dM, (size_t)i, H, h, dmi);
         if (sl == 0) ld9(dY, (size_t)i, H, h, acc);
         const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        for (int e = r0 + sl; e < r1; e += S) {
-            const int j = col[e];
-            const float4 g = geom[e];
-            float f[3], df[3], yj[9], dmj[9];
-            filter_val_grad<TAB>(fv, (size_t)e, g.w, H, h, f, df);
-            ld9(Y, (size_t)j, H, h, yj);
-            ld9(dM, (size_t)j, H, h, dmj);
-            acc[0] += f[0] * dmj[0];
-            acc[1] += f[1] * dmj[1]; acc[2] += f[1] * dmj[2]; acc[3] += f[1] * dmj[3];
-            acc[4] += f[2] * dmj[4]; acc[5] += f[2] * dmj[5]; acc[6] += f[2] * dmj[6];
-            acc[7] += f[2] * dmj[7]; acc[8] += f[2] * dmj[8];
-            const float s0 = dmi[0] * yj[0] + dmj[0] * yi[0];
-            float s1 = 0.f, s2 = 0.f;
+        for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
+            float4 g[NB];
+            FilterRaw<TAB> fr[NB];
+            float yj[NB][9], dmj[NB][9];
+            bool on[NB];
 #pragma unroll
-            for (int c = 1; c < 4; ++c) s1 += dmi[c] * yj[c] + dmj[c] * yi[c];
+            for (int b = 0; b < NB; ++b) {           // all loads of the batch first
+                const int e = e0 + b * S;
+                on[b] = e < r1;
+                const int ee = on[b] ? e : e0;
+                const int j = col[ee];
+                g[b] = geom[ee];
+                filter_load<TAB>(fv, (size_t)ee, g[b].w, H, h, fr[b]);
+                ld9(Y, (size_t)j, H, h, yj[b]);
+                ld9(dM, (size_t)j, H, h, dmj[b]);
+            }
 #pragma unroll
-            for (int c = 4; c < 9; ++c) s2 += dmi[c] * yj[c] + dmj[c] * yi[c];
-            const float ge = df[0] * s0 + df[1] * s1 + df[2] * s2;
-            gp[0] += g.x * ge; gp[1] += g.y * ge; gp[2] += g.z * ge;
+            for (int b = 0; b < NB; ++b) {           // then the sums, in edge order
+                if (!on[b]) continue;
+                float f[3], df[3];
+                filter_eval<TAB>(fv, fr[b], f, df);
+                acc[0] += f[0] * dmj[b][0];
+                acc[1] += f[1] * dmj[b][1]; acc[2] += f[1] * dmj[b][2]; acc[3] += f[1] * dmj[b][3];
+                acc[4] += f[2] * dmj[b][4]; acc[5] += f[2] * dmj[b][5]; acc[6] += f[2] * dmj[b][6];
+                acc[7] += f[2] * dmj[b][7]; acc[8] += f[2] * dmj[b][8];
+                const float s0 = dmi[0] * yj[b][0] + dmj[b][0] * yi[0];
+                float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+                for (int c = 1; c < 4; ++c) s1 += dmi[c] * yj[b][c] + dmj[b][c] * yi[c];
+#pragma unroll
+                for (int c = 4; c < 9; ++c) s2 += dmi[c] * yj[b][c] + dmj[b][c] * yi[c];
+                const float ge = df[0] * s0 + df[1] * s1 + df[2] * s2;
+                gp[0] += g[b].x * ge; gp[1] += g[b].y * ge; gp[2] += g[b].z * ge;
+            }
         }
     }
     slice_reduce<9>(acc, s_part, H);
@@ -913,8 +992,10 @@ struct TnRun {
         const float4* geom = (const float4*)w.geom;
         const int apb = H >= 128 ? 1 : 128 / H;
         const dim3 rblock(H, apb);
-        const EdgeLaunch el = edge_launch(N, H, 1024);    // forward edge kernels: <= 64 registers/thread
-        const EdgeLaunch elb = edge_launch(N, H, 512);    // backward edge kernels: <= 128 registers/thread
+        const EdgeLaunch el = edge_launch(N, H, 1024);    // embedding edge kernels: <= 64 registers/thread
+        const EdgeLaunch elb = edge_launch(N, H, 512);
+        const EdgeLaunch elf2 = edge_launch(N, H, MSG_FWD_THREADS);
+        const EdgeLaunch elb2 = edge_launch(N, H, MSG_BWD_THREADS);   // two edges in flight per thread
         const unsigned rgrid = (unsigned)cdiv(N, apb);
         const long long NH = (long long)N * H;
         const unsigned egrid = (unsigned)cdiv(NH, 256);
@@ -984,10 +1065,10 @@ struct TnRun {
             {
                 KTimer ktimer__("tn_msg_fwd", stream);
                 if (tab)
-                    tn_msg_fwd<true><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
+                    tn_msg_fwd<true><<<elf2.grid, elf2.block, elf2.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
                                                                              H, m->so3, w.M[l], w.tauh);
                 else
-                    tn_msg_fwd<false><<<el.grid, el.block, el.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
+                    tn_msg_fwd<false><<<elf2.grid, elf2.block, elf2.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
                                                                               H, m->so3, w.M[l], w.tauh);
                 TMDN_LAUNCH_CHECK();
             }
@@ -1053,10 +1134,10 @@ struct TnRun {
             {
                 KTimer ktimer__("tn_msg_bwd", stream);
                 if (tab)
-                    tn_msg_bwd<true><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
+                    tn_msg_bwd<true><<<elb2.grid, elb2.block, elb2.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
                                                                                 w.dB, w.dC, w.gpos, N, H);
                 else
-                    tn_msg_bwd<false><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
+                    tn_msg_bwd<false><<<elb2.grid, elb2.block, elb2.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
                                                                                  w.dB, w.dC, w.gpos, N, H);
                 TMDN_LAUNCH_CHECK();
             }
