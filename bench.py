@@ -189,6 +189,23 @@ def algorithmic_bytes(family, N, E, H, L):
     return table.get(family, 2 * node)
 
 
+def l2_bytes(family, E, H):
+    """Bytes one launch moves L2 -> SM through its gathers: table row + neighbour rows per edge-channel."""
+    per = {"tn_msg_fwd": 84, "tn_msg_bwd": 120, "tn_embed_edge_fwd": 48, "tn_embed_edge_bwd": 48,
+           "et_edge_fwd": 92, "et_edge_bwd": 112}
+    return per.get(family, 0) * H * E
+
+
+def ncu_capture(workload, family):
+    """dram bytes / L2 throughput of `family` from the committed ncu full capture of this workload, if there is one
+    (profiles/ncu_traffic.json, written from `ncu --set full` reports by profiles/summarize.py traffic)."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(path):
+        return None
+    with open(path) as fh:
+        return json.load(fh).get(workload, {}).get(family)
+
+
 def profile_families(run_step, steps):
     torch.ops.torchmdnet_b200.profile_enable(True)
     for i in range(steps):
@@ -470,11 +487,16 @@ def main():
             peak, peak_src = float(json.load(fh)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
     else:
         peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+    cap = ncu_capture("%s:%d" % (args.workload, N), dom)
+    l2b = l2_bytes(dom, E, H)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": cap["dram_bytes"] if cap else None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_us": ms / cnt * 1e3,
                 "share_of_step": ms / n_prof / step_ms_prof,
-                "note": "time of the kernel = CUDA events inside the library over %d eager steps" % n_prof}
+                "l2_bytes_per_launch": l2b, "l2_achieved_gbs": l2b / (ms / cnt * 1e-3) / 1e9,
+                "ncu": cap,
+                "note": "time of the kernel = CUDA events inside the library over %d eager steps; the gathers of this "
+                        "kernel are served by L2 (DESIGN.md 4.3), l2_* is the traffic that bounds it" % n_prof}
     families = {k: {"launches_per_step": c / n_prof, "us_per_step": m / n_prof * 1e3} for k, (c, m) in
                 sorted(fam.items(), key=lambda kv: -kv[1][1])}
 

@@ -25,19 +25,32 @@ struct Tab {
     float inv_h;
     int n_int;
 };
-// NF filters per interval: value and d/dd from the same cubic
+// NF filters per interval: value and d/dd from the same cubic.  Split into the loads (tab_load) and the arithmetic
+// (tab_poly) so that an edge kernel can put the loads of several edges in flight before it starts to compute.
+template <int NF> struct TabRow { float4 c[NF]; float s; };
 template <int NF>
-__device__ __forceinline__ void tab_eval(const Tab& tb, float d, int H, int h, float (&f)[NF], float (&df)[NF]) {
+__device__ __forceinline__ void tab_load(const Tab& tb, float d, int H, int h, TabRow<NF>& r) {
     float s = d * tb.inv_h;
     int k = (int)s;
     k = k > tb.n_int - 1 ? tb.n_int - 1 : k;
-    s -= (float)k;
+    r.s = s - (float)k;
+#pragma unroll
+    for (int g = 0; g < NF; ++g) r.c[g] = __ldg(&tb.t[((size_t)k * NF + g) * H + h]);
+}
+template <int NF>
+__device__ __forceinline__ void tab_poly(const Tab& tb, const TabRow<NF>& r, float (&f)[NF], float (&df)[NF]) {
 #pragma unroll
     for (int g = 0; g < NF; ++g) {
-        const float4 c = __ldg(&tb.t[((size_t)k * NF + g) * H + h]);
-        f[g] = c.x + s * (c.y + s * (c.z + s * c.w));
-        df[g] = (c.y + s * (2.0f * c.z + 3.0f * s * c.w)) * tb.inv_h;
+        const float4 c = r.c[g];
+        f[g] = c.x + r.s * (c.y + r.s * (c.z + r.s * c.w));
+        df[g] = (c.y + r.s * (2.0f * c.z + 3.0f * r.s * c.w)) * tb.inv_h;
     }
+}
+template <int NF>
+__device__ __forceinline__ void tab_eval(const Tab& tb, float d, int H, int h, float (&f)[NF], float (&df)[NF]) {
+    TabRow<NF> r;
+    tab_load<NF>(tb, d, H, h, r);
+    tab_poly<NF>(tb, r, f, df);
 }
 // sum over the hd consecutive lanes of a head (hd power of two <= 32); result in every lane of the segment
 __device__ __forceinline__ float seg_sum(float v, int hd) {
@@ -134,7 +147,9 @@ __global__ void et_ln_bwd(const float* __restrict__ x, const float* __restrict__
 // ------------------------------------------------------------------ attention edge kernel (torchmd_et.py:314-347)
 // xa[i] = sum_e v0_j dv0 * attn_e ;  va[i] = sum_e vec_j (v1_j dv1) + (v2_j dv2) dhat_e,  dhat = -u
 // attn_e(head) = attn_act(sum_{c in head} q_i k_j dk) * C(d_e)
-__global__ void __launch_bounds__(1024)
+constexpr int ET_FWD_THREADS = 512, ET_BWD_THREADS = 256;   // register budgets for two edges in flight per thread
+template <int NB = 2>
+__global__ void __launch_bounds__(ET_FWD_THREADS)
 et_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
             float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
             int N, int H, float* __restrict__ xa, float* __restrict__ va) {
@@ -148,22 +163,38 @@ et_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
     if (valid) {
         const float qi = qkv[(size_t)i * H5 + h];
         const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        for (int e = r0 + sl; e < r1; e += S) {
-            const int j = col[e];
-            const float4 g = geom[e];
-            float f[4], df[4], c, dc;
-            tab_eval<4>(tb, g.w, H, h, f, df);
-            cutoff_fn(g.w, lo, hi, c, dc);
-            const float* pj = qkv + (size_t)j * H5 + h;
-            const float kj = pj[H], v0 = pj[2 * H], v1 = pj[3 * H], v2 = pj[4 * H];
-            const float* vj = vec + (size_t)j * 3 * H + h;
-            const float s = seg_sum(qi * kj * f[0], hd);
-            const float attn = act_apply(attn_act, s) * c;
-            acc[0] += v0 * f[1] * attn;
-            const float a1 = v1 * f[2], a2 = v2 * f[3];
-            acc[1] += vj[0] * a1 - a2 * g.x;
-            acc[2] += vj[H] * a1 - a2 * g.y;
-            acc[3] += vj[2 * H] * a1 - a2 * g.z;
+        for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
+            float4 g[NB];
+            TabRow<4> tr[NB];
+            float kj[NB], v0[NB], v1[NB], v2[NB], vx[NB], vy[NB], vz[NB];
+            bool on[NB];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {           // all loads of the batch first (warp-uniform predicate)
+                const int e = e0 + b * S;
+                on[b] = e < r1;
+                const int ee = on[b] ? e : e0;
+                const int j = col[ee];
+                g[b] = geom[ee];
+                tab_load<4>(tb, g[b].w, H, h, tr[b]);
+                const float* pj = qkv + (size_t)j * H5 + h;
+                kj[b] = pj[H]; v0[b] = pj[2 * H]; v1[b] = pj[3 * H]; v2[b] = pj[4 * H];
+                const float* vj = vec + (size_t)j * 3 * H + h;
+                vx[b] = vj[0]; vy[b] = vj[H]; vz[b] = vj[2 * H];
+            }
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                if (!on[b]) continue;
+                float f[4], df[4], c, dc;
+                tab_poly<4>(tb, tr[b], f, df);
+                cutoff_fn(g[b].w, lo, hi, c, dc);
+                const float s = seg_sum(qi * kj[b] * f[0], hd);
+                const float attn = act_apply(attn_act, s) * c;
+                acc[0] += v0[b] * f[1] * attn;
+                const float a1 = v1[b] * f[2], a2 = v2[b] * f[3];
+                acc[1] += vx[b] * a1 - a2 * g[b].x;
+                acc[2] += vy[b] * a1 - a2 * g[b].y;
+                acc[3] += vz[b] * a1 - a2 * g[b].z;
+            }
         }
     }
     slice_reduce<4>(acc, s_part, H);
@@ -324,7 +355,8 @@ __global__ void et_update_bwd(const float* __restrict__ g_x, const float* __rest
 // Adjoint of et_edge_fwd evaluated in row i for both directions of every entry (i, j):
 //   A: edge (i <- j): g_q_i, and -G_A on pos_i          B: reverse edge (j <- i): g_k_i, g_v_i, g_vec_i, +G_B on pos_i
 //   G = g_d dhat + (g_dhat - (g_dhat.dhat) dhat)/d  is linear in (g_d, g_dhat), so every channel accumulates its share
-__global__ void __launch_bounds__(512)
+template <int NB = 2>
+__global__ void __launch_bounds__(ET_BWD_THREADS)
 et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
             float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
             const float* __restrict__ g_xa, const float* __restrict__ g_va, int N, int H, float* __restrict__ g_qkv,
@@ -350,20 +382,43 @@ et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
         const float* gvi = g_va + (size_t)i * 3 * H + h;
         const float gvix = gvi[0], gviy = gvi[H], gviz = gvi[2 * H];
         const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        for (int e = r0 + sl; e < r1; e += S) {
-            const int j = col[e];
-            const float4 g = geom[e];
+        for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
+            int jj[NB];
+            float4 gg[NB];
+            TabRow<4> tr[NB];
+            float L[NB][12];                         // q k v0 v1 v2 | vec xyz | g_xa | g_va xyz of atom j
+            bool on[NB];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {           // all loads of the batch first (warp-uniform predicate)
+                const int e = e0 + b * S;
+                on[b] = e < r1;
+                const int ee = on[b] ? e : e0;
+                const int j = col[ee];
+                jj[b] = j;
+                gg[b] = geom[ee];
+                tab_load<4>(tb, gg[b].w, H, h, tr[b]);
+                const float* pj = qkv + (size_t)j * H5 + h;
+#pragma unroll
+                for (int q = 0; q < 5; ++q) L[b][q] = pj[q * H];
+                const float* vcj = vec + (size_t)j * 3 * H + h;
+                L[b][5] = vcj[0]; L[b][6] = vcj[H]; L[b][7] = vcj[2 * H];
+                L[b][8] = g_xa[(size_t)j * H + h];
+                const float* gvj = g_va + (size_t)j * 3 * H + h;
+                L[b][9] = gvj[0]; L[b][10] = gvj[H]; L[b][11] = gvj[2 * H];
+            }
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+            if (!on[b]) continue;
+            const int j = jj[b];
+            const float4 g = gg[b];
             const float hx = -g.x, hy = -g.y, hz = -g.z;   // dhat of direction A; direction B uses +u
             float f[4], df[4], c, dc;
-            tab_eval<4>(tb, g.w, H, h, f, df);
+            tab_poly<4>(tb, tr[b], f, df);
             cutoff_fn(g.w, lo, hi, c, dc);
-            const float* pj = qkv + (size_t)j * H5 + h;
-            const float qj = pj[0], kj = pj[H], vj0 = pj[2 * H], vj1 = pj[3 * H], vj2 = pj[4 * H];
-            const float* vcj = vec + (size_t)j * 3 * H + h;
-            const float vjx = vcj[0], vjy = vcj[H], vjz = vcj[2 * H];
-            const float gxj = g_xa[(size_t)j * H + h];
-            const float* gvj = g_va + (size_t)j * 3 * H + h;
-            const float gvjx = gvj[0], gvjy = gvj[H], gvjz = gvj[2 * H];
+            const float qj = L[b][0], kj = L[b][1], vj0 = L[b][2], vj1 = L[b][3], vj2 = L[b][4];
+            const float vjx = L[b][5], vjy = L[b][6], vjz = L[b][7];
+            const float gxj = L[b][8];
+            const float gvjx = L[b][9], gvjy = L[b][10], gvjz = L[b][11];
             // ---- A
             const float sA = seg_sum(qi * kj * f[0], hd);
             const float aA = act_apply(attn_act, sA), attnA = aA * c;
@@ -401,6 +456,7 @@ et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
                 gp[0] += -(gdA * hx + (ghxA - dotA * hx) * inv_d) + (gdB * g.x + (ghxB - dotB * g.x) * inv_d);
                 gp[1] += -(gdA * hy + (ghyA - dotA * hy) * inv_d) + (gdB * g.y + (ghyB - dotB * g.y) * inv_d);
                 gp[2] += -(gdA * hz + (ghzA - dotA * hz) * inv_d) + (gdB * g.z + (ghzB - dotB * g.z) * inv_d);
+            }
             }
         }
     }
@@ -625,7 +681,8 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     const float4* geom = (const float4*)w.geom;
     const float inv_h = (float)((double)m->n_int / (double)hi);
     const Tab ne_tab{(const float4*)m->ne_table, inv_h, m->n_int};
-    const EdgeLaunch e1 = edge_launch(N, H, 1024, 1), e4 = edge_launch(N, H, 1024, 4), e8 = edge_launch(N, H, 512, 8);
+    const EdgeLaunch e1 = edge_launch(N, H, 1024, 1), e4 = edge_launch(N, H, ET_FWD_THREADS, 4), e8 = edge_launch(N, H, 512, 8);
+    const EdgeLaunch e8b = edge_launch(N, H, ET_BWD_THREADS, 8);
     const int apb = H >= 128 ? 1 : 128 / H;
     const dim3 lblock(H, 1, apb);
     const unsigned lgrid = (unsigned)cdiv(N, apb);
@@ -650,7 +707,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
         ET_K("et_ln_fwd", et_ln_fwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, ly.ln_b, w.xl, H, w.stat[l], N, H));
         TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.xl, H, ly.qkv_w, ly.qkv_b, w.QKV[l], 5 * H, N, 5 * H, H), stream));
         TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.VEC[l], H, ly.vp_w, nullptr, w.VP[l], 3 * H, 3 * N, 3 * H, H), stream));
-        ET_K("et_edge_fwd", et_edge_fwd<<<e4.grid, e4.block, e4.smem, stream>>>(
+        ET_K("et_edge_fwd", et_edge_fwd<2><<<e4.grid, e4.block, e4.smem, stream>>>(
                                 w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], N, H, w.xa,
                                 w.va));
         TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.xa, H, ly.o_w, ly.o_b, w.O[l], 3 * H, N, 3 * H, H), stream));
@@ -727,7 +784,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
             p.accumulate = 1;
             TMDN_TRY(gemm1(EPI_NONE, p, stream));
         }
-        ET_K("et_edge_bwd", et_edge_bwd<<<e8.grid, e8.block, e8.smem, stream>>>(
+        ET_K("et_edge_bwd", et_edge_bwd<2><<<e8b.grid, e8b.block, e8b.smem, stream>>>(
                                 w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], w.g_xa,
                                 g_vec, N, H, w.g_qkv, g_vec_new, w.gpos));
         TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_qkv, 5 * H, ly.qkv_wT, nullptr, w.g_xl, H, N, H, 5 * H), stream));
