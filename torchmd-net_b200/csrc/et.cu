@@ -147,8 +147,10 @@ __global__ void et_ln_bwd(const float* __restrict__ x, const float* __restrict__
 // ------------------------------------------------------------------ attention edge kernel (torchmd_et.py:314-347)
 // xa[i] = sum_e v0_j dv0 * attn_e ;  va[i] = sum_e vec_j (v1_j dv1) + (v2_j dv2) dhat_e,  dhat = -u
 // attn_e(head) = attn_act(sum_{c in head} q_i k_j dk) * C(d_e)
-constexpr int ET_FWD_THREADS = 512, ET_BWD_THREADS = 256;   // register budgets for two edges in flight per thread
-template <int NB = 2>
+// NB = edges whose loads are issued together.  Unlike the TensorNet messages these kernels are bound by arithmetic
+// (segmented shuffles, activation, cutoff), so occupancy wins: NB = 1 (measured: NB = 2 at 128 registers is 40 % slower).
+constexpr int ET_FWD_THREADS = 1024, ET_BWD_THREADS = 512;
+template <int NB = 1>
 __global__ void __launch_bounds__(ET_FWD_THREADS)
 et_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
             float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
@@ -355,8 +357,8 @@ __global__ void et_update_bwd(const float* __restrict__ g_x, const float* __rest
 // Adjoint of et_edge_fwd evaluated in row i for both directions of every entry (i, j):
 //   A: edge (i <- j): g_q_i, and -G_A on pos_i          B: reverse edge (j <- i): g_k_i, g_v_i, g_vec_i, +G_B on pos_i
 //   G = g_d dhat + (g_dhat - (g_dhat.dhat) dhat)/d  is linear in (g_d, g_dhat), so every channel accumulates its share
-template <int NB = 2>
-__global__ void __launch_bounds__(ET_BWD_THREADS)
+template <int NB = 1>
+__global__ void __launch_bounds__(ET_BWD_THREADS, 2)
 et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
             float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
             const float* __restrict__ g_xa, const float* __restrict__ g_va, int N, int H, float* __restrict__ g_qkv,
@@ -707,7 +709,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
         ET_K("et_ln_fwd", et_ln_fwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, ly.ln_b, w.xl, H, w.stat[l], N, H));
         TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.xl, H, ly.qkv_w, ly.qkv_b, w.QKV[l], 5 * H, N, 5 * H, H), stream));
         TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.VEC[l], H, ly.vp_w, nullptr, w.VP[l], 3 * H, 3 * N, 3 * H, H), stream));
-        ET_K("et_edge_fwd", et_edge_fwd<2><<<e4.grid, e4.block, e4.smem, stream>>>(
+        ET_K("et_edge_fwd", et_edge_fwd<1><<<e4.grid, e4.block, e4.smem, stream>>>(
                                 w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], N, H, w.xa,
                                 w.va));
         TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.xa, H, ly.o_w, ly.o_b, w.O[l], 3 * H, N, 3 * H, H), stream));
@@ -784,7 +786,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
             p.accumulate = 1;
             TMDN_TRY(gemm1(EPI_NONE, p, stream));
         }
-        ET_K("et_edge_bwd", et_edge_bwd<2><<<e8b.grid, e8b.block, e8b.smem, stream>>>(
+        ET_K("et_edge_bwd", et_edge_bwd<1><<<e8b.grid, e8b.block, e8b.smem, stream>>>(
                                 w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], w.g_xa,
                                 g_vec, N, H, w.g_qkv, g_vec_new, w.gpos));
         TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_qkv, 5 * H, ly.qkv_wT, nullptr, w.g_xl, H, N, H, 5 * H), stream));
