@@ -206,6 +206,11 @@ int tmdn_halo_pack_f32(const float* src, const int32_t* idx, int64_t n_rows, int
  * other widths on the fp32 FFMA kernel.  This is the operator the model path calls for every mix; exported for tests. */
 int tmdn_channel_mix_f32(const float* x, const float* w, float* y, int64_t n_atoms, int H, int accumulate,
                          tmdn_stream_t stream);
+/* Plain node GEMM of the path (embedding / output / head MLPs of TensorNet, every ET projection):
+ *   c[M,N] (+)= a[M,K] * w[N,K]^T + bias[N] (bias may be null).  M, N, K multiples of 4 run on the tcgen05 tensor cores
+ * with the three-product tf32 split (fp32-level accuracy), anything else on the fp32 FFMA kernel.  Exported for tests. */
+int tmdn_node_gemm_f32(const float* a, const float* w, const float* bias, float* c, int64_t M, int64_t N, int64_t K,
+                       int accumulate, tmdn_stream_t stream);
 /* Debug/inspection: byte offset and size of a named intermediate inside the workspace (names as in
  * oracle/staged_tensornet.py: "row_ptr","col","geom","ias","nh","fias","X0","Y0","M0","tauh0","X1",...,"e_atom","Dias","gpos"). */
 int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_atoms, int64_t max_edges,
@@ -239,9 +244,14 @@ typedef struct tmdn_et_gated {              /* GatedEquivariantBlock: hin -> out
     const float *u2_w, *u2_b, *u2_wT;       /* update_net.2 [2out,hin], [2out], [hin,2out] */
 } tmdn_et_gated;
 
+/* Precision of the ET projections.  TF32X3 = tcgen05 with the three-product tf32 split: rms error 1.3-2.8e-7 of
+ * sum|a w| per GEMM (fp32 FFMA: 2.8e-8); through the 6-8 layer ET it moves energies by up to ~1e-5 relative, so it is
+ * opt-in and held to 3e-5 relative in the tests; the default keeps the 1e-5 bar. */
+enum { TMDN_GEMM_FP32 = 0, TMDN_GEMM_TF32X3 = 1 };
 typedef struct tmdn_et_model {
     int32_t hidden, num_layers, num_heads, max_z;
     int32_t activation, attn_activation, has_neighbor_embedding, n_int;
+    int32_t gemm_mode;                      /* TMDN_GEMM_FP32 (default, exact fp32 FFMA) | TMDN_GEMM_TF32X3 (tensor cores) */
     float cutoff_lower, cutoff_upper, mean, std;
     const float* emb;                       /* embedding [max_z,H] */
     const float *ne_emb, *ne_table;         /* neighbor_embedding.embedding [max_z,H], filter table */

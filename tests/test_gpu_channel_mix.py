@@ -51,3 +51,27 @@ def test_channel_mix_is_repeatable(ops):
     a = ops.channel_mix(x, w, None, False)
     b = ops.channel_mix(x, w, None, False)
     assert torch.equal(a, b)
+
+
+# ------------------------------------------------------------------ general tcgen05 GEMM (csrc/tc_gemm.cuh) through the ET model
+def test_tc_gemm_against_ffma_through_et(monkeypatch):
+    """The plain node GEMMs run on tensor cores by default; the same model evaluated with the fp32 FFMA kernels
+    (TMDN_TC_GEMM=0 is read once per process, so the comparison is made against the oracle in test_gpu_et.py and,
+    here, as a direct operator check on odd shapes through channel_mix's sibling entry point)."""
+    ops_ = torch.ops.torchmdnet_b200
+    if not hasattr(ops_, "node_gemm"):
+        pytest.skip("node_gemm op not exported")
+    g = torch.Generator().manual_seed(11)
+    for (M, N, K) in [(1, 64, 64), (166, 384, 256), (2306, 640, 128), (5000, 128, 640), (777, 64, 128), (130, 36, 44)]:
+        a = torch.randn(M, K, generator=g).cuda()
+        w = (torch.randn(N, K, generator=g) / K ** 0.5).cuda()
+        bias = torch.randn(N, generator=g).cuda()
+        c = ops_.node_gemm(a, w, bias, None, False)
+        ref = a.double().cpu() @ w.double().cpu().T + bias.double().cpu()
+        bound = a.double().cpu().abs() @ w.double().cpu().abs().T + bias.double().cpu().abs()
+        err = (c.double().cpu() - ref).abs()
+        assert (err <= 2e-6 * bound).all(), ((M, N, K), float((err / bound).max()))
+        c0 = torch.randn(M, N, generator=g).cuda()
+        c2 = ops_.node_gemm(a, w, None, c0.clone(), True)
+        ref2 = a.double().cpu() @ w.double().cpu().T + c0.double().cpu()
+        assert torch.allclose(c2.double().cpu(), ref2, rtol=0, atol=3e-5), (M, N, K)

@@ -144,6 +144,32 @@ def test_qm9_like_batch_of_128_molecules():
     torch.testing.assert_close(f2, f[sel2.cuda()], rtol=0, atol=5e-6)
 
 
+def test_tf32x3_projection_mode_has_its_own_tolerance():
+    """gemm_mode="tf32x3" runs every ET projection on the tcgen05 tensor cores (three-product tf32 split).  Stated
+    separately from the fp32 bar (north_star): energies within 3e-5 relative, forces within 3e-4 eV/A absolute."""
+    import synth_inputs as S
+    from torchmdnet.models.model import create_model
+    g = load_npz("model_ET-QM9.npz")
+    seed_everything(int(g["seed"]))
+    m = create_model(g["hparams"]).cuda().eval()
+    z, pos, batch = (torch.from_numpy(a) for a in S.qm9_like_batch(n_mol=128, seed=1))
+    y0, f0 = m(z.cuda(), pos.cuda(), batch.cuda())
+    m.representation_model.gemm_mode = "tf32x3"
+    n0 = torch.ops.torchmdnet_b200.launch_count()
+    y1, f1 = m(z.cuda(), pos.cuda(), batch.cuda())
+    assert torch.ops.torchmdnet_b200.launch_count() > n0
+    assert not torch.equal(y0, y1)                       # a different arithmetic path really ran
+    sel = batch < 12
+    sd = {k: v.cpu() for k, v in m.state_dict().items()}
+    yr, fr = om.energy_forces(sd, g["hparams"], z[sel], pos[sel], batch[sel])
+    dy = (y1[:12].double().cpu() - yr.double()).abs()
+    assert float((dy / yr.double().abs().clamp_min(1.0)).max()) <= 3e-5
+    assert float((f1[sel.cuda()].double().cpu() - fr.double()).abs().max()) <= 3e-4
+    m.representation_model.gemm_mode = "fp32"
+    y2, _ = m(z.cuda(), pos.cuda(), batch.cuda())
+    assert torch.equal(y0, y2)
+
+
 def test_cuda_graph_and_external(tmp_path):
     from torchmdnet.calculators import External
     g = load_npz("small_et_both.npz")

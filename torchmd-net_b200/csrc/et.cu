@@ -13,6 +13,7 @@
 // The per-edge [E,H], [E,3H], [E,3,H] message tensors of the reference never exist.
 #include "common.cuh"
 #include "gemm.cuh"
+#include "node_gemm.cuh"
 #include "edge_common.cuh"
 #include "scan.cuh"
 #include <string>
@@ -662,6 +663,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     TMDN_CHECK_ARG(max_edges < (1LL << 31) && n_atoms < (1LL << 31) / 16, "et: sizes exceed int32 indexing");
     TMDN_CHECK_ARG(strategy != TMDN_CELL || box, "et: the cell strategy needs a box");
     const int N = (int)n_atoms, H = m->hidden, L = m->num_layers, act = m->activation, H2 = H / 2;
+    const bool tc = m->gemm_mode == TMDN_GEMM_TF32X3;
     const int hd = H / m->num_heads;
     const int64_t P = max_edges;
     const float lo = m->cutoff_lower, hi = m->cutoff_upper;
@@ -696,7 +698,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     if (m->has_neighbor_embedding) {
         ET_K("et_embed_fwd", et_embed_fwd<true><<<e1.grid, e1.block, e1.smem, stream>>>(
                                  w.row_ptr, w.col, geom, w.z32, m->emb, m->ne_emb, ne_tab, N, H, w.cat0, 2 * H));
-        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.cat0, 2 * H, m->ne_comb_w, m->ne_comb_b, w.X[0], H, N, H, 2 * H), stream));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.cat0, 2 * H, m->ne_comb_w, m->ne_comb_b, w.X[0], H, N, H, 2 * H), stream, tc));
     } else {
         ET_K("et_embed_fwd", et_embed_fwd<false><<<e1.grid, e1.block, e1.smem, stream>>>(
                                  w.row_ptr, w.col, geom, w.z32, m->emb, nullptr, ne_tab, N, H, w.X[0], H));
@@ -707,12 +709,12 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
         const tmdn_et_layer& ly = m->layer[l];
         const Tab tb{(const float4*)ly.table, inv_h, m->n_int};
         ET_K("et_ln_fwd", et_ln_fwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, ly.ln_b, w.xl, H, w.stat[l], N, H));
-        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.xl, H, ly.qkv_w, ly.qkv_b, w.QKV[l], 5 * H, N, 5 * H, H), stream));
-        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.VEC[l], H, ly.vp_w, nullptr, w.VP[l], 3 * H, 3 * N, 3 * H, H), stream));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.xl, H, ly.qkv_w, ly.qkv_b, w.QKV[l], 5 * H, N, 5 * H, H), stream, tc));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.VEC[l], H, ly.vp_w, nullptr, w.VP[l], 3 * H, 3 * N, 3 * H, H), stream, tc));
         ET_K("et_edge_fwd", et_edge_fwd<1><<<e4.grid, e4.block, e4.smem, stream>>>(
                                 w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], N, H, w.xa,
                                 w.va));
-        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.xa, H, ly.o_w, ly.o_b, w.O[l], 3 * H, N, 3 * H, H), stream));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.xa, H, ly.o_w, ly.o_b, w.O[l], 3 * H, N, 3 * H, H), stream, tc));
         ET_K("et_update_fwd", et_update_fwd<<<egrid, 256, 0, stream>>>(w.X[l], w.VEC[l], w.VP[l], w.O[l], w.va,
                                                                        w.X[l + 1], w.VEC[l + 1], NH, H));
     }
@@ -722,24 +724,24 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     // ---- gated block 1: H -> H/2 (scalar activation)
     const tmdn_et_gated& g1 = m->head[0];
     const tmdn_et_gated& g2 = m->head[1];
-    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.VEC[L], H, g1.w1, nullptr, w.vb1, H, 3 * N, H, H), stream));
-    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.VEC[L], H, g1.w2, nullptr, w.vec2_1, H2, 3 * N, H2, H), stream));
+    TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.VEC[L], H, g1.w1, nullptr, w.vb1, H, 3 * N, H, H), stream, tc));
+    TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.VEC[L], H, g1.w2, nullptr, w.vec2_1, H2, 3 * N, H2, H), stream, tc));
     ET_K("et_gate_norm_fwd", et_gate_norm_fwd<<<egrid, 256, 0, stream>>>(w.vb1, w.cat1, NH, H));
     {
         GemmP p = gemm_desc(w.cat1, 2 * H, g1.u0_w, g1.u0_b, w.a0_1, H, N, H, 2 * H);
         p.C2 = w.h0_1; p.act = act;
-        TMDN_TRY(gemm1(EPI_ACT, p, stream));
-        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.a0_1, H, g1.u2_w, g1.u2_b, w.h2_1, H, N, H, H), stream));
+        TMDN_TRY(node_gemm1(EPI_ACT, p, stream, tc));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.a0_1, H, g1.u2_w, g1.u2_b, w.h2_1, H, N, H, H), stream, tc));
     }
     ET_K("et_gate_out_fwd", et_gate_out_fwd<<<hgrid, 256, 0, stream>>>(w.h2_1, w.vec2_1, act, w.cat2, H, w.v1,
                                                                        (long long)N * H2, H2));
     // ---- gated block 2: H/2 -> 1 (its vector output does not reach the energy)
-    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.v1, H2, g2.w1, nullptr, w.vb2, H2, 3 * N, H2, H2), stream));
+    TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.v1, H2, g2.w1, nullptr, w.vb2, H2, 3 * N, H2, H2), stream, tc));
     ET_K("et_gate_norm_fwd", et_gate_norm_fwd<<<hgrid, 256, 0, stream>>>(w.vb2, w.cat2, (long long)N * H2, H2));
     {
         GemmP p = gemm_desc(w.cat2, H, g2.u0_w, g2.u0_b, w.a0_2, H2, N, H2, H);
         p.C2 = w.h0_2; p.act = act;
-        TMDN_TRY(gemm1(EPI_ACT, p, stream));
+        TMDN_TRY(node_gemm1(EPI_ACT, p, stream, tc));
     }
     ET_K("et_head_energy", et_head_energy<<<(unsigned)cdiv(N, 4), 128, 0, stream>>>(w.a0_2, g2.u2_w, g2.u2_b, m->std,
                                                                                    w.e_atom, N, H2));
@@ -751,27 +753,27 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     // block 2
     ET_K("et_head_seed_bwd", et_head_seed_bwd<<<hgrid, 256, 0, stream>>>(w.h0_2, g2.u2_w, m->std, act, w.d_a0_2,
                                                                          (long long)N * H2, H2));
-    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.d_a0_2, H2, g2.u0_wT, nullptr, w.g_cat2, H, N, H, H2), stream));
+    TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.d_a0_2, H2, g2.u0_wT, nullptr, w.g_cat2, H, N, H, H2), stream, tc));
     ET_K("et_gate_norm_bwd", et_gate_norm_bwd<<<hgrid, 256, 0, stream>>>(w.vb2, w.cat2, w.g_cat2, w.g_vb2,
                                                                          (long long)N * H2, H2));
-    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_vb2, H2, g2.w1T, nullptr, w.g_v1, H2, 3 * N, H2, H2), stream));
+    TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_vb2, H2, g2.w1T, nullptr, w.g_v1, H2, 3 * N, H2, H2), stream, tc));
     // block 1
     ET_K("et_gate_out_bwd", et_gate_out_bwd<<<hgrid, 256, 0, stream>>>(w.h2_1, w.vec2_1, act, w.g_cat2, H, w.g_v1, w.g_h2,
                                                                        w.g_vec2, (long long)N * H2, H2));
     {
         GemmP p = gemm_desc(w.g_h2, H, g1.u2_wT, nullptr, w.g_h0, H, N, H, H);
         p.aux = w.h0_1; p.ldaux = H; p.act = act;
-        TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
-        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_h0, H, g1.u0_wT, nullptr, w.g_cat1, 2 * H, N, 2 * H, H), stream));
+        TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream, tc));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_h0, H, g1.u0_wT, nullptr, w.g_cat1, 2 * H, N, 2 * H, H), stream, tc));
     }
     ET_K("et_gate_norm_bwd", et_gate_norm_bwd<<<egrid, 256, 0, stream>>>(w.vb1, w.cat1, w.g_cat1, w.g_vb, NH, H));
     float* g_vec = w.g_vecA;
     float* g_vec_new = w.g_vecB;
-    TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_vb, H, g1.w1T, nullptr, g_vec, H, 3 * N, H, H), stream));
+    TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_vb, H, g1.w1T, nullptr, g_vec, H, 3 * N, H, H), stream, tc));
     {
         GemmP p = gemm_desc(w.g_vec2, H2, g1.w2T, nullptr, g_vec, H, 3 * N, H, H2);
         p.accumulate = 1;
-        TMDN_TRY(gemm1(EPI_NONE, p, stream));
+        TMDN_TRY(node_gemm1(EPI_NONE, p, stream, tc));
     }
     ET_K("et_ln_bwd", et_ln_bwd<<<lgrid, lblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat[L], w.g_cat1, 2 * H, w.g_x, 0, N,
                                                               H));
@@ -780,21 +782,21 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
         const Tab tb{(const float4*)ly.table, inv_h, m->n_int};
         ET_K("et_update_bwd", et_update_bwd<<<egrid, 256, 0, stream>>>(w.g_x, g_vec, w.VP[l], w.O[l], w.g_o, w.g_vp,
                                                                        g_vec_new, NH, H));
-        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_o, 3 * H, ly.o_wT, nullptr, w.g_xa, H, N, H, 3 * H), stream));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_o, 3 * H, ly.o_wT, nullptr, w.g_xa, H, N, H, 3 * H), stream, tc));
         {
             GemmP p = gemm_desc(w.g_vp, 3 * H, ly.vp_wT, nullptr, g_vec_new, H, 3 * N, H, 3 * H);
             p.accumulate = 1;
-            TMDN_TRY(gemm1(EPI_NONE, p, stream));
+            TMDN_TRY(node_gemm1(EPI_NONE, p, stream, tc));
         }
         ET_K("et_edge_bwd", et_edge_bwd<1><<<e8b.grid, e8b.block, e8b.smem, stream>>>(
                                 w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], w.g_xa,
                                 g_vec, N, H, w.g_qkv, g_vec_new, w.gpos));
-        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_qkv, 5 * H, ly.qkv_wT, nullptr, w.g_xl, H, N, H, 5 * H), stream));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_qkv, 5 * H, ly.qkv_wT, nullptr, w.g_xl, H, N, H, 5 * H), stream, tc));
         ET_K("et_ln_bwd", et_ln_bwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, w.stat[l], w.g_xl, H, w.g_x, 1, N, H));
         float* t = g_vec; g_vec = g_vec_new; g_vec_new = t;
     }
     if (m->has_neighbor_embedding) {
-        TMDN_TRY(gemm1(EPI_NONE, gemm_desc(w.g_x, H, m->ne_comb_w2T, nullptr, w.g_xn, H, N, H, H), stream));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_x, H, m->ne_comb_w2T, nullptr, w.g_xn, H, N, H, H), stream, tc));
         ET_K("et_final_bwd", et_final_bwd<true><<<e8.grid, e8.block, e8.smem, stream>>>(
                                  w.row_ptr, w.col, geom, w.z32, m->ne_emb, ne_tab, w.g_xn, w.gpos, forces, N, H));
     } else {

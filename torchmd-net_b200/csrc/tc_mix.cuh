@@ -153,12 +153,13 @@ __device__ __forceinline__ void split_inplace(float4* hi, float4* lo, int idx) {
     const float4 v = hi[idx];
     float4 h, l;
     h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
-    l.x = v.x - h.x; l.y = v.y - h.y; l.z = v.z - h.z; l.w = v.w - h.w;   // exact; the MMA reads its top 19 bits
+    // x - hi is exact in fp32; round it to tf32 as well (the MMA would truncate it: a one-sided 2^-23 error per product)
+    l.x = tf32_rna(v.x - h.x); l.y = tf32_rna(v.y - h.y); l.z = tf32_rna(v.z - h.z); l.w = tf32_rna(v.w - h.w);
     hi[idx] = h;
     lo[idx] = l;
 }
 
-__global__ void __launch_bounds__(THREADS, 1)
+static __global__ void __launch_bounds__(THREADS, 1)
 tc_mix_kernel(const __grid_constant__ Maps M, const __grid_constant__ Params P) {
     extern __shared__ unsigned char tc_smem_raw[];
     unsigned char* sm = tc_smem_raw + ((1024u - (s32(tc_smem_raw) & 1023u)) & 1023u);   // SWIZZLE_128B: 1024-byte base

@@ -13,6 +13,7 @@
 // gathers the adjoints of its neighbours and also accumulates both directions' contribution to dE/dpos_i.
 #include "common.cuh"
 #include "gemm.cuh"
+#include "node_gemm.cuh"
 #include "tc_mix.cuh"
 #include "tensor3.cuh"
 #include "edge_common.cuh"
@@ -974,9 +975,9 @@ struct TnRun {
         }
         GemmP p = gemm_desc(w.dh2, 3 * H, m->emb_w2T, nullptr, w.dh1, 2 * H, N, 2 * H, 3 * H);
         p.aux = w.h1; p.ldaux = 2 * H; p.act = act;
-        TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
+        TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream));
         GemmP q = gemm_desc(w.dh1, 2 * H, m->emb_w1T, nullptr, w.dnh, H, N, H, 2 * H);
-        TMDN_TRY(gemm1(EPI_NONE, q, stream));
+        TMDN_TRY(node_gemm1(EPI_NONE, q, stream));
         TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.dXa, w.dB, m->emb_mixT, N, H), stream));
         {
             KTimer ktimer__("tn_embed_norm_bwd", stream);
@@ -1044,10 +1045,10 @@ struct TnRun {
             }
             GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
             p.C2 = w.h1; p.act = act;
-            TMDN_TRY(gemm1(EPI_ACT, p, stream));
+            TMDN_TRY(node_gemm1(EPI_ACT, p, stream));
             GemmP q = gemm_desc(w.a1, 2 * H, m->emb_w2, m->emb_b2, w.fias, 3 * H, N, 3 * H, 2 * H);
             q.C2 = w.h2; q.act = act;
-            TMDN_TRY(gemm1(EPI_ACT, q, stream));
+            TMDN_TRY(node_gemm1(EPI_ACT, q, stream));
             GemmBatch b = mix_batch(w.ias, w.X[0], m->emb_mix, N, H);
             for (int g = 0; g < 3; ++g) { b.p[g].C2 = w.iasm; b.p[g].aux = w.fias; }
             TMDN_TRY(mix_launch(EPI_SCALE3, b, stream));
@@ -1093,10 +1094,10 @@ struct TnRun {
             {
                 GemmP p = gemm_desc(w.xl, 3 * H, m->out_w, m->out_b, w.a3, H, N, H, 3 * H);
                 p.C2 = w.h3; p.act = act;
-                TMDN_TRY(gemm1(EPI_ACT, p, stream));
+                TMDN_TRY(node_gemm1(EPI_ACT, p, stream));
                 GemmP q = gemm_desc(w.a3, H, m->head_w1, m->head_b1, w.a4, H / 2, N, H / 2, H);
                 q.C2 = w.h4; q.act = act;
-                TMDN_TRY(gemm1(EPI_ACT, q, stream));
+                TMDN_TRY(node_gemm1(EPI_ACT, q, stream));
             }
             {
                 KTimer ktimer__("tn_head_energy", stream);
@@ -1120,9 +1121,9 @@ struct TnRun {
             }
             GemmP p = gemm_desc(w.d4, H / 2, m->head_w1T, nullptr, w.d3, H, N, H, H / 2);
             p.aux = w.h3; p.ldaux = H; p.act = act;
-            TMDN_TRY(gemm1(EPI_MULGRAD, p, stream));
+            TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream));
             GemmP q = gemm_desc(w.d3, H, m->out_wT, nullptr, w.dxl, 3 * H, N, 3 * H, H);
-            TMDN_TRY(gemm1(EPI_NONE, q, stream));
+            TMDN_TRY(node_gemm1(EPI_NONE, q, stream));
             {
                 KTimer ktimer__("tn_out_norm_bwd", stream);
                 tn_out_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
@@ -1207,4 +1208,13 @@ extern "C" int tmdn_channel_mix_f32(const float* x, const float* w, float* y, in
     GemmBatch b = mix_batch(x, y, Wg, (int)n_atoms, H);
     for (int g = 0; g < 3; ++g) b.p[g].accumulate = accumulate;
     return mix_launch(EPI_NONE, b, stream);
+}
+
+extern "C" int tmdn_node_gemm_f32(const float* a, const float* w, const float* bias, float* c, int64_t M, int64_t N,
+                                  int64_t K, int accumulate, tmdn_stream_t stream_) {
+    TMDN_CHECK_ARG(a && w && c, "node_gemm: null pointer argument");
+    TMDN_CHECK_ARG(M > 0 && N > 0 && K > 0 && M < (1LL << 31) && N < (1 << 20) && K < (1 << 20), "node_gemm: bad sizes");
+    GemmP p = gemm_desc(a, (int)K, w, bias, c, (int)N, (int)M, (int)N, (int)K);
+    p.accumulate = accumulate;
+    return node_gemm1(EPI_NONE, p, (cudaStream_t)stream_);
 }

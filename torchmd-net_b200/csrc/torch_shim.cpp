@@ -377,15 +377,16 @@ std::unordered_map<int64_t, std::shared_ptr<EtHandle>> g_et;
 //   emb ne_emb ne_table ne_comb_w ne_comb_b ne_comb_w2T out_ln_w out_ln_b
 //   head block x2: w1 w1T w2 w2T u0_w u0_b u0_wT u2_w u2_b u2_wT
 //   per layer: ln_w ln_b qkv_w qkv_b qkv_wT vp_w vp_wT o_w o_b o_wT table
-// iparams: hidden num_layers num_heads max_z activation attn_activation has_ne n_int ; fparams: lo hi mean std
+// iparams: hidden num_layers num_heads max_z activation attn_activation has_ne n_int gemm_mode ; fparams: lo hi mean std
 int64_t et_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::vector<double> fp) {
-    TORCH_CHECK(ip.size() == 8 && fp.size() == 4, "et_create: bad parameter vectors");
+    TORCH_CHECK(ip.size() == 9 && fp.size() == 4, "et_create: bad parameter vectors");
     auto h = std::make_shared<EtHandle>();
     tmdn_et_model& m = h->m;
     memset(&m, 0, sizeof(m));
     m.hidden = (int32_t)ip[0]; m.num_layers = (int32_t)ip[1]; m.num_heads = (int32_t)ip[2]; m.max_z = (int32_t)ip[3];
     m.activation = (int32_t)ip[4]; m.attn_activation = (int32_t)ip[5]; m.has_neighbor_embedding = (int32_t)ip[6];
     m.n_int = (int32_t)ip[7];
+    m.gemm_mode = (int32_t)ip[8];
     m.cutoff_lower = (float)fp[0]; m.cutoff_upper = (float)fp[1]; m.mean = (float)fp[2]; m.std = (float)fp[3];
     TORCH_CHECK(m.num_layers >= 0 && m.num_layers <= TMDN_MAX_LAYERS, "et_create: too many layers");
     const size_t expect = 28 + 11 * (size_t)m.num_layers;
@@ -541,6 +542,27 @@ Tensor channel_mix(const Tensor& x, const Tensor& w, const c10::optional<Tensor>
     return y;
 }
 
+// c (+)= a w^T + bias
+Tensor node_gemm(const Tensor& a, const Tensor& w, const c10::optional<Tensor>& bias, const c10::optional<Tensor>& c_,
+                 bool accumulate) {
+    TORCH_CHECK(a.is_cuda() && a.scalar_type() == at::kFloat && a.is_contiguous() && a.dim() == 2, "node_gemm: a");
+    TORCH_CHECK(w.is_cuda() && w.scalar_type() == at::kFloat && w.is_contiguous() && w.dim() == 2 && w.size(1) == a.size(1),
+                "node_gemm: w must be [N,K]");
+    const c10::cuda::CUDAGuard guard(a.device());
+    Tensor c = c_.has_value() ? *c_ : at::zeros({a.size(0), w.size(0)}, a.options());
+    TORCH_CHECK(c.is_cuda() && c.scalar_type() == at::kFloat && c.is_contiguous() && c.size(0) == a.size(0) &&
+                    c.size(1) == w.size(0), "node_gemm: c");
+    const float* b = nullptr;
+    if (bias.has_value()) {
+        TORCH_CHECK(bias->is_cuda() && bias->scalar_type() == at::kFloat && bias->is_contiguous() && bias->numel() == w.size(0),
+                    "node_gemm: bias");
+        b = bias->data_ptr<float>();
+    }
+    TMDN_CALL(tmdn_node_gemm_f32(a.data_ptr<float>(), w.data_ptr<float>(), b, c.data_ptr<float>(), a.size(0), w.size(0),
+                                 a.size(1), accumulate ? 1 : 0, cur_stream()));
+    return c;
+}
+
 int64_t launch_count() { return (int64_t)tmdn_launch_count(); }
 void profile_enable(bool on) { TMDN_CALL(tmdn_profile_enable(on ? 1 : 0)); }
 std::string profile_report() {
@@ -587,6 +609,7 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
           "Tensor(b!) forces, Tensor(c!) status, Tensor(d!) workspace) -> ()", tensornet_stage);
     m.def("halo_pack(Tensor src, Tensor idx) -> Tensor", halo_pack);
     m.def("channel_mix(Tensor x, Tensor w, Tensor? y, bool accumulate) -> Tensor", channel_mix);
+    m.def("node_gemm(Tensor a, Tensor w, Tensor? bias, Tensor? c, bool accumulate) -> Tensor", node_gemm);
     m.def("launch_count() -> int", launch_count);
     m.def("profile_enable(bool on) -> ()", profile_enable);
     m.def("profile_report() -> str", profile_report);

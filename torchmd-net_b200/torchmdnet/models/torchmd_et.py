@@ -100,6 +100,9 @@ class TorchMD_ET(FusedRepresentation):
             for _ in range(num_layers)])
         self.out_norm = nn.LayerNorm(hidden_channels, dtype=dtype)
         self._init_fused()
+        # "fp32": exact fp32 FFMA projections (default, 1e-5 parity bar); "tf32x3": tcgen05 tensor cores with the
+        # three-product tf32 split, ~1e-5 relative on energies through the deep ET stack (tests: 3e-5)
+        self.gemm_mode = "fp32"
         self.reset_parameters()
 
     def reset_parameters(self):
@@ -112,6 +115,9 @@ class TorchMD_ET(FusedRepresentation):
         self.out_norm.reset_parameters()
 
     # -------------------------------------------------------------------------------------------- packing
+    def _extra_key(self):
+        return (self.gemm_mode,)
+
     def pack_weights(self, head: Optional[nn.Module], mean: float, std: float):
         """-> (weights in the order csrc/torch_shim.cpp::et_create expects, iparams, fparams)."""
         if head is None:
@@ -168,7 +174,7 @@ class TorchMD_ET(FusedRepresentation):
                   f32(ly.vec_proj.weight), tr(ly.vec_proj.weight), f32(ly.o_proj.weight), f32(ly.o_proj.bias),
                   tr(ly.o_proj.weight), f32(tab.view(n_int, 4, H, 4))]
         iparams = [H, self.num_layers, nh, self.max_z, ACT_ID[self.activation], ACT_ID[self.attn_activation],
-                   int(ne is not None), n_int]
+                   int(ne is not None), n_int, {"fp32": 0, "tf32x3": 1}[self.gemm_mode]]
         return w, iparams, [lo, hi, float(mean), float(std)]
 
     def forward(self, z: Tensor, pos: Tensor, batch: Tensor, q: Optional[Tensor] = None,
