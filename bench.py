@@ -314,8 +314,9 @@ def main():
     ap.add_argument("--workload", default="chignolin", choices=list(HPARAMS))
     ap.add_argument("--filter", default="table", choices=["table", "exact"])
     ap.add_argument("--molecules", type=int, default=8192)
-    ap.add_argument("--et-gemm", default="fp32", choices=["fp32", "tf32x3"],
-                    help="ET projections: exact fp32 FFMA (parity bar 1e-5) or tcgen05 three-product tf32 (3e-5)")
+    ap.add_argument("--gemm", "--et-gemm", dest="et_gemm", default="fp32", choices=["fp32", "tf32x3"],
+                    help="plain node GEMMs (TensorNet MLPs, ET projections): exact fp32 FFMA (parity bar 1e-5) or tcgen05 "
+                         "three-product tf32 (3e-5); the TensorNet channel mixes always use the tensor cores")
     ap.add_argument("--water-side", type=int, default=32)
     ap.add_argument("--water-order", default="raster", choices=["raster", "morton", "shuffle"],
                     help="index order of the synthetic water molecules (raster = lattice order)")
@@ -349,11 +350,11 @@ def main():
     if args.workload == "water" and world > 1:
         return run_decomposed(args, model, hp, dev, rank, world, local)
     rm = model.representation_model
+    rm.gemm_mode = args.et_gemm
     if hp["model"] == "tensornet":
         rm.filter_mode = args.filter
     else:
         args.filter = "table"
-        rm.gemm_mode = args.et_gemm
     z_np, pos0, batch_np, box = make_inputs(args.workload, rank, args)
     if box is not None:
         rm.distance = OptimizedDistance(hp["cutoff_lower"], hp["cutoff_upper"], max_num_pairs=-hp["max_num_neighbors"],
@@ -434,10 +435,9 @@ def main():
     equal_sizes = n_mol == 1 or (N % n_mol == 0 and bool((np.bincount(batch_np) == N // n_mol).all()))
     emb = torch.from_numpy(z_np).view(n_mol, N // n_mol) if equal_sizes else torch.from_numpy(z_np).view(1, N)
     calc = External(ckpt, emb, dev)
+    calc.model.representation_model.gemm_mode = args.et_gemm
     if hp["model"] == "tensornet":
         calc.model.representation_model.filter_mode = args.filter
-    else:
-        calc.model.representation_model.gemm_mode = args.et_gemm
     if box is not None:
         calc.model.representation_model.distance = rm.distance
     if emb.shape[0] != n_mol:
@@ -515,8 +515,8 @@ def main():
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD_DESC[args.workload], "atoms_per_gpu": N, "molecules_per_gpu": n_mol,
                        "edges_per_gpu": E, "filter_mode": args.filter,
-                       "gemm": ("tcgen05 tf32x3 (channel mixes, MLPs >= 1024 rows), fp32 FFMA otherwise" if hp["model"] == "tensornet"
-                                else ("tcgen05 tf32x3" if args.et_gemm == "tf32x3" else "fp32 FFMA")),
+                       "gemm": ("channel mixes: tcgen05 tf32x3; " if hp["model"] == "tensornet" else "") +
+                               ("node GEMMs: tcgen05 tf32x3" if args.et_gemm == "tf32x3" else "node GEMMs: fp32 FFMA"),
                        "neighbor_strategy": rm.distance.strategy,
                        "l2": "flushed (512 MiB write) before every timed step",
                        "step": "one CUDA graph replay: neighbour list + CSR + forward + analytic backward",

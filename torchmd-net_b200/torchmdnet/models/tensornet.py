@@ -184,6 +184,9 @@ class TensorNet(FusedRepresentation):
                                           resize_to_fit=not static_shapes, long_edge_index=True)
         self._init_fused()
         self.filter_mode = "exact"
+        # MLP GEMMs: "fp32" = exact fp32 FFMA (default, 1e-5 parity bar); "tf32x3" = tcgen05 three-product tf32 (own,
+        # looser tolerance: the tensor-core accumulator truncates).  The channel mixes always run on the tensor cores.
+        self.gemm_mode = "fp32"
         self.reset_parameters()
 
     def reset_parameters(self):
@@ -252,12 +255,12 @@ class TensorNet(FusedRepresentation):
             w += [f32(l.weight) for l in layer.linears_tensor] + [tr(l.weight) for l in layer.linears_tensor]
         iparams = [H, K, self.num_layers, self.max_z, RBF_ID[self.rbf_type], ACT_ID[self.activation],
                    int(self.equivariance_invariance_group == "SO(3)"), FILTER_TABLE if table else FILTER_EXACT,
-                   n_int]
+                   n_int, {"fp32": 0, "tf32x3": 1}[self.gemm_mode]]
         fparams = [lo, hi, float(mean), float(std)]
         return w, iparams, fparams
 
     def _extra_key(self):
-        return (self.filter_mode,)
+        return (self.filter_mode, self.gemm_mode)
 
     def forward(self, z: Tensor, pos: Tensor, batch: Tensor, q: Optional[Tensor] = None,
                 s: Optional[Tensor] = None):

@@ -140,6 +140,10 @@ class TorchMD_ET(FusedRepresentation):
         def table(lin, act, n_out, cutoff):
             """[n_int, n_out, 4] Hermite coefficients of [act o] lin(rbf(d)) [* C(d)]; the constant 1 if lin is None"""
             if lin is None:
+                if cutoff:   # the bare cutoff C(d)
+                    from .tensornet import _cutoff_and_grad
+                    cc, dcc = _cutoff_and_grad(grid, lo, hi)
+                    return hermite_coefficients(cc[:, None].expand(-1, n_out), dcc[:, None].expand(-1, n_out), step)
                 c = torch.zeros(n_int, n_out, 4, device=dev, dtype=torch.float64)
                 c[..., 0] = 1.0
                 return c
@@ -169,7 +173,12 @@ class TorchMD_ET(FusedRepresentation):
             qkv_b = torch.cat([ly.q_proj.bias, ly.k_proj.bias, ly.v_proj.bias[perm]]).detach()
             dk = None if ly.dk_proj is None else (ly.dk_proj.weight, ly.dk_proj.bias)
             dv = None if ly.dv_proj is None else (ly.dv_proj.weight[perm], ly.dv_proj.bias[perm])
-            tab = torch.cat([table(dk, self.activation, H, False), table(dv, self.activation, 3 * H, False)], 1)
+            # the attention cutoff C(d) (torchmd_et.py:297) only ever multiplies the scalar value filter (part 0 of dv),
+            # so it is folded into that table: the edge kernels evaluate no cosine
+            dv0 = None if dv is None else (dv[0][:H], dv[1][:H])
+            dv12 = None if dv is None else (dv[0][H:], dv[1][H:])
+            tab = torch.cat([table(dk, self.activation, H, False), table(dv0, self.activation, H, True),
+                             table(dv12, self.activation, 2 * H, False)], 1)
             w += [f32(ly.layernorm.weight), f32(ly.layernorm.bias), f32(qkv_w), f32(qkv_b), tr(qkv_w),
                   f32(ly.vec_proj.weight), tr(ly.vec_proj.weight), f32(ly.o_proj.weight), f32(ly.o_proj.bias),
                   tr(ly.o_proj.weight), f32(tab.view(n_int, 4, H, 4))]
