@@ -314,9 +314,9 @@ def main():
     ap.add_argument("--workload", default="chignolin", choices=list(HPARAMS))
     ap.add_argument("--filter", default="table", choices=["table", "exact"])
     ap.add_argument("--molecules", type=int, default=8192)
-    ap.add_argument("--gemm", "--et-gemm", dest="et_gemm", default="fp32", choices=["fp32", "tf32x3"],
-                    help="plain node GEMMs (TensorNet MLPs, ET projections): exact fp32 FFMA (parity bar 1e-5) or tcgen05 "
-                         "three-product tf32 (3e-5); the TensorNet channel mixes always use the tensor cores")
+    ap.add_argument("--gemm", "--et-gemm", dest="et_gemm", default="tf32x3", choices=["fp32", "tf32x3"],
+                    help="plain node GEMMs (TensorNet MLPs, ET projections): tcgen05 three-product tf32 with fp32 chunk sums "
+                         "(default) or the fp32 FFMA kernel; the TensorNet channel mixes always use the tensor cores")
     ap.add_argument("--water-side", type=int, default=32)
     ap.add_argument("--water-order", default="raster", choices=["raster", "morton", "shuffle"],
                     help="index order of the synthetic water molecules (raster = lattice order)")

@@ -150,12 +150,11 @@ typedef struct tmdn_filter_set {
     int32_t pad_;
 } tmdn_filter_set;
 
-/* Precision of the plain node GEMMs (MLPs of TensorNet, projections of ET).  TF32X3 = tcgen05 with the three-product tf32
- * split: rms error 1.3-2.8e-7 of sum|a w| per GEMM (fp32 FFMA: 2.8e-8) and, because the tensor-core accumulator
- * truncates, a one-sided bias on same-sign sums (measured: 1.2e-5 relative on the energy of a 5184-atom water box when the
- * TensorNet MLPs use it, ~1e-5 through the ET stack).  It is therefore opt-in and held to 3e-5 relative in the tests; the
- * default keeps the 1e-5 bar.  The grouped channel mix of TensorNet (sign-symmetric tensor components, 1.2e-6 on the
- * same box) always runs on the tensor cores. */
+/* Kernel of the plain node GEMMs (MLPs of TensorNet, projections of ET).  TF32X3 = tcgen05 with the three-product tf32
+ * split; TMEM holds the partial product of one 32-channel K chunk and the chunks are summed in fp32 round-to-nearest
+ * on the CUDA cores, because the tensor-core accumulator truncates (accumulating all of K in TMEM biased same-sign sums:
+ * 1.2e-5 relative on the energy of a 5184-atom water box).  Measured rms error 1.0-1.9e-8 of sum|a w| per GEMM, below the
+ * 2.8e-8 of an fp32 FFMA GEMM.  FP32 = the FFMA kernel.  The host default is TF32X3. */
 enum { TMDN_GEMM_FP32 = 0, TMDN_GEMM_TF32X3 = 1 };
 
 typedef struct tmdn_tensornet_model {

@@ -41,27 +41,27 @@ def test_emulated_decomposition_matches_single_domain(world):
         p = pos.cuda() if step == 0 else torch.from_numpy(S.md_step_noise(pos.numpy(), 1, sigma=0.03)).cuda()
         y_ref, f_ref = m(z.cuda(), p)
         e, f = emulate_step(runners, p)
-        torch.testing.assert_close(e, y_ref, rtol=2e-6, atol=2e-5)
+        # the ranks are below the 1024-row threshold of the tensor-core MLP GEMMs (FFMA kernel), the single domain is
+        # above it: fp32-level differences per atom, summed over N atoms (same 3e-8 N allowance as the parity tests)
+        torch.testing.assert_close(e, y_ref, rtol=2e-6, atol=2e-5 + 3e-8 * pos.shape[0])
         torch.testing.assert_close(f, f_ref, rtol=0, atol=2e-5)
     assert sum(r.plan.n_own for r in runners) == pos.shape[0]
     assert all(int(r.status[1]) == 0 for r in runners)
 
 
-def test_tf32x3_mlp_mode_has_its_own_tolerance():
-    """gemm_mode="tf32x3" moves the MLP GEMMs of TensorNet to the tcgen05 tensor cores.  Stated separately from the fp32
-    bar: |dE| <= 3e-5 max(1,|E|) + 2e-7 N (the tensor-core accumulator truncates: a one-sided ~1e-7 per atom), forces
-    within 1e-4 eV/A of the default mode."""
-    m, hp, z, pos, box = _model_and_system(8)          # 1536 atoms: above the 1024-row threshold of tc_gemm
-    y0, f0 = m(z.cuda(), pos.cuda())
-    m.representation_model.gemm_mode = "tf32x3"
+def test_mlp_gemm_modes_agree():
+    """gemm_mode="tf32x3" (default: MLP GEMMs on tcgen05, K chunks summed in fp32) against "fp32" (FFMA kernel) on a
+    system above the 1024-row threshold of tc_gemm: no one-sided drift of the summed energy."""
+    m, hp, z, pos, box = _model_and_system(8)          # 1536 atoms
     y1, f1 = m(z.cuda(), pos.cuda())
-    assert not torch.equal(y0, y1)
-    n = pos.shape[0]
-    assert float((y1 - y0).abs().max()) <= 3e-5 * max(1.0, float(y0.abs().max())) + 2e-7 * n
-    assert float((f1 - f0).abs().max()) <= 1e-4
     m.representation_model.gemm_mode = "fp32"
+    y0, f0 = m(z.cuda(), pos.cuda())
+    assert not torch.equal(y0, y1)
+    assert float((y1 - y0).abs().max()) <= 1e-5 * max(1.0, float(y0.abs().max())) + 3e-8 * pos.shape[0]
+    assert float((f1 - f0).abs().max()) <= 2e-5
+    m.representation_model.gemm_mode = "tf32x3"
     y2, _ = m(z.cuda(), pos.cuda())
-    assert torch.equal(y0, y2)
+    assert torch.equal(y1, y2)
 
 
 def test_stage_api_equals_monolithic_call():

@@ -5,7 +5,8 @@
 //
 // Differences from tc_mix_kernel: the weight does not stay resident (K and N are arbitrary), so a ring stage holds a
 // 32-channel K chunk of BOTH operands (raw -> hi in place, lo beside it: 64 KB per stage, 3 stages) and the split warps
-// round both; tiles are 128 x 128 over a persistent grid, N-tiles of one M-tile adjacent in the schedule so that the
+// round both; TMEM holds one chunk's partial product at a time and the chunks are summed in fp32 round-to-nearest by two
+// epilogue warpgroups (the tensor-core accumulator truncates: see the MMA issuer); tiles are 128 x 128 over a persistent grid, N-tiles of one M-tile adjacent in the schedule so that the
 // A rows are fetched from HBM once and re-read from L2.  TMA zero-fills rows beyond M / N and channels beyond K and
 // clips the stores, so M, N, K only need to be multiples of 4.  Epilogues as in gemm.cuh (bias, activation with the
 // pre-activation saved, multiply by act'(saved), accumulate = TMA reduce-add).
@@ -29,17 +30,19 @@ struct GMaps {
     CUtensorMap a, w, c, c2;
 };
 
-static __global__ void __launch_bounds__(THREADS, 1)
+constexpr int GTHREADS_TC = 512;   // + a second epilogue warpgroup (warps 12-15): each thread keeps 64 fp32 partial sums
+
+static __global__ void __launch_bounds__(GTHREADS_TC, 1)
 tc_gemm_kernel(const __grid_constant__ GMaps M, const __grid_constant__ GParams P) {
     extern __shared__ unsigned char tcg_smem_raw[];
     unsigned char* sm = tcg_smem_raw + ((1024u - (s32(tcg_smem_raw) & 1023u)) & 1023u);
     float* ring = reinterpret_cast<float*>(sm);                 // stage s: [Ahi | Alo | Bhi | Blo], 16 KB each
-    float* Cst = ring + 4 * GSTAGES * CHUNK_FLOATS;
+    float* Cst = ring + 4 * GSTAGES * CHUNK_FLOATS;             // one staging buffer per epilogue warpgroup
     uint64_t* bars = reinterpret_cast<uint64_t*>(Cst + CSTAGES * CHUNK_FLOATS);
     uint64_t* full_raw = bars;            // [GSTAGES] TMA -> split
     uint64_t* lo_ready = bars + 3;        // [GSTAGES] split -> MMA
     uint64_t* empty = bars + 6;           // [GSTAGES] MMA -> TMA
-    uint64_t* tmem_full = bars + 9;       // [2] MMA -> epilogue
+    uint64_t* tmem_full = bars + 9;       // [2] MMA -> epilogue (one K chunk's partial product)
     uint64_t* tmem_empty = bars + 11;     // [2] epilogue -> MMA
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
 
@@ -51,7 +54,7 @@ tc_gemm_kernel(const __grid_constant__ GMaps M, const __grid_constant__ GParams 
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < GSTAGES; ++s) { mbar_init(&full_raw[s], 1); mbar_init(&lo_ready[s], 128); mbar_init(&empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 128); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 256); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         fence_async_smem();
     }
@@ -83,73 +86,96 @@ tc_gemm_kernel(const __grid_constant__ GMaps M, const __grid_constant__ GParams 
             }
         }
     } else if (warp == 1) {
-        // ================= MMA issuer
+        // ================= MMA issuer.  The tensor-core accumulator truncates (round toward zero), which biases long
+        // same-sign sums; so TMEM only ever holds the partial product of ONE 32-channel chunk (12 MMAs, the two
+        // correction products first), and the chunks are summed in fp32 round-to-nearest by the epilogue warps.
         if (lane == 0) {
             int it = 0;
             for (int t = 0; t < my_tiles; ++t) {
-                const int b = t & 1;
-                mbar_wait(&tmem_empty[b], ((t >> 1) & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t d = tmem + (uint32_t)(b * TILE);
                 for (int c = 0; c < kchunks; ++c, ++it) {
-                    const int s = it % GSTAGES;
+                    const int s = it % GSTAGES, b = it & 1;
+                    mbar_wait(&tmem_empty[b], ((it >> 1) & 1) ^ 1);
                     mbar_wait(&lo_ready[s], (it / GSTAGES) & 1);
                     tc_fence_after();
+                    const uint32_t d = tmem + (uint32_t)(b * TILE);
                     const uint32_t ah = s32(ring + 4 * s * CHUNK_FLOATS), al = ah + CHUNK_FLOATS * 4;
                     const uint32_t bh = al + CHUNK_FLOATS * 4, bl = bh + CHUNK_FLOATS * 4;
 #pragma unroll
                     for (int k = 0; k < KC / 8; ++k) {
                         const uint32_t off = (uint32_t)k * 32u;
-                        tc_mma_tf32(d, smem_desc(ah + off), smem_desc(bh + off), IDESC, (c | k) != 0);
-                        tc_mma_tf32(d, smem_desc(ah + off), smem_desc(bl + off), IDESC, 1);
+                        tc_mma_tf32(d, smem_desc(ah + off), smem_desc(bl + off), IDESC, k != 0);
                         tc_mma_tf32(d, smem_desc(al + off), smem_desc(bh + off), IDESC, 1);
                     }
+#pragma unroll
+                    for (int k = 0; k < KC / 8; ++k) {
+                        const uint32_t off = (uint32_t)k * 32u;
+                        tc_mma_tf32(d, smem_desc(ah + off), smem_desc(bh + off), IDESC, 1);
+                    }
                     tc_commit(&empty[s]);
+                    tc_commit(&tmem_full[b]);
                 }
-                tc_commit(&tmem_full[b]);
             }
         }
-    } else if (warp >= 4 && warp < 8) {
-        // ================= epilogue (thread = one row of the tile)
-        const int row = (warp - 4) * 32 + lane;
-        const bool issuer = threadIdx.x == 128;
-        int sb = 0;
-        auto stage_out = [&](const float (&v)[32], const CUtensorMap* map, int col0, int m0, bool add) {
-            if (issuer) tma_store_wait_read<CSTAGES - 1>();
-            epi_barrier();
-            float* buf = Cst + sb * CHUNK_FLOATS + row * KC;
+    } else if ((warp >= 4 && warp < 8) || warp >= 12) {
+        // ================= epilogue: two warpgroups, thread = one row x 64 columns of the tile
+        const int grp = warp >= 12 ? 1 : 0;
+        const int wq = warp & 3;                         // TMEM lane quarter this warp may read
+        const int row = wq * 32 + lane;
+        const bool issuer = (threadIdx.x & 127) == 0;    // first thread of the warpgroup
+        float* cbuf = Cst + grp * CHUNK_FLOATS;
+        auto group_barrier = [&]() {
+            if (grp == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+            else asm volatile("bar.sync 2, 128;" ::: "memory");
+        };
+        auto stage_out = [&](const float* v, const CUtensorMap* map, int col0, int m0, bool add) {
+            if (issuer) tma_store_wait_read<0>();        // the previous store of this group has read the buffer
+            group_barrier();
+            float* buf = cbuf + row * KC;
 #pragma unroll
             for (int j = 0; j < 8; ++j)
                 *reinterpret_cast<float4*>(buf + ((j ^ (row & 7)) << 2)) =
                     make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
             fence_async_smem();
-            epi_barrier();
+            group_barrier();
             if (issuer) {
                 if (add)
                     asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
-                                 "r"(s32(Cst + sb * CHUNK_FLOATS)), "r"(col0), "r"(m0)
+                                 "r"(s32(cbuf)), "r"(col0), "r"(m0)
                                  : "memory");
                 else
                     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
-                                 "r"(s32(Cst + sb * CHUNK_FLOATS)), "r"(col0), "r"(m0)
+                                 "r"(s32(cbuf)), "r"(col0), "r"(m0)
                                  : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }
-            sb ^= 1;
         };
+        float acc[64];
+        int it = 0;
         for (int t = 0; t < my_tiles; ++t) {
-            const int b = t & 1;
-            mbar_wait(&tmem_full[b], (t >> 1) & 1);
-            tc_fence_after();
             const int tile = rank + t * nctas;
             const int m0 = (tile / P.n_tiles) * TILE, n0 = (tile % P.n_tiles) * TILE;
             const int m = m0 + row;
-            const int ncols = min(TILE, P.N - n0);
-#pragma unroll 1
-            for (int cb = 0; cb * 32 < ncols; ++cb) {
-                float v[32];
-                tc_ld32(tmem + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)(b * TILE + cb * 32), v);
-                const int nb = n0 + cb * 32;
+#pragma unroll
+            for (int j = 0; j < 64; ++j) acc[j] = 0.f;
+            for (int c = 0; c < kchunks; ++c, ++it) {
+                const int b = it & 1;
+                mbar_wait(&tmem_full[b], (it >> 1) & 1);
+                tc_fence_after();
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    float v[32];
+                    tc_ld32(tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)(b * TILE + grp * 64 + half * 32), v);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) acc[half * 32 + j] += v[j];
+                }
+                tc_fence_before();
+                mbar_arrive(&tmem_empty[b]);
+            }
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int nb = n0 + grp * 64 + half * 32;
+                if (nb >= P.N) continue;                 // warpgroup-uniform
+                float* v = acc + half * 32;
                 if (P.bias) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
@@ -174,11 +200,9 @@ tc_gemm_kernel(const __grid_constant__ GMaps M, const __grid_constant__ GParams 
                 }
                 stage_out(v, &M.c, nb, m0, P.accumulate != 0);
             }
-            tc_fence_before();
-            mbar_arrive(&tmem_empty[b]);
         }
         if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-    } else if (warp >= 8) {
+    } else if (warp >= 8 && warp < 12) {
         // ================= split warps: A chunk and W chunk of the stage
         const int tid = threadIdx.x - 256;
         int it = 0;
@@ -245,7 +269,7 @@ static inline int launch(int epi, const GemmP& p, cudaStream_t stream) {
     }
     const long long tiles = (long long)P.m_tiles * P.n_tiles;
     const unsigned grid = (unsigned)(tiles < 148 ? tiles : 148);
-    tc_gemm_kernel<<<grid, THREADS, GSMEM_BYTES, stream>>>(M, P);
+    tc_gemm_kernel<<<grid, GTHREADS_TC, GSMEM_BYTES, stream>>>(M, P);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }

@@ -12,8 +12,10 @@
 // 128x1, 42x3 or 25x5 rows, fetched as ONE 3-D TMA box from the [N,9,H] tensor, so no permuted copy of X exists):
 //   warp 0       TMA producer: W once (4 K-chunks of 32), then X chunks [rows, 32] into a 2-stage ring (SWIZZLE_128B)
 //   warps 8-11   split: round the landed chunk to tf32 in place, write the low part beside it, fence to the async proxy
-//   warp 1       one thread issues 3 x 4 tcgen05.mma (M128 N128 K8) per chunk; tcgen05.commit frees the ring slot
-//   warps 4-7    epilogue: tcgen05.ld the 128x128 accumulator (double buffered in TMEM, 2 x 128 columns), apply the
+//   warp 1       one thread issues 3 x 4 tcgen05.mma (M128 N128 K8) per chunk; tcgen05.commit frees the ring slot and
+//                hands the chunk's partial product to the epilogue
+//   warps 4-7, 12-15  epilogue: tcgen05.ld each chunk's partial product (double buffered in TMEM, 2 x 128 columns)
+//                and sum the chunks in fp32 registers (the tensor-core accumulator truncates), apply the
 //                fused scale, stage 32-column slabs in shared memory and TMA-store (or reduce-add) them through
 //                the same 3-D box
 // Per tile the tensor pipe needs ~1.7 us and HBM (64 KB in, 64 KB out) ~2.9 us, so the kernel is bound by HBM.
@@ -32,7 +34,8 @@ constexpr int NCHUNK = TILE / KC;    // 4
 constexpr int STAGES = 2;           // X ring (raw/hi + lo per stage)
 constexpr int CSTAGES = 2;          // output staging buffers [128 rows x 32 columns]
 constexpr int CHUNK_FLOATS = TILE * KC;          // 4096 floats = 16 KB
-constexpr int THREADS = 384;
+constexpr int THREADS = 384;          // tc_gemm.cuh
+constexpr int MIX_THREADS = 512;      // 16 warps: TMA, MMA, alloc, -, epilogue group 0 (4), split (4), epilogue group 1 (4)
 constexpr int SMEM_BYTES = (2 * NCHUNK + 2 * STAGES + CSTAGES) * CHUNK_FLOATS * 4 + 256 + 1024;
 constexpr int TMEM_COLS = 256;
 
@@ -159,7 +162,7 @@ __device__ __forceinline__ void split_inplace(float4* hi, float4* lo, int idx) {
     lo[idx] = l;
 }
 
-static __global__ void __launch_bounds__(THREADS, 1)
+static __global__ void __launch_bounds__(MIX_THREADS, 1)
 tc_mix_kernel(const __grid_constant__ Maps M, const __grid_constant__ Params P) {
     extern __shared__ unsigned char tc_smem_raw[];
     unsigned char* sm = tc_smem_raw + ((1024u - (s32(tc_smem_raw) & 1023u)) & 1023u);   // SWIZZLE_128B: 1024-byte base
@@ -191,7 +194,7 @@ tc_mix_kernel(const __grid_constant__ Maps M, const __grid_constant__ Params P) 
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full_raw[s], 1); mbar_init(&lo_ready[s], 128); mbar_init(&empty[s], 1); }
         mbar_init(b_full, 1);
         mbar_init(b_ready, 128);
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 128); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 256); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         fence_async_smem();
     }
@@ -223,72 +226,98 @@ tc_mix_kernel(const __grid_constant__ Maps M, const __grid_constant__ Params P) 
             }
         }
     } else if (warp == 1) {
-        // ================= MMA issuer
+        // ================= MMA issuer.  The tensor-core accumulator truncates (round toward zero), which biases long
+        // same-sign sums (measured 1.2e-6 relative on the energy of a 5184-atom box); so TMEM only ever holds the
+        // partial product of ONE 32-channel chunk (12 MMAs, the two correction products first), and the four chunks
+        // are summed in fp32 round-to-nearest by the epilogue warps.
         if (lane == 0) {
             mbar_wait(b_ready, 0);
             tc_fence_after();
             int it = 0;
             for (int t = 0; t < my_tiles; ++t) {
-                const int b = t & 1;
-                mbar_wait(&tmem_empty[b], ((t >> 1) & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t d = tmem + (uint32_t)(b * TILE);
                 for (int c = 0; c < NCHUNK; ++c, ++it) {
-                    const int s = it % STAGES;
+                    const int s = it % STAGES, b = it & 1;
+                    mbar_wait(&tmem_empty[b], ((it >> 1) & 1) ^ 1);
                     mbar_wait(&lo_ready[s], (it / STAGES) & 1);
                     tc_fence_after();
+                    const uint32_t d = tmem + (uint32_t)(b * TILE);
                     const uint32_t ah = s32(Ahi + s * CHUNK_FLOATS), al = s32(Alo + s * CHUNK_FLOATS);
                     const uint32_t bh = s32(Bhi + c * CHUNK_FLOATS), bl = s32(Blo + c * CHUNK_FLOATS);
 #pragma unroll
                     for (int k = 0; k < KC / 8; ++k) {
                         const uint32_t off = (uint32_t)k * 32u;   // 8 tf32 = 32 bytes along K inside the swizzle row
-                        tc_mma_tf32(d, smem_desc(ah + off), smem_desc(bh + off), IDESC, (c | k) != 0);
-                        tc_mma_tf32(d, smem_desc(ah + off), smem_desc(bl + off), IDESC, 1);
+                        tc_mma_tf32(d, smem_desc(ah + off), smem_desc(bl + off), IDESC, k != 0);
                         tc_mma_tf32(d, smem_desc(al + off), smem_desc(bh + off), IDESC, 1);
                     }
+#pragma unroll
+                    for (int k = 0; k < KC / 8; ++k) {
+                        const uint32_t off = (uint32_t)k * 32u;
+                        tc_mma_tf32(d, smem_desc(ah + off), smem_desc(bh + off), IDESC, 1);
+                    }
                     tc_commit(&empty[s]);
+                    tc_commit(&tmem_full[b]);
                 }
-                tc_commit(&tmem_full[b]);
             }
         }
-    } else if (warp >= 4 && warp < 8) {
-        // ================= epilogue: warp w reads TMEM lanes 32 (w % 4) ..; thread = one row of the tile.  A 32-column
-        // slab goes registers -> swizzled staging buffer -> ONE TMA store (or reduce-add) through the same
+    } else if ((warp >= 4 && warp < 8) || warp >= 12) {
+        // ================= epilogue: two warpgroups, thread = one row x 64 columns of the tile; warp w reads TMEM lanes
+        // 32 (w % 4) ...  Per chunk: tcgen05.ld the partial product and add it (fp32, round to nearest).  Per tile: a
+        // 32-column slab goes registers -> swizzled staging buffer -> ONE TMA store (or reduce-add) through the same
         // (channel, component, atom) box as the input, so global memory sees whole 128-byte row segments.
-        const int row = (warp - 4) * 32 + lane;
-        const bool issuer = threadIdx.x == 128;
+        const int grp = warp >= 12 ? 1 : 0;
+        const int wq = warp & 3;
+        const int row = wq * 32 + lane;
+        const bool issuer = (threadIdx.x & 127) == 0;
         const CUtensorMap* mC = &M.c[pi];
         const CUtensorMap* mC2 = &M.c2[pi];
         const bool scale = P.epi == EPI_SCALE3;
-        int sb = 0;
-        auto stage_out = [&](const float (&v)[32], const CUtensorMap* map, int col0, int atom0, bool add) {
-            if (issuer) tma_store_wait_read<CSTAGES - 1>();   // the store that last read this buffer is done with it
-            epi_barrier();
-            float* buf = Cst + sb * CHUNK_FLOATS + row * KC;
+        float* cbuf = Cst + grp * CHUNK_FLOATS;
+        auto group_barrier = [&]() {
+            if (grp == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+            else asm volatile("bar.sync 2, 128;" ::: "memory");
+        };
+        auto stage_out = [&](const float* v, const CUtensorMap* map, int col0, int atom0, bool add) {
+            if (issuer) tma_store_wait_read<0>();            // the previous store of this group has read the buffer
+            group_barrier();
+            float* buf = cbuf + row * KC;
 #pragma unroll
             for (int j = 0; j < 8; ++j)
                 *reinterpret_cast<float4*>(buf + ((j ^ (row & 7)) << 2)) =
                     make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
             fence_async_smem();
-            epi_barrier();
-            if (issuer) tma_store_3d(map, Cst + sb * CHUNK_FLOATS, col0, pr.c0, atom0, add);
-            sb ^= 1;
+            group_barrier();
+            if (issuer) tma_store_3d(map, cbuf, col0, pr.c0, atom0, add);
         };
+        float acc[64];
+        int it = 0;
         for (int t = 0; t < my_tiles; ++t) {
-            const int b = t & 1;
-            mbar_wait(&tmem_full[b], (t >> 1) & 1);
-            tc_fence_after();
             const int atom0 = (rank + t * nctas) * pr.na;
             const int atom = atom0 + row / pr.gs;
             const bool valid = row < pr.gs * pr.na && atom < P.n_atoms;
-#pragma unroll 1
-            for (int cb = 0; cb < TILE / 32; ++cb) {
-                float v[32];
-                tc_ld32(tmem + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)(b * TILE + cb * 32), v);
+#pragma unroll
+            for (int j = 0; j < 64; ++j) acc[j] = 0.f;
+            for (int c = 0; c < NCHUNK; ++c, ++it) {
+                const int b = it & 1;
+                mbar_wait(&tmem_full[b], (it >> 1) & 1);
+                tc_fence_after();
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    float v[32];
+                    tc_ld32(tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)(b * TILE + grp * 64 + half * 32), v);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) acc[half * 32 + j] += v[j];
+                }
+                tc_fence_before();
+                mbar_arrive(&tmem_empty[b]);
+            }
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int col0 = grp * 64 + half * 32;
+                float* v = acc + half * 32;
                 if (scale) {
-                    if (pr.C2) stage_out(v, mC2, cb * 32, atom0, false);
+                    if (pr.C2) stage_out(v, mC2, col0, atom0, false);
                     if (valid) {
-                        const float4* sc = reinterpret_cast<const float4*>(pr.aux + ((size_t)atom * 3 + pr.g) * TILE + cb * 32);
+                        const float4* sc = reinterpret_cast<const float4*>(pr.aux + ((size_t)atom * 3 + pr.g) * TILE + col0);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             const float4 q = sc[j];
@@ -296,13 +325,11 @@ tc_mix_kernel(const __grid_constant__ Maps M, const __grid_constant__ Params P) 
                         }
                     }
                 }
-                stage_out(v, mC, cb * 32, atom0, P.accumulate != 0);
+                stage_out(v, mC, col0, atom0, P.accumulate != 0);
             }
-            tc_fence_before();
-            mbar_arrive(&tmem_empty[b]);
         }
         if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-    } else if (warp >= 8) {
+    } else if (warp >= 8 && warp < 12) {
         // ================= split warps
         const int tid = threadIdx.x - 256;
         mbar_wait(b_full, 0);
@@ -418,7 +445,7 @@ static inline int launch(int epi, const GemmBatch& b, cudaStream_t stream) {
     P.n_atoms = n_atoms;
     P.epi = epi;
     P.accumulate = b.p[0].accumulate;
-    tc_mix_kernel<<<(unsigned)used, THREADS, SMEM_BYTES, stream>>>(M, P);
+    tc_mix_kernel<<<(unsigned)used, MIX_THREADS, SMEM_BYTES, stream>>>(M, P);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }

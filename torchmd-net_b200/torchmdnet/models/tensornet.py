@@ -184,9 +184,9 @@ class TensorNet(FusedRepresentation):
                                           resize_to_fit=not static_shapes, long_edge_index=True)
         self._init_fused()
         self.filter_mode = "exact"
-        # MLP GEMMs: "fp32" = exact fp32 FFMA (default, 1e-5 parity bar); "tf32x3" = tcgen05 three-product tf32 (own,
-        # looser tolerance: the tensor-core accumulator truncates).  The channel mixes always run on the tensor cores.
-        self.gemm_mode = "fp32"
+        # MLP GEMMs: "tf32x3" (default) = tcgen05 three-product tf32 with the K chunks summed in fp32 outside the tensor
+        # core (rms error below an fp32 FFMA GEMM); "fp32" = fp32 FFMA kernel.  The channel mixes always use tcgen05.
+        self.gemm_mode = "tf32x3"
         self.reset_parameters()
 
     def reset_parameters(self):

@@ -100,9 +100,9 @@ class TorchMD_ET(FusedRepresentation):
             for _ in range(num_layers)])
         self.out_norm = nn.LayerNorm(hidden_channels, dtype=dtype)
         self._init_fused()
-        # "fp32": exact fp32 FFMA projections (default, 1e-5 parity bar); "tf32x3": tcgen05 tensor cores with the
-        # three-product tf32 split, ~1e-5 relative on energies through the deep ET stack (tests: 3e-5)
-        self.gemm_mode = "fp32"
+        # projections: "tf32x3" (default) = tcgen05 three-product tf32 with the K chunks summed in fp32 outside the
+        # tensor core (rms error below an fp32 FFMA GEMM); "fp32" = fp32 FFMA kernel
+        self.gemm_mode = "tf32x3"
         self.reset_parameters()
 
     def reset_parameters(self):
