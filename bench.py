@@ -505,6 +505,12 @@ def main():
     families = {k: {"launches_per_step": c / n_prof, "us_per_step": m / n_prof * 1e3} for k, (c, m) in
                 sorted(fam.items(), key=lambda kv: -kv[1][1])}
 
+    # which GEMM kernels this launch size selected (families observed by the library's own timers)
+    gemm_names = {"node_gemm_tc": "tcgen05 tf32x3 (three-product split, fp32 chunk sums)",
+                  "node_gemm_small": "latency-oriented fp32 FFMA (whole-K panels via cp.async, small systems)",
+                  "node_gemm": "tiled fp32 FFMA"}
+    gemm_desc = "; ".join("%s: %s x%d/step" % (k, v, round(fam[k][0] / n_prof)) for k, v in gemm_names.items() if k in fam)
+
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         v, cores, sample, _ = cpu_reference_steps(args.workload, hp, args, 3, 1)
@@ -515,8 +521,7 @@ def main():
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD_DESC[args.workload], "atoms_per_gpu": N, "molecules_per_gpu": n_mol,
                        "edges_per_gpu": E, "filter_mode": args.filter,
-                       "gemm": ("channel mixes: tcgen05 tf32x3; " if hp["model"] == "tensornet" else "") +
-                               ("node GEMMs: tcgen05 tf32x3" if args.et_gemm == "tf32x3" else "node GEMMs: fp32 FFMA"),
+                       "gemm": gemm_desc,
                        "neighbor_strategy": rm.distance.strategy,
                        "l2": "flushed (512 MiB write) before every timed step",
                        "step": "one CUDA graph replay: neighbour list + CSR + forward + analytic backward",

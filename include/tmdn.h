@@ -70,6 +70,14 @@ long long tmdn_launch_count(void);
 int tmdn_profile_enable(int on);
 int tmdn_profile_report(char* buf, size_t buf_bytes);
 
+/* Kernel-selection knobs (new; for A/B measurements and so that tests can force each path).  Keys:
+ *   "small_gemm" 1 = node GEMMs / channel mixes of small systems use the latency-oriented fp32 kernel (default 1)
+ *   "lpt_rows"   1 = edge kernels of small systems visit rows in order of decreasing degree (default 1)
+ *   "pdl"        1 = dependent kernels are launched with programmatic stream serialisation (default 1)
+ * Returns the previous value (>= 0); value < 0 only queries; -1 for an unknown key (tmdn_last_error says which).
+ * Process-wide. */
+int tmdn_set_tuning(const char* key, int value);
+
 /* ---------------------------------------------------------------- neighbor list
  * Semantics = the reference CUDA op: all pairs of atoms of the same batch with
  * cutoff_lower^2 <= d^2 < cutoff_upper^2; delta = pos[i]-pos[j] (minimum image if use_periodic:

@@ -20,9 +20,18 @@ def ops():
     return torch.ops.torchmdnet_b200
 
 
+@pytest.fixture(params=[1, 0], ids=["small_gemm", "tiled"])
+def small(ops, request):
+    """Both kernel selections for small launches: the latency-oriented fp32 kernel (default) and the throughput
+    kernels (tcgen05 for H = 128 / tiled FFMA) that large systems use."""
+    old = ops.set_tuning("small_gemm", request.param)
+    yield request.param
+    ops.set_tuning("small_gemm", old)
+
+
 @pytest.mark.parametrize("n", [1, 7, 25, 42, 43, 128, 166, 1000, 20011])
 @pytest.mark.parametrize("H", [128, 64])
-def test_channel_mix_matches_fp64(ops, n, H):
+def test_channel_mix_matches_fp64(ops, small, n, H):
     g = torch.Generator().manual_seed(n * 7 + H)
     x = (torch.randn(n, 9, H, generator=g) * torch.logspace(-2, 1, 9).view(1, 9, 1)).cuda()
     w = (torch.randn(3, H, H, generator=g) / H ** 0.5).cuda()
@@ -34,7 +43,7 @@ def test_channel_mix_matches_fp64(ops, n, H):
     assert (err <= 2e-6 * bound + 1e-30).all(), float((err / (bound + 1e-30)).max())
 
 
-def test_channel_mix_accumulates(ops):
+def test_channel_mix_accumulates(ops, small):
     g = torch.Generator().manual_seed(5)
     x = torch.randn(333, 9, 128, generator=g).cuda()
     w = (torch.randn(3, 128, 128, generator=g) / 128 ** 0.5).cuda()
@@ -54,7 +63,7 @@ def test_channel_mix_is_repeatable(ops):
 
 
 # ------------------------------------------------------------------ general tcgen05 GEMM (csrc/tc_gemm.cuh) through the ET model
-def test_tc_gemm_against_ffma_through_et(monkeypatch):
+def test_tc_gemm_against_ffma_through_et(monkeypatch, small):
     """The plain node GEMMs run on tensor cores by default; the same model evaluated with the fp32 FFMA kernels
     (TMDN_TC_GEMM=0 is read once per process, so the comparison is made against the oracle in test_gpu_et.py and,
     here, as a direct operator check on odd shapes through channel_mix's sibling entry point)."""
@@ -62,7 +71,8 @@ def test_tc_gemm_against_ffma_through_et(monkeypatch):
     if not hasattr(ops_, "node_gemm"):
         pytest.skip("node_gemm op not exported")
     g = torch.Generator().manual_seed(11)
-    for (M, N, K) in [(1, 64, 64), (166, 384, 256), (2306, 640, 128), (5000, 128, 640), (777, 64, 128), (130, 36, 44)]:
+    for (M, N, K) in [(1, 64, 64), (166, 384, 256), (2306, 640, 128), (5000, 128, 640), (777, 64, 128), (130, 36, 44),
+                      (166, 128, 384), (166, 256, 128), (40, 100, 768), (33, 7, 772), (500, 384, 640)]:
         a = torch.randn(M, K, generator=g).cuda()
         w = (torch.randn(N, K, generator=g) / K ** 0.5).cuda()
         bias = torch.randn(N, generator=g).cuda()

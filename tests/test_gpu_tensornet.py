@@ -89,6 +89,64 @@ def test_full_size_hparams_match_reference(cfg, mode):
     check(y, f, g["y"], g["forces"])
 
 
+def test_kernel_selection_knobs_agree():
+    """tmdn_set_tuning: small systems take the latency-oriented GEMM and visit rows in order of decreasing degree.
+    The row order only changes which CTA handles a row (bitwise identical results); the GEMM choice changes the
+    summation order (same tolerance against the reference's numbers)."""
+    from torchmdnet.models.model import create_model
+    ops = torch.ops.torchmdnet_b200
+    g = load_npz("model_TensorNet-SPICE.npz")
+    seed_everything(int(g["seed"]))
+    m = create_model(g["hparams"]).cuda().eval()
+    m.representation_model.filter_mode = "table"
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    old = {k: ops.set_tuning(k, -1) for k in ("small_gemm", "lpt_rows", "pdl")}
+    assert old == {"small_gemm": 1, "lpt_rows": 1, "pdl": 1}
+    with pytest.raises(RuntimeError):
+        ops.set_tuning("no_such_knob", 1)
+    out = {}
+    try:
+        for sg in (1, 0):
+            for lpt in (1, 0):
+                ops.set_tuning("small_gemm", sg)
+                ops.set_tuning("lpt_rows", lpt)
+                y, f = m(z, pos, batch)
+                check(y, f, g["y"], g["forces"])
+                out[sg, lpt] = (y.clone(), f.clone())
+        # programmatic dependent launch only overlaps launch latency with the predecessor's tail: same bits, eagerly
+        # and as a captured graph
+        ops.set_tuning("small_gemm", 1)
+        ops.set_tuning("lpt_rows", 1)
+        for pdl in (0, 1):
+            ops.set_tuning("pdl", pdl)
+            for _ in range(3):
+                y, f = m(z, pos, batch)
+                assert torch.equal(y, out[1, 1][0]) and torch.equal(f, out[1, 1][1]), pdl
+            gr = torch.cuda.CUDAGraph()
+            s_ = torch.cuda.Stream()
+            s_.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s_):
+                m(z, pos, batch)
+                with torch.cuda.graph(gr, stream=s_):
+                    yg, fg = m(z, pos, batch)
+            torch.cuda.current_stream().wait_stream(s_)
+            for _ in range(5):
+                gr.replay()
+            torch.cuda.synchronize()
+            assert torch.equal(yg, out[1, 1][0]) and torch.equal(fg, out[1, 1][1]), ("graph", pdl)
+    finally:
+        for k, v in old.items():
+            ops.set_tuning(k, v)
+    for sg in (1, 0):
+        assert torch.equal(out[sg, 1][0], out[sg, 0][0]) and torch.equal(out[sg, 1][1], out[sg, 0][1])
+    n = z.shape[0]
+    order = m.representation_model.debug_buffer("row_order", n, int(batch.max()) + 1, torch.int32)[:n].cpu().long()
+    rp = m.representation_model.debug_buffer("row_ptr", n, int(batch.max()) + 1, torch.int32)[:n + 1].cpu().long()
+    deg = rp[1:] - rp[:-1]
+    assert torch.equal(order.sort().values, torch.arange(n))
+    assert bool((deg[order][:-1] >= deg[order][1:]).all())
+
+
 def test_reference_expected_pkl_row():
     """tests/expected.pkl, TensorNet/Scalar row (tests/test_model.py:137-188): 5 atoms in 2 molecules."""
     from torchmdnet.models.model import create_model

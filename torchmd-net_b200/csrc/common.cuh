@@ -20,6 +20,10 @@ struct KTimer {
     cudaStream_t stream;
 };
 
+// process-wide tuning knobs (tmdn_set_tuning, defined in scan.cu)
+enum { TMDN_TUNE_SMALL_GEMM = 0, TMDN_TUNE_LPT_ROWS = 1, TMDN_TUNE_PDL = 2, TMDN_TUNE_COUNT = 3 };
+extern int g_tmdn_tuning[TMDN_TUNE_COUNT];
+
 #define TMDN_CHECK_ARG(cond, ...)                 \
     do {                                          \
         if (!(cond)) {                            \
@@ -54,6 +58,37 @@ struct KTimer {
         int rc__ = (call);             \
         if (rc__ != TMDN_OK) return rc__; \
     } while (0)
+
+// ------------------------------------------------------------------ kernel launch (programmatic dependent launch)
+// Every kernel of the library starts with pdl_sync(): it lets the NEXT kernel of the stream be scheduled as soon as
+// all CTAs of this one are resident (griddepcontrol.launch_dependents) and then waits until the PREVIOUS kernel has
+// completed and its writes are visible (griddepcontrol.wait).  Launched through launch_k with the programmatic
+// stream-serialisation attribute, consecutive kernels overlap launch latency, CTA scheduling and the prologue before
+// pdl_sync with the tail of their predecessor; data dependencies are unchanged because nothing is read or written
+// before the wait and completion is transitive along the stream.  Without the attribute both instructions are
+// no-ops.  A step of a small system is ~45 dependent launches of 3-30 us each, so this is where its time goes.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_sync() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                   Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_tmdn_tuning[TMDN_TUNE_PDL] ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(static_cast<Args&&>(args))...);
+}
+#endif
 
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }

@@ -10,6 +10,7 @@ namespace {
 
 __global__ void csr_count_kernel(const int32_t* __restrict__ nbr, const int32_t* __restrict__ num_found,
                                  long long max_pairs, int target_row, int* __restrict__ row_cnt) {
+    pdl_sync();
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     long long ne = *num_found;
     ne = ne < max_pairs ? ne : max_pairs;
@@ -21,6 +22,7 @@ __global__ void csr_count_kernel(const int32_t* __restrict__ nbr, const int32_t*
 __global__ void csr_fill_kernel(const int32_t* __restrict__ nbr, const int32_t* __restrict__ num_found,
                                 long long max_pairs, int target_row, const int* __restrict__ row_ptr,
                                 int* __restrict__ cursor, int* __restrict__ col_tmp, int* __restrict__ eid_tmp) {
+    pdl_sync();
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     long long ne = *num_found;
     ne = ne < max_pairs ? ne : max_pairs;
@@ -39,6 +41,7 @@ csr_sort_rows_kernel(const int* __restrict__ row_ptr, int n_atoms, const int* __
                      const int* __restrict__ eid_tmp, const float* __restrict__ deltas,
                      const float* __restrict__ dist, int target_row, int* __restrict__ col,
                      float4* __restrict__ geom) {
+    pdl_sync();
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= n_atoms) return;
@@ -99,13 +102,13 @@ extern "C" int tmdn_csr_from_pairs(const int32_t* neighbors, const float* deltas
     // row_cnt and cursor are adjacent in the arena: one memset clears both
     TMDN_CUDA(cudaMemsetAsync(w.row_cnt, 0, (size_t)((char*)w.col_tmp - (char*)w.row_cnt), stream));
     const unsigned eb = (unsigned)cdiv(max_pairs, 256);
-    csr_count_kernel<<<eb, 256, 0, stream>>>(neighbors, num_found, (long long)max_pairs, target_row, w.row_cnt);
+    launch_k(csr_count_kernel, eb, 256, 0, stream, neighbors, num_found, (long long)max_pairs, target_row, w.row_cnt);
     TMDN_LAUNCH_CHECK();
     TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));
-    csr_fill_kernel<<<eb, 256, 0, stream>>>(neighbors, num_found, (long long)max_pairs, target_row, row_ptr, w.cursor,
+    launch_k(csr_fill_kernel, eb, 256, 0, stream, neighbors, num_found, (long long)max_pairs, target_row, row_ptr, w.cursor,
                                             w.col_tmp, w.eid_tmp);
     TMDN_LAUNCH_CHECK();
-    csr_sort_rows_kernel<<<(unsigned)cdiv(n_atoms, 4), 128, 0, stream>>>(row_ptr, (int)n_atoms, w.col_tmp, w.eid_tmp,
+    launch_k(csr_sort_rows_kernel, (unsigned)cdiv(n_atoms, 4), 128, 0, stream, row_ptr, (int)n_atoms, w.col_tmp, w.eid_tmp,
                                                                          deltas, distances, target_row, col,
                                                                          (float4*)geom);
     TMDN_LAUNCH_CHECK();

@@ -59,6 +59,7 @@ template <bool FILL>
 __global__ void __launch_bounds__(CD_WARPS * 32)
 csr_brute_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int n, int n_rows, Box3<float> box,
                  int periodic, float lo2, float hi2, EdgeOut out) {
+    pdl_sync();
     const int i = blockIdx.x * CD_WARPS + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (i >= n_rows) return;
@@ -94,6 +95,7 @@ __global__ void cell_rank_kernel(const SortedAtom<float>* __restrict__ tmp, cons
                                  const int* __restrict__ cell_start, const int* __restrict__ cell_of,
                                  const int* __restrict__ slot_of, int n, SortedAtom<float>* __restrict__ spos,
                                  long long* __restrict__ sbatch) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int c = cell_of[i];
@@ -108,6 +110,7 @@ __global__ void cell_rank_kernel(const SortedAtom<float>* __restrict__ tmp, cons
 // num_found = edges found; row pointers are clamped to the capacity so that an overflowing list is truncated
 // (rows past the capacity become empty) instead of read out of bounds by the model kernels
 __global__ void csr_finish_kernel(int* __restrict__ row_ptr, int n, long long cap, int32_t* __restrict__ num_found) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i > n) return;
     const int v = row_ptr[i];
@@ -200,37 +203,37 @@ extern "C" int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int
     if (strategy == TMDN_CELL) {
         TMDN_CUDA(cudaMemsetAsync(w.cell_cnt, 0, sizeof(int) * (g.ncells + 1), stream));
         const int blocks = (int)cdiv(n, 256);
-        cell_assign_kernel<float><<<blocks, 256, 0, stream>>>(pos, n, g, w.cell_cnt, w.cell_of, w.slot_of);
+        launch_k(cell_assign_kernel<float>, blocks, 256, 0, stream, pos, n, g, w.cell_cnt, w.cell_of, w.slot_of);
         TMDN_LAUNCH_CHECK();
         TMDN_TRY(tmdn_scan_exclusive_i32(w.cell_cnt, w.cell_start, g.ncells, w.cell_scan_tmp, stream));
-        cell_scatter_kernel<float><<<blocks, 256, 0, stream>>>(pos, batch, n, w.cell_start, w.cell_of, w.slot_of, w.tmp,
+        launch_k(cell_scatter_kernel<float>, blocks, 256, 0, stream, pos, batch, n, w.cell_start, w.cell_of, w.slot_of, w.tmp,
                                                                w.tmp_batch);
         TMDN_LAUNCH_CHECK();
-        cell_rank_kernel<<<blocks, 256, 0, stream>>>(w.tmp, w.tmp_batch, w.cell_start, w.cell_of, w.slot_of, n, w.spos,
+        launch_k(cell_rank_kernel, blocks, 256, 0, stream, w.tmp, w.tmp_batch, w.cell_start, w.cell_of, w.slot_of, n, w.spos,
                                                      w.sbatch);
         TMDN_LAUNCH_CHECK();
         CellTileOut<float> to{};
         to.row_cnt = w.row_cnt; to.row_ptr = row_ptr; to.col = col; to.geom = (float4*)geom;
         to.cap = (long long)max_edges; to.n_rows = nr;
-        cell_tile_kernel<float, CT_CSR_COUNT><<<g.ncells, CT_THREADS, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g,
+        launch_k(cell_tile_kernel<float, CT_CSR_COUNT>, g.ncells, CT_THREADS, 0, stream, w.spos, w.sbatch, w.cell_start, g,
                                                                                   use_periodic, lo2, hi2, to);
         TMDN_LAUNCH_CHECK();
         TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));
         TMDN_CUDA(cudaMemsetAsync(w.row_cnt, 0, sizeof(int) * ((size_t)n + 1), stream));   // now the fill cursor
-        cell_tile_kernel<float, CT_CSR_FILL><<<g.ncells, CT_THREADS, 0, stream>>>(w.spos, w.sbatch, w.cell_start, g,
+        launch_k(cell_tile_kernel<float, CT_CSR_FILL>, g.ncells, CT_THREADS, 0, stream, w.spos, w.sbatch, w.cell_start, g,
                                                                                  use_periodic, lo2, hi2, to);
         TMDN_LAUNCH_CHECK();
     } else {
         Box3<float> b;
         for (int r = 0; r < 3; ++r)
             for (int c = 0; c < 3; ++c) b.m[r][c] = (use_periodic && box) ? (float)box[3 * r + c] : 0.f;
-        csr_brute_kernel<false><<<rgrid, CD_WARPS * 32, 0, stream>>>(pos, batch, n, nr, b, use_periodic, lo2, hi2, cnt);
+        launch_k(csr_brute_kernel<false>, rgrid, CD_WARPS * 32, 0, stream, pos, batch, n, nr, b, use_periodic, lo2, hi2, cnt);
         TMDN_LAUNCH_CHECK();
         TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));
-        csr_brute_kernel<true><<<rgrid, CD_WARPS * 32, 0, stream>>>(pos, batch, n, nr, b, use_periodic, lo2, hi2, fill);
+        launch_k(csr_brute_kernel<true>, rgrid, CD_WARPS * 32, 0, stream, pos, batch, n, nr, b, use_periodic, lo2, hi2, fill);
         TMDN_LAUNCH_CHECK();
     }
-    csr_finish_kernel<<<(unsigned)cdiv(n + 1, 256), 256, 0, stream>>>(row_ptr, n, (long long)max_edges, num_found);
+    launch_k(csr_finish_kernel, (unsigned)cdiv(n + 1, 256), 256, 0, stream, row_ptr, n, (long long)max_edges, num_found);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }

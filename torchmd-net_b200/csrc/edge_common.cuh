@@ -56,6 +56,14 @@ template <int NV> __device__ __forceinline__ void atom_reduce(float (&v)[NV], fl
         v[k] = t;
     }
 }
+// row handled by this (blockIdx.x, threadIdx.z): identity, or through the visiting order of small systems
+__device__ __forceinline__ int edge_row(const int* __restrict__ order, int N, bool& valid) {
+    int i = blockIdx.x * blockDim.z + threadIdx.z;
+    valid = i < N;
+    if (order != nullptr && valid) i = order[i];
+    return i;
+}
+
 struct EdgeLaunch { dim3 block; unsigned grid; size_t smem; };
 // s_red (<= 32 warps x 3 values per atom) lives at the start of dynamic shared memory, slice partials after it
 constexpr int EDGE_RED_FLOATS = 128;

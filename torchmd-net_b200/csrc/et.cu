@@ -71,6 +71,7 @@ template <int HDC> __device__ __forceinline__ float seg_sum_t(float v, int hd) {
 
 __global__ void et_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ z32, int n, int max_z,
                                const int32_t* __restrict__ num_found, long long max_edges, int32_t* __restrict__ status) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) {
         const int f = *num_found;
@@ -93,6 +94,7 @@ __global__ void __launch_bounds__(1024)
 et_embed_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom,
              const int* __restrict__ z32, const float* __restrict__ emb, const float* __restrict__ ne_emb, Tab tb, int N,
              int H, float* __restrict__ out, int ldo) {
+    pdl_sync();
     extern __shared__ float smem[];
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
@@ -118,6 +120,7 @@ et_embed_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const
 // ------------------------------------------------------------------ LayerNorm over H (block = (H,1,A))
 __global__ void et_ln_fwd(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                           float* __restrict__ y, int ldy, float* __restrict__ stat, int N, int H) {
+    pdl_sync();
     __shared__ float s_red[EDGE_RED_FLOATS * 4];
     const int h = threadIdx.x;
     const int i = blockIdx.x * blockDim.z + threadIdx.z;
@@ -136,6 +139,7 @@ __global__ void et_ln_fwd(const float* __restrict__ x, const float* __restrict__
 // gx (+)= LN^T(gy): gy has row stride ldg
 __global__ void et_ln_bwd(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ stat,
                           const float* __restrict__ gy, int ldg, float* __restrict__ gx, int accumulate, int N, int H) {
+    pdl_sync();
     __shared__ float s_red[EDGE_RED_FLOATS * 4];
     const int h = threadIdx.x;
     const int i = blockIdx.x * blockDim.z + threadIdx.z;
@@ -167,6 +171,7 @@ __global__ void __launch_bounds__(ET_FWD_THREADS)
 et_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
             float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
             int N, int H_, float* __restrict__ xa, float* __restrict__ va) {
+    pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
@@ -222,6 +227,7 @@ et_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
 __global__ void et_update_fwd(const float* __restrict__ x, const float* __restrict__ vec, const float* __restrict__ vp,
                               const float* __restrict__ o, const float* __restrict__ va, float* __restrict__ xn,
                               float* __restrict__ vecn, long long total, int H) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / H;
@@ -242,6 +248,7 @@ __global__ void et_update_fwd(const float* __restrict__ x, const float* __restri
 // ------------------------------------------------------------------ gated equivariant block pieces (models/utils.py:496-522)
 // cat[i, hin + c] = || vb[i,:,c] ||
 __global__ void et_gate_norm_fwd(const float* __restrict__ vb, float* __restrict__ cat, long long total, int hin) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / hin;
@@ -253,6 +260,7 @@ __global__ void et_gate_norm_fwd(const float* __restrict__ vb, float* __restrict
 // block with scalar activation: xo = act(h2[:, :out]) -> xout (row stride ldx); vo = h2[:, out:] * vec2
 __global__ void et_gate_out_fwd(const float* __restrict__ h2, const float* __restrict__ vec2, int act,
                                 float* __restrict__ xout, int ldx, float* __restrict__ vo, long long total, int out) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / out;
@@ -265,6 +273,7 @@ __global__ void et_gate_out_fwd(const float* __restrict__ h2, const float* __res
 // e_i = (w . a_i + b) * std ; one warp per atom
 __global__ void et_head_energy(const float* __restrict__ a, const float* __restrict__ w, const float* __restrict__ b,
                                float stdv, float* __restrict__ e_atom, int N, int K) {
+    pdl_sync();
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (i >= N) return;
@@ -275,6 +284,7 @@ __global__ void et_head_energy(const float* __restrict__ a, const float* __restr
 }
 __global__ void __launch_bounds__(128) et_mol_reduce(const float* __restrict__ e_atom, const int64_t* __restrict__ batch,
                                                      int N, float mean, float* __restrict__ energy) {
+    pdl_sync();
     __shared__ float s_part[128];
     const long long m = blockIdx.x;
     int lo = 0, hi = N;
@@ -298,6 +308,7 @@ __global__ void __launch_bounds__(128) et_mol_reduce(const float* __restrict__ e
 // d[i,n] = std * w[n] * act'(h0[i,n])      (seed of dE/d(update_net.0 output) of the last gated block)
 __global__ void et_head_seed_bwd(const float* __restrict__ h0, const float* __restrict__ w, float stdv, int act,
                                  float* __restrict__ d, long long total, int K) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     d[idx] = stdv * w[idx % K] * act_grad(act, h0[idx]);
@@ -305,6 +316,7 @@ __global__ void et_head_seed_bwd(const float* __restrict__ h0, const float* __re
 // g_vb[i,:,c] = g_cat[i,hin+c] * vb[i,:,c] / ||vb[i,:,c]||   (0 where the norm is 0: models/utils.py:499-512)
 __global__ void et_gate_norm_bwd(const float* __restrict__ vb, const float* __restrict__ cat,
                                  const float* __restrict__ g_cat, float* __restrict__ g_vb, long long total, int hin) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / hin;
@@ -318,6 +330,7 @@ __global__ void et_gate_norm_bwd(const float* __restrict__ vb, const float* __re
 __global__ void et_gate_out_bwd(const float* __restrict__ h2, const float* __restrict__ vec2, int act,
                                 const float* __restrict__ g_xo, int ldx, const float* __restrict__ g_vo,
                                 float* __restrict__ g_h2, float* __restrict__ g_vec2, long long total, int out) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / out;
@@ -339,6 +352,7 @@ __global__ void et_gate_out_bwd(const float* __restrict__ h2, const float* __res
 __global__ void et_update_bwd(const float* __restrict__ g_x, const float* __restrict__ g_vec,
                               const float* __restrict__ vp, const float* __restrict__ o, float* __restrict__ g_o,
                               float* __restrict__ g_vp, float* __restrict__ g_vec_new, long long total, int H) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / H;
@@ -375,6 +389,7 @@ et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
             float lo, float hi, int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ vec,
             const float* __restrict__ g_xa, const float* __restrict__ g_va, int N, int H_, float* __restrict__ g_qkv,
             float* __restrict__ g_vec_new, float* __restrict__ gpos) {
+    pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_red = smem;
@@ -495,6 +510,7 @@ __global__ void __launch_bounds__(512)
 et_final_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom,
              const int* __restrict__ z32, const float* __restrict__ ne_emb, Tab tb, const float* __restrict__ g_xn,
              const float* __restrict__ gpos, float* __restrict__ forces, int N, int H) {
+    pdl_sync();
     extern __shared__ float smem[];
     float* s_red = smem;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
@@ -690,7 +706,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
                                     w.num_found, w.graph_ws, w.graph_ws_bytes, stream_));
     }
     TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
-    ET_K("et_prep", et_prep_kernel<<<(unsigned)cdiv(N, 256), 256, 0, stream>>>(z, w.z32, N, m->max_z, w.num_found,
+    ET_K("et_prep", launch_k(et_prep_kernel, (unsigned)cdiv(N, 256), 256, 0, stream, z, w.z32, N, m->max_z, w.num_found,
                                                                                 (long long)P, status));
     const float4* geom = (const float4*)w.geom;
     const float inv_h = (float)((double)m->n_int / (double)hi);
@@ -706,11 +722,11 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
 
     // ---- embedding (+ neighbour embedding)
     if (m->has_neighbor_embedding) {
-        ET_K("et_embed_fwd", et_embed_fwd<true><<<e1.grid, e1.block, e1.smem, stream>>>(
+        ET_K("et_embed_fwd", launch_k(et_embed_fwd<true>, e1.grid, e1.block, e1.smem, stream, 
                                  w.row_ptr, w.col, geom, w.z32, m->emb, m->ne_emb, ne_tab, N, H, w.cat0, 2 * H));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.cat0, 2 * H, m->ne_comb_w, m->ne_comb_b, w.X[0], H, N, H, 2 * H), stream, tc));
     } else {
-        ET_K("et_embed_fwd", et_embed_fwd<false><<<e1.grid, e1.block, e1.smem, stream>>>(
+        ET_K("et_embed_fwd", launch_k(et_embed_fwd<false>, e1.grid, e1.block, e1.smem, stream, 
                                  w.row_ptr, w.col, geom, w.z32, m->emb, nullptr, ne_tab, N, H, w.X[0], H));
     }
     TMDN_CUDA(cudaMemsetAsync(w.VEC[0], 0, sizeof(float) * 3 * (size_t)NH, stream));
@@ -718,62 +734,62 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     for (int l = 0; l < L; ++l) {
         const tmdn_et_layer& ly = m->layer[l];
         const Tab tb{(const float4*)ly.table, inv_h, m->n_int};
-        ET_K("et_ln_fwd", et_ln_fwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, ly.ln_b, w.xl, H, w.stat[l], N, H));
+        ET_K("et_ln_fwd", launch_k(et_ln_fwd, lgrid, lblock, 0, stream, w.X[l], ly.ln_w, ly.ln_b, w.xl, H, w.stat[l], N, H));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.xl, H, ly.qkv_w, ly.qkv_b, w.QKV[l], 5 * H, N, 5 * H, H), stream, tc));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.VEC[l], H, ly.vp_w, nullptr, w.VP[l], 3 * H, 3 * N, 3 * H, H), stream, tc));
         if (H == 128 && hd == 16)
-            ET_K("et_edge_fwd", (et_edge_fwd<1, 128, 16><<<e4.grid, e4.block, e4.smem, stream>>>(
+            ET_K("et_edge_fwd", (launch_k(et_edge_fwd<1, 128, 16>, e4.grid, e4.block, e4.smem, stream, 
                                     w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], N, H, w.xa,
                                     w.va)));
         else
-            ET_K("et_edge_fwd", (et_edge_fwd<1><<<e4.grid, e4.block, e4.smem, stream>>>(
+            ET_K("et_edge_fwd", (launch_k(et_edge_fwd<1>, e4.grid, e4.block, e4.smem, stream, 
                                     w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], N, H, w.xa,
                                     w.va)));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.xa, H, ly.o_w, ly.o_b, w.O[l], 3 * H, N, 3 * H, H), stream, tc));
-        ET_K("et_update_fwd", et_update_fwd<<<egrid, 256, 0, stream>>>(w.X[l], w.VEC[l], w.VP[l], w.O[l], w.va,
+        ET_K("et_update_fwd", launch_k(et_update_fwd, egrid, 256, 0, stream, w.X[l], w.VEC[l], w.VP[l], w.O[l], w.va,
                                                                        w.X[l + 1], w.VEC[l + 1], NH, H));
     }
     // ---- out_norm written straight into the first half of cat1 = [xo | vec1]
-    ET_K("et_ln_fwd", et_ln_fwd<<<lgrid, lblock, 0, stream>>>(w.X[L], m->out_ln_w, m->out_ln_b, w.cat1, 2 * H, w.stat[L],
+    ET_K("et_ln_fwd", launch_k(et_ln_fwd, lgrid, lblock, 0, stream, w.X[L], m->out_ln_w, m->out_ln_b, w.cat1, 2 * H, w.stat[L],
                                                               N, H));
     // ---- gated block 1: H -> H/2 (scalar activation)
     const tmdn_et_gated& g1 = m->head[0];
     const tmdn_et_gated& g2 = m->head[1];
     TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.VEC[L], H, g1.w1, nullptr, w.vb1, H, 3 * N, H, H), stream, tc));
     TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.VEC[L], H, g1.w2, nullptr, w.vec2_1, H2, 3 * N, H2, H), stream, tc));
-    ET_K("et_gate_norm_fwd", et_gate_norm_fwd<<<egrid, 256, 0, stream>>>(w.vb1, w.cat1, NH, H));
+    ET_K("et_gate_norm_fwd", launch_k(et_gate_norm_fwd, egrid, 256, 0, stream, w.vb1, w.cat1, NH, H));
     {
         GemmP p = gemm_desc(w.cat1, 2 * H, g1.u0_w, g1.u0_b, w.a0_1, H, N, H, 2 * H);
         p.C2 = w.h0_1; p.act = act;
         TMDN_TRY(node_gemm1(EPI_ACT, p, stream, tc));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.a0_1, H, g1.u2_w, g1.u2_b, w.h2_1, H, N, H, H), stream, tc));
     }
-    ET_K("et_gate_out_fwd", et_gate_out_fwd<<<hgrid, 256, 0, stream>>>(w.h2_1, w.vec2_1, act, w.cat2, H, w.v1,
+    ET_K("et_gate_out_fwd", launch_k(et_gate_out_fwd, hgrid, 256, 0, stream, w.h2_1, w.vec2_1, act, w.cat2, H, w.v1,
                                                                        (long long)N * H2, H2));
     // ---- gated block 2: H/2 -> 1 (its vector output does not reach the energy)
     TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.v1, H2, g2.w1, nullptr, w.vb2, H2, 3 * N, H2, H2), stream, tc));
-    ET_K("et_gate_norm_fwd", et_gate_norm_fwd<<<hgrid, 256, 0, stream>>>(w.vb2, w.cat2, (long long)N * H2, H2));
+    ET_K("et_gate_norm_fwd", launch_k(et_gate_norm_fwd, hgrid, 256, 0, stream, w.vb2, w.cat2, (long long)N * H2, H2));
     {
         GemmP p = gemm_desc(w.cat2, H, g2.u0_w, g2.u0_b, w.a0_2, H2, N, H2, H);
         p.C2 = w.h0_2; p.act = act;
         TMDN_TRY(node_gemm1(EPI_ACT, p, stream, tc));
     }
-    ET_K("et_head_energy", et_head_energy<<<(unsigned)cdiv(N, 4), 128, 0, stream>>>(w.a0_2, g2.u2_w, g2.u2_b, m->std,
+    ET_K("et_head_energy", launch_k(et_head_energy, (unsigned)cdiv(N, 4), 128, 0, stream, w.a0_2, g2.u2_w, g2.u2_b, m->std,
                                                                                    w.e_atom, N, H2));
-    ET_K("et_mol_reduce", et_mol_reduce<<<(unsigned)n_mol, 128, 0, stream>>>(w.e_atom, batch, N, m->mean, energy));
+    ET_K("et_mol_reduce", launch_k(et_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy));
     if (!forces) return TMDN_OK;
 
     // ================================================================= backward
     TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
     // block 2
-    ET_K("et_head_seed_bwd", et_head_seed_bwd<<<hgrid, 256, 0, stream>>>(w.h0_2, g2.u2_w, m->std, act, w.d_a0_2,
+    ET_K("et_head_seed_bwd", launch_k(et_head_seed_bwd, hgrid, 256, 0, stream, w.h0_2, g2.u2_w, m->std, act, w.d_a0_2,
                                                                          (long long)N * H2, H2));
     TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.d_a0_2, H2, g2.u0_wT, nullptr, w.g_cat2, H, N, H, H2), stream, tc));
-    ET_K("et_gate_norm_bwd", et_gate_norm_bwd<<<hgrid, 256, 0, stream>>>(w.vb2, w.cat2, w.g_cat2, w.g_vb2,
+    ET_K("et_gate_norm_bwd", launch_k(et_gate_norm_bwd, hgrid, 256, 0, stream, w.vb2, w.cat2, w.g_cat2, w.g_vb2,
                                                                          (long long)N * H2, H2));
     TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_vb2, H2, g2.w1T, nullptr, w.g_v1, H2, 3 * N, H2, H2), stream, tc));
     // block 1
-    ET_K("et_gate_out_bwd", et_gate_out_bwd<<<hgrid, 256, 0, stream>>>(w.h2_1, w.vec2_1, act, w.g_cat2, H, w.g_v1, w.g_h2,
+    ET_K("et_gate_out_bwd", launch_k(et_gate_out_bwd, hgrid, 256, 0, stream, w.h2_1, w.vec2_1, act, w.g_cat2, H, w.g_v1, w.g_h2,
                                                                        w.g_vec2, (long long)N * H2, H2));
     {
         GemmP p = gemm_desc(w.g_h2, H, g1.u2_wT, nullptr, w.g_h0, H, N, H, H);
@@ -781,7 +797,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
         TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream, tc));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_h0, H, g1.u0_wT, nullptr, w.g_cat1, 2 * H, N, 2 * H, H), stream, tc));
     }
-    ET_K("et_gate_norm_bwd", et_gate_norm_bwd<<<egrid, 256, 0, stream>>>(w.vb1, w.cat1, w.g_cat1, w.g_vb, NH, H));
+    ET_K("et_gate_norm_bwd", launch_k(et_gate_norm_bwd, egrid, 256, 0, stream, w.vb1, w.cat1, w.g_cat1, w.g_vb, NH, H));
     float* g_vec = w.g_vecA;
     float* g_vec_new = w.g_vecB;
     TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_vb, H, g1.w1T, nullptr, g_vec, H, 3 * N, H, H), stream, tc));
@@ -790,12 +806,12 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
         p.accumulate = 1;
         TMDN_TRY(node_gemm1(EPI_NONE, p, stream, tc));
     }
-    ET_K("et_ln_bwd", et_ln_bwd<<<lgrid, lblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat[L], w.g_cat1, 2 * H, w.g_x, 0, N,
+    ET_K("et_ln_bwd", launch_k(et_ln_bwd, lgrid, lblock, 0, stream, w.X[L], m->out_ln_w, w.stat[L], w.g_cat1, 2 * H, w.g_x, 0, N,
                                                               H));
     for (int l = L - 1; l >= 0; --l) {
         const tmdn_et_layer& ly = m->layer[l];
         const Tab tb{(const float4*)ly.table, inv_h, m->n_int};
-        ET_K("et_update_bwd", et_update_bwd<<<egrid, 256, 0, stream>>>(w.g_x, g_vec, w.VP[l], w.O[l], w.g_o, w.g_vp,
+        ET_K("et_update_bwd", launch_k(et_update_bwd, egrid, 256, 0, stream, w.g_x, g_vec, w.VP[l], w.O[l], w.g_o, w.g_vp,
                                                                        g_vec_new, NH, H));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_o, 3 * H, ly.o_wT, nullptr, w.g_xa, H, N, H, 3 * H), stream, tc));
         {
@@ -804,23 +820,23 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
             TMDN_TRY(node_gemm1(EPI_NONE, p, stream, tc));
         }
         if (H == 128 && hd == 16)
-            ET_K("et_edge_bwd", (et_edge_bwd<1, 128, 16><<<e8b.grid, e8b.block, e8b.smem, stream>>>(
+            ET_K("et_edge_bwd", (launch_k(et_edge_bwd<1, 128, 16>, e8b.grid, e8b.block, e8b.smem, stream, 
                                     w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], w.g_xa,
                                     g_vec, N, H, w.g_qkv, g_vec_new, w.gpos)));
         else
-            ET_K("et_edge_bwd", (et_edge_bwd<1><<<e8b.grid, e8b.block, e8b.smem, stream>>>(
+            ET_K("et_edge_bwd", (launch_k(et_edge_bwd<1>, e8b.grid, e8b.block, e8b.smem, stream, 
                                     w.row_ptr, w.col, geom, tb, lo, hi, m->attn_activation, hd, w.QKV[l], w.VEC[l], w.g_xa,
                                     g_vec, N, H, w.g_qkv, g_vec_new, w.gpos)));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_qkv, 5 * H, ly.qkv_wT, nullptr, w.g_xl, H, N, H, 5 * H), stream, tc));
-        ET_K("et_ln_bwd", et_ln_bwd<<<lgrid, lblock, 0, stream>>>(w.X[l], ly.ln_w, w.stat[l], w.g_xl, H, w.g_x, 1, N, H));
+        ET_K("et_ln_bwd", launch_k(et_ln_bwd, lgrid, lblock, 0, stream, w.X[l], ly.ln_w, w.stat[l], w.g_xl, H, w.g_x, 1, N, H));
         float* t = g_vec; g_vec = g_vec_new; g_vec_new = t;
     }
     if (m->has_neighbor_embedding) {
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_x, H, m->ne_comb_w2T, nullptr, w.g_xn, H, N, H, H), stream, tc));
-        ET_K("et_final_bwd", et_final_bwd<true><<<e8.grid, e8.block, e8.smem, stream>>>(
+        ET_K("et_final_bwd", launch_k(et_final_bwd<true>, e8.grid, e8.block, e8.smem, stream, 
                                  w.row_ptr, w.col, geom, w.z32, m->ne_emb, ne_tab, w.g_xn, w.gpos, forces, N, H));
     } else {
-        ET_K("et_final_bwd", et_final_bwd<false><<<e8.grid, e8.block, e8.smem, stream>>>(
+        ET_K("et_final_bwd", launch_k(et_final_bwd<false>, e8.grid, e8.block, e8.smem, stream, 
                                  w.row_ptr, w.col, geom, w.z32, nullptr, ne_tab, nullptr, w.gpos, forces, N, H));
     }
     return TMDN_OK;

@@ -7,6 +7,7 @@
 //     physical_row(m) = (m / gs) * rpa + c0 + m % gs
 // (identity for gs = rpa = 1, c0 = 0).
 #pragma once
+#include <stdlib.h>
 #include "common.cuh"
 
 enum { EPI_NONE = 0, EPI_ACT = 1, EPI_MULGRAD = 2, EPI_SCALE3 = 3 };
@@ -23,6 +24,7 @@ struct GemmP {
     int gs, c0, rpa, g;
     int accumulate;     // C += result
     int act;
+    int w_static;       // W is a model parameter (not written by a preceding kernel): may be fetched before the PDL wait
 };
 struct GemmBatch {
     GemmP p[3];
@@ -33,6 +35,7 @@ constexpr int GBM = 64, GBN = 64, GBK = 16, GTHREADS = 256;
 
 template <int EPI>
 __global__ void __launch_bounds__(GTHREADS) sgemm_nt_kernel(GemmBatch batch) {
+    pdl_sync();
     const GemmP& P = batch.p[blockIdx.z];
     const int m0 = blockIdx.x * GBM, n0 = blockIdx.y * GBN;
     if (m0 >= P.M || n0 >= P.N) return;
@@ -126,6 +129,162 @@ __global__ void __launch_bounds__(GTHREADS) sgemm_nt_kernel(GemmBatch batch) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Latency-oriented variant for small problems (a few hundred rows: single molecules, MD of a peptide).  The tiled
+// kernel above walks K in 16-wide steps with one global round trip per step (K = 384 -> 24 dependent round trips,
+// 11-27 us at 166 atoms, ncu r01h); here a CTA owns a (16*RM) x 32 output tile, fetches its whole A and W panels with
+// one burst of 16-byte cp.async copies (a single memory round trip, nothing staged through registers) and then runs
+// the K loop out of shared memory.  Same epilogues, same row map, same fp32 FFMA arithmetic (sum order over k
+// differs from the tiled kernel only in being strictly sequential).
+constexpr int SBN = 32, STHREADS = 256, SMALL_MAX_K = 768;
+
+template <int EPI, int RM>
+__global__ void __launch_bounds__(STHREADS) sgemm_small_kernel(GemmBatch batch) {
+    extern __shared__ __align__(16) float sg_smem[];
+    constexpr int BM = 16 * RM;
+    const GemmP& P = batch.p[blockIdx.z];
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * SBN;
+    // the weight panel does not depend on the previous kernel: its copies are issued before the dependency wait, so
+    // under programmatic dependent launch they overlap the predecessor's tail
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const bool live = m0 < P.M && n0 < P.N;
+    const int K = P.K, ld = K + 4, kv = K >> 2;
+    float* As = sg_smem;
+    float* Ws = sg_smem + BM * ld;
+    const int t = threadIdx.x;
+    auto load_w = [&]() {
+        for (int idx = t; idx < SBN * kv; idx += STHREADS) {
+            const int row = idx / kv, k4 = idx - row * kv;
+            const int n = n0 + row;
+            const bool ok = n < P.N;
+            const float* src = P.W + (size_t)(ok ? n : 0) * K + 4 * k4;
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(Ws + row * ld + 4 * k4);
+            const int bytes = ok ? 16 : 0;   // zero-fill rows beyond the problem
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+        }
+    };
+    if (live && P.w_static) load_w();
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (!live) return;
+    if (!P.w_static) load_w();
+    for (int idx = t; idx < BM * kv; idx += STHREADS) {
+        const int row = idx / kv, k4 = idx - row * kv;
+        const int m = m0 + row;
+        const bool ok = m < P.M;
+        const size_t prow = ok ? ((size_t)(m / P.gs) * P.rpa + P.c0 + m % P.gs) : 0;
+        const float* src = P.A + prow * P.lda + 4 * k4;
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(As + row * ld + 4 * k4);
+        const int bytes = ok ? 16 : 0;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+    }
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+
+    const int tx = t & 15, ty = t >> 4;
+    float acc[RM][2];
+#pragma unroll
+    for (int r = 0; r < RM; ++r) acc[r][0] = acc[r][1] = 0.f;
+    const float* a0 = As + ty * ld;
+    const float* w0 = Ws + tx * ld;
+#pragma unroll 4
+    for (int k = 0; k < K; k += 4) {
+        float4 a[RM], w[2];
+#pragma unroll
+        for (int r = 0; r < RM; ++r) a[r] = *reinterpret_cast<const float4*>(a0 + r * 16 * ld + k);
+#pragma unroll
+        for (int c = 0; c < 2; ++c) w[c] = *reinterpret_cast<const float4*>(w0 + c * 16 * ld + k);
+#pragma unroll
+        for (int r = 0; r < RM; ++r)
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                acc[r][c] = fmaf(a[r].x, w[c].x, acc[r][c]);
+                acc[r][c] = fmaf(a[r].y, w[c].y, acc[r][c]);
+                acc[r][c] = fmaf(a[r].z, w[c].z, acc[r][c]);
+                acc[r][c] = fmaf(a[r].w, w[c].w, acc[r][c]);
+            }
+    }
+#pragma unroll
+    for (int r = 0; r < RM; ++r) {
+        const int m = m0 + ty + 16 * r;
+        if (m >= P.M) continue;
+        const int atom = m / P.gs;
+        const size_t prow = (size_t)atom * P.rpa + P.c0 + m % P.gs;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int n = n0 + tx + 16 * c;
+            if (n >= P.N) continue;
+            float v = acc[r][c];
+            if (P.bias) v += P.bias[n];
+            const size_t ci = prow * P.ldc + n;
+            if (EPI == EPI_ACT) {
+                if (P.C2) P.C2[ci] = v;
+                v = act_apply(P.act, v);
+            } else if (EPI == EPI_MULGRAD) {
+                v *= act_grad(P.act, P.aux[prow * P.ldaux + n]);
+            } else if (EPI == EPI_SCALE3) {
+                if (P.C2) P.C2[ci] = v;
+                v *= P.aux[((size_t)atom * 3 + P.g) * P.N + n];
+            }
+            if (P.accumulate) v += P.C[ci];
+            P.C[ci] = v;
+        }
+    }
+}
+
+// true when every problem of the batch fits the small kernel and the launch is small enough to be latency-bound
+static inline bool small_gemm_ok(const GemmBatch& b) {
+    if (!g_tmdn_tuning[TMDN_TUNE_SMALL_GEMM]) return false;
+    long long macs = 0;
+    for (int i = 0; i < b.n; ++i) {
+        const GemmP& p = b.p[i];
+        if (p.K > SMALL_MAX_K || (p.K & 3) || (p.lda & 3) || p.K != b.p[0].K) return false;
+        if (((uintptr_t)p.A & 15) || ((uintptr_t)p.W & 15)) return false;
+        macs += (long long)p.M * p.N * p.K;
+    }
+    return macs <= 160LL * 1000 * 1000;   // ~9k rows of a 128 x 128 mix; above that throughput kernels win
+}
+
+template <int RM>
+static inline int small_gemm_launch_rm(int epi, const GemmBatch& b, dim3 grid, size_t smem, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        const int maxb = (16 * RM + SBN) * (SMALL_MAX_K + 4) * (int)sizeof(float);
+        if (cudaFuncSetAttribute(sgemm_small_kernel<EPI_NONE, RM>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess ||
+            cudaFuncSetAttribute(sgemm_small_kernel<EPI_ACT, RM>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess ||
+            cudaFuncSetAttribute(sgemm_small_kernel<EPI_MULGRAD, RM>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess ||
+            cudaFuncSetAttribute(sgemm_small_kernel<EPI_SCALE3, RM>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess) {
+            tmdn_set_error("gemm: cudaFuncSetAttribute failed: %s", cudaGetErrorString(cudaGetLastError()));
+            return TMDN_ECUDA;
+        }
+        attr_set = true;
+    }
+    switch (epi) {
+        case EPI_NONE: launch_k(sgemm_small_kernel<EPI_NONE, RM>, grid, STHREADS, smem, stream, b); break;
+        case EPI_ACT: launch_k(sgemm_small_kernel<EPI_ACT, RM>, grid, STHREADS, smem, stream, b); break;
+        case EPI_MULGRAD: launch_k(sgemm_small_kernel<EPI_MULGRAD, RM>, grid, STHREADS, smem, stream, b); break;
+        case EPI_SCALE3: launch_k(sgemm_small_kernel<EPI_SCALE3, RM>, grid, STHREADS, smem, stream, b); break;
+        default: tmdn_set_error("gemm: bad epilogue"); return TMDN_EINVAL;
+    }
+    TMDN_LAUNCH_CHECK();
+    return TMDN_OK;
+}
+
+static inline int small_gemm_launch(int epi, const GemmBatch& b, cudaStream_t stream, const char* tag) {
+    KTimer ktimer__(tag, stream);
+    int maxM = 0, maxN = 0;
+    long long tiles32 = 0;
+    for (int i = 0; i < b.n; ++i) {
+        if (b.p[i].M > maxM) maxM = b.p[i].M;
+        if (b.p[i].N > maxN) maxN = b.p[i].N;
+        tiles32 += cdiv(b.p[i].M, 32) * cdiv(b.p[i].N, SBN);
+    }
+    if (maxM == 0 || maxN == 0) return TMDN_OK;
+    const int rm = tiles32 < 148 ? 1 : 2;   // 16-row tiles while the 32-row grid would leave SMs idle
+    const dim3 grid((unsigned)cdiv(maxM, 16 * rm), (unsigned)cdiv(maxN, SBN), (unsigned)b.n);
+    const size_t smem = (size_t)(16 * rm + SBN) * (b.p[0].K + 4) * sizeof(float);
+    return rm == 1 ? small_gemm_launch_rm<1>(epi, b, grid, smem, stream) : small_gemm_launch_rm<2>(epi, b, grid, smem, stream);
+}
+
 static inline GemmP gemm_desc(const float* A, int lda, const float* W, const float* bias, float* C, int ldc, int M,
                               int N, int K) {
     GemmP p;
@@ -133,10 +292,12 @@ static inline GemmP gemm_desc(const float* A, int lda, const float* W, const flo
     p.A = A; p.lda = lda; p.W = W; p.bias = bias; p.C = C; p.ldc = ldc;
     p.M = M; p.N = N; p.K = K;
     p.gs = 1; p.c0 = 0; p.rpa = 1; p.g = 0;
+    p.w_static = 1;
     return p;
 }
 
 static inline int gemm_launch(int epi, const GemmBatch& b, cudaStream_t stream, const char* tag = "node_gemm") {
+    if (small_gemm_ok(b)) return small_gemm_launch(epi, b, stream, strcmp(tag, "node_gemm") == 0 ? "node_gemm_small" : tag);
     KTimer ktimer__(tag, stream);
     int maxM = 0, maxN = 0;
     for (int i = 0; i < b.n; ++i) {
@@ -146,10 +307,10 @@ static inline int gemm_launch(int epi, const GemmBatch& b, cudaStream_t stream, 
     if (maxM == 0 || maxN == 0) return TMDN_OK;
     dim3 grid((unsigned)cdiv(maxM, GBM), (unsigned)cdiv(maxN, GBN), (unsigned)b.n);  // M tiles on x (2^31-1 limit)
     switch (epi) {
-        case EPI_NONE: sgemm_nt_kernel<EPI_NONE><<<grid, GTHREADS, 0, stream>>>(b); break;
-        case EPI_ACT: sgemm_nt_kernel<EPI_ACT><<<grid, GTHREADS, 0, stream>>>(b); break;
-        case EPI_MULGRAD: sgemm_nt_kernel<EPI_MULGRAD><<<grid, GTHREADS, 0, stream>>>(b); break;
-        case EPI_SCALE3: sgemm_nt_kernel<EPI_SCALE3><<<grid, GTHREADS, 0, stream>>>(b); break;
+        case EPI_NONE: launch_k(sgemm_nt_kernel<EPI_NONE>, grid, GTHREADS, 0, stream, b); break;
+        case EPI_ACT: launch_k(sgemm_nt_kernel<EPI_ACT>, grid, GTHREADS, 0, stream, b); break;
+        case EPI_MULGRAD: launch_k(sgemm_nt_kernel<EPI_MULGRAD>, grid, GTHREADS, 0, stream, b); break;
+        case EPI_SCALE3: launch_k(sgemm_nt_kernel<EPI_SCALE3>, grid, GTHREADS, 0, stream, b); break;
         default: tmdn_set_error("gemm: bad epilogue"); return TMDN_EINVAL;
     }
     TMDN_LAUNCH_CHECK();

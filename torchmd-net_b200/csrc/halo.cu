@@ -7,6 +7,7 @@
 namespace {
 __global__ void gather_rows_kernel(const float* __restrict__ src, const int32_t* __restrict__ idx, long long n_rows,
                                    int row_floats, float* __restrict__ out) {
+    pdl_sync();
     const long long total = n_rows * row_floats;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
         const long long r = t / row_floats;
@@ -16,6 +17,7 @@ __global__ void gather_rows_kernel(const float* __restrict__ src, const int32_t*
 }
 __global__ void gather_rows4_kernel(const float4* __restrict__ src, const int32_t* __restrict__ idx, long long n_rows,
                                     int row_vec, float4* __restrict__ out) {
+    pdl_sync();
     const long long total = n_rows * row_vec;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
         const long long r = t / row_vec;
@@ -37,10 +39,10 @@ extern "C" int tmdn_halo_pack_f32(const float* src, const int32_t* idx, int64_t 
     long long blocks = cdiv(total, 256);
     if (blocks > 148 * 16) blocks = 148 * 16;   // grid-stride over 16 CTAs per SM
     if (v4)
-        gather_rows4_kernel<<<(unsigned)blocks, 256, 0, stream>>>((const float4*)src, idx, n_rows, (int)(row_floats / 4),
+        launch_k(gather_rows4_kernel, (unsigned)blocks, 256, 0, stream, (const float4*)src, idx, n_rows, (int)(row_floats / 4),
                                                                   (float4*)out);
     else
-        gather_rows_kernel<<<(unsigned)blocks, 256, 0, stream>>>(src, idx, n_rows, (int)row_floats, out);
+        launch_k(gather_rows_kernel, (unsigned)blocks, 256, 0, stream, src, idx, n_rows, (int)row_floats, out);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }

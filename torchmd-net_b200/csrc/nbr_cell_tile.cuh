@@ -40,6 +40,7 @@ template <typename T, int MODE>
 __global__ void __launch_bounds__(CT_THREADS)
 cell_tile_kernel(const SortedAtom<T>* __restrict__ spos, const long long* __restrict__ sbatch,
                  const int* __restrict__ cell_start, CellGrid<T> g, int periodic, T lo2, T hi2, CellTileOut<T> out) {
+    pdl_sync();
     __shared__ T cx[CT_CAND], cy[CT_CAND], cz[CT_CAND];
     __shared__ long long cb[CT_CAND];
     __shared__ int cidx[CT_CAND];

@@ -67,6 +67,7 @@ template <typename T> __device__ __forceinline__ int cell_coord(T p, T L, int n)
 template <typename T>
 __global__ void cell_assign_kernel(const T* __restrict__ pos, int n, CellGrid<T> g, int* __restrict__ cell_cnt,
                                    int* __restrict__ cell_of, int* __restrict__ slot_of) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int cx = cell_coord(pos[3 * (size_t)i], g.L[0], g.n[0]);
@@ -82,6 +83,7 @@ __global__ void cell_scatter_kernel(const T* __restrict__ pos, const int64_t* __
                                     const int* __restrict__ cell_start, const int* __restrict__ cell_of,
                                     const int* __restrict__ slot_of, SortedAtom<T>* __restrict__ spos,
                                     long long* __restrict__ sbatch) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int p = cell_start[cell_of[i]] + slot_of[i];

@@ -59,6 +59,7 @@ __device__ __forceinline__ int block_excl_scan(int v, int& total, int* s_warp /*
 // ------------------------------------------------------------------ batch range of every 128-atom tile
 __global__ void __launch_bounds__(NB_THREADS) tile_batch_range_kernel(const int64_t* __restrict__ batch, int n,
                                                                       long long* __restrict__ tile_mm) {
+    pdl_sync();
     __shared__ long long s_min[NB_THREADS / 32], s_max[NB_THREADS / 32];
     const int i = blockIdx.x * NB_THREADS + threadIdx.x;
     long long lo = LLONG_MAX, hi = LLONG_MIN;
@@ -86,6 +87,7 @@ template <typename T>
 __global__ void __launch_bounds__(NB_THREADS)
 nbr_brute_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, int n, Box3<T> box, int periodic, T lo2,
                  T hi2, int loop, int transpose, PairOut<T> out, const long long* __restrict__ tile_mm) {
+    pdl_sync();
     __shared__ T sx[NB_THREADS], sy[NB_THREADS], sz[NB_THREADS];
     __shared__ long long sb[NB_THREADS];
     __shared__ int s_warp[NB_THREADS / 32 + 1];
@@ -149,6 +151,7 @@ nbr_brute_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, i
 
 // slots in [min(found, max_pairs), max_pairs) get the reference's padding values (common.cuh:70-76)
 template <typename T> __global__ void pad_fill_kernel(PairOut<T> out) {
+    pdl_sync();
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= out.max_pairs) return;
     const long long found = *out.counter;
@@ -169,6 +172,7 @@ template <typename T>
 __global__ void nbr_backward_kernel(const int32_t* __restrict__ nbr, const T* __restrict__ deltas,
                                     const T* __restrict__ dist, const T* __restrict__ gdel, const T* __restrict__ gdist,
                                     long long max_pairs, T* __restrict__ gpos) {
+    pdl_sync();
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= max_pairs) return;
     const T d = dist[e];
@@ -236,16 +240,16 @@ int neighbors_impl(int strategy, const T* pos, const int64_t* batch, int64_t n_a
         }
         TMDN_CUDA(cudaMemsetAsync(w.cell_cnt, 0, sizeof(int) * (g.ncells + 1), stream));
         const int blocks = (int)cdiv(n, 256);
-        cell_assign_kernel<T><<<blocks, 256, 0, stream>>>(pos, n, g, w.cell_cnt, w.cell_of, w.slot_of);
+        launch_k(cell_assign_kernel<T>, blocks, 256, 0, stream, pos, n, g, w.cell_cnt, w.cell_of, w.slot_of);
         TMDN_LAUNCH_CHECK();
         TMDN_TRY(tmdn_scan_exclusive_i32(w.cell_cnt, w.cell_start, g.ncells, w.scan_tmp, stream));
-        cell_scatter_kernel<T><<<blocks, 256, 0, stream>>>(pos, batch, n, w.cell_start, w.cell_of, w.slot_of,
+        launch_k(cell_scatter_kernel<T>, blocks, 256, 0, stream, pos, batch, n, w.cell_start, w.cell_of, w.slot_of,
                                                            (SortedAtom<T>*)w.spos, w.sbatch);
         TMDN_LAUNCH_CHECK();
         CellTileOut<T> to{};
         to.nbr = neighbors; to.deltas = deltas; to.dist = distances; to.counter = num_found;
         to.max_pairs = (long long)max_pairs; to.loop = loop; to.transpose = include_transpose;
-        cell_tile_kernel<T, CT_PAIRS><<<g.ncells, CT_THREADS, 0, stream>>>((const SortedAtom<T>*)w.spos, w.sbatch,
+        launch_k(cell_tile_kernel<T, CT_PAIRS>, g.ncells, CT_THREADS, 0, stream, (const SortedAtom<T>*)w.spos, w.sbatch,
                                                                           w.cell_start, g, use_periodic, lo2, hi2, to);
         TMDN_LAUNCH_CHECK();
     } else {
@@ -258,13 +262,13 @@ int neighbors_impl(int strategy, const T* pos, const int64_t* batch, int64_t n_a
             tmdn_set_error("neighbors(brute): workspace too small (%zu < %zu)", workspace_bytes, arena.off);
             return TMDN_EWORKSPACE;
         }
-        tile_batch_range_kernel<<<ntiles, NB_THREADS, 0, stream>>>(batch, n, tile_mm);
+        launch_k(tile_batch_range_kernel, ntiles, NB_THREADS, 0, stream, batch, n, tile_mm);
         TMDN_LAUNCH_CHECK();
-        nbr_brute_kernel<T><<<ntiles, NB_THREADS, 0, stream>>>(pos, batch, n, b, use_periodic, lo2, hi2, loop,
+        launch_k(nbr_brute_kernel<T>, ntiles, NB_THREADS, 0, stream, pos, batch, n, b, use_periodic, lo2, hi2, loop,
                                                                include_transpose, out, tile_mm);
         TMDN_LAUNCH_CHECK();
     }
-    pad_fill_kernel<T><<<(unsigned)cdiv(max_pairs, 256), 256, 0, stream>>>(out);
+    launch_k(pad_fill_kernel<T>, (unsigned)cdiv(max_pairs, 256), 256, 0, stream, out);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }
@@ -276,7 +280,7 @@ int backward_impl(const int32_t* neighbors, const T* deltas, const T* distances,
     TMDN_CHECK_ARG(n_atoms > 0 && max_pairs >= 0, "neighbors_backward: bad sizes");
     TMDN_CUDA(cudaMemsetAsync(grad_pos, 0, sizeof(T) * 3 * (size_t)n_atoms, stream));
     if (max_pairs == 0 || (!grad_deltas && !grad_distances)) return TMDN_OK;
-    nbr_backward_kernel<T><<<(unsigned)cdiv(max_pairs, 256), 256, 0, stream>>>(
+    launch_k(nbr_backward_kernel<T>, (unsigned)cdiv(max_pairs, 256), 256, 0, stream, 
         neighbors, deltas, distances, grad_deltas, grad_distances, (long long)max_pairs, grad_pos);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;

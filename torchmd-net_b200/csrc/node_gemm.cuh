@@ -6,7 +6,7 @@
 
 static inline int node_gemm1(int epi, const GemmP& p, cudaStream_t stream, bool allow_tc = true) {
     static const int use_tc = [] { const char* e = getenv("TMDN_TC_GEMM"); return e ? atoi(e) : 1; }();
-    // below ~1k rows the launch is a handful of tiles and the FFMA kernel's shorter prologue wins (166 atoms: 13 vs 25 us)
+    // below ~1k rows the launch is a handful of tiles: gemm1 picks the latency-oriented small kernel (gemm.cuh)
     if (use_tc && allow_tc && p.M >= 1024 && tcgemm::supported(epi, p)) return tcgemm::launch(epi, p, stream);
     return gemm1(epi, p, stream);
 }

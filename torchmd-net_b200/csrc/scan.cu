@@ -1,6 +1,7 @@
 // scan.cu -- exclusive prefix sum over int32 (cell offsets, CSR row pointers) + error-message storage.
 #include "common.cuh"
 #include "scan.cuh"
+#include <stdlib.h>
 
 static thread_local char g_err[512] = "";
 
@@ -33,6 +34,23 @@ extern "C" int tmdn_is_stream_capturing(tmdn_stream_t stream) {
 static std::atomic<long long> g_launches{0};
 void tmdn_note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 extern "C" long long tmdn_launch_count(void) { return g_launches.load(); }
+
+// ------------------------------------------------------------------ tuning knobs (tmdn_set_tuning)
+// Defaults can be overridden at load time by the environment (TMDN_SMALL_GEMM, TMDN_LPT_ROWS, TMDN_PDL).
+static int env_or(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
+int g_tmdn_tuning[TMDN_TUNE_COUNT] = {env_or("TMDN_SMALL_GEMM", 1), env_or("TMDN_LPT_ROWS", 1), env_or("TMDN_PDL", 0)};
+extern "C" int tmdn_set_tuning(const char* key, int value) {
+    static const char* names[TMDN_TUNE_COUNT] = {"small_gemm", "lpt_rows", "pdl"};
+    if (!key) { tmdn_set_error("set_tuning: null key"); return -1; }
+    for (int i = 0; i < TMDN_TUNE_COUNT; ++i)
+        if (strcmp(key, names[i]) == 0) {
+            const int old = g_tmdn_tuning[i];
+            if (value >= 0) g_tmdn_tuning[i] = value;
+            return old;
+        }
+    tmdn_set_error("set_tuning: unknown key '%s'", key);
+    return -1;
+}
 
 namespace {
 struct TimedSpan { std::string name; cudaEvent_t e0, e1; };
@@ -99,6 +117,7 @@ constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 // Elements with index >= n_in read as 0; outputs are written for index < n_out.
 __global__ void __launch_bounds__(SCAN_THREADS) scan_tile_kernel(const int* in, int* out,
                                                                  int64_t n_in, int64_t n_out, int* __restrict__ sums) {
+    pdl_sync();
     __shared__ int s_warp[32];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)t * SCAN_ITEMS;
@@ -131,6 +150,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_tile_kernel(const int* in, 
 
 __global__ void __launch_bounds__(SCAN_THREADS) scan_add_kernel(int* __restrict__ out, int64_t n_out,
                                                                 const int* __restrict__ carry) {
+    pdl_sync();
     const int c = carry[blockIdx.x];
     const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
 #pragma unroll
@@ -156,32 +176,32 @@ int tmdn_scan_exclusive_i32(const int* in, int* out, int64_t n_in, int* tmp, cud
     const int64_t n_out = n_in + 1;
     const int64_t nb = cdiv(n_out, SCAN_TILE);
     if (nb == 1) {
-        scan_tile_kernel<<<1, SCAN_THREADS, 0, stream>>>(in, out, n_in, n_out, nullptr);
+        launch_k(scan_tile_kernel, 1, SCAN_THREADS, 0, stream, in, out, n_in, n_out, nullptr);
         TMDN_LAUNCH_CHECK();
         return TMDN_OK;
     }
     int* sums = tmp;
     int* next_tmp = tmp + align_up((size_t)nb * sizeof(int)) / sizeof(int);
-    scan_tile_kernel<<<(unsigned)nb, SCAN_THREADS, 0, stream>>>(in, out, n_in, n_out, sums);
+    launch_k(scan_tile_kernel, (unsigned)nb, SCAN_THREADS, 0, stream, in, out, n_in, n_out, sums);
     TMDN_LAUNCH_CHECK();
     // exclusive scan of the tile totals, in place (only nb entries are needed)
     {
         const int64_t nb2 = cdiv(nb, SCAN_TILE);
         if (nb2 == 1) {
-            scan_tile_kernel<<<1, SCAN_THREADS, 0, stream>>>(sums, sums, nb, nb, nullptr);
+            launch_k(scan_tile_kernel, 1, SCAN_THREADS, 0, stream, sums, sums, nb, nb, nullptr);
             TMDN_LAUNCH_CHECK();
         } else {
             int* sums2 = next_tmp;
-            scan_tile_kernel<<<(unsigned)nb2, SCAN_THREADS, 0, stream>>>(sums, sums, nb, nb, sums2);
+            launch_k(scan_tile_kernel, (unsigned)nb2, SCAN_THREADS, 0, stream, sums, sums, nb, nb, sums2);
             TMDN_LAUNCH_CHECK();
             TMDN_CHECK_ARG(nb2 <= SCAN_TILE, "scan: too many elements (%lld)", (long long)n_in);
-            scan_tile_kernel<<<1, SCAN_THREADS, 0, stream>>>(sums2, sums2, nb2, nb2, nullptr);
+            launch_k(scan_tile_kernel, 1, SCAN_THREADS, 0, stream, sums2, sums2, nb2, nb2, nullptr);
             TMDN_LAUNCH_CHECK();
-            scan_add_kernel<<<(unsigned)nb2, SCAN_THREADS, 0, stream>>>(sums, nb, sums2);
+            launch_k(scan_add_kernel, (unsigned)nb2, SCAN_THREADS, 0, stream, sums, nb, sums2);
             TMDN_LAUNCH_CHECK();
         }
     }
-    scan_add_kernel<<<(unsigned)nb, SCAN_THREADS, 0, stream>>>(out, n_out, sums);
+    launch_k(scan_add_kernel, (unsigned)nb, SCAN_THREADS, 0, stream, out, n_out, sums);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }

@@ -34,6 +34,7 @@ constexpr int GTHREADS_TC = 512;   // + a second epilogue warpgroup (warps 12-15
 
 static __global__ void __launch_bounds__(GTHREADS_TC, 1)
 tc_gemm_kernel(const __grid_constant__ GMaps M, const __grid_constant__ GParams P) {
+    pdl_sync();
     extern __shared__ unsigned char tcg_smem_raw[];
     unsigned char* sm = tcg_smem_raw + ((1024u - (s32(tcg_smem_raw) & 1023u)) & 1023u);
     float* ring = reinterpret_cast<float*>(sm);                 // stage s: [Ahi | Alo | Bhi | Blo], 16 KB each
@@ -269,7 +270,7 @@ static inline int launch(int epi, const GemmP& p, cudaStream_t stream) {
     }
     const long long tiles = (long long)P.m_tiles * P.n_tiles;
     const unsigned grid = (unsigned)(tiles < 148 ? tiles : 148);
-    tc_gemm_kernel<<<grid, GTHREADS_TC, GSMEM_BYTES, stream>>>(M, P);
+    launch_k(tc_gemm_kernel, grid, GTHREADS_TC, GSMEM_BYTES, stream, M, P);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }

@@ -164,6 +164,7 @@ __device__ __forceinline__ void split_inplace(float4* hi, float4* lo, int idx) {
 
 static __global__ void __launch_bounds__(MIX_THREADS, 1)
 tc_mix_kernel(const __grid_constant__ Maps M, const __grid_constant__ Params P) {
+    pdl_sync();
     extern __shared__ unsigned char tc_smem_raw[];
     unsigned char* sm = tc_smem_raw + ((1024u - (s32(tc_smem_raw) & 1023u)) & 1023u);   // SWIZZLE_128B: 1024-byte base
     float* Bhi = reinterpret_cast<float*>(sm);
@@ -445,7 +446,7 @@ static inline int launch(int epi, const GemmBatch& b, cudaStream_t stream) {
     P.n_atoms = n_atoms;
     P.epi = epi;
     P.accumulate = b.p[0].accumulate;
-    tc_mix_kernel<<<(unsigned)used, MIX_THREADS, SMEM_BYTES, stream>>>(M, P);
+    launch_k(tc_mix_kernel, (unsigned)used, MIX_THREADS, SMEM_BYTES, stream, M, P);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }

@@ -102,9 +102,28 @@ template <int NV> __device__ __forceinline__ void row_reduce(float (&v)[NV], flo
     }
 }
 
+constexpr int LPT_MAX_ROWS = 1024;
+// z -> int32 with range check, overflow status; optionally (order != null, n_rows <= LPT_MAX_ROWS) the row visiting
+// order of the edge kernels: rows sorted by decreasing degree, ties by index (a pure function of the graph)
 __global__ void tn_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ z32, int n, int max_z,
-                               const int32_t* __restrict__ num_found, long long max_edges, int32_t* __restrict__ status) {
+                               const int32_t* __restrict__ num_found, long long max_edges, int32_t* __restrict__ status,
+                               const int* __restrict__ row_ptr, int n_rows, int* __restrict__ order) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (order != nullptr) {
+        __shared__ int s_deg[LPT_MAX_ROWS];
+        for (int j = threadIdx.x; j < n_rows; j += blockDim.x) s_deg[j] = row_ptr[j + 1] - row_ptr[j];
+        __syncthreads();
+        if (i < n_rows) {
+            const int di = s_deg[i];
+            int rank = 0;
+            for (int j = 0; j < n_rows; ++j) {
+                const int dj = s_deg[j];
+                rank += (dj > di || (dj == di && j < i)) ? 1 : 0;
+            }
+            order[rank] = i;
+        }
+    }
     if (i == 0) {
         const int f = *num_found;
         status[0] = f;
@@ -124,6 +143,7 @@ __global__ void tn_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ 
 __global__ void tn_rbf_kernel(const float4* __restrict__ geom, const int* __restrict__ row_ptr, int n_atoms,
                               long long e_cap, int K, int rbf_type, float lo, float hi, const float* __restrict__ p0,
                               const float* __restrict__ p1, float* __restrict__ R, float* __restrict__ dR) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= e_cap * K) return;
     const long long e = idx / K;
@@ -153,6 +173,7 @@ __global__ void tn_rbf_kernel(const float4* __restrict__ geom, const int* __rest
 // F = a*C(d), dF = t*C(d) + a*C'(d)    (in place on a/t)
 __global__ void tn_filter_finalize_kernel(const float4* __restrict__ geom, long long e_cap, int n3, float lo, float hi,
                                           float* __restrict__ a, float* __restrict__ t) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= e_cap * n3) return;
     const long long e = idx / n3;
@@ -173,14 +194,16 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict_
                                   const float4* __restrict__ geom, const int* __restrict__ z32,
                                   const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv, int N,
                                   int H_, float* __restrict__ ias, const float* __restrict__ ln_w,
-                                  const float* __restrict__ ln_b, float* __restrict__ nh) {
+                                  const float* __restrict__ ln_b, float* __restrict__ nh,
+                                  const int* __restrict__ order) {
+    pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_red = smem;
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
-    const int i = blockIdx.x * blockDim.z + threadIdx.z;
-    const bool valid = i < N;
+    bool valid;
+    const int i = edge_row(order, N, valid);
     float acc[9];
 #pragma unroll
     for (int c = 0; c < 9; ++c) acc[c] = 0.f;
@@ -219,6 +242,7 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict_
 
 // ------------------------------------------------------------------ per-(atom,channel) elementwise stages
 __global__ void tn_normalize_fwd(const float* __restrict__ X, float* __restrict__ Xh, long long total, int H) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / H;
@@ -229,6 +253,7 @@ __global__ void tn_normalize_fwd(const float* __restrict__ X, float* __restrict_
     st9(Xh, i, H, h, xh);
 }
 __global__ void tn_normalize_bwd(const float* __restrict__ X, float* __restrict__ dX, long long total, int H) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / H;
@@ -242,6 +267,7 @@ __global__ void tn_normalize_bwd(const float* __restrict__ X, float* __restrict_
 // Xn = Xh + dX + (dX)^2 ; optionally also the next layer's normalised input   (tensornet.py:409, :385)
 __global__ void tn_update_fwd(const float* Xh, const float* __restrict__ dX, float* __restrict__ Xn,
                               float* Xh_next, long long total, int H) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / H;
@@ -262,6 +288,7 @@ __global__ void tn_update_fwd(const float* Xh, const float* __restrict__ dX, flo
 // ddX = dXn + adjoint of the square term
 __global__ void tn_update_bwd(const float* __restrict__ dXn, const float* __restrict__ dX, float* __restrict__ ddX,
                               long long total, int H) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / H;
@@ -277,6 +304,7 @@ __global__ void tn_update_bwd(const float* __restrict__ dXn, const float* __rest
 // recompute tau = product(M,Y); dtau from dtauh; then dM -> dMout, dY(direct) -> dtauh buffer (in place)
 __global__ void tn_prod_bwd(const float* __restrict__ Y, const float* __restrict__ M, float* __restrict__ dtauh_dY,
                             float* __restrict__ dMout, long long total, int H, int so3) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / H;
@@ -346,13 +374,14 @@ constexpr int MSG_FWD_THREADS = 1024;   // 64 registers, one edge per batch: at 
 template <bool TAB, int NB = 1, int HC = 0>
 __global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H_,
-                           int so3, float* __restrict__ M, float* __restrict__ tauh) {
+                           int so3, float* __restrict__ M, float* __restrict__ tauh, const int* __restrict__ order) {
+    pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
-    const int i = blockIdx.x * blockDim.z + threadIdx.z;
-    const bool valid = i < N;
+    bool valid;
+    const int i = edge_row(order, N, valid);
     float m[9];
 #pragma unroll
     for (int c = 0; c < 9; ++c) m[c] = 0.f;
@@ -396,19 +425,22 @@ __global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restr
 // E3: adjoint of the message passing, evaluated in row i of the symmetric edge set:
 //   dY_i += sum_e f_e * dM_j
 //   dE/dpos_i += u_e * sum_{h,c} f'_g(c)(d_e)[h] * (dM_c[i,h] Y_c[j,h] + dM_c[j,h] Y_c[i,h])
-constexpr int MSG_BWD_THREADS = 256;   // 128 registers: two edges' gathers (60 loads) in flight per thread
-template <bool TAB, int NB = 2, int HC = 0>
-__global__ void __launch_bounds__(MSG_BWD_THREADS) tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+constexpr int MSG_BWD_THREADS = 256;   // 128 registers: two edges' gathers (60 loads) in flight per thread; small systems use 4 slices
+// MAXT = 512 (4 edge slices per row) is the small-system instantiation: same registers, more rows' worth of
+// gathers in flight when there are fewer rows than SMs can hold
+template <bool TAB, int NB = 2, int HC = 0, int MAXT = MSG_BWD_THREADS>
+__global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
                            const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
-                           int H_) {
+                           int H_, const int* __restrict__ order) {
+    pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_red = smem;
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
-    const int i = blockIdx.x * blockDim.z + threadIdx.z;
-    const bool valid = i < N;
+    bool valid;
+    const int i = edge_row(order, N, valid);
     float gp[3] = {0.f, 0.f, 0.f};
     float acc[9];
 #pragma unroll
@@ -470,6 +502,7 @@ __global__ void __launch_bounds__(MSG_BWD_THREADS) tn_msg_bwd(const int* __restr
 __global__ void tn_out_norm_fwd(const float* __restrict__ X, const float* __restrict__ ln_w,
                                 const float* __restrict__ ln_b, float* __restrict__ xl, float* __restrict__ stat,
                                 int N, int H) {
+    pdl_sync();
     __shared__ float s_red[64];
     const int h = threadIdx.x;
     const int i = blockIdx.x * blockDim.y + threadIdx.y;
@@ -496,6 +529,7 @@ __global__ void tn_out_norm_fwd(const float* __restrict__ X, const float* __rest
 __global__ void tn_out_norm_bwd(const float* __restrict__ X, const float* __restrict__ ln_w,
                                 const float* __restrict__ stat, const float* __restrict__ dxl,
                                 float* __restrict__ dXa, int N, int H) {
+    pdl_sync();
     __shared__ float s_red[64];
     const int h = threadIdx.x;
     const int i = blockIdx.x * blockDim.y + threadIdx.y;
@@ -534,6 +568,7 @@ __global__ void tn_out_norm_bwd(const float* __restrict__ X, const float* __rest
 // e_i = (w2 . a4_i + b2) * std      (output_modules.py:76-77, model.py:262-263); one warp per atom
 __global__ void tn_head_energy(const float* __restrict__ a4, const float* __restrict__ w2,
                                const float* __restrict__ b2, float stdv, float* __restrict__ e_atom, int N, int Hh) {
+    pdl_sync();
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (i >= N) return;
@@ -545,6 +580,7 @@ __global__ void tn_head_energy(const float* __restrict__ a4, const float* __rest
 // y[m] = sum_{i: batch[i]==m} e_i + mean  (batch sorted); one CTA per molecule, fixed-order tree => deterministic
 __global__ void __launch_bounds__(128) tn_mol_reduce(const float* __restrict__ e_atom, const int64_t* __restrict__ batch,
                                                      int N, float mean, float* __restrict__ energy) {
+    pdl_sync();
     __shared__ float s_part[128];
     const long long m = blockIdx.x;
     int lo = 0, hi = N;  // first index with batch >= m
@@ -566,6 +602,7 @@ __global__ void __launch_bounds__(128) tn_mol_reduce(const float* __restrict__ e
 // d4[i,n] = std * w2[n] * act'(h4[i,n])
 __global__ void tn_head_seed_bwd(const float* __restrict__ h4, const float* __restrict__ w2, float stdv, int act,
                                  float* __restrict__ d4, long long total, int Hh) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     d4[idx] = stdv * w2[idx % Hh] * act_grad(act, h4[idx]);
@@ -576,6 +613,7 @@ __global__ void tn_head_seed_bwd(const float* __restrict__ h4, const float* __re
 __global__ void tn_embed_scale_bwd(float* __restrict__ dXa, const float* __restrict__ iasm,
                                    const float* __restrict__ fias, const float* __restrict__ h2, int act,
                                    float* __restrict__ dh2, long long total, int H) {
+    pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t i = idx / H;
@@ -603,6 +641,7 @@ __global__ void tn_embed_scale_bwd(float* __restrict__ dXa, const float* __restr
 // Dias_c += LayerNorm^T(dnh)[h] * dq/dias_c
 __global__ void tn_embed_norm_bwd(const float* __restrict__ ias, const float* __restrict__ ln_w,
                                   const float* __restrict__ dnh, float* __restrict__ Dias, int N, int H) {
+    pdl_sync();
     __shared__ float s_red[64];
     const int h = threadIdx.x;
     const int i = blockIdx.x * blockDim.y + threadIdx.y;
@@ -635,17 +674,18 @@ __global__ void tn_embed_norm_bwd(const float* __restrict__ ias, const float* __
 // E4: adjoint of the embedding edge kernel w.r.t. positions, both directions of every edge inside row i.
 //   forces[i] = -(gpos[i] + sum_e [ u (gd_e + gd_e') + perp(gu_e) - perp(gu_e') ])
 template <bool TAB, int HC = 0>
-__global__ void __launch_bounds__(512) tn_embed_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+__global__ void __launch_bounds__(1024) tn_embed_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                                   const float4* __restrict__ geom, const int* __restrict__ z32,
                                   const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv,
                                   const float* __restrict__ Dias, const float* __restrict__ gpos,
-                                  float* __restrict__ forces, int N, int H_) {
+                                  float* __restrict__ forces, int N, int H_, const int* __restrict__ order) {
+    pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_red = smem;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
-    const int i = blockIdx.x * blockDim.z + threadIdx.z;
-    const bool valid = i < N;
+    bool valid;
+    const int i = edge_row(order, N, valid);
     float gp[3] = {0.f, 0.f, 0.f};
     if (valid) {
         float di[9];
@@ -706,6 +746,7 @@ struct TnWs {
     int32_t *num_found, *row_ptr, *col;
     float* geom;
     int* z32;
+    int* row_order;
     void* graph_ws;
     size_t graph_ws_bytes;
     // exact-mode filters
@@ -790,6 +831,7 @@ int carve_tn(Arena& a, const tmdn_tensornet_model* m, int64_t N, int64_t P, int6
     w.dh1 = carve<float>(a, names, "dh1", n * 2 * H);
     w.dnh = carve<float>(a, names, "dnh", n * H);
     w.gpos = carve<float>(a, names, "gpos", n * 3);
+    w.row_order = carve<int>(a, names, "row_order", LPT_MAX_ROWS);
     (void)n_mol;
     return TMDN_OK;
 }
@@ -829,6 +871,9 @@ GemmBatch mix_batch(const float* A, float* C, const float* const Wg[3], int N, i
 // tensor cores for H = 128 (tc_mix.cuh); TMDN_TC_MIX=0 keeps the FFMA kernel (A/B measurements)
 int mix_launch(int epi, const GemmBatch& b, cudaStream_t stream) {
     static const int use_tc = [] { const char* e = getenv("TMDN_TC_MIX"); return e ? atoi(e) : 1; }();
+    // small systems (<= ~1000 atoms): a handful of tensor-core tiles on 13 SMs loses to the latency-oriented FFMA
+    // kernel spread over the whole machine (166 atoms: 13 us -> see profiles/r01i)
+    if (small_gemm_ok(b)) return small_gemm_launch(epi, b, stream, "node_gemm_small");
     if (use_tc && (epi == EPI_NONE || epi == EPI_SCALE3) && tcmix::supported(b)) return tcmix::launch(epi, b, stream);
     return gemm_launch(epi, b, stream);
 }
@@ -865,7 +910,7 @@ int eval_filter_exact(const tmdn_tensornet_model* m, const tmdn_filter_set& fs, 
     const long long tot = (long long)P * fs.dims[fs.n_layers];
     {
         KTimer ktimer__("tn_filter_finalize_kernel", stream);
-        tn_filter_finalize_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>((const float4*)w.geom, (long long)P,
+        launch_k(tn_filter_finalize_kernel, (unsigned)cdiv(tot, 256), 256, 0, stream, (const float4*)w.geom, (long long)P,
                                                                                 fs.dims[fs.n_layers], m->cutoff_lower,
                                                                                 m->cutoff_upper, F, dF);
         TMDN_LAUNCH_CHECK();
@@ -957,13 +1002,13 @@ struct TnRun {
         const unsigned egrid = (unsigned)cdiv(NH, 256);
         {
             KTimer ktimer__("tn_update_bwd", stream);
-            tn_update_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.dX[l], w.dB, NH, H);
+            launch_k(tn_update_bwd, egrid, 256, 0, stream, w.dXa, w.dX[l], w.dB, NH, H);
             TMDN_LAUNCH_CHECK();
         }
         TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.dB, w.dC, m->layer_mixT[l] + 3, N, H), stream));
         {
             KTimer ktimer__("tn_prod_bwd", stream);
-            tn_prod_bwd<<<egrid, 256, 0, stream>>>(w.Y[l], w.M[l], w.dC, w.dB, NH, H, m->so3);
+            launch_k(tn_prod_bwd, egrid, 256, 0, stream, w.Y[l], w.M[l], w.dC, w.dB, NH, H, m->so3);
             TMDN_LAUNCH_CHECK();
         }
         return TMDN_OK;
@@ -976,7 +1021,7 @@ struct TnRun {
         const int apb = H >= 128 ? 1 : 128 / H;
         {
             KTimer ktimer__("tn_embed_scale_bwd", stream);
-            tn_embed_scale_bwd<<<egrid, 256, 0, stream>>>(w.dXa, w.iasm, w.fias, w.h2, act, w.dh2, NH, H);
+            launch_k(tn_embed_scale_bwd, egrid, 256, 0, stream, w.dXa, w.iasm, w.fias, w.h2, act, w.dh2, NH, H);
             TMDN_LAUNCH_CHECK();
         }
         GemmP p = gemm_desc(w.dh2, 3 * H, m->emb_w2T, nullptr, w.dh1, 2 * H, N, 2 * H, 3 * H);
@@ -987,7 +1032,7 @@ struct TnRun {
         TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.dXa, w.dB, m->emb_mixT, N, H), stream));
         {
             KTimer ktimer__("tn_embed_norm_bwd", stream);
-            tn_embed_norm_bwd<<<(unsigned)cdiv(N, apb), dim3(H, apb), 0, stream>>>(w.ias, m->emb_ln_w, w.dnh, w.dB, N, H);
+            launch_k(tn_embed_norm_bwd, (unsigned)cdiv(N, apb), dim3(H, apb), 0, stream, w.ias, m->emb_ln_w, w.dnh, w.dB, N, H);
             TMDN_LAUNCH_CHECK();
         }
         return TMDN_OK;
@@ -1000,12 +1045,17 @@ struct TnRun {
         const int apb = H >= 128 ? 1 : 128 / H;
         const dim3 rblock(H, apb);
         const EdgeLaunch el = edge_launch(N, H, 1024);    // embedding edge kernels: <= 64 registers/thread
-        const EdgeLaunch elb = edge_launch(N, H, 512);
+        const EdgeLaunch elb = edge_launch(N, H, 1024);   // 56 registers
         const EdgeLaunch elf2 = edge_launch(N, H, MSG_FWD_THREADS);
-        const EdgeLaunch elb2 = edge_launch(N, H, MSG_BWD_THREADS);   // two edges in flight per thread
+        // two edges in flight per thread; up to 4 slices per row when the rows alone cannot fill the machine
+        const bool bwd4 = tab && (long long)N * H * 2 < 148LL * 2048;
+        const EdgeLaunch elb2 = edge_launch(N, H, bwd4 ? 512 : MSG_BWD_THREADS);
         const unsigned rgrid = (unsigned)cdiv(N, apb);
         const long long NH = (long long)N * H;
         const unsigned egrid = (unsigned)cdiv(NH, 256);
+        // few rows: one CTA per row leaves a second partial wave (166 rows on 148 SMs); rows are visited in order of
+        // decreasing degree so that the short ones fill the tail (longest-processing-time-first)
+        const int* order = (g_tmdn_tuning[TMDN_TUNE_LPT_ROWS] && N <= LPT_MAX_ROWS) ? w.row_order : nullptr;
         TMDN_CHECK_ARG(s >= TMDN_TN_EMBED && s <= TMDN_TN_FINAL, "tensornet: bad stage %d", s);
         TMDN_CHECK_ARG((s != TMDN_TN_LAYER_FWD && s != TMDN_TN_LAYER_BWD) || (l >= 0 && l < L), "tensornet: bad layer %d", l);
 
@@ -1021,15 +1071,16 @@ struct TnRun {
             TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
             {
                 KTimer ktimer__("tn_prep_kernel", stream);
-                tn_prep_kernel<<<(unsigned)cdiv(NT, 256), 256, 0, stream>>>(z, w.z32, NT, m->max_z, w.num_found,
-                                                                            (long long)P, status);
+                launch_k(tn_prep_kernel, (unsigned)cdiv(NT, 256), 256, 0, stream, z, w.z32, NT, m->max_z, w.num_found,
+                                                                            (long long)P, status, w.row_ptr, N,
+                                                                            order ? w.row_order : nullptr);
                 TMDN_LAUNCH_CHECK();
             }
             if (!tab) {  // exact filters: rbf once, then one MLP chain per filter set
                 const long long tot = (long long)P * m->num_rbf;
                 {
                     KTimer ktimer__("tn_rbf_kernel", stream);
-                    tn_rbf_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(geom, w.row_ptr, N, (long long)P,
+                    launch_k(tn_rbf_kernel, (unsigned)cdiv(tot, 256), 256, 0, stream, geom, w.row_ptr, N, (long long)P,
                                                                                 m->num_rbf, m->rbf_type, m->cutoff_lower,
                                                                                 m->cutoff_upper, m->rbf_p0, m->rbf_p1,
                                                                                 w.R, w.dR);
@@ -1042,14 +1093,14 @@ struct TnRun {
             {
                 KTimer ktimer__("tn_embed_edge_fwd", stream);
                 if (tab && H == 128)
-                    tn_embed_edge_fwd<true, 128><<<el.grid, el.block, el.smem, stream>>>(
-                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+                    launch_k(tn_embed_edge_fwd<true, 128>, el.grid, el.block, el.smem, stream, 
+                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
                 else if (tab)
-                    tn_embed_edge_fwd<true><<<el.grid, el.block, el.smem, stream>>>(
-                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+                    launch_k(tn_embed_edge_fwd<true>, el.grid, el.block, el.smem, stream, 
+                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
                 else
-                    tn_embed_edge_fwd<false><<<el.grid, el.block, el.smem, stream>>>(
-                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh);
+                    launch_k(tn_embed_edge_fwd<false>, el.grid, el.block, el.smem, stream, 
+                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
                 TMDN_LAUNCH_CHECK();
             }
             GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
@@ -1064,7 +1115,7 @@ struct TnRun {
             if (L > 0) {
                 {
                     KTimer ktimer__("tn_normalize_fwd", stream);
-                    tn_normalize_fwd<<<egrid, 256, 0, stream>>>(w.X[0], w.Xh, NH, H);
+                    launch_k(tn_normalize_fwd, egrid, 256, 0, stream, w.X[0], w.Xh, NH, H);
                     TMDN_LAUNCH_CHECK();
                 }
                 TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.Xh, w.Y[0], m->layer_mix[0], N, H), stream));
@@ -1075,11 +1126,11 @@ struct TnRun {
             {
                 KTimer ktimer__("tn_msg_fwd", stream);
                 if (tab)
-                    tn_msg_fwd<true><<<elf2.grid, elf2.block, elf2.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
-                                                                             H, m->so3, w.M[l], w.tauh);
+                    launch_k(tn_msg_fwd<true>, elf2.grid, elf2.block, elf2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
+                                                                             H, m->so3, w.M[l], w.tauh, order);
                 else
-                    tn_msg_fwd<false><<<elf2.grid, elf2.block, elf2.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
-                                                                              H, m->so3, w.M[l], w.tauh);
+                    launch_k(tn_msg_fwd<false>, elf2.grid, elf2.block, elf2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
+                                                                              H, m->so3, w.M[l], w.tauh, order);
                 TMDN_LAUNCH_CHECK();
             }
             TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
@@ -1087,7 +1138,7 @@ struct TnRun {
             // (atom, channel) column before writing it.
             {
                 KTimer ktimer__("tn_update_fwd", stream);
-                tn_update_fwd<<<egrid, 256, 0, stream>>>(w.Xh, w.dX[l], w.X[l + 1], l + 1 < L ? w.Xh : nullptr, NH, H);
+                launch_k(tn_update_fwd, egrid, 256, 0, stream, w.Xh, w.dX[l], w.X[l + 1], l + 1 < L ? w.Xh : nullptr, NH, H);
                 TMDN_LAUNCH_CHECK();
             }
             if (l + 1 < L) TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.Xh, w.Y[l + 1], m->layer_mix[l + 1], N, H), stream));
@@ -1097,7 +1148,7 @@ struct TnRun {
             TMDN_CHECK_ARG(energy, "tensornet: null energy pointer");
             {
                 KTimer ktimer__("tn_out_norm_fwd", stream);
-                tn_out_norm_fwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, m->out_ln_b, w.xl, w.stat, N, H);
+                launch_k(tn_out_norm_fwd, rgrid, rblock, 0, stream, w.X[L], m->out_ln_w, m->out_ln_b, w.xl, w.stat, N, H);
                 TMDN_LAUNCH_CHECK();
             }
             {
@@ -1110,13 +1161,13 @@ struct TnRun {
             }
             {
                 KTimer ktimer__("tn_head_energy", stream);
-                tn_head_energy<<<(unsigned)cdiv(N, 4), 128, 0, stream>>>(w.a4, m->head_w2, m->head_b2, m->std, w.e_atom, N,
+                launch_k(tn_head_energy, (unsigned)cdiv(N, 4), 128, 0, stream, w.a4, m->head_w2, m->head_b2, m->std, w.e_atom, N,
                                                                          H / 2);
                 TMDN_LAUNCH_CHECK();
             }
             {
                 KTimer ktimer__("tn_mol_reduce", stream);
-                tn_mol_reduce<<<(unsigned)n_mol, 128, 0, stream>>>(w.e_atom, batch, N, m->mean, energy);
+                launch_k(tn_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy);
                 TMDN_LAUNCH_CHECK();
             }
             if (!forces) return TMDN_OK;
@@ -1124,7 +1175,7 @@ struct TnRun {
             const long long tot = (long long)N * (H / 2);
             {
                 KTimer ktimer__("tn_head_seed_bwd", stream);
-                tn_head_seed_bwd<<<(unsigned)cdiv(tot, 256), 256, 0, stream>>>(w.h4, m->head_w2, m->std, act, w.d4, tot,
+                launch_k(tn_head_seed_bwd, (unsigned)cdiv(tot, 256), 256, 0, stream, w.h4, m->head_w2, m->std, act, w.d4, tot,
                                                                                H / 2);
                 TMDN_LAUNCH_CHECK();
             }
@@ -1135,7 +1186,7 @@ struct TnRun {
             TMDN_TRY(node_gemm1(EPI_NONE, q, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
             {
                 KTimer ktimer__("tn_out_norm_bwd", stream);
-                tn_out_norm_bwd<<<rgrid, rblock, 0, stream>>>(w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
+                launch_k(tn_out_norm_bwd, rgrid, rblock, 0, stream, w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
                 TMDN_LAUNCH_CHECK();
             }
             return L > 0 ? pre_bwd(L - 1) : embed_node_bwd();
@@ -1143,12 +1194,15 @@ struct TnRun {
         if (s == TMDN_TN_LAYER_BWD) {
             {
                 KTimer ktimer__("tn_msg_bwd", stream);
-                if (tab)
-                    tn_msg_bwd<true><<<elb2.grid, elb2.block, elb2.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
-                                                                                w.dB, w.dC, w.gpos, N, H);
+                if (bwd4)
+                    launch_k(tn_msg_bwd<true, 2, 0, 512>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom,
+                             fv_layer[l], w.Y[l], w.dB, w.dC, w.gpos, N, H, order);
+                else if (tab)
+                    launch_k(tn_msg_bwd<true>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
+                                                                                w.dB, w.dC, w.gpos, N, H, order);
                 else
-                    tn_msg_bwd<false><<<elb2.grid, elb2.block, elb2.smem, stream>>>(w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
-                                                                                 w.dB, w.dC, w.gpos, N, H);
+                    launch_k(tn_msg_bwd<false>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
+                                                                                 w.dB, w.dC, w.gpos, N, H, order);
                 TMDN_LAUNCH_CHECK();
             }
             GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
@@ -1156,7 +1210,7 @@ struct TnRun {
             TMDN_TRY(mix_launch(EPI_NONE, b, stream));
             {
                 KTimer ktimer__("tn_normalize_bwd", stream);
-                tn_normalize_bwd<<<egrid, 256, 0, stream>>>(w.X[l], w.dXa, NH, H);
+                launch_k(tn_normalize_bwd, egrid, 256, 0, stream, w.X[l], w.dXa, NH, H);
                 TMDN_LAUNCH_CHECK();
             }
             return l > 0 ? pre_bwd(l - 1) : embed_node_bwd();
@@ -1166,14 +1220,14 @@ struct TnRun {
         {
             KTimer ktimer__("tn_embed_edge_bwd", stream);
             if (tab && H == 128)
-                tn_embed_edge_bwd<true, 128><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
-                                                                                   fv_emb, w.dB, w.gpos, forces, N, H);
+                launch_k(tn_embed_edge_bwd<true, 128>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
+                                                                                   fv_emb, w.dB, w.gpos, forces, N, H, order);
             else if (tab)
-                tn_embed_edge_bwd<true><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
-                                                                                   fv_emb, w.dB, w.gpos, forces, N, H);
+                launch_k(tn_embed_edge_bwd<true>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
+                                                                                   fv_emb, w.dB, w.gpos, forces, N, H, order);
             else
-                tn_embed_edge_bwd<false><<<elb.grid, elb.block, elb.smem, stream>>>(w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
-                                                                                    fv_emb, w.dB, w.gpos, forces, N, H);
+                launch_k(tn_embed_edge_bwd<false>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
+                                                                                    fv_emb, w.dB, w.gpos, forces, N, H, order);
             TMDN_LAUNCH_CHECK();
         }
         return TMDN_OK;
@@ -1218,7 +1272,7 @@ extern "C" int tmdn_channel_mix_f32(const float* x, const float* w, float* y, in
     TMDN_CHECK_ARG(H > 0 && H % 4 == 0, "channel_mix: H must be a positive multiple of 4");
     const float* Wg[3] = {w, w + (size_t)H * H, w + 2 * (size_t)H * H};
     GemmBatch b = mix_batch(x, y, Wg, (int)n_atoms, H);
-    for (int g = 0; g < 3; ++g) b.p[g].accumulate = accumulate;
+    for (int g = 0; g < 3; ++g) { b.p[g].accumulate = accumulate; b.p[g].w_static = 0; }   // caller's tensor
     return mix_launch(EPI_NONE, b, stream);
 }
 
@@ -1228,5 +1282,6 @@ extern "C" int tmdn_node_gemm_f32(const float* a, const float* w, const float* b
     TMDN_CHECK_ARG(M > 0 && N > 0 && K > 0 && M < (1LL << 31) && N < (1 << 20) && K < (1 << 20), "node_gemm: bad sizes");
     GemmP p = gemm_desc(a, (int)K, w, bias, c, (int)N, (int)M, (int)N, (int)K);
     p.accumulate = accumulate;
+    p.w_static = 0;   // caller's tensor, possibly written by the kernel just before this one
     return node_gemm1(EPI_NONE, p, (cudaStream_t)stream_);
 }

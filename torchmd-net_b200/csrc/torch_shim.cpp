@@ -565,6 +565,11 @@ Tensor node_gemm(const Tensor& a, const Tensor& w, const c10::optional<Tensor>& 
 }
 
 int64_t launch_count() { return (int64_t)tmdn_launch_count(); }
+int64_t set_tuning(std::string key, int64_t value) {
+    const int old = tmdn_set_tuning(key.c_str(), (int)value);
+    TORCH_CHECK(old >= 0, tmdn_last_error());
+    return old;
+}
 void profile_enable(bool on) { TMDN_CALL(tmdn_profile_enable(on ? 1 : 0)); }
 std::string profile_report() {
     std::vector<char> buf(1 << 16);
@@ -612,6 +617,7 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
     m.def("channel_mix(Tensor x, Tensor w, Tensor? y, bool accumulate) -> Tensor", channel_mix);
     m.def("node_gemm(Tensor a, Tensor w, Tensor? bias, Tensor? c, bool accumulate) -> Tensor", node_gemm);
     m.def("launch_count() -> int", launch_count);
+    m.def("set_tuning(str key, int value) -> int", set_tuning);
     m.def("profile_enable(bool on) -> ()", profile_enable);
     m.def("profile_report() -> str", profile_report);
     m.def("csr_build(str strategy, Tensor positions, Tensor batch, Tensor box_vectors, bool use_periodic, "
