@@ -73,7 +73,12 @@ int tmdn_profile_report(char* buf, size_t buf_bytes);
 /* Kernel-selection knobs (new; for A/B measurements and so that tests can force each path).  Keys:
  *   "small_gemm" 1 = node GEMMs / channel mixes of small systems use the latency-oriented fp32 kernel (default 1)
  *   "lpt_rows"   1 = edge kernels of small systems visit rows in order of decreasing degree (default 1)
- *   "pdl"        1 = dependent kernels are launched with programmatic stream serialisation (default 1)
+ *   "pdl"        1 = dependent kernels are launched with programmatic stream serialisation (default 0: measured
+ *                    slower inside CUDA graphs, profiles/r01i_bench_*_pdl_{on,off}.json)
+ *   "fused_nodes" 1 = TensorNet on small systems runs the row-local operations between two edge kernels (mixes, MLPs,
+ *                    LayerNorms, 3x3 algebra and their adjoints) as one kernel per chain: 18 launches per step instead
+ *                    of 45 (default 0: every CTA has to stream the chain's 0.4-0.9 MB of weights through one SM, which
+ *                    is slower than the per-operation kernels, profiles/r01i_node_chain_experiments.md; needs small_gemm)
  * Returns the previous value (>= 0); value < 0 only queries; -1 for an unknown key (tmdn_last_error says which).
  * Process-wide. */
 int tmdn_set_tuning(const char* key, int value);

@@ -74,7 +74,7 @@ def _bytes(v, unit):
 
 
 FAMILY = [("tn_msg_bwd", "tn_msg_bwd"), ("tn_msg_fwd", "tn_msg_fwd"), ("tn_embed_edge_bwd", "tn_embed_edge_bwd"),
-          ("tn_embed_edge_fwd", "tn_embed_edge_fwd"), ("tc_mix_kernel", "node_gemm_tc"), ("sgemm_nt_kernel", "node_gemm"),
+          ("tn_embed_edge_fwd", "tn_embed_edge_fwd"), ("tc_mix_kernel", "node_gemm_tc"), ("sgemm_nt_kernel", "node_gemm"), ("sgemm_small_kernel", "node_gemm_small"), ("tc_gemm_kernel", "node_gemm_tc"),
           ("cell_tile_kernel", "neighbors_csr"), ("et_edge_bwd", "et_edge_bwd"), ("et_edge_fwd", "et_edge_fwd")]
 
 

@@ -48,12 +48,20 @@ def check(y, f, y_ref, f_ref, e_rtol=E_RTOL, f_atol=F_ATOL):
     assert float((f - f_ref).abs().max()) <= f_atol, float((f - f_ref).abs().max())
 
 
+@pytest.fixture(params=[0, 1], ids=["per_op", "fused_chains"])
+def fused_nodes(request):
+    ops = torch.ops.torchmdnet_b200
+    old = ops.set_tuning("fused_nodes", request.param)
+    yield request.param
+    ops.set_tuning("fused_nodes", old)
+
+
 SMALL_TN = ["small_tensornet_o3.npz", "small_tensornet_so3.npz", "small_tensornet_gauss.npz"]
 
 
 @pytest.mark.parametrize("mode", ["exact", "table"])
 @pytest.mark.parametrize("name", SMALL_TN)
-def test_small_models_match_reference(name, mode):
+def test_small_models_match_reference(name, mode, fused_nodes):
     g = load_npz(name)
     m = build(g, mode)
     y, f = m(tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda())
@@ -100,12 +108,33 @@ def test_kernel_selection_knobs_agree():
     m = create_model(g["hparams"]).cuda().eval()
     m.representation_model.filter_mode = "table"
     z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
-    old = {k: ops.set_tuning(k, -1) for k in ("small_gemm", "lpt_rows", "pdl")}
-    assert old == {"small_gemm": 1, "lpt_rows": 1, "pdl": 1}
+    old = {k: ops.set_tuning(k, -1) for k in ("small_gemm", "lpt_rows", "pdl", "fused_nodes")}
+    assert old == {"small_gemm": 1, "lpt_rows": 1, "pdl": 0, "fused_nodes": 0}
     with pytest.raises(RuntimeError):
         ops.set_tuning("no_such_knob", 1)
     out = {}
     try:
+        # fused node chains (opt-in) against one launch per operation (default)
+        ops.set_tuning("fused_nodes", 1)
+        yF, fF = m(z, pos, batch)
+        check(yF, fF, g["y"], g["forces"])
+        c0 = ops.launch_count()
+        m(z, pos, batch)
+        n_fused = ops.launch_count() - c0
+        # the representation output and the stage buffers are written by the chains as well
+        xF = m.representation_model(z, pos, batch)[0].clone()
+        ops.set_tuning("fused_nodes", 0)
+        x0 = m.representation_model(z, pos, batch)[0]
+        torch.testing.assert_close(xF, x0, rtol=1e-5, atol=1e-6)
+        y0, f0 = m(z, pos, batch)
+        y1, f1 = y0.clone(), f0.clone()
+        c0 = ops.launch_count()
+        m(z, pos, batch)
+        n_unfused = ops.launch_count() - c0
+        assert n_fused < n_unfused - 20, (n_fused, n_unfused)
+        # (inside a chain the k range of a GEMM is split across warps: another summation order)
+        torch.testing.assert_close(yF, y0, rtol=3e-6, atol=3e-6)
+        torch.testing.assert_close(fF, f0, rtol=0, atol=1e-5)
         for sg in (1, 0):
             for lpt in (1, 0):
                 ops.set_tuning("small_gemm", sg)
@@ -117,11 +146,13 @@ def test_kernel_selection_knobs_agree():
         # and as a captured graph
         ops.set_tuning("small_gemm", 1)
         ops.set_tuning("lpt_rows", 1)
+        y, f = m(z, pos, batch)
+        assert torch.equal(y, y1) and torch.equal(f, f1)
         for pdl in (0, 1):
             ops.set_tuning("pdl", pdl)
             for _ in range(3):
                 y, f = m(z, pos, batch)
-                assert torch.equal(y, out[1, 1][0]) and torch.equal(f, out[1, 1][1]), pdl
+                assert torch.equal(y, y1) and torch.equal(f, f1), pdl
             gr = torch.cuda.CUDAGraph()
             s_ = torch.cuda.Stream()
             s_.wait_stream(torch.cuda.current_stream())
@@ -133,7 +164,7 @@ def test_kernel_selection_knobs_agree():
             for _ in range(5):
                 gr.replay()
             torch.cuda.synchronize()
-            assert torch.equal(yg, out[1, 1][0]) and torch.equal(fg, out[1, 1][1]), ("graph", pdl)
+            assert torch.equal(yg, y1) and torch.equal(fg, f1), ("graph", pdl)
     finally:
         for k, v in old.items():
             ops.set_tuning(k, v)
@@ -160,7 +191,7 @@ def test_reference_expected_pkl_row():
     torch.testing.assert_close(f.cpu(), torch.tensor(e["expected_deriv"]), rtol=1.3e-6, atol=1e-5)
 
 
-def test_intermediate_buffers_match_staged_restatement():
+def test_intermediate_buffers_match_staged_restatement(fused_nodes):
     g = load_npz("small_tensornet_o3.npz")
     m = build(g, "exact")
     z, pos, batch = tt(g["z"]), tt(g["pos"]), tt(g["batch"])

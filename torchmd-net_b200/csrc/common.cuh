@@ -21,7 +21,7 @@ struct KTimer {
 };
 
 // process-wide tuning knobs (tmdn_set_tuning, defined in scan.cu)
-enum { TMDN_TUNE_SMALL_GEMM = 0, TMDN_TUNE_LPT_ROWS = 1, TMDN_TUNE_PDL = 2, TMDN_TUNE_COUNT = 3 };
+enum { TMDN_TUNE_SMALL_GEMM = 0, TMDN_TUNE_LPT_ROWS = 1, TMDN_TUNE_PDL = 2, TMDN_TUNE_FUSED_NODES = 3, TMDN_TUNE_COUNT = 4 };
 extern int g_tmdn_tuning[TMDN_TUNE_COUNT];
 
 #define TMDN_CHECK_ARG(cond, ...)                 \

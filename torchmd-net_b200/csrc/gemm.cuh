@@ -152,30 +152,33 @@ __global__ void __launch_bounds__(STHREADS) sgemm_small_kernel(GemmBatch batch) 
     float* As = sg_smem;
     float* Ws = sg_smem + BM * ld;
     const int t = threadIdx.x;
+    // copies: a warp takes one row at a time (lane = 16-byte column, strided by 32 for K > 128), 8 rows per pass over
+    // the CTA -- no integer division per copy (the first version spent half of its instructions on idx / kv)
+    const int lane = t & 31, wrp = t >> 5;
     auto load_w = [&]() {
-        for (int idx = t; idx < SBN * kv; idx += STHREADS) {
-            const int row = idx / kv, k4 = idx - row * kv;
+        for (int row = wrp; row < SBN; row += STHREADS / 32) {
             const int n = n0 + row;
             const bool ok = n < P.N;
-            const float* src = P.W + (size_t)(ok ? n : 0) * K + 4 * k4;
-            const unsigned dst = (unsigned)__cvta_generic_to_shared(Ws + row * ld + 4 * k4);
+            const float* src = P.W + (size_t)(ok ? n : 0) * K;
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(Ws + row * ld);
             const int bytes = ok ? 16 : 0;   // zero-fill rows beyond the problem
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+            for (int k4 = lane; k4 < kv; k4 += 32)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + 16u * k4), "l"(src + 4 * k4), "r"(bytes) : "memory");
         }
     };
     if (live && P.w_static) load_w();
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (!live) return;
     if (!P.w_static) load_w();
-    for (int idx = t; idx < BM * kv; idx += STHREADS) {
-        const int row = idx / kv, k4 = idx - row * kv;
+    for (int row = wrp; row < BM; row += STHREADS / 32) {
         const int m = m0 + row;
         const bool ok = m < P.M;
-        const size_t prow = ok ? ((size_t)(m / P.gs) * P.rpa + P.c0 + m % P.gs) : 0;
-        const float* src = P.A + prow * P.lda + 4 * k4;
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(As + row * ld + 4 * k4);
+        const size_t prow = !ok ? 0 : (P.gs == 1 ? (size_t)m * P.rpa + P.c0 : (size_t)(m / P.gs) * P.rpa + P.c0 + m % P.gs);
+        const float* src = P.A + prow * P.lda;
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(As + row * ld);
         const int bytes = ok ? 16 : 0;
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+        for (int k4 = lane; k4 < kv; k4 += 32)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + 16u * k4), "l"(src + 4 * k4), "r"(bytes) : "memory");
     }
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
     __syncthreads();

@@ -36,11 +36,12 @@ void tmdn_note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 extern "C" long long tmdn_launch_count(void) { return g_launches.load(); }
 
 // ------------------------------------------------------------------ tuning knobs (tmdn_set_tuning)
-// Defaults can be overridden at load time by the environment (TMDN_SMALL_GEMM, TMDN_LPT_ROWS, TMDN_PDL).
+// Defaults can be overridden at load time by the environment (TMDN_SMALL_GEMM, TMDN_LPT_ROWS, TMDN_PDL, TMDN_FUSED_NODES).
 static int env_or(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
-int g_tmdn_tuning[TMDN_TUNE_COUNT] = {env_or("TMDN_SMALL_GEMM", 1), env_or("TMDN_LPT_ROWS", 1), env_or("TMDN_PDL", 0)};
+int g_tmdn_tuning[TMDN_TUNE_COUNT] = {env_or("TMDN_SMALL_GEMM", 1), env_or("TMDN_LPT_ROWS", 1), env_or("TMDN_PDL", 0),
+                                         env_or("TMDN_FUSED_NODES", 0)};
 extern "C" int tmdn_set_tuning(const char* key, int value) {
-    static const char* names[TMDN_TUNE_COUNT] = {"small_gemm", "lpt_rows", "pdl"};
+    static const char* names[TMDN_TUNE_COUNT] = {"small_gemm", "lpt_rows", "pdl", "fused_nodes"};
     if (!key) { tmdn_set_error("set_tuning: null key"); return -1; }
     for (int i = 0; i < TMDN_TUNE_COUNT; ++i)
         if (strcmp(key, names[i]) == 0) {

@@ -210,12 +210,19 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict_
     if (valid) {
         const float pz = Pz[(size_t)z32[i] * H + h];
         const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        for (int e = r0 + sl; e < r1; e += S) {
-            const int j = col[e];
-            const float4 g = geom[e];
+        // the index, geometry and element of the NEXT edge of this slice are fetched while the gathers of the current
+        // one are in flight: one dependent round trip per edge instead of three (col -> z32 -> Q row)
+        int e = r0 + sl, jn = 0, zn = 0;
+        float4 gn = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e < r1) { jn = col[e]; gn = geom[e]; zn = z32[jn]; }
+        for (; e < r1; e += S) {
+            const float4 g = gn;
+            const int zj = zn, e2 = e + S;
+            if (e2 < r1) { jn = col[e2]; gn = geom[e2]; }
             float f[3];
             filter_val<TAB>(fv, (size_t)e, g.w, H, h, f);
-            const float zv = pz + Qz[(size_t)z32[j] * H + h];
+            const float zv = pz + Qz[(size_t)zj * H + h];
+            if (e2 < r1) zn = z32[jn];
             const float w1 = zv * f[0], w2 = zv * f[1], w3 = zv * f[2];
             const float n2 = (g.x * g.x + g.y * g.y + g.z * g.z) * (1.0f / 3.0f);
             acc[0] += w1;
@@ -371,7 +378,9 @@ __device__ __forceinline__ void filter_eval(const FilterView& fv, const FilterRa
 // ------------------------------------------------------------------ E2: interaction message passing (+ product)
 // M_c[i,h] = sum_{e in row i} f_g(c)(d_e)[h] * Y_c[j,h]  ;  tauh = normalise(decompose(M Y + Y M))   (tensornet.py:392-405)
 constexpr int MSG_FWD_THREADS = 1024;   // 64 registers, one edge per batch: at 98k atoms this runs at 83 % of L2 throughput
-template <bool TAB, int NB = 1, int HC = 0>
+// PF: index and distance of the next batch of edges are fetched while the gathers of the current one are in flight
+// (small systems: the kernel is a chain of dependent round trips, col -> neighbour row)
+template <bool TAB, int NB = 1, int HC = 0, bool PF = false>
 __global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H_,
                            int so3, float* __restrict__ M, float* __restrict__ tauh, const int* __restrict__ order) {
@@ -387,17 +396,39 @@ __global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restr
     for (int c = 0; c < 9; ++c) m[c] = 0.f;
     if (valid) {
         const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        int jn[NB];
+        float dn[NB];
+        if (PF && r0 + sl < r1) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                const int e = r0 + sl + b * S, ee = e < r1 ? e : r0 + sl;
+                jn[b] = col[ee];
+                dn[b] = geom[ee].w;
+            }
+        }
         for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
             FilterRaw<TAB> fr[NB];
             float y[NB][9];
             bool on[NB];
+            int jc[NB];
+            float dc[NB];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) { jc[b] = jn[b]; dc[b] = dn[b]; }
+            if (PF && e0 + NB * S < r1) {
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    const int e = e0 + NB * S + b * S, ee = e < r1 ? e : e0 + NB * S;
+                    jn[b] = col[ee];
+                    dn[b] = geom[ee].w;
+                }
+            }
 #pragma unroll
             for (int b = 0; b < NB; ++b) {           // all loads of the batch first
                 const int e = e0 + b * S;
                 on[b] = e < r1;
                 const int ee = on[b] ? e : e0;
-                const int j = col[ee];
-                filter_load<TAB>(fv, (size_t)ee, geom[ee].w, H, h, fr[b]);
+                const int j = PF ? jc[b] : col[ee];
+                filter_load<TAB>(fv, (size_t)ee, PF ? dc[b] : geom[ee].w, H, h, fr[b]);
                 ld9(Y, (size_t)j, H, h, y[b]);
             }
 #pragma unroll
@@ -428,7 +459,7 @@ __global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restr
 constexpr int MSG_BWD_THREADS = 256;   // 128 registers: two edges' gathers (60 loads) in flight per thread; small systems use 4 slices
 // MAXT = 512 (4 edge slices per row) is the small-system instantiation: same registers, more rows' worth of
 // gathers in flight when there are fewer rows than SMs can hold
-template <bool TAB, int NB = 2, int HC = 0, int MAXT = MSG_BWD_THREADS>
+template <bool TAB, int NB = 2, int HC = 0, int MAXT = MSG_BWD_THREADS, bool PF = false>
 __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
                            const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
@@ -451,19 +482,41 @@ __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_p
         ld9(dM, (size_t)i, H, h, dmi);
         if (sl == 0) ld9(dY, (size_t)i, H, h, acc);
         const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        int jn[NB];
+        float dn[NB];
+        if (PF && r0 + sl < r1) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                const int e = r0 + sl + b * S, ee = e < r1 ? e : r0 + sl;
+                jn[b] = col[ee];
+                dn[b] = geom[ee].w;
+            }
+        }
         for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
             float4 g[NB];
             FilterRaw<TAB> fr[NB];
             float yj[NB][9], dmj[NB][9];
             bool on[NB];
+            int jc[NB];
+            float dc[NB];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) { jc[b] = jn[b]; dc[b] = dn[b]; }
+            if (PF && e0 + NB * S < r1) {
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    const int e = e0 + NB * S + b * S, ee = e < r1 ? e : e0 + NB * S;
+                    jn[b] = col[ee];
+                    dn[b] = geom[ee].w;
+                }
+            }
 #pragma unroll
             for (int b = 0; b < NB; ++b) {           // all loads of the batch first
                 const int e = e0 + b * S;
                 on[b] = e < r1;
                 const int ee = on[b] ? e : e0;
-                const int j = col[ee];
+                const int j = PF ? jc[b] : col[ee];
                 g[b] = geom[ee];
-                filter_load<TAB>(fv, (size_t)ee, g[b].w, H, h, fr[b]);
+                filter_load<TAB>(fv, (size_t)ee, PF ? dc[b] : g[b].w, H, h, fr[b]);
                 ld9(Y, (size_t)j, H, h, yj[b]);
                 ld9(dM, (size_t)j, H, h, dmj[b]);
             }
@@ -693,14 +746,20 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_bwd(const int* __restrict_
         const int zi = z32[i];
         const float pzi = Pz[(size_t)zi * H + h], qzi = Qz[(size_t)zi * H + h];
         const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        for (int e = r0 + sl; e < r1; e += S) {
-            const int j = col[e];
-            if (j == i) continue;  // self loop: d = 0, u = 0, no position dependence
-            const float4 g = geom[e];
+        int e = r0 + sl, jn = 0, zn = 0;     // next edge's index / geometry / element prefetched, as in the forward
+        float4 gn = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e < r1) { jn = col[e]; gn = geom[e]; zn = z32[jn]; }
+        for (; e < r1; e += S) {
+            const int j = jn, zj = zn, e2 = e + S;
+            const float4 g = gn;
+            if (e2 < r1) { jn = col[e2]; gn = geom[e2]; }
+            if (j == i) {          // self loop: d = 0, u = 0, no position dependence
+                if (e2 < r1) zn = z32[jn];
+                continue;
+            }
             float f[3], df[3], dj[9];
             filter_val_grad<TAB>(fv, (size_t)e, g.w, H, h, f, df);
             ld9(Dias, (size_t)j, H, h, dj);
-            const int zj = z32[j];
             const float ze = pzi + Qz[(size_t)zj * H + h];        // Z of edge (i <- j)
             const float zr = Pz[(size_t)zj * H + h] + qzi;        // Z of the reverse edge (j <- i)
             const float ux = g.x, uy = g.y, uz = g.z;
@@ -730,6 +789,7 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_bwd(const int* __restrict_
             gp[0] += ux * gd + (gx - dot * ux) * inv_d;
             gp[1] += uy * gd + (gy - dot * uy) * inv_d;
             gp[2] += uz * gd + (gz - dot * uz) * inv_d;
+            if (e2 < r1) zn = z32[jn];   // second level of the prefetch, after this edge's gathers were issued and used
         }
     }
     atom_reduce<3>(gp, s_red);
@@ -739,6 +799,8 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_bwd(const int* __restrict_
         forces[3 * (size_t)i + 2] = -(gpos[3 * (size_t)i + 2] + gp[2]);
     }
 }
+
+#include "tn_chain.cuh"
 
 // ------------------------------------------------------------------ workspace
 struct TnWs {
@@ -1056,6 +1118,14 @@ struct TnRun {
         // few rows: one CTA per row leaves a second partial wave (166 rows on 148 SMs); rows are visited in order of
         // decreasing degree so that the short ones fill the tail (longest-processing-time-first)
         const int* order = (g_tmdn_tuning[TMDN_TUNE_LPT_ROWS] && N <= LPT_MAX_ROWS) ? w.row_order : nullptr;
+        const bool fused = chain_ok(m, N);
+        auto chain_base = [&]() {
+            ChainArgs c;
+            memset(&c, 0, sizeof(c));
+            c.N = N; c.H = H; c.act = act; c.so3 = m->so3; c.stdv = m->std;
+            c.dbg = g_tmdn_tuning[TMDN_TUNE_FUSED_NODES] - 1;   // fused_nodes = 2, 3: timing experiments (wrong results)
+            return c;
+        };
         TMDN_CHECK_ARG(s >= TMDN_TN_EMBED && s <= TMDN_TN_FINAL, "tensornet: bad stage %d", s);
         TMDN_CHECK_ARG((s != TMDN_TN_LAYER_FWD && s != TMDN_TN_LAYER_BWD) || (l >= 0 && l < L), "tensornet: bad layer %d", l);
 
@@ -1103,6 +1173,19 @@ struct TnRun {
                         w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
                 TMDN_LAUNCH_CHECK();
             }
+            if (fused) {
+                ChainArgs c = chain_base();
+                c.flag = L > 0;
+                chain_seg1(c, m->emb_w1T, H, 2 * H);
+                chain_seg1(c, m->emb_w2T, 2 * H, 3 * H);
+                chain_seg(c, 3, m->emb_mixT, H, H);
+                if (L > 0) chain_seg(c, 3, m->layer_mixT[0], H, H);
+                c.b1 = m->emb_b1; c.b2 = m->emb_b2;
+                c.in0 = w.nh; c.in1 = w.ias;
+                c.out0 = w.h1; c.out1 = w.a1; c.out2 = w.h2; c.out3 = w.fias; c.out4 = w.iasm; c.out5 = w.X[0];
+                c.out6 = w.Xh; c.out7 = L > 0 ? w.Y[0] : nullptr;
+                return chain_launch<CH_EMBED>(c, stream, "tn_chain_embed");
+            }
             GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
             p.C2 = w.h1; p.act = act;
             TMDN_TRY(node_gemm1(EPI_ACT, p, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
@@ -1125,13 +1208,25 @@ struct TnRun {
         if (s == TMDN_TN_LAYER_FWD) {
             {
                 KTimer ktimer__("tn_msg_fwd", stream);
-                if (tab)
+                if (tab && order)
+                    launch_k(tn_msg_fwd<true, 1, 0, true>, elf2.grid, elf2.block, elf2.smem, stream, w.row_ptr, w.col, geom,
+                             fv_layer[l], w.Y[l], N, H, m->so3, w.M[l], w.tauh, order);
+                else if (tab)
                     launch_k(tn_msg_fwd<true>, elf2.grid, elf2.block, elf2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
                                                                              H, m->so3, w.M[l], w.tauh, order);
                 else
                     launch_k(tn_msg_fwd<false>, elf2.grid, elf2.block, elf2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
                                                                               H, m->so3, w.M[l], w.tauh, order);
                 TMDN_LAUNCH_CHECK();
+            }
+            if (fused) {
+                ChainArgs c = chain_base();
+                c.flag = l + 1 < L;
+                chain_seg(c, 3, m->layer_mixT[l] + 3, H, H);
+                if (l + 1 < L) chain_seg(c, 3, m->layer_mixT[l + 1], H, H);
+                c.in0 = w.tauh; c.in1 = w.Xh;
+                c.out0 = w.dX[l]; c.out1 = w.X[l + 1]; c.out2 = w.Xh; c.out3 = l + 1 < L ? w.Y[l + 1] : nullptr;
+                return chain_launch<CH_LAYER>(c, stream, "tn_chain_layer");
             }
             TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
             // Xh is both input (residual) and, for the next layer, output: safe because each thread reads its own
@@ -1146,6 +1241,29 @@ struct TnRun {
         }
         if (s == TMDN_TN_HEAD) {
             TMDN_CHECK_ARG(energy, "tensornet: null energy pointer");
+            if (fused) {
+                ChainArgs c = chain_base();
+                c.flag = forces != nullptr;
+                chain_seg1(c, m->out_wT, 3 * H, H);
+                chain_seg1(c, m->head_w1T, H, H / 2);
+                if (forces) {
+                    chain_seg1(c, m->head_w1, H / 2, H);
+                    chain_seg1(c, m->out_w, H, 3 * H);
+                    chain_seg(c, 3, m->layer_mix[L - 1] + 3, H, H);
+                }
+                c.b1 = m->out_b; c.b2 = m->head_b1;
+                c.ln_w = m->out_ln_w; c.ln_b = m->out_ln_b; c.hw2 = m->head_w2; c.hb2 = m->head_b2;
+                c.a3 = w.a3; c.a4 = w.a4;
+                c.in0 = w.X[L]; c.in1 = w.dX[L - 1]; c.in2 = w.Y[L - 1]; c.in3 = w.M[L - 1];
+                c.out0 = w.h3; c.out1 = w.h4; c.out2 = w.e_atom; c.out3 = w.dXa; c.out4 = w.dB; c.out5 = w.dC;
+                c.out6 = w.stat; c.out7 = w.xl;
+                if (forces) TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
+                TMDN_TRY(chain_launch<CH_HEAD>(c, stream, "tn_chain_head"));
+                KTimer ktimer__("tn_mol_reduce", stream);
+                launch_k(tn_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy);
+                TMDN_LAUNCH_CHECK();
+                return TMDN_OK;
+            }
             {
                 KTimer ktimer__("tn_out_norm_fwd", stream);
                 launch_k(tn_out_norm_fwd, rgrid, rblock, 0, stream, w.X[L], m->out_ln_w, m->out_ln_b, w.xl, w.stat, N, H);
@@ -1195,7 +1313,7 @@ struct TnRun {
             {
                 KTimer ktimer__("tn_msg_bwd", stream);
                 if (bwd4)
-                    launch_k(tn_msg_bwd<true, 2, 0, 512>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom,
+                    launch_k(tn_msg_bwd<true, 2, 0, 512, true>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom,
                              fv_layer[l], w.Y[l], w.dB, w.dC, w.gpos, N, H, order);
                 else if (tab)
                     launch_k(tn_msg_bwd<true>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
@@ -1204,6 +1322,24 @@ struct TnRun {
                     launch_k(tn_msg_bwd<false>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
                                                                                  w.dB, w.dC, w.gpos, N, H, order);
                 TMDN_LAUNCH_CHECK();
+            }
+            if (fused) {
+                ChainArgs c = chain_base();
+                c.in0 = w.dC; c.in1 = w.dXa; c.in2 = w.X[l];
+                chain_seg(c, 3, m->layer_mix[l], H, H);
+                if (l > 0) {
+                    chain_seg(c, 3, m->layer_mix[l - 1] + 3, H, H);
+                    c.in3 = w.dX[l - 1]; c.in4 = w.Y[l - 1]; c.in5 = w.M[l - 1];
+                    c.out0 = w.dXa; c.out1 = w.dB; c.out2 = w.dC;
+                    return chain_launch<CH_BWD>(c, stream, "tn_chain_bwd");
+                }
+                chain_seg1(c, m->emb_w2, 3 * H, 2 * H);
+                chain_seg1(c, m->emb_w1, 2 * H, H);
+                chain_seg(c, 3, m->emb_mix, H, H);
+                c.b1 = w.h2; c.b2 = w.h1; c.ln_w = m->emb_ln_w;
+                c.in3 = w.iasm; c.in4 = w.fias; c.in5 = w.ias;
+                c.out0 = w.dXa; c.out1 = w.dB; c.out2 = w.dh2; c.out3 = w.dh1; c.out4 = w.dnh;
+                return chain_launch<CH_BWD_EMB>(c, stream, "tn_chain_bwd_emb");
             }
             GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
             for (int g = 0; g < 3; ++g) b.p[g].accumulate = 1;
