@@ -50,6 +50,8 @@ def check(y, f, y_ref, f_ref, e_rtol=E_RTOL, f_atol=F_ATOL):
 
 @pytest.fixture(params=[0, 1], ids=["per_op", "fused_chains"])
 def fused_nodes(request):
+    from torchmdnet import _native
+    _native.load()
     ops = torch.ops.torchmdnet_b200
     old = ops.set_tuning("fused_nodes", request.param)
     yield request.param
@@ -101,7 +103,9 @@ def test_kernel_selection_knobs_agree():
     """tmdn_set_tuning: small systems take the latency-oriented GEMM and visit rows in order of decreasing degree.
     The row order only changes which CTA handles a row (bitwise identical results); the GEMM choice changes the
     summation order (same tolerance against the reference's numbers)."""
+    from torchmdnet import _native
     from torchmdnet.models.model import create_model
+    _native.load()
     ops = torch.ops.torchmdnet_b200
     g = load_npz("model_TensorNet-SPICE.npz")
     seed_everything(int(g["seed"]))
