@@ -10,16 +10,17 @@
 //   CH_HEAD     output LayerNorm, linear, head MLP, atom energy, and the whole adjoint back to dM, dY  (12 -> 1)
 //   CH_BWD      accumulate mix^T, normalise^T, square^T, mix^T, product^T                              (5 -> 1)
 //   CH_BWD_EMB  accumulate mix^T, normalise^T, scaling^T, MLP^T, mix^T, LayerNorm^T                    (7 -> 1)
-// A GEMM inside a chain reads its A operand from shared memory (the CTA's own rows, broadcast) and the weight in
-// [K, N] layout (every weight exists in both layouts because the adjoint needs the transpose).  The weights of ALL the
-// GEMMs of a chain form one stream of <= 24 KB chunks (16-32 consecutive k rows of a matrix, or of the three matrices of
-// a mix) that every thread helps to copy with 16-byte cp.async into an 8-stage shared-memory ring (192 KB), seven
-// chunks ahead of the arithmetic and across GEMM boundaries: the weights do not depend on the data, so a CTA is bound by the rate
-// at which its SM can pull the chain's weights out of L2 (0.4-0.9 MB per chain), not by one memory round trip per
-// k step (the first version read the weights with plain loads and spent 16 us per mix waiting for them, r01i).
-// Sums run over k in ascending order with fmaf starting from 0, bias / activation / accumulate applied afterwards: the
-// arithmetic of sgemm_small_kernel, so the fused and the unfused small-system paths agree to rounding of identical
-// operation sequences.
+// A GEMM inside a chain reads its A operand from shared memory (the CTA's own rows) and the weight in [K, N] layout
+// (every weight exists in both layouts because the adjoint needs the transpose).  The weights of ALL the GEMMs of a
+// chain form one stream of 16-row chunks (<= 24 KB: 16 consecutive k rows of a matrix, or of the three matrices of a mix)
+// that every thread helps to copy with 16-byte cp.async into a 7-stage shared-memory ring, six chunks ahead of the
+// arithmetic and across GEMM boundaries: the weights do not depend on the data.  The k range of a GEMM is split
+// across the warps of the CTA and the partial sums are added in slice order, so results differ from the per-operation
+// kernels by rounding only (tests: rtol 3e-6 on energies, 1e-5 eV/A on forces, and the reference's numbers).
+//
+// STATUS: opt-in (tmdn_set_tuning("fused_nodes", 1)).  Correct, 18 launches per step instead of 45, but not faster:
+// one SM pulls a chain's 0.4-0.9 MB of cold weights at 21-42 GB/s, while the per-operation kernels spread every
+// matrix over 44-312 CTAs.  Versions and measurements: profiles/r01i_node_chain_experiments.md.
 #pragma once
 
 enum { CH_EMBED = 0, CH_LAYER = 1, CH_HEAD = 2, CH_BWD = 3, CH_BWD_EMB = 4 };
