@@ -35,6 +35,16 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "torchmd-net_b200"))
 import synth_inputs as S  # noqa: E402
 
+# rank 0 prints ONE JSON line on stdout.  Libraries write there too (c10d prints "NCCL version ..." when the first
+# communicator is created), so file descriptor 1 is pointed at stderr for the whole run and the line goes to a
+# duplicate of the original stdout.
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+
 METRIC = "atom-steps/sec (energy+forces) TensorNet/ET at 1/2/4/8 B200; neighbor-list ms"
 UNIT = "atom-steps/s"
 
@@ -170,7 +180,7 @@ def run_reference(args):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------- roofline
@@ -259,7 +269,10 @@ def run_decomposed(args, model, hp, dev, rank, world, local):
     torch.cuda.synchronize()
     t_end = time.perf_counter()
     clocks = sampler.stop(t_begin, t_end) if sampler else None
-    t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], device=dev, dtype=torch.float64)
+    spans = [a.elapsed_time(b) for a, b in ev]
+    if os.environ.get("TMDN_BENCH_SPANS"):
+        print("rank %d spans ms: %s" % (rank, " ".join("%.2f" % x for x in spans)), file=sys.stderr, flush=True)
+    t = torch.tensor([sum(spans)], device=dev, dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_per_step = float(t) / K
     # e2e: pinned host positions of the owned atoms in, host forces of the owned atoms + total energy out
@@ -301,7 +314,7 @@ def run_decomposed(args, model, hp, dev, rank, world, local):
                     "d2h_bytes_per_step": N * 12 + 4, "api": "torchmdnet.distributed.DecomposedTensorNet.step"},
             "gpu_launches": int(launches_per_step) * K * world, "launches_per_step": int(launches_per_step),
             "clocks": clocks, "roofline": None, "cpu_baseline": None, "energy_checksum": float(e_tot)}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------- main arm
@@ -321,6 +334,8 @@ def main():
     ap.add_argument("--water-order", default="raster", choices=["raster", "morton", "shuffle"],
                     help="index order of the synthetic water molecules (raster = lattice order)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--table-intervals", type=int, default=0,
+                    help="intervals of the filter tables (0 = the model's default, 4096); A/B runs only")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -353,6 +368,8 @@ def main():
     rm.gemm_mode = args.et_gemm
     if hp["model"] == "tensornet":
         rm.filter_mode = args.filter
+        if args.table_intervals > 0:
+            rm.table_intervals = args.table_intervals
     else:
         args.filter = "table"
     z_np, pos0, batch_np, box = make_inputs(args.workload, rank, args)
@@ -438,6 +455,8 @@ def main():
     calc.model.representation_model.gemm_mode = args.et_gemm
     if hp["model"] == "tensornet":
         calc.model.representation_model.filter_mode = args.filter
+        if args.table_intervals > 0:
+            calc.model.representation_model.table_intervals = args.table_intervals
     if box is not None:
         calc.model.representation_model.distance = rm.distance
     if emb.shape[0] != n_mol:
@@ -531,7 +550,7 @@ def main():
             "gpu_launches": int(launches_per_step) * K, "launches_per_step": int(launches_per_step),
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "kernel_families": families,
             "energy_checksum": float(gy.double().sum())}
-    print(json.dumps(line))
+    emit(line)
 
 
 if __name__ == "__main__":
