@@ -334,6 +334,8 @@ def main():
     ap.add_argument("--water-order", default="raster", choices=["raster", "morton", "shuffle"],
                     help="index order of the synthetic water molecules (raster = lattice order)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-flush", action="store_true",
+                    help="experiment only: do not flush L2 between the timed steps of `value` (the line says so; not a bench number)")
     ap.add_argument("--table-intervals", type=int, default=0,
                     help="intervals of the filter tables (0 = the model's default, 4096); A/B runs only")
     args = ap.parse_args()
@@ -429,7 +431,8 @@ def main():
     barrier()
     t_begin = time.perf_counter()
     for i in range(K):
-        flush.zero_()                                   # L2 flush, outside the timed span
+        if not args.no_flush:
+            flush.zero_()                               # L2 flush, outside the timed span
         ev[i][0].record()
         graph_step(W + i)
         ev[i][1].record()
@@ -542,7 +545,8 @@ def main():
                        "edges_per_gpu": E, "filter_mode": args.filter,
                        "gemm": gemm_desc,
                        "neighbor_strategy": rm.distance.strategy,
-                       "l2": "flushed (512 MiB write) before every timed step",
+                       "l2": "NOT flushed (experiment, not a bench number)" if args.no_flush else
+                             "flushed (512 MiB write) before every timed step",
                        "step": "one CUDA graph replay: neighbour list + CSR + forward + analytic backward",
                        "parallelism": "independent replicas/shards per GPU, no collective in the step"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": N * 12,

@@ -380,15 +380,17 @@ __device__ __forceinline__ void filter_eval(const FilterView& fv, const FilterRa
 constexpr int MSG_FWD_THREADS = 1024;   // 64 registers, one edge per batch: at 98k atoms this runs at 83 % of L2 throughput
 // PF: index and distance of the next batch of edges are fetched while the gathers of the current one are in flight
 // (small systems: the kernel is a chain of dependent round trips, col -> neighbour row)
-template <bool TAB, int NB = 1, int HC = 0, bool PF = false>
-__global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
+template <bool TAB, int NB = 1, int HC = 0, bool PF = false, int MAXT = MSG_FWD_THREADS>
+__global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H_,
                            int so3, float* __restrict__ M, float* __restrict__ tauh, const int* __restrict__ order) {
     pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
-    const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
+    // blockIdx.y > 0 only in the small-system launch, where a CTA takes a 32-channel slab of a row (finer work units:
+    // 166 rows on 148 SMs are two full waves of whole-row CTAs, 664 slabs are 4.5 waves of quarter-length ones)
+    const int h = blockIdx.y * blockDim.x + threadIdx.x, sl = threadIdx.y, S = blockDim.y;
     bool valid;
     const int i = edge_row(order, N, valid);
     float m[9];
@@ -443,7 +445,7 @@ __global__ void __launch_bounds__(MSG_FWD_THREADS) tn_msg_fwd(const int* __restr
             }
         }
     }
-    slice_reduce<9>(m, s_part, H);
+    slice_reduce<9>(m, s_part, blockDim.x);
     if (!valid || sl != 0) return;
     st9(M, (size_t)i, H, h, m);
     float yi[9], tau[9], th[9];
@@ -1208,9 +1210,16 @@ struct TnRun {
         if (s == TMDN_TN_LAYER_FWD) {
             {
                 KTimer ktimer__("tn_msg_fwd", stream);
-                if (tab && order)
-                    launch_k(tn_msg_fwd<true, 1, 0, true>, elf2.grid, elf2.block, elf2.smem, stream, w.row_ptr, w.col, geom,
+                // small systems: 4 slices x 2 edges per thread at 128 registers instead of 8 slices x 1 at 64 -- the same
+                // number of edges in flight per SM, but with 64 registers ptxas reuses the landing registers of the
+                // table rows and an iteration becomes 3-4 dependent round trips instead of one (SASS, r01i)
+                if (tab && N <= LPT_MAX_ROWS) {   // (independent of the lpt_rows knob: the summation order must not depend on it)
+                    // (a CTA per 32-channel slab of a row -- 664 quarter-length CTAs instead of 166 -- was measured slower:
+                    // 32 us against 26 us per launch; the kernel still accepts that launch shape through blockIdx.y)
+                    const EdgeLaunch e4 = edge_launch(N, H, 512);
+                    launch_k(tn_msg_fwd<true, 2, 0, true, 512>, e4.grid, e4.block, e4.smem, stream, w.row_ptr, w.col, geom,
                              fv_layer[l], w.Y[l], N, H, m->so3, w.M[l], w.tauh, order);
+                }
                 else if (tab)
                     launch_k(tn_msg_fwd<true>, elf2.grid, elf2.block, elf2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
                                                                              H, m->so3, w.M[l], w.tauh, order);
