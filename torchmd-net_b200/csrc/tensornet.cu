@@ -259,18 +259,6 @@ __global__ void tn_normalize_fwd(const float* __restrict__ X, float* __restrict_
     t3_normalize(x, xh);
     st9(Xh, i, H, h, xh);
 }
-__global__ void tn_normalize_bwd(const float* __restrict__ X, float* __restrict__ dX, long long total, int H) {
-    pdl_sync();
-    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= total) return;
-    const size_t i = idx / H;
-    const int h = (int)(idx % H);
-    float x[9], dxh[9], dx[9];
-    ld9(X, i, H, h, x);
-    ld9(dX, i, H, h, dxh);
-    t3_normalize_bwd(x, dxh, dx);
-    st9(dX, i, H, h, dx);
-}
 // Xn = Xh + dX + (dX)^2 ; optionally also the next layer's normalised input   (tensornet.py:409, :385)
 __global__ void tn_update_fwd(const float* Xh, const float* __restrict__ dX, float* __restrict__ Xn,
                               float* Xh_next, long long total, int H) {
@@ -308,6 +296,27 @@ __global__ void tn_update_bwd(const float* __restrict__ dXn, const float* __rest
     for (int c = 0; c < 9; ++c) dd[c] += g[c];
     st9(ddX, i, H, h, dd);
 }
+// tn_normalize_bwd followed by tn_update_bwd of the layer below, one pass over the (atom, channel) pairs: the same
+// operations in the same order (dXa is still written: it is the residual branch of the next stage)
+__global__ void tn_normalize_update_bwd(const float* __restrict__ X, float* __restrict__ dXa,
+                                        const float* __restrict__ dXprev, float* __restrict__ ddX, long long total, int H) {
+    pdl_sync();
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t i = idx / H;
+    const int h = (int)(idx % H);
+    float x[9], dxh[9], g[9], d[9], dd[9];
+    ld9(X, i, H, h, x);
+    ld9(dXa, i, H, h, dxh);
+    t3_normalize_bwd(x, dxh, g);
+    st9(dXa, i, H, h, g);
+    ld9(dXprev, i, H, h, d);
+    t3_square_bwd(d, g, dd);
+#pragma unroll
+    for (int c = 0; c < 9; ++c) dd[c] += g[c];
+    st9(ddX, i, H, h, dd);
+}
+
 // recompute tau = product(M,Y); dtau from dtauh; then dM -> dMout, dY(direct) -> dtauh buffer (in place)
 __global__ void tn_prod_bwd(const float* __restrict__ Y, const float* __restrict__ M, float* __restrict__ dtauh_dY,
                             float* __restrict__ dMout, long long total, int H, int so3) {
@@ -583,7 +592,8 @@ __global__ void tn_out_norm_fwd(const float* __restrict__ X, const float* __rest
 }
 __global__ void tn_out_norm_bwd(const float* __restrict__ X, const float* __restrict__ ln_w,
                                 const float* __restrict__ stat, const float* __restrict__ dxl,
-                                float* __restrict__ dXa, int N, int H) {
+                                float* __restrict__ dXa, int N, int H, const float* __restrict__ dXprev,
+                                float* __restrict__ ddX) {
     pdl_sync();
     __shared__ float s_red[64];
     const int h = threadIdx.x;
@@ -619,10 +629,20 @@ __global__ void tn_out_norm_bwd(const float* __restrict__ X, const float* __rest
 #pragma unroll
     for (int c = 4; c < 9; ++c) out[c] = gq[c] * dq[2];
     st9(dXa, (size_t)i, H, h, out);
+    if (dXprev != nullptr) {   // tn_update_bwd of the last layer, fused (same operations in the same order)
+        float d[9], dd[9];
+        ld9(dXprev, (size_t)i, H, h, d);
+        t3_square_bwd(d, out, dd);
+#pragma unroll
+        for (int c = 0; c < 9; ++c) dd[c] += out[c];
+        st9(ddX, (size_t)i, H, h, dd);
+    }
 }
 // e_i = (w2 . a4_i + b2) * std      (output_modules.py:76-77, model.py:262-263); one warp per atom
+// d4 != null: also the seed of the backward pass, d4[i,n] = std * w2[n] * act'(h4[i,n])
 __global__ void tn_head_energy(const float* __restrict__ a4, const float* __restrict__ w2,
-                               const float* __restrict__ b2, float stdv, float* __restrict__ e_atom, int N, int Hh) {
+                               const float* __restrict__ b2, float stdv, float* __restrict__ e_atom, int N, int Hh,
+                               const float* __restrict__ h4, int act, float* __restrict__ d4) {
     pdl_sync();
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
@@ -631,6 +651,8 @@ __global__ void tn_head_energy(const float* __restrict__ a4, const float* __rest
     for (int k = lane; k < Hh; k += 32) s += a4[(size_t)i * Hh + k] * w2[k];
     s = warp_sum(s);
     if (lane == 0) e_atom[i] = (s + b2[0]) * stdv;
+    if (d4 != nullptr)
+        for (int k = lane; k < Hh; k += 32) d4[(size_t)i * Hh + k] = stdv * w2[k] * act_grad(act, h4[(size_t)i * Hh + k]);
 }
 // y[m] = sum_{i: batch[i]==m} e_i + mean  (batch sorted); one CTA per molecule, fixed-order tree => deterministic
 __global__ void __launch_bounds__(128) tn_mol_reduce(const float* __restrict__ e_atom, const int64_t* __restrict__ batch,
@@ -654,20 +676,11 @@ __global__ void __launch_bounds__(128) tn_mol_reduce(const float* __restrict__ e
     }
     if (threadIdx.x == 0) energy[m] = s_part[0] + mean;
 }
-// d4[i,n] = std * w2[n] * act'(h4[i,n])
-__global__ void tn_head_seed_bwd(const float* __restrict__ h4, const float* __restrict__ w2, float stdv, int act,
-                                 float* __restrict__ d4, long long total, int Hh) {
-    pdl_sync();
-    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= total) return;
-    d4[idx] = stdv * w2[idx % Hh] * act_grad(act, h4[idx]);
-}
-
 // ------------------------------------------------------------------ embedding backward (node part)
 // X0_c = fias_g(c) * iasm_c :  dh2[g*H+h] = (sum_{c in g} dX_c iasm_c) * act'(h2) ;  diasm_c = dX_c * fias_g  (in place)
 __global__ void tn_embed_scale_bwd(float* __restrict__ dXa, const float* __restrict__ iasm,
                                    const float* __restrict__ fias, const float* __restrict__ h2, int act,
-                                   float* __restrict__ dh2, long long total, int H) {
+                                   float* __restrict__ dh2, long long total, int H, const float* __restrict__ Xn) {
     pdl_sync();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
@@ -675,6 +688,13 @@ __global__ void tn_embed_scale_bwd(float* __restrict__ dXa, const float* __restr
     const int h = (int)(idx % H);
     float dx[9], im[9], f[3];
     ld9(dXa, i, H, h, dx);
+    if (Xn != nullptr) {   // tn_normalize_bwd of layer 0 fused in front (same operations)
+        float x[9], g[9];
+        ld9(Xn, i, H, h, x);
+        t3_normalize_bwd(x, dx, g);
+#pragma unroll
+        for (int c = 0; c < 9; ++c) dx[c] = g[c];
+    }
     ld9(iasm, i, H, h, im);
 #pragma unroll
     for (int g = 0; g < 3; ++g) f[g] = fias[i * 3 * H + g * H + h];
@@ -1060,11 +1080,11 @@ struct TnRun {
     }
 
     // adjoint of X_{l+1} = Xh + dX + dX^2 and of the (M, Y) product: dXa -> dB (= dM_l), dC (= direct dY_l)
-    int pre_bwd(int l) {
+    int pre_bwd(int l, bool update_done = false) {
         const int N = (int)n_rows, H = m->hidden;
         const long long NH = (long long)N * H;
         const unsigned egrid = (unsigned)cdiv(NH, 256);
-        {
+        if (!update_done) {
             KTimer ktimer__("tn_update_bwd", stream);
             launch_k(tn_update_bwd, egrid, 256, 0, stream, w.dXa, w.dX[l], w.dB, NH, H);
             TMDN_LAUNCH_CHECK();
@@ -1078,14 +1098,14 @@ struct TnRun {
         return TMDN_OK;
     }
     // adjoint of the embedding node stage: dXa -> dB (= dE/d ias, "Dias")
-    int embed_node_bwd() {
+    int embed_node_bwd(const float* Xn = nullptr) {
         const int N = (int)n_rows, H = m->hidden, act = m->activation;
         const long long NH = (long long)N * H;
         const unsigned egrid = (unsigned)cdiv(NH, 256);
         const int apb = H >= 128 ? 1 : 128 / H;
         {
             KTimer ktimer__("tn_embed_scale_bwd", stream);
-            launch_k(tn_embed_scale_bwd, egrid, 256, 0, stream, w.dXa, w.iasm, w.fias, w.h2, act, w.dh2, NH, H);
+            launch_k(tn_embed_scale_bwd, egrid, 256, 0, stream, w.dXa, w.iasm, w.fias, w.h2, act, w.dh2, NH, H, Xn);
             TMDN_LAUNCH_CHECK();
         }
         GemmP p = gemm_desc(w.dh2, 3 * H, m->emb_w2T, nullptr, w.dh1, 2 * H, N, 2 * H, 3 * H);
@@ -1289,7 +1309,7 @@ struct TnRun {
             {
                 KTimer ktimer__("tn_head_energy", stream);
                 launch_k(tn_head_energy, (unsigned)cdiv(N, 4), 128, 0, stream, w.a4, m->head_w2, m->head_b2, m->std, w.e_atom, N,
-                                                                         H / 2);
+                         H / 2, (const float*)w.h4, act, forces ? w.d4 : (float*)nullptr);
                 TMDN_LAUNCH_CHECK();
             }
             {
@@ -1299,13 +1319,6 @@ struct TnRun {
             }
             if (!forces) return TMDN_OK;
             TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
-            const long long tot = (long long)N * (H / 2);
-            {
-                KTimer ktimer__("tn_head_seed_bwd", stream);
-                launch_k(tn_head_seed_bwd, (unsigned)cdiv(tot, 256), 256, 0, stream, w.h4, m->head_w2, m->std, act, w.d4, tot,
-                                                                               H / 2);
-                TMDN_LAUNCH_CHECK();
-            }
             GemmP p = gemm_desc(w.d4, H / 2, m->head_w1T, nullptr, w.d3, H, N, H, H / 2);
             p.aux = w.h3; p.ldaux = H; p.act = act;
             TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
@@ -1313,10 +1326,11 @@ struct TnRun {
             TMDN_TRY(node_gemm1(EPI_NONE, q, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
             {
                 KTimer ktimer__("tn_out_norm_bwd", stream);
-                launch_k(tn_out_norm_bwd, rgrid, rblock, 0, stream, w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H);
+                launch_k(tn_out_norm_bwd, rgrid, rblock, 0, stream, w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H,
+                         L > 0 ? (const float*)w.dX[L - 1] : (const float*)nullptr, L > 0 ? w.dB : (float*)nullptr);
                 TMDN_LAUNCH_CHECK();
             }
-            return L > 0 ? pre_bwd(L - 1) : embed_node_bwd();
+            return L > 0 ? pre_bwd(L - 1, true) : embed_node_bwd();
         }
         if (s == TMDN_TN_LAYER_BWD) {
             {
@@ -1353,12 +1367,13 @@ struct TnRun {
             GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
             for (int g = 0; g < 3; ++g) b.p[g].accumulate = 1;
             TMDN_TRY(mix_launch(EPI_NONE, b, stream));
-            {
+            if (l > 0) {
                 KTimer ktimer__("tn_normalize_bwd", stream);
-                launch_k(tn_normalize_bwd, egrid, 256, 0, stream, w.X[l], w.dXa, NH, H);
+                launch_k(tn_normalize_update_bwd, egrid, 256, 0, stream, w.X[l], w.dXa, w.dX[l - 1], w.dB, NH, H);
                 TMDN_LAUNCH_CHECK();
             }
-            return l > 0 ? pre_bwd(l - 1) : embed_node_bwd();
+            if (l > 0) return pre_bwd(l - 1, true);
+            return embed_node_bwd(w.X[0]);   // layer 0: the normalise adjoint runs inside tn_embed_scale_bwd
         }
         // TMDN_TN_FINAL
         TMDN_CHECK_ARG(forces, "tensornet: null forces pointer");
