@@ -86,6 +86,23 @@ def test_cabi_rejects_bad_arguments_without_a_gpu():
     assert rc == 1 and b"null pointer" in lib.tmdn_last_error()
 
 
+def test_cabi_tuning_knobs_without_a_gpu():
+    """tmdn_set_tuning (include/tmdn.h): query with a negative value, set, restore; unknown keys are an error."""
+    from torchmdnet import _native
+    lib = _native.cabi()
+    lib.tmdn_last_error.restype = ctypes.c_char_p
+    lib.tmdn_set_tuning.restype = ctypes.c_int
+    lib.tmdn_set_tuning.argtypes = [ctypes.c_char_p, ctypes.c_int]
+    defaults = {b"small_gemm": 1, b"lpt_rows": 1, b"pdl": 0, b"fused_nodes": 0}
+    for key, dflt in defaults.items():
+        assert lib.tmdn_set_tuning(key, -1) == dflt, key
+        assert lib.tmdn_set_tuning(key, 1 - dflt) == dflt
+        assert lib.tmdn_set_tuning(key, -1) == 1 - dflt
+        assert lib.tmdn_set_tuning(key, dflt) == 1 - dflt
+    assert lib.tmdn_set_tuning(b"no_such_knob", 1) == -1 and b"no_such_knob" in lib.tmdn_last_error()
+    assert lib.tmdn_set_tuning(None, 1) == -1
+
+
 def test_cpu_tensors_fail_loudly():
     from torchmdnet.models.model import create_model
     from torchmdnet.models.utils import OptimizedDistance
