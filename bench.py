@@ -337,7 +337,9 @@ def main():
     ap.add_argument("--no-flush", action="store_true",
                     help="experiment only: do not flush L2 between the timed steps of `value` (the line says so; not a bench number)")
     ap.add_argument("--table-intervals", type=int, default=0,
-                    help="intervals of the filter tables (0 = the model's default, 4096); A/B runs only")
+                    help="intervals of the filter tables (0 = the model's default, 16 * num_rbf); A/B runs only")
+    ap.add_argument("--no-table-warp", action="store_true",
+                    help="A/B runs only: filter tables on a grid uniform in d (round-1 layout; use with --table-intervals 4096)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -372,6 +374,7 @@ def main():
         rm.filter_mode = args.filter
         if args.table_intervals > 0:
             rm.table_intervals = args.table_intervals
+        rm.table_warp = not args.no_table_warp
     else:
         args.filter = "table"
     z_np, pos0, batch_np, box = make_inputs(args.workload, rank, args)
@@ -460,6 +463,7 @@ def main():
         calc.model.representation_model.filter_mode = args.filter
         if args.table_intervals > 0:
             calc.model.representation_model.table_intervals = args.table_intervals
+        calc.model.representation_model.table_warp = not args.no_table_warp
     if box is not None:
         calc.model.representation_model.distance = rm.distance
     if emb.shape[0] != n_mol:

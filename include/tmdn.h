@@ -75,10 +75,10 @@ int tmdn_profile_report(char* buf, size_t buf_bytes);
  *   "lpt_rows"   1 = edge kernels of small systems visit rows in order of decreasing degree (default 1)
  *   "pdl"        1 = dependent kernels are launched with programmatic stream serialisation (default 0: measured
  *                    slower inside CUDA graphs, profiles/r01i_bench_*_pdl_{on,off}.json)
- *   "fused_nodes" 1 = TensorNet on small systems runs the row-local operations between two edge kernels (mixes, MLPs,
- *                    LayerNorms, 3x3 algebra and their adjoints) as one kernel per chain: 18 launches per step instead
- *                    of 45 (default 0: every CTA has to stream the chain's 0.4-0.9 MB of weights through one SM, which
- *                    is slower than the per-operation kernels, profiles/r01i_node_chain_experiments.md; needs small_gemm)
+ *   "edge_persist" 1 = on large systems (>= 8192 rows, H = 128, table filters) the TensorNet edge kernels run as one
+ *                    persistent CTA per SM that keeps the last "hot_rows" rows of the filter table -- the far end of
+ *                    the grid, where most neighbours of a condensed system are -- in shared memory (default 1)
+ *   "hot_rows"     number of table rows those kernels keep in shared memory (default 24 = 144 KB at H = 128)
  * Returns the previous value (>= 0); value < 0 only queries; -1 for an unknown key (tmdn_last_error says which).
  * Process-wide. */
 int tmdn_set_tuning(const char* key, int value);
@@ -157,10 +157,12 @@ typedef struct tmdn_filter_set {
     int32_t dims[4]; /* K, n1, n2, n3 */
     const float* w[3];
     const float* b[3];
-    /* TABLE mode: [n_int][3][H] float4 cubic coefficients of f(d)*C(d) on a uniform grid over [0, cutoff_upper] */
+    /* TABLE mode: [n_int][3][H] float4 cubic coefficients of f(d)*C(d) on n_int intervals over [0, cutoff_upper],
+     * uniform in S(d) = 1 - exp(-grid_alpha d) + grid_gamma d (grid_alpha = 0: uniform in d); local coordinate
+     * s = S(d) n_int / S(cutoff_upper) - k, value = c.x + s (c.y + s (c.z + s c.w)).  See csrc/table_grid.cuh. */
     const float* table;
     int32_t n_int;
-    int32_t pad_;
+    float grid_alpha, grid_gamma;
 } tmdn_filter_set;
 
 /* Kernel of the plain node GEMMs (MLPs of TensorNet, projections of ET).  TF32X3 = tcgen05 with the three-product tf32
@@ -243,7 +245,8 @@ int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_ato
  * (torchmdnet/models/torchmd_et.py:154-187,272-347; models/utils.py:73-108,496-522; models/output_modules.py:111-115).
  * Weights are device fp32 arrays prepared once by the host side.  "T" = transposed copy for the backward GEMMs.
  * v_proj / dv_proj rows are re-ordered part-major (row p*H + head*hd + c <- reference row head*3hd + p*hd + c).
- * The distance filters are univariate in d and are passed as cubic Hermite tables built in fp64:
+ * The distance filters are univariate in d and are passed as cubic Hermite tables built in fp64 on the grid
+ * (n_int, grid_alpha, grid_gamma) of tmdn_filter_set:
  *   layer table [n_int][4][H] float4 : act(dk_proj(rbf(d))), act(dv_proj(rbf(d))) parts 0..2 (NO cutoff factor;
  *                                      a missing filter (distance_influence) is the constant 1)
  *   ne_table    [n_int][H]    float4 : distance_proj(rbf(d)) * C(d)      (models/utils.py:98-99)
@@ -270,6 +273,7 @@ typedef struct tmdn_et_model {
     int32_t activation, attn_activation, has_neighbor_embedding, n_int;
     int32_t gemm_mode;                      /* TMDN_GEMM_FP32 (default, exact fp32 FFMA) | TMDN_GEMM_TF32X3 (tensor cores) */
     float cutoff_lower, cutoff_upper, mean, std;
+    float grid_alpha, grid_gamma;           /* interval grid of all tables (see tmdn_filter_set) */
     const float* emb;                       /* embedding [max_z,H] */
     const float *ne_emb, *ne_table;         /* neighbor_embedding.embedding [max_z,H], filter table */
     const float *ne_comb_w, *ne_comb_b;     /* combine [H,2H], [H] */

@@ -42,6 +42,31 @@ def test_full_size_hparams_match_reference(cfg):
     check(y, f, g["y"], g["forces"])
 
 
+@pytest.mark.parametrize("cfg", ["ET-QM9", "ET-MD17"])
+def test_table_grid_sweep_against_the_reference(cfg):
+    """ET evaluates its distance filters only through tables, so its parity rests on the table grid: the default
+    (16 * num_rbf intervals uniform in S(d), tensornet.TableGrid), half and twice of it, and the round-1 grid
+    (4096 intervals uniform in d) all meet the reference fixture at the parity tolerances; the spread between the
+    grids shows the margin."""
+    from torchmdnet.models.model import create_model
+    g = load_npz("model_%s.npz" % cfg)
+    seed_everything(int(g["seed"]))
+    m = create_model(g["hparams"]).cuda().eval()
+    rm = m.representation_model
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    K = int(g["hparams"]["num_rbf"])
+    out = {}
+    for warp, n_int in [(True, None), (True, 8 * K), (True, 32 * K), (True, 1024), (True, 2048), (False, 4096)]:
+        rm.table_warp, rm.table_intervals = warp, n_int
+        y, f = m(z, pos, batch)
+        check(y, f, g["y"], g["forces"])
+        out[warp, n_int] = (y.double().cpu(), f.double().cpu())
+    y_ref, f_ref = out[False, 4096]
+    y, f = out[True, None]
+    assert float((y - y_ref).abs().max()) <= 2e-6 * max(1.0, float(y_ref.abs().max()))
+    assert float((f - f_ref).abs().max()) <= 2e-5
+
+
 def test_reference_expected_pkl_row():
     """tests/expected.pkl, equivariant-transformer/Scalar row (tests/test_model.py:137-188)."""
     from torchmdnet.models.model import create_model

@@ -48,22 +48,12 @@ def check(y, f, y_ref, f_ref, e_rtol=E_RTOL, f_atol=F_ATOL):
     assert float((f - f_ref).abs().max()) <= f_atol, float((f - f_ref).abs().max())
 
 
-@pytest.fixture(params=[0, 1], ids=["per_op", "fused_chains"])
-def fused_nodes(request):
-    from torchmdnet import _native
-    _native.load()
-    ops = torch.ops.torchmdnet_b200
-    old = ops.set_tuning("fused_nodes", request.param)
-    yield request.param
-    ops.set_tuning("fused_nodes", old)
-
-
 SMALL_TN = ["small_tensornet_o3.npz", "small_tensornet_so3.npz", "small_tensornet_gauss.npz"]
 
 
 @pytest.mark.parametrize("mode", ["exact", "table"])
 @pytest.mark.parametrize("name", SMALL_TN)
-def test_small_models_match_reference(name, mode, fused_nodes):
+def test_small_models_match_reference(name, mode):
     g = load_npz(name)
     m = build(g, mode)
     y, f = m(tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda())
@@ -112,33 +102,14 @@ def test_kernel_selection_knobs_agree():
     m = create_model(g["hparams"]).cuda().eval()
     m.representation_model.filter_mode = "table"
     z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
-    old = {k: ops.set_tuning(k, -1) for k in ("small_gemm", "lpt_rows", "pdl", "fused_nodes")}
-    assert old == {"small_gemm": 1, "lpt_rows": 1, "pdl": 0, "fused_nodes": 0}
+    old = {k: ops.set_tuning(k, -1) for k in ("small_gemm", "lpt_rows", "pdl", "edge_persist", "hot_rows")}
+    assert old == {"small_gemm": 1, "lpt_rows": 1, "pdl": 0, "edge_persist": 1, "hot_rows": 24}
     with pytest.raises(RuntimeError):
         ops.set_tuning("no_such_knob", 1)
     out = {}
     try:
-        # fused node chains (opt-in) against one launch per operation (default)
-        ops.set_tuning("fused_nodes", 1)
-        yF, fF = m(z, pos, batch)
-        check(yF, fF, g["y"], g["forces"])
-        c0 = ops.launch_count()
-        m(z, pos, batch)
-        n_fused = ops.launch_count() - c0
-        # the representation output and the stage buffers are written by the chains as well
-        xF = m.representation_model(z, pos, batch)[0].clone()
-        ops.set_tuning("fused_nodes", 0)
-        x0 = m.representation_model(z, pos, batch)[0]
-        torch.testing.assert_close(xF, x0, rtol=1e-5, atol=1e-6)
         y0, f0 = m(z, pos, batch)
         y1, f1 = y0.clone(), f0.clone()
-        c0 = ops.launch_count()
-        m(z, pos, batch)
-        n_unfused = ops.launch_count() - c0
-        assert n_fused < n_unfused - 20, (n_fused, n_unfused)
-        # (inside a chain the k range of a GEMM is split across warps: another summation order)
-        torch.testing.assert_close(yF, y0, rtol=3e-6, atol=3e-6)
-        torch.testing.assert_close(fF, f0, rtol=0, atol=1e-5)
         for sg in (1, 0):
             for lpt in (1, 0):
                 ops.set_tuning("small_gemm", sg)
@@ -195,7 +166,7 @@ def test_reference_expected_pkl_row():
     torch.testing.assert_close(f.cpu(), torch.tensor(e["expected_deriv"]), rtol=1.3e-6, atol=1e-5)
 
 
-def test_intermediate_buffers_match_staged_restatement(fused_nodes):
+def test_intermediate_buffers_match_staged_restatement():
     g = load_npz("small_tensornet_o3.npz")
     m = build(g, "exact")
     z, pos, batch = tt(g["z"]), tt(g["pos"]), tt(g["batch"])
@@ -356,6 +327,75 @@ def test_overflow_is_reported():
     z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
     y, f, status = rm.energy_forces(z, pos, batch, int(batch.max()) + 1, m.output_model, 0.0, 1.0)
     assert int(status[1]) == 1 and int(status[0]) > z.shape[0]
+    # a truncated edge list is not symmetric, so the analytic forces would not belong to the energy: both are
+    # poisoned on the device (nothing on the sync-free path reads the status flags)
+    assert bool(torch.isnan(y).all()) and bool(torch.isnan(f).all())
     rm.distance.check_errors = True
     with pytest.raises(RuntimeError, match="max_num_pairs"):
         m(z, pos, batch)
+
+
+def test_bad_inputs_poison_the_result():
+    """z outside [0, max_z) and an unsorted batch vector (molecule ranges are found by binary search) cannot be
+    evaluated; the kernels flag them in status[2] / status[3] and write NaN instead of a wrong number."""
+    g = load_npz("small_tensornet_o3.npz")
+    m = build(g, "table")
+    rm = m.representation_model
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    n_mol = int(batch.max()) + 1
+    y0, f0, st0 = rm.energy_forces(z, pos, batch, n_mol, m.output_model, 0.0, 1.0)
+    assert st0[1:].tolist() == [0, 0, 0] and bool(torch.isfinite(y0).all()) and bool(torch.isfinite(f0).all())
+    zb = z.clone()
+    zb[0] = int(g["hparams"]["max_z"]) + 3
+    y, f, st = rm.energy_forces(zb, pos, batch, n_mol, m.output_model, 0.0, 1.0)
+    assert int(st[2]) == 1 and bool(torch.isnan(y).all()) and bool(torch.isnan(f).all())
+    if n_mol > 1:
+        bb = batch.flip(0).contiguous()
+        y, f, st = rm.energy_forces(z, pos, bb, n_mol, m.output_model, 0.0, 1.0)
+        assert int(st[3]) == 1 and bool(torch.isnan(y).all()) and bool(torch.isnan(f).all())
+
+
+def _water_model(n_side):
+    import synth_inputs as S
+    from torchmdnet.models.model import create_model
+    from torchmdnet.models.utils import OptimizedDistance
+    hp = dict(model="tensornet", precision=32, trainable_rbf=False, activation="silu", cutoff_lower=0.0, max_z=128,
+              rbf_type="expnorm", equivariance_invariance_group="O(3)", derivative=True, atom_filter=-1,
+              prior_model=None, output_model="Scalar", reduce_op="add", num_layers=2, embedding_dimension=128,
+              num_rbf=32, cutoff_upper=4.5, max_num_neighbors=128)          # examples/TensorNet-ANI1X.yaml
+    seed_everything(1234)
+    m = create_model(hp).cuda().eval()
+    z, pos, batch, box = S.water_box(n_side, seed=4)
+    m.representation_model.distance = OptimizedDistance(0.0, 4.5, max_num_pairs=-128, return_vecs=True, loop=True,
+                                                        check_errors=False, resize_to_fit=False, box=tt(box),
+                                                        strategy="cell")
+    return m, hp, tt(z).cuda(), tt(pos).cuda(), tt(batch).cuda(), tt(box)
+
+
+def test_persistent_edge_kernels_are_bit_identical_to_the_per_row_ones():
+    """Large systems (>= 8192 rows) run the edge kernels as persistent CTAs with the hot rows of the filter table in
+    shared memory (tmdn_set_tuning "edge_persist", "hot_rows").  Where a coefficient comes from and which CTA handles
+    a row do not change a single bit: same energies and forces with the feature off and for every hot-row count; the
+    exact-filter mode (no tables) agrees to the parity tolerances."""
+    from torchmdnet import _native
+    _native.load()
+    ops = torch.ops.torchmdnet_b200
+    m, hp, z, pos, batch, box = _water_model(14)          # 8232 atoms
+    rm = m.representation_model
+    rm.filter_mode = "table"
+    old = {k: ops.set_tuning(k, -1) for k in ("edge_persist", "hot_rows")}
+    try:
+        ops.set_tuning("edge_persist", 0)
+        y0, f0 = m(z, pos, batch)
+        c0 = ops.launch_count()
+        for hot in (24, 0, 7, 32):
+            ops.set_tuning("edge_persist", 1)
+            ops.set_tuning("hot_rows", hot)
+            y1, f1 = m(z, pos, batch)
+            assert torch.equal(y0, y1) and torch.equal(f0, f1), hot
+    finally:
+        for k, v in old.items():
+            ops.set_tuning(k, v)
+    rm.filter_mode = "exact"
+    ye, fe = m(z, pos, batch)
+    check(y0, f0, ye.cpu(), fe.cpu())

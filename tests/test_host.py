@@ -93,7 +93,7 @@ def test_cabi_tuning_knobs_without_a_gpu():
     lib.tmdn_last_error.restype = ctypes.c_char_p
     lib.tmdn_set_tuning.restype = ctypes.c_int
     lib.tmdn_set_tuning.argtypes = [ctypes.c_char_p, ctypes.c_int]
-    defaults = {b"small_gemm": 1, b"lpt_rows": 1, b"pdl": 0, b"fused_nodes": 0}
+    defaults = {b"small_gemm": 1, b"lpt_rows": 1, b"pdl": 0, b"edge_persist": 1}
     for key, dflt in defaults.items():
         assert lib.tmdn_set_tuning(key, -1) == dflt, key
         assert lib.tmdn_set_tuning(key, 1 - dflt) == dflt
@@ -140,26 +140,59 @@ def test_rbf_modules_match_oracle():
     assert float(e(torch.tensor([5.5])).abs().max()) == 0.0
 
 
-def test_filter_table_interpolates_filter():
-    """The Hermite table the host builds for filter_mode='table' reproduces the filter MLP to ~1e-7."""
+@pytest.mark.parametrize("name,warp", [("small_tensornet_o3.npz", True), ("small_tensornet_o3.npz", False),
+                                       ("small_tensornet_gauss.npz", True)])
+def test_filter_table_interpolates_filter(name, warp):
+    """The Hermite tables the host builds for filter_mode='table' (TableGrid: 16*num_rbf intervals uniform in
+    S(d) = 1 - exp(-alpha d) + gamma d; uniform in d for Gaussian smearing / warp=False with 4096 intervals)
+    reproduce the filter MLP and its derivative, evaluated the way the kernels do (tab_locate)."""
     from torchmdnet.models.model import create_model
-    from torchmdnet.models.tensornet import filter_table, hermite_coefficients
-    g = load_npz("small_tensornet_o3.npz")
+    from torchmdnet.models.tensornet import TableGrid, filter_table
+    g = load_npz(name)
     m = create_model(g["hparams"]).double()
     m.load_state_dict({k: v.double() if v.is_floating_point() else v for k, v in g["sd"].items()})
     rm = m.representation_model
-    hi = float(rm.cutoff_upper)
+    lo, hi = float(rm.cutoff_lower), float(rm.cutoff_upper)
     ls = rm.layers[0].linears_scalar
     layers = [(l.weight.detach(), l.bias.detach()) for l in ls]
-    p0, p1 = rm.distance_expansion.means, rm.distance_expansion.betas
-    n_int = 4096
-    grid = torch.linspace(0, hi, n_int + 1, dtype=torch.float64)
-    f, df = filter_table(grid, "expnorm", p0, p1, 0.0, hi, layers, "silu", True)
-    c = hermite_coefficients(f, df, hi / n_int)
-    d = torch.rand(2000, dtype=torch.float64) * hi * 0.999
-    k = (d / (hi / n_int)).long().clamp(max=n_int - 1)
-    s = (d / (hi / n_int) - k)[:, None]
-    ck = c[k]
+    if rm.rbf_type == "expnorm":
+        p0, p1 = rm.distance_expansion.means, rm.distance_expansion.betas
+    else:
+        p0, p1 = rm.distance_expansion.offset, rm.distance_expansion.coeff.expand(rm.num_rbf)
+    n_int = rm.resolved_table_intervals() if warp and rm.rbf_type == "expnorm" else 4096
+    grid = TableGrid(n_int, lo, hi, rm.rbf_type, warp)
+    assert (grid.alpha > 0) == (warp and rm.rbf_type == "expnorm")
+    nodes = grid.nodes()
+    assert float(nodes[0]) == 0.0 and float(nodes[-1]) == hi and bool((nodes[1:] > nodes[:-1]).all())
+    torch.testing.assert_close(grid.S(nodes) / grid.step, torch.arange(n_int + 1, dtype=torch.float64), rtol=0, atol=1e-9)
+    f, df = filter_table(nodes, rm.rbf_type, p0, p1, lo, hi, layers, "silu", True)
+    c = grid.coefficients(nodes, f, df)
+    d = torch.cat([torch.zeros(1, dtype=torch.float64), 0.5 + torch.rand(4000, dtype=torch.float64) * (hi * 0.999 - 0.5)])
+    k, s, ds = grid.locate(d)
+    s, ck = s[:, None], c[k]
     approx = ck[..., 0] + s * (ck[..., 1] + s * (ck[..., 2] + s * ck[..., 3]))
-    exact, _ = filter_table(d, "expnorm", p0, p1, 0.0, hi, layers, "silu", True)
+    dapprox = (ck[..., 1] + s * (2 * ck[..., 2] + 3 * s * ck[..., 3])) * ds[:, None]
+    exact, dexact = filter_table(d, rm.rbf_type, p0, p1, lo, hi, layers, "silu", True)
     assert float((approx - exact).abs().max()) < 2e-7 * max(1.0, float(exact.abs().max()))
+    assert float((dapprox - dexact).abs().max()) < 5e-6 * max(1.0, float(dexact.abs().max()))
+
+
+def test_deepcopy_and_pickle_do_not_share_the_native_handle():
+    """A copied model must not carry the original's integer handle / workspace (its first call would destroy the
+    original's packed weights): FusedRepresentation.__getstate__ resets them."""
+    import copy
+    import pickle
+    from torchmdnet.models.model import create_model
+    g = load_npz("small_tensornet_o3.npz")
+    m = create_model(g["hparams"])
+    rm = m.representation_model
+    rm._handle, rm._pack_key, rm._workspace = 7, ("k",), torch.zeros(4)
+    try:
+        for c in (copy.deepcopy(m), pickle.loads(pickle.dumps(m))):
+            crm = c.representation_model
+            assert crm._handle is None and crm._pack_key is None and crm._workspace is None
+            assert crm.table_warp is True and crm.filter_mode == rm.filter_mode
+            assert all(torch.equal(a, b) for a, b in zip(c.state_dict().values(), m.state_dict().values()))
+        assert rm._handle == 7
+    finally:
+        rm._handle = rm._pack_key = rm._workspace = None

@@ -21,7 +21,8 @@ struct KTimer {
 };
 
 // process-wide tuning knobs (tmdn_set_tuning, defined in scan.cu)
-enum { TMDN_TUNE_SMALL_GEMM = 0, TMDN_TUNE_LPT_ROWS = 1, TMDN_TUNE_PDL = 2, TMDN_TUNE_FUSED_NODES = 3, TMDN_TUNE_COUNT = 4 };
+enum { TMDN_TUNE_SMALL_GEMM = 0, TMDN_TUNE_LPT_ROWS = 1, TMDN_TUNE_PDL = 2, TMDN_TUNE_EDGE_PERSIST = 3, TMDN_TUNE_HOT_ROWS = 4,
+       TMDN_TUNE_COUNT = 5 };
 extern int g_tmdn_tuning[TMDN_TUNE_COUNT];
 
 #define TMDN_CHECK_ARG(cond, ...)                 \
@@ -90,6 +91,16 @@ static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 blo
 }
 #endif
 
+// SM count of the current device (B200: 148); queried once -- one process drives one GPU model
+static inline int tmdn_sm_count() {
+    static const int n = [] {
+        int dev = 0, v = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
+            v = 148;
+        return v;
+    }();
+    return n;
+}
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 

@@ -70,7 +70,7 @@ constexpr int EDGE_RED_FLOATS = 128;
 static inline EdgeLaunch edge_launch(int N, int H, int max_threads, int nv = 9) {
     int smax = max_threads / H;
     if (smax < 1) smax = 1;
-    const long long target = 148LL * 2048;
+    const long long target = (long long)tmdn_sm_count() * 2048;
     int S = 1;
     while (S < smax && (long long)N * H * S < target) S *= 2;
     int A = 128 / (H * S);

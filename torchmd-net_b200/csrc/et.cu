@@ -15,6 +15,7 @@
 #include "gemm.cuh"
 #include "node_gemm.cuh"
 #include "edge_common.cuh"
+#include "table_grid.cuh"
 #include "scan.cuh"
 #include <string>
 #include <vector>
@@ -23,18 +24,15 @@ namespace {
 
 struct Tab {
     const float4* t;
-    float inv_h;
-    int n_int;
+    TabGrid grid;   // table_grid.cuh
 };
 // NF filters per interval: value and d/dd from the same cubic.  Split into the loads (tab_load) and the arithmetic
 // (tab_poly) so that an edge kernel can put the loads of several edges in flight before it starts to compute.
-template <int NF> struct TabRow { float4 c[NF]; float s; };
+template <int NF> struct TabRow { float4 c[NF]; float s, ds; };
 template <int NF>
 __device__ __forceinline__ void tab_load(const Tab& tb, float d, int H, int h, TabRow<NF>& r) {
-    float s = d * tb.inv_h;
-    int k = (int)s;
-    k = k > tb.n_int - 1 ? tb.n_int - 1 : k;
-    r.s = s - (float)k;
+    int k;
+    tab_locate(tb.grid, d, k, r.s, r.ds);
 #pragma unroll
     for (int g = 0; g < NF; ++g) r.c[g] = __ldg(&tb.t[((size_t)k * NF + g) * H + h]);
 }
@@ -44,7 +42,7 @@ __device__ __forceinline__ void tab_poly(const Tab& tb, const TabRow<NF>& r, flo
     for (int g = 0; g < NF; ++g) {
         const float4 c = r.c[g];
         f[g] = c.x + r.s * (c.y + r.s * (c.z + r.s * c.w));
-        df[g] = (c.y + r.s * (2.0f * c.z + 3.0f * r.s * c.w)) * tb.inv_h;
+        df[g] = (c.y + r.s * (2.0f * c.z + 3.0f * r.s * c.w)) * r.ds;
     }
 }
 template <int NF>
@@ -70,7 +68,8 @@ template <int HDC> __device__ __forceinline__ float seg_sum_t(float v, int hd) {
 }
 
 __global__ void et_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ z32, int n, int max_z,
-                               const int32_t* __restrict__ num_found, long long max_edges, int32_t* __restrict__ status) {
+                               const int32_t* __restrict__ num_found, long long max_edges, int32_t* __restrict__ status,
+                               const int64_t* __restrict__ batch) {
     pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) {
@@ -79,6 +78,7 @@ __global__ void et_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ 
         status[1] = f > max_edges ? 1 : 0;
     }
     if (i >= n) return;
+    if (i > 0 && batch[i] < batch[i - 1]) status[3] = 1;   // the molecule ranges are found by binary search: batch must be sorted
     long long v = z[i];
     if (v < 0 || v >= max_z) {
         status[2] = 1;
@@ -282,8 +282,10 @@ __global__ void et_head_energy(const float* __restrict__ a, const float* __restr
     s = warp_sum(s);
     if (lane == 0) e_atom[i] = (s + b[0]) * stdv;
 }
+// status[1] / status[2] (edge capacity exceeded, z out of range) poison the result with NaN: see tn_mol_reduce
 __global__ void __launch_bounds__(128) et_mol_reduce(const float* __restrict__ e_atom, const int64_t* __restrict__ batch,
-                                                     int N, float mean, float* __restrict__ energy) {
+                                                     int N, float mean, float* __restrict__ energy,
+                                                     const int32_t* __restrict__ status) {
     pdl_sync();
     __shared__ float s_part[128];
     const long long m = blockIdx.x;
@@ -301,7 +303,7 @@ __global__ void __launch_bounds__(128) et_mol_reduce(const float* __restrict__ e
         if (threadIdx.x < o) s_part[threadIdx.x] += s_part[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) energy[m] = s_part[0] + mean;
+    if (threadIdx.x == 0) energy[m] = (status[1] | status[2] | status[3]) ? __int_as_float(0x7fc00000) : s_part[0] + mean;
 }
 
 // ================================================================== backward kernels
@@ -509,7 +511,8 @@ template <bool NE>
 __global__ void __launch_bounds__(512)
 et_final_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom,
              const int* __restrict__ z32, const float* __restrict__ ne_emb, Tab tb, const float* __restrict__ g_xn,
-             const float* __restrict__ gpos, float* __restrict__ forces, int N, int H) {
+             const float* __restrict__ gpos, float* __restrict__ forces, int N, int H,
+             const int32_t* __restrict__ status) {
     pdl_sync();
     extern __shared__ float smem[];
     float* s_red = smem;
@@ -532,9 +535,11 @@ et_final_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const
     }
     atom_reduce<3>(gp, s_red);
     if (valid && h == 0 && sl == 0) {
-        forces[3 * (size_t)i] = -(gpos[3 * (size_t)i] + gp[0]);
-        forces[3 * (size_t)i + 1] = -(gpos[3 * (size_t)i + 1] + gp[1]);
-        forces[3 * (size_t)i + 2] = -(gpos[3 * (size_t)i + 2] + gp[2]);
+        const bool bad = (status[1] | status[2] | status[3]) != 0;
+        const float nan = __int_as_float(0x7fc00000);
+        forces[3 * (size_t)i] = bad ? nan : -(gpos[3 * (size_t)i] + gp[0]);
+        forces[3 * (size_t)i + 1] = bad ? nan : -(gpos[3 * (size_t)i + 1] + gp[1]);
+        forces[3 * (size_t)i + 2] = bad ? nan : -(gpos[3 * (size_t)i + 2] + gp[2]);
     }
 }
 
@@ -707,10 +712,10 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     }
     TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
     ET_K("et_prep", launch_k(et_prep_kernel, (unsigned)cdiv(N, 256), 256, 0, stream, z, w.z32, N, m->max_z, w.num_found,
-                                                                                (long long)P, status));
+                                                                                (long long)P, status, batch));
     const float4* geom = (const float4*)w.geom;
-    const float inv_h = (float)((double)m->n_int / (double)hi);
-    const Tab ne_tab{(const float4*)m->ne_table, inv_h, m->n_int};
+    const TabGrid tgrid = make_tab_grid(m->n_int, hi, m->grid_alpha, m->grid_gamma);
+    const Tab ne_tab{(const float4*)m->ne_table, tgrid};
     const EdgeLaunch e1 = edge_launch(N, H, 1024, 1), e4 = edge_launch(N, H, ET_FWD_THREADS, 4), e8 = edge_launch(N, H, 512, 8);
     const EdgeLaunch e8b = edge_launch(N, H, ET_BWD_THREADS, 8);
     const int apb = H >= 128 ? 1 : 128 / H;
@@ -733,7 +738,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     // ---- attention layers
     for (int l = 0; l < L; ++l) {
         const tmdn_et_layer& ly = m->layer[l];
-        const Tab tb{(const float4*)ly.table, inv_h, m->n_int};
+        const Tab tb{(const float4*)ly.table, tgrid};
         ET_K("et_ln_fwd", launch_k(et_ln_fwd, lgrid, lblock, 0, stream, w.X[l], ly.ln_w, ly.ln_b, w.xl, H, w.stat[l], N, H));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.xl, H, ly.qkv_w, ly.qkv_b, w.QKV[l], 5 * H, N, 5 * H, H), stream, tc));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.VEC[l], H, ly.vp_w, nullptr, w.VP[l], 3 * H, 3 * N, 3 * H, H), stream, tc));
@@ -776,7 +781,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     }
     ET_K("et_head_energy", launch_k(et_head_energy, (unsigned)cdiv(N, 4), 128, 0, stream, w.a0_2, g2.u2_w, g2.u2_b, m->std,
                                                                                    w.e_atom, N, H2));
-    ET_K("et_mol_reduce", launch_k(et_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy));
+    ET_K("et_mol_reduce", launch_k(et_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy, status));
     if (!forces) return TMDN_OK;
 
     // ================================================================= backward
@@ -810,7 +815,7 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
                                                               H));
     for (int l = L - 1; l >= 0; --l) {
         const tmdn_et_layer& ly = m->layer[l];
-        const Tab tb{(const float4*)ly.table, inv_h, m->n_int};
+        const Tab tb{(const float4*)ly.table, tgrid};
         ET_K("et_update_bwd", launch_k(et_update_bwd, egrid, 256, 0, stream, w.g_x, g_vec, w.VP[l], w.O[l], w.g_o, w.g_vp,
                                                                        g_vec_new, NH, H));
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_o, 3 * H, ly.o_wT, nullptr, w.g_xa, H, N, H, 3 * H), stream, tc));
@@ -834,10 +839,10 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     if (m->has_neighbor_embedding) {
         TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_x, H, m->ne_comb_w2T, nullptr, w.g_xn, H, N, H, H), stream, tc));
         ET_K("et_final_bwd", launch_k(et_final_bwd<true>, e8.grid, e8.block, e8.smem, stream, 
-                                 w.row_ptr, w.col, geom, w.z32, m->ne_emb, ne_tab, w.g_xn, w.gpos, forces, N, H));
+                                 w.row_ptr, w.col, geom, w.z32, m->ne_emb, ne_tab, w.g_xn, w.gpos, forces, N, H, status));
     } else {
         ET_K("et_final_bwd", launch_k(et_final_bwd<false>, e8.grid, e8.block, e8.smem, stream, 
-                                 w.row_ptr, w.col, geom, w.z32, nullptr, ne_tab, nullptr, w.gpos, forces, N, H));
+                                 w.row_ptr, w.col, geom, w.z32, nullptr, ne_tab, nullptr, w.gpos, forces, N, H, status));
     }
     return TMDN_OK;
 }

@@ -228,7 +228,12 @@ tc_gemm_kernel(const __grid_constant__ GMaps M, const __grid_constant__ GParams 
 }
 
 // 2-D row-major fp32 matrix [rows, cols] with leading dimension ld; box = 32 columns x 128 rows, 128-byte swizzle
+static inline bool make_map_2d_raw(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld);
 static inline bool make_map_2d(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld) {
+    return tcmix::map_cached(m, tcmix::MapKey{p, rows, cols, ld, 2},
+                             [&](CUtensorMap* o) { return make_map_2d_raw(o, p, rows, cols, ld); });
+}
+static inline bool make_map_2d_raw(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld) {
     const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
     const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
     const cuuint32_t box[2] = {(cuuint32_t)KC, (cuuint32_t)TILE};
@@ -269,7 +274,7 @@ static inline int launch(int epi, const GemmP& p, cudaStream_t stream) {
         return TMDN_EINVAL;
     }
     const long long tiles = (long long)P.m_tiles * P.n_tiles;
-    const unsigned grid = (unsigned)(tiles < 148 ? tiles : 148);
+    const unsigned grid = (unsigned)(tiles < tmdn_sm_count() ? tiles : tmdn_sm_count());
     launch_k(tc_gemm_kernel, grid, GTHREADS_TC, GSMEM_BYTES, stream, M, P);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;

@@ -23,6 +23,8 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <mutex>
+#include <unordered_map>
 #include "common.cuh"
 #include "gemm.cuh"
 
@@ -370,8 +372,35 @@ static inline EncodeTiledFn encode_fn() {
     }();
     return fn;
 }
+// An encoded map is a pure function of (pointer, extents, box): memoised, because one encode costs about a
+// microsecond of host time and a mix launch needs 9-12 of them (invisible inside a CUDA graph, a real cost in
+// eager calls and in the staged, spatially decomposed path).
+struct MapKey {
+    const void* p;
+    int64_t a, b, c;
+    int kind;
+    bool operator==(const MapKey& o) const { return p == o.p && a == o.a && b == o.b && c == o.c && kind == o.kind; }
+};
+struct MapKeyHash {
+    size_t operator()(const MapKey& k) const {
+        size_t h = (size_t)(uintptr_t)k.p * 0x9E3779B97F4A7C15ull;
+        h ^= (size_t)k.a * 0xC2B2AE3D27D4EB4Full + (size_t)k.b * 0x165667B19E3779F9ull + (size_t)k.c * 31 + (size_t)k.kind;
+        return h;
+    }
+};
+template <class Build> static inline bool map_cached(CUtensorMap* out, const MapKey& key, Build build) {
+    static std::mutex mu;
+    static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return true; }
+    if (!build(out)) return false;
+    if (cache.size() > 8192) cache.clear();
+    cache.emplace(key, *out);
+    return true;
+}
 // X viewed as [atoms][9][H] fp32; box = 32 channels x gs components x na atoms, 128-byte swizzle
-static inline bool make_map_x(CUtensorMap* m, const float* X, int64_t n_atoms, int H, int gs, int na) {
+static inline bool make_map_x_raw(CUtensorMap* m, const float* X, int64_t n_atoms, int H, int gs, int na) {
     const cuuint64_t dims[3] = {(cuuint64_t)H, 9, (cuuint64_t)n_atoms};
     const cuuint64_t strides[2] = {(cuuint64_t)H * 4, (cuuint64_t)H * 36};
     const cuuint32_t box[3] = {(cuuint32_t)KC, (cuuint32_t)gs, (cuuint32_t)na};
@@ -380,7 +409,15 @@ static inline bool make_map_x(CUtensorMap* m, const float* X, int64_t n_atoms, i
                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
+static inline bool make_map_w_raw(CUtensorMap* m, const float* W, int H);
+static inline bool make_map_x(CUtensorMap* m, const float* X, int64_t n_atoms, int H, int gs, int na) {
+    return map_cached(m, MapKey{X, n_atoms, H, gs * 1024 + na, 0},
+                      [&](CUtensorMap* o) { return make_map_x_raw(o, X, n_atoms, H, gs, na); });
+}
 static inline bool make_map_w(CUtensorMap* m, const float* W, int H) {
+    return map_cached(m, MapKey{W, H, 0, 0, 1}, [&](CUtensorMap* o) { return make_map_w_raw(o, W, H); });
+}
+static inline bool make_map_w_raw(CUtensorMap* m, const float* W, int H) {
     const cuuint64_t dims[2] = {(cuuint64_t)H, (cuuint64_t)H};
     const cuuint64_t strides[1] = {(cuuint64_t)H * 4};
     const cuuint32_t box[2] = {(cuuint32_t)KC, (cuuint32_t)TILE};
@@ -432,7 +469,7 @@ static inline int launch(int epi, const GemmBatch& b, cudaStream_t stream) {
         }
     }
     // CTAs per problem in proportion to its tiles (at least one, at most its tile count)
-    const int sms = 148;
+    const int sms = tmdn_sm_count();
     int ctas[3], used = 0;
     for (int g = 0; g < 3; ++g) {
         long long c = total_tiles <= sms ? P.p[g].tiles : (long long)P.p[g].tiles * sms / total_tiles;

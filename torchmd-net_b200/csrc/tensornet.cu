@@ -17,6 +17,7 @@
 #include "tc_mix.cuh"
 #include "tensor3.cuh"
 #include "edge_common.cuh"
+#include "table_grid.cuh"
 #include "scan.cuh"
 #include <vector>
 #include <string>
@@ -27,21 +28,28 @@ namespace {
 struct FilterView {
     const float* F;     // [E,3,H]   (exact mode, CSR edge order)
     const float* dF;    // [E,3,H]
-    const float4* tab;  // [n_int,3,H] cubic coefficients (table mode)
-    float inv_h;
-    int n_int;
+    const float4* tab;  // [n_int,3,H] cubic coefficients (table mode) on the grid `grid` (table_grid.cuh)
+    TabGrid grid;
+    const float4* hot;  // shared-memory copy of rows [k_hot, n_int) (persistent large-system kernels only)
+    int k_hot;
 };
 
-template <bool TAB>
+// coefficient row of filter g of interval k for channel h: shared memory for the hot rows, L2 for the rest
+template <bool HOT>
+__device__ __forceinline__ float4 filter_row(const FilterView& fv, int k, int g, int H, int h) {
+    if (HOT && k >= fv.k_hot) return fv.hot[((size_t)(k - fv.k_hot) * 3 + g) * H + h];
+    return __ldg(&fv.tab[((size_t)k * 3 + g) * H + h]);
+}
+
+template <bool TAB, bool HOT = false>
 __device__ __forceinline__ void filter_val(const FilterView& fv, size_t e, float d, int H, int h, float f[3]) {
     if (TAB) {
-        float s = d * fv.inv_h;
-        int k = (int)s;
-        k = k > fv.n_int - 1 ? fv.n_int - 1 : k;
-        s -= (float)k;
+        int k;
+        float s, ds;
+        tab_locate(fv.grid, d, k, s, ds);
 #pragma unroll
         for (int g = 0; g < 3; ++g) {
-            const float4 c = __ldg(&fv.tab[((size_t)k * 3 + g) * H + h]);
+            const float4 c = filter_row<HOT>(fv, k, g, H, h);
             f[g] = c.x + s * (c.y + s * (c.z + s * c.w));
         }
     } else {
@@ -49,19 +57,18 @@ __device__ __forceinline__ void filter_val(const FilterView& fv, size_t e, float
         for (int g = 0; g < 3; ++g) f[g] = fv.F[(e * 3 + g) * H + h];
     }
 }
-template <bool TAB>
+template <bool TAB, bool HOT = false>
 __device__ __forceinline__ void filter_val_grad(const FilterView& fv, size_t e, float d, int H, int h, float f[3],
                                                 float df[3]) {
     if (TAB) {
-        float s = d * fv.inv_h;
-        int k = (int)s;
-        k = k > fv.n_int - 1 ? fv.n_int - 1 : k;
-        s -= (float)k;
+        int k;
+        float s, ds;
+        tab_locate(fv.grid, d, k, s, ds);
 #pragma unroll
         for (int g = 0; g < 3; ++g) {
-            const float4 c = __ldg(&fv.tab[((size_t)k * 3 + g) * H + h]);
+            const float4 c = filter_row<HOT>(fv, k, g, H, h);
             f[g] = c.x + s * (c.y + s * (c.z + s * c.w));
-            df[g] = (c.y + s * (2.0f * c.z + 3.0f * s * c.w)) * fv.inv_h;
+            df[g] = (c.y + s * (2.0f * c.z + 3.0f * s * c.w)) * ds;
         }
     } else {
 #pragma unroll
@@ -107,7 +114,8 @@ constexpr int LPT_MAX_ROWS = 1024;
 // order of the edge kernels: rows sorted by decreasing degree, ties by index (a pure function of the graph)
 __global__ void tn_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ z32, int n, int max_z,
                                const int32_t* __restrict__ num_found, long long max_edges, int32_t* __restrict__ status,
-                               const int* __restrict__ row_ptr, int n_rows, int* __restrict__ order) {
+                               const int* __restrict__ row_ptr, int n_rows, int* __restrict__ order,
+                               const int64_t* __restrict__ batch) {
     pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (order != nullptr) {
@@ -130,6 +138,7 @@ __global__ void tn_prep_kernel(const int64_t* __restrict__ z, int* __restrict__ 
         status[1] = f > max_edges ? 1 : 0;
     }
     if (i >= n) return;
+    if (i > 0 && batch[i] < batch[i - 1]) status[3] = 1;   // molecule ranges are found by binary search: batch must be sorted
     long long v = z[i];
     if (v < 0 || v >= max_z) {
         status[2] = 1;
@@ -189,6 +198,39 @@ __global__ void tn_filter_finalize_kernel(const float4* __restrict__ geom, long 
 // nh = LayerNorm_H(||I+A+S||^2)                                                     (tensornet.py:316)
 // HC > 0: hidden width known at compile time -> the 9 component rows of a node tensor are immediate offsets from one
 // base pointer (saves ~40 address instructions per edge; the kernels are issue-bound once the gathers hit L2)
+// partial sums of row i over the edges r0+sl, r0+sl+S, ... (one slice of the row)
+template <bool TAB, bool HOT>
+__device__ __forceinline__ void embed_fwd_row(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                                              const float4* __restrict__ geom, const int* __restrict__ z32,
+                                              const float* __restrict__ Pz, const float* __restrict__ Qz,
+                                              const FilterView& fv, int i, int sl, int S, int H, int h, float acc[9]) {
+    const float pz = Pz[(size_t)z32[i] * H + h];
+    const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+    // the index, geometry and element of the NEXT edge of this slice are fetched while the gathers of the current
+    // one are in flight: one dependent round trip per edge instead of three (col -> z32 -> Q row)
+    int e = r0 + sl, jn = 0, zn = 0;
+    float4 gn = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (e < r1) { jn = col[e]; gn = geom[e]; zn = z32[jn]; }
+    for (; e < r1; e += S) {
+        const float4 g = gn;
+        const int zj = zn, e2 = e + S;
+        if (e2 < r1) { jn = col[e2]; gn = geom[e2]; }
+        float f[3];
+        filter_val<TAB, HOT>(fv, (size_t)e, g.w, H, h, f);
+        const float zv = pz + Qz[(size_t)zj * H + h];
+        if (e2 < r1) zn = z32[jn];
+        const float w1 = zv * f[0], w2 = zv * f[1], w3 = zv * f[2];
+        const float n2 = (g.x * g.x + g.y * g.y + g.z * g.z) * (1.0f / 3.0f);
+        acc[0] += w1;
+        acc[1] += w2 * g.x; acc[2] += w2 * g.y; acc[3] += w2 * g.z;
+        acc[4] += w3 * (g.x * g.x - n2);
+        acc[5] += w3 * (g.y * g.y - n2);
+        acc[6] += w3 * (g.x * g.y);
+        acc[7] += w3 * (g.x * g.z);
+        acc[8] += w3 * (g.y * g.z);
+    }
+}
+
 template <bool TAB, int HC = 0>
 __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                                   const float4* __restrict__ geom, const int* __restrict__ z32,
@@ -207,33 +249,7 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict_
     float acc[9];
 #pragma unroll
     for (int c = 0; c < 9; ++c) acc[c] = 0.f;
-    if (valid) {
-        const float pz = Pz[(size_t)z32[i] * H + h];
-        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        // the index, geometry and element of the NEXT edge of this slice are fetched while the gathers of the current
-        // one are in flight: one dependent round trip per edge instead of three (col -> z32 -> Q row)
-        int e = r0 + sl, jn = 0, zn = 0;
-        float4 gn = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (e < r1) { jn = col[e]; gn = geom[e]; zn = z32[jn]; }
-        for (; e < r1; e += S) {
-            const float4 g = gn;
-            const int zj = zn, e2 = e + S;
-            if (e2 < r1) { jn = col[e2]; gn = geom[e2]; }
-            float f[3];
-            filter_val<TAB>(fv, (size_t)e, g.w, H, h, f);
-            const float zv = pz + Qz[(size_t)zj * H + h];
-            if (e2 < r1) zn = z32[jn];
-            const float w1 = zv * f[0], w2 = zv * f[1], w3 = zv * f[2];
-            const float n2 = (g.x * g.x + g.y * g.y + g.z * g.z) * (1.0f / 3.0f);
-            acc[0] += w1;
-            acc[1] += w2 * g.x; acc[2] += w2 * g.y; acc[3] += w2 * g.z;
-            acc[4] += w3 * (g.x * g.x - n2);
-            acc[5] += w3 * (g.y * g.y - n2);
-            acc[6] += w3 * (g.x * g.y);
-            acc[7] += w3 * (g.x * g.z);
-            acc[8] += w3 * (g.y * g.z);
-        }
-    }
+    if (valid) embed_fwd_row<TAB, false>(row_ptr, col, geom, z32, Pz, Qz, fv, i, sl, S, H, h, acc);
     slice_reduce<9>(acc, s_part, H);
     const bool lead = sl == 0;
     if (valid && lead) st9(ias, (size_t)i, H, h, acc);
@@ -245,6 +261,71 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict_
     atom_reduce<1>(v, s_red);
     const float rstd = rsqrtf(v[0] / (float)H + 1e-5f);
     if (valid && lead) nh[(size_t)i * H + h] = (q - mean) * rstd * ln_w[h] + ln_b[h];
+}
+
+// ---- persistent large-system variants of the edge kernels (table mode) ------------------------------------------
+// One CTA per SM; a CTA is W "row workers" of H threads (threadIdx.y = worker), worker w of CTA b takes the rows
+// b*W + w + k*gridDim.x*W, so the rows in flight on the chip at any time are one contiguous window of the
+// (spatially ordered) atom index, exactly as with one-CTA-per-row launches: neighbouring rows gather the same
+// source rows and L2 serves them.  What the persistent form adds: the last `n_hot` rows of the filter table -- the
+// far end of the grid of table_grid.cuh, where 50-75 % of the edges of a condensed system fall -- are copied once
+// per CTA into shared memory, so that most table lookups (48 of the 84 / 120 bytes an edge-channel moves) no
+// longer go through L2, the resource these kernels are bound by.  Sums run in the same order as in the
+// one-row-per-CTA kernels (a worker is 4 warps, like a 128-thread CTA): results are bit-identical.
+__device__ __forceinline__ void hot_rows_load(FilterView& fv, float4* s_hot, int n_hot, int H) {
+    fv.k_hot = fv.grid.n_int - n_hot;
+    fv.hot = s_hot;
+    const float4* src = fv.tab + (size_t)fv.k_hot * 3 * H;
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x, nt = blockDim.x * blockDim.y;
+    for (int q = tid; q < n_hot * 3 * H; q += nt) s_hot[q] = __ldg(&src[q]);
+    __syncthreads();
+}
+// sum over the H threads of one worker (named barrier 1 + worker id); every thread of the worker must call
+template <int NV> __device__ __forceinline__ void worker_reduce(float (&v)[NV], float* s_red_w, int H) {
+    const int lane = threadIdx.x & 31, wr = threadIdx.x >> 5, nw = H >> 5;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) v[k] = warp_sum(v[k]);
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + (int)threadIdx.y), "r"(H) : "memory");
+    if (lane == 0)
+#pragma unroll
+        for (int k = 0; k < NV; ++k) s_red_w[wr * NV + k] = v[k];
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + (int)threadIdx.y), "r"(H) : "memory");
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        float t = 0.f;
+        for (int w = 0; w < nw; ++w) t += s_red_w[w * NV + k];
+        v[k] = t;
+    }
+}
+constexpr int WORKER_RED_FLOATS = 32;   // per-worker scratch of worker_reduce (<= 8 warps x 3 values)
+
+template <int HC>
+__global__ void __launch_bounds__(1024, 1) tn_embed_edge_fwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                                    const float4* __restrict__ geom, const int* __restrict__ z32,
+                                    const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv, int N,
+                                    float* __restrict__ ias, const float* __restrict__ ln_w,
+                                    const float* __restrict__ ln_b, float* __restrict__ nh, int n_hot) {
+    pdl_sync();
+    constexpr int H = HC;
+    extern __shared__ float4 s_hot[];
+    float* s_red_w = (float*)(s_hot + (size_t)n_hot * 3 * H) + WORKER_RED_FLOATS * threadIdx.y;
+    hot_rows_load(fv, s_hot, n_hot, H);
+    const int h = threadIdx.x, W = blockDim.y;
+    for (int i = blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
+        float acc[9];
+#pragma unroll
+        for (int c = 0; c < 9; ++c) acc[c] = 0.f;
+        embed_fwd_row<true, true>(row_ptr, col, geom, z32, Pz, Qz, fv, i, 0, 1, H, h, acc);
+        st9(ias, (size_t)i, H, h, acc);
+        const float q = t3_q(acc);
+        float s[1] = {q};
+        worker_reduce<1>(s, s_red_w, H);
+        const float mean = s[0] / (float)H;
+        float v[1] = {(q - mean) * (q - mean)};
+        worker_reduce<1>(v, s_red_w, H);
+        const float rstd = rsqrtf(v[0] / (float)H + 1e-5f);
+        nh[(size_t)i * H + h] = (q - mean) * rstd * ln_w[h] + ln_b[h];
+    }
 }
 
 // ------------------------------------------------------------------ per-(atom,channel) elementwise stages
@@ -338,17 +419,15 @@ __global__ void tn_prod_bwd(const float* __restrict__ Y, const float* __restrict
 
 // NB = edges whose loads are issued together (independent register sets): the kernel is bound by the latency of the
 // gathers, and the compiler does not overlap the loads of consecutive iterations on its own.
-template <bool TAB> struct FilterRaw { float4 c[3]; float s; };
+template <bool TAB> struct FilterRaw { float4 c[3]; float s, ds; };
 template <> struct FilterRaw<false> { float f[3], df[3]; };
-template <bool TAB>
+template <bool TAB, bool HOT = false>
 __device__ __forceinline__ void filter_load(const FilterView& fv, size_t e, float d, int H, int h, FilterRaw<TAB>& r) {
     if constexpr (TAB) {
-        float s = d * fv.inv_h;
-        int k = (int)s;
-        k = k > fv.n_int - 1 ? fv.n_int - 1 : k;
-        r.s = s - (float)k;
+        int k;
+        tab_locate(fv.grid, d, k, r.s, r.ds);
 #pragma unroll
-        for (int g = 0; g < 3; ++g) r.c[g] = __ldg(&fv.tab[((size_t)k * 3 + g) * H + h]);
+        for (int g = 0; g < 3; ++g) r.c[g] = filter_row<HOT>(fv, k, g, H, h);
     } else {
 #pragma unroll
         for (int g = 0; g < 3; ++g) {
@@ -370,13 +449,13 @@ template <bool TAB> __device__ __forceinline__ void filter_eval_val(const Filter
     }
 }
 template <bool TAB>
-__device__ __forceinline__ void filter_eval(const FilterView& fv, const FilterRaw<TAB>& r, float f[3], float df[3]) {
+__device__ __forceinline__ void filter_eval(const FilterRaw<TAB>& r, float f[3], float df[3]) {
     if constexpr (TAB) {
 #pragma unroll
         for (int g = 0; g < 3; ++g) {
             const float4 c = r.c[g];
             f[g] = c.x + r.s * (c.y + r.s * (c.z + r.s * c.w));
-            df[g] = (c.y + r.s * (2.0f * c.z + 3.0f * r.s * c.w)) * fv.inv_h;
+            df[g] = (c.y + r.s * (2.0f * c.z + 3.0f * r.s * c.w)) * r.ds;
         }
     } else {
 #pragma unroll
@@ -389,6 +468,70 @@ __device__ __forceinline__ void filter_eval(const FilterView& fv, const FilterRa
 constexpr int MSG_FWD_THREADS = 1024;   // 64 registers, one edge per batch: at 98k atoms this runs at 83 % of L2 throughput
 // PF: index and distance of the next batch of edges are fetched while the gathers of the current one are in flight
 // (small systems: the kernel is a chain of dependent round trips, col -> neighbour row)
+// partial sums m[9] of row i over the edges r0+sl, r0+sl+S, ...
+template <bool TAB, int NB, bool PF, bool HOT>
+__device__ __forceinline__ void msg_fwd_row(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                                            const float4* __restrict__ geom, const FilterView& fv,
+                                            const float* __restrict__ Y, int i, int sl, int S, int H, int h, float m[9]) {
+    const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+    int jn[NB];
+    float dn[NB];
+    if (PF && r0 + sl < r1) {
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+            const int e = r0 + sl + b * S, ee = e < r1 ? e : r0 + sl;
+            jn[b] = col[ee];
+            dn[b] = geom[ee].w;
+        }
+    }
+    for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
+        FilterRaw<TAB> fr[NB];
+        float y[NB][9];
+        bool on[NB];
+        int jc[NB];
+        float dc[NB];
+#pragma unroll
+        for (int b = 0; b < NB; ++b) { jc[b] = jn[b]; dc[b] = dn[b]; }
+        if (PF && e0 + NB * S < r1) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                const int e = e0 + NB * S + b * S, ee = e < r1 ? e : e0 + NB * S;
+                jn[b] = col[ee];
+                dn[b] = geom[ee].w;
+            }
+        }
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {           // all loads of the batch first
+            const int e = e0 + b * S;
+            on[b] = e < r1;
+            const int ee = on[b] ? e : e0;
+            const int j = PF ? jc[b] : col[ee];
+            filter_load<TAB, HOT>(fv, (size_t)ee, PF ? dc[b] : geom[ee].w, H, h, fr[b]);
+            ld9(Y, (size_t)j, H, h, y[b]);
+        }
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+            if (!on[b]) continue;
+            float f[3];
+            filter_eval_val<TAB>(fr[b], f);
+            m[0] += f[0] * y[b][0];
+            m[1] += f[1] * y[b][1]; m[2] += f[1] * y[b][2]; m[3] += f[1] * y[b][3];
+            m[4] += f[2] * y[b][4]; m[5] += f[2] * y[b][5]; m[6] += f[2] * y[b][6]; m[7] += f[2] * y[b][7];
+            m[8] += f[2] * y[b][8];
+        }
+    }
+}
+// M -> HBM, tauh = normalise(decompose(M Y + Y M))
+__device__ __forceinline__ void msg_fwd_finish(const float* __restrict__ Y, int i, int H, int h, int so3, const float m[9],
+                                               float* __restrict__ M, float* __restrict__ tauh) {
+    st9(M, (size_t)i, H, h, m);
+    float yi[9], tau[9], th[9];
+    ld9(Y, (size_t)i, H, h, yi);
+    t3_product(m, yi, so3 != 0, tau);
+    t3_normalize(tau, th);
+    st9(tauh, (size_t)i, H, h, th);
+}
+
 template <bool TAB, int NB = 1, int HC = 0, bool PF = false, int MAXT = MSG_FWD_THREADS>
 __global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H_,
@@ -405,63 +548,29 @@ __global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_p
     float m[9];
 #pragma unroll
     for (int c = 0; c < 9; ++c) m[c] = 0.f;
-    if (valid) {
-        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        int jn[NB];
-        float dn[NB];
-        if (PF && r0 + sl < r1) {
-#pragma unroll
-            for (int b = 0; b < NB; ++b) {
-                const int e = r0 + sl + b * S, ee = e < r1 ? e : r0 + sl;
-                jn[b] = col[ee];
-                dn[b] = geom[ee].w;
-            }
-        }
-        for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
-            FilterRaw<TAB> fr[NB];
-            float y[NB][9];
-            bool on[NB];
-            int jc[NB];
-            float dc[NB];
-#pragma unroll
-            for (int b = 0; b < NB; ++b) { jc[b] = jn[b]; dc[b] = dn[b]; }
-            if (PF && e0 + NB * S < r1) {
-#pragma unroll
-                for (int b = 0; b < NB; ++b) {
-                    const int e = e0 + NB * S + b * S, ee = e < r1 ? e : e0 + NB * S;
-                    jn[b] = col[ee];
-                    dn[b] = geom[ee].w;
-                }
-            }
-#pragma unroll
-            for (int b = 0; b < NB; ++b) {           // all loads of the batch first
-                const int e = e0 + b * S;
-                on[b] = e < r1;
-                const int ee = on[b] ? e : e0;
-                const int j = PF ? jc[b] : col[ee];
-                filter_load<TAB>(fv, (size_t)ee, PF ? dc[b] : geom[ee].w, H, h, fr[b]);
-                ld9(Y, (size_t)j, H, h, y[b]);
-            }
-#pragma unroll
-            for (int b = 0; b < NB; ++b) {
-                if (!on[b]) continue;
-                float f[3];
-                filter_eval_val<TAB>(fr[b], f);
-                m[0] += f[0] * y[b][0];
-                m[1] += f[1] * y[b][1]; m[2] += f[1] * y[b][2]; m[3] += f[1] * y[b][3];
-                m[4] += f[2] * y[b][4]; m[5] += f[2] * y[b][5]; m[6] += f[2] * y[b][6]; m[7] += f[2] * y[b][7];
-                m[8] += f[2] * y[b][8];
-            }
-        }
-    }
+    if (valid) msg_fwd_row<TAB, NB, PF, false>(row_ptr, col, geom, fv, Y, i, sl, S, H, h, m);
     slice_reduce<9>(m, s_part, blockDim.x);
     if (!valid || sl != 0) return;
-    st9(M, (size_t)i, H, h, m);
-    float yi[9], tau[9], th[9];
-    ld9(Y, (size_t)i, H, h, yi);
-    t3_product(m, yi, so3 != 0, tau);
-    t3_normalize(tau, th);
-    st9(tauh, (size_t)i, H, h, th);
+    msg_fwd_finish(Y, i, H, h, so3, m, M, tauh);
+}
+
+// persistent large-system variant (see tn_embed_edge_fwd_p): W row workers, hot table rows in shared memory
+template <int HC, int NB>
+__global__ void __launch_bounds__(1024, 1) tn_msg_fwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                             const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N,
+                             int so3, float* __restrict__ M, float* __restrict__ tauh, int n_hot) {
+    pdl_sync();
+    constexpr int H = HC;
+    extern __shared__ float4 s_hot[];
+    hot_rows_load(fv, s_hot, n_hot, H);
+    const int h = threadIdx.x, W = blockDim.y;
+    for (int i = blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
+        float m[9];
+#pragma unroll
+        for (int c = 0; c < 9; ++c) m[c] = 0.f;
+        msg_fwd_row<true, NB, false, true>(row_ptr, col, geom, fv, Y, i, 0, 1, H, h, m);
+        msg_fwd_finish(Y, i, H, h, so3, m, M, tauh);
+    }
 }
 
 // E3: adjoint of the message passing, evaluated in row i of the symmetric edge set:
@@ -470,6 +579,77 @@ __global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_p
 constexpr int MSG_BWD_THREADS = 256;   // 128 registers: two edges' gathers (60 loads) in flight per thread; small systems use 4 slices
 // MAXT = 512 (4 edge slices per row) is the small-system instantiation: same registers, more rows' worth of
 // gathers in flight when there are fewer rows than SMs can hold
+// partial sums of row i over one slice of its edges: acc[9] += f dM_j (acc enters holding dY_i for slice 0), gp[3]
+template <bool TAB, int NB, bool PF, bool HOT>
+__device__ __forceinline__ void msg_bwd_row(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                                            const float4* __restrict__ geom, const FilterView& fv,
+                                            const float* __restrict__ Y, const float* __restrict__ dM,
+                                            const float* dY /* also written by the caller */, int i, int sl,
+                                            int S, int H, int h, float acc[9], float gp[3]) {
+    float yi[9], dmi[9];
+    ld9(Y, (size_t)i, H, h, yi);
+    ld9(dM, (size_t)i, H, h, dmi);
+    if (sl == 0) ld9(dY, (size_t)i, H, h, acc);
+    const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+    int jn[NB];
+    float dn[NB];
+    if (PF && r0 + sl < r1) {
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+            const int e = r0 + sl + b * S, ee = e < r1 ? e : r0 + sl;
+            jn[b] = col[ee];
+            dn[b] = geom[ee].w;
+        }
+    }
+    for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
+        float4 g[NB];
+        FilterRaw<TAB> fr[NB];
+        float yj[NB][9], dmj[NB][9];
+        bool on[NB];
+        int jc[NB];
+        float dc[NB];
+#pragma unroll
+        for (int b = 0; b < NB; ++b) { jc[b] = jn[b]; dc[b] = dn[b]; }
+        if (PF && e0 + NB * S < r1) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                const int e = e0 + NB * S + b * S, ee = e < r1 ? e : e0 + NB * S;
+                jn[b] = col[ee];
+                dn[b] = geom[ee].w;
+            }
+        }
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {           // all loads of the batch first
+            const int e = e0 + b * S;
+            on[b] = e < r1;
+            const int ee = on[b] ? e : e0;
+            const int j = PF ? jc[b] : col[ee];
+            g[b] = geom[ee];
+            filter_load<TAB, HOT>(fv, (size_t)ee, PF ? dc[b] : g[b].w, H, h, fr[b]);
+            ld9(Y, (size_t)j, H, h, yj[b]);
+            ld9(dM, (size_t)j, H, h, dmj[b]);
+        }
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {           // then the sums, in edge order
+            if (!on[b]) continue;
+            float f[3], df[3];
+            filter_eval<TAB>(fr[b], f, df);
+            acc[0] += f[0] * dmj[b][0];
+            acc[1] += f[1] * dmj[b][1]; acc[2] += f[1] * dmj[b][2]; acc[3] += f[1] * dmj[b][3];
+            acc[4] += f[2] * dmj[b][4]; acc[5] += f[2] * dmj[b][5]; acc[6] += f[2] * dmj[b][6];
+            acc[7] += f[2] * dmj[b][7]; acc[8] += f[2] * dmj[b][8];
+            const float s0 = dmi[0] * yj[b][0] + dmj[b][0] * yi[0];
+            float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+            for (int c = 1; c < 4; ++c) s1 += dmi[c] * yj[b][c] + dmj[b][c] * yi[c];
+#pragma unroll
+            for (int c = 4; c < 9; ++c) s2 += dmi[c] * yj[b][c] + dmj[b][c] * yi[c];
+            const float ge = df[0] * s0 + df[1] * s1 + df[2] * s2;
+            gp[0] += g[b].x * ge; gp[1] += g[b].y * ge; gp[2] += g[b].z * ge;
+        }
+    }
+}
+
 template <bool TAB, int NB = 2, int HC = 0, int MAXT = MSG_BWD_THREADS, bool PF = false>
 __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
@@ -487,70 +667,7 @@ __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_p
     float acc[9];
 #pragma unroll
     for (int c = 0; c < 9; ++c) acc[c] = 0.f;
-    if (valid) {
-        float yi[9], dmi[9];
-        ld9(Y, (size_t)i, H, h, yi);
-        ld9(dM, (size_t)i, H, h, dmi);
-        if (sl == 0) ld9(dY, (size_t)i, H, h, acc);
-        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        int jn[NB];
-        float dn[NB];
-        if (PF && r0 + sl < r1) {
-#pragma unroll
-            for (int b = 0; b < NB; ++b) {
-                const int e = r0 + sl + b * S, ee = e < r1 ? e : r0 + sl;
-                jn[b] = col[ee];
-                dn[b] = geom[ee].w;
-            }
-        }
-        for (int e0 = r0 + sl; e0 < r1; e0 += NB * S) {
-            float4 g[NB];
-            FilterRaw<TAB> fr[NB];
-            float yj[NB][9], dmj[NB][9];
-            bool on[NB];
-            int jc[NB];
-            float dc[NB];
-#pragma unroll
-            for (int b = 0; b < NB; ++b) { jc[b] = jn[b]; dc[b] = dn[b]; }
-            if (PF && e0 + NB * S < r1) {
-#pragma unroll
-                for (int b = 0; b < NB; ++b) {
-                    const int e = e0 + NB * S + b * S, ee = e < r1 ? e : e0 + NB * S;
-                    jn[b] = col[ee];
-                    dn[b] = geom[ee].w;
-                }
-            }
-#pragma unroll
-            for (int b = 0; b < NB; ++b) {           // all loads of the batch first
-                const int e = e0 + b * S;
-                on[b] = e < r1;
-                const int ee = on[b] ? e : e0;
-                const int j = PF ? jc[b] : col[ee];
-                g[b] = geom[ee];
-                filter_load<TAB>(fv, (size_t)ee, PF ? dc[b] : g[b].w, H, h, fr[b]);
-                ld9(Y, (size_t)j, H, h, yj[b]);
-                ld9(dM, (size_t)j, H, h, dmj[b]);
-            }
-#pragma unroll
-            for (int b = 0; b < NB; ++b) {           // then the sums, in edge order
-                if (!on[b]) continue;
-                float f[3], df[3];
-                filter_eval<TAB>(fv, fr[b], f, df);
-                acc[0] += f[0] * dmj[b][0];
-                acc[1] += f[1] * dmj[b][1]; acc[2] += f[1] * dmj[b][2]; acc[3] += f[1] * dmj[b][3];
-                acc[4] += f[2] * dmj[b][4]; acc[5] += f[2] * dmj[b][5]; acc[6] += f[2] * dmj[b][6];
-                acc[7] += f[2] * dmj[b][7]; acc[8] += f[2] * dmj[b][8];
-                const float s0 = dmi[0] * yj[b][0] + dmj[b][0] * yi[0];
-                float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-                for (int c = 1; c < 4; ++c) s1 += dmi[c] * yj[b][c] + dmj[b][c] * yi[c];
-#pragma unroll
-                for (int c = 4; c < 9; ++c) s2 += dmi[c] * yj[b][c] + dmj[b][c] * yi[c];
-                const float ge = df[0] * s0 + df[1] * s1 + df[2] * s2;
-                gp[0] += g[b].x * ge; gp[1] += g[b].y * ge; gp[2] += g[b].z * ge;
-            }
-        }
-    }
+    if (valid) msg_bwd_row<TAB, NB, PF, false>(row_ptr, col, geom, fv, Y, dM, dY, i, sl, S, H, h, acc, gp);
     slice_reduce<9>(acc, s_part, H);
     if (valid && sl == 0) st9(dY, (size_t)i, H, h, acc);
     atom_reduce<3>(gp, s_red);
@@ -558,6 +675,32 @@ __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_p
         gpos[3 * (size_t)i] += gp[0];
         gpos[3 * (size_t)i + 1] += gp[1];
         gpos[3 * (size_t)i + 2] += gp[2];
+    }
+}
+
+// persistent large-system variant (see tn_embed_edge_fwd_p): 4 row workers at 128 registers
+template <int HC, int NB>
+__global__ void __launch_bounds__(512, 1) tn_msg_bwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
+                            const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
+                            int n_hot) {
+    pdl_sync();
+    constexpr int H = HC;
+    extern __shared__ float4 s_hot[];
+    float* s_red_w = (float*)(s_hot + (size_t)n_hot * 3 * H) + WORKER_RED_FLOATS * threadIdx.y;
+    hot_rows_load(fv, s_hot, n_hot, H);
+    const int h = threadIdx.x, W = blockDim.y;
+    for (int i = blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
+        float gp[3] = {0.f, 0.f, 0.f};
+        float acc[9];
+        msg_bwd_row<true, NB, false, true>(row_ptr, col, geom, fv, Y, dM, dY, i, 0, 1, H, h, acc, gp);
+        st9(dY, (size_t)i, H, h, acc);
+        worker_reduce<3>(gp, s_red_w, H);
+        if (h == 0) {
+            gpos[3 * (size_t)i] += gp[0];
+            gpos[3 * (size_t)i + 1] += gp[1];
+            gpos[3 * (size_t)i + 2] += gp[2];
+        }
     }
 }
 
@@ -655,8 +798,12 @@ __global__ void tn_head_energy(const float* __restrict__ a4, const float* __rest
         for (int k = lane; k < Hh; k += 32) d4[(size_t)i * Hh + k] = stdv * w2[k] * act_grad(act, h4[(size_t)i * Hh + k]);
 }
 // y[m] = sum_{i: batch[i]==m} e_i + mean  (batch sorted); one CTA per molecule, fixed-order tree => deterministic
+// status[1] (edge capacity exceeded -> truncated, asymmetric edge set) or status[2] (z out of range) poison the
+// result with NaN on the device: the analytic backward assumes a symmetric edge set, so forces of a truncated list
+// would not be -dE/dpos of the returned energy, and nothing on a sync-free path reads the flags.
 __global__ void __launch_bounds__(128) tn_mol_reduce(const float* __restrict__ e_atom, const int64_t* __restrict__ batch,
-                                                     int N, float mean, float* __restrict__ energy) {
+                                                     int N, float mean, float* __restrict__ energy,
+                                                     const int32_t* __restrict__ status) {
     pdl_sync();
     __shared__ float s_part[128];
     const long long m = blockIdx.x;
@@ -674,7 +821,7 @@ __global__ void __launch_bounds__(128) tn_mol_reduce(const float* __restrict__ e
         if (threadIdx.x < o) s_part[threadIdx.x] += s_part[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) energy[m] = s_part[0] + mean;
+    if (threadIdx.x == 0) energy[m] = (status[1] | status[2] | status[3]) ? __int_as_float(0x7fc00000) : s_part[0] + mean;
 }
 // ------------------------------------------------------------------ embedding backward (node part)
 // X0_c = fias_g(c) * iasm_c :  dh2[g*H+h] = (sum_{c in g} dX_c iasm_c) * act'(h2) ;  diasm_c = dX_c * fias_g  (in place)
@@ -748,12 +895,81 @@ __global__ void tn_embed_norm_bwd(const float* __restrict__ ias, const float* __
 
 // E4: adjoint of the embedding edge kernel w.r.t. positions, both directions of every edge inside row i.
 //   forces[i] = -(gpos[i] + sum_e [ u (gd_e + gd_e') + perp(gu_e) - perp(gu_e') ])
+template <bool TAB, bool HOT>
+__device__ __forceinline__ void embed_bwd_row(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                                              const float4* __restrict__ geom, const int* __restrict__ z32,
+                                              const float* __restrict__ Pz, const float* __restrict__ Qz,
+                                              const FilterView& fv, const float* __restrict__ Dias, int i, int sl,
+                                              int S, int H, int h, float gp[3]) {
+    float di[9];
+    ld9(Dias, (size_t)i, H, h, di);
+    const int zi = z32[i];
+    const float pzi = Pz[(size_t)zi * H + h], qzi = Qz[(size_t)zi * H + h];
+    const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+    int e = r0 + sl, jn = 0, zn = 0;     // next edge's index / geometry / element prefetched, as in the forward
+    float4 gn = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (e < r1) { jn = col[e]; gn = geom[e]; zn = z32[jn]; }
+    for (; e < r1; e += S) {
+        const int j = jn, zj = zn, e2 = e + S;
+        const float4 g = gn;
+        if (e2 < r1) { jn = col[e2]; gn = geom[e2]; }
+        if (j == i) {          // self loop: d = 0, u = 0, no position dependence
+            if (e2 < r1) zn = z32[jn];
+            continue;
+        }
+        float f[3], df[3], dj[9];
+        filter_val_grad<TAB, HOT>(fv, (size_t)e, g.w, H, h, f, df);
+        ld9(Dias, (size_t)j, H, h, dj);
+        const float ze = pzi + Qz[(size_t)zj * H + h];        // Z of edge (i <- j)
+        const float zr = Pz[(size_t)zj * H + h] + qzi;        // Z of the reverse edge (j <- i)
+        const float ux = g.x, uy = g.y, uz = g.z;
+        const float n2 = (ux * ux + uy * uy + uz * uz) * (1.0f / 3.0f);
+        const float g4 = ux * ux - n2, g5 = uy * uy - n2, g6 = ux * uy, g7 = ux * uz, g8 = uy * uz;
+        // a_c = Dias_c[i]*Z_e ; r_c = Dias_c[j]*Z_r ; geom of the reverse edge: odd components flip sign
+        float a[9], r[9];
+#pragma unroll
+        for (int c = 0; c < 9; ++c) { a[c] = di[c] * ze; r[c] = dj[c] * zr; }
+        const float gd = df[0] * (a[0] + r[0]) +
+                         df[1] * ((a[1] - r[1]) * ux + (a[2] - r[2]) * uy + (a[3] - r[3]) * uz) +
+                         df[2] * ((a[4] + r[4]) * g4 + (a[5] + r[5]) * g5 + (a[6] + r[6]) * g6 +
+                                  (a[7] + r[7]) * g7 + (a[8] + r[8]) * g8);
+        // dL/du of edge e minus dL/du' of the reverse edge (d geom_c/du is even for c=1..3, odd for c=4..8):
+        //   gu_e - gu_r  with gu_r evaluated at u' = -u  ==  sum_c (a_c*f - r_c*f*sign_c) dgeom_c(u)
+        float w[9];
+#pragma unroll
+        for (int c = 1; c < 4; ++c) w[c] = (a[c] - r[c]) * f[1];
+#pragma unroll
+        for (int c = 4; c < 9; ++c) w[c] = (a[c] + r[c]) * f[2];
+        const float tw = 2.0f / 3.0f;
+        const float gx = w[1] + w[4] * (2.0f * ux - tw * ux) - w[5] * tw * ux + w[6] * uy + w[7] * uz;
+        const float gy = w[2] - w[4] * tw * uy + w[5] * (2.0f * uy - tw * uy) + w[6] * ux + w[8] * uz;
+        const float gz = w[3] - (w[4] + w[5]) * tw * uz + w[7] * ux + w[8] * uy;
+        const float dot = gx * ux + gy * uy + gz * uz;
+        const float inv_d = 1.0f / g.w;
+        gp[0] += ux * gd + (gx - dot * ux) * inv_d;
+        gp[1] += uy * gd + (gy - dot * uy) * inv_d;
+        gp[2] += uz * gd + (gz - dot * uz) * inv_d;
+        if (e2 < r1) zn = z32[jn];   // second level of the prefetch, after this edge's gathers were issued and used
+    }
+
+}
+
+__device__ __forceinline__ void embed_bwd_finish(const float* __restrict__ gpos, float* __restrict__ forces, int i,
+                                                 const float gp[3], const int32_t* __restrict__ status) {
+    const bool bad = (status[1] | status[2] | status[3]) != 0;    // see tn_mol_reduce
+    const float nan = __int_as_float(0x7fc00000);
+    forces[3 * (size_t)i] = bad ? nan : -(gpos[3 * (size_t)i] + gp[0]);
+    forces[3 * (size_t)i + 1] = bad ? nan : -(gpos[3 * (size_t)i + 1] + gp[1]);
+    forces[3 * (size_t)i + 2] = bad ? nan : -(gpos[3 * (size_t)i + 2] + gp[2]);
+}
+
 template <bool TAB, int HC = 0>
 __global__ void __launch_bounds__(1024) tn_embed_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                                   const float4* __restrict__ geom, const int* __restrict__ z32,
                                   const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv,
                                   const float* __restrict__ Dias, const float* __restrict__ gpos,
-                                  float* __restrict__ forces, int N, int H_, const int* __restrict__ order) {
+                                  float* __restrict__ forces, int N, int H_, const int* __restrict__ order,
+                                  const int32_t* __restrict__ status) {
     pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
@@ -762,67 +978,31 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_bwd(const int* __restrict_
     bool valid;
     const int i = edge_row(order, N, valid);
     float gp[3] = {0.f, 0.f, 0.f};
-    if (valid) {
-        float di[9];
-        ld9(Dias, (size_t)i, H, h, di);
-        const int zi = z32[i];
-        const float pzi = Pz[(size_t)zi * H + h], qzi = Qz[(size_t)zi * H + h];
-        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
-        int e = r0 + sl, jn = 0, zn = 0;     // next edge's index / geometry / element prefetched, as in the forward
-        float4 gn = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (e < r1) { jn = col[e]; gn = geom[e]; zn = z32[jn]; }
-        for (; e < r1; e += S) {
-            const int j = jn, zj = zn, e2 = e + S;
-            const float4 g = gn;
-            if (e2 < r1) { jn = col[e2]; gn = geom[e2]; }
-            if (j == i) {          // self loop: d = 0, u = 0, no position dependence
-                if (e2 < r1) zn = z32[jn];
-                continue;
-            }
-            float f[3], df[3], dj[9];
-            filter_val_grad<TAB>(fv, (size_t)e, g.w, H, h, f, df);
-            ld9(Dias, (size_t)j, H, h, dj);
-            const float ze = pzi + Qz[(size_t)zj * H + h];        // Z of edge (i <- j)
-            const float zr = Pz[(size_t)zj * H + h] + qzi;        // Z of the reverse edge (j <- i)
-            const float ux = g.x, uy = g.y, uz = g.z;
-            const float n2 = (ux * ux + uy * uy + uz * uz) * (1.0f / 3.0f);
-            const float g4 = ux * ux - n2, g5 = uy * uy - n2, g6 = ux * uy, g7 = ux * uz, g8 = uy * uz;
-            // a_c = Dias_c[i]*Z_e ; r_c = Dias_c[j]*Z_r ; geom of the reverse edge: odd components flip sign
-            float a[9], r[9];
-#pragma unroll
-            for (int c = 0; c < 9; ++c) { a[c] = di[c] * ze; r[c] = dj[c] * zr; }
-            const float gd = df[0] * (a[0] + r[0]) +
-                             df[1] * ((a[1] - r[1]) * ux + (a[2] - r[2]) * uy + (a[3] - r[3]) * uz) +
-                             df[2] * ((a[4] + r[4]) * g4 + (a[5] + r[5]) * g5 + (a[6] + r[6]) * g6 +
-                                      (a[7] + r[7]) * g7 + (a[8] + r[8]) * g8);
-            // dL/du of edge e minus dL/du' of the reverse edge (d geom_c/du is even for c=1..3, odd for c=4..8):
-            //   gu_e - gu_r  with gu_r evaluated at u' = -u  ==  sum_c (a_c*f - r_c*f*sign_c) dgeom_c(u)
-            float w[9];
-#pragma unroll
-            for (int c = 1; c < 4; ++c) w[c] = (a[c] - r[c]) * f[1];
-#pragma unroll
-            for (int c = 4; c < 9; ++c) w[c] = (a[c] + r[c]) * f[2];
-            const float tw = 2.0f / 3.0f;
-            const float gx = w[1] + w[4] * (2.0f * ux - tw * ux) - w[5] * tw * ux + w[6] * uy + w[7] * uz;
-            const float gy = w[2] - w[4] * tw * uy + w[5] * (2.0f * uy - tw * uy) + w[6] * ux + w[8] * uz;
-            const float gz = w[3] - (w[4] + w[5]) * tw * uz + w[7] * ux + w[8] * uy;
-            const float dot = gx * ux + gy * uy + gz * uz;
-            const float inv_d = 1.0f / g.w;
-            gp[0] += ux * gd + (gx - dot * ux) * inv_d;
-            gp[1] += uy * gd + (gy - dot * uy) * inv_d;
-            gp[2] += uz * gd + (gz - dot * uz) * inv_d;
-            if (e2 < r1) zn = z32[jn];   // second level of the prefetch, after this edge's gathers were issued and used
-        }
-    }
+    if (valid) embed_bwd_row<TAB, false>(row_ptr, col, geom, z32, Pz, Qz, fv, Dias, i, sl, S, H, h, gp);
     atom_reduce<3>(gp, s_red);
-    if (valid && h == 0 && sl == 0) {
-        forces[3 * (size_t)i] = -(gpos[3 * (size_t)i] + gp[0]);
-        forces[3 * (size_t)i + 1] = -(gpos[3 * (size_t)i + 1] + gp[1]);
-        forces[3 * (size_t)i + 2] = -(gpos[3 * (size_t)i + 2] + gp[2]);
-    }
+    if (valid && h == 0 && sl == 0) embed_bwd_finish(gpos, forces, i, gp, status);
 }
 
-#include "tn_chain.cuh"
+// persistent large-system variant (see tn_embed_edge_fwd_p)
+template <int HC>
+__global__ void __launch_bounds__(1024, 1) tn_embed_edge_bwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
+                                    const float4* __restrict__ geom, const int* __restrict__ z32,
+                                    const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv,
+                                    const float* __restrict__ Dias, const float* __restrict__ gpos,
+                                    float* __restrict__ forces, int N, const int32_t* __restrict__ status, int n_hot) {
+    pdl_sync();
+    constexpr int H = HC;
+    extern __shared__ float4 s_hot[];
+    float* s_red_w = (float*)(s_hot + (size_t)n_hot * 3 * H) + WORKER_RED_FLOATS * threadIdx.y;
+    hot_rows_load(fv, s_hot, n_hot, H);
+    const int h = threadIdx.x, W = blockDim.y;
+    for (int i = blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
+        float gp[3] = {0.f, 0.f, 0.f};
+        embed_bwd_row<true, true>(row_ptr, col, geom, z32, Pz, Qz, fv, Dias, i, 0, 1, H, h, gp);
+        worker_reduce<3>(gp, s_red_w, H);
+        if (h == 0) embed_bwd_finish(gpos, forces, i, gp, status);
+    }
+}
 
 // ------------------------------------------------------------------ workspace
 struct TnWs {
@@ -1006,8 +1186,9 @@ FilterView make_view(const tmdn_tensornet_model* m, const tmdn_filter_set& fs, c
     FilterView v;
     v.F = F; v.dF = dF;
     v.tab = (const float4*)fs.table;
-    v.n_int = fs.n_int;
-    v.inv_h = fs.n_int > 0 ? (float)((double)fs.n_int / (double)m->cutoff_upper) : 0.f;
+    v.grid = make_tab_grid(fs.n_int, m->cutoff_upper, fs.grid_alpha, fs.grid_gamma);
+    v.hot = nullptr;
+    v.k_hot = fs.n_int;
     return v;
 }
 
@@ -1040,6 +1221,31 @@ extern "C" int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, in
     tmdn_set_error("lookup: unknown buffer '%s'", name);
     return TMDN_EINVAL;
 }
+
+namespace {
+// launch shape of the persistent edge kernels: one CTA per SM, W workers of H threads, n_hot table rows + worker scratch
+struct PersistLaunch { bool ok; unsigned grid; dim3 block; size_t smem; int n_hot; };
+template <typename Kern>
+PersistLaunch persist_launch(Kern kernel, bool eligible, int N, int H, int workers, const FilterView& fv) {
+    PersistLaunch p;
+    memset(&p, 0, sizeof(p));
+    if (!eligible || !g_tmdn_tuning[TMDN_TUNE_EDGE_PERSIST] || H != 128 || N < 8192 || fv.grid.n_int <= 0) return p;
+    int n_hot = g_tmdn_tuning[TMDN_TUNE_HOT_ROWS];
+    if (n_hot > fv.grid.n_int) n_hot = fv.grid.n_int;
+    if (n_hot > 32) n_hot = 32;    // 192 KB at H = 128
+    if (n_hot < 0) n_hot = 0;
+    p.n_hot = n_hot;
+    p.smem = (size_t)n_hot * 3 * H * sizeof(float4) + sizeof(float) * WORKER_RED_FLOATS * workers;
+    p.block = dim3((unsigned)H, (unsigned)workers, 1);
+    p.grid = (unsigned)tmdn_sm_count();
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem) != cudaSuccess) {
+        cudaGetLastError();
+        return p;
+    }
+    p.ok = true;
+    return p;
+}
+}  // namespace
 
 namespace {
 // One evaluation = the stage sequence below.  Halo points (the only places where a spatially decomposed run needs
@@ -1132,7 +1338,7 @@ struct TnRun {
         const EdgeLaunch elb = edge_launch(N, H, 1024);   // 56 registers
         const EdgeLaunch elf2 = edge_launch(N, H, MSG_FWD_THREADS);
         // two edges in flight per thread; up to 4 slices per row when the rows alone cannot fill the machine
-        const bool bwd4 = tab && (long long)N * H * 2 < 148LL * 2048;
+        const bool bwd4 = tab && (long long)N * H * 2 < (long long)tmdn_sm_count() * 2048;
         const EdgeLaunch elb2 = edge_launch(N, H, bwd4 ? 512 : MSG_BWD_THREADS);
         const unsigned rgrid = (unsigned)cdiv(N, apb);
         const long long NH = (long long)N * H;
@@ -1140,14 +1346,6 @@ struct TnRun {
         // few rows: one CTA per row leaves a second partial wave (166 rows on 148 SMs); rows are visited in order of
         // decreasing degree so that the short ones fill the tail (longest-processing-time-first)
         const int* order = (g_tmdn_tuning[TMDN_TUNE_LPT_ROWS] && N <= LPT_MAX_ROWS) ? w.row_order : nullptr;
-        const bool fused = chain_ok(m, N);
-        auto chain_base = [&]() {
-            ChainArgs c;
-            memset(&c, 0, sizeof(c));
-            c.N = N; c.H = H; c.act = act; c.so3 = m->so3; c.stdv = m->std;
-            c.dbg = g_tmdn_tuning[TMDN_TUNE_FUSED_NODES] - 1;   // fused_nodes = 2, 3: timing experiments (wrong results)
-            return c;
-        };
         TMDN_CHECK_ARG(s >= TMDN_TN_EMBED && s <= TMDN_TN_FINAL, "tensornet: bad stage %d", s);
         TMDN_CHECK_ARG((s != TMDN_TN_LAYER_FWD && s != TMDN_TN_LAYER_BWD) || (l >= 0 && l < L), "tensornet: bad layer %d", l);
 
@@ -1165,7 +1363,7 @@ struct TnRun {
                 KTimer ktimer__("tn_prep_kernel", stream);
                 launch_k(tn_prep_kernel, (unsigned)cdiv(NT, 256), 256, 0, stream, z, w.z32, NT, m->max_z, w.num_found,
                                                                             (long long)P, status, w.row_ptr, N,
-                                                                            order ? w.row_order : nullptr);
+                                                                            order ? w.row_order : nullptr, batch);
                 TMDN_LAUNCH_CHECK();
             }
             if (!tab) {  // exact filters: rbf once, then one MLP chain per filter set
@@ -1184,7 +1382,11 @@ struct TnRun {
             }
             {
                 KTimer ktimer__("tn_embed_edge_fwd", stream);
-                if (tab && H == 128)
+                const PersistLaunch pl = persist_launch(tn_embed_edge_fwd_p<128>, tab, N, H, 8, fv_emb);
+                if (pl.ok)
+                    launch_k(tn_embed_edge_fwd_p<128>, pl.grid, pl.block, pl.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P,
+                             m->Q, fv_emb, N, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, pl.n_hot);
+                else if (tab && H == 128)
                     launch_k(tn_embed_edge_fwd<true, 128>, el.grid, el.block, el.smem, stream, 
                         w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
                 else if (tab)
@@ -1194,19 +1396,6 @@ struct TnRun {
                     launch_k(tn_embed_edge_fwd<false>, el.grid, el.block, el.smem, stream, 
                         w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
                 TMDN_LAUNCH_CHECK();
-            }
-            if (fused) {
-                ChainArgs c = chain_base();
-                c.flag = L > 0;
-                chain_seg1(c, m->emb_w1T, H, 2 * H);
-                chain_seg1(c, m->emb_w2T, 2 * H, 3 * H);
-                chain_seg(c, 3, m->emb_mixT, H, H);
-                if (L > 0) chain_seg(c, 3, m->layer_mixT[0], H, H);
-                c.b1 = m->emb_b1; c.b2 = m->emb_b2;
-                c.in0 = w.nh; c.in1 = w.ias;
-                c.out0 = w.h1; c.out1 = w.a1; c.out2 = w.h2; c.out3 = w.fias; c.out4 = w.iasm; c.out5 = w.X[0];
-                c.out6 = w.Xh; c.out7 = L > 0 ? w.Y[0] : nullptr;
-                return chain_launch<CH_EMBED>(c, stream, "tn_chain_embed");
             }
             GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
             p.C2 = w.h1; p.act = act;
@@ -1230,6 +1419,11 @@ struct TnRun {
         if (s == TMDN_TN_LAYER_FWD) {
             {
                 KTimer ktimer__("tn_msg_fwd", stream);
+                const PersistLaunch pl = persist_launch(tn_msg_fwd_p<128, 1>, tab, N, H, 8, fv_layer[l]);
+                if (pl.ok)
+                    launch_k(tn_msg_fwd_p<128, 1>, pl.grid, pl.block, pl.smem, stream, w.row_ptr, w.col, geom, fv_layer[l],
+                             w.Y[l], N, m->so3, w.M[l], w.tauh, pl.n_hot);
+                else
                 // small systems: 4 slices x 2 edges per thread at 128 registers instead of 8 slices x 1 at 64 -- the same
                 // number of edges in flight per SM, but with 64 registers ptxas reuses the landing registers of the
                 // table rows and an iteration becomes 3-4 dependent round trips instead of one (SASS, r01i)
@@ -1248,15 +1442,6 @@ struct TnRun {
                                                                               H, m->so3, w.M[l], w.tauh, order);
                 TMDN_LAUNCH_CHECK();
             }
-            if (fused) {
-                ChainArgs c = chain_base();
-                c.flag = l + 1 < L;
-                chain_seg(c, 3, m->layer_mixT[l] + 3, H, H);
-                if (l + 1 < L) chain_seg(c, 3, m->layer_mixT[l + 1], H, H);
-                c.in0 = w.tauh; c.in1 = w.Xh;
-                c.out0 = w.dX[l]; c.out1 = w.X[l + 1]; c.out2 = w.Xh; c.out3 = l + 1 < L ? w.Y[l + 1] : nullptr;
-                return chain_launch<CH_LAYER>(c, stream, "tn_chain_layer");
-            }
             TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
             // Xh is both input (residual) and, for the next layer, output: safe because each thread reads its own
             // (atom, channel) column before writing it.
@@ -1270,29 +1455,6 @@ struct TnRun {
         }
         if (s == TMDN_TN_HEAD) {
             TMDN_CHECK_ARG(energy, "tensornet: null energy pointer");
-            if (fused) {
-                ChainArgs c = chain_base();
-                c.flag = forces != nullptr;
-                chain_seg1(c, m->out_wT, 3 * H, H);
-                chain_seg1(c, m->head_w1T, H, H / 2);
-                if (forces) {
-                    chain_seg1(c, m->head_w1, H / 2, H);
-                    chain_seg1(c, m->out_w, H, 3 * H);
-                    chain_seg(c, 3, m->layer_mix[L - 1] + 3, H, H);
-                }
-                c.b1 = m->out_b; c.b2 = m->head_b1;
-                c.ln_w = m->out_ln_w; c.ln_b = m->out_ln_b; c.hw2 = m->head_w2; c.hb2 = m->head_b2;
-                c.a3 = w.a3; c.a4 = w.a4;
-                c.in0 = w.X[L]; c.in1 = w.dX[L - 1]; c.in2 = w.Y[L - 1]; c.in3 = w.M[L - 1];
-                c.out0 = w.h3; c.out1 = w.h4; c.out2 = w.e_atom; c.out3 = w.dXa; c.out4 = w.dB; c.out5 = w.dC;
-                c.out6 = w.stat; c.out7 = w.xl;
-                if (forces) TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
-                TMDN_TRY(chain_launch<CH_HEAD>(c, stream, "tn_chain_head"));
-                KTimer ktimer__("tn_mol_reduce", stream);
-                launch_k(tn_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy);
-                TMDN_LAUNCH_CHECK();
-                return TMDN_OK;
-            }
             {
                 KTimer ktimer__("tn_out_norm_fwd", stream);
                 launch_k(tn_out_norm_fwd, rgrid, rblock, 0, stream, w.X[L], m->out_ln_w, m->out_ln_b, w.xl, w.stat, N, H);
@@ -1314,7 +1476,7 @@ struct TnRun {
             }
             {
                 KTimer ktimer__("tn_mol_reduce", stream);
-                launch_k(tn_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy);
+                launch_k(tn_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy, status);
                 TMDN_LAUNCH_CHECK();
             }
             if (!forces) return TMDN_OK;
@@ -1335,7 +1497,11 @@ struct TnRun {
         if (s == TMDN_TN_LAYER_BWD) {
             {
                 KTimer ktimer__("tn_msg_bwd", stream);
-                if (bwd4)
+                const PersistLaunch pl = persist_launch(tn_msg_bwd_p<128, 2>, tab, N, H, 4, fv_layer[l]);
+                if (pl.ok)
+                    launch_k(tn_msg_bwd_p<128, 2>, pl.grid, pl.block, pl.smem, stream, w.row_ptr, w.col, geom, fv_layer[l],
+                             w.Y[l], w.dB, w.dC, w.gpos, N, pl.n_hot);
+                else if (bwd4)
                     launch_k(tn_msg_bwd<true, 2, 0, 512, true>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom,
                              fv_layer[l], w.Y[l], w.dB, w.dC, w.gpos, N, H, order);
                 else if (tab)
@@ -1345,24 +1511,6 @@ struct TnRun {
                     launch_k(tn_msg_bwd<false>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
                                                                                  w.dB, w.dC, w.gpos, N, H, order);
                 TMDN_LAUNCH_CHECK();
-            }
-            if (fused) {
-                ChainArgs c = chain_base();
-                c.in0 = w.dC; c.in1 = w.dXa; c.in2 = w.X[l];
-                chain_seg(c, 3, m->layer_mix[l], H, H);
-                if (l > 0) {
-                    chain_seg(c, 3, m->layer_mix[l - 1] + 3, H, H);
-                    c.in3 = w.dX[l - 1]; c.in4 = w.Y[l - 1]; c.in5 = w.M[l - 1];
-                    c.out0 = w.dXa; c.out1 = w.dB; c.out2 = w.dC;
-                    return chain_launch<CH_BWD>(c, stream, "tn_chain_bwd");
-                }
-                chain_seg1(c, m->emb_w2, 3 * H, 2 * H);
-                chain_seg1(c, m->emb_w1, 2 * H, H);
-                chain_seg(c, 3, m->emb_mix, H, H);
-                c.b1 = w.h2; c.b2 = w.h1; c.ln_w = m->emb_ln_w;
-                c.in3 = w.iasm; c.in4 = w.fias; c.in5 = w.ias;
-                c.out0 = w.dXa; c.out1 = w.dB; c.out2 = w.dh2; c.out3 = w.dh1; c.out4 = w.dnh;
-                return chain_launch<CH_BWD_EMB>(c, stream, "tn_chain_bwd_emb");
             }
             GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
             for (int g = 0; g < 3; ++g) b.p[g].accumulate = 1;
@@ -1379,15 +1527,19 @@ struct TnRun {
         TMDN_CHECK_ARG(forces, "tensornet: null forces pointer");
         {
             KTimer ktimer__("tn_embed_edge_bwd", stream);
-            if (tab && H == 128)
+            const PersistLaunch pl = persist_launch(tn_embed_edge_bwd_p<128>, tab, N, H, 8, fv_emb);
+            if (pl.ok)
+                launch_k(tn_embed_edge_bwd_p<128>, pl.grid, pl.block, pl.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P,
+                         m->Q, fv_emb, w.dB, w.gpos, forces, N, status, pl.n_hot);
+            else if (tab && H == 128)
                 launch_k(tn_embed_edge_bwd<true, 128>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
-                                                                                   fv_emb, w.dB, w.gpos, forces, N, H, order);
+                                                                                   fv_emb, w.dB, w.gpos, forces, N, H, order, status);
             else if (tab)
                 launch_k(tn_embed_edge_bwd<true>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
-                                                                                   fv_emb, w.dB, w.gpos, forces, N, H, order);
+                                                                                   fv_emb, w.dB, w.gpos, forces, N, H, order, status);
             else
                 launch_k(tn_embed_edge_bwd<false>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
-                                                                                    fv_emb, w.dB, w.gpos, forces, N, H, order);
+                                                                                    fv_emb, w.dB, w.gpos, forces, N, H, order, status);
             TMDN_LAUNCH_CHECK();
         }
         return TMDN_OK;

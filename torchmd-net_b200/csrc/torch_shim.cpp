@@ -256,9 +256,10 @@ const float* fptr(const Tensor& t) {
 //   rbf_p0 rbf_p1 P Q | emb_filter: w b table | emb_mix x3 emb_mixT x3 | emb_ln_w emb_ln_b
 //   emb_w1 emb_b1 emb_w1T emb_w2 emb_b2 emb_w2T | out_ln_w out_ln_b out_w out_b out_wT
 //   head_w1 head_b1 head_w1T head_w2 head_b2 | per layer: w0 b0 w1 b1 w2 b2 table mix x6 mixT x6
-// iparams: hidden num_rbf num_layers max_z rbf_type activation so3 filter_mode n_int gemm_mode ; fparams: lo hi mean std
+// iparams: hidden num_rbf num_layers max_z rbf_type activation so3 filter_mode n_int gemm_mode ;
+// fparams: lo hi mean std grid_alpha grid_gamma
 int64_t tensornet_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::vector<double> fp) {
-    TORCH_CHECK(ip.size() == 10 && fp.size() == 4, "tensornet_create: bad parameter vectors");
+    TORCH_CHECK(ip.size() == 10 && fp.size() == 6, "tensornet_create: bad parameter vectors");
     auto h = std::make_shared<TnHandle>();
     tmdn_tensornet_model& m = h->m;
     memset(&m, 0, sizeof(m));
@@ -277,6 +278,7 @@ int64_t tensornet_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::ve
     m.emb_filter.n_layers = 1; m.emb_filter.final_act = 0;
     m.emb_filter.dims[0] = K; m.emb_filter.dims[1] = 3 * H;
     m.emb_filter.w[0] = next(); m.emb_filter.b[0] = next(); m.emb_filter.table = next(); m.emb_filter.n_int = n_int;
+    m.emb_filter.grid_alpha = (float)fp[4]; m.emb_filter.grid_gamma = (float)fp[5];
     for (int g = 0; g < 3; ++g) m.emb_mix[g] = next();
     for (int g = 0; g < 3; ++g) m.emb_mixT[g] = next();
     m.emb_ln_w = next(); m.emb_ln_b = next();
@@ -289,7 +291,7 @@ int64_t tensornet_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::ve
         f.n_layers = 3; f.final_act = 1;
         f.dims[0] = K; f.dims[1] = H; f.dims[2] = 2 * H; f.dims[3] = 3 * H;
         for (int j = 0; j < 3; ++j) { f.w[j] = next(); f.b[j] = next(); }
-        f.table = next(); f.n_int = n_int;
+        f.table = next(); f.n_int = n_int; f.grid_alpha = (float)fp[4]; f.grid_gamma = (float)fp[5];
         for (int j = 0; j < 6; ++j) m.layer_mix[l][j] = next();
         for (int j = 0; j < 6; ++j) m.layer_mixT[l][j] = next();
     }
@@ -329,6 +331,8 @@ std::tuple<Tensor, Tensor, Tensor, Tensor> tensornet_energy_forces(int64_t handl
                     batch.size(0) == pos.size(0),
                 "tensornet_energy_forces: batch must be a contiguous int64 [N] tensor");
     TORCH_CHECK(z.device() == pos.device() && batch.device() == pos.device(), "tensornet_energy_forces: device mismatch");
+    TORCH_CHECK(h->keep.empty() || h->keep[0].device() == pos.device(),
+                "tensornet_energy_forces: the model was packed on ", h->keep[0].device(), " but pos is on ", pos.device());
     const c10::cuda::CUDAGuard guard(pos.device());
     const int64_t n = pos.size(0);
     const int sid = strategy_id(strategy);
@@ -339,7 +343,7 @@ std::tuple<Tensor, Tensor, Tensor, Tensor> tensornet_energy_forces(int64_t handl
     TORCH_CHECK(need > 0, "tensornet_energy_forces: ", tmdn_last_error());
     Tensor ws;
     if (workspace.has_value() && workspace->defined() && (size_t)workspace->numel() >= need && workspace->is_cuda() &&
-        workspace->scalar_type() == at::kByte)
+        workspace->device() == pos.device() && workspace->scalar_type() == at::kByte)
         ws = *workspace;
     else
         ws = at::empty({(int64_t)need}, pos.options().dtype(at::kByte));
@@ -378,9 +382,10 @@ std::unordered_map<int64_t, std::shared_ptr<EtHandle>> g_et;
 //   emb ne_emb ne_table ne_comb_w ne_comb_b ne_comb_w2T out_ln_w out_ln_b
 //   head block x2: w1 w1T w2 w2T u0_w u0_b u0_wT u2_w u2_b u2_wT
 //   per layer: ln_w ln_b qkv_w qkv_b qkv_wT vp_w vp_wT o_w o_b o_wT table
-// iparams: hidden num_layers num_heads max_z activation attn_activation has_ne n_int gemm_mode ; fparams: lo hi mean std
+// iparams: hidden num_layers num_heads max_z activation attn_activation has_ne n_int gemm_mode ;
+// fparams: lo hi mean std grid_alpha grid_gamma
 int64_t et_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::vector<double> fp) {
-    TORCH_CHECK(ip.size() == 9 && fp.size() == 4, "et_create: bad parameter vectors");
+    TORCH_CHECK(ip.size() == 9 && fp.size() == 6, "et_create: bad parameter vectors");
     auto h = std::make_shared<EtHandle>();
     tmdn_et_model& m = h->m;
     memset(&m, 0, sizeof(m));
@@ -389,6 +394,7 @@ int64_t et_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::vector<do
     m.n_int = (int32_t)ip[7];
     m.gemm_mode = (int32_t)ip[8];
     m.cutoff_lower = (float)fp[0]; m.cutoff_upper = (float)fp[1]; m.mean = (float)fp[2]; m.std = (float)fp[3];
+    m.grid_alpha = (float)fp[4]; m.grid_gamma = (float)fp[5];
     TORCH_CHECK(m.num_layers >= 0 && m.num_layers <= TMDN_MAX_LAYERS, "et_create: too many layers");
     const size_t expect = 28 + 11 * (size_t)m.num_layers;
     TORCH_CHECK(w.size() == expect, "et_create: expected ", expect, " weight tensors, got ", w.size());
@@ -440,6 +446,8 @@ std::tuple<Tensor, Tensor, Tensor, Tensor> et_energy_forces(int64_t handle, cons
                     batch.size(0) == pos.size(0),
                 "et_energy_forces: batch must be a contiguous int64 [N] tensor");
     TORCH_CHECK(z.device() == pos.device() && batch.device() == pos.device(), "et_energy_forces: device mismatch");
+    TORCH_CHECK(h->keep.empty() || h->keep[0].device() == pos.device(),
+                "et_energy_forces: the model was packed on ", h->keep[0].device(), " but pos is on ", pos.device());
     const c10::cuda::CUDAGuard guard(pos.device());
     const int64_t n = pos.size(0);
     const int sid = strategy_id(strategy);
@@ -450,7 +458,7 @@ std::tuple<Tensor, Tensor, Tensor, Tensor> et_energy_forces(int64_t handle, cons
     TORCH_CHECK(need > 0, "et_energy_forces: ", tmdn_last_error());
     Tensor ws;
     if (workspace.has_value() && workspace->defined() && (size_t)workspace->numel() >= need && workspace->is_cuda() &&
-        workspace->scalar_type() == at::kByte)
+        workspace->device() == pos.device() && workspace->scalar_type() == at::kByte)
         ws = *workspace;
     else
         ws = at::empty({(int64_t)need}, pos.options().dtype(at::kByte));

@@ -13,10 +13,14 @@ class FusedRepresentation(nn.Module):
     _kernel_name = ""
 
     def _init_fused(self):
-        self.table_intervals = 4096
+        self.table_intervals = None     # None: 16 * num_rbf intervals (TableGrid in tensornet.py)
+        self.table_warp = True
         self._handle = None
         self._pack_key = None
         self._workspace = None
+
+    def resolved_table_intervals(self) -> int:
+        return int(self.table_intervals) if self.table_intervals else 16 * int(self.num_rbf)
 
     # subclasses: pack_weights(head, mean, std) -> (weights, iparams, fparams); _extra_key() -> hashable
     def _extra_key(self):
@@ -43,10 +47,18 @@ class FusedRepresentation(nn.Module):
                 raise NotImplementedError("%s kernels are fp32 (precision: 32); got %s" % (self._kernel_name, p.dtype))
             if self._handle is not None:
                 self._ops("destroy")(self._handle)
+            self._workspace = None          # may live on the previous device
             w, ip, fp = self.pack_weights(head, mean, std)
             self._handle = self._ops("create")(w, ip, fp)
             self._pack_key = key
         return self._handle
+
+    def __getstate__(self):
+        """copy.deepcopy / pickle: the native handle, its key and the workspace belong to THIS instance (a copy that
+        kept the integer handle would destroy the original's packed model on its first call)."""
+        state = dict(self.__dict__)
+        state["_handle"] = state["_pack_key"] = state["_workspace"] = None
+        return state
 
     def invalidate_cache(self):
         """Force re-packing (needed only after in-place edits through ``.data`` that bypass version counters)."""
@@ -68,8 +80,12 @@ class FusedRepresentation(nn.Module):
         """One fused evaluation: -> (y[n_mol,1], forces[N,3] (empty if not compute_forces), status int32[4]).
         status[0] = edges found (incl. self loops), status[1] = 1 if they exceeded the capacity
         max_num_neighbors*N (models/utils.py:234-236), status[2] = 1 if some z was outside [0,max_z).
+        When status[1] or status[2] is set the kernels write NaN into y and forces (a truncated edge list is not
+        symmetric, so the analytic forces would not belong to the returned energy).
         Neighbour search parameters (cutoffs, box, strategy, capacity, check_errors) are read from
-        ``self.distance`` on every call, so a periodic ``OptimizedDistance`` can be swapped in by attribute."""
+        ``self.distance`` on every call, so a periodic ``OptimizedDistance`` can be swapped in by attribute.
+        ``batch`` must be sorted ascending (molecules contiguous), as the reference's own collate produces it.
+        One instance owns one workspace: do not evaluate the same instance concurrently on two streams."""
         handle = self.native_handle(head, mean, std)
         _native.require_cuda(pos, self._kernel_name)
         if pos.dtype != torch.float32:

@@ -10,7 +10,8 @@ neighbour search, embedding, interactions, head and the analytic backward in one
 Two deliberate differences from the reference's *CUDA* behaviour (both documented in DESIGN.md):
   * the unpadded edge semantics of the reference CPU path are implemented -- the static-shape padding
     artefact of tensornet.py:215-221 (spurious self-loop messages on atom 0) is not reproduced;
-  * matmuls are exact fp32 (the reference flips TF32 on process-wide at import, tensornet.py:13-14).
+  * matmuls keep fp32-level accuracy (default: three-product tf32 on the tensor cores with fp32 chunk sums,
+    ``gemm_mode = "fp32"`` = FFMA); the reference flips plain TF32 on process-wide at import (tensornet.py:13-14).
 """
 from typing import Optional, Tuple
 
@@ -134,6 +135,54 @@ def filter_table(d, rbf_type, p0, p1, lo, hi, layers, act, final_act, cutoff=Tru
     return h * c[:, None], t * c[:, None] + h * dc[:, None]
 
 
+class TableGrid:
+    """Interval grid of the filter tables (csrc/table_grid.cuh): ``n_int`` intervals over [0, hi], uniform in
+    S(d) = 1 - exp(-alpha d) + gamma d.  ExpNormal filters have features of constant width in exp(-alpha d)
+    (models/utils.py:339-344) times factors that vary on the scale of the cutoff, so this grid needs ~8x fewer
+    intervals than one uniform in d and packs the far end, where most neighbours are, into few rows.
+    alpha = 0 (Gaussian smearing, cutoff_lower > 0, or ``warp=False``) is the plain grid uniform in d."""
+
+    def __init__(self, n_int, lo, hi, rbf_type, warp=True):
+        self.n_int, self.hi = int(n_int), float(hi)
+        if warp and rbf_type == "expnorm" and float(lo) == 0.0:
+            self.alpha, self.gamma = 5.0 / self.hi, 0.05 / self.hi
+        else:
+            self.alpha = self.gamma = 0.0
+
+    def S(self, d):
+        return 1.0 - torch.exp(-self.alpha * d) + self.gamma * d if self.alpha > 0 else d
+
+    def dS(self, d):
+        return self.alpha * torch.exp(-self.alpha * d) + self.gamma if self.alpha > 0 else torch.ones_like(d)
+
+    @property
+    def step(self):
+        import math
+        T = 1.0 - math.exp(-self.alpha * self.hi) + self.gamma * self.hi if self.alpha > 0 else self.hi
+        return T / self.n_int
+
+    def nodes(self, device=None):
+        """d_k with S(d_k) = k * step, k = 0..n_int (fp64; Newton on the monotone S)."""
+        sk = torch.arange(self.n_int + 1, device=device, dtype=torch.float64) * self.step
+        if self.alpha == 0:
+            return sk
+        d = sk / (self.step * self.n_int) * self.hi
+        for _ in range(80):
+            d = (d - (self.S(d) - sk) / self.dS(d)).clamp(0.0, self.hi)
+        d[0], d[-1] = 0.0, self.hi
+        return d
+
+    def coefficients(self, d, f, df):
+        """Cubic Hermite coefficients in the local coordinate of each interval from f, df/dd at the nodes ``d``."""
+        return hermite_coefficients(f, df / self.dS(d)[:, None], self.step)
+
+    def locate(self, d):
+        """-> (interval k, local coordinate s, ds/dd) exactly as the kernels compute them (tab_locate)."""
+        sv = self.S(d) / self.step
+        k = sv.floor().clamp(min=0, max=self.n_int - 1).long()
+        return k, sv - k, self.dS(d) / self.step
+
+
 def hermite_coefficients(f, df, h):
     """Cubic Hermite coefficients per interval: value(s) = c0 + s(c1 + s(c2 + s c3)), s in [0,1).
     f, df: [n_int+1, C] -> [n_int, C, 4]."""
@@ -144,7 +193,8 @@ def hermite_coefficients(f, df, h):
 class TensorNet(FusedRepresentation):
     """Drop-in for ``torchmdnet.models.tensornet.TensorNet`` (tensornet.py:70-234): same constructor, same
     parameters.  ``filter_mode``: "exact" evaluates the per-edge filter MLPs with fp32 GEMMs, "table"
-    evaluates them from a cubic Hermite table in d built in fp64 from the weights (``table_intervals``)."""
+    evaluates them from a cubic Hermite table built in fp64 from the weights on the grid of ``TableGrid``
+    (``table_intervals`` intervals, default 16 * num_rbf; ``table_warp=False`` = uniform in d)."""
     _op = "tensornet"
     _kernel_name = "TensorNet"
 
@@ -206,7 +256,7 @@ class TensorNet(FusedRepresentation):
         tr = lambda t: f32(t.detach().t())                                             # noqa: E731
         te = self.tensor_embedding
         table = self.filter_mode == "table"
-        n_int = int(self.table_intervals) if table else 0
+        n_int = self.resolved_table_intervals() if table else 0
         empty = torch.empty(0, device=dev, dtype=torch.float32)
         lo, hi = float(self.cutoff_lower), float(self.cutoff_upper)
 
@@ -215,14 +265,15 @@ class TensorNet(FusedRepresentation):
         else:
             p0 = self.distance_expansion.offset
             p1 = self.distance_expansion.coeff.expand(K)
-        grid = torch.linspace(0.0, hi, n_int + 1, device=dev, dtype=torch.float64) if table else None
+        grid = TableGrid(max(n_int, 1), lo, hi, self.rbf_type, self.table_warp)
+        nodes = grid.nodes(dev) if table else None
 
         def make_table(layers, final_act):
             if not table:
                 return empty
-            f, df = filter_table(grid, self.rbf_type, f64(p0), f64(p1), lo, hi,
+            f, df = filter_table(nodes, self.rbf_type, f64(p0), f64(p1), lo, hi,
                                  [(f64(w), f64(b)) for w, b in layers], self.activation, final_act)
-            return f32(hermite_coefficients(f, df, hi / n_int).view(n_int, 3, H, 4))
+            return f32(grid.coefficients(nodes, f, df).view(n_int, 3, H, 4))
 
         # Z_ij = emb2([emb(z_i) | emb(z_j)]) = P[z_i] + Q[z_j]      (tensornet.py:310-312)
         emb, w2, b2 = f64(te.emb.weight), f64(te.emb2.weight), f64(te.emb2.bias)
@@ -256,11 +307,11 @@ class TensorNet(FusedRepresentation):
         iparams = [H, K, self.num_layers, self.max_z, RBF_ID[self.rbf_type], ACT_ID[self.activation],
                    int(self.equivariance_invariance_group == "SO(3)"), FILTER_TABLE if table else FILTER_EXACT,
                    n_int, {"fp32": 0, "tf32x3": 1}[self.gemm_mode]]
-        fparams = [lo, hi, float(mean), float(std)]
+        fparams = [lo, hi, float(mean), float(std), grid.alpha, grid.gamma]
         return w, iparams, fparams
 
     def _extra_key(self):
-        return (self.filter_mode, self.gemm_mode)
+        return (self.filter_mode, self.gemm_mode, self.table_warp)
 
     def forward(self, z: Tensor, pos: Tensor, batch: Tensor, q: Optional[Tensor] = None,
                 s: Optional[Tensor] = None):

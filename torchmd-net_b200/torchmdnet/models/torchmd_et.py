@@ -7,7 +7,7 @@ import torch
 from torch import Tensor, nn
 
 from ._fused import FusedRepresentation
-from .tensornet import filter_table, hermite_coefficients
+from .tensornet import TableGrid, filter_table, hermite_coefficients
 from .utils import (ACT_ID, CosineCutoff, NeighborEmbedding, OptimizedDistance, _fused_only, _xavier_zero_bias,
                     act_class_mapping, rbf_class_mapping)
 
@@ -60,7 +60,8 @@ class TorchMD_ET(FusedRepresentation):
     """Drop-in for ``torchmdnet.models.torchmd_et.TorchMD_ET`` (torchmd_et.py:55-152): same constructor, same
     parameters; evaluated by the fused kernels of csrc/et.cu.  The distance filters (dk_proj, dv_proj, the
     neighbour-embedding distance_proj) are univariate in d and are evaluated from cubic Hermite tables built in fp64
-    from the weights (``table_intervals`` intervals over [0, cutoff_upper])."""
+    from the weights on the grid of ``tensornet.TableGrid`` (``table_intervals`` intervals over [0, cutoff_upper],
+    default 16 * num_rbf)."""
     _op = "et"
     _kernel_name = "TorchMD_ET"
 
@@ -116,7 +117,7 @@ class TorchMD_ET(FusedRepresentation):
 
     # -------------------------------------------------------------------------------------------- packing
     def _extra_key(self):
-        return (self.gemm_mode,)
+        return (self.gemm_mode, self.table_warp)
 
     def pack_weights(self, head: Optional[nn.Module], mean: float, std: float):
         """-> (weights in the order csrc/torch_shim.cpp::et_create expects, iparams, fparams)."""
@@ -129,13 +130,13 @@ class TorchMD_ET(FusedRepresentation):
         f64 = lambda t: t.detach().to(device=dev, dtype=torch.float64)                 # noqa: E731
         tr = lambda t: f32(t.detach().t())                                             # noqa: E731
         lo, hi = float(self.cutoff_lower), float(self.cutoff_upper)
-        n_int = int(self.table_intervals)
+        n_int = self.resolved_table_intervals()
         if self.rbf_type == "expnorm":
             p0, p1 = f64(self.distance_expansion.means), f64(self.distance_expansion.betas)
         else:
             p0, p1 = f64(self.distance_expansion.offset), f64(self.distance_expansion.coeff).expand(K)
-        grid = torch.linspace(0.0, hi, n_int + 1, device=dev, dtype=torch.float64)
-        step = hi / n_int
+        tgrid = TableGrid(n_int, lo, hi, self.rbf_type, self.table_warp)
+        grid = tgrid.nodes(dev)
 
         def table(lin, act, n_out, cutoff):
             """[n_int, n_out, 4] Hermite coefficients of [act o] lin(rbf(d)) [* C(d)]; the constant 1 if lin is None"""
@@ -143,13 +144,13 @@ class TorchMD_ET(FusedRepresentation):
                 if cutoff:   # the bare cutoff C(d)
                     from .tensornet import _cutoff_and_grad
                     cc, dcc = _cutoff_and_grad(grid, lo, hi)
-                    return hermite_coefficients(cc[:, None].expand(-1, n_out), dcc[:, None].expand(-1, n_out), step)
+                    return tgrid.coefficients(grid, cc[:, None].expand(-1, n_out), dcc[:, None].expand(-1, n_out))
                 c = torch.zeros(n_int, n_out, 4, device=dev, dtype=torch.float64)
                 c[..., 0] = 1.0
                 return c
             f, df = filter_table(grid, self.rbf_type, p0, p1, lo, hi, [(f64(lin[0]), f64(lin[1]))],
                                  act, act is not None, cutoff=cutoff)
-            return hermite_coefficients(f, df, step)
+            return tgrid.coefficients(grid, f, df)
 
         # part-major row order of v / dv: row p*H + head*hd + c <- reference row head*3hd + p*hd + c
         perm = torch.arange(3 * H, device=dev).view(nh, 3, hd).permute(1, 0, 2).reshape(-1)
@@ -184,7 +185,7 @@ class TorchMD_ET(FusedRepresentation):
                   tr(ly.o_proj.weight), f32(tab.view(n_int, 4, H, 4))]
         iparams = [H, self.num_layers, nh, self.max_z, ACT_ID[self.activation], ACT_ID[self.attn_activation],
                    int(ne is not None), n_int, {"fp32": 0, "tf32x3": 1}[self.gemm_mode]]
-        return w, iparams, [lo, hi, float(mean), float(std)]
+        return w, iparams, [lo, hi, float(mean), float(std), tgrid.alpha, tgrid.gamma]
 
     def forward(self, z: Tensor, pos: Tensor, batch: Tensor, q: Optional[Tensor] = None,
                 s: Optional[Tensor] = None):
