@@ -75,10 +75,10 @@ int tmdn_profile_report(char* buf, size_t buf_bytes);
  *   "lpt_rows"   1 = edge kernels of small systems visit rows in order of decreasing degree (default 1)
  *   "pdl"        1 = dependent kernels are launched with programmatic stream serialisation (default 0: measured
  *                    slower inside CUDA graphs, profiles/r01i_bench_*_pdl_{on,off}.json)
- *   "edge_persist" 1 = on large systems (>= 8192 rows, H = 128, table filters) the TensorNet edge kernels run as one
- *                    persistent CTA per SM that keeps the last "hot_rows" rows of the filter table -- the far end of
- *                    the grid, where most neighbours of a condensed system are -- in shared memory (default 1)
- *   "hot_rows"     number of table rows those kernels keep in shared memory (default 24 = 144 KB at H = 128)
+ *   "edge_persist" 1 = on large systems (>= 8192 rows, H = 128, table filters) the TensorNet message-passing kernels
+ *                    run as one persistent CTA per SM (default 1; 10-17 % faster than one CTA per row at 98 k atoms)
+ *   "hot_rows"     number of filter-table rows (from the cutoff end of the grid) those kernels keep in shared memory
+ *                    (default 0: measured no gain, shared memory and L1 share the data pipe that bounds them)
  * Returns the previous value (>= 0); value < 0 only queries; -1 for an unknown key (tmdn_last_error says which).
  * Process-wide. */
 int tmdn_set_tuning(const char* key, int value);
@@ -158,8 +158,9 @@ typedef struct tmdn_filter_set {
     const float* w[3];
     const float* b[3];
     /* TABLE mode: [n_int][3][H] float4 cubic coefficients of f(d)*C(d) on n_int intervals over [0, cutoff_upper],
-     * uniform in S(d) = 1 - exp(-grid_alpha d) + grid_gamma d (grid_alpha = 0: uniform in d); local coordinate
-     * s = S(d) n_int / S(cutoff_upper) - k, value = c.x + s (c.y + s (c.z + s c.w)).  See csrc/table_grid.cuh. */
+     * uniform in t(d) = (exp(-grid_alpha d) - exp(-grid_alpha r_c)) + grid_gamma (r_c - d), counted from the cutoff
+     * (row 0 ends at d = r_c; grid_alpha = 0: uniform in d, t = r_c - d); local coordinate s = t(d) n_int / t(0) - k,
+     * value = c.x + s (c.y + s (c.z + s c.w)).  See csrc/table_grid.cuh. */
     const float* table;
     int32_t n_int;
     float grid_alpha, grid_gamma;

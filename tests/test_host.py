@@ -143,9 +143,9 @@ def test_rbf_modules_match_oracle():
 @pytest.mark.parametrize("name,warp", [("small_tensornet_o3.npz", True), ("small_tensornet_o3.npz", False),
                                        ("small_tensornet_gauss.npz", True)])
 def test_filter_table_interpolates_filter(name, warp):
-    """The Hermite tables the host builds for filter_mode='table' (TableGrid: 16*num_rbf intervals uniform in
-    S(d) = 1 - exp(-alpha d) + gamma d; uniform in d for Gaussian smearing / warp=False with 4096 intervals)
-    reproduce the filter MLP and its derivative, evaluated the way the kernels do (tab_locate)."""
+    """The Hermite tables the host builds for filter_mode='table' (TableGrid: max(1024, 32*num_rbf) intervals uniform
+    in t(d) = exp(-alpha d) - exp(-alpha r_c) + gamma (r_c - d); uniform in d for Gaussian smearing / warp=False with
+    4096 intervals) reproduce the filter MLP and its derivative, evaluated the way the kernels do (tab_locate)."""
     from torchmdnet.models.model import create_model
     from torchmdnet.models.tensornet import TableGrid, filter_table
     g = load_npz(name)
@@ -159,12 +159,14 @@ def test_filter_table_interpolates_filter(name, warp):
         p0, p1 = rm.distance_expansion.means, rm.distance_expansion.betas
     else:
         p0, p1 = rm.distance_expansion.offset, rm.distance_expansion.coeff.expand(rm.num_rbf)
-    n_int = rm.resolved_table_intervals() if warp and rm.rbf_type == "expnorm" else 4096
+    rm.table_warp = warp and rm.rbf_type == "expnorm"
+    n_int = rm.resolved_table_intervals()
+    assert n_int == (1024 if rm.table_warp else 4096)
     grid = TableGrid(n_int, lo, hi, rm.rbf_type, warp)
     assert (grid.alpha > 0) == (warp and rm.rbf_type == "expnorm")
     nodes = grid.nodes()
-    assert float(nodes[0]) == 0.0 and float(nodes[-1]) == hi and bool((nodes[1:] > nodes[:-1]).all())
-    torch.testing.assert_close(grid.S(nodes) / grid.step, torch.arange(n_int + 1, dtype=torch.float64), rtol=0, atol=1e-9)
+    assert float(nodes[0]) == hi and float(nodes[-1]) == 0.0 and bool((nodes[1:] < nodes[:-1]).all())
+    torch.testing.assert_close(grid.t(nodes) / grid.step, torch.arange(n_int + 1, dtype=torch.float64), rtol=0, atol=1e-9)
     f, df = filter_table(nodes, rm.rbf_type, p0, p1, lo, hi, layers, "silu", True)
     c = grid.coefficients(nodes, f, df)
     d = torch.cat([torch.zeros(1, dtype=torch.float64), 0.5 + torch.rand(4000, dtype=torch.float64) * (hi * 0.999 - 0.5)])
@@ -173,8 +175,8 @@ def test_filter_table_interpolates_filter(name, warp):
     approx = ck[..., 0] + s * (ck[..., 1] + s * (ck[..., 2] + s * ck[..., 3]))
     dapprox = (ck[..., 1] + s * (2 * ck[..., 2] + 3 * s * ck[..., 3])) * ds[:, None]
     exact, dexact = filter_table(d, rm.rbf_type, p0, p1, lo, hi, layers, "silu", True)
-    assert float((approx - exact).abs().max()) < 2e-7 * max(1.0, float(exact.abs().max()))
-    assert float((dapprox - dexact).abs().max()) < 5e-6 * max(1.0, float(dexact.abs().max()))
+    assert float((approx - exact).abs().max()) < 2e-8 * max(1.0, float(exact.abs().max()))
+    assert float((dapprox - dexact).abs().max()) < 2e-6 * max(1.0, float(dexact.abs().max()))
 
 
 def test_deepcopy_and_pickle_do_not_share_the_native_handle():

@@ -38,11 +38,11 @@ extern "C" long long tmdn_launch_count(void) { return g_launches.load(); }
 // ------------------------------------------------------------------ tuning knobs (tmdn_set_tuning)
 // Defaults can be overridden at load time by the environment (TMDN_SMALL_GEMM, TMDN_LPT_ROWS, TMDN_PDL, TMDN_EDGE_PERSIST,
 // TMDN_HOT_ROWS).  Every setting computes the same function; the knobs select kernels / launch shapes.
-//   edge_persist: large systems run the TensorNet edge kernels as persistent CTAs with the hot table rows in shared memory
+//   edge_persist: large systems run the TensorNet message-passing kernels as persistent CTAs (one per SM)
 //   hot_rows:     number of table rows (from the far end of the grid) those kernels keep in shared memory
 static int env_or(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 int g_tmdn_tuning[TMDN_TUNE_COUNT] = {env_or("TMDN_SMALL_GEMM", 1), env_or("TMDN_LPT_ROWS", 1), env_or("TMDN_PDL", 0),
-                                         env_or("TMDN_EDGE_PERSIST", 1), env_or("TMDN_HOT_ROWS", 24)};
+                                         env_or("TMDN_EDGE_PERSIST", 1), env_or("TMDN_HOT_ROWS", 0)};
 extern "C" int tmdn_set_tuning(const char* key, int value) {
     static const char* names[TMDN_TUNE_COUNT] = {"small_gemm", "lpt_rows", "pdl", "edge_persist", "hot_rows"};
     if (!key) { tmdn_set_error("set_tuning: null key"); return -1; }

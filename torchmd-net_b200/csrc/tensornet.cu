@@ -30,14 +30,14 @@ struct FilterView {
     const float* dF;    // [E,3,H]
     const float4* tab;  // [n_int,3,H] cubic coefficients (table mode) on the grid `grid` (table_grid.cuh)
     TabGrid grid;
-    const float4* hot;  // shared-memory copy of rows [k_hot, n_int) (persistent large-system kernels only)
-    int k_hot;
+    const float4* hot;  // shared-memory copy of rows [0, n_hot): the far end of the grid (persistent kernels only)
+    int n_hot;
 };
 
 // coefficient row of filter g of interval k for channel h: shared memory for the hot rows, L2 for the rest
 template <bool HOT>
 __device__ __forceinline__ float4 filter_row(const FilterView& fv, int k, int g, int H, int h) {
-    if (HOT && k >= fv.k_hot) return fv.hot[((size_t)(k - fv.k_hot) * 3 + g) * H + h];
+    if (HOT && k < fv.n_hot) return fv.hot[((size_t)k * 3 + g) * H + h];
     return __ldg(&fv.tab[((size_t)k * 3 + g) * H + h]);
 }
 
@@ -263,19 +263,21 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict_
     if (valid && lead) nh[(size_t)i * H + h] = (q - mean) * rstd * ln_w[h] + ln_b[h];
 }
 
-// ---- persistent large-system variants of the edge kernels (table mode) ------------------------------------------
+// ---- persistent large-system variants of the message-passing kernels (table mode) -------------------------------
 // One CTA per SM; a CTA is W "row workers" of H threads (threadIdx.y = worker), worker w of CTA b takes the rows
 // b*W + w + k*gridDim.x*W, so the rows in flight on the chip at any time are one contiguous window of the
 // (spatially ordered) atom index, exactly as with one-CTA-per-row launches: neighbouring rows gather the same
-// source rows and L2 serves them.  What the persistent form adds: the last `n_hot` rows of the filter table -- the
-// far end of the grid of table_grid.cuh, where 50-75 % of the edges of a condensed system fall -- are copied once
-// per CTA into shared memory, so that most table lookups (48 of the 84 / 120 bytes an edge-channel moves) no
-// longer go through L2, the resource these kernels are bound by.  Sums run in the same order as in the
-// one-row-per-CTA kernels (a worker is 4 warps, like a 128-thread CTA): results are bit-identical.
+// source rows and L2 serves them.  Measured at 98 304 atoms (gpurun r02a): tn_msg_fwd 2.21 -> 2.00 ms, tn_msg_bwd
+// 4.27 -> 3.53 ms per launch against one CTA per row; the embedding edge kernels did not gain and keep that form.
+// Optional (tuning knob "hot_rows", default 0): the first n_hot rows of the filter table -- the far end of the grid
+// of table_grid.cuh, where most neighbours of a condensed system are -- are copied once per CTA into shared memory.
+// Measured: no gain for 0 / 16 / 24 / 32 rows (23.72 / 23.68 / 23.58 / 23.61 ms per step), because shared memory and
+// L1 share one data pipe and that pipe (l1tex 71-75 % busy, L2 only 40 %), not L2, is what bounds these kernels
+// once the table is 6 MB.  Sums run in the same order as in the one-row-per-CTA kernels: results are bit-identical.
 __device__ __forceinline__ void hot_rows_load(FilterView& fv, float4* s_hot, int n_hot, int H) {
-    fv.k_hot = fv.grid.n_int - n_hot;
+    fv.n_hot = n_hot;
     fv.hot = s_hot;
-    const float4* src = fv.tab + (size_t)fv.k_hot * 3 * H;
+    const float4* src = fv.tab;
     const int tid = threadIdx.y * blockDim.x + threadIdx.x, nt = blockDim.x * blockDim.y;
     for (int q = tid; q < n_hot * 3 * H; q += nt) s_hot[q] = __ldg(&src[q]);
     __syncthreads();
@@ -298,35 +300,6 @@ template <int NV> __device__ __forceinline__ void worker_reduce(float (&v)[NV], 
     }
 }
 constexpr int WORKER_RED_FLOATS = 32;   // per-worker scratch of worker_reduce (<= 8 warps x 3 values)
-
-template <int HC>
-__global__ void __launch_bounds__(1024, 1) tn_embed_edge_fwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
-                                    const float4* __restrict__ geom, const int* __restrict__ z32,
-                                    const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv, int N,
-                                    float* __restrict__ ias, const float* __restrict__ ln_w,
-                                    const float* __restrict__ ln_b, float* __restrict__ nh, int n_hot) {
-    pdl_sync();
-    constexpr int H = HC;
-    extern __shared__ float4 s_hot[];
-    float* s_red_w = (float*)(s_hot + (size_t)n_hot * 3 * H) + WORKER_RED_FLOATS * threadIdx.y;
-    hot_rows_load(fv, s_hot, n_hot, H);
-    const int h = threadIdx.x, W = blockDim.y;
-    for (int i = blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
-        float acc[9];
-#pragma unroll
-        for (int c = 0; c < 9; ++c) acc[c] = 0.f;
-        embed_fwd_row<true, true>(row_ptr, col, geom, z32, Pz, Qz, fv, i, 0, 1, H, h, acc);
-        st9(ias, (size_t)i, H, h, acc);
-        const float q = t3_q(acc);
-        float s[1] = {q};
-        worker_reduce<1>(s, s_red_w, H);
-        const float mean = s[0] / (float)H;
-        float v[1] = {(q - mean) * (q - mean)};
-        worker_reduce<1>(v, s_red_w, H);
-        const float rstd = rsqrtf(v[0] / (float)H + 1e-5f);
-        nh[(size_t)i * H + h] = (q - mean) * rstd * ln_w[h] + ln_b[h];
-    }
-}
 
 // ------------------------------------------------------------------ per-(atom,channel) elementwise stages
 __global__ void tn_normalize_fwd(const float* __restrict__ X, float* __restrict__ Xh, long long total, int H) {
@@ -554,7 +527,7 @@ __global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_p
     msg_fwd_finish(Y, i, H, h, so3, m, M, tauh);
 }
 
-// persistent large-system variant (see tn_embed_edge_fwd_p): W row workers, hot table rows in shared memory
+// persistent large-system variant: W row workers
 template <int HC, int NB>
 __global__ void __launch_bounds__(1024, 1) tn_msg_fwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
                              const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N,
@@ -678,7 +651,7 @@ __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_p
     }
 }
 
-// persistent large-system variant (see tn_embed_edge_fwd_p): 4 row workers at 128 registers
+// persistent large-system variant: 4 row workers at 128 registers
 template <int HC, int NB>
 __global__ void __launch_bounds__(512, 1) tn_msg_bwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
                             const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
@@ -983,27 +956,6 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_bwd(const int* __restrict_
     if (valid && h == 0 && sl == 0) embed_bwd_finish(gpos, forces, i, gp, status);
 }
 
-// persistent large-system variant (see tn_embed_edge_fwd_p)
-template <int HC>
-__global__ void __launch_bounds__(1024, 1) tn_embed_edge_bwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
-                                    const float4* __restrict__ geom, const int* __restrict__ z32,
-                                    const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv,
-                                    const float* __restrict__ Dias, const float* __restrict__ gpos,
-                                    float* __restrict__ forces, int N, const int32_t* __restrict__ status, int n_hot) {
-    pdl_sync();
-    constexpr int H = HC;
-    extern __shared__ float4 s_hot[];
-    float* s_red_w = (float*)(s_hot + (size_t)n_hot * 3 * H) + WORKER_RED_FLOATS * threadIdx.y;
-    hot_rows_load(fv, s_hot, n_hot, H);
-    const int h = threadIdx.x, W = blockDim.y;
-    for (int i = blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
-        float gp[3] = {0.f, 0.f, 0.f};
-        embed_bwd_row<true, true>(row_ptr, col, geom, z32, Pz, Qz, fv, Dias, i, 0, 1, H, h, gp);
-        worker_reduce<3>(gp, s_red_w, H);
-        if (h == 0) embed_bwd_finish(gpos, forces, i, gp, status);
-    }
-}
-
 // ------------------------------------------------------------------ workspace
 struct TnWs {
     // graph
@@ -1188,7 +1140,7 @@ FilterView make_view(const tmdn_tensornet_model* m, const tmdn_filter_set& fs, c
     v.tab = (const float4*)fs.table;
     v.grid = make_tab_grid(fs.n_int, m->cutoff_upper, fs.grid_alpha, fs.grid_gamma);
     v.hot = nullptr;
-    v.k_hot = fs.n_int;
+    v.n_hot = 0;
     return v;
 }
 
@@ -1382,11 +1334,7 @@ struct TnRun {
             }
             {
                 KTimer ktimer__("tn_embed_edge_fwd", stream);
-                const PersistLaunch pl = persist_launch(tn_embed_edge_fwd_p<128>, tab, N, H, 8, fv_emb);
-                if (pl.ok)
-                    launch_k(tn_embed_edge_fwd_p<128>, pl.grid, pl.block, pl.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P,
-                             m->Q, fv_emb, N, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, pl.n_hot);
-                else if (tab && H == 128)
+                if (tab && H == 128)
                     launch_k(tn_embed_edge_fwd<true, 128>, el.grid, el.block, el.smem, stream, 
                         w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
                 else if (tab)
@@ -1527,11 +1475,7 @@ struct TnRun {
         TMDN_CHECK_ARG(forces, "tensornet: null forces pointer");
         {
             KTimer ktimer__("tn_embed_edge_bwd", stream);
-            const PersistLaunch pl = persist_launch(tn_embed_edge_bwd_p<128>, tab, N, H, 8, fv_emb);
-            if (pl.ok)
-                launch_k(tn_embed_edge_bwd_p<128>, pl.grid, pl.block, pl.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P,
-                         m->Q, fv_emb, w.dB, w.gpos, forces, N, status, pl.n_hot);
-            else if (tab && H == 128)
+            if (tab && H == 128)
                 launch_k(tn_embed_edge_bwd<true, 128>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
                                                                                    fv_emb, w.dB, w.gpos, forces, N, H, order, status);
             else if (tab)

@@ -13,14 +13,16 @@ class FusedRepresentation(nn.Module):
     _kernel_name = ""
 
     def _init_fused(self):
-        self.table_intervals = None     # None: 16 * num_rbf intervals (TableGrid in tensornet.py)
+        self.table_intervals = None     # None: max(1024, 32 * num_rbf) intervals (TableGrid in tensornet.py)
         self.table_warp = True
         self._handle = None
         self._pack_key = None
         self._workspace = None
 
     def resolved_table_intervals(self) -> int:
-        return int(self.table_intervals) if self.table_intervals else 16 * int(self.num_rbf)
+        if self.table_intervals:
+            return int(self.table_intervals)
+        return max(1024, 32 * int(self.num_rbf)) if self.table_warp else 4096
 
     # subclasses: pack_weights(head, mean, std) -> (weights, iparams, fparams); _extra_key() -> hashable
     def _extra_key(self):

@@ -137,10 +137,10 @@ def filter_table(d, rbf_type, p0, p1, lo, hi, layers, act, final_act, cutoff=Tru
 
 class TableGrid:
     """Interval grid of the filter tables (csrc/table_grid.cuh): ``n_int`` intervals over [0, hi], uniform in
-    S(d) = 1 - exp(-alpha d) + gamma d.  ExpNormal filters have features of constant width in exp(-alpha d)
-    (models/utils.py:339-344) times factors that vary on the scale of the cutoff, so this grid needs ~8x fewer
-    intervals than one uniform in d and packs the far end, where most neighbours are, into few rows.
-    alpha = 0 (Gaussian smearing, cutoff_lower > 0, or ``warp=False``) is the plain grid uniform in d."""
+    t(d) = (exp(-alpha d) - exp(-alpha hi)) + gamma (hi - d), counted from the cutoff (row 0 ends at d = hi).
+    ExpNormal filters have features of constant width in exp(-alpha d) (models/utils.py:339-344) times factors that
+    vary on the scale of the cutoff, so this grid needs far fewer intervals than one uniform in d.  alpha = 0
+    (Gaussian smearing, cutoff_lower > 0, or ``warp=False``) is the grid uniform in d."""
 
     def __init__(self, n_int, lo, hi, rbf_type, warp=True):
         self.n_int, self.hi = int(n_int), float(hi)
@@ -149,11 +149,14 @@ class TableGrid:
         else:
             self.alpha = self.gamma = 0.0
 
-    def S(self, d):
-        return 1.0 - torch.exp(-self.alpha * d) + self.gamma * d if self.alpha > 0 else d
+    def t(self, d):
+        if self.alpha == 0:
+            return self.hi - d
+        import math
+        return (torch.exp(-self.alpha * d) - math.exp(-self.alpha * self.hi)) + self.gamma * (self.hi - d)
 
-    def dS(self, d):
-        return self.alpha * torch.exp(-self.alpha * d) + self.gamma if self.alpha > 0 else torch.ones_like(d)
+    def dt(self, d):
+        return -(self.alpha * torch.exp(-self.alpha * d) + self.gamma) if self.alpha > 0 else -torch.ones_like(d)
 
     @property
     def step(self):
@@ -162,25 +165,25 @@ class TableGrid:
         return T / self.n_int
 
     def nodes(self, device=None):
-        """d_k with S(d_k) = k * step, k = 0..n_int (fp64; Newton on the monotone S)."""
-        sk = torch.arange(self.n_int + 1, device=device, dtype=torch.float64) * self.step
+        """d_k with t(d_k) = k * step, k = 0..n_int: descending from hi to 0 (fp64; Newton on the monotone t)."""
+        tk = torch.arange(self.n_int + 1, device=device, dtype=torch.float64) * self.step
         if self.alpha == 0:
-            return sk
-        d = sk / (self.step * self.n_int) * self.hi
+            return self.hi - tk
+        d = self.hi * (1.0 - tk / (self.step * self.n_int))
         for _ in range(80):
-            d = (d - (self.S(d) - sk) / self.dS(d)).clamp(0.0, self.hi)
-        d[0], d[-1] = 0.0, self.hi
+            d = (d - (self.t(d) - tk) / self.dt(d)).clamp(0.0, self.hi)
+        d[0], d[-1] = self.hi, 0.0
         return d
 
     def coefficients(self, d, f, df):
         """Cubic Hermite coefficients in the local coordinate of each interval from f, df/dd at the nodes ``d``."""
-        return hermite_coefficients(f, df / self.dS(d)[:, None], self.step)
+        return hermite_coefficients(f, df / self.dt(d)[:, None], self.step)
 
     def locate(self, d):
         """-> (interval k, local coordinate s, ds/dd) exactly as the kernels compute them (tab_locate)."""
-        sv = self.S(d) / self.step
-        k = sv.floor().clamp(min=0, max=self.n_int - 1).long()
-        return k, sv - k, self.dS(d) / self.step
+        q = self.t(d) / self.step
+        k = q.floor().clamp(min=0, max=self.n_int - 1).long()
+        return k, q - k, self.dt(d) / self.step
 
 
 def hermite_coefficients(f, df, h):
@@ -194,7 +197,7 @@ class TensorNet(FusedRepresentation):
     """Drop-in for ``torchmdnet.models.tensornet.TensorNet`` (tensornet.py:70-234): same constructor, same
     parameters.  ``filter_mode``: "exact" evaluates the per-edge filter MLPs with fp32 GEMMs, "table"
     evaluates them from a cubic Hermite table built in fp64 from the weights on the grid of ``TableGrid``
-    (``table_intervals`` intervals, default 16 * num_rbf; ``table_warp=False`` = uniform in d)."""
+    (``table_intervals`` intervals, default max(1024, 32 * num_rbf); ``table_warp=False`` = uniform in d)."""
     _op = "tensornet"
     _kernel_name = "TensorNet"
 

@@ -61,7 +61,7 @@ class TorchMD_ET(FusedRepresentation):
     parameters; evaluated by the fused kernels of csrc/et.cu.  The distance filters (dk_proj, dv_proj, the
     neighbour-embedding distance_proj) are univariate in d and are evaluated from cubic Hermite tables built in fp64
     from the weights on the grid of ``tensornet.TableGrid`` (``table_intervals`` intervals over [0, cutoff_upper],
-    default 16 * num_rbf)."""
+    default max(1024, 32 * num_rbf))."""
     _op = "et"
     _kernel_name = "TorchMD_ET"
 
