@@ -145,6 +145,23 @@ int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int64_t* batch
                             int64_t max_edges, int32_t* row_ptr, int32_t* col, float* geom, int32_t* num_found,
                             void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
 
+/* Allocation-free variant of tmdn_csr_build_f32.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments and results as tmdn_csr_build_f32 without the workspace: the scratch (row counters,
+ * scan partials, cell-sorted atom copies) is a file-scope static __device__ array of TMDN_CSR_STATIC_SCRATCH_BYTES
+ * (4 MiB) that every GPU loading the library holds until exit -- enough for about 1 000 000 atoms with the brute /
+ * shared strategies (4 B per atom) and about 65 000 with the cell strategy (60 B per atom + 8 B per cell;
+ * tmdn_csr_build_workspace_bytes gives the exact need).  Larger
+ * problems are refused with TMDN_EWORKSPACE and a message naming the limit.  The call allocates nothing (no cudaMalloc,
+ * cudaFree or allocating library routine) and does not synchronise.  All calls on a device share the one array, which
+ * keeps the previous call's contents (the builder clears what must start at zero): calls that overlap on the GPU --
+ * different streams without an ordering between them -- race on it; calls on one stream are ordered and safe. */
+#define TMDN_CSR_STATIC_SCRATCH_BYTES (4 << 20)
+int tmdn_csr_build_static_f32(int strategy, const float* pos, const int64_t* batch, int64_t n_atoms, const double box[9],
+                              int use_periodic, double cutoff_lower, double cutoff_upper, int64_t max_edges,
+                              int32_t* row_ptr, int32_t* col, float* geom /* [max_edges,4] */, int32_t* num_found,
+                              tmdn_stream_t stream);
+
 /* ---------------------------------------------------------------- TensorNet energy + forces (fp32)
  * All weight pointers are device fp32 arrays prepared once by the host side (layouts below; H = hidden,
  * K = num_rbf).  "T" suffix = transposed copy used by the backward kernels.

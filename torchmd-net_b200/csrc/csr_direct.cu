@@ -7,6 +7,7 @@
 // No atomics on the output, no sort, and the edge order inside a row is a pure function of the positions
 // (ascending source index for brute; cell-traversal order of nbr_cell_tile.cuh with cells internally sorted by index for cell), so
 // every downstream segmented sum is bit-reproducible.  Same pair set and same rounding as tmdn_neighbors_f32.
+#include <mutex>
 #include "common.cuh"
 #include "nbr_cell_tile.cuh"
 #include "scan.cuh"
@@ -236,4 +237,52 @@ extern "C" int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int
     launch_k(csr_finish_kernel, (unsigned)cdiv(n + 1, 256), 256, 0, stream, row_ptr, n, (long long)max_edges, num_found);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
+}
+
+// ------------------------------------------------------------------ allocation-free variant (static device scratch)
+// tmdn_csr_build_static_f32: tmdn_csr_build_f32 with its scratch (row counters, scan partials, the cell-sorted copies of
+// the atoms) in a file-scope device array instead of a caller-provided workspace, for callers that cannot allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds
+// the array until exit.  g_csr_scratch is a host-side stand-in in host code, not a device address: its address is
+// taken once per device with cudaGetSymbolAddress (with that device current) and that pointer is what the kernels get.
+static __device__ __align__(256) unsigned char g_csr_scratch[TMDN_CSR_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int STATIC_MAX_DEVICES = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[STATIC_MAX_DEVICES] = {nullptr};
+}  // namespace
+
+extern "C" int tmdn_csr_build_static_f32(int strategy, const float* pos, const int64_t* batch, int64_t n_atoms,
+                                         const double box[9], int use_periodic, double cutoff_lower, double cutoff_upper,
+                                         int64_t max_edges, int32_t* row_ptr, int32_t* col, float* geom,
+                                         int32_t* num_found, tmdn_stream_t stream_) {
+    TMDN_CHECK_ARG(n_atoms > 0, "csr_build_static: bad atom count");
+    TMDN_CHECK_ARG(strategy == TMDN_BRUTE || strategy == TMDN_SHARED || strategy == TMDN_CELL, "Unknown kernel name");
+    const size_t need = tmdn_csr_build_workspace_bytes(strategy, n_atoms, box, cutoff_upper);
+    TMDN_CHECK_ARG(need > 0, "csr_build_static: bad box for the cell strategy");
+    if (need > (size_t)TMDN_CSR_STATIC_SCRATCH_BYTES) {
+        tmdn_set_error("csr_build_static: %lld atoms need %zu bytes of scratch, the static array holds %d "
+                       "(TMDN_CSR_STATIC_SCRATCH_BYTES); use tmdn_csr_build_f32 with a caller-provided workspace",
+                       (long long)n_atoms, need, TMDN_CSR_STATIC_SCRATCH_BYTES);
+        return TMDN_EWORKSPACE;
+    }
+    int dev = -1;
+    TMDN_CUDA(cudaGetDevice(&dev));
+    TMDN_CHECK_ARG(dev >= 0 && dev < STATIC_MAX_DEVICES, "csr_build_static: device index %d out of range", dev);
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (g_static_ptr[dev] == nullptr) {   // once per device, with that device current
+            void* p = nullptr;
+            TMDN_CUDA(cudaGetSymbolAddress(&p, g_csr_scratch));
+            g_static_ptr[dev] = p;
+        }
+        scratch = g_static_ptr[dev];
+    }
+    // the builder clears the counters it accumulates into and overwrites everything else it reads, so the contents
+    // left by the previous call do not matter (the caller-provided workspaces are uninitialised memory as well)
+    return tmdn_csr_build_rows_f32(strategy, pos, batch, n_atoms, n_atoms, box, use_periodic, cutoff_lower, cutoff_upper,
+                                   max_edges, row_ptr, col, geom, num_found, scratch, (size_t)TMDN_CSR_STATIC_SCRATCH_BYTES,
+                                   stream_);
 }
