@@ -219,7 +219,10 @@ size_t tmdn_tensornet_workspace_bytes(const tmdn_tensornet_model* m, int64_t n_a
  * [0,n_mol)); pos fp32 device [n_atoms,3]; energy fp32 device [n_mol]; forces fp32 device [n_atoms,3] or NULL
  * (forward only).  Neighbors are searched with `strategy` under box/use_periodic; max_edges is the pair
  * capacity INCLUDING self loops (reference: max_num_neighbors * n_atoms, models/utils.py:234-236).
- * status (device int32[4]): [0] edges found, [1] 1 if found > max_edges (result then invalid), [2..3] reserved.
+ * status (device int32[4]): [0] edges found, [1] 1 if found > max_edges, [2] 1 if some z was outside [0, max_z),
+ * [3] 1 if batch was not sorted.  When any of [1..3] is set, energy and forces are filled with NaN on the device: a
+ * truncated edge list is not symmetric, so the analytic forces would not belong to the energy (the reference's
+ * autograd forces stay consistent with its truncated energy; this path says "invalid" instead of being subtly wrong).
  */
 int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const int64_t* z, const float* pos,
                                  const int64_t* batch, int64_t n_atoms, int64_t n_mol, const double box[9],
@@ -227,20 +230,43 @@ int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const int64_t* z
                                  int32_t* status, void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
 /* The same evaluation cut at its halo points, for spatially decomposed runs (one rank owns the first n_rows atoms of
  * its local arrays, the remaining n_atoms - n_rows are ghosts owned by other ranks).  Call order:
- *   EMBED, [exchange "Y0"], LAYER_FWD(0), [exchange "Y1"], ..., LAYER_FWD(L-1), HEAD, [exchange "Dias"],
- *   LAYER_BWD(L-1), [exchange "Dias"], ..., LAYER_BWD(0), [exchange "Dias"], FINAL
+ *   EMBED, [exchange "Y0"], LAYER_FWD(0), [exchange "Y1"], ..., LAYER_FWD(L-1), HEAD, [exchange B0],
+ *   LAYER_BWD(L-1), [exchange B1], ..., LAYER_BWD(0), [exchange B_L], FINAL
  * where an exchange copies the rows of the named workspace buffer ([n_atoms,9,H] fp32) from their owners into the
- * ghost rows.  energy receives the sum over the OWNED atoms only (+ mean); forces has n_rows rows.
+ * ghost rows, and B_k = "Dias" for even k, "Dias1" for odd k: consecutive backward halo points alternate between two
+ * buffers, so a rank may deliver its rows into a neighbour's ghost rows while that neighbour still reads the previous
+ * halo point.  energy receives the sum over the OWNED atoms only (+ mean); forces has n_rows rows.
  * tmdn_tensornet_energy_forces == all stages in sequence with n_rows = n_atoms. */
-enum tmdn_tn_stage { TMDN_TN_EMBED = 0, TMDN_TN_LAYER_FWD = 1, TMDN_TN_HEAD = 2, TMDN_TN_LAYER_BWD = 3, TMDN_TN_FINAL = 4 };
+enum tmdn_tn_stage { TMDN_TN_EMBED = 0, TMDN_TN_LAYER_FWD = 1, TMDN_TN_HEAD = 2, TMDN_TN_LAYER_BWD = 3, TMDN_TN_FINAL = 4,
+                     TMDN_TN_GRAPH = 5 };
 int tmdn_tensornet_stage(const tmdn_tensornet_model* m, int stage, int layer, const int64_t* z, const float* pos,
                          const int64_t* batch, int64_t n_atoms, int64_t n_rows, int64_t n_mol, const double box[9],
                          int use_periodic, int strategy, int64_t max_edges, float* energy, float* forces,
                          int32_t* status, void* workspace, size_t workspace_bytes, tmdn_stream_t stream);
+/* A stage over the owned rows [row_begin, row_end) only -- every operation between two halo points is local to a row
+ * (the edge kernels gather from any local atom but write their own row), so a rank can evaluate the rows its neighbours
+ * are waiting for first, start their transfer, and evaluate the interior rows while the transfer is in flight.
+ * Here GRAPH (neighbour search -> CSR of all owned rows, z conversion, exact-mode filters; row range ignored) is a
+ * stage of its own and must precede EMBED; HEAD performs the molecular sums in the call whose range ends at n_rows
+ * (make it the last one).  Edge-kernel sums do not depend on the split (launch shapes follow n_rows); the node GEMMs
+ * pick their kernel by the size of the range, so a split result is bit-identical when both parts select the same
+ * GEMM kernel as the whole (always beyond ~10^4 rows) and within rounding otherwise. */
+int tmdn_tensornet_stage_rows(const tmdn_tensornet_model* m, int stage, int layer, const int64_t* z, const float* pos,
+                              const int64_t* batch, int64_t n_atoms, int64_t n_rows, int64_t row_begin, int64_t row_end,
+                              int64_t n_mol, const double box[9], int use_periodic, int strategy, int64_t max_edges,
+                              float* energy, float* forces, int32_t* status, void* workspace, size_t workspace_bytes,
+                              tmdn_stream_t stream);
 /* Halo pack: out[r, :] = src[idx[r], :] for r < n_rows (rows of row_floats fp32).  The receive side writes straight into
  * the ghost rows (the contiguous tail of the local arrays), so there is no unpack. */
 int tmdn_halo_pack_f32(const float* src, const int32_t* idx, int64_t n_rows, int64_t row_floats, float* out,
                        tmdn_stream_t stream);
+/* Halo push over peer memory (NVLink): the pack and the transport in one kernel.  For peer p (p < n_peers) the rows
+ * idx[seg[p] .. seg[p+1]) of src are written to dst[p], a device pointer into the PEER's address space (its ghost rows;
+ * obtained by the host side through CUDA IPC / symmetric memory), row r of the segment at dst[p] + r * row_floats.
+ * seg (int64[n_peers+1]), idx (int32) and dst (float*[n_peers]) are device arrays.  The stores are followed by a
+ * system-scope fence; the caller orders "data has landed" with a cross-rank barrier on the same stream. */
+int tmdn_halo_push_f32(const float* src, const int32_t* idx, const int64_t* seg, float* const* dst, int n_peers,
+                       int64_t n_rows_total, int64_t row_floats, tmdn_stream_t stream);
 /* Grouped channel mix of TensorNet (tensornet.py:273-284, 386-408: linears_tensor on the I | A | S parts):
  *   y[a, c, :] (+)= x[a, c, :] * w[g(c)]^T,   x, y [n_atoms,9,H] fp32, w [3,H,H] (g = 0 for c = 0, 1 for c = 1..3, 2 for
  *   c = 4..8).  H = 128 runs on the tcgen05 tensor cores with the three-product tf32 split (fp32-level accuracy);

@@ -56,9 +56,10 @@ template <int NV> __device__ __forceinline__ void atom_reduce(float (&v)[NV], fl
         v[k] = t;
     }
 }
-// row handled by this (blockIdx.x, threadIdx.z): identity, or through the visiting order of small systems
-__device__ __forceinline__ int edge_row(const int* __restrict__ order, int N, bool& valid) {
-    int i = blockIdx.x * blockDim.z + threadIdx.z;
+// row handled by this (blockIdx.x, threadIdx.z) of a launch over the rows [row0, N): identity, or through the visiting
+// order of small systems (full-range launches only)
+__device__ __forceinline__ int edge_row(const int* __restrict__ order, int row0, int N, bool& valid) {
+    int i = row0 + blockIdx.x * blockDim.z + threadIdx.z;
     valid = i < N;
     if (order != nullptr && valid) i = order[i];
     return i;

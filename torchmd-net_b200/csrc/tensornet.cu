@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict_
                                   const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv, int N,
                                   int H_, float* __restrict__ ias, const float* __restrict__ ln_w,
                                   const float* __restrict__ ln_b, float* __restrict__ nh,
-                                  const int* __restrict__ order) {
+                                  const int* __restrict__ order, int row0) {
     pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_fwd(const int* __restrict_
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
     bool valid;
-    const int i = edge_row(order, N, valid);
+    const int i = edge_row(order, row0, N, valid);
     float acc[9];
 #pragma unroll
     for (int c = 0; c < 9; ++c) acc[c] = 0.f;
@@ -508,7 +508,7 @@ __device__ __forceinline__ void msg_fwd_finish(const float* __restrict__ Y, int 
 template <bool TAB, int NB = 1, int HC = 0, bool PF = false, int MAXT = MSG_FWD_THREADS>
 __global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N, int H_,
-                           int so3, float* __restrict__ M, float* __restrict__ tauh, const int* __restrict__ order) {
+                           int so3, float* __restrict__ M, float* __restrict__ tauh, const int* __restrict__ order, int row0) {
     pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_p
     // 166 rows on 148 SMs are two full waves of whole-row CTAs, 664 slabs are 4.5 waves of quarter-length ones)
     const int h = blockIdx.y * blockDim.x + threadIdx.x, sl = threadIdx.y, S = blockDim.y;
     bool valid;
-    const int i = edge_row(order, N, valid);
+    const int i = edge_row(order, row0, N, valid);
     float m[9];
 #pragma unroll
     for (int c = 0; c < 9; ++c) m[c] = 0.f;
@@ -531,13 +531,13 @@ __global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_p
 template <int HC, int NB>
 __global__ void __launch_bounds__(1024, 1) tn_msg_fwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
                              const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N,
-                             int so3, float* __restrict__ M, float* __restrict__ tauh, int n_hot) {
+                             int so3, float* __restrict__ M, float* __restrict__ tauh, int n_hot, int row0) {
     pdl_sync();
     constexpr int H = HC;
     extern __shared__ float4 s_hot[];
     hot_rows_load(fv, s_hot, n_hot, H);
     const int h = threadIdx.x, W = blockDim.y;
-    for (int i = blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
+    for (int i = row0 + blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
         float m[9];
 #pragma unroll
         for (int c = 0; c < 9; ++c) m[c] = 0.f;
@@ -627,7 +627,7 @@ template <bool TAB, int NB = 2, int HC = 0, int MAXT = MSG_BWD_THREADS, bool PF 
 __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col,
                            const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
                            const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
-                           int H_, const int* __restrict__ order) {
+                           int H_, const int* __restrict__ order, int row0) {
     pdl_sync();
     const int H = HC > 0 ? HC : H_;
     extern __shared__ float smem[];
@@ -635,7 +635,7 @@ __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_p
     float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
     bool valid;
-    const int i = edge_row(order, N, valid);
+    const int i = edge_row(order, row0, N, valid);
     float gp[3] = {0.f, 0.f, 0.f};
     float acc[9];
 #pragma unroll
@@ -656,14 +656,14 @@ template <int HC, int NB>
 __global__ void __launch_bounds__(512, 1) tn_msg_bwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
                             const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
                             const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
-                            int n_hot) {
+                            int n_hot, int row0) {
     pdl_sync();
     constexpr int H = HC;
     extern __shared__ float4 s_hot[];
     float* s_red_w = (float*)(s_hot + (size_t)n_hot * 3 * H) + WORKER_RED_FLOATS * threadIdx.y;
     hot_rows_load(fv, s_hot, n_hot, H);
     const int h = threadIdx.x, W = blockDim.y;
-    for (int i = blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
+    for (int i = row0 + blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
         float gp[3] = {0.f, 0.f, 0.f};
         float acc[9];
         msg_bwd_row<true, NB, false, true>(row_ptr, col, geom, fv, Y, dM, dY, i, 0, 1, H, h, acc, gp);
@@ -941,7 +941,7 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_bwd(const int* __restrict_
                                   const float4* __restrict__ geom, const int* __restrict__ z32,
                                   const float* __restrict__ Pz, const float* __restrict__ Qz, FilterView fv,
                                   const float* __restrict__ Dias, const float* __restrict__ gpos,
-                                  float* __restrict__ forces, int N, int H_, const int* __restrict__ order,
+                                  float* __restrict__ forces, int N, int H_, const int* __restrict__ order, int row0,
                                   const int32_t* __restrict__ status) {
     pdl_sync();
     const int H = HC > 0 ? HC : H_;
@@ -949,7 +949,7 @@ __global__ void __launch_bounds__(1024) tn_embed_edge_bwd(const int* __restrict_
     float* s_red = smem;
     const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
     bool valid;
-    const int i = edge_row(order, N, valid);
+    const int i = edge_row(order, row0, N, valid);
     float gp[3] = {0.f, 0.f, 0.f};
     if (valid) embed_bwd_row<TAB, false>(row_ptr, col, geom, z32, Pz, Qz, fv, Dias, i, sl, S, H, h, gp);
     atom_reduce<3>(gp, s_red);
@@ -972,7 +972,7 @@ struct TnWs {
     float *ias, *iasm, *nh, *h1, *a1, *h2, *fias, *X[TMDN_MAX_LAYERS + 1], *Xh, *Y[TMDN_MAX_LAYERS],
         *M[TMDN_MAX_LAYERS], *tauh, *dX[TMDN_MAX_LAYERS], *xl, *stat, *h3, *a3, *h4, *a4, *e_atom;
     // backward
-    float *dXa, *dB, *dC, *d4, *d3, *dxl, *dh2, *dh1, *dnh, *gpos;
+    float *dXa, *dB, *dB2, *dC, *d4, *d3, *dxl, *dh2, *dh1, *dnh, *gpos;
 };
 struct WsEntry { std::string name; size_t off, bytes; };
 
@@ -1038,7 +1038,8 @@ int carve_tn(Arena& a, const tmdn_tensornet_model* m, int64_t N, int64_t P, int6
     w.a4 = carve<float>(a, names, "a4", n * (H / 2));
     w.e_atom = carve<float>(a, names, "e_atom", n);
     w.dXa = carve<float>(a, names, "dXa", nh9);
-    w.dB = carve<float>(a, names, "Dias", nh9);   // last content: dE/d ias (staged name "Dias")
+    w.dB = carve<float>(a, names, "Dias", nh9);    // backward halo points 0, 2, ... (TnRun::dBk); with an even number
+    w.dB2 = carve<float>(a, names, "Dias1", nh9);  // of layers the last content of "Dias" is dE/d ias, else of "Dias1"
     w.dC = carve<float>(a, names, "dC", nh9);
     w.d4 = carve<float>(a, names, "d4", n * (H / 2));
     w.d3 = carve<float>(a, names, "d3", n * H);
@@ -1237,27 +1238,41 @@ struct TnRun {
         return TMDN_OK;
     }
 
-    // adjoint of X_{l+1} = Xh + dX + dX^2 and of the (M, Y) product: dXa -> dB (= dM_l), dC (= direct dY_l)
-    int pre_bwd(int l, bool update_done = false) {
-        const int N = (int)n_rows, H = m->hidden;
+    // node buffers advanced to row r0 (every per-row array is row-major, so a row range is a pointer shift)
+    static TnWs shift_rows(const TnWs& a, size_t r0, size_t H, int L) {
+        TnWs x = a;
+        auto sh = [&](float*& p, size_t row_floats) { if (p) p += r0 * row_floats; };
+        sh(x.ias, 9 * H); sh(x.iasm, 9 * H); sh(x.nh, H); sh(x.h1, 2 * H); sh(x.a1, 2 * H); sh(x.h2, 3 * H);
+        sh(x.fias, 3 * H); sh(x.Xh, 9 * H); sh(x.tauh, 9 * H); sh(x.xl, 3 * H); sh(x.stat, 2); sh(x.h3, H);
+        sh(x.a3, H); sh(x.h4, H / 2); sh(x.a4, H / 2); sh(x.e_atom, 1); sh(x.dXa, 9 * H); sh(x.dB, 9 * H);
+        sh(x.dB2, 9 * H); sh(x.dC, 9 * H); sh(x.d4, H / 2); sh(x.d3, H); sh(x.dxl, 3 * H); sh(x.dh2, 3 * H);
+        sh(x.dh1, 2 * H); sh(x.dnh, H); sh(x.gpos, 3);
+        for (int l = 0; l <= L; ++l) sh(x.X[l], 9 * H);
+        for (int l = 0; l < L; ++l) { sh(x.Y[l], 9 * H); sh(x.M[l], 9 * H); sh(x.dX[l], 9 * H); }
+        return x;
+    }
+    // Backward halo point k (k = 0: after HEAD, k: after LAYER_BWD(L-k)) lives in buffer k & 1 ("Dias" / "Dias1"):
+    // a stage reads the neighbours' rows of one buffer and produces the rows of the other, so a rank that runs ahead
+    // can deliver its rows into a neighbour's ghost rows while that neighbour still reads the previous ones.
+    static float* dBk(const TnWs& x, int k) { return (k & 1) ? x.dB2 : x.dB; }
+
+    // adjoint of the (M, Y) product of layer l: dB (= d tau-hat mixed back) -> dB (= dM_l), dC (= direct dY_l)
+    // (w: row-shifted buffers, N rows, dB: the rows of this halo point's buffer)
+    int pre_bwd(const TnWs& w, int N, float* dB, int l) {
+        const int H = m->hidden;
         const long long NH = (long long)N * H;
         const unsigned egrid = (unsigned)cdiv(NH, 256);
-        if (!update_done) {
-            KTimer ktimer__("tn_update_bwd", stream);
-            launch_k(tn_update_bwd, egrid, 256, 0, stream, w.dXa, w.dX[l], w.dB, NH, H);
-            TMDN_LAUNCH_CHECK();
-        }
-        TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.dB, w.dC, m->layer_mixT[l] + 3, N, H), stream));
+        TMDN_TRY(mix_launch(EPI_NONE, mix_batch(dB, w.dC, m->layer_mixT[l] + 3, N, H), stream));
         {
             KTimer ktimer__("tn_prod_bwd", stream);
-            launch_k(tn_prod_bwd, egrid, 256, 0, stream, w.Y[l], w.M[l], w.dC, w.dB, NH, H, m->so3);
+            launch_k(tn_prod_bwd, egrid, 256, 0, stream, w.Y[l], w.M[l], w.dC, dB, NH, H, m->so3);
             TMDN_LAUNCH_CHECK();
         }
         return TMDN_OK;
     }
-    // adjoint of the embedding node stage: dXa -> dB (= dE/d ias, "Dias")
-    int embed_node_bwd(const float* Xn = nullptr) {
-        const int N = (int)n_rows, H = m->hidden, act = m->activation;
+    // adjoint of the embedding node stage: dXa -> dB (= dE/d ias)
+    int embed_node_bwd(const TnWs& w, int N, float* dB, const float* Xn = nullptr) {
+        const int H = m->hidden, act = m->activation;
         const long long NH = (long long)N * H;
         const unsigned egrid = (unsigned)cdiv(NH, 256);
         const int apb = H >= 128 ? 1 : 128 / H;
@@ -1271,78 +1286,96 @@ struct TnRun {
         TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
         GemmP q = gemm_desc(w.dh1, 2 * H, m->emb_w1T, nullptr, w.dnh, H, N, H, 2 * H);
         TMDN_TRY(node_gemm1(EPI_NONE, q, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
-        TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.dXa, w.dB, m->emb_mixT, N, H), stream));
+        TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.dXa, dB, m->emb_mixT, N, H), stream));
         {
             KTimer ktimer__("tn_embed_norm_bwd", stream);
-            launch_k(tn_embed_norm_bwd, (unsigned)cdiv(N, apb), dim3(H, apb), 0, stream, w.ias, m->emb_ln_w, w.dnh, w.dB, N, H);
+            launch_k(tn_embed_norm_bwd, (unsigned)cdiv(N, apb), dim3(H, apb), 0, stream, w.ias, m->emb_ln_w, w.dnh, dB, N, H);
             TMDN_LAUNCH_CHECK();
         }
         return TMDN_OK;
     }
 
-    int stage(int s, int l) {
-        const int N = (int)n_rows, NT = (int)n_atoms, H = m->hidden, L = m->num_layers, act = m->activation;
+    // One stage over the rows [r0, r1) of the owned atoms.  Row-local kernels run on row-shifted buffers, the edge
+    // kernels index rows absolutely (their gathers reach every local atom, ghosts included).
+    int stage(int s, int l, int64_t r0_, int64_t r1_) {
+        TMDN_CHECK_ARG(s >= TMDN_TN_EMBED && s <= TMDN_TN_GRAPH, "tensornet: bad stage %d", s);
+        TMDN_CHECK_ARG(r0_ >= 0 && r0_ < r1_ && r1_ <= n_rows, "tensornet: bad row range [%lld, %lld)", (long long)r0_,
+                       (long long)r1_);
+        const int r0 = (int)r0_, r1 = (int)r1_, N = r1 - r0, NT = (int)n_atoms, H = m->hidden, L = m->num_layers;
+        const int act = m->activation;
         const bool tab = m->filter_mode == TMDN_FILTER_TABLE;
-        const float4* geom = (const float4*)w.geom;
+        const bool full = r0 == 0 && r1 == (int)n_rows;
+        const TnWs& wa = this->w;                                  // absolute buffers (edge kernels)
+        const TnWs w = shift_rows(wa, (size_t)r0, (size_t)H, L);   // buffers of rows [r0, r1) (row-local kernels)
+        const float4* geom = (const float4*)wa.geom;
         const int apb = H >= 128 ? 1 : 128 / H;
         const dim3 rblock(H, apb);
-        const EdgeLaunch el = edge_launch(N, H, 1024);    // embedding edge kernels: <= 64 registers/thread
-        const EdgeLaunch elb = edge_launch(N, H, 1024);   // 56 registers
-        const EdgeLaunch elf2 = edge_launch(N, H, MSG_FWD_THREADS);
+        // launch shapes (edge slices per row) follow the size of the whole problem, not of the row range, so that a
+        // split evaluation sums in the same order as the unsplit one
+        auto edge_shape = [&](int max_threads) {
+            EdgeLaunch e = edge_launch((int)n_rows, H, max_threads);
+            e.grid = (unsigned)cdiv(N, (int)e.block.z);
+            return e;
+        };
+        const EdgeLaunch el = edge_shape(1024);    // embedding edge kernels: <= 64 registers/thread
+        const EdgeLaunch elb = edge_shape(1024);   // 56 registers
+        const EdgeLaunch elf2 = edge_shape(MSG_FWD_THREADS);
         // two edges in flight per thread; up to 4 slices per row when the rows alone cannot fill the machine
-        const bool bwd4 = tab && (long long)N * H * 2 < (long long)tmdn_sm_count() * 2048;
-        const EdgeLaunch elb2 = edge_launch(N, H, bwd4 ? 512 : MSG_BWD_THREADS);
+        const bool bwd4 = tab && (long long)n_rows * H * 2 < (long long)tmdn_sm_count() * 2048;
+        const EdgeLaunch elb2 = edge_shape(bwd4 ? 512 : MSG_BWD_THREADS);
         const unsigned rgrid = (unsigned)cdiv(N, apb);
         const long long NH = (long long)N * H;
         const unsigned egrid = (unsigned)cdiv(NH, 256);
         // few rows: one CTA per row leaves a second partial wave (166 rows on 148 SMs); rows are visited in order of
         // decreasing degree so that the short ones fill the tail (longest-processing-time-first)
-        const int* order = (g_tmdn_tuning[TMDN_TUNE_LPT_ROWS] && N <= LPT_MAX_ROWS) ? w.row_order : nullptr;
-        TMDN_CHECK_ARG(s >= TMDN_TN_EMBED && s <= TMDN_TN_FINAL, "tensornet: bad stage %d", s);
+        const bool lpt = g_tmdn_tuning[TMDN_TUNE_LPT_ROWS] && n_rows <= LPT_MAX_ROWS;
+        const int* order = (lpt && full) ? wa.row_order : nullptr;
+        const bool small_rows = n_rows <= LPT_MAX_ROWS;
         TMDN_CHECK_ARG((s != TMDN_TN_LAYER_FWD && s != TMDN_TN_LAYER_BWD) || (l >= 0 && l < L), "tensornet: bad layer %d", l);
 
-        if (s == TMDN_TN_EMBED) {
+        if (s == TMDN_TN_GRAPH) {
             // graph: neighbour search straight into CSR by target (= row 0 of the reference's pair list,
             // tensornet.py:313-315), self loops included
             {
                 KTimer ktimer__("neighbors_csr", stream);
                 TMDN_TRY(tmdn_csr_build_rows_f32(strategy, pos, batch, n_atoms, n_rows, box, use_periodic, m->cutoff_lower,
-                                                 m->cutoff_upper, P, w.row_ptr, w.col, w.geom, w.num_found, w.graph_ws,
-                                                 w.graph_ws_bytes, (tmdn_stream_t)stream));
+                                                 m->cutoff_upper, P, wa.row_ptr, wa.col, wa.geom, wa.num_found, wa.graph_ws,
+                                                 wa.graph_ws_bytes, (tmdn_stream_t)stream));
             }
             TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
             {
                 KTimer ktimer__("tn_prep_kernel", stream);
-                launch_k(tn_prep_kernel, (unsigned)cdiv(NT, 256), 256, 0, stream, z, w.z32, NT, m->max_z, w.num_found,
-                                                                            (long long)P, status, w.row_ptr, N,
-                                                                            order ? w.row_order : nullptr, batch);
+                launch_k(tn_prep_kernel, (unsigned)cdiv(NT, 256), 256, 0, stream, z, wa.z32, NT, m->max_z, wa.num_found,
+                         (long long)P, status, wa.row_ptr, (int)n_rows, lpt ? wa.row_order : nullptr, batch);
                 TMDN_LAUNCH_CHECK();
             }
             if (!tab) {  // exact filters: rbf once, then one MLP chain per filter set
                 const long long tot = (long long)P * m->num_rbf;
                 {
                     KTimer ktimer__("tn_rbf_kernel", stream);
-                    launch_k(tn_rbf_kernel, (unsigned)cdiv(tot, 256), 256, 0, stream, geom, w.row_ptr, N, (long long)P,
-                                                                                m->num_rbf, m->rbf_type, m->cutoff_lower,
-                                                                                m->cutoff_upper, m->rbf_p0, m->rbf_p1,
-                                                                                w.R, w.dR);
+                    launch_k(tn_rbf_kernel, (unsigned)cdiv(tot, 256), 256, 0, stream, geom, wa.row_ptr, (int)n_rows,
+                             (long long)P, m->num_rbf, m->rbf_type, m->cutoff_lower, m->cutoff_upper, m->rbf_p0, m->rbf_p1,
+                             wa.R, wa.dR);
                     TMDN_LAUNCH_CHECK();
                 }
-                TMDN_TRY(eval_filter_exact(m, m->emb_filter, w, n_atoms, P, w.F[0], w.dF[0], stream));
+                TMDN_TRY(eval_filter_exact(m, m->emb_filter, wa, n_atoms, P, wa.F[0], wa.dF[0], stream));
                 for (int k = 0; k < L; ++k)
-                    TMDN_TRY(eval_filter_exact(m, m->layer_filter[k], w, n_atoms, P, w.F[k + 1], w.dF[k + 1], stream));
+                    TMDN_TRY(eval_filter_exact(m, m->layer_filter[k], wa, n_atoms, P, wa.F[k + 1], wa.dF[k + 1], stream));
             }
+            return TMDN_OK;
+        }
+        if (s == TMDN_TN_EMBED) {
             {
                 KTimer ktimer__("tn_embed_edge_fwd", stream);
                 if (tab && H == 128)
-                    launch_k(tn_embed_edge_fwd<true, 128>, el.grid, el.block, el.smem, stream, 
-                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
+                    launch_k(tn_embed_edge_fwd<true, 128>, el.grid, el.block, el.smem, stream, wa.row_ptr, wa.col, geom,
+                             wa.z32, m->P, m->Q, fv_emb, r1, H, wa.ias, m->emb_ln_w, m->emb_ln_b, wa.nh, order, r0);
                 else if (tab)
-                    launch_k(tn_embed_edge_fwd<true>, el.grid, el.block, el.smem, stream, 
-                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
+                    launch_k(tn_embed_edge_fwd<true>, el.grid, el.block, el.smem, stream, wa.row_ptr, wa.col, geom, wa.z32,
+                             m->P, m->Q, fv_emb, r1, H, wa.ias, m->emb_ln_w, m->emb_ln_b, wa.nh, order, r0);
                 else
-                    launch_k(tn_embed_edge_fwd<false>, el.grid, el.block, el.smem, stream, 
-                        w.row_ptr, w.col, geom, w.z32, m->P, m->Q, fv_emb, N, H, w.ias, m->emb_ln_w, m->emb_ln_b, w.nh, order);
+                    launch_k(tn_embed_edge_fwd<false>, el.grid, el.block, el.smem, stream, wa.row_ptr, wa.col, geom, wa.z32,
+                             m->P, m->Q, fv_emb, r1, H, wa.ias, m->emb_ln_w, m->emb_ln_b, wa.nh, order, r0);
                 TMDN_LAUNCH_CHECK();
             }
             GemmP p = gemm_desc(w.nh, H, m->emb_w1, m->emb_b1, w.a1, 2 * H, N, 2 * H, H);
@@ -1368,26 +1401,22 @@ struct TnRun {
             {
                 KTimer ktimer__("tn_msg_fwd", stream);
                 const PersistLaunch pl = persist_launch(tn_msg_fwd_p<128, 1>, tab, N, H, 8, fv_layer[l]);
-                if (pl.ok)
-                    launch_k(tn_msg_fwd_p<128, 1>, pl.grid, pl.block, pl.smem, stream, w.row_ptr, w.col, geom, fv_layer[l],
-                             w.Y[l], N, m->so3, w.M[l], w.tauh, pl.n_hot);
-                else
                 // small systems: 4 slices x 2 edges per thread at 128 registers instead of 8 slices x 1 at 64 -- the same
                 // number of edges in flight per SM, but with 64 registers ptxas reuses the landing registers of the
                 // table rows and an iteration becomes 3-4 dependent round trips instead of one (SASS, r01i)
-                if (tab && N <= LPT_MAX_ROWS) {   // (independent of the lpt_rows knob: the summation order must not depend on it)
-                    // (a CTA per 32-channel slab of a row -- 664 quarter-length CTAs instead of 166 -- was measured slower:
-                    // 32 us against 26 us per launch; the kernel still accepts that launch shape through blockIdx.y)
-                    const EdgeLaunch e4 = edge_launch(N, H, 512);
-                    launch_k(tn_msg_fwd<true, 2, 0, true, 512>, e4.grid, e4.block, e4.smem, stream, w.row_ptr, w.col, geom,
-                             fv_layer[l], w.Y[l], N, H, m->so3, w.M[l], w.tauh, order);
-                }
-                else if (tab)
-                    launch_k(tn_msg_fwd<true>, elf2.grid, elf2.block, elf2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
-                                                                             H, m->so3, w.M[l], w.tauh, order);
+                if (pl.ok)
+                    launch_k(tn_msg_fwd_p<128, 1>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom, fv_layer[l],
+                             wa.Y[l], r1, m->so3, wa.M[l], wa.tauh, pl.n_hot, r0);
+                else if (tab && small_rows) {
+                    const EdgeLaunch e4 = edge_shape(512);
+                    launch_k(tn_msg_fwd<true, 2, 0, true, 512>, e4.grid, e4.block, e4.smem, stream, wa.row_ptr, wa.col, geom,
+                             fv_layer[l], wa.Y[l], r1, H, m->so3, wa.M[l], wa.tauh, order, r0);
+                } else if (tab)
+                    launch_k(tn_msg_fwd<true>, elf2.grid, elf2.block, elf2.smem, stream, wa.row_ptr, wa.col, geom, fv_layer[l],
+                             wa.Y[l], r1, H, m->so3, wa.M[l], wa.tauh, order, r0);
                 else
-                    launch_k(tn_msg_fwd<false>, elf2.grid, elf2.block, elf2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l], N,
-                                                                              H, m->so3, w.M[l], w.tauh, order);
+                    launch_k(tn_msg_fwd<false>, elf2.grid, elf2.block, elf2.smem, stream, wa.row_ptr, wa.col, geom,
+                             fv_layer[l], wa.Y[l], r1, H, m->so3, wa.M[l], wa.tauh, order, r0);
                 TMDN_LAUNCH_CHECK();
             }
             TMDN_TRY(mix_launch(EPI_NONE, mix_batch(w.tauh, w.dX[l], m->layer_mix[l] + 3, N, H), stream));
@@ -1422,9 +1451,9 @@ struct TnRun {
                          H / 2, (const float*)w.h4, act, forces ? w.d4 : (float*)nullptr);
                 TMDN_LAUNCH_CHECK();
             }
-            {
+            if (r1 == (int)n_rows) {   // the molecular sums run in the call that ends the row range (make it the last one)
                 KTimer ktimer__("tn_mol_reduce", stream);
-                launch_k(tn_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy, status);
+                launch_k(tn_mol_reduce, (unsigned)n_mol, 128, 0, stream, wa.e_atom, batch, (int)n_rows, m->mean, energy, status);
                 TMDN_LAUNCH_CHECK();
             }
             if (!forces) return TMDN_OK;
@@ -1434,62 +1463,81 @@ struct TnRun {
             TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
             GemmP q = gemm_desc(w.d3, H, m->out_wT, nullptr, w.dxl, 3 * H, N, 3 * H, H);
             TMDN_TRY(node_gemm1(EPI_NONE, q, stream, m->gemm_mode == TMDN_GEMM_TF32X3));
+            float* dB = dBk(w, 0);
             {
                 KTimer ktimer__("tn_out_norm_bwd", stream);
                 launch_k(tn_out_norm_bwd, rgrid, rblock, 0, stream, w.X[L], m->out_ln_w, w.stat, w.dxl, w.dXa, N, H,
-                         L > 0 ? (const float*)w.dX[L - 1] : (const float*)nullptr, L > 0 ? w.dB : (float*)nullptr);
+                         L > 0 ? (const float*)w.dX[L - 1] : (const float*)nullptr, L > 0 ? dB : (float*)nullptr);
                 TMDN_LAUNCH_CHECK();
             }
-            return L > 0 ? pre_bwd(L - 1, true) : embed_node_bwd();
+            return L > 0 ? pre_bwd(w, N, dB, L - 1) : embed_node_bwd(w, N, dB);
         }
         if (s == TMDN_TN_LAYER_BWD) {
+            const int k_in = L - 1 - l;
+            const float* dM = dBk(wa, k_in);        // gathered over all local atoms
+            float* dB = dBk(w, k_in + 1);           // rows of the next halo point
             {
                 KTimer ktimer__("tn_msg_bwd", stream);
                 const PersistLaunch pl = persist_launch(tn_msg_bwd_p<128, 2>, tab, N, H, 4, fv_layer[l]);
                 if (pl.ok)
-                    launch_k(tn_msg_bwd_p<128, 2>, pl.grid, pl.block, pl.smem, stream, w.row_ptr, w.col, geom, fv_layer[l],
-                             w.Y[l], w.dB, w.dC, w.gpos, N, pl.n_hot);
+                    launch_k(tn_msg_bwd_p<128, 2>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom, fv_layer[l],
+                             wa.Y[l], dM, wa.dC, wa.gpos, r1, pl.n_hot, r0);
                 else if (bwd4)
-                    launch_k(tn_msg_bwd<true, 2, 0, 512, true>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom,
-                             fv_layer[l], w.Y[l], w.dB, w.dC, w.gpos, N, H, order);
+                    launch_k(tn_msg_bwd<true, 2, 0, 512, true>, elb2.grid, elb2.block, elb2.smem, stream, wa.row_ptr, wa.col,
+                             geom, fv_layer[l], wa.Y[l], dM, wa.dC, wa.gpos, r1, H, order, r0);
                 else if (tab)
-                    launch_k(tn_msg_bwd<true>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
-                                                                                w.dB, w.dC, w.gpos, N, H, order);
+                    launch_k(tn_msg_bwd<true>, elb2.grid, elb2.block, elb2.smem, stream, wa.row_ptr, wa.col, geom, fv_layer[l],
+                             wa.Y[l], dM, wa.dC, wa.gpos, r1, H, order, r0);
                 else
-                    launch_k(tn_msg_bwd<false>, elb2.grid, elb2.block, elb2.smem, stream, w.row_ptr, w.col, geom, fv_layer[l], w.Y[l],
-                                                                                 w.dB, w.dC, w.gpos, N, H, order);
+                    launch_k(tn_msg_bwd<false>, elb2.grid, elb2.block, elb2.smem, stream, wa.row_ptr, wa.col, geom, fv_layer[l],
+                             wa.Y[l], dM, wa.dC, wa.gpos, r1, H, order, r0);
                 TMDN_LAUNCH_CHECK();
             }
             GemmBatch b = mix_batch(w.dC, w.dXa, m->layer_mixT[l], N, H);
             for (int g = 0; g < 3; ++g) b.p[g].accumulate = 1;
             TMDN_TRY(mix_launch(EPI_NONE, b, stream));
             if (l > 0) {
-                KTimer ktimer__("tn_normalize_bwd", stream);
-                launch_k(tn_normalize_update_bwd, egrid, 256, 0, stream, w.X[l], w.dXa, w.dX[l - 1], w.dB, NH, H);
-                TMDN_LAUNCH_CHECK();
+                {
+                    KTimer ktimer__("tn_normalize_bwd", stream);
+                    launch_k(tn_normalize_update_bwd, egrid, 256, 0, stream, w.X[l], w.dXa, w.dX[l - 1], dB, NH, H);
+                    TMDN_LAUNCH_CHECK();
+                }
+                return pre_bwd(w, N, dB, l - 1);
             }
-            if (l > 0) return pre_bwd(l - 1, true);
-            return embed_node_bwd(w.X[0]);   // layer 0: the normalise adjoint runs inside tn_embed_scale_bwd
+            return embed_node_bwd(w, N, dB, w.X[0]);   // layer 0: the normalise adjoint runs inside tn_embed_scale_bwd
         }
         // TMDN_TN_FINAL
         TMDN_CHECK_ARG(forces, "tensornet: null forces pointer");
         {
+            const float* Dias = dBk(wa, L);
             KTimer ktimer__("tn_embed_edge_bwd", stream);
             if (tab && H == 128)
-                launch_k(tn_embed_edge_bwd<true, 128>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
-                                                                                   fv_emb, w.dB, w.gpos, forces, N, H, order, status);
+                launch_k(tn_embed_edge_bwd<true, 128>, elb.grid, elb.block, elb.smem, stream, wa.row_ptr, wa.col, geom, wa.z32,
+                         m->P, m->Q, fv_emb, Dias, wa.gpos, forces, r1, H, order, r0, status);
             else if (tab)
-                launch_k(tn_embed_edge_bwd<true>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
-                                                                                   fv_emb, w.dB, w.gpos, forces, N, H, order, status);
+                launch_k(tn_embed_edge_bwd<true>, elb.grid, elb.block, elb.smem, stream, wa.row_ptr, wa.col, geom, wa.z32,
+                         m->P, m->Q, fv_emb, Dias, wa.gpos, forces, r1, H, order, r0, status);
             else
-                launch_k(tn_embed_edge_bwd<false>, elb.grid, elb.block, elb.smem, stream, w.row_ptr, w.col, geom, w.z32, m->P, m->Q,
-                                                                                    fv_emb, w.dB, w.gpos, forces, N, H, order, status);
+                launch_k(tn_embed_edge_bwd<false>, elb.grid, elb.block, elb.smem, stream, wa.row_ptr, wa.col, geom, wa.z32,
+                         m->P, m->Q, fv_emb, Dias, wa.gpos, forces, r1, H, order, r0, status);
             TMDN_LAUNCH_CHECK();
         }
         return TMDN_OK;
     }
 };
 }  // namespace
+
+extern "C" int tmdn_tensornet_stage_rows(const tmdn_tensornet_model* m, int stage, int layer, const int64_t* z,
+                                         const float* pos, const int64_t* batch, int64_t n_atoms, int64_t n_rows,
+                                         int64_t row_begin, int64_t row_end, int64_t n_mol, const double box[9],
+                                         int use_periodic, int strategy, int64_t max_edges, float* energy, float* forces,
+                                         int32_t* status, void* workspace, size_t workspace_bytes, tmdn_stream_t stream_) {
+    TnRun r{m, z, pos, batch, n_atoms, n_rows, n_mol, max_edges, box, use_periodic, strategy, energy, forces, status,
+            (cudaStream_t)stream_};
+    TMDN_TRY(r.init(workspace, workspace_bytes));
+    if (stage == TMDN_TN_GRAPH) return r.stage(TMDN_TN_GRAPH, 0, 0, n_rows);
+    return r.stage(stage, layer, row_begin, row_end);
+}
 
 extern "C" int tmdn_tensornet_stage(const tmdn_tensornet_model* m, int stage, int layer, const int64_t* z,
                                     const float* pos, const int64_t* batch, int64_t n_atoms, int64_t n_rows,
@@ -1499,7 +1547,8 @@ extern "C" int tmdn_tensornet_stage(const tmdn_tensornet_model* m, int stage, in
     TnRun r{m, z, pos, batch, n_atoms, n_rows, n_mol, max_edges, box, use_periodic, strategy, energy, forces, status,
             (cudaStream_t)stream_};
     TMDN_TRY(r.init(workspace, workspace_bytes));
-    return r.stage(stage, layer);
+    if (stage == TMDN_TN_EMBED) TMDN_TRY(r.stage(TMDN_TN_GRAPH, 0, 0, n_rows));   // whole-range form: graph + embedding
+    return r.stage(stage, layer, 0, n_rows);
 }
 
 extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const int64_t* z, const float* pos,
@@ -1512,12 +1561,14 @@ extern "C" int tmdn_tensornet_energy_forces(const tmdn_tensornet_model* m, const
             (cudaStream_t)stream_};
     TMDN_TRY(r.init(workspace, workspace_bytes));
     const int L = m->num_layers;
-    TMDN_TRY(r.stage(TMDN_TN_EMBED, 0));
-    for (int l = 0; l < L; ++l) TMDN_TRY(r.stage(TMDN_TN_LAYER_FWD, l));
-    TMDN_TRY(r.stage(TMDN_TN_HEAD, 0));
+    const int64_t N = n_atoms;
+    TMDN_TRY(r.stage(TMDN_TN_GRAPH, 0, 0, N));
+    TMDN_TRY(r.stage(TMDN_TN_EMBED, 0, 0, N));
+    for (int l = 0; l < L; ++l) TMDN_TRY(r.stage(TMDN_TN_LAYER_FWD, l, 0, N));
+    TMDN_TRY(r.stage(TMDN_TN_HEAD, 0, 0, N));
     if (!forces) return TMDN_OK;
-    for (int l = L - 1; l >= 0; --l) TMDN_TRY(r.stage(TMDN_TN_LAYER_BWD, l));
-    return r.stage(TMDN_TN_FINAL, 0);
+    for (int l = L - 1; l >= 0; --l) TMDN_TRY(r.stage(TMDN_TN_LAYER_BWD, l, 0, N));
+    return r.stage(TMDN_TN_FINAL, 0, 0, N);
 }
 
 extern "C" int tmdn_channel_mix_f32(const float* x, const float* w, float* y, int64_t n_atoms, int H, int accumulate,

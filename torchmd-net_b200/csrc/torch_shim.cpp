@@ -522,6 +522,49 @@ void tensornet_stage(int64_t handle, int64_t stage, int64_t layer, const Tensor&
                                    cur_stream()));
 }
 
+// One stage over the owned rows [row_begin, row_end) (include/tmdn.h: tmdn_tensornet_stage_rows).
+void tensornet_stage_rows(int64_t handle, int64_t stage, int64_t layer, const Tensor& z, const Tensor& pos, const Tensor& batch,
+                          int64_t n_rows, int64_t row_begin, int64_t row_end, const Tensor& box_vectors, bool use_periodic,
+                          const std::string& strategy, int64_t max_edges, int64_t n_mol, Tensor energy, Tensor forces,
+                          Tensor status, Tensor workspace) {
+    auto h = tn_get(handle);
+    TORCH_CHECK(pos.is_cuda() && pos.scalar_type() == at::kFloat && pos.is_contiguous() && pos.dim() == 2 &&
+                    pos.size(1) == 3, "tensornet_stage_rows: pos must be a contiguous CUDA float32 [N,3] tensor");
+    TORCH_CHECK(z.scalar_type() == at::kLong && z.is_contiguous() && z.size(0) == pos.size(0) &&
+                    batch.scalar_type() == at::kLong && batch.is_contiguous() && batch.size(0) == pos.size(0),
+                "tensornet_stage_rows: z / batch must be contiguous int64 [N] tensors");
+    TORCH_CHECK(energy.is_cuda() && energy.scalar_type() == at::kFloat && energy.numel() >= n_mol &&
+                    status.scalar_type() == at::kInt && status.numel() >= 4 && workspace.scalar_type() == at::kByte,
+                "tensornet_stage_rows: bad output tensors");
+    TORCH_CHECK(!forces.defined() || forces.numel() == 0 ||
+                    (forces.scalar_type() == at::kFloat && forces.is_contiguous() && forces.numel() >= 3 * n_rows),
+                "tensornet_stage_rows: forces must be a contiguous float32 [n_rows,3] tensor");
+    const c10::cuda::CUDAGuard guard(pos.device());
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    float* fptr_ = (forces.defined() && forces.numel() > 0) ? forces.data_ptr<float>() : nullptr;
+    TMDN_CALL(tmdn_tensornet_stage_rows(&h->m, (int)stage, (int)layer, z.data_ptr<int64_t>(), pos.data_ptr<float>(),
+                                        batch.data_ptr<int64_t>(), pos.size(0), n_rows, row_begin, row_end, n_mol,
+                                        have_box ? box : nullptr, use_periodic, strategy_id(strategy), max_edges,
+                                        energy.data_ptr<float>(), fptr_, status.data_ptr<int32_t>(), workspace.data_ptr(),
+                                        (size_t)workspace.numel(), cur_stream()));
+}
+
+// Rows idx[seg[p]..seg[p+1]) of src -> the peer address dst[p] (device pointers into other GPUs' memory, as int64)
+void halo_push(const Tensor& src, const Tensor& idx, const Tensor& seg, const Tensor& dst) {
+    TORCH_CHECK(src.is_cuda() && src.scalar_type() == at::kFloat && src.is_contiguous() && src.dim() == 2,
+                "halo_push: src must be a contiguous CUDA float32 [n,row] tensor");
+    TORCH_CHECK(idx.is_cuda() && idx.scalar_type() == at::kInt && idx.is_contiguous(), "halo_push: idx must be int32");
+    TORCH_CHECK(seg.is_cuda() && seg.scalar_type() == at::kLong && seg.is_contiguous() && seg.numel() >= 2,
+                "halo_push: seg must be a CUDA int64 [n_peers+1] tensor");
+    TORCH_CHECK(dst.is_cuda() && dst.scalar_type() == at::kLong && dst.is_contiguous() && dst.numel() == seg.numel() - 1,
+                "halo_push: dst must be a CUDA int64 [n_peers] tensor of device pointers");
+    const c10::cuda::CUDAGuard guard(src.device());
+    TMDN_CALL(tmdn_halo_push_f32(src.data_ptr<float>(), idx.data_ptr<int32_t>(), seg.data_ptr<int64_t>(),
+                                 reinterpret_cast<float* const*>(dst.data_ptr<int64_t>()), (int)dst.numel(), idx.numel(),
+                                 src.size(1), cur_stream()));
+}
+
 // out[r,:] = src[idx[r],:]
 Tensor halo_pack(const Tensor& src, const Tensor& idx) {
     TORCH_CHECK(src.is_cuda() && src.scalar_type() == at::kFloat && src.is_contiguous() && src.dim() == 2,
@@ -621,7 +664,11 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
     m.def("tensornet_stage(int handle, int stage, int layer, Tensor z, Tensor pos, Tensor batch, int n_rows, "
           "Tensor box_vectors, bool use_periodic, str strategy, int max_edges, int n_mol, Tensor(a!) energy, "
           "Tensor(b!) forces, Tensor(c!) status, Tensor(d!) workspace) -> ()", tensornet_stage);
+    m.def("tensornet_stage_rows(int handle, int stage, int layer, Tensor z, Tensor pos, Tensor batch, int n_rows, "
+          "int row_begin, int row_end, Tensor box_vectors, bool use_periodic, str strategy, int max_edges, int n_mol, "
+          "Tensor(a!) energy, Tensor(b!) forces, Tensor(c!) status, Tensor(d!) workspace) -> ()", tensornet_stage_rows);
     m.def("halo_pack(Tensor src, Tensor idx) -> Tensor", halo_pack);
+    m.def("halo_push(Tensor src, Tensor idx, Tensor seg, Tensor dst) -> ()", halo_push);
     m.def("channel_mix(Tensor x, Tensor w, Tensor? y, bool accumulate) -> Tensor", channel_mix);
     m.def("node_gemm(Tensor a, Tensor w, Tensor? bias, Tensor? c, bool accumulate) -> Tensor", node_gemm);
     m.def("launch_count() -> int", launch_count);
