@@ -11,6 +11,10 @@ One "step" = one energy+force evaluation (neighbour search included) of the work
   water     (configs[3], single-GPU slice): TensorNet-ANI1X hparams, periodic water box, cell-list neighbours.
 With --gpus N > 1 (torchrun, one rank per GPU) every rank evaluates its own shard / replica with no collective in
 the step (molecules and replicas are independent): weak scaling, value = N * atoms / max-over-ranks step time.
+Every run of the default workload ALSO evaluates configs[3] on all N GPUs together -- one 1 029 000-atom periodic water
+box, monolithic at N = 1, brick-decomposed with halo exchange over NVLink at N > 1 -- and reports it as the
+"strong_scaling" object of the same JSON line (ms_per_step, atom-steps/s, ghost atoms, halo bytes / duration / exposed
+time, launches, roofline of tn_msg_bwd, and the decomposed result checked against rank 0's monolithic evaluation).
 
 Timing: W >= 3 warm-up steps; L2 is flushed (a 512 MiB write) before every timed step, outside the timed span;
 each step is bracketed by CUDA events on the launching stream; ms_per_step = sum of the K spans / K, max over
@@ -134,7 +138,7 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------- CPU (reference) arm
-def cpu_reference_steps(workload, hp, args, steps, warmup):
+def cpu_reference_steps(workload, hp, args, steps, warmup, wall_budget_s=0.0):
     """Times oracle/model.py (the CPU restatement of the reference's PyTorch path, pinned to the reference's
     goldens) on all host threads.  -> (atom-steps/s, cores, sample description)."""
     from oracle import model as om
@@ -155,15 +159,20 @@ def cpu_reference_steps(workload, hp, args, steps, warmup):
         sample = "a 1536-atom periodic box (8^3 waters) per step"
     tz, tb = torch.from_numpy(z), torch.from_numpy(batch)
     tbox = None if box is None else torch.from_numpy(box)
-    poss = step_positions(pos0, steps + warmup, 2)
     times = []
-    for i, p in enumerate(poss):
+    t_start = time.perf_counter()
+    for i in range(steps + warmup):
+        p = S.md_step_noise(pos0, i, seed=2)
         t0 = time.perf_counter()
         om.energy_forces(sd, hp, tz, torch.from_numpy(p), tb, box=tbox)
         if i >= warmup:
             times.append(time.perf_counter() - t0)
+        # bounded sample: the requested step count is honoured unless the wall budget runs out first
+        if wall_budget_s and times and time.perf_counter() - t_start > wall_budget_s:
+            break
     per = sum(times) / len(times)
-    return z.shape[0] / per, cores, "%s, %d timed step(s) after %d warm-up, %.3f s/step" % (sample, steps, warmup, per), per
+    return (z.shape[0] / per, cores, "%s, %d timed step(s) after %d warm-up, %.3f s/step" % (sample, len(times), warmup, per),
+            per, len(times))
 
 
 def run_reference(args):
@@ -171,13 +180,17 @@ def run_reference(args):
     if rank != 0:
         return
     hp = HPARAMS[args.workload]
-    steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
-    v, cores, sample, per = cpu_reference_steps(args.workload, hp, args, steps, warmup)
+    # --steps / --warmup are honoured; a wall budget (not a step cap) keeps the run within a few minutes
+    warmup = max(1, args.warmup)
+    v, cores, sample, per, steps = cpu_reference_steps(args.workload, hp, args, max(1, args.steps), warmup, wall_budget_s=150.0)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": warmup, "ms_per_step": per * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD_DESC[args.workload], "device": "host CPU, %d threads" % cores},
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                             "note": "oracle/model.py: the CPU restatement of the reference's PyTorch path (pinned to its "
+                                     "goldens), not the reference package itself, which cannot be installed here (DESIGN.md 2); "
+                                     "the survey measured the reference's own code at 0.97 s/step on 8 threads"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
@@ -230,91 +243,207 @@ def profile_families(run_step, steps):
     return fam
 
 
-# ------------------------------------------------------------------------------------------- decomposed arm
-def run_decomposed(args, model, hp, dev, rank, world, local):
-    """--workload water with N > 1 ranks: ONE periodic box, slab decomposition, halo exchange over NCCL
-    (torchmdnet/distributed.py).  Strong scaling: the box is fixed, value = total atoms / max-over-ranks step time."""
+# ------------------------------------------------------------------------------------------- strong-scaling arm
+def strong_scaling(args, dev, rank, world, local):
+    """BASELINE.json configs[3]: ONE periodic water box (TensorNet-ANI1X hparams, --strong-side^3 molecules; default
+    70 -> 1 029 000 atoms), energy + forces.  N = 1: the monolithic call.  N > 1: brick decomposition over N GPUs
+    (torchmdnet/distributed.py), halo exchange overlapped with the interior rows; the result is checked inside the
+    bench against rank 0's monolithic evaluation of the same positions (north_star tolerances).  Strong scaling: the
+    box is fixed, value = atoms / max-over-ranks step time.  -> dict on rank 0, None elsewhere."""
     import torch.distributed as dist
-    from torchmdnet.distributed import DecomposedTensorNet, slab_plans
-    model.representation_model.filter_mode = args.filter
-    z_np, pos0, _, box = S.water_box(args.water_side, seed=4)
+    from torchmdnet.distributed import DecomposedTensorNet, domain_plans
+    from torchmdnet.models.model import create_model
+    from torchmdnet.models.utils import OptimizedDistance
+    hp = HPARAMS["water"]
+    H, L = hp["embedding_dimension"], hp["num_layers"]
+    seed_everything(1234)
+    model = create_model(hp).to(dev).eval()
+    rm = model.representation_model
+    rm.filter_mode = "table"
+    z_np, pos0, batch_np, box = S.water_box(args.strong_side, seed=4)
     N = z_np.shape[0]
-    K, W = args.steps, args.warmup
-    n_pos = min(K + W, 16)
-    plans = slab_plans(torch.from_numpy(pos0), torch.from_numpy(box), hp["cutoff_upper"], world, skin=0.5)
-    runner = DecomposedTensorNet(model, plans, rank, torch.from_numpy(z_np), torch.from_numpy(box), dev)
-    own = plans[rank].own
-    poss_np = [S.md_step_noise(pos0, i, seed=2)[own.numpy()] for i in range(n_pos)]
-    poss = torch.stack([torch.from_numpy(p) for p in poss_np]).to(dev)
+    K, W = max(1, min(args.steps, args.strong_steps)), 3
+    n_pos = 4
+    tbox = torch.from_numpy(box)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
-    for i in range(W):
-        runner.step(poss[i % n_pos])
-    torch.cuda.synchronize()
-    c0 = torch.ops.torchmdnet_b200.launch_count()
-    runner.step(poss[0])
-    torch.cuda.synchronize()
-    launches_per_step = torch.ops.torchmdnet_b200.launch_count() - c0
-    sampler = ClockSampler(local) if rank == 0 else None
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    dist.barrier()
-    torch.cuda.synchronize()
-    t_begin = time.perf_counter()
-    for i in range(K):
-        flush.zero_()
-        ev[i][0].record()
-        runner.step(poss[(W + i) % n_pos])
-        e_tot = runner.total_energy()
-        ev[i][1].record()
-    dist.barrier()
-    torch.cuda.synchronize()
-    t_end = time.perf_counter()
-    clocks = sampler.stop(t_begin, t_end) if sampler else None
-    spans = [a.elapsed_time(b) for a, b in ev]
-    if os.environ.get("TMDN_BENCH_SPANS"):
-        print("rank %d spans ms: %s" % (rank, " ".join("%.2f" % x for x in spans)), file=sys.stderr, flush=True)
-    t = torch.tensor([sum(spans)], device=dev, dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_per_step = float(t) / K
-    # e2e: pinned host positions of the owned atoms in, host forces of the owned atoms + total energy out
-    host_pos = [torch.from_numpy(p).pin_memory() for p in poss_np]
-    h_f = torch.empty(len(own), 3).pin_memory()
-    h_e = torch.empty(1, 1).pin_memory()
-    dpos = torch.empty(len(own), 3, device=dev)
-    e2e_t = 0.0
-    for i in range(W + K):
-        flush.zero_()
-        dist.barrier()
+    ops = torch.ops.torchmdnet_b200
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
         torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        dpos.copy_(host_pos[i % n_pos], non_blocking=True)
-        runner.step(dpos)
-        h_e.copy_(runner.total_energy(), non_blocking=True)
-        h_f.copy_(runner.forces, non_blocking=True)
+
+    def timed(step_fn, k, w):
+        for i in range(w):
+            step_fn(i)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k)]
+        barrier()
+        for i in range(k):
+            flush.zero_()
+            if world > 1:
+                dist.barrier()          # every rank starts the step together (device-side: NCCL on the current stream)
+            ev[i][0].record()
+            step_fn(w + i)
+            ev[i][1].record()
+        barrier()
+        t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t) / k
+
+    def monolithic():
+        rm.distance = OptimizedDistance(hp["cutoff_lower"], hp["cutoff_upper"], max_num_pairs=-hp["max_num_neighbors"],
+                                        return_vecs=True, loop=True, check_errors=False, resize_to_fit=False, box=tbox,
+                                        strategy="cell")
+        return torch.from_numpy(z_np).to(dev), torch.from_numpy(batch_np).to(dev)
+
+    out = {"atoms_total": N, "workload": WORKLOAD_DESC["water"], "box_A": float(box[0, 0]), "n_gpus": world,
+           "steps": K, "warmup": W, "l2": "flushed (512 MiB write) before every timed step"}
+    if world == 1:
+        z, batch = monolithic()
+        poss = torch.stack([torch.from_numpy(S.md_step_noise(pos0, i, seed=2)) for i in range(n_pos)]).to(dev)
+
+        def step(i):
+            return model(z, poss[i % n_pos], batch)
+        step(0)
         torch.cuda.synchronize()
-        if i >= W:
-            e2e_t += time.perf_counter() - t0
-    t = torch.tensor([e2e_t], device=dev, dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    stat = runner.status.cpu()
-    ghosts = torch.tensor([plans[rank].n_local - plans[rank].n_own], device=dev)
-    dist.all_reduce(ghosts, op=dist.ReduceOp.MAX)
-    assert int(stat[1]) == 0, "pair capacity exceeded"
+        c0 = ops.launch_count()
+        y, f = step(0)
+        torch.cuda.synchronize()
+        launches = ops.launch_count() - c0
+        status = rm.energy_forces(z, poss[0], batch, 1, model.output_model, *model._mean_std())[2].cpu()
+        assert status[1:].tolist() == [0, 0, 0], "bad status %s" % status.tolist()
+        E = int(status[0])
+        ms = timed(step, K, W)
+        fam = profile_families(step, 2)
+        out.update({"ms_per_step": ms, "value": N / (ms * 1e-3), "unit": UNIT, "parallelism": "one GPU, monolithic call",
+                    "ghost_atoms_max": 0, "halo_bytes_per_step": 0, "halo_ms_per_step": 0.0,
+                    "halo_exposed_ms_per_step": 0.0, "launches_per_step": int(launches), "edges": E,
+                    "correctness": {"reference": "this IS the monolithic evaluation", "max_abs_dF": 0.0, "rel_dE": 0.0},
+                    "energy": float(y)})
+        n_own, n_prof = N, 2
+    else:
+        grid = tuple(int(x) for x in args.grid.split("x")) if args.grid else None
+        plans = domain_plans(torch.from_numpy(pos0), tbox, hp["cutoff_upper"], world, skin=0.5, grid=grid)
+        plan = plans[rank]
+        transport, note = args.transport, None
+        try:
+            runner = DecomposedTensorNet(model, plans, rank, torch.from_numpy(z_np), tbox, dev, transport=transport)
+        except Exception as exc:            # symmetric memory unavailable on this box: NCCL transport
+            if transport != "peer":
+                raise
+            note = "peer transport unavailable (%s: %s); NCCL send/recv used" % (type(exc).__name__, str(exc)[:120])
+            transport = "nccl"
+            runner = DecomposedTensorNet(model, plans, rank, torch.from_numpy(z_np), tbox, dev, transport=transport)
+        own = plan.own
+        poss = torch.stack([torch.from_numpy(S.md_step_noise(pos0, i, seed=2)[own.numpy()]) for i in range(n_pos)]).to(dev)
+
+        def step(i):
+            runner.step(poss[i % n_pos])
+            return runner.total_energy()
+        step(0)
+        torch.cuda.synchronize()
+        c0 = ops.launch_count()
+        step(0)
+        torch.cuda.synchronize()
+        launches = ops.launch_count() - c0
+        assert runner.status.cpu()[1:].tolist() == [0, 0, 0], "bad status on rank %d" % rank
+        ms = timed(step, K, W)
+        # exchange durations: CUDA events around the pack + transfer of every halo point (communication stream)
+        runner.exchange_events = []
+        step(0)
+        step(1)
+        torch.cuda.synchronize()
+        ex = runner.exchange_report()
+        runner.exchange_events = None
+        halo_ms = torch.tensor([sum(r["transfer_ms"] for r in ex) / 2, sum(r.get("exposed_ms", 0.0) for r in ex) / 2],
+                               device=dev, dtype=torch.float64)
+        dist.all_reduce(halo_ms, op=dist.ReduceOp.MAX)
+        per_point = {}
+        for r in ex:
+            d = per_point.setdefault(r["name"], {"transfer_ms": 0.0, "exposed_ms": 0.0})
+            d["transfer_ms"] += r["transfer_ms"] / 2
+            d["exposed_ms"] += r.get("exposed_ms", 0.0) / 2
+        # exposed part: the same step with the exchanges switched off (ghost rows keep stale values: timing only)
+        halo_obj = runner.halo
+        runner.halo = type("NoExchange", (), {"start": lambda self, b, n="": None, "finish": lambda self, b, n="": None})()
+        ms_noex = timed(step, K, 1)
+        runner.halo = halo_obj
+        step(0)                                       # a valid state again
+        fam = profile_families(step, 2)
+        rows_sent, n_points = runner.halo_rows_per_step()
+        gh = torch.tensor([plan.n_ghost, plan.n_boundary, rows_sent], device=dev)
+        dist.all_reduce(gh, op=dist.ReduceOp.MAX)
+        # ---- correctness against the monolithic evaluation on rank 0 (same positions)
+        runner.step(poss[0])
+        e_dec = runner.total_energy().clone()
+        f_own = runner.forces.clone()
+        sizes = [p.n_own for p in plans]
+        pad = max(sizes)
+        fbuf = torch.zeros(pad, 3, device=dev)
+        fbuf[:plan.n_own] = f_own
+        gathered = [torch.zeros(pad, 3, device=dev) for _ in range(world)] if rank == 0 else None
+        dist.gather(fbuf, gathered, dst=0)
+        E = int(runner.status[0])
+        et = torch.tensor([E], device=dev)
+        dist.all_reduce(et)
+        del runner, halo_obj
+        torch.cuda.empty_cache()
+        corr = None
+        if rank == 0:
+            f_dec = torch.zeros(N, 3, device=dev)
+            for p, t in zip(plans, gathered):
+                f_dec[p.own.to(dev)] = t[:p.n_own]
+            del gathered
+            z, batch = monolithic()
+            y_ref, f_ref = model(z, torch.from_numpy(S.md_step_noise(pos0, 0, seed=2)).to(dev), batch)
+            d_f = float((f_dec - f_ref).abs().max())
+            d_e = float((e_dec - y_ref).abs().max()) / max(1.0, float(y_ref.abs().max()))
+            corr = {"reference": "rank 0 monolithic evaluation of the same positions", "max_abs_dF": d_f, "rel_dE": d_e,
+                    "tolerance": {"max_abs_dF": 1e-4, "rel_dE": 1e-5}, "energy_decomposed": float(e_dec),
+                    "energy_monolithic": float(y_ref)}
+            assert d_f <= 1e-4 and d_e <= 1e-5, "decomposed result differs from the monolithic one: %s" % corr
+        barrier()
+        out.update({"ms_per_step": ms, "value": N / (ms * 1e-3), "unit": UNIT,
+                    "parallelism": "%dx%dx%d bricks, %d halo points of [rows,9,%d] fp32 + positions per step, transport %s, "
+                                   "boundary rows first and the exchange overlapped with the interior rows; one scalar "
+                                   "all-reduce" % (plans[0].grid + (n_points, H, transport)),
+                    "transport": transport, "transport_note": note, "grid": list(plans[0].grid),
+                    "ghost_atoms_max": int(gh[0]), "boundary_atoms_max": int(gh[1]),
+                    "halo_bytes_per_step": int(gh[2]) * (12 + n_points * 36 * H),
+                    "halo_ms_per_step": float(halo_ms[0]), "halo_exposed_ms_per_step": float(halo_ms[1]),
+                    "halo_per_point_rank0": per_point, "ms_per_step_without_exchange": ms_noex,
+                    "ms_per_step_minus_without_exchange": ms - ms_noex, "launches_per_step": int(launches),
+                    "halo_note": "halo_ms = pack + transfer time on the communication stream (CUDA events, max over ranks); "
+                                 "exposed = the part of each exchange (incl. its completion barrier) that ended after the "
+                                 "interior rows of the producing stage were done, plus the positions halo",
+                    "edges": int(et), "correctness": corr})
+        n_own, n_prof = plan.n_own, 2
+        E = int(et) // world
     if rank != 0:
-        return
-    H = hp["embedding_dimension"]
-    line = {"metric": METRIC, "value": N / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_DESC["water"], "atoms_total": N, "atoms_per_gpu": N // world,
-                       "max_ghost_atoms_per_gpu": int(ghosts), "filter_mode": args.filter, "neighbor_strategy": "cell",
-                       "l2": "flushed (512 MiB write) before every timed step",
-                       "parallelism": "slab decomposition, %d halo exchanges of [ghosts,9,%d] fp32 rows per step over "
-                                      "NCCL send/recv + one scalar all-reduce" % (2 * hp["num_layers"] + 2, H)},
-            "e2e": {"value": N / (float(t) / K), "unit": UNIT, "h2d_bytes_per_step": N * 12,
-                    "d2h_bytes_per_step": N * 12 + 4, "api": "torchmdnet.distributed.DecomposedTensorNet.step"},
-            "gpu_launches": int(launches_per_step) * K * world, "launches_per_step": int(launches_per_step),
-            "clocks": clocks, "roofline": None, "cpu_baseline": None, "energy_checksum": float(e_tot)}
-    emit(line)
+        return None
+    if "tn_msg_bwd" in fam:
+        cnt, tms = fam["tn_msg_bwd"]
+        bpl = algorithmic_bytes("tn_msg_bwd", n_own, E, H, L)
+        peak = hbm_peak()
+        ach = bpl / (tms / cnt * 1e-3) / 1e9
+        out["roofline"] = {"bound": "hbm", "kernel": "tn_msg_bwd", "achieved": ach, "peak": peak[0], "unit": "GB/s",
+                           "frac": ach / peak[0], "traffic": None, "peak_source": peak[1],
+                           "algorithmic_bytes_per_launch": bpl, "avg_launch_us": tms / cnt * 1e3,
+                           "l2_bytes_per_launch": l2_bytes("tn_msg_bwd", E, H),
+                           "note": "rank 0's launches (all rows of one stage = boundary + interior launch); CUDA events "
+                                   "inside the library over %d eager steps" % n_prof}
+    out["kernel_families"] = {k: {"launches_per_step": c / n_prof, "us_per_step": m_ / n_prof * 1e3} for k, (c, m_) in
+                              sorted(fam.items(), key=lambda kv: -kv[1][1])[:8]}
+    return out
+
+
+def hbm_peak():
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        with open(peaks_path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
+    return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
 
 
 # ------------------------------------------------------------------------------------------- main arm
@@ -334,6 +463,13 @@ def main():
     ap.add_argument("--water-order", default="raster", choices=["raster", "morton", "shuffle"],
                     help="index order of the synthetic water molecules (raster = lattice order)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true",
+                    help="skip the strong-scaling arm (the 1 M-atom periodic water box evaluated on all N GPUs together)")
+    ap.add_argument("--strong-side", type=int, default=70, help="water molecules per box edge of the strong-scaling arm (70 -> 1 029 000 atoms)")
+    ap.add_argument("--strong-steps", type=int, default=5, help="timed steps of the strong-scaling arm (<= --steps)")
+    ap.add_argument("--transport", default="peer", choices=["peer", "nccl"],
+                    help="halo transport of the decomposed step: fused pack+push kernel over NVLink peer memory, or NCCL send/recv")
+    ap.add_argument("--grid", default="", help="brick grid of the decomposed step, e.g. 2x2x2 (default: smallest ghost volume)")
     ap.add_argument("--no-flush", action="store_true",
                     help="experiment only: do not flush L2 between the timed steps of `value` (the line says so; not a bench number)")
     ap.add_argument("--table-intervals", type=int, default=0,
@@ -366,8 +502,20 @@ def main():
     hp = HPARAMS[args.workload]
     seed_everything(1234)
     model = create_model(hp).to(dev).eval()
-    if args.workload == "water" and world > 1:
-        return run_decomposed(args, model, hp, dev, rank, world, local)
+    if args.workload == "water" and world > 1:      # one box on all GPUs: the strong-scaling arm IS the line
+        del model
+        args.strong_side, args.strong_steps = args.water_side, args.steps
+        ss = strong_scaling(args, dev, rank, world, local)
+        if rank == 0:
+            emit({"metric": METRIC, "value": ss["value"], "unit": UNIT, "n_gpus": world, "steps": ss["steps"],
+                  "warmup": ss["warmup"], "ms_per_step": ss["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+                  "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                  "config": {"workload": WORKLOAD_DESC["water"], "atoms_total": ss["atoms_total"],
+                             "parallelism": ss["parallelism"], "l2": ss["l2"]},
+                  "e2e": None, "gpu_launches": ss["launches_per_step"] * ss["steps"] * world,
+                  "launches_per_step": ss["launches_per_step"], "roofline": ss.get("roofline"), "cpu_baseline": None,
+                  "strong_scaling": ss})
+        return
     rm = model.representation_model
     rm.gemm_mode = args.et_gemm
     if hp["model"] == "tensornet":
@@ -498,6 +646,11 @@ def main():
     # the e2e result must be the product's result
     assert torch.allclose(h_f, calc.calculate(host_pos[(W + Ke - 1) % n_pos], None)[1].view(N, 3).cpu())
 
+    # ---- strong-scaling arm: the 1 M-atom periodic box on all N GPUs together (every rank takes part)
+    strong = None
+    if args.workload == "chignolin" and not args.no_strong:
+        strong = strong_scaling(args, dev, rank, world, local)
+        torch.cuda.set_device(local)
     if rank != 0:
         return
     # ---- per-kernel-family device times (separate eager pass, events inside the library) -> roofline
@@ -512,12 +665,7 @@ def main():
     H, L = hp["embedding_dimension"], hp["num_layers"]
     bytes_per_launch = algorithmic_bytes(dom, N, E, H, L)
     achieved = bytes_per_launch / (ms / cnt * 1e-3) / 1e9
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        with open(peaks_path) as fh:
-            peak, peak_src = float(json.load(fh)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
-    else:
-        peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+    peak, peak_src = hbm_peak()
     cap = ncu_capture("%s:%d" % (args.workload, N), dom)
     l2b = l2_bytes(dom, E, H)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -539,7 +687,7 @@ def main():
 
     cpu = None
     if not args.no_cpu_baseline and world == 1:
-        v, cores, sample, _ = cpu_reference_steps(args.workload, hp, args, 3, 1)
+        v, cores, sample, _, _ = cpu_reference_steps(args.workload, hp, args, 3, 1)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
@@ -557,7 +705,7 @@ def main():
                     "d2h_bytes_per_step": N * 12 + n_mol * 4, "api": "torchmdnet.calculators.External.calculate"},
             "gpu_launches": int(launches_per_step) * K, "launches_per_step": int(launches_per_step),
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "kernel_families": families,
-            "energy_checksum": float(gy.double().sum())}
+            "energy_checksum": float(gy.double().sum()), "strong_scaling": strong}
     emit(line)
 
 

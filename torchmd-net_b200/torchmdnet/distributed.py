@@ -334,7 +334,7 @@ class DecomposedTensorNet:
         self.forces = torch.zeros(p.n_own, 3, device=self.device)
         self.status = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.comm_stream = torch.cuda.Stream(device=self.device) if self.overlap else None
-        self.exchange_events = None     # set to [] to record (start, end) CUDA events around every exchange
+        self.exchange_events = None     # set to [] to record CUDA events around every exchange (exchange_report)
 
     def __del__(self):
         try:
@@ -404,18 +404,25 @@ class DecomposedTensorNet:
                 yield self._buffer(g.produces), g.produces
 
     def _exchange_begin(self, buf, name):
-        if self.exchange_events is not None:
+        """pack + transfer on the current (communication) stream; with ``exchange_events`` set, CUDA events bracket it"""
+        rec = self.exchange_events is not None
+        if rec:
             e0 = torch.cuda.Event(enable_timing=True)
             e0.record()
-            self._ev0 = e0
         self.halo.start(buf, name)
-
-    def _exchange_end(self, buf, name):
-        self.halo.finish(buf, name)
-        if self.exchange_events is not None:
+        if rec:
             e1 = torch.cuda.Event(enable_timing=True)
             e1.record()
-            self.exchange_events.append((name, self._ev0, e1, buf.shape[1] * 4))
+            self.exchange_events.append({"name": name, "start": e0, "sent": e1, "row_bytes": buf.shape[1] * 4})
+
+    def _exchange_end(self, buf, name, interior_done=None):
+        """completion (peer transport: the cross-rank barrier).  ``interior_done``: event recorded on the compute stream
+        after the interior rows -- the part of the exchange that ends after it is what the overlap did not hide."""
+        self.halo.finish(buf, name)
+        if self.exchange_events is not None:
+            e2 = torch.cuda.Event(enable_timing=True)
+            e2.record()
+            self.exchange_events[-1].update(done=e2, interior_done=interior_done)
 
     def step(self, pos_own: torch.Tensor):
         """-> (sum of the owned atoms' energies [1,1] (no mean), forces of the owned atoms [n_own,3])."""
@@ -449,13 +456,13 @@ class DecomposedTensorNet:
                     self._exchange_begin(buf, g.produces)       # in flight during the interior rows
             self._run_group(g, nb, p.n_own, False)
             if g.produces is not None:
-                ev_i = torch.cuda.Event()
+                ev_i = torch.cuda.Event(enable_timing=self.exchange_events is not None)
                 ev_i.record(cs)
                 with torch.cuda.stream(ms):
                     # completion is only signalled once the local readers of the buffer this halo point's successor will
                     # overwrite are done (the ping-pong argument of include/tmdn.h needs every rank past its interior rows)
                     ms.wait_event(ev_i)
-                    self._exchange_end(buf, g.produces)
+                    self._exchange_end(buf, g.produces, ev_i)
                     ev_c = torch.cuda.Event()
                     ev_c.record(ms)
                 cs.wait_event(ev_c)
@@ -468,6 +475,19 @@ class DecomposedTensorNet:
         if self.plan.world > 1:
             dist.all_reduce(e, group=group)
         return e + self.model._mean_std()[0]
+
+    def exchange_report(self):
+        """From the recorded events (after a synchronize): per halo point the duration of pack + transfer on the
+        communication stream and the part of the exchange that ended after the interior rows were done (exposed)."""
+        rows = []
+        for e in self.exchange_events or []:
+            r = {"name": e["name"], "transfer_ms": e["start"].elapsed_time(e["sent"])}
+            if e.get("interior_done") is not None:
+                r["exposed_ms"] = max(0.0, e["interior_done"].elapsed_time(e["done"]))
+            elif "done" in e:
+                r["exposed_ms"] = e["start"].elapsed_time(e["done"])         # not overlapped: all of it is exposed
+            rows.append(r)
+        return rows
 
     def halo_rows_per_step(self):
         """(rows sent per halo point, number of node-row halo points): bytes = rows * (12 + n_points * 36 * H)"""
