@@ -35,12 +35,59 @@ def timed(fn, flush, reps=10, warm=3):
     return float(np.median(ts))
 
 
+def reference_sweep(args):
+    """The same cases through torch.ops.torchmdnet_neighbors.get_neighbor_pairs of the reference's CUDA op.  Runs in a
+    process that never loads the product's shim (both register the same op name).  Bench infrastructure only."""
+    lib = os.path.join(ROOT, "oracle", "_ref", "torchmdnet_neighbors_ref_cuda.so")
+    if not os.path.exists(lib):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/torchmdnet_neighbors_ref_cuda.so not built"}))
+        return
+    torch.ops.load_library(lib)
+    op = torch.ops.torchmdnet_neighbors.get_neighbor_pairs
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
+    for n in [int(x) for x in args.sizes.split(",")]:
+        pos_np, box_np = S.uniform_gas(n, seed=5)
+        pos = torch.from_numpy(pos_np).cuda()
+        batch = torch.zeros(n, dtype=torch.long, device="cuda")
+        for rc in [float(x) for x in args.cutoffs.split(",")]:
+            if rc == 10.0 and n > 1048576:
+                continue
+            expected = n * 0.1 * 4.0 / 3.0 * math.pi * rc ** 3
+            for periodic in (True, False):
+                if periodic and box_np[0, 0] < 2 * rc:
+                    continue
+                for strategy in ("brute", "shared", "cell"):
+                    if strategy != "cell" and n > args.brute_max:
+                        continue
+                    if strategy == "brute" and n >= 32768:
+                        continue                             # neighbors_cuda_brute.cuh:75 refuses N >= 32768
+                    cap = int(min(expected * 1.3 + 1000, 2 ** 31 - 2))
+                    box = torch.from_numpy(box_np)           # CPU tensor, as the reference requires
+                    try:
+                        fn = lambda: op(strategy, pos, batch, box, periodic, 0.0, rc, cap, False, True)  # noqa: E731
+                        out = fn()
+                        found = int(out[3])
+                        ms = timed(fn, flush)
+                        print(json.dumps({"impl": "reference", "op": "get_neighbor_pairs", "n": n, "cutoff": rc,
+                                          "periodic": periodic, "strategy": strategy, "ms": ms, "pairs": found}), flush=True)
+                        del out
+                    except Exception as ex:      # noqa: BLE001
+                        print(json.dumps({"impl": "reference", "n": n, "cutoff": rc, "periodic": periodic,
+                                          "strategy": strategy, "error": str(ex)[:200]}), flush=True)
+                    torch.cuda.empty_cache()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--sizes", default="1000,4000,16000,32767,65536,262144,1048576,4194304")
     ap.add_argument("--cutoffs", default="5.0,7.5,10.0")
     ap.add_argument("--brute-max", type=int, default=65536)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"],
+                    help="reference = the reference's own CUDA kernels (neighbors_cuda_{brute,shared,cell}.cuh) recompiled "
+                         "for sm_100 by BUILD_REF_CUDA=1 oracle/build_ref.sh: the GPU-side bar (SURVEY 2.2)")
     args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_sweep(args)
     from torchmdnet import _native
     from torchmdnet.models.utils import OptimizedDistance
     _native.load()
