@@ -198,3 +198,53 @@ def test_deepcopy_and_pickle_do_not_share_the_native_handle():
         assert rm._handle == 7
     finally:
         rm._handle = rm._pack_key = rm._workspace = None
+
+
+@pytest.mark.parametrize("name", ["small_tensornet_o3.npz", "small_et_both.npz"])
+def test_models_are_scriptable_and_saveable(name, tmp_path):
+    """torch.jit.script(model) (reference: tests/test_model.py:40-58) compiles the stand-in of models/scripted.py: the
+    packed weights travel as one buffer, survive save -> load, and the graph calls the fused op.  No GPU needed to
+    script; running the scripted model on CPU tensors is refused by the op (no CPU fallback)."""
+    from torchmdnet.models.model import create_model
+    g = load_npz(name)
+    m = create_model(g["hparams"])
+    m.load_state_dict(g["sd"])
+    if g["hparams"]["model"] == "tensornet":
+        m.representation_model.filter_mode = "table"
+    sm = torch.jit.script(m)
+    op = "tensornet_energy_forces_packed" if g["hparams"]["model"] == "tensornet" else "et_energy_forces_packed"
+    assert op in str(sm.graph)
+    path = str(tmp_path / "model.pt")
+    torch.jit.save(sm, path)
+    lm = torch.jit.load(path)
+    assert torch.equal(lm.packed, sm.packed) and lm.layout == sm.layout and lm.iparams == sm.iparams
+    assert lm.packed.numel() > 1000 and all(o % 64 == 0 for o in sm.layout[:len(sm.layout) // 2])
+    with pytest.raises(RuntimeError, match="CUDA"):
+        lm(tt(g["z"]), tt(g["pos"]), tt(g["batch"]))
+
+
+def test_external_box_routing(tmp_path):
+    """External.calculate(pos, box): a non-zero box selects periodic boundaries on the model's distance module (cell list
+    for wide rectangular boxes, brute otherwise); None / zeros keep open boundaries; an unchanged box changes nothing."""
+    from torchmdnet.calculators import External
+    from torchmdnet.models.model import create_model
+    g = load_npz("small_tensornet_o3.npz")
+    m = create_model(g["hparams"])
+    ckpt = str(tmp_path / "m.ckpt")
+    torch.save({"hyper_parameters": dict(g["hparams"]), "state_dict": {"model." + k: v for k, v in m.state_dict().items()}}, ckpt)
+    calc = External(ckpt, torch.ones(1, 9, dtype=torch.long), "cpu")
+    rm = calc.model.representation_model
+    rc = float(rm.cutoff_upper)
+    assert calc._use_box(None) is False and calc._use_box(torch.zeros(3, 3)) is False and not rm.distance.use_periodic
+    wide = torch.eye(3) * (4 * rc)
+    assert calc._use_box(wide) is True
+    assert rm.distance.use_periodic and rm.distance.strategy == "cell" and torch.equal(rm.distance.box, wide)
+    assert calc._use_box(wide) is False and calc._use_box(wide.clone()) is False
+    small = torch.eye(3) * (2.5 * rc)
+    assert calc._use_box(small.unsqueeze(0)) is True and rm.distance.strategy == "brute"
+    tric = wide.clone()
+    tric[1, 0] = 1.0
+    assert calc._use_box(tric) is True and rm.distance.strategy == "brute" and rm.distance.use_periodic
+    assert calc._use_box(torch.tensor([4 * rc] * 3)) is True and rm.distance.strategy == "cell"
+    assert calc._use_box(None) is True and not rm.distance.use_periodic
+    assert rm.distance.max_num_pairs == -g["hparams"]["max_num_neighbors"] and rm.distance.loop

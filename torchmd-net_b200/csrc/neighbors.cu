@@ -105,7 +105,11 @@ nbr_brute_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, i
     }
     const long long bmin = tile_mm[2 * blockIdx.x], bmax = tile_mm[2 * blockIdx.x + 1];
     const int per_hit = transpose ? 2 : 1;
-    for (int jt = 0; jt <= (int)blockIdx.x; ++jt) {
+    // 2-D grid: the source tiles jt <= blockIdx.x of this target tile are dealt round-robin to the gridDim.y CTAs of the
+    // row, so a single system of 1k atoms (8 target tiles) still fills the chip and the triangular imbalance between
+    // the first and the last target tile is spread over all CTAs (the reference uses one THREAD per pair:
+    // neighbors_cuda_brute.cuh:81-92).  Pair order in the output depends on CTA scheduling, as in the reference.
+    for (int jt = blockIdx.y; jt <= (int)blockIdx.x; jt += gridDim.y) {
         if (tile_mm[2 * jt + 1] < bmin || tile_mm[2 * jt] > bmax) continue;  // block-uniform
         __syncthreads();
         const int j0 = jt * NB_THREADS;
@@ -264,8 +268,12 @@ int neighbors_impl(int strategy, const T* pos, const int64_t* batch, int64_t n_a
         }
         launch_k(tile_batch_range_kernel, ntiles, NB_THREADS, 0, stream, batch, n, tile_mm);
         TMDN_LAUNCH_CHECK();
-        launch_k(nbr_brute_kernel<T>, ntiles, NB_THREADS, 0, stream, pos, batch, n, b, use_periodic, lo2, hi2, loop,
-                                                               include_transpose, out, tile_mm);
+        // source-tile chunks per target tile: enough CTAs for ~one full wave of 16 CTAs per SM
+        long long ny = cdiv((long long)tmdn_sm_count() * 16, ntiles);
+        if (ny > ntiles) ny = ntiles;
+        if (ny < 1) ny = 1;
+        launch_k(nbr_brute_kernel<T>, dim3((unsigned)ntiles, (unsigned)ny), NB_THREADS, 0, stream, pos, batch, n, b,
+                 use_periodic, lo2, hi2, loop, include_transpose, out, tile_mm);
         TMDN_LAUNCH_CHECK();
     }
     launch_k(pad_fill_kernel<T>, (unsigned)cdiv(max_pairs, 256), 256, 0, stream, out);

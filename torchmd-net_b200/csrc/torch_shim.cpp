@@ -15,8 +15,10 @@
 #include <torch/autograd.h>
 #include <torch/library.h>
 
+#include <map>
 #include <mutex>
 #include <string>
+#include <tuple>
 #include <unordered_map>
 #include <vector>
 
@@ -483,6 +485,77 @@ std::vector<int64_t> et_debug_lookup(int64_t handle, int64_t n_atoms, int64_t ma
     return {(int64_t)off, (int64_t)bytes};
 }
 
+// ------------------------------------------------------------------ script-friendly entry points
+// A scripted / saved / re-loaded model cannot carry a process-local handle.  It carries ONE flat fp32 buffer with every
+// packed weight (segments aligned to 256 bytes; `offsets` has n_weights + 1 entries, in floats) plus the integer / float
+// parameter vectors of *_create, and these ops find -- or create -- the native handle from the identity of that buffer
+// (address, version counter, device).  The workspace is cached with the handle.  box: 9 floats, or empty.
+struct PackedEntry { int64_t handle; Tensor workspace; };
+struct PackedKeyT {
+    const void* ptr; uint32_t version; int device; std::vector<int64_t> ip; std::vector<double> fp; int kind;
+    bool operator<(const PackedKeyT& o) const {
+        return std::tie(ptr, version, device, kind, ip, fp) < std::tie(o.ptr, o.version, o.device, o.kind, o.ip, o.fp);
+    }
+};
+std::map<PackedKeyT, PackedEntry> g_packed;
+
+// offsets = [o_0 .. o_n | len_0 .. len_{n-1}]: segment i starts at o_i (multiple of 64 floats) and holds len_i floats
+PackedEntry& packed_entry(int kind, const Tensor& flat, const std::vector<int64_t>& layout, const std::vector<int64_t>& ip,
+                          const std::vector<double>& fp) {
+    TORCH_CHECK(layout.size() % 2 == 0 && !layout.empty(), "packed model: bad layout vector");
+    PackedKeyT key{flat.data_ptr(), flat._version(), (int)flat.get_device(), ip, fp, kind};
+    std::unique_lock<std::mutex> lock(g_mu);
+    auto it = g_packed.find(key);
+    if (it != g_packed.end()) return it->second;
+    TORCH_CHECK(flat.is_cuda() && flat.scalar_type() == at::kFloat && flat.is_contiguous() && flat.dim() == 1,
+                "packed model: the weight buffer must be a contiguous 1-D CUDA float32 tensor (sm_100a build, no CPU fallback)");
+    const size_t n = layout.size() / 2;
+    std::vector<Tensor> w;
+    for (size_t i = 0; i < n; ++i) {
+        const int64_t off = layout[i], len = layout[n + i];
+        TORCH_CHECK(off >= 0 && len >= 0 && off + len <= flat.numel(), "packed model: segment ", i, " out of range");
+        w.push_back(len > 0 ? flat.narrow(0, off, len) : at::empty({0}, flat.options()));
+    }
+    if (g_packed.size() >= 64) {            // stale versions of re-packed models: start over
+        for (auto& kv : g_packed) { g_tn.erase(kv.second.handle); g_et.erase(kv.second.handle); }
+        g_packed.clear();
+    }
+    lock.unlock();                          // *_create takes the lock itself
+    const int64_t h = kind == 0 ? tensornet_create(w, ip, fp) : et_create(w, ip, fp);
+    lock.lock();
+    return g_packed.emplace(key, PackedEntry{h, Tensor()}).first->second;
+}
+
+Tensor box_tensor(const std::vector<double>& box) {
+    if (box.empty()) return at::empty({0, 0}, at::TensorOptions().dtype(at::kDouble));
+    TORCH_CHECK(box.size() == 9, "packed model: box must have 9 entries (row-major 3x3) or none");
+    Tensor b = at::empty({3, 3}, at::TensorOptions().dtype(at::kDouble));
+    for (int i = 0; i < 9; ++i) b.data_ptr<double>()[i] = box[i];
+    return b;
+}
+
+std::tuple<Tensor, Tensor, Tensor> tensornet_energy_forces_packed(
+    const Tensor& flat, std::vector<int64_t> layout, std::vector<int64_t> ip, std::vector<double> fp, const Tensor& z,
+    const Tensor& pos, const Tensor& batch, std::vector<double> box, bool use_periodic, const std::string& strategy,
+    int64_t max_edges, int64_t n_mol, bool compute_forces) {
+    PackedEntry& e = packed_entry(0, flat, layout, ip, fp);
+    auto r = tensornet_energy_forces(e.handle, z, pos, batch, box_tensor(box), use_periodic, strategy, max_edges, n_mol,
+                                     compute_forces, e.workspace.defined() ? c10::optional<Tensor>(e.workspace) : c10::nullopt);
+    e.workspace = std::get<3>(r);
+    return std::make_tuple(std::get<0>(r), std::get<1>(r), std::get<2>(r));
+}
+
+std::tuple<Tensor, Tensor, Tensor> et_energy_forces_packed(
+    const Tensor& flat, std::vector<int64_t> layout, std::vector<int64_t> ip, std::vector<double> fp, const Tensor& z,
+    const Tensor& pos, const Tensor& batch, std::vector<double> box, bool use_periodic, const std::string& strategy,
+    int64_t max_edges, int64_t n_mol, bool compute_forces) {
+    PackedEntry& e = packed_entry(1, flat, layout, ip, fp);
+    auto r = et_energy_forces(e.handle, z, pos, batch, box_tensor(box), use_periodic, strategy, max_edges, n_mol,
+                              compute_forces, e.workspace.defined() ? c10::optional<Tensor>(e.workspace) : c10::nullopt);
+    e.workspace = std::get<3>(r);
+    return std::make_tuple(std::get<0>(r), std::get<1>(r), std::get<2>(r));
+}
+
 // ------------------------------------------------------------------ staged evaluation (spatial decomposition)
 int64_t tensornet_workspace_bytes(int64_t handle, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
                                   const std::string& strategy, const Tensor& box_vectors) {
@@ -650,6 +723,12 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
           "bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces, Tensor? workspace) -> "
           "(Tensor, Tensor, Tensor, Tensor)",
           tensornet_energy_forces);
+    m.def("tensornet_energy_forces_packed(Tensor flat, int[] layout, int[] iparams, float[] fparams, Tensor z, Tensor pos, "
+          "Tensor batch, float[] box, bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces) -> "
+          "(Tensor, Tensor, Tensor)", tensornet_energy_forces_packed);
+    m.def("et_energy_forces_packed(Tensor flat, int[] layout, int[] iparams, float[] fparams, Tensor z, Tensor pos, "
+          "Tensor batch, float[] box, bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces) -> "
+          "(Tensor, Tensor, Tensor)", et_energy_forces_packed);
     m.def("et_create(Tensor[] weights, int[] iparams, float[] fparams) -> int", et_create);
     m.def("et_destroy(int handle) -> ()", et_destroy);
     m.def("et_energy_forces(int handle, Tensor z, Tensor pos, Tensor batch, Tensor box_vectors, "

@@ -119,6 +119,14 @@ class TorchMD_Net(nn.Module):
                                                                 compute_forces=self.derivative)
         return y, (neg_dy if self.derivative else None)
 
+    def __prepare_scriptable__(self):
+        """``torch.jit.script(model)`` compiles this stand-in (models/scripted.py): one flat weight buffer + the fused op.
+        The weights are packed as they are now; script again after changing them."""
+        from .. import _native
+        from .scripted import ScriptableTorchMD_Net
+        _native.load()
+        return ScriptableTorchMD_Net(self)
+
     def _num_molecules(self, batch):
         """``batch.max()+1`` (output_modules.py:33); cached while capturing a CUDA graph, as the reference."""
         from .utils import check_stream_capturing

@@ -1,0 +1,90 @@
+"""TorchScript deployment of the fused models (the reference pins it with tests/test_model.py:40-58,
+85-125: script -> save -> load -> CUDA graph).
+
+``torch.jit.script(model)`` on a ``TorchMD_Net`` of this package returns the scripted form of ``ScriptableTorchMD_Net``
+(through ``TorchMD_Net.__prepare_scriptable__``): a module that holds ONE flat fp32 buffer with every packed weight
+(filter tables included) and calls the fused op ``torchmdnet_b200::{tensornet,et}_energy_forces_packed``, which finds or
+creates the native model from the identity of that buffer.  The buffer follows ``.to(device)``, is written by
+``torch.jit.save`` and restored by ``torch.jit.load`` in another process; nothing process-local is serialised.
+
+The weights are a snapshot taken at scripting time (deployment is inference).  As in the reference, the number of
+molecules is ``batch.max() + 1`` (one sync) unless the stream is being captured, in which case the value of the last
+eager call is used (output_modules.py:27-43)."""
+from typing import Dict, List, Optional, Tuple
+
+import torch
+from torch import Tensor, nn
+
+
+def _flatten(weights: List[Tensor]):
+    """-> (flat fp32 tensor, layout = [offset_0..offset_{n-1} | len_0..len_{n-1}]), segments aligned to 256 bytes"""
+    offs, lens, cur = [], [], 0
+    for w in weights:
+        offs.append(cur)
+        lens.append(int(w.numel()))
+        cur += (int(w.numel()) + 63) // 64 * 64
+    dev = weights[0].device
+    flat = torch.zeros(max(cur, 64), dtype=torch.float32, device=dev)
+    for w, o in zip(weights, offs):
+        if w.numel():
+            flat[o:o + w.numel()] = w.reshape(-1).to(torch.float32)
+    return flat, offs + lens
+
+
+class ScriptableTorchMD_Net(nn.Module):
+    """``forward(z, pos, batch=None, q=None, s=None, extra_args=None) -> (y, neg_dy | None)`` with the signature of
+    ``TorchMD_Net.forward`` (models/model.py:232-300), scriptable, saveable, CUDA-graph capturable."""
+
+    layout: List[int]
+    iparams: List[int]
+    fparams: List[float]
+    box: List[float]
+
+    def __init__(self, model):
+        super().__init__()
+        rm = model.representation_model
+        mean, std = model._mean_std()
+        w, ip, fp = rm.pack_weights(model.output_model, mean, std)
+        flat, layout = _flatten(w)
+        self.register_buffer("packed", flat)
+        self.layout = [int(x) for x in layout]
+        self.iparams = [int(x) for x in ip]
+        self.fparams = [float(x) for x in fp]
+        self.is_tensornet: bool = rm._op == "tensornet"
+        self.derivative: bool = bool(model.derivative)
+        dist = rm.distance
+        self.max_num_pairs: int = int(dist.max_num_pairs)
+        self.use_periodic: bool = bool(dist.use_periodic)
+        self.strategy: str = str(dist.strategy)
+        box = dist.box
+        self.box = [] if box is None or box.numel() == 0 else [float(x) for x in box.double().reshape(-1)]
+        self.dim_size: int = 0
+
+    def forward(self, z: Tensor, pos: Tensor, batch: Optional[Tensor] = None, q: Optional[Tensor] = None,
+                s: Optional[Tensor] = None, extra_args: Optional[Dict[str, Tensor]] = None
+                ) -> Tuple[Tensor, Optional[Tensor]]:
+        assert z.dim() == 1 and z.dtype == torch.long
+        if batch is None:
+            b = torch.zeros_like(z)
+            n_mol = 1
+        else:
+            b = batch
+            if torch.ops.torch_extension.is_stream_capturing():
+                assert self.dim_size > 0, "Warming up is needed before capturing the model into a CUDA graph"
+                n_mol = self.dim_size
+            else:
+                n_mol = int(batch.max().item()) + 1
+                self.dim_size = n_mol
+        n = pos.size(0)
+        max_edges = self.max_num_pairs if self.max_num_pairs > 0 else -self.max_num_pairs * n
+        if self.is_tensornet:
+            y, f, status = torch.ops.torchmdnet_b200.tensornet_energy_forces_packed(
+                self.packed, self.layout, self.iparams, self.fparams, z.contiguous(), pos.detach().contiguous(),
+                b.contiguous(), self.box, self.use_periodic, self.strategy, max_edges, n_mol, self.derivative)
+        else:
+            y, f, status = torch.ops.torchmdnet_b200.et_energy_forces_packed(
+                self.packed, self.layout, self.iparams, self.fparams, z.contiguous(), pos.detach().contiguous(),
+                b.contiguous(), self.box, self.use_periodic, self.strategy, max_edges, n_mol, self.derivative)
+        if self.derivative:
+            return y, f
+        return y, None
