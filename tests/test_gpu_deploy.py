@@ -1,0 +1,138 @@
+"""Deployment surface: TorchScript of the fused models -- script, save, load, CUDA-graph capture -- as
+the reference pins it (tests/test_model.py:40-58, 85-125), and calculators.External with a periodic box."""
+import pytest
+import torch
+
+import synth_inputs as S
+from helpers import load_npz, tt
+from test_gpu_tensornet import check, seed_everything
+
+pytestmark = pytest.mark.gpu
+
+
+def _small(name, mode="table"):
+    from torchmdnet.models.model import create_model
+    g = load_npz(name)
+    m = create_model(g["hparams"])
+    m.load_state_dict(g["sd"])
+    m = m.cuda().eval()
+    if g["hparams"]["model"] == "tensornet":
+        m.representation_model.filter_mode = mode
+    return g, m
+
+
+@pytest.mark.parametrize("name", ["small_tensornet_o3.npz", "small_tensornet_so3.npz", "small_et_both.npz",
+                                  "small_et_keys_nonbr.npz"])
+def test_scripted_model_equals_eager_and_survives_save_load(name, tmp_path):
+    g, m = _small(name)
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    y0, f0 = m(z, pos, batch)
+    check(y0, f0, g["y"], g["forces"])
+    sm = torch.jit.script(m)
+    y1, f1 = sm(z, pos, batch)
+    assert torch.equal(y0, y1) and torch.equal(f0, f1)          # the same native model behind both
+    path = str(tmp_path / "model.pt")
+    torch.jit.save(sm, path)
+    lm = torch.jit.load(path, map_location="cuda")
+    y2, f2 = lm(z, pos, batch)
+    assert torch.equal(y0, y2) and torch.equal(f0, f2)
+    # scripted on the CPU, moved afterwards: the packed buffer follows .to()
+    g2, mc = _small(name)
+    sc = torch.jit.script(mc.cpu()).to("cuda")
+    y3, f3 = sc(z, pos, batch)
+    check(y3, f3, g["y"], g["forces"])
+    # batch=None: one molecule
+    n0 = int((batch == 0).sum())
+    ya, fa = m(z[:n0], pos[:n0])
+    yb, fb = lm(z[:n0], pos[:n0], None)
+    assert torch.equal(ya, yb) and torch.equal(fa, fb)
+
+
+def test_scripted_model_in_a_cuda_graph(tmp_path):
+    """script -> save -> load -> capture (reference: tests/test_model.py:85-125): warm up eagerly (caches the number of
+    molecules), capture, replay on new positions."""
+    g, m = _small("small_tensornet_o3.npz")
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    path = str(tmp_path / "model.pt")
+    torch.jit.save(torch.jit.script(m), path)
+    lm = torch.jit.load(path, map_location="cuda")
+    static_pos = pos.clone()
+    s_ = torch.cuda.Stream()
+    s_.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s_):
+        for _ in range(2):
+            lm(z, static_pos, batch)
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=s_):
+            yg, fg = lm(z, static_pos, batch)
+    torch.cuda.current_stream().wait_stream(s_)
+    for k in range(3):
+        p = pos + 0.01 * k * torch.sin(torch.arange(pos.numel(), device="cuda").float()).view_as(pos)
+        static_pos.copy_(p)
+        gr.replay()
+        torch.cuda.synchronize()
+        y, f = m(z, p, batch)
+        assert torch.equal(y, yg) and torch.equal(f, fg), k
+
+
+def test_scripted_periodic_model_carries_its_box():
+    from torchmdnet.models.utils import OptimizedDistance
+    g, m = _small("small_tensornet_periodic.npz")
+    hp = g["hparams"]
+    m.representation_model.distance = OptimizedDistance(
+        hp["cutoff_lower"], hp["cutoff_upper"], max_num_pairs=-hp["max_num_neighbors"], return_vecs=True, loop=True,
+        check_errors=False, resize_to_fit=False, box=tt(g["box"]), strategy="cell")
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    sm = torch.jit.script(m)
+    assert len(sm.box) == 9 and sm.use_periodic and sm.strategy == "cell"
+    y, f = sm(z, pos, batch)
+    check(y, f, g["y"], g["forces"])
+
+
+def test_external_uses_its_box(tmp_path):
+    """External.calculate(pos, box): the reference ignores box (calculators.py:50-56); here it selects periodic boundaries.
+    Checked against the reference-written periodic fixture (375 atoms; cell list) and against open boundaries."""
+    from torchmdnet.calculators import External
+    g = load_npz("small_tensornet_periodic.npz")
+    ckpt = str(tmp_path / "m.ckpt")
+    torch.save({"hyper_parameters": dict(g["hparams"]), "state_dict": {"model." + k: v for k, v in g["sd"].items()}}, ckpt)
+    n = g["z"].shape[0]
+    calc = External(ckpt, tt(g["z"]).view(1, n), "cuda")
+    calc.model.representation_model.filter_mode = "table"
+    pos, box = tt(g["pos"]), tt(g["box"])
+    for k in range(5):                                   # eager calls, graph capture, replays
+        e, f = calc.calculate(pos, box)
+        check(e, f.view(n, 3), g["y"], g["forces"])
+    assert calc.model.representation_model.distance.strategy == "cell" and calc._graph is not None
+    e_open, f_open = calc.calculate(pos, None)           # open boundaries: another answer, graph dropped and rebuilt
+    assert not calc.model.representation_model.distance.use_periodic
+    assert float((e_open - e).abs().max()) > 1e-3
+    for k in range(3):
+        e2, f2 = calc.calculate(pos, None)
+        assert torch.equal(e2, e_open) and torch.equal(f2, f_open)
+    e3, f3 = calc.calculate(pos, box.unsqueeze(0))       # [1,3,3], back to periodic
+    check(e3, f3.view(n, 3), g["y"], g["forces"])
+
+
+def test_atomref_prior_matches_reference(tmp_path):
+    """TensorNet + Atomref prior against the fixture written by the unmodified reference; through TorchMD_Net.forward and
+    through External (legacy checkpoint keys included)."""
+    from torchmdnet.calculators import External
+    g, m = _small("small_tensornet_atomref.npz")
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    y, f = m(z, pos, batch)
+    check(y, f, g["y"], g["forces"])
+    m.prior_model = None                      # the prior is what separates the two results
+    y0, _ = m(z, pos, batch)
+    assert float((y0 - y).abs().min()) > 0.1
+    n0 = int((tt(g["batch"]) == 0).sum())
+    legacy = {"model." + k.replace("prior_model.0.", "prior_model."): v for k, v in g["sd"].items()}
+    path = str(tmp_path / "legacy.ckpt")
+    torch.save({"hyper_parameters": dict(g["hparams"]), "state_dict": legacy}, path)
+    calc = External(path, tt(g["z"])[:n0].view(1, n0), "cuda")
+    for _ in range(4):
+        e, frc = calc.calculate(tt(g["pos"])[:n0], None)
+    g1, m1 = _small("small_tensornet_atomref.npz", mode="exact")
+    y1, f1 = m1(z[:n0], pos[:n0])
+    torch.testing.assert_close(e, y1, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(frc.view(n0, 3), f1, rtol=0, atol=1e-5)

@@ -248,3 +248,42 @@ def test_external_box_routing(tmp_path):
     assert calc._use_box(torch.tensor([4 * rc] * 3)) is True and rm.distance.strategy == "cell"
     assert calc._use_box(None) is True and not rm.distance.use_periodic
     assert rm.distance.max_num_pairs == -g["hparams"]["max_num_neighbors"] and rm.distance.loop
+
+
+def test_atomref_prior_and_legacy_checkpoint_keys(tmp_path):
+    """create_model / load_model with the Atomref prior (priors/atomref.py, models/model.py:96-98,146-177): the reference's
+    state_dict keys load as they are, checkpoints from the time when Atomref was the only prior (un-indexed
+    ``prior_model.*`` keys, model.py:134-141) are renamed, the prior adds sum_i atomref[z_i] per molecule, and the
+    pairwise priors are refused by name."""
+    from torchmdnet.models.model import create_model, load_model
+    g = load_npz("small_tensornet_atomref.npz")
+    hp = g["hparams"]
+    m = create_model(hp)
+    assert set(m.state_dict()) == set(g["sd"]) and "prior_model.0.atomref.weight" in g["sd"]
+    m.load_state_dict(g["sd"])
+    assert m.prior_model[0].get_init_args() == {"max_z": hp["max_z"]}
+    z, batch = tt(g["z"]), tt(g["batch"])
+    add = m.apply_priors(torch.zeros(int(batch.max()) + 1, 1), z, batch, int(batch.max()) + 1)
+    w = g["sd"]["prior_model.0.atomref.weight"][:, 0]
+    expect = torch.zeros(int(batch.max()) + 1).index_add_(0, batch, w[z])
+    torch.testing.assert_close(add[:, 0], expect)
+    # legacy keys + the Lightning "model." prefix
+    legacy = {}
+    for k, v in g["sd"].items():
+        legacy["model." + k.replace("prior_model.0.", "prior_model.")] = v
+    path = str(tmp_path / "legacy.ckpt")
+    torch.save({"hyper_parameters": dict(hp), "state_dict": legacy}, path)
+    lm = load_model(path)
+    assert all(torch.equal(a, b) for a, b in zip(lm.state_dict().values(), m.state_dict().values()))
+    # hparams overrides through kwargs (model.py:126-129): unknown keys warn, known keys replace
+    with pytest.warns(UserWarning, match="Unknown hyperparameter"):
+        lm2 = load_model(path, derivative=False, some_new_flag=1)
+    assert lm2.derivative is False
+    # the forms the option can take (str | dict | list) and the priors outside this build
+    from torchmdnet.models.model import create_prior_models
+    assert create_prior_models({"prior_model": None}) is None
+    assert create_prior_models({"prior_model": {"Atomref": {"max_z": 7}}})[0].initial_atomref.shape == (7, 1)
+    assert len(create_prior_models({"prior_model": ["Atomref"], "prior_args": [{"max_z": 5}]})) == 1
+    for name in ("ZBL", "D2", "Coulomb"):
+        with pytest.raises(NotImplementedError, match=name):
+            create_model(dict(hp, prior_model=name, prior_args=None))

@@ -22,7 +22,7 @@ struct KTimer {
 
 // process-wide tuning knobs (tmdn_set_tuning, defined in scan.cu)
 enum { TMDN_TUNE_SMALL_GEMM = 0, TMDN_TUNE_LPT_ROWS = 1, TMDN_TUNE_PDL = 2, TMDN_TUNE_EDGE_PERSIST = 3, TMDN_TUNE_HOT_ROWS = 4,
-       TMDN_TUNE_COUNT = 5 };
+       TMDN_TUNE_EDGE_VARIANT = 5, TMDN_TUNE_COUNT = 6 };
 extern int g_tmdn_tuning[TMDN_TUNE_COUNT];
 
 #define TMDN_CHECK_ARG(cond, ...)                 \
@@ -150,6 +150,16 @@ __device__ __forceinline__ float act_apply(int act, float x) {
             float sp = x > 20.0f ? x : log1pf(expf(x));
             return sp - 0.69314718055994530942f;
         }
+    }
+}
+// value and derivative from ONE evaluation of the transcendental (same expressions as act_apply / act_grad, so the
+// results are bit-identical to calling both)
+__device__ __forceinline__ void act_both(int act, float x, float& a, float& g) {
+    switch (act) {
+        case TMDN_ACT_SILU: { const float s = sigmoidf_(x); a = x * s; g = s * (1.0f + x * (1.0f - s)); break; }
+        case TMDN_ACT_TANH: { const float y = tanhf(x); a = y; g = 1.0f - y * y; break; }
+        case TMDN_ACT_SIGMOID: { const float s = sigmoidf_(x); a = s; g = s * (1.0f - s); break; }
+        default: { a = act_apply(act, x); g = sigmoidf_(x); }
     }
 }
 __device__ __forceinline__ float act_grad(int act, float x) {

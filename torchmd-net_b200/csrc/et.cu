@@ -451,9 +451,10 @@ et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
             const float gvjx = L[b][9], gvjy = L[b][10], gvjz = L[b][11];
             // ---- A
             const float sA = seg_sum_t<HDC>(qi * kj * f[0], hd);
-            const float aA = act_apply(attn_act, sA), attnA = aA;
+            float attnA, dactA;
+            act_both(attn_act, sA, attnA, dactA);               // one sigmoid for value and derivative
             const float gattA = seg_sum_t<HDC>(gxi * vj0 * f[1], hd);
-            const float gsA = gattA * act_grad(attn_act, sA);
+            const float gsA = gattA * dactA;
             acc[0] += gsA * kj * f[0];
             const float gv1A = gvix * vjx + gviy * vjy + gviz * vjz;
             const float gv2A = gvix * hx + gviy * hy + gviz * hz;
@@ -463,9 +464,10 @@ et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
             const float ghxA = gvix * v2A, ghyA = gviy * v2A, ghzA = gviz * v2A;
             // ---- B (roles swapped, dhat' = +u)
             const float sB = seg_sum_t<HDC>(qj * ki * f[0], hd);
-            const float aB = act_apply(attn_act, sB), attnB = aB;
+            float attnB, dactB;
+            act_both(attn_act, sB, attnB, dactB);
             const float gattB = seg_sum_t<HDC>(gxj * vi0 * f[1], hd);
-            const float gsB = gattB * act_grad(attn_act, sB);
+            const float gsB = gattB * dactB;
             acc[1] += gsB * qj * f[0];
             const float gv1B = gvjx * vix + gvjy * viy + gvjz * viz;
             const float gv2B = gvjx * g.x + gvjy * g.y + gvjz * g.z;

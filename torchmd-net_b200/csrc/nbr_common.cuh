@@ -26,20 +26,36 @@ __device__ __forceinline__ double round_(double a) { return round(a); }
 __device__ __forceinline__ float floor_(float a) { return floorf(a); }
 __device__ __forceinline__ double floor_(double a) { return floor(a); }
 
+// Number of box lengths to subtract: round(d / L) as the reference computes it (IEEE division, then round), without the
+// division for the cases that matter.  Exact: for |d| < L/2 the quotient rounds to a float strictly below 0.5 (the
+// neighbour of 0.5 is 2^-25 away, the quotient at least that far), so the result is 0; for L/2 < |d| < 1.25 L it
+// rounds into (0.5, 1.5), so the result is +-1.  Ties (|d| == L/2 exactly) and far images take the division.
+template <typename T> __device__ __forceinline__ T image_count(T d, T L) {
+    const T a = fabs(d), h = T(0.5) * L;      // 0.5 * L is exact
+    if (a < h) return T(0);
+    if (a > h && a < T(1.25) * L) return d < T(0) ? T(-1) : T(1);
+    return round_(rn_div(d, L));
+}
 // neighbors/common.cuh:180-194 (triclinic minimum image, z -> y -> x)
 template <typename T> __device__ __forceinline__ void min_image_tric(T& dx, T& dy, T& dz, const Box3<T>& b) {
-    T s = round_(rn_div(dz, b.m[2][2]));
-    dx = rn_sub(dx, rn_mul(s, b.m[2][0]));
-    dy = rn_sub(dy, rn_mul(s, b.m[2][1]));
-    dz = rn_sub(dz, rn_mul(s, b.m[2][2]));
-    s = round_(rn_div(dy, b.m[1][1]));
-    dx = rn_sub(dx, rn_mul(s, b.m[1][0]));
-    dy = rn_sub(dy, rn_mul(s, b.m[1][1]));
-    dz = rn_sub(dz, rn_mul(s, b.m[1][2]));
-    s = round_(rn_div(dx, b.m[0][0]));
-    dx = rn_sub(dx, rn_mul(s, b.m[0][0]));
-    dy = rn_sub(dy, rn_mul(s, b.m[0][1]));
-    dz = rn_sub(dz, rn_mul(s, b.m[0][2]));
+    T s = image_count(dz, b.m[2][2]);
+    if (s != T(0)) {
+        dx = rn_sub(dx, rn_mul(s, b.m[2][0]));
+        dy = rn_sub(dy, rn_mul(s, b.m[2][1]));
+        dz = rn_sub(dz, rn_mul(s, b.m[2][2]));
+    }
+    s = image_count(dy, b.m[1][1]);
+    if (s != T(0)) {
+        dx = rn_sub(dx, rn_mul(s, b.m[1][0]));
+        dy = rn_sub(dy, rn_mul(s, b.m[1][1]));
+        dz = rn_sub(dz, rn_mul(s, b.m[1][2]));
+    }
+    s = image_count(dx, b.m[0][0]);
+    if (s != T(0)) {
+        dx = rn_sub(dx, rn_mul(s, b.m[0][0]));
+        dy = rn_sub(dy, rn_mul(s, b.m[0][1]));
+        dz = rn_sub(dz, rn_mul(s, b.m[0][2]));
+    }
 }
 // neighbors/common.cuh:142-148 (rectangular minimum image)
 template <typename T> __device__ __forceinline__ T min_image_rect1(T d, T L) {

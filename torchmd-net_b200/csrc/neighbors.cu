@@ -103,14 +103,15 @@ nbr_brute_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, i
         zi = pos[3 * (size_t)i + 2];
         bi = batch[i];
     }
-    const long long bmin = tile_mm[2 * blockIdx.x], bmax = tile_mm[2 * blockIdx.x + 1];
+    // tile_mm == null (few tiles): no batch-range skipping, one launch less
+    const long long bmin = tile_mm ? tile_mm[2 * blockIdx.x] : LLONG_MIN, bmax = tile_mm ? tile_mm[2 * blockIdx.x + 1] : LLONG_MAX;
     const int per_hit = transpose ? 2 : 1;
     // 2-D grid: the source tiles jt <= blockIdx.x of this target tile are dealt round-robin to the gridDim.y CTAs of the
     // row, so a single system of 1k atoms (8 target tiles) still fills the chip and the triangular imbalance between
     // the first and the last target tile is spread over all CTAs (the reference uses one THREAD per pair:
     // neighbors_cuda_brute.cuh:81-92).  Pair order in the output depends on CTA scheduling, as in the reference.
     for (int jt = blockIdx.y; jt <= (int)blockIdx.x; jt += gridDim.y) {
-        if (tile_mm[2 * jt + 1] < bmin || tile_mm[2 * jt] > bmax) continue;  // block-uniform
+        if (tile_mm && (tile_mm[2 * jt + 1] < bmin || tile_mm[2 * jt] > bmax)) continue;  // block-uniform
         __syncthreads();
         const int j0 = jt * NB_THREADS;
         const int nj = min(NB_THREADS, n - j0);
@@ -122,13 +123,24 @@ nbr_brute_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, i
         }
         __syncthreads();
         const int jend = vi ? min(nj, i - j0) : 0;  // only j < i
+        // pass 1: test every candidate once; the hits of this thread (<= 128 per tile) are kept as a bit mask in four
+        // registers, so that the write pass below only revisits hits (0.3 % of the tests at liquid density)
+        unsigned hit[NB_THREADS / 32];
         int cnt = 0;
-        for (int jj = 0; jj < jend; ++jj) {
-            if (sb[jj] != bi) continue;
-            T dx = rn_sub(xi, sx[jj]), dy = rn_sub(yi, sy[jj]), dz = rn_sub(zi, sz[jj]);
-            if (periodic) min_image_tric(dx, dy, dz, box);
-            const T d2 = dist2(dx, dy, dz);
-            cnt += (d2 < hi2 && d2 >= lo2) ? 1 : 0;
+#pragma unroll
+        for (int w = 0; w < NB_THREADS / 32; ++w) {
+            unsigned m = 0;
+            const int je = min(32, jend - 32 * w);
+            for (int bq = 0; bq < je; ++bq) {
+                const int jj = 32 * w + bq;
+                if (sb[jj] != bi) continue;
+                T dx = rn_sub(xi, sx[jj]), dy = rn_sub(yi, sy[jj]), dz = rn_sub(zi, sz[jj]);
+                if (periodic) min_image_tric(dx, dy, dz, box);
+                const T d2 = dist2(dx, dy, dz);
+                if (d2 < hi2 && d2 >= lo2) m |= 1u << bq;
+            }
+            hit[w] = m;
+            cnt += __popc(m);
         }
         const int self = (loop && vi && jt == (int)blockIdx.x) ? 1 : 0;
         const int items = cnt * per_hit + self;
@@ -138,13 +150,15 @@ nbr_brute_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, i
         if (t == 0) s_base = atomicAdd(out.counter, total);
         __syncthreads();
         long long slot = (long long)s_base + off;
-        for (int jj = 0; jj < jend; ++jj) {
-            if (sb[jj] != bi) continue;
-            T dx = rn_sub(xi, sx[jj]), dy = rn_sub(yi, sy[jj]), dz = rn_sub(zi, sz[jj]);
-            if (periodic) min_image_tric(dx, dy, dz, box);
-            const T d2 = dist2(dx, dy, dz);
-            if (d2 < hi2 && d2 >= lo2) {
-                const T d = sqrt_rn(d2);
+#pragma unroll
+        for (int w = 0; w < NB_THREADS / 32; ++w) {
+            unsigned m = hit[w];
+            while (m) {
+                const int jj = 32 * w + __ffs(m) - 1;
+                m &= m - 1;
+                T dx = rn_sub(xi, sx[jj]), dy = rn_sub(yi, sy[jj]), dz = rn_sub(zi, sz[jj]);
+                if (periodic) min_image_tric(dx, dy, dz, box);
+                const T d = sqrt_rn(dist2(dx, dy, dz));
                 write_pair(out, slot++, i, j0 + jj, dx, dy, dz, d);
                 if (transpose) write_pair(out, slot++, j0 + jj, i, -dx, -dy, -dz, d);
             }
@@ -266,8 +280,12 @@ int neighbors_impl(int strategy, const T* pos, const int64_t* batch, int64_t n_a
             tmdn_set_error("neighbors(brute): workspace too small (%zu < %zu)", workspace_bytes, arena.off);
             return TMDN_EWORKSPACE;
         }
-        launch_k(tile_batch_range_kernel, ntiles, NB_THREADS, 0, stream, batch, n, tile_mm);
-        TMDN_LAUNCH_CHECK();
+        if (ntiles > 32) {      // skipping tiles of other molecules pays from a few thousand atoms on
+            launch_k(tile_batch_range_kernel, ntiles, NB_THREADS, 0, stream, batch, n, tile_mm);
+            TMDN_LAUNCH_CHECK();
+        } else {
+            tile_mm = nullptr;
+        }
         // source-tile chunks per target tile: enough CTAs for ~one full wave of 16 CTAs per SM
         long long ny = cdiv((long long)tmdn_sm_count() * 16, ntiles);
         if (ny > ntiles) ny = ntiles;

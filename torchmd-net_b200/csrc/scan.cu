@@ -40,11 +40,14 @@ extern "C" long long tmdn_launch_count(void) { return g_launches.load(); }
 // TMDN_HOT_ROWS).  Every setting computes the same function; the knobs select kernels / launch shapes.
 //   edge_persist: large systems run the TensorNet message-passing kernels as persistent CTAs (one per SM)
 //   hot_rows:     number of table rows (from the far end of the grid) those kernels keep in shared memory
+//   edge_variant: A/B instantiations of the persistent kernels (bit 0: forward 2 edges per batch; bit 1: backward 8 workers x 1 edge);
+//                 same sums in the same order
 static int env_or(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 int g_tmdn_tuning[TMDN_TUNE_COUNT] = {env_or("TMDN_SMALL_GEMM", 1), env_or("TMDN_LPT_ROWS", 1), env_or("TMDN_PDL", 0),
-                                         env_or("TMDN_EDGE_PERSIST", 1), env_or("TMDN_HOT_ROWS", 0)};
+                                         env_or("TMDN_EDGE_PERSIST", 1), env_or("TMDN_HOT_ROWS", 0),
+                                         env_or("TMDN_EDGE_VARIANT", 0)};
 extern "C" int tmdn_set_tuning(const char* key, int value) {
-    static const char* names[TMDN_TUNE_COUNT] = {"small_gemm", "lpt_rows", "pdl", "edge_persist", "hot_rows"};
+    static const char* names[TMDN_TUNE_COUNT] = {"small_gemm", "lpt_rows", "pdl", "edge_persist", "hot_rows", "edge_variant"};
     if (!key) { tmdn_set_error("set_tuning: null key"); return -1; }
     for (int i = 0; i < TMDN_TUNE_COUNT; ++i)
         if (strcmp(key, names[i]) == 0) {

@@ -652,8 +652,8 @@ __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_p
 }
 
 // persistent large-system variant: 4 row workers at 128 registers
-template <int HC, int NB>
-__global__ void __launch_bounds__(512, 1) tn_msg_bwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
+template <int HC, int NB, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) tn_msg_bwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
                             const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
                             const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
                             int n_hot, int row0) {
@@ -1404,7 +1404,10 @@ struct TnRun {
                 // small systems: 4 slices x 2 edges per thread at 128 registers instead of 8 slices x 1 at 64 -- the same
                 // number of edges in flight per SM, but with 64 registers ptxas reuses the landing registers of the
                 // table rows and an iteration becomes 3-4 dependent round trips instead of one (SASS, r01i)
-                if (pl.ok)
+                if (pl.ok && (g_tmdn_tuning[TMDN_TUNE_EDGE_VARIANT] & 1))
+                    launch_k(tn_msg_fwd_p<128, 2>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom, fv_layer[l],
+                             wa.Y[l], r1, m->so3, wa.M[l], wa.tauh, pl.n_hot, r0);
+                else if (pl.ok)
                     launch_k(tn_msg_fwd_p<128, 1>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom, fv_layer[l],
                              wa.Y[l], r1, m->so3, wa.M[l], wa.tauh, pl.n_hot, r0);
                 else if (tab && small_rows) {
@@ -1478,10 +1481,15 @@ struct TnRun {
             float* dB = dBk(w, k_in + 1);           // rows of the next halo point
             {
                 KTimer ktimer__("tn_msg_bwd", stream);
-                const PersistLaunch pl = persist_launch(tn_msg_bwd_p<128, 2>, tab, N, H, 4, fv_layer[l]);
-                if (pl.ok)
-                    launch_k(tn_msg_bwd_p<128, 2>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom, fv_layer[l],
-                             wa.Y[l], dM, wa.dC, wa.gpos, r1, pl.n_hot, r0);
+                const int variant = g_tmdn_tuning[TMDN_TUNE_EDGE_VARIANT];
+                const PersistLaunch pl = (variant & 2) ? persist_launch(tn_msg_bwd_p<128, 1, 1024>, tab, N, H, 8, fv_layer[l])
+                                                       : persist_launch(tn_msg_bwd_p<128, 2, 512>, tab, N, H, 4, fv_layer[l]);
+                if (pl.ok && (variant & 2))
+                    launch_k(tn_msg_bwd_p<128, 1, 1024>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom,
+                             fv_layer[l], wa.Y[l], dM, wa.dC, wa.gpos, r1, pl.n_hot, r0);
+                else if (pl.ok)
+                    launch_k(tn_msg_bwd_p<128, 2, 512>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom,
+                             fv_layer[l], wa.Y[l], dM, wa.dC, wa.gpos, r1, pl.n_hot, r0);
                 else if (bwd4)
                     launch_k(tn_msg_bwd<true, 2, 0, 512, true>, elb2.grid, elb2.block, elb2.smem, stream, wa.row_ptr, wa.col,
                              geom, fv_layer[l], wa.Y[l], dM, wa.dC, wa.gpos, r1, H, order, r0);

@@ -711,7 +711,11 @@ TORCH_LIBRARY(torchmdnet_neighbors, m) {
 TORCH_LIBRARY_IMPL(torchmdnet_neighbors, AutogradCUDA, m) { m.impl("get_neighbor_pairs", get_neighbor_pairs_autograd); }
 TORCH_LIBRARY_IMPL(torchmdnet_neighbors, CPU, m) { m.impl("get_neighbor_pairs", get_neighbor_pairs_cpu); }
 
-TORCH_LIBRARY(torch_extension, m) { m.def("is_stream_capturing() -> bool", is_stream_capturing); }
+// CONSERVATIVE alias analysis = "has side effects": TorchScript must not constant-fold or hoist a call that takes no
+// arguments (it would freeze the answer of the first, non-capturing run into the graph)
+TORCH_LIBRARY(torch_extension, m) {
+    m.def(torch::schema("is_stream_capturing() -> bool", c10::AliasAnalysisKind::CONSERVATIVE), is_stream_capturing);
+}
 
 TORCH_LIBRARY(torchmdnet_b200, m) {
     m.def("csr_from_pairs(Tensor neighbors, Tensor deltas, Tensor distances, Tensor num_found, int n_atoms, "

@@ -47,8 +47,8 @@ def create_model(args, prior_model=None, mean=None, std=None):
         if args["derivative"]:
             raise ValueError("Derivative and atom filter can't be used together")
         raise NotImplementedError("AtomFilter is outside the accelerated energy+force path of this build")
-    if args.get("prior_model") or prior_model is not None:
-        raise NotImplementedError("prior models are outside the accelerated energy+force path of this build")
+    if prior_model is None:
+        prior_model = create_prior_models(args)      # when loading a model (model.py:96-98)
     if args["output_model"] != "Scalar":
         raise NotImplementedError('output_model "%s": only the Scalar energy head is built' % args["output_model"])
     if args.get("reduce_op", "add") not in ("add", "sum"):
@@ -56,8 +56,38 @@ def create_model(args, prior_model=None, mean=None, std=None):
     output_prefix = "Equivariant" if is_equivariant else ""
     output_model = getattr(output_modules, output_prefix + args["output_model"])(
         args["embedding_dimension"], activation=args["activation"], reduce_op=args["reduce_op"], dtype=dtype)
-    return TorchMD_Net(representation_model, output_model, prior_model=None, mean=mean, std=std,
+    return TorchMD_Net(representation_model, output_model, prior_model=prior_model, mean=mean, std=std,
                        derivative=args["derivative"], dtype=dtype)
+
+
+def create_prior_models(args, dataset=None):
+    """Parse the ``prior_model`` option (str | dict | list of them, with ``prior_args``) as models/model.py:146-177.
+    Only ``Atomref`` is built here; the pairwise priors are refused."""
+    from .. import priors
+    prior_models = []
+    if args.get("prior_model"):
+        prior_model = args["prior_model"]
+        prior_names, prior_args = [], []
+        if not isinstance(prior_model, list):
+            prior_model = [prior_model]
+        for prior in prior_model:
+            if isinstance(prior, dict):
+                for key, value in prior.items():
+                    prior_names.append(key)
+                    prior_args.append({} if value is None else value)
+            else:
+                prior_names.append(prior)
+                prior_args.append({})
+        if "prior_args" in args and args["prior_args"] is not None:
+            prior_args = args["prior_args"]
+            if not isinstance(prior_args, list):
+                prior_args = [prior_args]
+        for name, arg in zip(prior_names, prior_args):
+            if not hasattr(priors, name):
+                raise NotImplementedError('prior model "%s" is outside this build (available: %s)'
+                                          % (name, ", ".join(priors.__all__)))
+            prior_models.append(getattr(priors, name)(dataset=dataset, **arg))
+    return prior_models or None
 
 
 def load_model(filepath, args=None, device="cpu", **kwargs):
@@ -72,6 +102,11 @@ def load_model(filepath, args=None, device="cpu", **kwargs):
         args[key] = value
     model = create_model(args)
     state_dict = {re.sub(r"^model\.", "", k): v for k, v in ckpt["state_dict"].items()}
+    # backward compatibility with checkpoints written when Atomref was the only prior (model.py:134-141)
+    for old, new in (("prior_model.initial_atomref", "prior_model.0.initial_atomref"),
+                     ("prior_model.atomref.weight", "prior_model.0.atomref.weight")):
+        if old in state_dict:
+            state_dict[new] = state_dict.pop(old)
     model.load_state_dict(state_dict)
     return model.to(device)
 
@@ -84,9 +119,12 @@ class TorchMD_Net(nn.Module):
         super().__init__()
         self.representation_model = representation_model.to(dtype=dtype)
         self.output_model = output_model.to(dtype=dtype)
-        if prior_model is not None:
-            raise NotImplementedError("prior models are outside the accelerated energy+force path of this build")
-        self.prior_model = None
+        from ..priors.atomref import Atomref, BasePrior
+        if isinstance(prior_model, BasePrior):
+            prior_model = [prior_model]
+        if prior_model is not None and not all(isinstance(p, Atomref) for p in prior_model):
+            raise NotImplementedError("only the Atomref prior is built (pairwise priors are outside this build)")
+        self.prior_model = None if not prior_model else nn.ModuleList(prior_model).to(dtype=dtype)
         self.derivative = derivative
         mean = torch.scalar_tensor(0) if mean is None else mean
         self.register_buffer("mean", mean.to(dtype=dtype))
@@ -117,13 +155,24 @@ class TorchMD_Net(nn.Module):
         mean, std = self._mean_std()
         y, neg_dy, _ = self.representation_model.energy_forces(z, pos, batch, n_mol, self.output_model, mean, std,
                                                                 compute_forces=self.derivative)
-        return y, (neg_dy if self.derivative else None)
+        return self.apply_priors(y, z, batch, n_mol), (neg_dy if self.derivative else None)
+
+    def apply_priors(self, y: Tensor, z: Tensor, batch: Tensor, n_mol: int) -> Tensor:
+        """Atom-wise reference energies (Atomref.pre_reduce + reduce, model.py:266-272): position independent, so the
+        forces of the fused call stand as they are."""
+        if self.prior_model is not None:
+            for prior in self.prior_model:
+                y = y + prior.molecular_sum(z, batch, n_mol).to(y.dtype)
+        return y
 
     def __prepare_scriptable__(self):
         """``torch.jit.script(model)`` compiles this stand-in (models/scripted.py): one flat weight buffer + the fused op.
         The weights are packed as they are now; script again after changing them."""
         from .. import _native
         from .scripted import ScriptableTorchMD_Net
+        if self.prior_model is not None:
+            raise NotImplementedError("scripting a model with a prior is not built; fold the atom references into the "
+                                      "checkpoint's mean or evaluate the eager model")
         _native.load()
         return ScriptableTorchMD_Net(self)
 
