@@ -286,6 +286,24 @@ int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_ato
                                     int64_t n_mol, int strategy, const double box[9], const char* name,
                                     size_t* offset, size_t* bytes);
 
+/* ---------------------------------------------------------------- pairwise priors: energy + analytic forces (fp32)
+ * ZBL.post_reduce (torchmdnet/priors/zbl.py:47-63) and Coulomb.post_reduce (priors/coulomb.py:38-50) plus the autograd pass
+ * that differentiates them (models/model.py:286-298), on the pair set of the legacy Distance module (models/utils.py:393-455:
+ * open boundaries, both directions, no self pairs): the neighbour search runs inside the call (brute strategy, the prior's
+ * own cutoff; Coulomb has none: every pair of a molecule).
+ *   energy[m] += 0.5 * energy_prefactor * sum_{pairs of m} V(d);   forces[i] -= dE/dpos_i   (forces may be NULL)
+ *   ZBL:     V = phi(d * distance_scale / a_ij) * C(d; cutoff) * Z_i Z_j / d,  weight[i] = atomic number of atom i
+ *   Coulomb: V = erf(alpha d) q_i q_j / (1e9 distance_scale d),               weight[i] = partial charge of atom i
+ * energy_prefactor = 2.30707755e-28 / energy_scale / distance_scale (the caller's unit conversion, zbl.py:58).
+ * *num_found = directed pairs + n_atoms self entries found; if it exceeds max_edges the pair set was truncated (the
+ * reference asserts in that case, models/utils.py:419-425; the host side raises). */
+enum { TMDN_PRIOR_ZBL = 0, TMDN_PRIOR_COULOMB = 1 };
+size_t tmdn_pair_prior_workspace_bytes(int64_t n_atoms, int64_t max_edges);
+int tmdn_pair_prior_f32(int kind, const float* pos, const int64_t* batch, const float* weight, int64_t n_atoms,
+                        int64_t n_mol, double cutoff, double energy_prefactor, double distance_scale, double alpha,
+                        int64_t max_edges, float* energy, float* forces, int32_t* num_found, void* workspace,
+                        size_t workspace_bytes, tmdn_stream_t stream);
+
 /* ---------------------------------------------------------------- Equivariant Transformer energy + forces (fp32)
  * TorchMD_ET.forward + NeighborEmbedding + EquivariantMultiHeadAttention + EquivariantScalar head + force path
  * (torchmdnet/models/torchmd_et.py:154-187,272-347; models/utils.py:73-108,496-522; models/output_modules.py:111-115).
@@ -337,6 +355,47 @@ int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, const float*
                           int64_t max_edges, float* energy, float* forces, int32_t* status, void* workspace,
                           size_t workspace_bytes, tmdn_stream_t stream);
 int tmdn_et_workspace_lookup(const tmdn_et_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol, int strategy,
+                             const double box[9], const char* name, size_t* offset, size_t* bytes);
+
+/* ---------------------------------------------------------------- Graph network (TorchMD_GN) energy + forces (fp32)
+ * TorchMD_GN.forward + NeighborEmbedding + InteractionBlock / CFConv + Scalar head + force path
+ * (torchmdnet/models/torchmd_gn.py:148-290; models/utils.py:73-108; models/output_modules.py:49-77; model.py:286-298):
+ *   x = emb(z) [-> neighbour embedding];  per layer: h = lin1 x;  agg_i = sum_{j != i, d_ij < r_c} W(d_ij) * h_j,
+ *   W(d) = mlp(rbf(d)) C(d);  x += lin(act(lin2 agg));  e_i = (w2 . act(W1 x + b1) + b2) std;  y = sum e_i + mean.
+ * The pair set is the one of the reference's legacy Distance module (no self pairs); aggr = "add" only.  The filters are
+ * univariate in d and are passed as cubic Hermite tables on the grid of tmdn_filter_set:
+ *   layer table [n_int][F] float4 : mlp(rbf(d)) * C(d);   ne_table [n_int][H] float4 : distance_proj(rbf(d)) * C(d).
+ * "T" = transposed copy for the backward GEMMs.  hidden, num_filters: multiples of 32 in [32,1024]. */
+typedef struct tmdn_gn_layer {
+    const float *lin1_w, *lin1_wT;          /* conv.lin1 [F,H] (no bias), [H,F] */
+    const float* table;
+    const float *lin2_w, *lin2_b, *lin2_wT; /* conv.lin2 [H,F], [H], [F,H] */
+    const float *lin_w, *lin_b, *lin_wT;    /* lin [H,H], [H], [H,H] */
+} tmdn_gn_layer;
+
+typedef struct tmdn_gn_model {
+    int32_t hidden, num_filters, num_layers, max_z;
+    int32_t activation, has_neighbor_embedding, n_int, gemm_mode;
+    float cutoff_lower, cutoff_upper, mean, std;
+    float grid_alpha, grid_gamma;
+    const float* emb;                       /* embedding [max_z,H] */
+    const float *ne_emb, *ne_table;         /* neighbor_embedding.embedding [max_z,H], filter table */
+    const float *ne_comb_w, *ne_comb_b;     /* combine [H,2H], [H] */
+    const float* ne_comb_w2T;               /* (combine.weight[:, H:])^T [H,H] */
+    tmdn_gn_layer layer[TMDN_MAX_LAYERS];
+    const float *head_w1, *head_b1, *head_w1T;   /* output_network.0 [H/2,H], [H/2], [H,H/2] */
+    const float *head_w2, *head_b2;              /* output_network.2 [1,H/2], [1] */
+} tmdn_gn_model;
+
+size_t tmdn_gn_workspace_bytes(const tmdn_gn_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol, int strategy,
+                               const double box[9]);
+/* Same contract as tmdn_tensornet_energy_forces (status, NaN poisoning, sorted batch, max_edges incl. one self entry
+ * per atom: (max_num_neighbors + 1) * n_atoms covers the reference's per-atom budget). */
+int tmdn_gn_energy_forces(const tmdn_gn_model* m, const int64_t* z, const float* pos, const int64_t* batch,
+                          int64_t n_atoms, int64_t n_mol, const double box[9], int use_periodic, int strategy,
+                          int64_t max_edges, float* energy, float* forces, int32_t* status, void* workspace,
+                          size_t workspace_bytes, tmdn_stream_t stream);
+int tmdn_gn_workspace_lookup(const tmdn_gn_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol, int strategy,
                              const double box[9], const char* name, size_t* offset, size_t* bytes);
 
 #ifdef __cplusplus

@@ -136,3 +136,31 @@ def test_atomref_prior_matches_reference(tmp_path):
     y1, f1 = m1(z[:n0], pos[:n0])
     torch.testing.assert_close(e, y1, rtol=1e-5, atol=1e-5)
     torch.testing.assert_close(frc.view(n0, 3), f1, rtol=0, atol=1e-5)
+
+
+def test_pairwise_priors_match_reference():
+    """TensorNet + ZBL + Coulomb against the fixture written by the unmodified reference (priors/zbl.py, priors/coulomb.py;
+    forces from its autograd pass).  The prior part is two orders of magnitude larger than the network's output in this
+    fixture, so the check is on the priors; energies 1e-5 relative, forces 1e-4 absolute + 2e-6 relative (|F| up to 44)."""
+    g, m = _small("small_tensornet_pairpriors.npz")
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    q = tt(g["partial_charges"]).cuda()
+    y, f = m(z, pos, batch, extra_args={"partial_charges": q})
+    y_ref, f_ref = torch.as_tensor(g["y"]).double(), torch.as_tensor(g["forces"]).double()
+    assert float(((y.cpu().double() - y_ref).abs() / y_ref.abs().clamp_min(1.0)).max()) <= 1e-5
+    assert float(((f.cpu().double() - f_ref).abs() - 2e-6 * f_ref.abs()).max()) <= 1e-4
+    # the priors' share, against the reference's run without them
+    m.prior_model = None
+    y0, f0 = m(z, pos, batch)
+    check(y0, f0, g["y_noprior"], g["forces_noprior"])
+    dy = (y - y0).cpu().double()
+    dy_ref = torch.as_tensor(g["y"]).double() - torch.as_tensor(g["y_noprior"]).double()
+    assert float(((dy - dy_ref).abs() / dy_ref.abs().clamp_min(1.0)).max()) <= 1e-5
+    # Coulomb without charges is an error, as in the reference (KeyError on extra_args)
+    g2, m2 = _small("small_tensornet_pairpriors.npz")
+    with pytest.raises((KeyError, TypeError)):
+        m2(z, pos, batch)
+    # too small a neighbour budget is caught (models/utils.py:419-425 asserts)
+    m2.prior_model[0].max_num_neighbors = 1
+    with pytest.raises(AssertionError, match="max_num_neighbors"):
+        m2(z, pos, batch, extra_args={"partial_charges": q})

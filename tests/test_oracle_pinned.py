@@ -16,7 +16,7 @@ from oracle import neighbors as onb
 RTOL, ATOL = 1.3e-6, 1e-5
 
 
-@pytest.mark.parametrize("name", SMALL + ["small_tensornet_periodic.npz"])
+@pytest.mark.parametrize("name", SMALL + ["small_tensornet_periodic.npz", "small_gn_ne.npz", "small_gn_plain.npz"])
 def test_oracle_matches_reference_small_models(name):
     g = load_npz(name)
     box = tt(g["box"]) if "box" in g else None
@@ -52,3 +52,31 @@ def test_neighbor_backward_restatement_matches_autograd():
     loss = (v[nz] * torch.from_numpy(gd)[nz]).sum() + (w * torch.from_numpy(gw)[nz]).sum()
     loss.backward()
     np.testing.assert_allclose(onb.neighbor_backward(nb, dl, ds, gd, gw, 30), p.grad.numpy(), atol=1e-10)
+
+
+def test_oracle_matches_reference_graph_network_goldens():
+    """The graph-network restatement against the reference's own golden row (tests/expected.pkl graph-network/Scalar,
+    numbers in tests/golden/expected_pkl_gn.json) and the full-size fixture model_GN.npz; weights = seeded create_model of
+    this package, whose initial values are checked against the reference's checksums."""
+    import json
+    import random
+    from torchmdnet.models.model import create_model
+    with open(os.path.join(GOLDEN, "expected_pkl_gn.json")) as fh:
+        e = json.load(fh)["graph-network"]
+    for hp, seed, z, pos, batch, y_ref, f_ref, sums in (
+            (e["hparams"], 1234, torch.tensor(e["z"]), torch.tensor(e["pos"]), torch.tensor(e["batch"]),
+             torch.tensor(e["expected_pred"]), torch.tensor(e["expected_deriv"]), e["checksums"]),) + tuple(
+            (g["hparams"], int(g["seed"]), tt(g["z"]), tt(g["pos"]), tt(g["batch"]), tt(g["y"]), tt(g["forces"]), g["checksums"])
+            for g in [load_npz("model_GN.npz")]):
+        random.seed(seed)
+        np.random.seed(seed)
+        torch.manual_seed(seed)
+        m = create_model(hp)
+        sd = m.state_dict()
+        assert set(sd) == set(sums)
+        for k, v in sd.items():
+            assert abs(float(v.double().sum()) - sums[k][0]) <= 1e-5 * max(1.0, abs(sums[k][0])), k
+            assert abs(float(v.double().abs().sum()) - sums[k][1]) <= 1e-5 * max(1.0, sums[k][1]), k
+        y, f = om.energy_forces({k: v.detach() for k, v in sd.items()}, hp, z, pos, batch)
+        torch.testing.assert_close(y, y_ref, rtol=RTOL, atol=ATOL)
+        torch.testing.assert_close(f, f_ref, rtol=1e-5, atol=ATOL)

@@ -20,7 +20,7 @@ SHIM = os.path.join(LIBDIR, "libtmdn_torch.so")
 CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
 NVCC = os.path.join(CUDA_HOME, "bin", "nvcc")
 
-CU_SOURCES = ["scan.cu", "neighbors.cu", "csr.cu", "csr_direct.cu", "halo.cu", "tensornet.cu", "et.cu"]
+CU_SOURCES = ["scan.cu", "neighbors.cu", "csr.cu", "csr_direct.cu", "halo.cu", "pair_prior.cu", "tensornet.cu", "et.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--threads", "4"]
 

@@ -848,3 +848,279 @@ extern "C" int tmdn_et_energy_forces(const tmdn_et_model* m, const int64_t* z, c
     }
     return TMDN_OK;
 }
+
+// ====================================================================================================================
+// Graph network (TorchMD_GN): torchmdnet/models/torchmd_gn.py:148-290.  Shares the embedding / neighbour-embedding
+// kernels, the table lookup, the head and the force write-out with the transformer above; what is specific are the two
+// CFConv edge kernels.  Stage list (names = workspace buffers):
+//   x0 = emb(z) [NE]; per layer l: h_l = lin1 x_l; agg = conv(h_l); a2_l = act(m2_l = lin2 agg + b); x_{l+1} = x_l + lin a2_l + b
+//   h3 = W1 x_L + b1; a3 = act(h3); e_i = (w2 . a3 + b2) std
+// backward: d3 = std w2 act'(h3); g_x = d3 W1; per layer (reverse): g_m = (g_x lin_w) act'(m2_l); g_agg = g_m lin2_w;
+//   conv adjoint -> g_h, gpos; g_x += g_h lin1_w;  then the neighbour-embedding adjoint and the force write-out.
+namespace {
+
+// agg[i,f] = sum_{e in row i, j != i} W(d_e)[f] * h[j,f]                          (CFConv.message / aggregate, "add")
+__global__ void __launch_bounds__(1024)
+gn_conv_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
+            const float* __restrict__ h, int N, int F, float* __restrict__ agg) {
+    pdl_sync();
+    extern __shared__ float smem[];
+    float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
+    const int f = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    float acc[1] = {0.f};
+    if (valid) {
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0 + sl; e < r1; e += S) {
+            const int j = col[e];
+            if (j == i) continue;
+            float w[1], dw[1];
+            tab_eval<1>(tb, geom[e].w, F, f, w, dw);
+            acc[0] += w[0] * h[(size_t)j * F + f];
+        }
+    }
+    slice_reduce<1>(acc, s_part, F);
+    if (valid && sl == 0) agg[(size_t)i * F + f] = acc[0];
+}
+
+// adjoint, in row i of the symmetric pair set:  g_h[i,f] = sum_e W(d_e)[f] g_agg[j,f]
+//   dE/dpos_i += u_e * sum_f W'(d_e)[f] (g_agg[i,f] h[j,f] + g_agg[j,f] h[i,f])       (both directions of the pair)
+__global__ void __launch_bounds__(1024)
+gn_conv_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
+            const float* __restrict__ h, const float* __restrict__ g_agg, int N, int F, float* __restrict__ g_h,
+            float* __restrict__ gpos) {
+    pdl_sync();
+    extern __shared__ float smem[];
+    float* s_red = smem;
+    float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
+    const int f = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    float acc[1] = {0.f};
+    float gp[3] = {0.f, 0.f, 0.f};
+    if (valid) {
+        const float hi_ = h[(size_t)i * F + f], gi = g_agg[(size_t)i * F + f];
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0 + sl; e < r1; e += S) {
+            const int j = col[e];
+            if (j == i) continue;
+            const float4 g = geom[e];
+            float w[1], dw[1];
+            tab_eval<1>(tb, g.w, F, f, w, dw);
+            const float gj = g_agg[(size_t)j * F + f];
+            acc[0] += w[0] * gj;
+            const float gd = dw[0] * (gi * h[(size_t)j * F + f] + gj * hi_);
+            gp[0] += g.x * gd; gp[1] += g.y * gd; gp[2] += g.z * gd;
+        }
+    }
+    slice_reduce<1>(acc, s_part, F);
+    if (valid && sl == 0) g_h[(size_t)i * F + f] = acc[0];
+    atom_reduce<3>(gp, s_red);
+    if (valid && f == 0 && sl == 0) {
+        gpos[3 * (size_t)i] += gp[0];
+        gpos[3 * (size_t)i + 1] += gp[1];
+        gpos[3 * (size_t)i + 2] += gp[2];
+    }
+}
+
+struct GnWs {
+    int32_t *num_found, *row_ptr, *col;
+    float* geom;
+    int* z32;
+    void* graph_ws;
+    size_t graph_ws_bytes;
+    float *cat0, *X[TMDN_MAX_LAYERS + 1], *Hh[TMDN_MAX_LAYERS], *M2[TMDN_MAX_LAYERS], *A2[TMDN_MAX_LAYERS], *agg, *h3, *a3,
+        *e_atom, *d3, *g_x, *g_m, *g_agg, *g_h, *g_xn, *gpos;
+};
+
+int carve_gn(Arena& a, const tmdn_gn_model* m, int64_t N, int64_t P, GnWs& w, std::vector<EtEntry>* names,
+             const double* box, int strategy) {
+    const size_t H = m->hidden, F = m->num_filters, L = m->num_layers, n = (size_t)N, H2 = H / 2;
+    char buf[32];
+    w.num_found = ecarve<int32_t>(a, names, "num_found", 4);
+    w.row_ptr = ecarve<int32_t>(a, names, "row_ptr", n + 1);
+    w.col = ecarve<int32_t>(a, names, "col", (size_t)P);
+    w.geom = ecarve<float>(a, names, "geom", 4 * (size_t)P);
+    w.z32 = ecarve<int>(a, names, "z32", n);
+    w.graph_ws_bytes = tmdn_csr_build_workspace_bytes(strategy, N, box, m->cutoff_upper);
+    if (w.graph_ws_bytes == 0) {
+        tmdn_set_error("gn: bad box for the cell strategy");
+        return TMDN_EINVAL;
+    }
+    w.graph_ws = ecarve<char>(a, names, "graph_ws", w.graph_ws_bytes);
+    w.cat0 = ecarve<float>(a, names, "cat0", n * 2 * H);
+    for (size_t l = 0; l <= L; ++l) { snprintf(buf, sizeof buf, "x%zu", l); w.X[l] = ecarve<float>(a, names, buf, n * H); }
+    for (size_t l = 0; l < L; ++l) {
+        snprintf(buf, sizeof buf, "h%zu", l); w.Hh[l] = ecarve<float>(a, names, buf, n * F);
+        snprintf(buf, sizeof buf, "m2_%zu", l); w.M2[l] = ecarve<float>(a, names, buf, n * H);
+        snprintf(buf, sizeof buf, "a2_%zu", l); w.A2[l] = ecarve<float>(a, names, buf, n * H);
+    }
+    w.agg = ecarve<float>(a, names, "agg", n * F);
+    w.h3 = ecarve<float>(a, names, "h3", n * H2);
+    w.a3 = ecarve<float>(a, names, "a3", n * H2);
+    w.e_atom = ecarve<float>(a, names, "e_atom", n);
+    w.d3 = ecarve<float>(a, names, "d3", n * H2);
+    w.g_x = ecarve<float>(a, names, "g_x", n * H);
+    w.g_m = ecarve<float>(a, names, "g_m", n * H);
+    w.g_agg = ecarve<float>(a, names, "g_agg", n * F);
+    w.g_h = ecarve<float>(a, names, "g_h", n * F);
+    w.g_xn = ecarve<float>(a, names, "g_xn", n * H);
+    w.gpos = ecarve<float>(a, names, "gpos", n * 3);
+    return TMDN_OK;
+}
+
+int check_gn(const tmdn_gn_model* m) {
+    TMDN_CHECK_ARG(m, "gn: null model");
+    TMDN_CHECK_ARG(m->hidden >= 32 && m->hidden <= 1024 && m->hidden % 32 == 0,
+                   "gn: hidden_channels must be a multiple of 32 in [32,1024] (got %d)", m->hidden);
+    TMDN_CHECK_ARG(m->num_filters >= 32 && m->num_filters <= 1024 && m->num_filters % 32 == 0,
+                   "gn: num_filters must be a multiple of 32 in [32,1024] (got %d)", m->num_filters);
+    TMDN_CHECK_ARG(m->num_layers >= 0 && m->num_layers <= TMDN_MAX_LAYERS, "gn: num_layers out of range");
+    TMDN_CHECK_ARG(m->max_z > 0 && m->n_int > 0, "gn: bad max_z / table size");
+    TMDN_CHECK_ARG(m->cutoff_upper > m->cutoff_lower && m->cutoff_lower >= 0, "gn: bad cutoffs");
+    TMDN_CHECK_ARG(m->emb && m->head_w1 && m->head_w2 && m->head_w1T, "gn: missing weights");
+    for (int l = 0; l < m->num_layers; ++l)
+        TMDN_CHECK_ARG(m->layer[l].table && m->layer[l].lin1_w && m->layer[l].lin2_w && m->layer[l].lin_w,
+                       "gn: missing weights of layer %d", l);
+    if (m->has_neighbor_embedding) TMDN_CHECK_ARG(m->ne_emb && m->ne_table && m->ne_comb_w, "gn: missing NE weights");
+    return TMDN_OK;
+}
+}  // namespace
+
+extern "C" size_t tmdn_gn_workspace_bytes(const tmdn_gn_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                          int strategy, const double box[9]) {
+    (void)n_mol;
+    if (check_gn(m) != TMDN_OK || n_atoms <= 0 || max_edges <= 0) return 0;
+    Arena a(nullptr, 0);
+    GnWs w;
+    if (carve_gn(a, m, n_atoms, max_edges, w, nullptr, box, strategy) != TMDN_OK) return 0;
+    return a.off + 256;
+}
+
+extern "C" int tmdn_gn_workspace_lookup(const tmdn_gn_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                        int strategy, const double box[9], const char* name, size_t* offset,
+                                        size_t* bytes) {
+    (void)n_mol;
+    TMDN_TRY(check_gn(m));
+    TMDN_CHECK_ARG(name && offset && bytes, "lookup: null argument");
+    Arena a(nullptr, 0);
+    GnWs w;
+    std::vector<EtEntry> names;
+    TMDN_TRY(carve_gn(a, m, n_atoms, max_edges, w, &names, box, strategy));
+    for (const auto& e : names)
+        if (e.name == name) {
+            *offset = e.off;
+            *bytes = e.bytes;
+            return TMDN_OK;
+        }
+    tmdn_set_error("lookup: unknown buffer '%s'", name);
+    return TMDN_EINVAL;
+}
+
+extern "C" int tmdn_gn_energy_forces(const tmdn_gn_model* m, const int64_t* z, const float* pos, const int64_t* batch,
+                                     int64_t n_atoms, int64_t n_mol, const double box[9], int use_periodic,
+                                     int strategy, int64_t max_edges, float* energy, float* forces, int32_t* status,
+                                     void* workspace, size_t workspace_bytes, tmdn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    TMDN_TRY(check_gn(m));
+    TMDN_CHECK_ARG(z && pos && batch && energy && status && workspace, "gn: null pointer argument");
+    TMDN_CHECK_ARG(n_atoms > 0 && n_mol > 0 && max_edges > 0, "gn: bad sizes");
+    TMDN_CHECK_ARG(max_edges < (1LL << 31) && n_atoms < (1LL << 31) / 16, "gn: sizes exceed int32 indexing");
+    TMDN_CHECK_ARG(strategy != TMDN_CELL || box, "gn: the cell strategy needs a box");
+    const int N = (int)n_atoms, H = m->hidden, F = m->num_filters, L = m->num_layers, act = m->activation, H2 = H / 2;
+    const bool tc = m->gemm_mode == TMDN_GEMM_TF32X3;
+    const int64_t P = max_edges;
+    const float lo = m->cutoff_lower, hi = m->cutoff_upper;
+    Arena arena(workspace, workspace_bytes);
+    GnWs w;
+    TMDN_TRY(carve_gn(arena, m, n_atoms, P, w, nullptr, box, strategy));
+    if (!arena.ok) {
+        tmdn_set_error("gn: workspace too small (%zu < %zu)", workspace_bytes, arena.off);
+        return TMDN_EWORKSPACE;
+    }
+    {
+        KTimer ktimer__("neighbors_csr", stream);
+        TMDN_TRY(tmdn_csr_build_f32(strategy, pos, batch, n_atoms, box, use_periodic, lo, hi, P, w.row_ptr, w.col, w.geom,
+                                    w.num_found, w.graph_ws, w.graph_ws_bytes, stream_));
+    }
+    TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
+    ET_K("et_prep", launch_k(et_prep_kernel, (unsigned)cdiv(N, 256), 256, 0, stream, z, w.z32, N, m->max_z, w.num_found,
+                             (long long)P, status, batch));
+    const float4* geom = (const float4*)w.geom;
+    const TabGrid tgrid = make_tab_grid(m->n_int, hi, m->grid_alpha, m->grid_gamma);
+    const Tab ne_tab{(const float4*)m->ne_table, tgrid};
+    const EdgeLaunch e1 = edge_launch(N, H, 1024, 1), ef = edge_launch(N, F, 1024, 1), e8 = edge_launch(N, H, 512, 8);
+    const unsigned hgrid = (unsigned)cdiv((long long)N * H2, 256);
+
+    // ---- embedding (+ neighbour embedding)
+    if (m->has_neighbor_embedding) {
+        ET_K("et_embed_fwd", launch_k(et_embed_fwd<true>, e1.grid, e1.block, e1.smem, stream, w.row_ptr, w.col, geom, w.z32,
+                                      m->emb, m->ne_emb, ne_tab, N, H, w.cat0, 2 * H));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.cat0, 2 * H, m->ne_comb_w, m->ne_comb_b, w.X[0], H, N, H, 2 * H), stream, tc));
+    } else {
+        ET_K("et_embed_fwd", launch_k(et_embed_fwd<false>, e1.grid, e1.block, e1.smem, stream, w.row_ptr, w.col, geom, w.z32,
+                                      m->emb, nullptr, ne_tab, N, H, w.X[0], H));
+    }
+    // ---- interaction blocks
+    for (int l = 0; l < L; ++l) {
+        const tmdn_gn_layer& ly = m->layer[l];
+        const Tab tb{(const float4*)ly.table, tgrid};
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.X[l], H, ly.lin1_w, nullptr, w.Hh[l], F, N, F, H), stream, tc));
+        ET_K("gn_conv_fwd", launch_k(gn_conv_fwd, ef.grid, ef.block, ef.smem, stream, w.row_ptr, w.col, geom, tb, w.Hh[l], N, F,
+                                     w.agg));
+        {
+            GemmP p = gemm_desc(w.agg, F, ly.lin2_w, ly.lin2_b, w.A2[l], H, N, H, F);
+            p.C2 = w.M2[l]; p.act = act;
+            TMDN_TRY(node_gemm1(EPI_ACT, p, stream, tc));
+        }
+        TMDN_CUDA(cudaMemcpyAsync(w.X[l + 1], w.X[l], sizeof(float) * (size_t)N * H, cudaMemcpyDeviceToDevice, stream));
+        {
+            GemmP p = gemm_desc(w.A2[l], H, ly.lin_w, ly.lin_b, w.X[l + 1], H, N, H, H);
+            p.accumulate = 1;
+            TMDN_TRY(node_gemm1(EPI_NONE, p, stream, tc));
+        }
+    }
+    // ---- Scalar head (output_modules.py:49-77) and molecular sums
+    {
+        GemmP p = gemm_desc(w.X[L], H, m->head_w1, m->head_b1, w.a3, H2, N, H2, H);
+        p.C2 = w.h3; p.act = act;
+        TMDN_TRY(node_gemm1(EPI_ACT, p, stream, tc));
+    }
+    ET_K("et_head_energy", launch_k(et_head_energy, (unsigned)cdiv(N, 4), 128, 0, stream, w.a3, m->head_w2, m->head_b2, m->std,
+                                    w.e_atom, N, H2));
+    ET_K("et_mol_reduce", launch_k(et_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy, status));
+    if (!forces) return TMDN_OK;
+
+    // ---- backward
+    TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
+    ET_K("et_head_seed_bwd", launch_k(et_head_seed_bwd, hgrid, 256, 0, stream, w.h3, m->head_w2, m->std, act, w.d3,
+                                      (long long)N * H2, H2));
+    TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.d3, H2, m->head_w1T, nullptr, w.g_x, H, N, H, H2), stream, tc));
+    for (int l = L - 1; l >= 0; --l) {
+        const tmdn_gn_layer& ly = m->layer[l];
+        const Tab tb{(const float4*)ly.table, tgrid};
+        {
+            GemmP p = gemm_desc(w.g_x, H, ly.lin_wT, nullptr, w.g_m, H, N, H, H);
+            p.aux = w.M2[l]; p.ldaux = H; p.act = act;
+            TMDN_TRY(node_gemm1(EPI_MULGRAD, p, stream, tc));
+        }
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_m, H, ly.lin2_wT, nullptr, w.g_agg, F, N, F, H), stream, tc));
+        ET_K("gn_conv_bwd", launch_k(gn_conv_bwd, ef.grid, ef.block, ef.smem, stream, w.row_ptr, w.col, geom, tb, w.Hh[l],
+                                     w.g_agg, N, F, w.g_h, w.gpos));
+        {
+            GemmP p = gemm_desc(w.g_h, F, ly.lin1_wT, nullptr, w.g_x, H, N, H, F);
+            p.accumulate = 1;
+            TMDN_TRY(node_gemm1(EPI_NONE, p, stream, tc));
+        }
+    }
+    if (m->has_neighbor_embedding) {
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_x, H, m->ne_comb_w2T, nullptr, w.g_xn, H, N, H, H), stream, tc));
+        ET_K("et_final_bwd", launch_k(et_final_bwd<true>, e8.grid, e8.block, e8.smem, stream, w.row_ptr, w.col, geom, w.z32,
+                                      m->ne_emb, ne_tab, w.g_xn, w.gpos, forces, N, H, status));
+    } else {
+        ET_K("et_final_bwd", launch_k(et_final_bwd<false>, e8.grid, e8.block, e8.smem, stream, w.row_ptr, w.col, geom, w.z32,
+                                      nullptr, ne_tab, nullptr, w.gpos, forces, N, H, status));
+    }
+    return TMDN_OK;
+}

@@ -485,6 +485,109 @@ std::vector<int64_t> et_debug_lookup(int64_t handle, int64_t n_atoms, int64_t ma
     return {(int64_t)off, (int64_t)bytes};
 }
 
+// ------------------------------------------------------------------ graph network (TorchMD_GN) model handles
+struct GnHandle {
+    tmdn_gn_model m;
+    std::vector<Tensor> keep;
+};
+std::unordered_map<int64_t, std::shared_ptr<GnHandle>> g_gn;
+
+// Weight order (must match torchmdnet/models/torchmd_gn.py::pack_weights):
+//   emb ne_emb ne_table ne_comb_w ne_comb_b ne_comb_w2T head_w1 head_b1 head_w1T head_w2 head_b2
+//   per layer: lin1_w lin1_wT table lin2_w lin2_b lin2_wT lin_w lin_b lin_wT
+// iparams: hidden num_filters num_layers max_z activation has_ne n_int gemm_mode ; fparams: lo hi mean std grid_alpha grid_gamma
+int64_t gn_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::vector<double> fp) {
+    TORCH_CHECK(ip.size() == 8 && fp.size() == 6, "gn_create: bad parameter vectors");
+    auto h = std::make_shared<GnHandle>();
+    tmdn_gn_model& m = h->m;
+    memset(&m, 0, sizeof(m));
+    m.hidden = (int32_t)ip[0]; m.num_filters = (int32_t)ip[1]; m.num_layers = (int32_t)ip[2]; m.max_z = (int32_t)ip[3];
+    m.activation = (int32_t)ip[4]; m.has_neighbor_embedding = (int32_t)ip[5]; m.n_int = (int32_t)ip[6];
+    m.gemm_mode = (int32_t)ip[7];
+    m.cutoff_lower = (float)fp[0]; m.cutoff_upper = (float)fp[1]; m.mean = (float)fp[2]; m.std = (float)fp[3];
+    m.grid_alpha = (float)fp[4]; m.grid_gamma = (float)fp[5];
+    TORCH_CHECK(m.num_layers >= 0 && m.num_layers <= TMDN_MAX_LAYERS, "gn_create: too many layers");
+    const size_t expect = 11 + 9 * (size_t)m.num_layers;
+    TORCH_CHECK(w.size() == expect, "gn_create: expected ", expect, " weight tensors, got ", w.size());
+    size_t k = 0;
+    auto next = [&]() -> const float* { return fptr(w[k++]); };
+    m.emb = next(); m.ne_emb = next(); m.ne_table = next(); m.ne_comb_w = next(); m.ne_comb_b = next();
+    m.ne_comb_w2T = next();
+    m.head_w1 = next(); m.head_b1 = next(); m.head_w1T = next(); m.head_w2 = next(); m.head_b2 = next();
+    for (int l = 0; l < m.num_layers; ++l) {
+        tmdn_gn_layer& y = m.layer[l];
+        y.lin1_w = next(); y.lin1_wT = next(); y.table = next(); y.lin2_w = next(); y.lin2_b = next(); y.lin2_wT = next();
+        y.lin_w = next(); y.lin_b = next(); y.lin_wT = next();
+    }
+    h->keep = std::move(w);
+    std::lock_guard<std::mutex> lock(g_mu);
+    const int64_t id = g_next++;
+    g_gn[id] = h;
+    return id;
+}
+void gn_destroy(int64_t id) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    g_gn.erase(id);
+}
+std::shared_ptr<GnHandle> gn_get(int64_t id) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    auto it = g_gn.find(id);
+    TORCH_CHECK(it != g_gn.end(), "gn: unknown model handle ", id);
+    return it->second;
+}
+
+std::tuple<Tensor, Tensor, Tensor, Tensor> gn_energy_forces(int64_t handle, const Tensor& z, const Tensor& pos,
+                                                            const Tensor& batch, const Tensor& box_vectors,
+                                                            bool use_periodic, const std::string& strategy,
+                                                            int64_t max_edges, int64_t n_mol, bool compute_forces,
+                                                            const c10::optional<Tensor>& workspace) {
+    auto h = gn_get(handle);
+    TORCH_CHECK(pos.is_cuda(), "gn_energy_forces: CUDA tensors required (sm_100a build, no CPU fallback)");
+    TORCH_CHECK(pos.scalar_type() == at::kFloat && pos.dim() == 2 && pos.size(1) == 3 && pos.is_contiguous(),
+                "gn_energy_forces: pos must be a contiguous float32 [N,3] tensor");
+    TORCH_CHECK(z.scalar_type() == at::kLong && z.dim() == 1 && z.is_contiguous() && z.size(0) == pos.size(0),
+                "gn_energy_forces: z must be a contiguous int64 [N] tensor");
+    TORCH_CHECK(batch.scalar_type() == at::kLong && batch.dim() == 1 && batch.is_contiguous() &&
+                    batch.size(0) == pos.size(0),
+                "gn_energy_forces: batch must be a contiguous int64 [N] tensor");
+    TORCH_CHECK(z.device() == pos.device() && batch.device() == pos.device(), "gn_energy_forces: device mismatch");
+    TORCH_CHECK(h->keep.empty() || h->keep[0].device() == pos.device(),
+                "gn_energy_forces: the model was packed on ", h->keep[0].device(), " but pos is on ", pos.device());
+    const c10::cuda::CUDAGuard guard(pos.device());
+    const int64_t n = pos.size(0);
+    const int sid = strategy_id(strategy);
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    TORCH_CHECK(have_box || !(use_periodic || sid == TMDN_CELL), "gn_energy_forces: box required");
+    const size_t need = tmdn_gn_workspace_bytes(&h->m, n, max_edges, n_mol, sid, have_box ? box : nullptr);
+    TORCH_CHECK(need > 0, "gn_energy_forces: ", tmdn_last_error());
+    Tensor ws;
+    if (workspace.has_value() && workspace->defined() && (size_t)workspace->numel() >= need && workspace->is_cuda() &&
+        workspace->device() == pos.device() && workspace->scalar_type() == at::kByte)
+        ws = *workspace;
+    else
+        ws = at::empty({(int64_t)need}, pos.options().dtype(at::kByte));
+    Tensor energy = at::empty({n_mol, 1}, pos.options());
+    Tensor forces = compute_forces ? at::empty({n, 3}, pos.options()) : at::empty({0, 3}, pos.options());
+    Tensor status = at::empty({4}, pos.options().dtype(at::kInt));
+    TMDN_CALL(tmdn_gn_energy_forces(&h->m, z.data_ptr<int64_t>(), pos.data_ptr<float>(), batch.data_ptr<int64_t>(), n,
+                                    n_mol, have_box ? box : nullptr, use_periodic, sid, max_edges,
+                                    energy.data_ptr<float>(), compute_forces ? forces.data_ptr<float>() : nullptr,
+                                    status.data_ptr<int32_t>(), ws.data_ptr(), (size_t)ws.numel(), cur_stream()));
+    return std::make_tuple(energy, forces, status, ws);
+}
+
+std::vector<int64_t> gn_debug_lookup(int64_t handle, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                     const std::string& strategy, const Tensor& box_vectors, const std::string& name) {
+    auto h = gn_get(handle);
+    size_t off = 0, bytes = 0;
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    TMDN_CALL(tmdn_gn_workspace_lookup(&h->m, n_atoms, max_edges, n_mol, strategy_id(strategy),
+                                       have_box ? box : nullptr, name.c_str(), &off, &bytes));
+    return {(int64_t)off, (int64_t)bytes};
+}
+
 // ------------------------------------------------------------------ script-friendly entry points
 // A scripted / saved / re-loaded model cannot carry a process-local handle.  It carries ONE flat fp32 buffer with every
 // packed weight (segments aligned to 256 bytes; `offsets` has n_weights + 1 entries, in floats) plus the integer / float
@@ -517,11 +620,11 @@ PackedEntry& packed_entry(int kind, const Tensor& flat, const std::vector<int64_
         w.push_back(len > 0 ? flat.narrow(0, off, len) : at::empty({0}, flat.options()));
     }
     if (g_packed.size() >= 64) {            // stale versions of re-packed models: start over
-        for (auto& kv : g_packed) { g_tn.erase(kv.second.handle); g_et.erase(kv.second.handle); }
+        for (auto& kv : g_packed) { g_tn.erase(kv.second.handle); g_et.erase(kv.second.handle); g_gn.erase(kv.second.handle); }
         g_packed.clear();
     }
     lock.unlock();                          // *_create takes the lock itself
-    const int64_t h = kind == 0 ? tensornet_create(w, ip, fp) : et_create(w, ip, fp);
+    const int64_t h = kind == 0 ? tensornet_create(w, ip, fp) : kind == 1 ? et_create(w, ip, fp) : gn_create(w, ip, fp);
     lock.lock();
     return g_packed.emplace(key, PackedEntry{h, Tensor()}).first->second;
 }
@@ -551,6 +654,17 @@ std::tuple<Tensor, Tensor, Tensor> et_energy_forces_packed(
     int64_t max_edges, int64_t n_mol, bool compute_forces) {
     PackedEntry& e = packed_entry(1, flat, layout, ip, fp);
     auto r = et_energy_forces(e.handle, z, pos, batch, box_tensor(box), use_periodic, strategy, max_edges, n_mol,
+                              compute_forces, e.workspace.defined() ? c10::optional<Tensor>(e.workspace) : c10::nullopt);
+    e.workspace = std::get<3>(r);
+    return std::make_tuple(std::get<0>(r), std::get<1>(r), std::get<2>(r));
+}
+
+std::tuple<Tensor, Tensor, Tensor> gn_energy_forces_packed(
+    const Tensor& flat, std::vector<int64_t> layout, std::vector<int64_t> ip, std::vector<double> fp, const Tensor& z,
+    const Tensor& pos, const Tensor& batch, std::vector<double> box, bool use_periodic, const std::string& strategy,
+    int64_t max_edges, int64_t n_mol, bool compute_forces) {
+    PackedEntry& e = packed_entry(2, flat, layout, ip, fp);
+    auto r = gn_energy_forces(e.handle, z, pos, batch, box_tensor(box), use_periodic, strategy, max_edges, n_mol,
                               compute_forces, e.workspace.defined() ? c10::optional<Tensor>(e.workspace) : c10::nullopt);
     e.workspace = std::get<3>(r);
     return std::make_tuple(std::get<0>(r), std::get<1>(r), std::get<2>(r));
@@ -688,6 +802,35 @@ Tensor node_gemm(const Tensor& a, const Tensor& w, const c10::optional<Tensor>& 
     return c;
 }
 
+// energy[n_mol,1] and forces[N,3] are updated in place; -> num_found int32[1]
+Tensor pair_prior(const std::string& kind, const Tensor& pos, const Tensor& batch, const Tensor& weight, double cutoff,
+                  double energy_prefactor, double distance_scale, double alpha, int64_t max_edges, Tensor energy,
+                  const c10::optional<Tensor>& forces) {
+    check_input(pos, batch);
+    TORCH_CHECK(pos.scalar_type() == at::kFloat, "pair_prior: fp32 positions only");
+    TORCH_CHECK(weight.is_cuda() && weight.scalar_type() == at::kFloat && weight.is_contiguous() &&
+                    weight.numel() == pos.size(0), "pair_prior: weight must be a contiguous CUDA float32 [N] tensor");
+    TORCH_CHECK(energy.is_cuda() && energy.scalar_type() == at::kFloat && energy.is_contiguous(), "pair_prior: energy");
+    const int k = kind == "zbl" ? TMDN_PRIOR_ZBL : kind == "coulomb" ? TMDN_PRIOR_COULOMB : -1;
+    TORCH_CHECK(k >= 0, "pair_prior: unknown kind '", kind, "'");
+    float* fp = nullptr;
+    if (forces.has_value() && forces->defined() && forces->numel() > 0) {
+        TORCH_CHECK(forces->is_cuda() && forces->scalar_type() == at::kFloat && forces->is_contiguous() &&
+                        forces->numel() == 3 * pos.size(0), "pair_prior: forces must be a contiguous float32 [N,3] tensor");
+        fp = forces->data_ptr<float>();
+    }
+    const c10::cuda::CUDAGuard guard(pos.device());
+    const int64_t n = pos.size(0);
+    const size_t ws_bytes = tmdn_pair_prior_workspace_bytes(n, max_edges);
+    TORCH_CHECK(ws_bytes > 0, "pair_prior: bad sizes");
+    Tensor ws = at::empty({(int64_t)ws_bytes}, pos.options().dtype(at::kByte));
+    Tensor num = at::empty({1}, pos.options().dtype(at::kInt));
+    TMDN_CALL(tmdn_pair_prior_f32(k, pos.data_ptr<float>(), batch.data_ptr<int64_t>(), weight.data_ptr<float>(), n,
+                                  energy.numel(), cutoff, energy_prefactor, distance_scale, alpha, max_edges,
+                                  energy.data_ptr<float>(), fp, num.data_ptr<int32_t>(), ws.data_ptr(), ws_bytes, cur_stream()));
+    return num;
+}
+
 int64_t launch_count() { return (int64_t)tmdn_launch_count(); }
 int64_t set_tuning(std::string key, int64_t value) {
     const int old = tmdn_set_tuning(key.c_str(), (int)value);
@@ -733,6 +876,16 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
     m.def("et_energy_forces_packed(Tensor flat, int[] layout, int[] iparams, float[] fparams, Tensor z, Tensor pos, "
           "Tensor batch, float[] box, bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces) -> "
           "(Tensor, Tensor, Tensor)", et_energy_forces_packed);
+    m.def("gn_create(Tensor[] weights, int[] iparams, float[] fparams) -> int", gn_create);
+    m.def("gn_destroy(int handle) -> ()", gn_destroy);
+    m.def("gn_energy_forces(int handle, Tensor z, Tensor pos, Tensor batch, Tensor box_vectors, "
+          "bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces, Tensor? workspace) -> "
+          "(Tensor, Tensor, Tensor, Tensor)", gn_energy_forces);
+    m.def("gn_debug_lookup(int handle, int n_atoms, int max_edges, int n_mol, str strategy, Tensor box_vectors, "
+          "str name) -> int[]", gn_debug_lookup);
+    m.def("gn_energy_forces_packed(Tensor flat, int[] layout, int[] iparams, float[] fparams, Tensor z, Tensor pos, "
+          "Tensor batch, float[] box, bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces) -> "
+          "(Tensor, Tensor, Tensor)", gn_energy_forces_packed);
     m.def("et_create(Tensor[] weights, int[] iparams, float[] fparams) -> int", et_create);
     m.def("et_destroy(int handle) -> ()", et_destroy);
     m.def("et_energy_forces(int handle, Tensor z, Tensor pos, Tensor batch, Tensor box_vectors, "
@@ -754,6 +907,8 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
     m.def("halo_push(Tensor src, Tensor idx, Tensor seg, Tensor dst) -> ()", halo_push);
     m.def("channel_mix(Tensor x, Tensor w, Tensor? y, bool accumulate) -> Tensor", channel_mix);
     m.def("node_gemm(Tensor a, Tensor w, Tensor? bias, Tensor? c, bool accumulate) -> Tensor", node_gemm);
+    m.def("pair_prior(str kind, Tensor pos, Tensor batch, Tensor weight, float cutoff, float energy_prefactor, "
+          "float distance_scale, float alpha, int max_edges, Tensor(a!) energy, Tensor(b!)? forces) -> Tensor", pair_prior);
     m.def("launch_count() -> int", launch_count);
     m.def("set_tuning(str key, int value) -> int", set_tuning);
     m.def("profile_enable(bool on) -> ()", profile_enable);

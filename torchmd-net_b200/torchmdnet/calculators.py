@@ -53,7 +53,7 @@ class External:
         mean, std = m._mean_std()
         energy, forces, _ = m.representation_model.energy_forces(self.embeddings, pos, self.batch, self._n_mol,
                                                                  m.output_model, mean, std, compute_forces=True)
-        return m.apply_priors(energy, self.embeddings, self.batch, self._n_mol), forces
+        return m.apply_priors(energy, self.embeddings, self.batch, self._n_mol, pos, forces), forces
 
     def invalidate_graph(self):
         """Call after changing the model (weights, filter mode, distance module) to re-capture."""

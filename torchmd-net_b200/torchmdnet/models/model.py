@@ -38,9 +38,14 @@ def create_model(args, prior_model=None, mean=None, std=None):
         is_equivariant = False          # TensorNet always takes the plain Scalar head (model.py:79-80)
         representation_model = TensorNet(equivariance_invariance_group=args["equivariance_invariance_group"],
                                          **shared_args)
-    elif args["model"] in ("graph-network", "transformer"):
-        raise NotImplementedError('architecture "%s" is outside the accelerated energy+force path of this build '
-                                  "(equivariant-transformer and tensornet only)" % args["model"])
+    elif args["model"] == "graph-network":
+        from .torchmd_gn import TorchMD_GN
+        is_equivariant = False
+        representation_model = TorchMD_GN(num_filters=args["embedding_dimension"], aggr=args["aggr"],
+                                          neighbor_embedding=args["neighbor_embedding"], **shared_args)
+    elif args["model"] == "transformer":
+        raise NotImplementedError('architecture "transformer" (TorchMD_T) is outside this build '
+                                  "(equivariant-transformer, tensornet and graph-network are built)")
     else:
         raise ValueError(f'Unknown architecture: {args["model"]}')
     if args.get("atom_filter", -1) > -1:
@@ -62,7 +67,7 @@ def create_model(args, prior_model=None, mean=None, std=None):
 
 def create_prior_models(args, dataset=None):
     """Parse the ``prior_model`` option (str | dict | list of them, with ``prior_args``) as models/model.py:146-177.
-    Only ``Atomref`` is built here; the pairwise priors are refused."""
+    Built here: ``Atomref``, ``ZBL``, ``Coulomb``; ``D2`` is refused."""
     from .. import priors
     prior_models = []
     if args.get("prior_model"):
@@ -119,11 +124,11 @@ class TorchMD_Net(nn.Module):
         super().__init__()
         self.representation_model = representation_model.to(dtype=dtype)
         self.output_model = output_model.to(dtype=dtype)
-        from ..priors.atomref import Atomref, BasePrior
+        from ..priors import Atomref, BasePrior, Coulomb, ZBL
         if isinstance(prior_model, BasePrior):
             prior_model = [prior_model]
-        if prior_model is not None and not all(isinstance(p, Atomref) for p in prior_model):
-            raise NotImplementedError("only the Atomref prior is built (pairwise priors are outside this build)")
+        if prior_model is not None and not all(isinstance(p, (Atomref, ZBL, Coulomb)) for p in prior_model):
+            raise NotImplementedError("priors built here: Atomref, ZBL, Coulomb")
         self.prior_model = None if not prior_model else nn.ModuleList(prior_model).to(dtype=dtype)
         self.derivative = derivative
         mean = torch.scalar_tensor(0) if mean is None else mean
@@ -136,6 +141,9 @@ class TorchMD_Net(nn.Module):
     def reset_parameters(self):
         self.representation_model.reset_parameters()
         self.output_model.reset_parameters()
+        if self.prior_model is not None:          # model.py:224-226
+            for prior in self.prior_model:
+                prior.reset_parameters()
 
     def _mean_std(self):
         key = (self.mean.data_ptr(), self.mean._version, self.std.data_ptr(), self.std._version)
@@ -155,14 +163,21 @@ class TorchMD_Net(nn.Module):
         mean, std = self._mean_std()
         y, neg_dy, _ = self.representation_model.energy_forces(z, pos, batch, n_mol, self.output_model, mean, std,
                                                                 compute_forces=self.derivative)
-        return self.apply_priors(y, z, batch, n_mol), (neg_dy if self.derivative else None)
+        y = self.apply_priors(y, z, batch, n_mol, pos, neg_dy if self.derivative else None, extra_args)
+        return y, (neg_dy if self.derivative else None)
 
-    def apply_priors(self, y: Tensor, z: Tensor, batch: Tensor, n_mol: int) -> Tensor:
-        """Atom-wise reference energies (Atomref.pre_reduce + reduce, model.py:266-272): position independent, so the
-        forces of the fused call stand as they are."""
+    def apply_priors(self, y: Tensor, z: Tensor, batch: Tensor, n_mol: int, pos: Optional[Tensor] = None,
+                     forces: Optional[Tensor] = None, extra_args: Optional[Dict[str, Tensor]] = None) -> Tensor:
+        """Priors on top of the fused call's output.  Atom-wise reference energies (Atomref.pre_reduce + reduce,
+        model.py:266-272) are position independent: forces stand as they are.  Pairwise priors (post_reduce,
+        model.py:281-284) add their energy to ``y`` and their analytic forces to ``forces`` in place."""
         if self.prior_model is not None:
+            from ..priors import Atomref
             for prior in self.prior_model:
-                y = y + prior.molecular_sum(z, batch, n_mol).to(y.dtype)
+                if isinstance(prior, Atomref):
+                    y = y + prior.molecular_sum(z, batch, n_mol).to(y.dtype)
+                else:
+                    y = prior.add_energy_forces(y.contiguous(), forces, z, pos, batch, extra_args)
         return y
 
     def __prepare_scriptable__(self):

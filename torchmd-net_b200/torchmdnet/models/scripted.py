@@ -3,7 +3,7 @@
 
 ``torch.jit.script(model)`` on a ``TorchMD_Net`` of this package returns the scripted form of ``ScriptableTorchMD_Net``
 (through ``TorchMD_Net.__prepare_scriptable__``): a module that holds ONE flat fp32 buffer with every packed weight
-(filter tables included) and calls the fused op ``torchmdnet_b200::{tensornet,et}_energy_forces_packed``, which finds or
+(filter tables included) and calls the fused op ``torchmdnet_b200::{tensornet,et,gn}_energy_forces_packed``, which finds or
 creates the native model from the identity of that buffer.  The buffer follows ``.to(device)``, is written by
 ``torch.jit.save`` and restored by ``torch.jit.load`` in another process; nothing process-local is serialised.
 
@@ -50,7 +50,7 @@ class ScriptableTorchMD_Net(nn.Module):
         self.layout = [int(x) for x in layout]
         self.iparams = [int(x) for x in ip]
         self.fparams = [float(x) for x in fp]
-        self.is_tensornet: bool = rm._op == "tensornet"
+        self.kind: int = {"tensornet": 0, "et": 1, "gn": 2}[rm._op]
         self.derivative: bool = bool(model.derivative)
         dist = rm.distance
         self.max_num_pairs: int = int(dist.max_num_pairs)
@@ -77,12 +77,16 @@ class ScriptableTorchMD_Net(nn.Module):
                 self.dim_size = n_mol
         n = pos.size(0)
         max_edges = self.max_num_pairs if self.max_num_pairs > 0 else -self.max_num_pairs * n
-        if self.is_tensornet:
+        if self.kind == 0:
             y, f, status = torch.ops.torchmdnet_b200.tensornet_energy_forces_packed(
                 self.packed, self.layout, self.iparams, self.fparams, z.contiguous(), pos.detach().contiguous(),
                 b.contiguous(), self.box, self.use_periodic, self.strategy, max_edges, n_mol, self.derivative)
-        else:
+        elif self.kind == 1:
             y, f, status = torch.ops.torchmdnet_b200.et_energy_forces_packed(
+                self.packed, self.layout, self.iparams, self.fparams, z.contiguous(), pos.detach().contiguous(),
+                b.contiguous(), self.box, self.use_periodic, self.strategy, max_edges, n_mol, self.derivative)
+        else:
+            y, f, status = torch.ops.torchmdnet_b200.gn_energy_forces_packed(
                 self.packed, self.layout, self.iparams, self.fparams, z.contiguous(), pos.detach().contiguous(),
                 b.contiguous(), self.box, self.use_periodic, self.strategy, max_edges, n_mol, self.derivative)
         if self.derivative:
