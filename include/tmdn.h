@@ -398,6 +398,40 @@ int tmdn_gn_energy_forces(const tmdn_gn_model* m, const int64_t* z, const float*
 int tmdn_gn_workspace_lookup(const tmdn_gn_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol, int strategy,
                              const double box[9], const char* name, size_t* offset, size_t* bytes);
 
+/* ---------------------------------------------------------------- Transformer (TorchMD_T) energy + forces (fp32)
+ * TorchMD_T.forward + NeighborEmbedding + MultiHeadAttention + Scalar head + force path
+ * (torchmdnet/models/torchmd_t.py:144-300): the attention of the equivariant transformer without its vector channel;
+ * self pairs are part of the attention (Distance(..., loop=True), torchmd_t.py:102-104).
+ *   layer table [n_int][2][H] float4 : act(dk_proj(rbf(d))), act(dv_proj(rbf(d))) * C(d)   (a missing filter is 1, resp. C)
+ * qkv = q | k | v rows of one [3H,H] projection.  head_dim = hidden/num_heads must be a power of two <= 32. */
+typedef struct tmdn_t_layer {
+    const float *ln_w, *ln_b;
+    const float *qkv_w, *qkv_b, *qkv_wT;    /* [3H,H], [3H], [H,3H] */
+    const float *o_w, *o_b, *o_wT;          /* o_proj [H,H], [H], [H,H] */
+    const float* table;
+} tmdn_t_layer;
+
+typedef struct tmdn_t_model {
+    int32_t hidden, num_layers, num_heads, max_z;
+    int32_t activation, attn_activation, has_neighbor_embedding, n_int;
+    int32_t gemm_mode;
+    float cutoff_lower, cutoff_upper, mean, std;
+    float grid_alpha, grid_gamma;
+    const float* emb;
+    const float *ne_emb, *ne_table, *ne_comb_w, *ne_comb_b, *ne_comb_w2T;
+    tmdn_t_layer layer[TMDN_MAX_LAYERS];
+    const float *out_ln_w, *out_ln_b;
+    const float *head_w1, *head_b1, *head_w1T, *head_w2, *head_b2;   /* Scalar head, as tmdn_gn_model */
+} tmdn_t_model;
+
+size_t tmdn_t_workspace_bytes(const tmdn_t_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol, int strategy,
+                              const double box[9]);
+/* Same contract as tmdn_tensornet_energy_forces. */
+int tmdn_t_energy_forces(const tmdn_t_model* m, const int64_t* z, const float* pos, const int64_t* batch, int64_t n_atoms,
+                         int64_t n_mol, const double box[9], int use_periodic, int strategy, int64_t max_edges,
+                         float* energy, float* forces, int32_t* status, void* workspace, size_t workspace_bytes,
+                         tmdn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,5 +1,5 @@
-"""Fused CUDA graph network (TorchMD_GN) energy+forces against fixtures written by the unmodified reference, the
-reference's own golden row (tests/expected.pkl graph-network/Scalar) and the oracle restatement; scripting and capture."""
+"""Fused CUDA graph network (TorchMD_GN) and transformer (TorchMD_T) energy+forces against fixtures written by the unmodified reference, the
+reference's own golden rows (tests/expected.pkl graph-network/Scalar, transformer/Scalar) and the oracle restatement; scripting and capture."""
 import json
 import os
 
@@ -20,7 +20,7 @@ def build(g):
     return m.cuda().eval()
 
 
-@pytest.mark.parametrize("name", ["small_gn_ne.npz", "small_gn_plain.npz"])
+@pytest.mark.parametrize("name", ["small_gn_ne.npz", "small_gn_plain.npz", "small_t_both.npz", "small_t_values_nonbr.npz"])
 def test_small_models_match_reference(name):
     g = load_npz(name)
     m = build(g)
@@ -44,15 +44,16 @@ def test_small_models_match_reference(name):
     torch.testing.assert_close(fa, f2[:n0], rtol=0, atol=1e-5)
 
 
-def test_full_size_and_reference_golden_row():
+@pytest.mark.parametrize("arch,tag,fixture", [("graph-network", "gn", "model_GN.npz"), ("transformer", "t", "model_T.npz")])
+def test_full_size_and_reference_golden_row(arch, tag, fixture):
     from torchmdnet.models.model import create_model
-    g = load_npz("model_GN.npz")
+    g = load_npz(fixture)
     seed_everything(int(g["seed"]))
     m = create_model(g["hparams"]).cuda().eval()
     y, f = m(tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda())
     check(y, f, g["y"], g["forces"])
-    with open(os.path.join(GOLDEN, "expected_pkl_gn.json")) as fh:
-        e = json.load(fh)["graph-network"]
+    with open(os.path.join(GOLDEN, "expected_pkl_%s.json" % tag)) as fh:
+        e = json.load(fh)[arch]
     seed_everything(1234)
     m = create_model(e["hparams"]).cuda().eval()
     y, f = m(torch.tensor(e["z"]).cuda(), torch.tensor(e["pos"]).cuda(), torch.tensor(e["batch"]).cuda())
@@ -60,8 +61,9 @@ def test_full_size_and_reference_golden_row():
     torch.testing.assert_close(f.cpu(), torch.tensor(e["expected_deriv"]), rtol=1.3e-6, atol=1e-5)
 
 
-def test_forces_are_minus_energy_gradient_and_rotations():
-    g = load_npz("small_gn_ne.npz")
+@pytest.mark.parametrize("name", ["small_gn_ne.npz", "small_t_both.npz"])
+def test_forces_are_minus_energy_gradient_and_rotations(name):
+    g = load_npz(name)
     m = build(g)
     m.representation_model.gemm_mode = "fp32"
     z, batch = tt(g["z"]).cuda(), tt(g["batch"]).cuda()
@@ -83,8 +85,9 @@ def test_forces_are_minus_energy_gradient_and_rotations():
     torch.testing.assert_close(f1.cpu(), f0.cpu() @ R.t(), rtol=0, atol=5e-5)
 
 
-def test_scripted_graph_network_and_capture(tmp_path):
-    g = load_npz("small_gn_ne.npz")
+@pytest.mark.parametrize("name", ["small_gn_ne.npz", "small_t_both.npz"])
+def test_scripted_model_and_capture(name, tmp_path):
+    g = load_npz(name)
     m = build(g)
     z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
     y0, f0 = m(z, pos, batch)

@@ -119,8 +119,6 @@ def test_unsupported_configurations_are_refused():
     from torchmdnet.models.model import create_model
     hp = dict(load_npz("small_tensornet_o3.npz")["hparams"])
     with pytest.raises(NotImplementedError):
-        create_model(dict(hp, model="transformer"))
-    with pytest.raises(NotImplementedError):
         create_model(dict(hp, model="graph-network", aggr="mean", neighbor_embedding=True))
     with pytest.raises(NotImplementedError):
         create_model(dict(hp, output_model="DipoleMoment"))

@@ -16,7 +16,8 @@ from oracle import neighbors as onb
 RTOL, ATOL = 1.3e-6, 1e-5
 
 
-@pytest.mark.parametrize("name", SMALL + ["small_tensornet_periodic.npz", "small_gn_ne.npz", "small_gn_plain.npz"])
+@pytest.mark.parametrize("name", SMALL + ["small_tensornet_periodic.npz", "small_gn_ne.npz", "small_gn_plain.npz",
+                                          "small_t_both.npz", "small_t_values_nonbr.npz"])
 def test_oracle_matches_reference_small_models(name):
     g = load_npz(name)
     box = tt(g["box"]) if "box" in g else None
@@ -54,20 +55,21 @@ def test_neighbor_backward_restatement_matches_autograd():
     np.testing.assert_allclose(onb.neighbor_backward(nb, dl, ds, gd, gw, 30), p.grad.numpy(), atol=1e-10)
 
 
-def test_oracle_matches_reference_graph_network_goldens():
-    """The graph-network restatement against the reference's own golden row (tests/expected.pkl graph-network/Scalar,
-    numbers in tests/golden/expected_pkl_gn.json) and the full-size fixture model_GN.npz; weights = seeded create_model of
-    this package, whose initial values are checked against the reference's checksums."""
+@pytest.mark.parametrize("arch,tag,fixture", [("graph-network", "gn", "model_GN.npz"), ("transformer", "t", "model_T.npz")])
+def test_oracle_matches_reference_gn_and_t_goldens(arch, tag, fixture):
+    """The graph-network / transformer restatements against the reference's own golden rows (tests/expected.pkl
+    <arch>/Scalar, numbers in tests/golden/expected_pkl_{gn,t}.json) and the full-size fixtures; weights = seeded
+    create_model of this package, whose initial values are checked against the reference's checksums."""
     import json
     import random
     from torchmdnet.models.model import create_model
-    with open(os.path.join(GOLDEN, "expected_pkl_gn.json")) as fh:
-        e = json.load(fh)["graph-network"]
+    with open(os.path.join(GOLDEN, "expected_pkl_%s.json" % tag)) as fh:
+        e = json.load(fh)[arch]
     for hp, seed, z, pos, batch, y_ref, f_ref, sums in (
             (e["hparams"], 1234, torch.tensor(e["z"]), torch.tensor(e["pos"]), torch.tensor(e["batch"]),
              torch.tensor(e["expected_pred"]), torch.tensor(e["expected_deriv"]), e["checksums"]),) + tuple(
             (g["hparams"], int(g["seed"]), tt(g["z"]), tt(g["pos"]), tt(g["batch"]), tt(g["y"]), tt(g["forces"]), g["checksums"])
-            for g in [load_npz("model_GN.npz")]):
+            for g in [load_npz(fixture)]):
         random.seed(seed)
         np.random.seed(seed)
         torch.manual_seed(seed)

@@ -1124,3 +1124,276 @@ extern "C" int tmdn_gn_energy_forces(const tmdn_gn_model* m, const int64_t* z, c
     }
     return TMDN_OK;
 }
+
+// ====================================================================================================================
+// Transformer (TorchMD_T): torchmdnet/models/torchmd_t.py:144-300 -- the attention of the equivariant transformer
+// without its vector channel.  Per layer: xl = LN(x); q|k|v = proj(xl); attn_e = attn_act(sum_head q_i k_j dk(d_e)) C(d_e);
+// out_i = sum_e v_j dv(d_e) attn_e (self pairs included, loop = True); x += o_proj(out).  Then out_norm and the Scalar head.
+// Filter table per layer: [n_int][2][H] float4 = act(dk_proj(rbf)), act(dv_proj(rbf)) * C(d)  (a missing filter is 1 / C).
+namespace {
+
+template <int HDC = 0>
+__global__ void __launch_bounds__(1024)
+t_edge_fwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
+           int attn_act, int hd, const float* __restrict__ qkv, int N, int H, float* __restrict__ out) {
+    pdl_sync();
+    extern __shared__ float smem[];
+    float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
+    const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    const int H3 = 3 * H;
+    float acc[1] = {0.f};
+    if (valid) {
+        const float qi = qkv[(size_t)i * H3 + h];
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0 + sl; e < r1; e += S) {
+            const int j = col[e];
+            float f[2], df[2];
+            tab_eval<2>(tb, geom[e].w, H, h, f, df);
+            const float* pj = qkv + (size_t)j * H3 + h;
+            const float s = seg_sum_t<HDC>(qi * pj[H] * f[0], hd);
+            acc[0] += pj[2 * H] * f[1] * act_apply(attn_act, s);
+        }
+    }
+    slice_reduce<1>(acc, s_part, H);
+    if (valid && sl == 0) out[(size_t)i * H + h] = acc[0];
+}
+
+// adjoint in row i of the symmetric pair set, both directions of every pair (A: i <- j, B: j <- i):
+//   g_q_i = sum gsA k_j dk;  g_k_i = sum gsB q_j dk;  g_v_i = sum g_out_j attnB dv;  dE/dpos_i += u (gdA + gdB)
+template <int HDC = 0>
+__global__ void __launch_bounds__(512)
+t_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const float4* __restrict__ geom, Tab tb,
+           int attn_act, int hd, const float* __restrict__ qkv, const float* __restrict__ g_out, int N, int H,
+           float* __restrict__ g_qkv, float* __restrict__ gpos) {
+    pdl_sync();
+    extern __shared__ float smem[];
+    float* s_red = smem;
+    float* s_part = smem + EDGE_RED_FLOATS * blockDim.z;
+    const int h = threadIdx.x, sl = threadIdx.y, S = blockDim.y;
+    const int i = blockIdx.x * blockDim.z + threadIdx.z;
+    const bool valid = i < N;
+    const int H3 = 3 * H;
+    float acc[3] = {0.f, 0.f, 0.f};   // g_q, g_k, g_v
+    float gp[3] = {0.f, 0.f, 0.f};
+    if (valid) {
+        const float* pi = qkv + (size_t)i * H3 + h;
+        const float qi = pi[0], ki = pi[H], vi = pi[2 * H];
+        const float gi = g_out[(size_t)i * H + h];
+        const int r0 = row_ptr[i], r1 = row_ptr[i + 1];
+        for (int e = r0 + sl; e < r1; e += S) {
+            const int j = col[e];
+            const float4 g = geom[e];
+            float f[2], df[2];
+            tab_eval<2>(tb, g.w, H, h, f, df);
+            const float* pj = qkv + (size_t)j * H3 + h;
+            const float qj = pj[0], kj = pj[H], vj = pj[2 * H];
+            const float gj = g_out[(size_t)j * H + h];
+            float attnA, dactA, attnB, dactB;
+            act_both(attn_act, seg_sum_t<HDC>(qi * kj * f[0], hd), attnA, dactA);
+            const float gsA = seg_sum_t<HDC>(gi * vj * f[1], hd) * dactA;
+            acc[0] += gsA * kj * f[0];
+            act_both(attn_act, seg_sum_t<HDC>(qj * ki * f[0], hd), attnB, dactB);
+            const float gsB = seg_sum_t<HDC>(gj * vi * f[1], hd) * dactB;
+            acc[1] += gsB * qj * f[0];
+            acc[2] += gj * attnB * f[1];
+            if (j != i) {   // the self pair has d = 0 and no position dependence
+                const float gd = gsA * qi * kj * df[0] + gi * attnA * vj * df[1] + gsB * qj * ki * df[0] + gj * attnB * vi * df[1];
+                gp[0] += g.x * gd; gp[1] += g.y * gd; gp[2] += g.z * gd;
+            }
+        }
+    }
+    slice_reduce<3>(acc, s_part, H);
+    if (valid && sl == 0) {
+        float* o = g_qkv + (size_t)i * H3 + h;
+        o[0] = acc[0]; o[H] = acc[1]; o[2 * H] = acc[2];
+    }
+    atom_reduce<3>(gp, s_red);
+    if (valid && h == 0 && sl == 0) {
+        gpos[3 * (size_t)i] += gp[0];
+        gpos[3 * (size_t)i + 1] += gp[1];
+        gpos[3 * (size_t)i + 2] += gp[2];
+    }
+}
+
+struct TWs {
+    int32_t *num_found, *row_ptr, *col;
+    float* geom;
+    int* z32;
+    void* graph_ws;
+    size_t graph_ws_bytes;
+    float *cat0, *X[TMDN_MAX_LAYERS + 1], *stat[TMDN_MAX_LAYERS + 1], *QKV[TMDN_MAX_LAYERS], *xl, *out, *xo, *h3, *a3, *e_atom,
+        *d3, *g_xo, *g_x, *g_out, *g_qkv, *g_xl, *g_xn, *gpos;
+};
+
+int carve_t(Arena& a, const tmdn_t_model* m, int64_t N, int64_t P, TWs& w, std::vector<EtEntry>* names, const double* box,
+            int strategy) {
+    const size_t H = m->hidden, L = m->num_layers, n = (size_t)N, H2 = H / 2;
+    char buf[32];
+    w.num_found = ecarve<int32_t>(a, names, "num_found", 4);
+    w.row_ptr = ecarve<int32_t>(a, names, "row_ptr", n + 1);
+    w.col = ecarve<int32_t>(a, names, "col", (size_t)P);
+    w.geom = ecarve<float>(a, names, "geom", 4 * (size_t)P);
+    w.z32 = ecarve<int>(a, names, "z32", n);
+    w.graph_ws_bytes = tmdn_csr_build_workspace_bytes(strategy, N, box, m->cutoff_upper);
+    if (w.graph_ws_bytes == 0) {
+        tmdn_set_error("t: bad box for the cell strategy");
+        return TMDN_EINVAL;
+    }
+    w.graph_ws = ecarve<char>(a, names, "graph_ws", w.graph_ws_bytes);
+    w.cat0 = ecarve<float>(a, names, "cat0", n * 2 * H);
+    for (size_t l = 0; l <= L; ++l) {
+        snprintf(buf, sizeof buf, "x%zu", l); w.X[l] = ecarve<float>(a, names, buf, n * H);
+        snprintf(buf, sizeof buf, "stat%zu", l); w.stat[l] = ecarve<float>(a, names, buf, n * 2);
+    }
+    for (size_t l = 0; l < L; ++l) { snprintf(buf, sizeof buf, "qkv%zu", l); w.QKV[l] = ecarve<float>(a, names, buf, n * 3 * H); }
+    w.xl = ecarve<float>(a, names, "xl", n * H);
+    w.out = ecarve<float>(a, names, "out", n * H);
+    w.xo = ecarve<float>(a, names, "xo", n * H);
+    w.h3 = ecarve<float>(a, names, "h3", n * H2);
+    w.a3 = ecarve<float>(a, names, "a3", n * H2);
+    w.e_atom = ecarve<float>(a, names, "e_atom", n);
+    w.d3 = ecarve<float>(a, names, "d3", n * H2);
+    w.g_xo = ecarve<float>(a, names, "g_xo", n * H);
+    w.g_x = ecarve<float>(a, names, "g_x", n * H);
+    w.g_out = ecarve<float>(a, names, "g_out", n * H);
+    w.g_qkv = ecarve<float>(a, names, "g_qkv", n * 3 * H);
+    w.g_xl = ecarve<float>(a, names, "g_xl", n * H);
+    w.g_xn = ecarve<float>(a, names, "g_xn", n * H);
+    w.gpos = ecarve<float>(a, names, "gpos", n * 3);
+    return TMDN_OK;
+}
+
+int check_t(const tmdn_t_model* m) {
+    TMDN_CHECK_ARG(m, "t: null model");
+    TMDN_CHECK_ARG(m->hidden >= 32 && m->hidden <= 1024 && m->hidden % 32 == 0,
+                   "t: hidden_channels must be a multiple of 32 in [32,1024] (got %d)", m->hidden);
+    TMDN_CHECK_ARG(m->num_layers >= 0 && m->num_layers <= TMDN_MAX_LAYERS, "t: num_layers out of range");
+    TMDN_CHECK_ARG(m->num_heads > 0 && m->hidden % m->num_heads == 0, "t: hidden must be divisible by num_heads");
+    const int hd = m->hidden / m->num_heads;
+    TMDN_CHECK_ARG(hd <= 32 && (hd & (hd - 1)) == 0, "t: head_dim must be a power of two <= 32 (got %d)", hd);
+    TMDN_CHECK_ARG(m->max_z > 0 && m->n_int > 0, "t: bad max_z / table size");
+    TMDN_CHECK_ARG(m->cutoff_upper > m->cutoff_lower && m->cutoff_lower >= 0, "t: bad cutoffs");
+    TMDN_CHECK_ARG(m->emb && m->out_ln_w && m->out_ln_b && m->head_w1 && m->head_w2 && m->head_w1T, "t: missing weights");
+    for (int l = 0; l < m->num_layers; ++l)
+        TMDN_CHECK_ARG(m->layer[l].table && m->layer[l].qkv_w && m->layer[l].o_w, "t: missing weights of layer %d", l);
+    if (m->has_neighbor_embedding) TMDN_CHECK_ARG(m->ne_emb && m->ne_table && m->ne_comb_w, "t: missing NE weights");
+    return TMDN_OK;
+}
+}  // namespace
+
+extern "C" size_t tmdn_t_workspace_bytes(const tmdn_t_model* m, int64_t n_atoms, int64_t max_edges, int64_t n_mol,
+                                         int strategy, const double box[9]) {
+    (void)n_mol;
+    if (check_t(m) != TMDN_OK || n_atoms <= 0 || max_edges <= 0) return 0;
+    Arena a(nullptr, 0);
+    TWs w;
+    if (carve_t(a, m, n_atoms, max_edges, w, nullptr, box, strategy) != TMDN_OK) return 0;
+    return a.off + 256;
+}
+
+extern "C" int tmdn_t_energy_forces(const tmdn_t_model* m, const int64_t* z, const float* pos, const int64_t* batch,
+                                    int64_t n_atoms, int64_t n_mol, const double box[9], int use_periodic, int strategy,
+                                    int64_t max_edges, float* energy, float* forces, int32_t* status, void* workspace,
+                                    size_t workspace_bytes, tmdn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    TMDN_TRY(check_t(m));
+    TMDN_CHECK_ARG(z && pos && batch && energy && status && workspace, "t: null pointer argument");
+    TMDN_CHECK_ARG(n_atoms > 0 && n_mol > 0 && max_edges > 0, "t: bad sizes");
+    TMDN_CHECK_ARG(max_edges < (1LL << 31) && n_atoms < (1LL << 31) / 16, "t: sizes exceed int32 indexing");
+    TMDN_CHECK_ARG(strategy != TMDN_CELL || box, "t: the cell strategy needs a box");
+    const int N = (int)n_atoms, H = m->hidden, L = m->num_layers, act = m->activation, H2 = H / 2;
+    const bool tc = m->gemm_mode == TMDN_GEMM_TF32X3;
+    const int hd = H / m->num_heads;
+    const int64_t P = max_edges;
+    const float lo = m->cutoff_lower, hi = m->cutoff_upper;
+    Arena arena(workspace, workspace_bytes);
+    TWs w;
+    TMDN_TRY(carve_t(arena, m, n_atoms, P, w, nullptr, box, strategy));
+    if (!arena.ok) {
+        tmdn_set_error("t: workspace too small (%zu < %zu)", workspace_bytes, arena.off);
+        return TMDN_EWORKSPACE;
+    }
+    {
+        KTimer ktimer__("neighbors_csr", stream);
+        TMDN_TRY(tmdn_csr_build_f32(strategy, pos, batch, n_atoms, box, use_periodic, lo, hi, P, w.row_ptr, w.col, w.geom,
+                                    w.num_found, w.graph_ws, w.graph_ws_bytes, stream_));
+    }
+    TMDN_CUDA(cudaMemsetAsync(status, 0, 4 * sizeof(int32_t), stream));
+    ET_K("et_prep", launch_k(et_prep_kernel, (unsigned)cdiv(N, 256), 256, 0, stream, z, w.z32, N, m->max_z, w.num_found,
+                             (long long)P, status, batch));
+    const float4* geom = (const float4*)w.geom;
+    const TabGrid tgrid = make_tab_grid(m->n_int, hi, m->grid_alpha, m->grid_gamma);
+    const Tab ne_tab{(const float4*)m->ne_table, tgrid};
+    const EdgeLaunch e1 = edge_launch(N, H, 1024, 1), e3 = edge_launch(N, H, 512, 3), e8 = edge_launch(N, H, 512, 8);
+    const int apb = H >= 128 ? 1 : 128 / H;
+    const dim3 lblock(H, 1, apb);
+    const unsigned lgrid = (unsigned)cdiv(N, apb);
+    const unsigned hgrid = (unsigned)cdiv((long long)N * H2, 256);
+
+    if (m->has_neighbor_embedding) {
+        ET_K("et_embed_fwd", launch_k(et_embed_fwd<true>, e1.grid, e1.block, e1.smem, stream, w.row_ptr, w.col, geom, w.z32,
+                                      m->emb, m->ne_emb, ne_tab, N, H, w.cat0, 2 * H));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.cat0, 2 * H, m->ne_comb_w, m->ne_comb_b, w.X[0], H, N, H, 2 * H), stream, tc));
+    } else {
+        ET_K("et_embed_fwd", launch_k(et_embed_fwd<false>, e1.grid, e1.block, e1.smem, stream, w.row_ptr, w.col, geom, w.z32,
+                                      m->emb, nullptr, ne_tab, N, H, w.X[0], H));
+    }
+    for (int l = 0; l < L; ++l) {
+        const tmdn_t_layer& ly = m->layer[l];
+        const Tab tb{(const float4*)ly.table, tgrid};
+        ET_K("et_ln_fwd", launch_k(et_ln_fwd, lgrid, lblock, 0, stream, w.X[l], ly.ln_w, ly.ln_b, w.xl, H, w.stat[l], N, H));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.xl, H, ly.qkv_w, ly.qkv_b, w.QKV[l], 3 * H, N, 3 * H, H), stream, tc));
+        if (hd == 16)
+            ET_K("t_edge_fwd", launch_k(t_edge_fwd<16>, e1.grid, e1.block, e1.smem, stream, w.row_ptr, w.col, geom, tb,
+                                        m->attn_activation, hd, w.QKV[l], N, H, w.out));
+        else
+            ET_K("t_edge_fwd", launch_k(t_edge_fwd<0>, e1.grid, e1.block, e1.smem, stream, w.row_ptr, w.col, geom, tb,
+                                        m->attn_activation, hd, w.QKV[l], N, H, w.out));
+        TMDN_CUDA(cudaMemcpyAsync(w.X[l + 1], w.X[l], sizeof(float) * (size_t)N * H, cudaMemcpyDeviceToDevice, stream));
+        {
+            GemmP p = gemm_desc(w.out, H, ly.o_w, ly.o_b, w.X[l + 1], H, N, H, H);
+            p.accumulate = 1;
+            TMDN_TRY(node_gemm1(EPI_NONE, p, stream, tc));
+        }
+    }
+    ET_K("et_ln_fwd", launch_k(et_ln_fwd, lgrid, lblock, 0, stream, w.X[L], m->out_ln_w, m->out_ln_b, w.xo, H, w.stat[L], N, H));
+    {
+        GemmP p = gemm_desc(w.xo, H, m->head_w1, m->head_b1, w.a3, H2, N, H2, H);
+        p.C2 = w.h3; p.act = act;
+        TMDN_TRY(node_gemm1(EPI_ACT, p, stream, tc));
+    }
+    ET_K("et_head_energy", launch_k(et_head_energy, (unsigned)cdiv(N, 4), 128, 0, stream, w.a3, m->head_w2, m->head_b2, m->std,
+                                    w.e_atom, N, H2));
+    ET_K("et_mol_reduce", launch_k(et_mol_reduce, (unsigned)n_mol, 128, 0, stream, w.e_atom, batch, N, m->mean, energy, status));
+    if (!forces) return TMDN_OK;
+
+    TMDN_CUDA(cudaMemsetAsync(w.gpos, 0, sizeof(float) * 3 * (size_t)N, stream));
+    ET_K("et_head_seed_bwd", launch_k(et_head_seed_bwd, hgrid, 256, 0, stream, w.h3, m->head_w2, m->std, act, w.d3,
+                                      (long long)N * H2, H2));
+    TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.d3, H2, m->head_w1T, nullptr, w.g_xo, H, N, H, H2), stream, tc));
+    ET_K("et_ln_bwd", launch_k(et_ln_bwd, lgrid, lblock, 0, stream, w.X[L], m->out_ln_w, w.stat[L], w.g_xo, H, w.g_x, 0, N, H));
+    for (int l = L - 1; l >= 0; --l) {
+        const tmdn_t_layer& ly = m->layer[l];
+        const Tab tb{(const float4*)ly.table, tgrid};
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_x, H, ly.o_wT, nullptr, w.g_out, H, N, H, H), stream, tc));
+        if (hd == 16)
+            ET_K("t_edge_bwd", launch_k(t_edge_bwd<16>, e3.grid, e3.block, e3.smem, stream, w.row_ptr, w.col, geom, tb,
+                                        m->attn_activation, hd, w.QKV[l], w.g_out, N, H, w.g_qkv, w.gpos));
+        else
+            ET_K("t_edge_bwd", launch_k(t_edge_bwd<0>, e3.grid, e3.block, e3.smem, stream, w.row_ptr, w.col, geom, tb,
+                                        m->attn_activation, hd, w.QKV[l], w.g_out, N, H, w.g_qkv, w.gpos));
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_qkv, 3 * H, ly.qkv_wT, nullptr, w.g_xl, H, N, H, 3 * H), stream, tc));
+        ET_K("et_ln_bwd", launch_k(et_ln_bwd, lgrid, lblock, 0, stream, w.X[l], ly.ln_w, w.stat[l], w.g_xl, H, w.g_x, 1, N, H));
+    }
+    if (m->has_neighbor_embedding) {
+        TMDN_TRY(node_gemm1(EPI_NONE, gemm_desc(w.g_x, H, m->ne_comb_w2T, nullptr, w.g_xn, H, N, H, H), stream, tc));
+        ET_K("et_final_bwd", launch_k(et_final_bwd<true>, e8.grid, e8.block, e8.smem, stream, w.row_ptr, w.col, geom, w.z32,
+                                      m->ne_emb, ne_tab, w.g_xn, w.gpos, forces, N, H, status));
+    } else {
+        ET_K("et_final_bwd", launch_k(et_final_bwd<false>, e8.grid, e8.block, e8.smem, stream, w.row_ptr, w.col, geom, w.z32,
+                                      nullptr, ne_tab, nullptr, w.gpos, forces, N, H, status));
+    }
+    return TMDN_OK;
+}

@@ -588,6 +588,99 @@ std::vector<int64_t> gn_debug_lookup(int64_t handle, int64_t n_atoms, int64_t ma
     return {(int64_t)off, (int64_t)bytes};
 }
 
+// ------------------------------------------------------------------ transformer (TorchMD_T) model handles
+struct TfHandle {
+    tmdn_t_model m;
+    std::vector<Tensor> keep;
+};
+std::unordered_map<int64_t, std::shared_ptr<TfHandle>> g_tf;
+
+// Weight order (must match torchmdnet/models/torchmd_t.py::pack_weights):
+//   emb ne_emb ne_table ne_comb_w ne_comb_b ne_comb_w2T out_ln_w out_ln_b head_w1 head_b1 head_w1T head_w2 head_b2
+//   per layer: ln_w ln_b qkv_w qkv_b qkv_wT o_w o_b o_wT table
+// iparams: hidden num_layers num_heads max_z activation attn_activation has_ne n_int gemm_mode ;
+// fparams: lo hi mean std grid_alpha grid_gamma
+int64_t t_create(std::vector<Tensor> w, std::vector<int64_t> ip, std::vector<double> fp) {
+    TORCH_CHECK(ip.size() == 9 && fp.size() == 6, "t_create: bad parameter vectors");
+    auto h = std::make_shared<TfHandle>();
+    tmdn_t_model& m = h->m;
+    memset(&m, 0, sizeof(m));
+    m.hidden = (int32_t)ip[0]; m.num_layers = (int32_t)ip[1]; m.num_heads = (int32_t)ip[2]; m.max_z = (int32_t)ip[3];
+    m.activation = (int32_t)ip[4]; m.attn_activation = (int32_t)ip[5]; m.has_neighbor_embedding = (int32_t)ip[6];
+    m.n_int = (int32_t)ip[7]; m.gemm_mode = (int32_t)ip[8];
+    m.cutoff_lower = (float)fp[0]; m.cutoff_upper = (float)fp[1]; m.mean = (float)fp[2]; m.std = (float)fp[3];
+    m.grid_alpha = (float)fp[4]; m.grid_gamma = (float)fp[5];
+    TORCH_CHECK(m.num_layers >= 0 && m.num_layers <= TMDN_MAX_LAYERS, "t_create: too many layers");
+    const size_t expect = 13 + 9 * (size_t)m.num_layers;
+    TORCH_CHECK(w.size() == expect, "t_create: expected ", expect, " weight tensors, got ", w.size());
+    size_t k = 0;
+    auto next = [&]() -> const float* { return fptr(w[k++]); };
+    m.emb = next(); m.ne_emb = next(); m.ne_table = next(); m.ne_comb_w = next(); m.ne_comb_b = next();
+    m.ne_comb_w2T = next(); m.out_ln_w = next(); m.out_ln_b = next();
+    m.head_w1 = next(); m.head_b1 = next(); m.head_w1T = next(); m.head_w2 = next(); m.head_b2 = next();
+    for (int l = 0; l < m.num_layers; ++l) {
+        tmdn_t_layer& y = m.layer[l];
+        y.ln_w = next(); y.ln_b = next(); y.qkv_w = next(); y.qkv_b = next(); y.qkv_wT = next();
+        y.o_w = next(); y.o_b = next(); y.o_wT = next(); y.table = next();
+    }
+    h->keep = std::move(w);
+    std::lock_guard<std::mutex> lock(g_mu);
+    const int64_t id = g_next++;
+    g_tf[id] = h;
+    return id;
+}
+void t_destroy(int64_t id) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    g_tf.erase(id);
+}
+
+std::tuple<Tensor, Tensor, Tensor, Tensor> t_energy_forces(int64_t handle, const Tensor& z, const Tensor& pos,
+                                                           const Tensor& batch, const Tensor& box_vectors,
+                                                           bool use_periodic, const std::string& strategy,
+                                                           int64_t max_edges, int64_t n_mol, bool compute_forces,
+                                                           const c10::optional<Tensor>& workspace) {
+    std::shared_ptr<TfHandle> h;
+    {
+        std::lock_guard<std::mutex> lock(g_mu);
+        auto it = g_tf.find(handle);
+        TORCH_CHECK(it != g_tf.end(), "t: unknown model handle ", handle);
+        h = it->second;
+    }
+    TORCH_CHECK(pos.is_cuda(), "t_energy_forces: CUDA tensors required (sm_100a build, no CPU fallback)");
+    TORCH_CHECK(pos.scalar_type() == at::kFloat && pos.dim() == 2 && pos.size(1) == 3 && pos.is_contiguous(),
+                "t_energy_forces: pos must be a contiguous float32 [N,3] tensor");
+    TORCH_CHECK(z.scalar_type() == at::kLong && z.dim() == 1 && z.is_contiguous() && z.size(0) == pos.size(0),
+                "t_energy_forces: z must be a contiguous int64 [N] tensor");
+    TORCH_CHECK(batch.scalar_type() == at::kLong && batch.dim() == 1 && batch.is_contiguous() &&
+                    batch.size(0) == pos.size(0),
+                "t_energy_forces: batch must be a contiguous int64 [N] tensor");
+    TORCH_CHECK(z.device() == pos.device() && batch.device() == pos.device(), "t_energy_forces: device mismatch");
+    TORCH_CHECK(h->keep.empty() || h->keep[0].device() == pos.device(),
+                "t_energy_forces: the model was packed on ", h->keep[0].device(), " but pos is on ", pos.device());
+    const c10::cuda::CUDAGuard guard(pos.device());
+    const int64_t n = pos.size(0);
+    const int sid = strategy_id(strategy);
+    double box[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool have_box = read_box(box_vectors, box);
+    TORCH_CHECK(have_box || !(use_periodic || sid == TMDN_CELL), "t_energy_forces: box required");
+    const size_t need = tmdn_t_workspace_bytes(&h->m, n, max_edges, n_mol, sid, have_box ? box : nullptr);
+    TORCH_CHECK(need > 0, "t_energy_forces: ", tmdn_last_error());
+    Tensor ws;
+    if (workspace.has_value() && workspace->defined() && (size_t)workspace->numel() >= need && workspace->is_cuda() &&
+        workspace->device() == pos.device() && workspace->scalar_type() == at::kByte)
+        ws = *workspace;
+    else
+        ws = at::empty({(int64_t)need}, pos.options().dtype(at::kByte));
+    Tensor energy = at::empty({n_mol, 1}, pos.options());
+    Tensor forces = compute_forces ? at::empty({n, 3}, pos.options()) : at::empty({0, 3}, pos.options());
+    Tensor status = at::empty({4}, pos.options().dtype(at::kInt));
+    TMDN_CALL(tmdn_t_energy_forces(&h->m, z.data_ptr<int64_t>(), pos.data_ptr<float>(), batch.data_ptr<int64_t>(), n, n_mol,
+                                   have_box ? box : nullptr, use_periodic, sid, max_edges, energy.data_ptr<float>(),
+                                   compute_forces ? forces.data_ptr<float>() : nullptr, status.data_ptr<int32_t>(),
+                                   ws.data_ptr(), (size_t)ws.numel(), cur_stream()));
+    return std::make_tuple(energy, forces, status, ws);
+}
+
 // ------------------------------------------------------------------ script-friendly entry points
 // A scripted / saved / re-loaded model cannot carry a process-local handle.  It carries ONE flat fp32 buffer with every
 // packed weight (segments aligned to 256 bytes; `offsets` has n_weights + 1 entries, in floats) plus the integer / float
@@ -620,11 +713,11 @@ PackedEntry& packed_entry(int kind, const Tensor& flat, const std::vector<int64_
         w.push_back(len > 0 ? flat.narrow(0, off, len) : at::empty({0}, flat.options()));
     }
     if (g_packed.size() >= 64) {            // stale versions of re-packed models: start over
-        for (auto& kv : g_packed) { g_tn.erase(kv.second.handle); g_et.erase(kv.second.handle); g_gn.erase(kv.second.handle); }
+        for (auto& kv : g_packed) { g_tn.erase(kv.second.handle); g_et.erase(kv.second.handle); g_gn.erase(kv.second.handle); g_tf.erase(kv.second.handle); }
         g_packed.clear();
     }
     lock.unlock();                          // *_create takes the lock itself
-    const int64_t h = kind == 0 ? tensornet_create(w, ip, fp) : kind == 1 ? et_create(w, ip, fp) : gn_create(w, ip, fp);
+    const int64_t h = kind == 0 ? tensornet_create(w, ip, fp) : kind == 1 ? et_create(w, ip, fp) : kind == 2 ? gn_create(w, ip, fp) : t_create(w, ip, fp);
     lock.lock();
     return g_packed.emplace(key, PackedEntry{h, Tensor()}).first->second;
 }
@@ -666,6 +759,17 @@ std::tuple<Tensor, Tensor, Tensor> gn_energy_forces_packed(
     PackedEntry& e = packed_entry(2, flat, layout, ip, fp);
     auto r = gn_energy_forces(e.handle, z, pos, batch, box_tensor(box), use_periodic, strategy, max_edges, n_mol,
                               compute_forces, e.workspace.defined() ? c10::optional<Tensor>(e.workspace) : c10::nullopt);
+    e.workspace = std::get<3>(r);
+    return std::make_tuple(std::get<0>(r), std::get<1>(r), std::get<2>(r));
+}
+
+std::tuple<Tensor, Tensor, Tensor> t_energy_forces_packed(
+    const Tensor& flat, std::vector<int64_t> layout, std::vector<int64_t> ip, std::vector<double> fp, const Tensor& z,
+    const Tensor& pos, const Tensor& batch, std::vector<double> box, bool use_periodic, const std::string& strategy,
+    int64_t max_edges, int64_t n_mol, bool compute_forces) {
+    PackedEntry& e = packed_entry(3, flat, layout, ip, fp);
+    auto r = t_energy_forces(e.handle, z, pos, batch, box_tensor(box), use_periodic, strategy, max_edges, n_mol,
+                             compute_forces, e.workspace.defined() ? c10::optional<Tensor>(e.workspace) : c10::nullopt);
     e.workspace = std::get<3>(r);
     return std::make_tuple(std::get<0>(r), std::get<1>(r), std::get<2>(r));
 }
@@ -876,6 +980,14 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
     m.def("et_energy_forces_packed(Tensor flat, int[] layout, int[] iparams, float[] fparams, Tensor z, Tensor pos, "
           "Tensor batch, float[] box, bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces) -> "
           "(Tensor, Tensor, Tensor)", et_energy_forces_packed);
+    m.def("t_create(Tensor[] weights, int[] iparams, float[] fparams) -> int", t_create);
+    m.def("t_destroy(int handle) -> ()", t_destroy);
+    m.def("t_energy_forces(int handle, Tensor z, Tensor pos, Tensor batch, Tensor box_vectors, "
+          "bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces, Tensor? workspace) -> "
+          "(Tensor, Tensor, Tensor, Tensor)", t_energy_forces);
+    m.def("t_energy_forces_packed(Tensor flat, int[] layout, int[] iparams, float[] fparams, Tensor z, Tensor pos, "
+          "Tensor batch, float[] box, bool use_periodic, str strategy, int max_edges, int n_mol, bool compute_forces) -> "
+          "(Tensor, Tensor, Tensor)", t_energy_forces_packed);
     m.def("gn_create(Tensor[] weights, int[] iparams, float[] fparams) -> int", gn_create);
     m.def("gn_destroy(int handle) -> ()", gn_destroy);
     m.def("gn_energy_forces(int handle, Tensor z, Tensor pos, Tensor batch, Tensor box_vectors, "

@@ -44,8 +44,11 @@ def create_model(args, prior_model=None, mean=None, std=None):
         representation_model = TorchMD_GN(num_filters=args["embedding_dimension"], aggr=args["aggr"],
                                           neighbor_embedding=args["neighbor_embedding"], **shared_args)
     elif args["model"] == "transformer":
-        raise NotImplementedError('architecture "transformer" (TorchMD_T) is outside this build '
-                                  "(equivariant-transformer, tensornet and graph-network are built)")
+        from .torchmd_t import TorchMD_T
+        is_equivariant = False
+        representation_model = TorchMD_T(attn_activation=args["attn_activation"], num_heads=args["num_heads"],
+                                         distance_influence=args["distance_influence"],
+                                         neighbor_embedding=args["neighbor_embedding"], **shared_args)
     else:
         raise ValueError(f'Unknown architecture: {args["model"]}')
     if args.get("atom_filter", -1) > -1:

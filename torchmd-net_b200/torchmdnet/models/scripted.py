@@ -50,7 +50,7 @@ class ScriptableTorchMD_Net(nn.Module):
         self.layout = [int(x) for x in layout]
         self.iparams = [int(x) for x in ip]
         self.fparams = [float(x) for x in fp]
-        self.kind: int = {"tensornet": 0, "et": 1, "gn": 2}[rm._op]
+        self.kind: int = {"tensornet": 0, "et": 1, "gn": 2, "t": 3}[rm._op]
         self.derivative: bool = bool(model.derivative)
         dist = rm.distance
         self.max_num_pairs: int = int(dist.max_num_pairs)
@@ -83,6 +83,10 @@ class ScriptableTorchMD_Net(nn.Module):
                 b.contiguous(), self.box, self.use_periodic, self.strategy, max_edges, n_mol, self.derivative)
         elif self.kind == 1:
             y, f, status = torch.ops.torchmdnet_b200.et_energy_forces_packed(
+                self.packed, self.layout, self.iparams, self.fparams, z.contiguous(), pos.detach().contiguous(),
+                b.contiguous(), self.box, self.use_periodic, self.strategy, max_edges, n_mol, self.derivative)
+        elif self.kind == 3:
+            y, f, status = torch.ops.torchmdnet_b200.t_energy_forces_packed(
                 self.packed, self.layout, self.iparams, self.fparams, z.contiguous(), pos.detach().contiguous(),
                 b.contiguous(), self.box, self.use_periodic, self.strategy, max_edges, n_mol, self.derivative)
         else:
