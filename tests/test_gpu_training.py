@@ -1,0 +1,85 @@
+"""Training mode: model.train() routes TorchMD_Net.forward through the differentiable composition of
+models/eager.py on the GPU -- parameter gradients of an energy + force-matching loss (the second-order path of
+models/model.py:286-298, caller module.py:130-179) against the oracle's autograd on the CPU, for all four architectures;
+eval mode stays on the fused kernels and agrees with the training-mode forward."""
+import pytest
+import torch
+
+from helpers import load_npz, tt
+from oracle import model as om
+
+pytestmark = pytest.mark.gpu
+
+CASES = ["small_tensornet_o3.npz", "small_et_both.npz", "small_t_both.npz", "small_gn_ne.npz"]
+
+
+def _loss(y, f, wy, wf):
+    return (y * wy).sum() + (f * wf).pow(2).sum() + f.sum(0).pow(2).sum()
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_parameter_gradients_of_a_force_matching_loss(name):
+    from torchmdnet.models.model import create_model
+    g = load_npz(name)
+    hp = g["hparams"]
+    m = create_model(hp)
+    m.load_state_dict(g["sd"])
+    m = m.cuda()
+    z, pos, batch = tt(g["z"]), tt(g["pos"]), tt(g["batch"])
+    n_mol = int(batch.max()) + 1
+    gen = torch.Generator().manual_seed(5)
+    wy, wf = torch.randn(n_mol, 1, generator=gen), torch.randn(pos.shape[0], 3, generator=gen)
+    # ---- eval mode: fused kernels, no graph
+    m.eval()
+    if hp["model"] == "tensornet":
+        m.representation_model.filter_mode = "exact"
+    y_e, f_e = m(z.cuda(), pos.cuda(), batch.cuda())
+    assert not y_e.requires_grad and not f_e.requires_grad
+    # ---- training mode: differentiable, the same numbers
+    m.train()
+    y, f = m(z.cuda(), pos.cuda(), batch.cuda())
+    assert y.requires_grad and f.requires_grad
+    torch.testing.assert_close(y.detach(), y_e, rtol=1e-5, atol=2e-5)
+    torch.testing.assert_close(f.detach(), f_e, rtol=0, atol=5e-5)
+    _loss(y, f, wy.cuda(), wf.cuda()).backward()
+    grads = {k: p.grad.detach().cpu() for k, p in m.named_parameters() if p.grad is not None}
+    # ---- oracle: the same loss through autograd on the CPU (fp64 weights for a clean reference)
+    sd = {k: (v.double().requires_grad_(v.is_floating_point() and k in dict(m.named_parameters())))
+          if v.is_floating_point() else v for k, v in g["sd"].items()}
+    p64 = pos.double().requires_grad_(True)
+    ei, shift = om.build_edges(p64, batch, hp, None)
+    if hp["model"] == "graph-network":
+        pass                                               # gn_representation drops the self pairs itself
+    x = om.atom_energies(sd, hp, z, p64, ei, shift.double())
+    y_o = torch.zeros(n_mol, 1, dtype=torch.float64).index_add(0, batch, x) + sd["mean"]
+    (dy,) = torch.autograd.grad(y_o.sum(), p64, create_graph=True)
+    _loss(y_o, -dy, wy.double(), wf.double()).backward()
+    checked = 0
+    for k, v in sd.items():
+        if not (torch.is_tensor(v) and v.requires_grad) or v.grad is None:
+            continue
+        if k.startswith("representation_model.") and ".conv.net." in k:
+            continue                                        # the GN filter MLP is registered twice; compared under .mlp.
+        assert k in grads, k
+        scale = max(1.0, float(v.grad.abs().max()))
+        assert float((grads[k].double() - v.grad).abs().max()) <= 2e-3 * scale, (k, float((grads[k].double() - v.grad).abs().max()), scale)
+        checked += 1
+    assert checked >= 10
+    torch.testing.assert_close(y.detach().cpu().double(), y_o.detach(), rtol=1e-5, atol=2e-5)
+
+
+def test_training_mode_with_frozen_parameters_uses_the_fused_path():
+    from torchmdnet.models.model import create_model
+    g = load_npz("small_tensornet_o3.npz")
+    m = create_model(g["hparams"])
+    m.load_state_dict(g["sd"])
+    m = m.cuda().train()
+    for p in m.parameters():
+        p.requires_grad_(False)
+    y, f = m(tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda())
+    assert not y.requires_grad
+    with torch.no_grad():
+        for p in m.parameters():
+            p.requires_grad_(True)
+        y2, _ = m(tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda())
+    assert not y2.requires_grad and torch.equal(y, y2)

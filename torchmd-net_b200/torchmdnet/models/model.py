@@ -4,9 +4,10 @@
 ``TorchMD_Net.forward(z, pos, batch=None, q=None, s=None, extra_args=None) -> (y, neg_dy | None)`` performs ONE
 native call: neighbour search, representation, head, per-molecule reduction, ``* std + mean`` and -- when
 ``derivative`` -- the hand-written backward kernels that give ``neg_dy = -dy/dpos`` (the reference replays the
-graph with ``torch.autograd.grad(create_graph=True)``, model.py:286-298).  The returned tensors carry no
-autograd graph: training through forces (double backward) is outside this build and is
-refused rather than silently approximated.
+graph with ``torch.autograd.grad(create_graph=True)``, model.py:286-298).  In evaluation mode the returned tensors carry
+no autograd graph.  In training mode (``model.train()``, grad enabled, parameters requiring grad) the forward is the
+differentiable composition of ``models/eager.py`` on the GPU -- edge list from this package's neighbour op, forces by
+``autograd.grad(create_graph=True)`` -- so energy and force-matching losses train the same parameters.
 """
 import re
 import warnings
@@ -163,11 +164,45 @@ class TorchMD_Net(nn.Module):
             n_mol = 1
         else:
             n_mol = self._num_molecules(batch)
+        if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            return self._forward_training(z, pos, batch, n_mol, extra_args)
         mean, std = self._mean_std()
         y, neg_dy, _ = self.representation_model.energy_forces(z, pos, batch, n_mol, self.output_model, mean, std,
                                                                 compute_forces=self.derivative)
         y = self.apply_priors(y, z, batch, n_mol, pos, neg_dy if self.derivative else None, extra_args)
         return y, (neg_dy if self.derivative else None)
+
+    def _forward_training(self, z, pos, batch, n_mol, extra_args):
+        """``model.train()`` with grad enabled: the differentiable composition of models/eager.py (training and
+        double backward are outside the fused kernels).  Forces come from ``autograd.grad(create_graph=True)`` exactly as in
+        the reference (model.py:286-298), so a force-matching loss back-propagates into the parameters.  Pairwise priors
+        have no parameters: their energy and analytic forces are added as constants."""
+        from . import eager
+        if not getattr(self, "_warned_training_path", False):
+            self._warned_training_path = True
+            warnings.warn("TorchMD_Net is in training mode: forward runs the differentiable PyTorch composition "
+                          "(models/eager.py) so that losses reach the parameters; call model.eval() for the fused "
+                          "CUDA energy+force kernels")
+        if self.derivative:
+            pos = pos.requires_grad_(True) if pos.is_leaf else pos
+            if not pos.requires_grad:
+                pos = pos.detach().requires_grad_(True)
+        y = eager.energy(self, z, pos, batch, n_mol)
+        neg_dy = None
+        if self.derivative:
+            (dy,) = torch.autograd.grad([y], [pos], grad_outputs=[torch.ones_like(y)], create_graph=True, retain_graph=True)
+            neg_dy = -dy
+        if self.prior_model is not None:
+            from ..priors import Atomref
+            for prior in self.prior_model:
+                if not isinstance(prior, Atomref):
+                    e = torch.zeros_like(y).detach()
+                    f = torch.zeros_like(pos).detach() if self.derivative else None
+                    prior.add_energy_forces(e, f, z, pos.detach(), batch, extra_args)
+                    y = y + e
+                    if f is not None:
+                        neg_dy = neg_dy + f
+        return y, neg_dy
 
     def apply_priors(self, y: Tensor, z: Tensor, batch: Tensor, n_mol: int, pos: Optional[Tensor] = None,
                      forces: Optional[Tensor] = None, extra_args: Optional[Dict[str, Tensor]] = None) -> Tensor:
