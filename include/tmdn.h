@@ -80,7 +80,8 @@ int tmdn_profile_report(char* buf, size_t buf_bytes);
  *   "hot_rows"     number of filter-table rows (from the cutoff end of the grid) those kernels keep in shared memory
  *                    (default 0: measured no gain, shared memory and L1 share the data pipe that bounds them)
  *   "edge_variant" A/B instantiations of those kernels (bit 0: forward with 2 edges per batch, bit 1: backward with 8
- *                    workers of one edge at 64 registers instead of 4 workers of two edges at 128); same results
+ *                    workers of one edge at 64 registers instead of 4 workers of two edges at 128, bit 3: forward as
+ *                    one CTA of 8 workers per SM instead of two CTAs of 5); same results
  * Returns the previous value (>= 0); value < 0 only queries; -1 for an unknown key (tmdn_last_error says which).
  * Process-wide. */
 int tmdn_set_tuning(const char* key, int value);

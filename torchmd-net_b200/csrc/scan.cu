@@ -40,7 +40,7 @@ extern "C" long long tmdn_launch_count(void) { return g_launches.load(); }
 // TMDN_HOT_ROWS).  Every setting computes the same function; the knobs select kernels / launch shapes.
 //   edge_persist: large systems run the TensorNet message-passing kernels as persistent CTAs (one per SM)
 //   hot_rows:     number of table rows (from the far end of the grid) those kernels keep in shared memory
-//   edge_variant: A/B instantiations of the persistent kernels (bit 0: forward 2 edges per batch; bit 1: backward 8 workers x 1 edge);
+//   edge_variant: A/B instantiations of the persistent kernels (bit 0: forward 2 edges per batch; bit 1: backward 8 workers x 1 edge; bit 3: forward 1 x 8 workers);
 //                 same sums in the same order
 static int env_or(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 int g_tmdn_tuning[TMDN_TUNE_COUNT] = {env_or("TMDN_SMALL_GEMM", 1), env_or("TMDN_LPT_ROWS", 1), env_or("TMDN_PDL", 0),

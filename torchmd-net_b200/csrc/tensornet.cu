@@ -528,8 +528,8 @@ __global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_p
 }
 
 // persistent large-system variant: W row workers
-template <int HC, int NB>
-__global__ void __launch_bounds__(1024, 1) tn_msg_fwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
+template <int HC, int NB, int MAXT = 1024, int MINB = 1>
+__global__ void __launch_bounds__(MAXT, MINB) tn_msg_fwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
                              const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N,
                              int so3, float* __restrict__ M, float* __restrict__ tauh, int n_hot, int row0) {
     pdl_sync();
@@ -1179,7 +1179,7 @@ namespace {
 // launch shape of the persistent edge kernels: one CTA per SM, W workers of H threads, n_hot table rows + worker scratch
 struct PersistLaunch { bool ok; unsigned grid; dim3 block; size_t smem; int n_hot; };
 template <typename Kern>
-PersistLaunch persist_launch(Kern kernel, bool eligible, int N, int H, int workers, const FilterView& fv) {
+PersistLaunch persist_launch(Kern kernel, bool eligible, int N, int H, int workers, const FilterView& fv, int ctas_per_sm = 1) {
     PersistLaunch p;
     memset(&p, 0, sizeof(p));
     if (!eligible || !g_tmdn_tuning[TMDN_TUNE_EDGE_PERSIST] || H != 128 || N < 8192 || fv.grid.n_int <= 0) return p;
@@ -1190,7 +1190,7 @@ PersistLaunch persist_launch(Kern kernel, bool eligible, int N, int H, int worke
     p.n_hot = n_hot;
     p.smem = (size_t)n_hot * 3 * H * sizeof(float4) + sizeof(float) * WORKER_RED_FLOATS * workers;
     p.block = dim3((unsigned)H, (unsigned)workers, 1);
-    p.grid = (unsigned)tmdn_sm_count();
+    p.grid = (unsigned)(tmdn_sm_count() * ctas_per_sm);
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem) != cudaSuccess) {
         cudaGetLastError();
         return p;
@@ -1400,11 +1400,17 @@ struct TnRun {
         if (s == TMDN_TN_LAYER_FWD) {
             {
                 KTimer ktimer__("tn_msg_fwd", stream);
-                const PersistLaunch pl = persist_launch(tn_msg_fwd_p<128, 1>, tab, N, H, 8, fv_layer[l]);
+                const int fvar = g_tmdn_tuning[TMDN_TUNE_EDGE_VARIANT];
+                // default: two CTAs of 5 workers per SM (1280 threads at 46 registers; 4 % faster than one CTA of 8 workers, r02m)
+                const PersistLaunch pl = (fvar & 9) ? persist_launch(tn_msg_fwd_p<128, 1>, tab, N, H, 8, fv_layer[l])
+                                                    : persist_launch(tn_msg_fwd_p<128, 1, 640, 2>, tab, N, H, 5, fv_layer[l], 2);
                 // small systems: 4 slices x 2 edges per thread at 128 registers instead of 8 slices x 1 at 64 -- the same
                 // number of edges in flight per SM, but with 64 registers ptxas reuses the landing registers of the
                 // table rows and an iteration becomes 3-4 dependent round trips instead of one (SASS, r01i)
-                if (pl.ok && (g_tmdn_tuning[TMDN_TUNE_EDGE_VARIANT] & 1))
+                if (pl.ok && !(fvar & 9))
+                    launch_k(tn_msg_fwd_p<128, 1, 640, 2>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom,
+                             fv_layer[l], wa.Y[l], r1, m->so3, wa.M[l], wa.tauh, pl.n_hot, r0);
+                else if (pl.ok && (fvar & 1))
                     launch_k(tn_msg_fwd_p<128, 2>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom, fv_layer[l],
                              wa.Y[l], r1, m->so3, wa.M[l], wa.tauh, pl.n_hot, r0);
                 else if (pl.ok)
@@ -1483,7 +1489,9 @@ struct TnRun {
                 KTimer ktimer__("tn_msg_bwd", stream);
                 const int variant = g_tmdn_tuning[TMDN_TUNE_EDGE_VARIANT];
                 const PersistLaunch pl = (variant & 2) ? persist_launch(tn_msg_bwd_p<128, 1, 1024>, tab, N, H, 8, fv_layer[l])
-                                                       : persist_launch(tn_msg_bwd_p<128, 2, 512>, tab, N, H, 4, fv_layer[l]);
+                                                         : persist_launch(tn_msg_bwd_p<128, 2, 512>, tab, N, H, 4, fv_layer[l]);
+                // (capping the registers to fit 5 or 6 workers -- 96 / 80 registers -- makes ptxas serialise the gathers:
+                // 16.1 / 13.1 ms per step against 7.6 ms, r02m)
                 if (pl.ok && (variant & 2))
                     launch_k(tn_msg_bwd_p<128, 1, 1024>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom,
                              fv_layer[l], wa.Y[l], dM, wa.dC, wa.gpos, r1, pl.n_hot, r0);
