@@ -2,6 +2,7 @@
 // Rows of a node tensor ([n, row_floats] fp32; row_floats = 9*H for TensorNet features, 3 for positions) owned by
 // this rank and needed by a neighbour are gathered into one contiguous send buffer; the receive side needs no
 // unpack because ghost rows are the contiguous tail of every local array.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace {
@@ -79,7 +80,10 @@ extern "C" int tmdn_halo_push_f32(const float* src, const int32_t* idx, const in
     const bool v4 = row_floats % 4 == 0 && ((uintptr_t)src % 16 == 0);   // ghost rows of 16-byte-aligned arrays stay aligned
     const long long total = n_rows_total * (v4 ? row_floats / 4 : row_floats);
     long long blocks = cdiv(total, 256);
-    const long long cap = (long long)tmdn_sm_count() * 8;
+    // CTAs of the push: it runs beside the interior rows of the producing stage and takes SM slots from them
+    // (TMDN_PUSH_CTAS overrides the cap for A/B runs)
+    static const long long cap_env = [] { const char* e = getenv("TMDN_PUSH_CTAS"); return e ? atoll(e) : 0LL; }();
+    const long long cap = cap_env > 0 ? cap_env : (long long)tmdn_sm_count() * 8;
     if (blocks > cap) blocks = cap;
     if (v4)
         launch_k(push_rows_kernel<float4>, (unsigned)blocks, 256, 0, stream, (const float4*)src, idx, (const long long*)seg,

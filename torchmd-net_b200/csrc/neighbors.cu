@@ -167,19 +167,27 @@ nbr_brute_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, i
     }
 }
 
-// slots in [min(found, max_pairs), max_pairs) get the reference's padding values (common.cuh:70-76)
+// slots in [min(found, max_pairs), max_pairs) get the reference's padding values (common.cuh:70-76).  A thread covers
+// PAD_SPAN consecutive slots, so the (usually much larger) filled part of the list costs one early exit per 8 slots
+// instead of one thread per slot (0.29 -> 0.05 ms at 71 M slots).
+constexpr int PAD_SPAN = 8;
 template <typename T> __global__ void pad_fill_kernel(PairOut<T> out) {
     pdl_sync();
-    const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= out.max_pairs) return;
+    const long long s0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * PAD_SPAN;
+    if (s0 >= out.max_pairs) return;
     const long long found = *out.counter;
-    if (s < found) return;
-    out.nbr[s] = -1;
-    out.nbr[out.max_pairs + s] = -1;
-    out.deltas[3 * s] = T(0);
-    out.deltas[3 * s + 1] = T(0);
-    out.deltas[3 * s + 2] = T(0);
-    out.dist[s] = T(0);
+    if (s0 + PAD_SPAN <= found) return;
+#pragma unroll
+    for (int k = 0; k < PAD_SPAN; ++k) {
+        const long long s = s0 + k;
+        if (s < found || s >= out.max_pairs) continue;
+        out.nbr[s] = -1;
+        out.nbr[out.max_pairs + s] = -1;
+        out.deltas[3 * s] = T(0);
+        out.deltas[3 * s + 1] = T(0);
+        out.deltas[3 * s + 2] = T(0);
+        out.dist[s] = T(0);
+    }
 }
 
 // ------------------------------------------------------------------ cell list: binning in nbr_common.cuh, traversal in
@@ -294,7 +302,7 @@ int neighbors_impl(int strategy, const T* pos, const int64_t* batch, int64_t n_a
                  use_periodic, lo2, hi2, loop, include_transpose, out, tile_mm);
         TMDN_LAUNCH_CHECK();
     }
-    launch_k(pad_fill_kernel<T>, (unsigned)cdiv(max_pairs, 256), 256, 0, stream, out);
+    launch_k(pad_fill_kernel<T>, (unsigned)cdiv(cdiv(max_pairs, PAD_SPAN), 256), 256, 0, stream, out);
     TMDN_LAUNCH_CHECK();
     return TMDN_OK;
 }
