@@ -83,3 +83,38 @@ def test_training_mode_with_frozen_parameters_uses_the_fused_path():
             p.requires_grad_(True)
         y2, _ = m(tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda())
     assert not y2.requires_grad and torch.equal(y, y2)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_double_precision_models(name):
+    """precision: 64 -- the fused kernels are fp32, double-precision models evaluate through models/eager.py with the fp64
+    neighbour op: energies and forces against the oracle in fp64 (1e-9), forces = -dE/dpos by central differences, and the
+    result carries a graph only when grad is enabled (reference: tests/test_model.py:191-211 runs gradcheck on such models)."""
+    from torchmdnet.models.model import create_model
+    g = load_npz(name)
+    hp = dict(g["hparams"], precision=64)
+    m = create_model(hp)
+    m.load_state_dict({k: v.double() if v.is_floating_point() else v for k, v in g["sd"].items()})
+    m = m.cuda().eval()
+    z, pos, batch = tt(g["z"]), tt(g["pos"]).double(), tt(g["batch"])
+    with torch.no_grad():
+        y, f = m(z.cuda(), pos.cuda(), batch.cuda())
+    assert y.dtype == torch.float64 and not y.requires_grad and not f.requires_grad
+    sd = {k: v.double() if v.is_floating_point() else v for k, v in g["sd"].items()}
+    y_o, f_o = om.energy_forces(sd, hp, z, pos, batch)
+    torch.testing.assert_close(y.cpu(), y_o, rtol=1e-9, atol=1e-9)
+    torch.testing.assert_close(f.cpu(), f_o, rtol=0, atol=1e-8)
+    h = 1e-5
+    for (i, c) in ((1, 0), (7, 2)):
+        pp, pm = pos.clone(), pos.clone()
+        pp[i, c] += h
+        pm[i, c] -= h
+        with torch.no_grad():
+            ep = m(z.cuda(), pp.cuda(), batch.cuda())[0].sum()
+            em = m(z.cuda(), pm.cuda(), batch.cuda())[0].sum()
+        assert abs(float(-(ep - em) / (2 * h)) - float(f[i, c])) <= 1e-6 * max(1.0, abs(float(f[i, c])))
+    p = pos.cuda().requires_grad_(True)
+    y2, f2 = m(z.cuda(), p, batch.cuda())
+    assert y2.requires_grad and f2.requires_grad                 # second derivatives are available (create_graph=True)
+    (h2,) = torch.autograd.grad(f2.pow(2).sum(), p)
+    assert bool(torch.isfinite(h2).all())

@@ -166,19 +166,29 @@ class TorchMD_Net(nn.Module):
             n_mol = self._num_molecules(batch)
         if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
             return self._forward_training(z, pos, batch, n_mol, extra_args)
+        if self.mean.dtype == torch.float64:
+            # precision: 64 (models/utils.py:586): the fused kernels are fp32; double-precision models run the differentiable
+            # composition (models/eager.py) with the fp64 neighbour op, which is what the reference's fp64 gradient check
+            # (tests/test_model.py:191-211) exercises.  Outside training the result is detached, like the fused path's.
+            with torch.enable_grad():
+                y, neg_dy = self._forward_training(z, pos.detach() if not torch.is_grad_enabled() else pos, batch, n_mol,
+                                                   extra_args, quiet=True)
+            if not torch.is_grad_enabled():
+                y, neg_dy = y.detach(), (None if neg_dy is None else neg_dy.detach())
+            return y, neg_dy
         mean, std = self._mean_std()
         y, neg_dy, _ = self.representation_model.energy_forces(z, pos, batch, n_mol, self.output_model, mean, std,
                                                                 compute_forces=self.derivative)
         y = self.apply_priors(y, z, batch, n_mol, pos, neg_dy if self.derivative else None, extra_args)
         return y, (neg_dy if self.derivative else None)
 
-    def _forward_training(self, z, pos, batch, n_mol, extra_args):
+    def _forward_training(self, z, pos, batch, n_mol, extra_args, quiet=False):
         """``model.train()`` with grad enabled: the differentiable composition of models/eager.py (training and
         double backward are outside the fused kernels).  Forces come from ``autograd.grad(create_graph=True)`` exactly as in
         the reference (model.py:286-298), so a force-matching loss back-propagates into the parameters.  Pairwise priors
         have no parameters: their energy and analytic forces are added as constants."""
         from . import eager
-        if not getattr(self, "_warned_training_path", False):
+        if not quiet and not getattr(self, "_warned_training_path", False):
             self._warned_training_path = True
             warnings.warn("TorchMD_Net is in training mode: forward runs the differentiable PyTorch composition "
                           "(models/eager.py) so that losses reach the parameters; call model.eval() for the fused "
