@@ -167,19 +167,18 @@ nbr_brute_kernel(const T* __restrict__ pos, const int64_t* __restrict__ batch, i
     }
 }
 
-// slots in [min(found, max_pairs), max_pairs) get the reference's padding values (common.cuh:70-76).  A thread covers
-// PAD_SPAN consecutive slots, so the (usually much larger) filled part of the list costs one early exit per 8 slots
-// instead of one thread per slot (0.29 -> 0.05 ms at 71 M slots).
+// slots in [min(found, max_pairs), max_pairs) get the reference's padding values (common.cuh:70-76).  A CTA covers
+// PAD_SPAN * 256 consecutive slots in PAD_SPAN coalesced passes, so the (usually much larger) filled part of the list
+// costs one early exit per CTA of 2048 slots instead of one thread per slot.
 constexpr int PAD_SPAN = 8;
 template <typename T> __global__ void pad_fill_kernel(PairOut<T> out) {
     pdl_sync();
-    const long long s0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * PAD_SPAN;
-    if (s0 >= out.max_pairs) return;
+    const long long base = (long long)blockIdx.x * blockDim.x * PAD_SPAN;
     const long long found = *out.counter;
-    if (s0 + PAD_SPAN <= found) return;
+    if (base + (long long)blockDim.x * PAD_SPAN <= found) return;
 #pragma unroll
     for (int k = 0; k < PAD_SPAN; ++k) {
-        const long long s = s0 + k;
+        const long long s = base + (long long)k * blockDim.x + threadIdx.x;
         if (s < found || s >= out.max_pairs) continue;
         out.nbr[s] = -1;
         out.nbr[out.max_pairs + s] = -1;
