@@ -82,6 +82,9 @@ int tmdn_profile_report(char* buf, size_t buf_bytes);
  *   "edge_variant" A/B instantiations of those kernels (bit 0: forward with 2 edges per batch, bit 1: backward with 8
  *                    workers of one edge at 64 registers instead of 4 workers of two edges at 128, bit 3: forward as
  *                    one CTA of 8 workers per SM instead of two CTAs of 5); same results
+ *   "small_csr"  1 = brute-force CSR builds of <= 256 atoms run as ONE kernel (count, scan, fill, clamp in a cluster of 8
+ *                    CTAs exchanging their row counts through distributed shared memory) instead of four launches; same
+ *                    rows in the same order (default 1)
  * Returns the previous value (>= 0); value < 0 only queries; -1 for an unknown key (tmdn_last_error says which).
  * Process-wide. */
 int tmdn_set_tuning(const char* key, int value);
@@ -288,17 +291,22 @@ int tmdn_tensornet_workspace_lookup(const tmdn_tensornet_model* m, int64_t n_ato
                                     size_t* offset, size_t* bytes);
 
 /* ---------------------------------------------------------------- pairwise priors: energy + analytic forces (fp32)
- * ZBL.post_reduce (torchmdnet/priors/zbl.py:47-63) and Coulomb.post_reduce (priors/coulomb.py:38-50) plus the autograd pass
+ * ZBL.post_reduce (torchmdnet/priors/zbl.py:47-63), Coulomb.post_reduce (priors/coulomb.py:38-50) and D2.post_reduce
+ * (priors/d2.py:163-193) plus the autograd pass
  * that differentiates them (models/model.py:286-298), on the pair set of the legacy Distance module (models/utils.py:393-455:
  * open boundaries, both directions, no self pairs): the neighbour search runs inside the call (brute strategy, the prior's
  * own cutoff; Coulomb has none: every pair of a molecule).
  *   energy[m] += 0.5 * energy_prefactor * sum_{pairs of m} V(d);   forces[i] -= dE/dpos_i   (forces may be NULL)
  *   ZBL:     V = phi(d * distance_scale / a_ij) * C(d; cutoff) * Z_i Z_j / d,  weight[i] = atomic number of atom i
  *   Coulomb: V = erf(alpha d) q_i q_j / (1e9 distance_scale d),               weight[i] = partial charge of atom i
- * energy_prefactor = 2.30707755e-28 / energy_scale / distance_scale (the caller's unit conversion, zbl.py:58).
+ *   D2:      V = sqrt(C6_i C6_j) / R^6 / (1 + exp(-alpha (R / (Rr_i + Rr_j) - 1))),  R = 1e9 distance_scale d  (nm);
+ *            weight has 2 * n_atoms entries: weight[i] = sqrt(C_6 of atom i) in (J/mol nm^6)^(1/2), weight[n_atoms + i] =
+ *            its van der Waals radius in nm; alpha = the damping steepness (20); the pair set ends at `cutoff`
+ * energy_prefactor = 2.30707755e-28 / energy_scale / distance_scale for ZBL and Coulomb (the caller's unit conversion,
+ * zbl.py:58), -s_6 / (energy_scale * 6.02214076e23) for D2 (d2.py:168,188-191).
  * *num_found = directed pairs + n_atoms self entries found; if it exceeds max_edges the pair set was truncated (the
  * reference asserts in that case, models/utils.py:419-425; the host side raises). */
-enum { TMDN_PRIOR_ZBL = 0, TMDN_PRIOR_COULOMB = 1 };
+enum { TMDN_PRIOR_ZBL = 0, TMDN_PRIOR_COULOMB = 1, TMDN_PRIOR_D2 = 2 };
 size_t tmdn_pair_prior_workspace_bytes(int64_t n_atoms, int64_t max_edges);
 int tmdn_pair_prior_f32(int kind, const float* pos, const int64_t* batch, const float* weight, int64_t n_atoms,
                         int64_t n_mol, double cutoff, double energy_prefactor, double distance_scale, double alpha,

@@ -164,3 +164,55 @@ def test_pairwise_priors_match_reference():
     m2.prior_model[0].max_num_neighbors = 1
     with pytest.raises(AssertionError, match="max_num_neighbors"):
         m2(z, pos, batch, extra_args={"partial_charges": q})
+
+
+# known answers of the reference's own test (tests/test_prior_d2.py:33-62; computed with Psi4, TPSS-D2, Hartree)
+D2_CASES = {
+    "he": ([2], [[0.0, 0.0, 0.0]], [0], [0.0]),
+    "h2": ([1, 1], [[0.0, 0.0, 0.0], [1.0, 0.0, 0.0]], [0, 0], [-2.396695338419219e-06]),
+    "h2o_n2_ch4": ([1, 8, 1, 7, 7, 6, 1, 1, 1],
+                   [[0.0, 0.0, 0.0], [0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [1.0, 2.0, 3.0], [2.0, 1.0, 3.0], [0.0, 0.0, 0.0],
+                    [1.0, 1.0, 0.0], [0.0, 1.0, 1.0], [1.0, 0.0, 1.0]], [0, 0, 0, 1, 1, 2, 2, 2, 2],
+                   [-4.7815923481300465e-06, -3.0071055390390565e-06, -7.100283425158895e-05]),
+}
+
+
+@pytest.mark.parametrize("name", list(D2_CASES))
+def test_d2_known_answers(name):
+    """D2.post_reduce against the Psi4 energies the reference pins (tests/test_prior_d2.py:65-85, same constructor call).
+    The reference compares with assert_allclose's fp32 defaults (rtol 1.3e-6, atol 1e-5 -- looser than the values); here
+    1e-5 relative, no absolute slack."""
+    from torchmdnet.priors import D2
+    z, pos, batch, y_ref = D2_CASES[name]
+    prior = D2(cutoff_distance=10.0, max_num_neighbors=128, atomic_number=list(range(100)), distance_scale=1e-10,
+               energy_scale=4.35974e-18).cuda()
+    y_ref = torch.tensor(y_ref)
+    y = prior.post_reduce(torch.zeros_like(y_ref).cuda(), torch.tensor(z).cuda(), torch.tensor(pos).cuda(),
+                          torch.tensor(batch).cuda(), {})
+    torch.testing.assert_close(y.cpu(), y_ref, rtol=1e-5, atol=0)
+
+
+def test_d2_prior_matches_reference():
+    """TensorNet + D2 against the fixture written by the unmodified reference (priors/d2.py; forces from its autograd pass),
+    and the prior alone against the reference's fp64 evaluation: energies 1e-5 relative, forces 1e-6 absolute (|F| <= 0.09)."""
+    g, m = _small("small_tensornet_d2.npz")
+    z, pos, batch = tt(g["z"]).cuda(), tt(g["pos"]).cuda(), tt(g["batch"]).cuda()
+    y, f = m(z, pos, batch)
+    check(y, f, g["y"], g["forces"])
+    prior = m.prior_model[0]
+    n_mol = int(batch.max()) + 1
+    e = torch.zeros(n_mol, 1, device="cuda")
+    frc = torch.zeros_like(pos)
+    prior.add_energy_forces(e, frc, z, pos, batch, None)
+    e_ref, f_ref = torch.as_tensor(g["y_prior_f64"]), torch.as_tensor(g["forces_prior_f64"])
+    assert float(((e.cpu().double() - e_ref).abs() / e_ref.abs()).max()) <= 1e-5
+    assert float((frc.cpu().double() - f_ref).abs().max()) <= 1e-6
+    torch.testing.assert_close(prior.post_reduce(torch.ones(n_mol, 1, device="cuda"), z, pos, batch, {}), e + 1.0)
+    # without the prior: the reference's run without it
+    m.prior_model = None
+    y0, f0 = m(z, pos, batch)
+    check(y0, f0, g["y_noprior"], g["forces_noprior"])
+    # too small a neighbour budget is caught (models/utils.py:419-425 asserts)
+    prior.max_num_neighbors = 1
+    with pytest.raises(AssertionError, match="max_num_neighbors"):
+        prior.post_reduce(torch.zeros(n_mol, 1, device="cuda"), z, pos, batch, {})

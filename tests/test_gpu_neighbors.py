@@ -301,3 +301,63 @@ def test_direct_csr_build_matches_oracle(case):
                                                                  torch.from_numpy(batch).cuda(), tb, periodic, 0.0,
                                                                  hi, E // 2)
     assert int(num3) == E and int(rp3.max()) == E // 2
+
+
+@pytest.mark.parametrize("case", ["one_molecule_166", "molecules_256", "periodic_tric_200", "single_atom", "lower_cutoff_97"])
+def test_small_csr_single_kernel_equals_the_four_launch_build(case):
+    """Systems of <= 256 atoms build their CSR in one single-CTA kernel (tuning knob "small_csr", csr_direct.cu): checked
+    against the oracle's pair list and bit for bit against the four-launch build, truncated structures included."""
+    from torchmdnet import _native
+    _native.load()
+    ops = torch.ops.torchmdnet_b200
+    rng = np.random.RandomState(33)
+    box, periodic, lo, hi = None, False, 0.0, 3.0
+    if case == "one_molecule_166":
+        pos, batch = (rng.rand(166, 3) * 9).astype(np.float32), np.zeros(166, dtype=np.int64)
+    elif case == "molecules_256":
+        sizes = [1, 40, 33, 2, 64, 17, 99]
+        batch = np.repeat(np.arange(len(sizes), dtype=np.int64), sizes)
+        pos = (rng.rand(256, 3) * 5).astype(np.float32)
+    elif case == "periodic_tric_200":
+        pos, batch = (rng.rand(200, 3) * 20 - 10).astype(np.float32), np.zeros(200, dtype=np.int64)
+        box, periodic = np.array([[10.0, 0, 0], [1.0, 10.0, 0], [3.0, 2.0, 10.0]], dtype=np.float32), True
+    elif case == "single_atom":
+        pos, batch = np.zeros((1, 3), dtype=np.float32), np.zeros(1, dtype=np.int64)
+    else:
+        pos, batch, lo = (rng.rand(97, 3) * 6).astype(np.float32), np.zeros(97, dtype=np.int64), 1.5
+    tb = torch.empty(0, 0) if box is None else torch.from_numpy(box)
+    tp, tbatch = torch.from_numpy(pos).cuda(), torch.from_numpy(batch).cuda()
+    if lo == 0.0:
+        ref_nb, ref_dl, ref_ds = _csr_reference(pos, batch, box if periodic else None, hi, rect=False)
+        E = ref_nb.shape[1]
+    else:
+        E = None
+    old = ops.set_tuning("small_csr", -1)
+    assert old == 1
+    try:
+        out = {}
+        for knob in (1, 0):
+            ops.set_tuning("small_csr", knob)
+            n0 = ops.launch_count()
+            full = ops.csr_build("brute", tp, tbatch, tb, periodic, lo, hi, 256 * 257)
+            launches = ops.launch_count() - n0
+            assert (launches == 1) if knob else (launches >= 4), launches
+            found = int(full[3])
+            cut = ops.csr_build("brute", tp, tbatch, tb, periodic, lo, hi, max(found // 2, 1))
+            out[knob] = (full, cut)
+        for a, b in zip(out[1], out[0]):
+            found = int(a[3])
+            assert found == int(b[3]) and torch.equal(a[0], b[0])
+            k = int(a[0][-1])          # row pointers are clamped to the capacity
+            assert torch.equal(a[1][:k], b[1][:k]) and torch.equal(a[2][:k], b[2][:k])
+        rp, col, geom, num = out[1][0]
+        if E is not None:
+            assert int(num) == E and np.array_equal(col.cpu().numpy()[:E], ref_nb[1])
+            assert np.array_equal(geom.cpu().numpy()[:E, 3], ref_ds)
+            assert np.array_equal(np.diff(rp.cpu().numpy()), np.bincount(ref_nb[0], minlength=pos.shape[0]))
+        else:
+            d = geom.cpu().numpy()[:int(num), 3]
+            assert ((d == 0) | ((d >= lo) & (d < hi))).all() and int(num) > pos.shape[0]
+        assert int(out[1][1][0].max()) == max(int(num) // 2, 1)
+    finally:
+        ops.set_tuning("small_csr", old)

@@ -160,6 +160,11 @@ def test_kernel_selection_knobs_agree():
         ops.set_tuning("lpt_rows", 1)
         y, f = m(z, pos, batch)
         assert torch.equal(y, y1) and torch.equal(f, f1)
+        # the single-kernel CSR build of small systems gives the same structure as the four-launch build: same bits
+        assert ops.set_tuning("small_csr", 0) == 1
+        y, f = m(z, pos, batch)
+        ops.set_tuning("small_csr", 1)
+        assert torch.equal(y, y1) and torch.equal(f, f1)
         for pdl in (0, 1):
             ops.set_tuning("pdl", pdl)
             for _ in range(3):

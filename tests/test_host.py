@@ -93,7 +93,7 @@ def test_cabi_tuning_knobs_without_a_gpu():
     lib.tmdn_last_error.restype = ctypes.c_char_p
     lib.tmdn_set_tuning.restype = ctypes.c_int
     lib.tmdn_set_tuning.argtypes = [ctypes.c_char_p, ctypes.c_int]
-    defaults = {b"small_gemm": 1, b"lpt_rows": 1, b"pdl": 0, b"edge_persist": 1}
+    defaults = {b"small_gemm": 1, b"lpt_rows": 1, b"pdl": 0, b"edge_persist": 1, b"small_csr": 1}
     for key, dflt in defaults.items():
         assert lib.tmdn_set_tuning(key, -1) == dflt, key
         assert lib.tmdn_set_tuning(key, 1 - dflt) == dflt
@@ -253,8 +253,8 @@ def test_external_box_routing(tmp_path):
 def test_atomref_prior_and_legacy_checkpoint_keys(tmp_path):
     """create_model / load_model with the Atomref prior (priors/atomref.py, models/model.py:96-98,146-177): the reference's
     state_dict keys load as they are, checkpoints from the time when Atomref was the only prior (un-indexed
-    ``prior_model.*`` keys, model.py:134-141) are renamed, the prior adds sum_i atomref[z_i] per molecule; ZBL and Coulomb are constructible
-    with the reference's arguments and D2 is refused by name."""
+    ``prior_model.*`` keys, model.py:134-141) are renamed, the prior adds sum_i atomref[z_i] per molecule; ZBL, Coulomb and D2 are constructible
+    with the reference's arguments and an unknown prior is refused by name."""
     from torchmdnet.models.model import create_model, load_model
     g = load_npz("small_tensornet_atomref.npz")
     hp = g["hparams"]
@@ -284,8 +284,8 @@ def test_atomref_prior_and_legacy_checkpoint_keys(tmp_path):
     assert create_prior_models({"prior_model": None}) is None
     assert create_prior_models({"prior_model": {"Atomref": {"max_z": 7}}})[0].initial_atomref.shape == (7, 1)
     assert len(create_prior_models({"prior_model": ["Atomref"], "prior_args": [{"max_z": 5}]})) == 1
-    with pytest.raises(NotImplementedError, match="D2"):
-        create_model(dict(hp, prior_model="D2", prior_args=None))
+    with pytest.raises(NotImplementedError, match="LearnableAtomref"):
+        create_model(dict(hp, prior_model="LearnableAtomref", prior_args=None))
     # the pairwise priors keep the reference's constructor arguments and init-arg round trip (zbl.py:20-45, coulomb.py:17-36)
     zargs = dict(cutoff_distance=4.0, max_num_neighbors=50, atomic_number=list(range(10)), distance_scale=1e-10,
                  energy_scale=1.602e-19)
@@ -295,3 +295,26 @@ def test_atomref_prior_and_legacy_checkpoint_keys(tmp_path):
     assert pm[1].get_init_args()["alpha"] == 1.8 and len(pm[1].state_dict()) == 0
     m3 = create_model(dict(hp, prior_model=[{"ZBL": zargs}], prior_args=None))
     assert "prior_model.0.atomic_number" in m3.state_dict()
+    # D2 (d2.py:109-161): constructor, buffers and parameter table as the reference's (the fixture holds ITS buffers);
+    # the list form of tests/priors.yaml with a dataset supplying the units (tests/test_priors.py:95-127)
+    gd = load_npz("small_tensornet_d2.npz")
+    dargs = gd["hparams"]["prior_model"][0]["D2"]
+    d2 = create_prior_models({"prior_model": [{"D2": dargs}]})[0]
+    assert d2.get_init_args() == dargs and list(d2.state_dict()) == ["Z_map", "C_6", "R_r"]
+    for k in ("Z_map", "C_6", "R_r"):
+        assert torch.equal(d2.state_dict()[k][1:], gd["sd"]["prior_model.0." + k][1:]), k       # entry 0 is NaN
+    assert torch.isnan(d2.C_6[0]) and d2.d == 20 and d2.s_6 == 1
+
+    class _Dataset:
+        atomic_number = list(range(20))
+        distance_scale = 1e-10
+        energy_scale = 4.35974e-18
+
+        def get_atomref(self):
+            return torch.arange(20.0)
+
+    pm = create_prior_models({"prior_model": [{"ZBL": {"cutoff_distance": 4.0, "max_num_neighbors": 50}},
+                                              {"D2": {"cutoff_distance": 10.0, "max_num_neighbors": 100}}, "Atomref"]},
+                             dataset=_Dataset())
+    assert [type(p).__name__ for p in pm] == ["ZBL", "D2", "Atomref"]
+    assert pm[1].cutoff_distance == 10.0 and pm[1].max_num_neighbors == 100 and pm[1].energy_scale == 4.35974e-18

@@ -7,6 +7,7 @@
 // No atomics on the output, no sort, and the edge order inside a row is a pure function of the positions
 // (ascending source index for brute; cell-traversal order of nbr_cell_tile.cuh with cells internally sorted by index for cell), so
 // every downstream segmented sum is bit-reproducible.  Same pair set and same rounding as tmdn_neighbors_f32.
+#include <cooperative_groups.h>
 #include <mutex>
 #include "common.cuh"
 #include "nbr_cell_tile.cuh"
@@ -56,18 +57,11 @@ __device__ __forceinline__ void emit(bool hit, int lane, int j, float dx, float 
 }
 
 // ------------------------------------------------------------------ brute: sources = the target's own molecule
+// one warp walks the sources [m0, m1) of target i in ascending order; -> number of hits
 template <bool FILL>
-__global__ void __launch_bounds__(CD_WARPS * 32)
-csr_brute_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int n, int n_rows, Box3<float> box,
-                 int periodic, float lo2, float hi2, EdgeOut out) {
-    pdl_sync();
-    const int i = blockIdx.x * CD_WARPS + (threadIdx.x >> 5);
-    const int lane = threadIdx.x & 31;
-    if (i >= n_rows) return;
-    const long long bi = batch[i];
-    const int m0 = lower_bound_batch(batch, n, bi), m1 = lower_bound_batch(batch, n, bi + 1);
+__device__ __forceinline__ int brute_row(const float* __restrict__ pos, int i, int lane, int m0, int m1, const Box3<float>& box,
+                                         int periodic, float lo2, float hi2, long long base, const EdgeOut& out) {
     const float xi = pos[3 * (size_t)i], yi = pos[3 * (size_t)i + 1], zi = pos[3 * (size_t)i + 2];
-    const long long base = FILL ? out.row_ptr[i] : 0;
     int run = 0;
     for (int j0 = m0; j0 < m1; j0 += 32) {
         const int j = j0 + lane;
@@ -87,7 +81,90 @@ csr_brute_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batc
         }
         emit<FILL>(hit, lane, j, dx, dy, dz, d2, run, base, out);
     }
+    return run;
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(CD_WARPS * 32)
+csr_brute_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int n, int n_rows, Box3<float> box,
+                 int periodic, float lo2, float hi2, EdgeOut out) {
+    pdl_sync();
+    const int i = blockIdx.x * CD_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (i >= n_rows) return;
+    const long long bi = batch[i];
+    const int m0 = lower_bound_batch(batch, n, bi), m1 = lower_bound_batch(batch, n, bi + 1);
+    const int run = brute_row<FILL>(pos, i, lane, m0, m1, box, periodic, lo2, hi2, FILL ? out.row_ptr[i] : 0, out);
     if (!FILL && lane == 0) out.row_cnt[i] = run;
+}
+
+// Small systems (n <= CS_MAX_ATOMS: a peptide in an MD loop): count, scan, fill and the capacity clamp of
+// csr_finish_kernel in ONE launch instead of four dependent ones.  One thread-block cluster of 8 CTAs: CTA r owns the
+// contiguous rows [r * per, (r + 1) * per), a warp walks a row (brute_row, as above), the CTAs exchange their edge totals
+// through distributed shared memory between the counting and the filling pass.  Same walk, same order inside a row,
+// same clamping: bitwise the same structure.  (A single CTA was tried first: 35 us at 166 atoms against 22 us for the
+// four launches -- 2 x 27 k pair tests are instruction-bound on one SM, gpurun r02v.)
+constexpr int CS_MAX_ATOMS = 256, CS_CLUSTER = 8, CS_ROWS = CS_MAX_ATOMS / CS_CLUSTER, CS_THREADS = 512;
+__global__ void __cluster_dims__(CS_CLUSTER, 1, 1) __launch_bounds__(CS_THREADS)
+csr_brute_small_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int n, Box3<float> box,
+                       int periodic, float lo2, float hi2, int* __restrict__ row_ptr, int32_t* __restrict__ col,
+                       float4* __restrict__ geom, long long cap, int32_t* __restrict__ num_found) {
+    pdl_sync();
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    __shared__ int s_m0[CS_ROWS], s_m1[CS_ROWS], s_start[CS_ROWS], s_total, s_base;
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    const int rank = (int)cluster.block_rank();
+    const int per = (n + CS_CLUSTER - 1) / CS_CLUSTER;           // <= CS_ROWS = 32
+    const int r0 = rank * per;
+    const EdgeOut out{nullptr, nullptr, col, geom, cap};
+    for (int li = wrp; li < per; li += CS_THREADS / 32) {
+        const int i = r0 + li;
+        int run = 0, m0 = 0, m1 = 0;
+        if (i < n) {
+            const long long bi = batch[i];
+            m0 = lower_bound_batch(batch, n, bi);
+            m1 = lower_bound_batch(batch, n, bi + 1);
+            run = brute_row<false>(pos, i, lane, m0, m1, box, periodic, lo2, hi2, 0, out);
+        }
+        if (lane == 0) { s_m0[li] = m0; s_m1[li] = m1; s_start[li] = run; }
+    }
+    __syncthreads();
+    if (wrp == 0) {                                              // exclusive scan of this CTA's <= 32 counts
+        const int v = lane < per ? s_start[lane] : 0;
+        int incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += u;
+        }
+        if (lane < per) s_start[lane] = incl - v;
+        if (lane == 31) s_total = incl;
+    }
+    cluster.sync();
+    if (wrp == 0) {                                              // edges of the CTAs before this one, and of all of them
+        const int t = lane < CS_CLUSTER ? *cluster.map_shared_rank(&s_total, lane) : 0;
+        const int before = warp_sum_i(lane < rank ? t : 0);
+        const int all = warp_sum_i(t);
+        if (lane == 0) {
+            s_base = before;
+            if (rank == 0) {
+                row_ptr[n] = all > cap ? (int)cap : all;
+                *num_found = all;
+            }
+        }
+    }
+    __syncthreads();
+    const int base = s_base;
+    if (threadIdx.x < per && r0 + threadIdx.x < n) {
+        const int start = base + s_start[threadIdx.x];
+        row_ptr[r0 + threadIdx.x] = start > cap ? (int)cap : start;
+    }
+    for (int li = wrp; li < per; li += CS_THREADS / 32) {
+        const int i = r0 + li;
+        if (i < n) brute_row<true>(pos, i, lane, s_m0[li], s_m1[li], box, periodic, lo2, hi2, base + s_start[li], out);
+    }
+    cluster.sync();                                              // nobody leaves while its shared memory may still be read
 }
 
 // ------------------------------------------------------------------ cell list
@@ -228,6 +305,12 @@ extern "C" int tmdn_csr_build_rows_f32(int strategy, const float* pos, const int
         Box3<float> b;
         for (int r = 0; r < 3; ++r)
             for (int c = 0; c < 3; ++c) b.m[r][c] = (use_periodic && box) ? (float)box[3 * r + c] : 0.f;
+        if (nr == n && n <= CS_MAX_ATOMS && g_tmdn_tuning[TMDN_TUNE_SMALL_CSR]) {
+            launch_k(csr_brute_small_kernel, CS_CLUSTER, CS_THREADS, 0, stream, pos, batch, n, b, use_periodic, lo2, hi2, row_ptr, col,
+                     (float4*)geom, (long long)max_edges, num_found);
+            TMDN_LAUNCH_CHECK();
+            return TMDN_OK;
+        }
         launch_k(csr_brute_kernel<false>, rgrid, CD_WARPS * 32, 0, stream, pos, batch, n, nr, b, use_periodic, lo2, hi2, cnt);
         TMDN_LAUNCH_CHECK();
         TMDN_TRY(tmdn_scan_exclusive_i32(w.row_cnt, row_ptr, n_atoms, w.scan_tmp, stream));

@@ -289,12 +289,8 @@ __global__ void __launch_bounds__(128) et_mol_reduce(const float* __restrict__ e
     pdl_sync();
     __shared__ float s_part[128];
     const long long m = blockIdx.x;
-    int lo = 0, hi = N;
-    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m) lo = mid + 1; else hi = mid; }
-    const int a = lo;
-    hi = N;
-    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m + 1) lo = mid + 1; else hi = mid; }
-    const int b = lo;
+    int a, b;
+    block_molecule_range(batch, N, m, a, b);
     float s = 0.f;
     for (int i = a + threadIdx.x; i < b; i += 128) s += e_atom[i];
     s_part[threadIdx.x] = s;

@@ -132,16 +132,29 @@ __global__ void __launch_bounds__(GTHREADS) sgemm_nt_kernel(GemmBatch batch) {
 // ---------------------------------------------------------------------------------------------------------------
 // Latency-oriented variant for small problems (a few hundred rows: single molecules, MD of a peptide).  The tiled
 // kernel above walks K in 16-wide steps with one global round trip per step (K = 384 -> 24 dependent round trips,
-// 11-27 us at 166 atoms, ncu r01h); here a CTA owns a (16*RM) x 32 output tile, fetches its whole A and W panels with
+// 11-27 us at 166 atoms, ncu r01h); here a CTA owns a (16*RM) x 32 output tile (RM = 1 in use), fetches its whole A and W panels with
 // one burst of 16-byte cp.async copies (a single memory round trip, nothing staged through registers) and then runs
 // the K loop out of shared memory.  Same epilogues, same row map, same fp32 FFMA arithmetic (sum order over k
 // differs from the tiled kernel only in being strictly sequential).
-constexpr int SBN = 32, STHREADS = 256, SMALL_MAX_K = 768;
+constexpr int SBN = 32, SMALL_MAX_K = 768;
+// Tile and thread tile in use.  Chain of channel mixes inside a CUDA graph, us per launch at 42 / 166 / 500 / 1000 atoms
+// (profiles/microbench_small_gemm.cu, r02w): 32 x 32 tiles, 2 x 2 per thread, 256 threads (the first version; it switched
+// to 16 x 32, 1 x 2 below 148 tiles) 4.8 / 8.3 / 14.4 / 27.7; 16 x 32, 2 x 2, 128 threads 5.2 / 7.7 / 11.3 / 20.2;
+// larger thread tiles (4 x 2 ... 8 x 2) are slower (fewer warps to hide the LDS latency), an empty kernel of the same
+// shape takes 0.6 and the panel fetch alone 3.5 us.
+constexpr int SMALL_RM = 1, SMALL_TM = 2, SMALL_TN = 2;
 
-template <int EPI, int RM>
-__global__ void __launch_bounds__(STHREADS) sgemm_small_kernel(GemmBatch batch) {
+// A thread owns TM x TN outputs: rows ty + (BM / TM) r, columns tx + (SBN / TN) c -- interleaved so that the 16-byte
+// shared-memory reads of a warp fall on distinct banks or coincide (row stride K + 4 words = 4 banks).  The first version
+// (TM x TN = RM x 2, 256 threads) issued 4 LDS.128 per 16 FFMA and was bound by the shared-memory pipe: of the 8.1 us a
+// 166-atom channel mix takes inside a graph, 0.6 are the launch, 2.8 the panel fetch and 4.7 the K loop
+// (profiles/microbench_small_gemm.cu, gpurun r02w).  Every output is still one strictly sequential fmaf chain over k, so
+// all tilings give the same bits.
+template <int EPI, int RM, int TM, int TN>
+__global__ void __launch_bounds__((16 * RM / TM) * (SBN / TN)) sgemm_small_kernel(GemmBatch batch) {
     extern __shared__ __align__(16) float sg_smem[];
-    constexpr int BM = 16 * RM;
+    constexpr int BM = 16 * RM, TROWS = BM / TM, TCOLS = SBN / TN, NT = TROWS * TCOLS, NW = NT / 32;
+    static_assert(NT % 32 == 0 && BM % TM == 0 && SBN % TN == 0, "thread tile");
     const GemmP& P = batch.p[blockIdx.z];
     const int m0 = blockIdx.x * BM, n0 = blockIdx.y * SBN;
     // the weight panel does not depend on the previous kernel: its copies are issued before the dependency wait, so
@@ -152,11 +165,11 @@ __global__ void __launch_bounds__(STHREADS) sgemm_small_kernel(GemmBatch batch) 
     float* As = sg_smem;
     float* Ws = sg_smem + BM * ld;
     const int t = threadIdx.x;
-    // copies: a warp takes one row at a time (lane = 16-byte column, strided by 32 for K > 128), 8 rows per pass over
-    // the CTA -- no integer division per copy (the first version spent half of its instructions on idx / kv)
+    // copies: a warp takes one row at a time (lane = 16-byte column, strided by 32 for K > 128) -- no integer division
+    // per copy (the first version spent half of its instructions on idx / kv)
     const int lane = t & 31, wrp = t >> 5;
     auto load_w = [&]() {
-        for (int row = wrp; row < SBN; row += STHREADS / 32) {
+        for (int row = wrp; row < SBN; row += NW) {
             const int n = n0 + row;
             const bool ok = n < P.N;
             const float* src = P.W + (size_t)(ok ? n : 0) * K;
@@ -170,7 +183,7 @@ __global__ void __launch_bounds__(STHREADS) sgemm_small_kernel(GemmBatch batch) 
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (!live) return;
     if (!P.w_static) load_w();
-    for (int row = wrp; row < BM; row += STHREADS / 32) {
+    for (int row = wrp; row < BM; row += NW) {
         const int m = m0 + row;
         const bool ok = m < P.M;
         const size_t prow = !ok ? 0 : (P.gs == 1 ? (size_t)m * P.rpa + P.c0 : (size_t)(m / P.gs) * P.rpa + P.c0 + m % P.gs);
@@ -183,23 +196,25 @@ __global__ void __launch_bounds__(STHREADS) sgemm_small_kernel(GemmBatch batch) 
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
-    const int tx = t & 15, ty = t >> 4;
-    float acc[RM][2];
+    const int tx = t % TCOLS, ty = t / TCOLS;
+    float acc[TM][TN];
 #pragma unroll
-    for (int r = 0; r < RM; ++r) acc[r][0] = acc[r][1] = 0.f;
+    for (int r = 0; r < TM; ++r)
+#pragma unroll
+        for (int c = 0; c < TN; ++c) acc[r][c] = 0.f;
     const float* a0 = As + ty * ld;
     const float* w0 = Ws + tx * ld;
-#pragma unroll 4
+#pragma unroll 2
     for (int k = 0; k < K; k += 4) {
-        float4 a[RM], w[2];
+        float4 a[TM], w[TN];
 #pragma unroll
-        for (int r = 0; r < RM; ++r) a[r] = *reinterpret_cast<const float4*>(a0 + r * 16 * ld + k);
+        for (int r = 0; r < TM; ++r) a[r] = *reinterpret_cast<const float4*>(a0 + r * TROWS * ld + k);
 #pragma unroll
-        for (int c = 0; c < 2; ++c) w[c] = *reinterpret_cast<const float4*>(w0 + c * 16 * ld + k);
+        for (int c = 0; c < TN; ++c) w[c] = *reinterpret_cast<const float4*>(w0 + c * TCOLS * ld + k);
 #pragma unroll
-        for (int r = 0; r < RM; ++r)
+        for (int r = 0; r < TM; ++r)
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
+            for (int c = 0; c < TN; ++c) {
                 acc[r][c] = fmaf(a[r].x, w[c].x, acc[r][c]);
                 acc[r][c] = fmaf(a[r].y, w[c].y, acc[r][c]);
                 acc[r][c] = fmaf(a[r].z, w[c].z, acc[r][c]);
@@ -207,14 +222,14 @@ __global__ void __launch_bounds__(STHREADS) sgemm_small_kernel(GemmBatch batch) 
             }
     }
 #pragma unroll
-    for (int r = 0; r < RM; ++r) {
-        const int m = m0 + ty + 16 * r;
+    for (int r = 0; r < TM; ++r) {
+        const int m = m0 + ty + TROWS * r;
         if (m >= P.M) continue;
         const int atom = m / P.gs;
         const size_t prow = (size_t)atom * P.rpa + P.c0 + m % P.gs;
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            const int n = n0 + tx + 16 * c;
+        for (int c = 0; c < TN; ++c) {
+            const int n = n0 + tx + TCOLS * c;
             if (n >= P.N) continue;
             float v = acc[r][c];
             if (P.bias) v += P.bias[n];
@@ -247,25 +262,26 @@ static inline bool small_gemm_ok(const GemmBatch& b) {
     return macs <= 160LL * 1000 * 1000;   // ~9k rows of a 128 x 128 mix; above that throughput kernels win
 }
 
-template <int RM>
-static inline int small_gemm_launch_rm(int epi, const GemmBatch& b, dim3 grid, size_t smem, cudaStream_t stream) {
+template <int RM, int TM, int TN>
+static inline int small_gemm_launch_cfg(int epi, const GemmBatch& b, dim3 grid, size_t smem, cudaStream_t stream) {
     static bool attr_set = false;
     if (!attr_set) {
         const int maxb = (16 * RM + SBN) * (SMALL_MAX_K + 4) * (int)sizeof(float);
-        if (cudaFuncSetAttribute(sgemm_small_kernel<EPI_NONE, RM>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess ||
-            cudaFuncSetAttribute(sgemm_small_kernel<EPI_ACT, RM>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess ||
-            cudaFuncSetAttribute(sgemm_small_kernel<EPI_MULGRAD, RM>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess ||
-            cudaFuncSetAttribute(sgemm_small_kernel<EPI_SCALE3, RM>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess) {
+        if (cudaFuncSetAttribute(sgemm_small_kernel<EPI_NONE, RM, TM, TN>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess ||
+            cudaFuncSetAttribute(sgemm_small_kernel<EPI_ACT, RM, TM, TN>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess ||
+            cudaFuncSetAttribute(sgemm_small_kernel<EPI_MULGRAD, RM, TM, TN>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess ||
+            cudaFuncSetAttribute(sgemm_small_kernel<EPI_SCALE3, RM, TM, TN>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb) != cudaSuccess) {
             tmdn_set_error("gemm: cudaFuncSetAttribute failed: %s", cudaGetErrorString(cudaGetLastError()));
             return TMDN_ECUDA;
         }
         attr_set = true;
     }
+    constexpr unsigned threads = (16 * RM / TM) * (SBN / TN);
     switch (epi) {
-        case EPI_NONE: launch_k(sgemm_small_kernel<EPI_NONE, RM>, grid, STHREADS, smem, stream, b); break;
-        case EPI_ACT: launch_k(sgemm_small_kernel<EPI_ACT, RM>, grid, STHREADS, smem, stream, b); break;
-        case EPI_MULGRAD: launch_k(sgemm_small_kernel<EPI_MULGRAD, RM>, grid, STHREADS, smem, stream, b); break;
-        case EPI_SCALE3: launch_k(sgemm_small_kernel<EPI_SCALE3, RM>, grid, STHREADS, smem, stream, b); break;
+        case EPI_NONE: launch_k(sgemm_small_kernel<EPI_NONE, RM, TM, TN>, grid, threads, smem, stream, b); break;
+        case EPI_ACT: launch_k(sgemm_small_kernel<EPI_ACT, RM, TM, TN>, grid, threads, smem, stream, b); break;
+        case EPI_MULGRAD: launch_k(sgemm_small_kernel<EPI_MULGRAD, RM, TM, TN>, grid, threads, smem, stream, b); break;
+        case EPI_SCALE3: launch_k(sgemm_small_kernel<EPI_SCALE3, RM, TM, TN>, grid, threads, smem, stream, b); break;
         default: tmdn_set_error("gemm: bad epilogue"); return TMDN_EINVAL;
     }
     TMDN_LAUNCH_CHECK();
@@ -275,17 +291,14 @@ static inline int small_gemm_launch_rm(int epi, const GemmBatch& b, dim3 grid, s
 static inline int small_gemm_launch(int epi, const GemmBatch& b, cudaStream_t stream, const char* tag) {
     KTimer ktimer__(tag, stream);
     int maxM = 0, maxN = 0;
-    long long tiles32 = 0;
     for (int i = 0; i < b.n; ++i) {
         if (b.p[i].M > maxM) maxM = b.p[i].M;
         if (b.p[i].N > maxN) maxN = b.p[i].N;
-        tiles32 += cdiv(b.p[i].M, 32) * cdiv(b.p[i].N, SBN);
     }
     if (maxM == 0 || maxN == 0) return TMDN_OK;
-    const int rm = tiles32 < 148 ? 1 : 2;   // 16-row tiles while the 32-row grid would leave SMs idle
-    const dim3 grid((unsigned)cdiv(maxM, 16 * rm), (unsigned)cdiv(maxN, SBN), (unsigned)b.n);
-    const size_t smem = (size_t)(16 * rm + SBN) * (b.p[0].K + 4) * sizeof(float);
-    return rm == 1 ? small_gemm_launch_rm<1>(epi, b, grid, smem, stream) : small_gemm_launch_rm<2>(epi, b, grid, smem, stream);
+    const dim3 grid((unsigned)cdiv(maxM, 16 * SMALL_RM), (unsigned)cdiv(maxN, SBN), (unsigned)b.n);
+    const size_t smem = (size_t)(16 * SMALL_RM + SBN) * (b.p[0].K + 4) * sizeof(float);
+    return small_gemm_launch_cfg<SMALL_RM, SMALL_TM, SMALL_TN>(epi, b, grid, smem, stream);
 }
 
 static inline GemmP gemm_desc(const float* A, int lda, const float* W, const float* bias, float* C, int ldc, int M,

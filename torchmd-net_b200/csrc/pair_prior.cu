@@ -9,17 +9,19 @@
 //     F_i   -= scale * sum_{e in row i} V'(d_e) * u_e               (the pair appears in row i and in row j; both depend on pos_i)
 //   ZBL      V = phi(d s / a_ij) C(d) Z_i Z_j / d,   a_ij = 0.8854 a0 / (Z_i^0.23 + Z_j^0.23),   phi = sum_k c_k exp(-b_k x)
 //   Coulomb  V = erf(alpha d) q_i q_j / (1e9 s d)                   (positions converted to nm, priors/coulomb.py:40-41)
+//   D2       V = sqrt(C6_i C6_j) / R^6 / (1 + exp(-dmp (R / (Rr_i + Rr_j) - 1))),  R = 1e9 s d  (nm; priors/d2.py:171-191,
+//            Grimme 2006; scale = -s_6 / (energy_scale N_A), no cutoff function: the pair set ends at the cutoff)
 #include "common.cuh"
 #include "edge_common.cuh"
 
 namespace {
 
 struct PriorParams {
-    int kind;            // TMDN_PRIOR_ZBL | TMDN_PRIOR_COULOMB
+    int kind;            // TMDN_PRIOR_ZBL | TMDN_PRIOR_COULOMB | TMDN_PRIOR_D2
     float scale;         // energy prefactor WITHOUT the 0.5 of the double counting
     float cutoff;        // ZBL: cosine cutoff radius
     float dist_scale;    // distance unit -> metres
-    float alpha;         // Coulomb
+    float alpha;         // Coulomb: erf range parameter; D2: steepness of the damping function
 };
 
 __device__ __forceinline__ void zbl_pair(float d, float zi, float zj, const PriorParams& p, float& v, float& dv) {
@@ -44,7 +46,20 @@ __device__ __forceinline__ void coulomb_pair(float d, float qi, float qj, const 
     dv = qq * (1.1283791670955126f * p.alpha * expf(-ad * ad) * inv - er * inv * inv);
 }
 
-// one warp per target atom; w[i] = atomic number (ZBL: table[z_i], as float) or partial charge (Coulomb)
+// wi/wj = sqrt(C_6) of the atoms (J/mol nm^6)^(1/2), ri/rj = their van der Waals radii in nm
+__device__ __forceinline__ void d2_pair(float d, float wi, float wj, float ri, float rj, const PriorParams& p, float& v,
+                                        float& dv) {
+    const float nm = 1e9f * p.dist_scale;
+    const float R = d * nm, inv = 1.0f / R, inv2 = inv * inv;
+    const float c = wi * wj * inv2 * inv2 * inv2;          // C6_ij / R^6
+    const float inv_rr = 1.0f / (ri + rj);
+    const float f = 1.0f / (1.0f + expf(-p.alpha * (R * inv_rr - 1.0f)));
+    v = c * f;
+    dv = nm * c * f * (p.alpha * inv_rr * (1.0f - f) - 6.0f * inv);
+}
+
+// one warp per target atom; w[i] = atomic number (ZBL: table[z_i], as float) or partial charge (Coulomb);
+// D2: w[i] = sqrt(C_6) and w[n + i] = R_r of atom i
 __global__ void __launch_bounds__(128) pair_prior_rows(const int* __restrict__ row_ptr, const int* __restrict__ col,
                                                        const float4* __restrict__ geom, const float* __restrict__ w,
                                                        PriorParams p, int n, float* __restrict__ e_row,
@@ -53,6 +68,7 @@ __global__ void __launch_bounds__(128) pair_prior_rows(const int* __restrict__ r
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (i >= n) return;
     const float wi = w[i];
+    const float ri = p.kind == TMDN_PRIOR_D2 ? w[n + i] : 0.f;
     float e = 0.f, fx = 0.f, fy = 0.f, fz = 0.f;
     for (int k = row_ptr[i] + lane; k < row_ptr[i + 1]; k += 32) {
         const int j = col[k];
@@ -60,6 +76,7 @@ __global__ void __launch_bounds__(128) pair_prior_rows(const int* __restrict__ r
         const float4 g = geom[k];
         float v, dv;
         if (p.kind == TMDN_PRIOR_ZBL) zbl_pair(g.w, wi, w[j], p, v, dv);
+        else if (p.kind == TMDN_PRIOR_D2) d2_pair(g.w, wi, w[j], ri, w[n + j], p, v, dv);
         else coulomb_pair(g.w, wi, w[j], p, v, dv);
         e += v;
         fx += dv * g.x; fy += dv * g.y; fz += dv * g.z;
@@ -81,13 +98,10 @@ __global__ void __launch_bounds__(128) pair_prior_mol_add(const float* __restric
     pdl_sync();
     __shared__ float s_part[128];
     const long long m = blockIdx.x;
-    int lo = 0, hi = n;
-    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m) lo = mid + 1; else hi = mid; }
-    const int a = lo;
-    hi = n;
-    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m + 1) lo = mid + 1; else hi = mid; }
+    int a, b;
+    block_molecule_range(batch, n, m, a, b);
     float s = 0.f;
-    for (int i = a + threadIdx.x; i < lo; i += 128) s += e_row[i];
+    for (int i = a + threadIdx.x; i < b; i += 128) s += e_row[i];
     s_part[threadIdx.x] = s;
     __syncthreads();
     for (int o = 64; o > 0; o >>= 1) {
@@ -112,10 +126,10 @@ extern "C" int tmdn_pair_prior_f32(int kind, const float* pos, const int64_t* ba
                                    double alpha, int64_t max_edges, float* energy, float* forces, int32_t* num_found,
                                    void* workspace, size_t workspace_bytes, tmdn_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
-    TMDN_CHECK_ARG(kind == TMDN_PRIOR_ZBL || kind == TMDN_PRIOR_COULOMB, "pair_prior: unknown kind %d", kind);
+    TMDN_CHECK_ARG(kind == TMDN_PRIOR_ZBL || kind == TMDN_PRIOR_COULOMB || kind == TMDN_PRIOR_D2, "pair_prior: unknown kind %d", kind);
     TMDN_CHECK_ARG(pos && batch && weight && energy && num_found && workspace, "pair_prior: null pointer argument");
     TMDN_CHECK_ARG(n_atoms > 0 && n_mol > 0 && max_edges > 0, "pair_prior: bad sizes");
-    TMDN_CHECK_ARG(kind != TMDN_PRIOR_ZBL || cutoff > 0, "pair_prior: ZBL needs a positive cutoff distance");
+    TMDN_CHECK_ARG(kind == TMDN_PRIOR_COULOMB || cutoff > 0, "pair_prior: ZBL and D2 need a positive cutoff distance");
     Arena a(workspace, workspace_bytes);
     int32_t* row_ptr = a.get<int32_t>(n_atoms + 1);
     int32_t* col = a.get<int32_t>(max_edges);
@@ -129,7 +143,7 @@ extern "C" int tmdn_pair_prior_f32(int kind, const float* pos, const int64_t* ba
         return TMDN_EWORKSPACE;
     }
     // Coulomb has no cutoff (Distance(0, inf)): every pair of a molecule; a huge finite radius keeps the builder's d^2 test
-    const double rc = kind == TMDN_PRIOR_ZBL ? cutoff : 1e18;
+    const double rc = kind == TMDN_PRIOR_COULOMB ? 1e18 : cutoff;
     TMDN_TRY(tmdn_csr_build_f32(TMDN_BRUTE, pos, batch, n_atoms, nullptr, 0, 0.0, rc, max_edges, row_ptr, col, geom, found,
                                 graph_ws, gws, stream_));
     TMDN_CUDA(cudaMemcpyAsync(num_found, found, sizeof(int32_t), cudaMemcpyDeviceToDevice, stream));

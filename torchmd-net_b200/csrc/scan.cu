@@ -42,12 +42,14 @@ extern "C" long long tmdn_launch_count(void) { return g_launches.load(); }
 //   hot_rows:     number of table rows (from the far end of the grid) those kernels keep in shared memory
 //   edge_variant: A/B instantiations of the persistent kernels (bit 0: forward 2 edges per batch; bit 1: backward 8 workers x 1 edge; bit 3: forward 1 x 8 workers);
 //                 same sums in the same order
+//   small_csr:    systems of <= 256 atoms build their CSR neighbour structure in ONE kernel (a cluster of 8 CTAs; same rows, same order)
 static int env_or(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 int g_tmdn_tuning[TMDN_TUNE_COUNT] = {env_or("TMDN_SMALL_GEMM", 1), env_or("TMDN_LPT_ROWS", 1), env_or("TMDN_PDL", 0),
                                          env_or("TMDN_EDGE_PERSIST", 1), env_or("TMDN_HOT_ROWS", 0),
-                                         env_or("TMDN_EDGE_VARIANT", 0)};
+                                         env_or("TMDN_EDGE_VARIANT", 0), env_or("TMDN_SMALL_CSR", 1)};
 extern "C" int tmdn_set_tuning(const char* key, int value) {
-    static const char* names[TMDN_TUNE_COUNT] = {"small_gemm", "lpt_rows", "pdl", "edge_persist", "hot_rows", "edge_variant"};
+    static const char* names[TMDN_TUNE_COUNT] = {"small_gemm", "lpt_rows", "pdl", "edge_persist", "hot_rows", "edge_variant",
+                                                 "small_csr"};
     if (!key) { tmdn_set_error("set_tuning: null key"); return -1; }
     for (int i = 0; i < TMDN_TUNE_COUNT; ++i)
         if (strcmp(key, names[i]) == 0) {

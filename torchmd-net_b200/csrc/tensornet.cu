@@ -780,12 +780,8 @@ __global__ void __launch_bounds__(128) tn_mol_reduce(const float* __restrict__ e
     pdl_sync();
     __shared__ float s_part[128];
     const long long m = blockIdx.x;
-    int lo = 0, hi = N;  // first index with batch >= m
-    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m) lo = mid + 1; else hi = mid; }
-    const int a = lo;
-    hi = N;
-    while (lo < hi) { const int mid = (lo + hi) >> 1; if (batch[mid] < m + 1) lo = mid + 1; else hi = mid; }
-    const int b = lo;
+    int a, b;
+    block_molecule_range(batch, N, m, a, b);
     float s = 0.f;
     for (int i = a + threadIdx.x; i < b; i += 128) s += e_atom[i];
     s_part[threadIdx.x] = s;
@@ -1090,7 +1086,7 @@ int mix_launch(int epi, const GemmBatch& b, cudaStream_t stream) {
     static const int use_tc = [] { const char* e = getenv("TMDN_TC_MIX"); return e ? atoi(e) : 1; }();
     // small systems (<= ~1000 atoms): a handful of tensor-core tiles on 13 SMs loses to the latency-oriented FFMA
     // kernel spread over the whole machine (166 atoms: 13 us -> see profiles/r01i)
-    if (small_gemm_ok(b)) return small_gemm_launch(epi, b, stream, "node_gemm_small");
+    if (small_gemm_ok(b)) return gemm_launch(epi, b, stream);
     if (use_tc && (epi == EPI_NONE || epi == EPI_SCALE3) && tcmix::supported(b)) return tcmix::launch(epi, b, stream);
     return gemm_launch(epi, b, stream);
 }

@@ -913,9 +913,10 @@ Tensor pair_prior(const std::string& kind, const Tensor& pos, const Tensor& batc
     check_input(pos, batch);
     TORCH_CHECK(pos.scalar_type() == at::kFloat, "pair_prior: fp32 positions only");
     TORCH_CHECK(weight.is_cuda() && weight.scalar_type() == at::kFloat && weight.is_contiguous() &&
-                    weight.numel() == pos.size(0), "pair_prior: weight must be a contiguous CUDA float32 [N] tensor");
+                    weight.numel() == (kind == "d2" ? 2 : 1) * pos.size(0),
+                "pair_prior: weight must be a contiguous CUDA float32 [N] tensor ([2,N] for d2)");
     TORCH_CHECK(energy.is_cuda() && energy.scalar_type() == at::kFloat && energy.is_contiguous(), "pair_prior: energy");
-    const int k = kind == "zbl" ? TMDN_PRIOR_ZBL : kind == "coulomb" ? TMDN_PRIOR_COULOMB : -1;
+    const int k = kind == "zbl" ? TMDN_PRIOR_ZBL : kind == "coulomb" ? TMDN_PRIOR_COULOMB : kind == "d2" ? TMDN_PRIOR_D2 : -1;
     TORCH_CHECK(k >= 0, "pair_prior: unknown kind '", kind, "'");
     float* fp = nullptr;
     if (forces.has_value() && forces->defined() && forces->numel() > 0) {

@@ -71,7 +71,7 @@ def create_model(args, prior_model=None, mean=None, std=None):
 
 def create_prior_models(args, dataset=None):
     """Parse the ``prior_model`` option (str | dict | list of them, with ``prior_args``) as models/model.py:146-177.
-    Built here: ``Atomref``, ``ZBL``, ``Coulomb``; ``D2`` is refused."""
+    Built here: ``Atomref``, ``ZBL``, ``Coulomb``, ``D2``."""
     from .. import priors
     prior_models = []
     if args.get("prior_model"):
@@ -128,11 +128,11 @@ class TorchMD_Net(nn.Module):
         super().__init__()
         self.representation_model = representation_model.to(dtype=dtype)
         self.output_model = output_model.to(dtype=dtype)
-        from ..priors import Atomref, BasePrior, Coulomb, ZBL
+        from ..priors import D2, Atomref, BasePrior, Coulomb, ZBL
         if isinstance(prior_model, BasePrior):
             prior_model = [prior_model]
-        if prior_model is not None and not all(isinstance(p, (Atomref, ZBL, Coulomb)) for p in prior_model):
-            raise NotImplementedError("priors built here: Atomref, ZBL, Coulomb")
+        if prior_model is not None and not all(isinstance(p, (Atomref, ZBL, Coulomb, D2)) for p in prior_model):
+            raise NotImplementedError("priors built here: Atomref, ZBL, Coulomb, D2")
         self.prior_model = None if not prior_model else nn.ModuleList(prior_model).to(dtype=dtype)
         self.derivative = derivative
         mean = torch.scalar_tensor(0) if mean is None else mean

@@ -1,7 +1,7 @@
 """Prior models (reference: torchmdnet/priors/).  Built: ``Atomref`` (atom-wise reference energies; forces are not
-affected, one gather + segment sum on the GPU) and the pairwise ``ZBL`` and ``Coulomb`` potentials (one fused CUDA call for
-energy and analytic forces, priors/pairwise.py).  ``D2`` is outside this build and is refused by ``create_model``."""
+affected, one gather + segment sum on the GPU) and the pairwise ``ZBL``, ``Coulomb`` and ``D2`` potentials (one fused CUDA
+call for energy and analytic forces, priors/pairwise.py)."""
 from .atomref import Atomref, BasePrior
-from .pairwise import ZBL, Coulomb
+from .pairwise import D2, ZBL, Coulomb
 
-__all__ = ["Atomref", "ZBL", "Coulomb"]
+__all__ = ["Atomref", "ZBL", "Coulomb", "D2"]
