@@ -528,20 +528,20 @@ __global__ void __launch_bounds__(MAXT) tn_msg_fwd(const int* __restrict__ row_p
 }
 
 // persistent large-system variant: W row workers
-template <int HC, int NB, int MAXT = 1024, int MINB = 1>
+template <int HC, int NB, int MAXT = 1024, int MINB = 1, bool HOT = true>
 __global__ void __launch_bounds__(MAXT, MINB) tn_msg_fwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
                              const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y, int N,
                              int so3, float* __restrict__ M, float* __restrict__ tauh, int n_hot, int row0) {
     pdl_sync();
     constexpr int H = HC;
     extern __shared__ float4 s_hot[];
-    hot_rows_load(fv, s_hot, n_hot, H);
+    if (HOT) hot_rows_load(fv, s_hot, n_hot, H);       // HOT = false (no hot rows requested): the loop carries no shared-memory branch
     const int h = threadIdx.x, W = blockDim.y;
     for (int i = row0 + blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
         float m[9];
 #pragma unroll
         for (int c = 0; c < 9; ++c) m[c] = 0.f;
-        msg_fwd_row<true, NB, false, true>(row_ptr, col, geom, fv, Y, i, 0, 1, H, h, m);
+        msg_fwd_row<true, NB, false, HOT>(row_ptr, col, geom, fv, Y, i, 0, 1, H, h, m);
         msg_fwd_finish(Y, i, H, h, so3, m, M, tauh);
     }
 }
@@ -652,7 +652,7 @@ __global__ void __launch_bounds__(MAXT) tn_msg_bwd(const int* __restrict__ row_p
 }
 
 // persistent large-system variant: 4 row workers at 128 registers
-template <int HC, int NB, int MAXT>
+template <int HC, int NB, int MAXT, bool HOT = true>
 __global__ void __launch_bounds__(MAXT, 1) tn_msg_bwd_p(const int* __restrict__ row_ptr, const int* __restrict__ col,
                             const float4* __restrict__ geom, FilterView fv, const float* __restrict__ Y,
                             const float* __restrict__ dM, float* __restrict__ dY, float* __restrict__ gpos, int N,
@@ -661,12 +661,12 @@ __global__ void __launch_bounds__(MAXT, 1) tn_msg_bwd_p(const int* __restrict__ 
     constexpr int H = HC;
     extern __shared__ float4 s_hot[];
     float* s_red_w = (float*)(s_hot + (size_t)n_hot * 3 * H) + WORKER_RED_FLOATS * threadIdx.y;
-    hot_rows_load(fv, s_hot, n_hot, H);
+    if (HOT) hot_rows_load(fv, s_hot, n_hot, H);
     const int h = threadIdx.x, W = blockDim.y;
     for (int i = row0 + blockIdx.x * W + threadIdx.y; i < N; i += gridDim.x * W) {
         float gp[3] = {0.f, 0.f, 0.f};
         float acc[9];
-        msg_bwd_row<true, NB, false, true>(row_ptr, col, geom, fv, Y, dM, dY, i, 0, 1, H, h, acc, gp);
+        msg_bwd_row<true, NB, false, HOT>(row_ptr, col, geom, fv, Y, dM, dY, i, 0, 1, H, h, acc, gp);
         st9(dY, (size_t)i, H, h, acc);
         worker_reduce<3>(gp, s_red_w, H);
         if (h == 0) {
@@ -1403,7 +1403,10 @@ struct TnRun {
                 // small systems: 4 slices x 2 edges per thread at 128 registers instead of 8 slices x 1 at 64 -- the same
                 // number of edges in flight per SM, but with 64 registers ptxas reuses the landing registers of the
                 // table rows and an iteration becomes 3-4 dependent round trips instead of one (SASS, r01i)
-                if (pl.ok && !(fvar & 9))
+                if (pl.ok && !(fvar & 9) && pl.n_hot == 0)
+                    launch_k(tn_msg_fwd_p<128, 1, 640, 2, false>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom,
+                             fv_layer[l], wa.Y[l], r1, m->so3, wa.M[l], wa.tauh, 0, r0);
+                else if (pl.ok && !(fvar & 9))
                     launch_k(tn_msg_fwd_p<128, 1, 640, 2>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom,
                              fv_layer[l], wa.Y[l], r1, m->so3, wa.M[l], wa.tauh, pl.n_hot, r0);
                 else if (pl.ok && (fvar & 1))
@@ -1491,6 +1494,9 @@ struct TnRun {
                 if (pl.ok && (variant & 2))
                     launch_k(tn_msg_bwd_p<128, 1, 1024>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom,
                              fv_layer[l], wa.Y[l], dM, wa.dC, wa.gpos, r1, pl.n_hot, r0);
+                else if (pl.ok && pl.n_hot == 0)
+                    launch_k(tn_msg_bwd_p<128, 2, 512, false>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom,
+                             fv_layer[l], wa.Y[l], dM, wa.dC, wa.gpos, r1, 0, r0);
                 else if (pl.ok)
                     launch_k(tn_msg_bwd_p<128, 2, 512>, pl.grid, pl.block, pl.smem, stream, wa.row_ptr, wa.col, geom,
                              fv_layer[l], wa.Y[l], dM, wa.dC, wa.gpos, r1, pl.n_hot, r0);
