@@ -43,7 +43,10 @@ static inline TabGrid make_tab_grid(int n_int, double hi, double alpha, double g
 __device__ __forceinline__ void tab_locate(const TabGrid& g, float d, int& k, float& s, float& dsdd) {
     float q;
     if (g.alpha > 0.f) {
-        const float u = exp2f(g.a2 * d);
+        // a2 * d lies in [-7.3, 0]: the bare MUFU.EX2 (what exp2f issues inside the normal range, without its four
+        // instructions of denormal-range handling -- these loops are issue-bound); same bits
+        float u;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(u) : "f"(g.a2 * d));
         q = ((u - g.u_min) + g.gamma * (g.hi - d)) * g.inv_h;
         dsdd = -(g.alpha * u + g.gamma) * g.inv_h;
     } else {
