@@ -1,10 +1,10 @@
-# usage: bash profiles/r02z_run.sh -- HEAD after the instruction diet of the message kernels: full GPU suite, all workloads
-mkdir -p gpurun_out; TAG=r02z
-(time timeout 1500 python -m pytest tests -m gpu -q) > gpurun_out/${TAG}_pytest.log 2>&1; grep -E "passed|failed" gpurun_out/${TAG}_pytest.log; grep -E "^FAILED|Error" gpurun_out/${TAG}_pytest.log | head -5
-for w in water md17 qm9-et md17-et; do
+# usage: bash profiles/r02z_run.sh -- A/B after FFMA-only forms in the adjoint message kernel
+mkdir -p gpurun_out; TAG=r02z2
+(time timeout 900 python -m pytest tests/test_gpu_tensornet.py -m gpu -q -x) > gpurun_out/${TAG}_pytest.log 2>&1; grep -E "passed|failed" gpurun_out/${TAG}_pytest.log; grep -E "^FAILED|Error|assert" gpurun_out/${TAG}_pytest.log | head -8
+for w in water md17; do
   timeout 600 python bench.py --workload $w --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_bench_${w}.json 2> gpurun_out/${TAG}_bench_${w}.err
   python -c "
 import json
-d=json.load(open('gpurun_out/${TAG}_bench_${w}.json')); print('$w', round(d['ms_per_step'],3), round(d['value']), 'frac', round(d['roofline']['frac'],4), {k:(round(v['us_per_step']/1000,3), v['launches_per_step']) for k,v in d['kernel_families'].items() if k.startswith('tn_msg') or k.startswith('et_edge')}, d['energy_checksum'])
+d=json.load(open('gpurun_out/${TAG}_bench_${w}.json')); print('$w', round(d['ms_per_step'],3), {k:(round(v['us_per_step']/1000,3), v['launches_per_step']) for k,v in d['kernel_families'].items() if k.startswith('tn_msg') or k.startswith('tn_embed_edge')}, d['energy_checksum'])
 "
 done

@@ -64,11 +64,12 @@ __device__ __forceinline__ void filter_val_grad(const FilterView& fv, size_t e, 
         int k;
         float s, ds;
         tab_locate(fv.grid, d, k, s, ds);
+        const float s2 = 2.0f * s, s3 = 3.0f * s * s;      // df/ds = c.y + 2 s c.z + 3 s^2 c.w as two FFMA per filter
 #pragma unroll
         for (int g = 0; g < 3; ++g) {
             const float4 c = filter_row<HOT>(fv, k, g, H, h);
             f[g] = c.x + s * (c.y + s * (c.z + s * c.w));
-            df[g] = (c.y + s * (2.0f * c.z + 3.0f * s * c.w)) * ds;
+            df[g] = fmaf(s3, c.w, fmaf(s2, c.z, c.y)) * ds;
         }
     } else {
 #pragma unroll
@@ -424,11 +425,12 @@ template <bool TAB> __device__ __forceinline__ void filter_eval_val(const Filter
 template <bool TAB>
 __device__ __forceinline__ void filter_eval(const FilterRaw<TAB>& r, float f[3], float df[3]) {
     if constexpr (TAB) {
+        const float s2 = 2.0f * r.s, s3 = 3.0f * r.s * r.s;   // df/ds = c.y + 2 s c.z + 3 s^2 c.w as two FFMA per filter
 #pragma unroll
         for (int g = 0; g < 3; ++g) {
             const float4 c = r.c[g];
             f[g] = c.x + r.s * (c.y + r.s * (c.z + r.s * c.w));
-            df[g] = (c.y + r.s * (2.0f * c.z + 3.0f * r.s * c.w)) * r.ds;
+            df[g] = fmaf(s3, c.w, fmaf(s2, c.z, c.y)) * r.ds;
         }
     } else {
 #pragma unroll
@@ -611,12 +613,13 @@ __device__ __forceinline__ void msg_bwd_row(const int* __restrict__ row_ptr, con
             acc[1] += f[1] * dmj[b][1]; acc[2] += f[1] * dmj[b][2]; acc[3] += f[1] * dmj[b][3];
             acc[4] += f[2] * dmj[b][4]; acc[5] += f[2] * dmj[b][5]; acc[6] += f[2] * dmj[b][6];
             acc[7] += f[2] * dmj[b][7]; acc[8] += f[2] * dmj[b][8];
-            const float s0 = dmi[0] * yj[b][0] + dmj[b][0] * yi[0];
+            // pure FFMA chains (the loop is issue-bound: a product, an FFMA and an add per component cost half again as much)
+            const float s0 = fmaf(dmi[0], yj[b][0], dmj[b][0] * yi[0]);
             float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-            for (int c = 1; c < 4; ++c) s1 += dmi[c] * yj[b][c] + dmj[b][c] * yi[c];
+            for (int c = 1; c < 4; ++c) s1 = fmaf(dmi[c], yj[b][c], fmaf(dmj[b][c], yi[c], s1));
 #pragma unroll
-            for (int c = 4; c < 9; ++c) s2 += dmi[c] * yj[b][c] + dmj[b][c] * yi[c];
+            for (int c = 4; c < 9; ++c) s2 = fmaf(dmi[c], yj[b][c], fmaf(dmj[b][c], yi[c], s2));
             const float ge = df[0] * s0 + df[1] * s1 + df[2] * s2;
             gp[0] += g[b].x * ge; gp[1] += g[b].y * ge; gp[2] += g[b].z * ge;
         }
@@ -894,27 +897,31 @@ __device__ __forceinline__ void embed_bwd_row(const int* __restrict__ row_ptr, c
         const float ux = g.x, uy = g.y, uz = g.z;
         const float n2 = (ux * ux + uy * uy + uz * uz) * (1.0f / 3.0f);
         const float g4 = ux * ux - n2, g5 = uy * uy - n2, g6 = ux * uy, g7 = ux * uz, g8 = uy * uz;
-        // a_c = Dias_c[i]*Z_e ; r_c = Dias_c[j]*Z_r ; geom of the reverse edge: odd components flip sign
-        float a[9], r[9];
+        // a_c = Dias_c[i]*Z_e ; r_c = Dias_c[j]*Z_r ; geom of the reverse edge: odd components flip sign.
+        // p_c = a_c - r_c (c = 1..3) or a_c + r_c (else) is all that is needed of them: one product + one FFMA each
+        float p[9];
+        const float nzr = -zr;
+        p[0] = fmaf(di[0], ze, dj[0] * zr);
 #pragma unroll
-        for (int c = 0; c < 9; ++c) { a[c] = di[c] * ze; r[c] = dj[c] * zr; }
-        const float gd = df[0] * (a[0] + r[0]) +
-                         df[1] * ((a[1] - r[1]) * ux + (a[2] - r[2]) * uy + (a[3] - r[3]) * uz) +
-                         df[2] * ((a[4] + r[4]) * g4 + (a[5] + r[5]) * g5 + (a[6] + r[6]) * g6 +
-                                  (a[7] + r[7]) * g7 + (a[8] + r[8]) * g8);
+        for (int c = 1; c < 4; ++c) p[c] = fmaf(di[c], ze, dj[c] * nzr);
+#pragma unroll
+        for (int c = 4; c < 9; ++c) p[c] = fmaf(di[c], ze, dj[c] * zr);
+        const float t1 = fmaf(p[1], ux, fmaf(p[2], uy, p[3] * uz));
+        const float t2 = fmaf(p[4], g4, fmaf(p[5], g5, fmaf(p[6], g6, fmaf(p[7], g7, p[8] * g8))));
+        const float gd = fmaf(df[0], p[0], fmaf(df[1], t1, df[2] * t2));
         // dL/du of edge e minus dL/du' of the reverse edge (d geom_c/du is even for c=1..3, odd for c=4..8):
         //   gu_e - gu_r  with gu_r evaluated at u' = -u  ==  sum_c (a_c*f - r_c*f*sign_c) dgeom_c(u)
         float w[9];
 #pragma unroll
-        for (int c = 1; c < 4; ++c) w[c] = (a[c] - r[c]) * f[1];
+        for (int c = 1; c < 4; ++c) w[c] = p[c] * f[1];
 #pragma unroll
-        for (int c = 4; c < 9; ++c) w[c] = (a[c] + r[c]) * f[2];
+        for (int c = 4; c < 9; ++c) w[c] = p[c] * f[2];
         const float tw = 2.0f / 3.0f;
         const float gx = w[1] + w[4] * (2.0f * ux - tw * ux) - w[5] * tw * ux + w[6] * uy + w[7] * uz;
         const float gy = w[2] - w[4] * tw * uy + w[5] * (2.0f * uy - tw * uy) + w[6] * ux + w[8] * uz;
         const float gz = w[3] - (w[4] + w[5]) * tw * uz + w[7] * ux + w[8] * uy;
         const float dot = gx * ux + gy * uy + gz * uz;
-        const float inv_d = 1.0f / g.w;
+        const float inv_d = __frcp_rn(g.w);      // the correctly rounded reciprocal = 1.0f / d without the division's slow path
         gp[0] += ux * gd + (gx - dot * ux) * inv_d;
         gp[1] += uy * gd + (gy - dot * uy) * inv_d;
         gp[2] += uz * gd + (gz - dot * uz) * inv_d;
