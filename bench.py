@@ -273,11 +273,15 @@ def strong_scaling(args, dev, rank, world, local):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(step_fn, k, w):
+    clocks_seen = {}
+
+    def timed(step_fn, k, w, sample_clocks=False):
         for i in range(w):
             step_fn(i)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k)]
+        sampler = ClockSampler(local) if (sample_clocks and rank == 0) else None
         barrier()
+        t_begin = time.perf_counter()
         for i in range(k):
             flush.zero_()
             if world > 1:
@@ -286,6 +290,8 @@ def strong_scaling(args, dev, rank, world, local):
             step_fn(w + i)
             ev[i][1].record()
         barrier()
+        if sampler is not None:
+            clocks_seen.update(sampler.stop(t_begin, time.perf_counter()))
         t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -314,7 +320,7 @@ def strong_scaling(args, dev, rank, world, local):
         status = rm.energy_forces(z, poss[0], batch, 1, model.output_model, *model._mean_std())[2].cpu()
         assert status[1:].tolist() == [0, 0, 0], "bad status %s" % status.tolist()
         E = int(status[0])
-        ms = timed(step, K, W)
+        ms = timed(step, K, W, sample_clocks=True)
         fam = profile_families(step, 2)
         out.update({"ms_per_step": ms, "value": N / (ms * 1e-3), "unit": UNIT, "parallelism": "one GPU, monolithic call",
                     "ghost_atoms_max": 0, "halo_bytes_per_step": 0, "halo_ms_per_step": 0.0,
@@ -348,7 +354,7 @@ def strong_scaling(args, dev, rank, world, local):
         torch.cuda.synchronize()
         launches = ops.launch_count() - c0
         assert runner.status.cpu()[1:].tolist() == [0, 0, 0], "bad status on rank %d" % rank
-        ms = timed(step, K, W)
+        ms = timed(step, K, W, sample_clocks=True)
         # exchange durations: CUDA events around the pack + transfer of every halo point (communication stream)
         runner.exchange_events = []
         step(0)
@@ -433,6 +439,7 @@ def strong_scaling(args, dev, rank, world, local):
                            "l2_bytes_per_launch": l2_bytes("tn_msg_bwd", E, H),
                            "note": "rank 0's launches (all rows of one stage = boundary + interior launch); CUDA events "
                                    "inside the library over %d eager steps" % n_prof}
+    out["clocks"] = dict(clocks_seen) if clocks_seen else None     # nvidia-smi samples of rank 0's GPU during the timed steps
     out["kernel_families"] = {k: {"launches_per_step": c / n_prof, "us_per_step": m_ / n_prof * 1e3} for k, (c, m_) in
                               sorted(fam.items(), key=lambda kv: -kv[1][1])[:8]}
     return out
