@@ -38,11 +38,12 @@ __device__ __forceinline__ void tab_load(const Tab& tb, float d, int H, int h, T
 }
 template <int NF>
 __device__ __forceinline__ void tab_poly(const Tab& tb, const TabRow<NF>& r, float (&f)[NF], float (&df)[NF]) {
+    const float s2 = 2.0f * r.s, s3 = 3.0f * r.s * r.s;     // df/ds = c.y + 2 s c.z + 3 s^2 c.w as two FFMA per filter
 #pragma unroll
     for (int g = 0; g < NF; ++g) {
         const float4 c = r.c[g];
         f[g] = c.x + r.s * (c.y + r.s * (c.z + r.s * c.w));
-        df[g] = (c.y + r.s * (2.0f * c.z + 3.0f * r.s * c.w)) * r.ds;
+        df[g] = fmaf(s3, c.w, fmaf(s2, c.z, c.y)) * r.ds;
     }
 }
 template <int NF>
@@ -64,6 +65,33 @@ template <int HDC> __device__ __forceinline__ float seg_sum_t(float v, int hd) {
         return v;
     } else {
         return seg_sum(v, hd);
+    }
+}
+
+// Four segmented sums at once (the adjoint needs q.k and g_x.v of both directions of an edge): the first two butterfly
+// steps halve the number of live values instead of duplicating them, the remaining steps run on ONE value per lane, four
+// shuffles hand every lane all four results: 9 shuffles + 5 adds instead of 16 + 16 at hd = 16 (a warp shuffle costs four
+// issue slots of the SM, and this kernel is bound by them).  hd >= 4 only.
+template <int HDC>
+__device__ __forceinline__ void seg_sum4_t(float& a0, float& a1, float& a2, float& a3, int hd) {
+    if constexpr (HDC >= 4) {
+        const int lane = threadIdx.x & 31;
+        const bool b0 = lane & 1, b1 = lane & 2;
+        float x0 = b0 ? a2 : a0, x1 = b0 ? a3 : a1;
+        x0 += __shfl_xor_sync(0xffffffffu, b0 ? a0 : a2, 1);
+        x1 += __shfl_xor_sync(0xffffffffu, b0 ? a1 : a3, 1);
+        float k = b1 ? x1 : x0;
+        k += __shfl_xor_sync(0xffffffffu, b1 ? x0 : x1, 2);
+#pragma unroll
+        for (int o = 4; o < HDC; o <<= 1) k += __shfl_xor_sync(0xffffffffu, k, o);
+        // lane (b1, b0) of every group of four holds: (0,0) a0, (1,0) a1, (0,1) a2, (1,1) a3
+        const int base = lane & ~3;
+        a0 = __shfl_sync(0xffffffffu, k, base);
+        a1 = __shfl_sync(0xffffffffu, k, base + 2);
+        a2 = __shfl_sync(0xffffffffu, k, base + 1);
+        a3 = __shfl_sync(0xffffffffu, k, base + 3);
+    } else {
+        a0 = seg_sum_t<HDC>(a0, hd); a1 = seg_sum_t<HDC>(a1, hd); a2 = seg_sum_t<HDC>(a2, hd); a3 = seg_sum_t<HDC>(a3, hd);
     }
 }
 
@@ -445,45 +473,37 @@ et_edge_bwd(const int* __restrict__ row_ptr, const int* __restrict__ col, const 
             const float vjx = L[b][5], vjy = L[b][6], vjz = L[b][7];
             const float gxj = L[b][8];
             const float gvjx = L[b][9], gvjy = L[b][10], gvjz = L[b][11];
-            // ---- A
-            const float sA = seg_sum_t<HDC>(qi * kj * f[0], hd);
-            float attnA, dactA;
+            // ---- A (edge i <- j, dhat = -u) and B (edge j <- i, dhat' = +u).  The issue slots bound this kernel: shared
+            // products are named once, the position gradient is assembled from its closed form (below)
+            const float tA = qi * kj, uA = gxi * vj0, tB = qj * ki, uB = gxj * vi0;
+            float sA = tA * f[0], gattA = uA * f[1], sB = tB * f[0], gattB = uB * f[1];
+            seg_sum4_t<HDC>(sA, gattA, sB, gattB, hd);
+            float attnA, dactA, attnB, dactB;
             act_both(attn_act, sA, attnA, dactA);               // one sigmoid for value and derivative
-            const float gattA = seg_sum_t<HDC>(gxi * vj0 * f[1], hd);
-            const float gsA = gattA * dactA;
-            acc[0] += gsA * kj * f[0];
-            const float gv1A = gvix * vjx + gviy * vjy + gviz * vjz;
-            const float gv2A = gvix * hx + gviy * hy + gviz * hz;
-            const float gdA = gsA * qi * kj * df[0] + gxi * attnA * vj0 * df[1] + gv1A * vj1 * df[2] +
-                              gv2A * vj2 * df[3];
-            const float v2A = vj2 * f[3];
-            const float ghxA = gvix * v2A, ghyA = gviy * v2A, ghzA = gviz * v2A;
-            // ---- B (roles swapped, dhat' = +u)
-            const float sB = seg_sum_t<HDC>(qj * ki * f[0], hd);
-            float attnB, dactB;
             act_both(attn_act, sB, attnB, dactB);
-            const float gattB = seg_sum_t<HDC>(gxj * vi0 * f[1], hd);
-            const float gsB = gattB * dactB;
-            acc[1] += gsB * qj * f[0];
-            const float gv1B = gvjx * vix + gvjy * viy + gvjz * viz;
-            const float gv2B = gvjx * g.x + gvjy * g.y + gvjz * g.z;
-            acc[2] += gxj * attnB * f[1];
-            acc[3] += gv1B * f[2];
-            acc[4] += gv2B * f[3];
+            const float gsA = gattA * dactA, gsB = gattB * dactB;
+            acc[0] = fmaf(gsA * kj, f[0], acc[0]);
+            acc[1] = fmaf(gsB * qj, f[0], acc[1]);
+            const float gv1A = fmaf(gvix, vjx, fmaf(gviy, vjy, gviz * vjz));
+            const float gv2A = fmaf(gvix, hx, fmaf(gviy, hy, gviz * hz));
+            const float gv1B = fmaf(gvjx, vix, fmaf(gvjy, viy, gvjz * viz));
+            const float gv2B = fmaf(gvjx, g.x, fmaf(gvjy, g.y, gvjz * g.z));
+            acc[2] = fmaf(gxj * attnB, f[1], acc[2]);
+            acc[3] = fmaf(gv1B, f[2], acc[3]);
+            acc[4] = fmaf(gv2B, f[3], acc[4]);
             const float s1B = vi1 * f[2];
-            acc[5] += gvjx * s1B; acc[6] += gvjy * s1B; acc[7] += gvjz * s1B;
+            acc[5] = fmaf(gvjx, s1B, acc[5]); acc[6] = fmaf(gvjy, s1B, acc[6]); acc[7] = fmaf(gvjz, s1B, acc[7]);
             if (j != i) {   // the self loop has d = 0 and no position dependence
-                const float gdB = gsB * qj * ki * df[0] + gxj * attnB * vi0 * df[1] + gv1B * vi1 * df[2] +
-                                  gv2B * vi2 * df[3];
-                const float v2B = vi2 * f[3];
-                const float ghxB = gvjx * v2B, ghyB = gvjy * v2B, ghzB = gvjz * v2B;
-                const float inv_d = 1.0f / g.w;
-                const float dotA = ghxA * hx + ghyA * hy + ghzA * hz;
-                const float dotB = ghxB * g.x + ghyB * g.y + ghzB * g.z;
-                // -G_A + G_B
-                gp[0] += -(gdA * hx + (ghxA - dotA * hx) * inv_d) + (gdB * g.x + (ghxB - dotB * g.x) * inv_d);
-                gp[1] += -(gdA * hy + (ghyA - dotA * hy) * inv_d) + (gdB * g.y + (ghyB - dotB * g.y) * inv_d);
-                gp[2] += -(gdA * hz + (ghzA - dotA * hz) * inv_d) + (gdB * g.z + (ghzB - dotB * g.z) * inv_d);
+                const float gdA = fmaf(gsA * tA, df[0], fmaf(uA * attnA, df[1], fmaf(gv1A * vj1, df[2], gv2A * vj2 * df[3])));
+                const float gdB = fmaf(gsB * tB, df[0], fmaf(uB * attnB, df[1], fmaf(gv1B * vi1, df[2], gv2B * vi2 * df[3])));
+                // -G_A + G_B with G = g_d dhat + (g_dhat - (g_dhat . dhat) dhat) / d, g_dhat(A) = vj2 f3 g_va_i, g_dhat(B) = vi2 f3 g_va_j:
+                //   = u (g_dA + g_dB - wA gv2A - wB gv2B) + wB g_va_j - wA g_va_i,   wA = vj2 f3 / d, wB = vi2 f3 / d
+                const float fd = f[3] * __frcp_rn(g.w);
+                const float wA = vj2 * fd, wB = vi2 * fd;
+                const float cu = (gdA + gdB) - fmaf(wA, gv2A, wB * gv2B);
+                gp[0] += fmaf(g.x, cu, fmaf(wB, gvjx, -wA * gvix));
+                gp[1] += fmaf(g.y, cu, fmaf(wB, gvjy, -wA * gviy));
+                gp[2] += fmaf(g.z, cu, fmaf(wB, gvjz, -wA * gviz));
             }
             }
         }
