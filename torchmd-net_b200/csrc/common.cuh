@@ -164,7 +164,8 @@ __device__ __forceinline__ int warp_incl_scan_i(int v, int lane) {
 }
 
 // Activations (models/utils.py act_class_mapping) and their derivatives.
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+// the correctly rounded reciprocal equals 1.0f / y bit for bit (y in [1, inf]) without the division's slow path
+__device__ __forceinline__ float sigmoidf_(float x) { return __frcp_rn(1.0f + expf(-x)); }
 __device__ __forceinline__ float act_apply(int act, float x) {
     switch (act) {
         case TMDN_ACT_SILU: return x * sigmoidf_(x);
