@@ -229,13 +229,11 @@ class TorchMD_Net(nn.Module):
         return y
 
     def __prepare_scriptable__(self):
-        """``torch.jit.script(model)`` compiles this stand-in (models/scripted.py): one flat weight buffer + the fused op.
-        The weights are packed as they are now; script again after changing them."""
+        """``torch.jit.script(model)`` compiles this stand-in (models/scripted.py): one flat weight buffer + the fused op,
+        priors included (their tables are packed too).  The weights are packed as they are now; script again after
+        changing them."""
         from .. import _native
         from .scripted import ScriptableTorchMD_Net
-        if self.prior_model is not None:
-            raise NotImplementedError("scripting a model with a prior is not built; fold the atom references into the "
-                                      "checkpoint's mean or evaluate the eager model")
         _native.load()
         return ScriptableTorchMD_Net(self)
 

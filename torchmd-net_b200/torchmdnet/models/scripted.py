@@ -39,6 +39,10 @@ class ScriptableTorchMD_Net(nn.Module):
     iparams: List[int]
     fparams: List[float]
     box: List[float]
+    prior_kind: List[int]          # per prior: 0 Atomref, 1 ZBL, 2 Coulomb, 3 D2
+    prior_off: List[int]           # offset of the prior's per-element table in ``prior_data``
+    prior_len: List[int]           # entries per table (D2: two tables of this length, back to back)
+    prior_par: List[float]         # per prior: cutoff, energy prefactor, distance scale, alpha, max_num_neighbors
 
     def __init__(self, model):
         super().__init__()
@@ -59,6 +63,34 @@ class ScriptableTorchMD_Net(nn.Module):
         box = dist.box
         self.box = [] if box is None or box.numel() == 0 else [float(x) for x in box.double().reshape(-1)]
         self.dim_size: int = 0
+        # priors (models/model.py:266-284): per-element tables in one flat buffer, scalars in plain lists
+        self.prior_kind, self.prior_off, self.prior_len, self.prior_par = [], [], [], []
+        tables = []
+        cur = 0
+        for prior in (model.prior_model if model.prior_model is not None else []):
+            name = type(prior).__name__
+            if name == "Atomref":
+                kind, tabs, par = 0, [prior.atomref.weight.detach().reshape(-1)], [0.0, 0.0, 0.0, 0.0, 0.0]
+            elif name == "ZBL":
+                kind, tabs = 1, [prior.atomic_number.detach()]
+                par = list(prior._params()) + [float(prior.max_num_neighbors)]
+            elif name == "Coulomb":
+                kind, tabs = 2, [torch.zeros(1)]
+                par = list(prior._params()) + [float(prior.max_num_neighbors)]
+            elif name == "D2":
+                zz = prior.Z_map
+                kind, tabs = 3, [prior.C_6[zz].detach().to(torch.float32).sqrt(), prior.R_r[zz].detach().to(torch.float32)]
+                par = list(prior._params()) + [float(prior.max_num_neighbors)]
+            else:
+                raise NotImplementedError("scripting a model with a %s prior is not built" % name)
+            self.prior_kind.append(kind)
+            self.prior_off.append(cur)
+            self.prior_len.append(int(tabs[0].numel()))
+            self.prior_par += [float(x) for x in par]
+            for t in tabs:
+                tables.append(t.to(device=flat.device, dtype=torch.float32).reshape(-1))
+                cur += int(t.numel())
+        self.register_buffer("prior_data", torch.cat(tables) if tables else torch.zeros(1, device=flat.device))
 
     def forward(self, z: Tensor, pos: Tensor, batch: Optional[Tensor] = None, q: Optional[Tensor] = None,
                 s: Optional[Tensor] = None, extra_args: Optional[Dict[str, Tensor]] = None
@@ -93,6 +125,32 @@ class ScriptableTorchMD_Net(nn.Module):
             y, f, status = torch.ops.torchmdnet_b200.gn_energy_forces_packed(
                 self.packed, self.layout, self.iparams, self.fparams, z.contiguous(), pos.detach().contiguous(),
                 b.contiguous(), self.box, self.use_periodic, self.strategy, max_edges, n_mol, self.derivative)
+        for ip in range(len(self.prior_kind)):
+            kind, off, ln = self.prior_kind[ip], self.prior_off[ip], self.prior_len[ip]
+            if kind == 0:      # Atomref.pre_reduce + the molecular sum: forces stand as they are
+                w = self.prior_data[off:off + ln]
+                y = y + torch.zeros(n_mol, 1, dtype=y.dtype, device=y.device).index_add_(0, b, w[z].to(y.dtype).unsqueeze(1))
+            else:              # pair priors: energy and analytic forces in place (csrc/pair_prior.cu)
+                cutoff, pref, dscale, alpha = (self.prior_par[5 * ip], self.prior_par[5 * ip + 1], self.prior_par[5 * ip + 2],
+                                               self.prior_par[5 * ip + 3])
+                cap = (int(self.prior_par[5 * ip + 4]) + 1) * n
+                if kind == 1:
+                    name, w = "zbl", self.prior_data[off:off + ln][z]
+                elif kind == 2:
+                    assert extra_args is not None and "partial_charges" in extra_args, \
+                        "the Coulomb prior needs extra_args['partial_charges']"
+                    name, w = "coulomb", extra_args["partial_charges"].to(torch.float32)
+                else:
+                    name = "d2"
+                    w = torch.stack([self.prior_data[off:off + ln][z], self.prior_data[off + ln:off + 2 * ln][z]])
+                y = y.contiguous()
+                found = torch.ops.torchmdnet_b200.pair_prior(name, pos.detach().to(torch.float32).contiguous(), b.contiguous(),
+                                                             w.contiguous(), cutoff, pref, dscale, alpha, cap, y,
+                                                             f if self.derivative else None)
+                if not torch.ops.torch_extension.is_stream_capturing():
+                    assert int(found.item()) <= cap, ("The neighbor search missed some atoms due to max_num_neighbors being "
+                                                      "too low. Please increase this parameter to include the maximum "
+                                                      "number of atoms within the cutoff.")
         if self.derivative:
             return y, f
         return y, None
