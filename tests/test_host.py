@@ -318,3 +318,28 @@ def test_atomref_prior_and_legacy_checkpoint_keys(tmp_path):
                              dataset=_Dataset())
     assert [type(p).__name__ for p in pm] == ["ZBL", "D2", "Atomref"]
     assert pm[1].cutoff_distance == 10.0 and pm[1].max_num_neighbors == 100 and pm[1].energy_scale == 4.35974e-18
+
+
+@pytest.mark.parametrize("name,kinds", [("small_tensornet_atomref.npz", [0]), ("small_tensornet_pairpriors.npz", [1, 2]),
+                                        ("small_tensornet_d2.npz", [3])])
+def test_models_with_priors_script_on_the_cpu(name, kinds, tmp_path):
+    """torch.jit.script of a model with priors needs no GPU (compute does): the priors' tables and scalars are packed into the
+    scripted module (models/scripted.py) and survive save / load."""
+    from torchmdnet.models.model import create_model
+    g = load_npz(name)
+    m = create_model(g["hparams"])
+    m.load_state_dict(g["sd"])
+    sm = torch.jit.script(m.eval())
+    assert list(sm.prior_kind) == kinds and len(sm.prior_par) == 5 * len(kinds)
+    path = str(tmp_path / "m.pt")
+    torch.jit.save(sm, path)
+    lm = torch.jit.load(path)
+    assert list(lm.prior_kind) == kinds
+    torch.testing.assert_close(lm.prior_data, sm.prior_data, rtol=0, atol=0, equal_nan=True)   # D2: element 0 is NaN
+    if kinds == [3]:        # D2: sqrt(C_6) and R_r per element type, back to back
+        n = sm.prior_len[0]
+        pr = m.prior_model[0]
+        torch.testing.assert_close(sm.prior_data[1:n] ** 2, pr.C_6[pr.Z_map][1:].float())
+        torch.testing.assert_close(sm.prior_data[n + 1:2 * n], pr.R_r[pr.Z_map][1:].float())
+    with pytest.raises(Exception):          # evaluation still needs the CUDA extension and CUDA tensors
+        lm(tt(g["z"]), tt(g["pos"]), tt(g["batch"]))
