@@ -335,23 +335,8 @@ __global__ void tn_update_fwd(const float* Xh, const float* __restrict__ dX, flo
         st9(Xh_next, i, H, h, nx);
     }
 }
-// ddX = dXn + adjoint of the square term
-__global__ void tn_update_bwd(const float* __restrict__ dXn, const float* __restrict__ dX, float* __restrict__ ddX,
-                              long long total, int H) {
-    pdl_sync();
-    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= total) return;
-    const size_t i = idx / H;
-    const int h = (int)(idx % H);
-    float g[9], d[9], dd[9];
-    ld9(dXn, i, H, h, g);
-    ld9(dX, i, H, h, d);
-    t3_square_bwd(d, g, dd);
-#pragma unroll
-    for (int c = 0; c < 9; ++c) dd[c] += g[c];
-    st9(ddX, i, H, h, dd);
-}
-// tn_normalize_bwd followed by tn_update_bwd of the layer below, one pass over the (atom, channel) pairs: the same
+// adjoint of the normalisation followed by the adjoint of the update of the layer below (ddX = dXn + adjoint of the square
+// term), one pass over the (atom, channel) pairs: the same
 // operations in the same order (dXa is still written: it is the residual branch of the next stage)
 __global__ void tn_normalize_update_bwd(const float* __restrict__ X, float* __restrict__ dXa,
                                         const float* __restrict__ dXprev, float* __restrict__ ddX, long long total, int H) {
@@ -748,7 +733,7 @@ __global__ void tn_out_norm_bwd(const float* __restrict__ X, const float* __rest
 #pragma unroll
     for (int c = 4; c < 9; ++c) out[c] = gq[c] * dq[2];
     st9(dXa, (size_t)i, H, h, out);
-    if (dXprev != nullptr) {   // tn_update_bwd of the last layer, fused (same operations in the same order)
+    if (dXprev != nullptr) {   // adjoint of the last layer's update, fused (same operations in the same order)
         float d[9], dd[9];
         ld9(dXprev, (size_t)i, H, h, d);
         t3_square_bwd(d, out, dd);
