@@ -313,6 +313,12 @@ int tmdn_pair_prior_f32(int kind, const float* pos, const int64_t* batch, const 
                         int64_t max_edges, float* energy, float* forces, int32_t* num_found, void* workspace,
                         size_t workspace_bytes, tmdn_stream_t stream);
 
+/* out[m] += sum of values[i] over the atoms of molecule m (batch sorted ascending), one CTA per molecule, fixed summation
+ * order: the deterministic molecular sum behind the Atomref prior (torchmdnet/priors/atomref.py:35-44 adds atomref[z] per atom
+ * before the head's scatter, models/model.py:266-272; torch's index_add_ on CUDA sums with atomics). */
+int tmdn_segment_add_f32(const float* values, const int64_t* batch, int64_t n_atoms, int64_t n_mol, float* out,
+                         tmdn_stream_t stream);
+
 /* ---------------------------------------------------------------- Equivariant Transformer energy + forces (fp32)
  * TorchMD_ET.forward + NeighborEmbedding + EquivariantMultiHeadAttention + EquivariantScalar head + force path
  * (torchmdnet/models/torchmd_et.py:154-187,272-347; models/utils.py:73-108,496-522; models/output_modules.py:111-115).

@@ -166,3 +166,17 @@ extern "C" int tmdn_pair_prior_f32(int kind, const float* pos, const int64_t* ba
     }
     return TMDN_OK;
 }
+
+// out[m] += sum_{i in molecule m} values[i]  (batch sorted): the molecular sum of the Atomref prior, deterministic
+// (torch's index_add_ on CUDA adds with atomics in arbitrary order).  No counterpart call in the reference: there the sum
+// is part of the output head's scatter (models/model.py:266-272).
+extern "C" int tmdn_segment_add_f32(const float* values, const int64_t* batch, int64_t n_atoms, int64_t n_mol, float* out,
+                                    tmdn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    TMDN_CHECK_ARG(values && batch && out, "segment_add: null pointer argument");
+    TMDN_CHECK_ARG(n_atoms > 0 && n_mol > 0 && n_atoms < (1LL << 31), "segment_add: bad sizes");
+    KTimer ktimer__("segment_add", stream);
+    launch_k(pair_prior_mol_add, (unsigned)n_mol, 128, 0, stream, values, batch, (int)n_atoms, out);
+    TMDN_LAUNCH_CHECK();
+    return TMDN_OK;
+}

@@ -936,6 +936,20 @@ Tensor pair_prior(const std::string& kind, const Tensor& pos, const Tensor& batc
     return num;
 }
 
+// out[m] += sum of values over molecule m (batch sorted); deterministic
+void segment_add(const Tensor& values, const Tensor& batch, Tensor out) {
+    TORCH_CHECK(values.is_cuda() && values.scalar_type() == at::kFloat && values.is_contiguous() && values.dim() == 1,
+                "segment_add: values must be a contiguous CUDA float32 vector");
+    TORCH_CHECK(batch.is_cuda() && batch.scalar_type() == at::kLong && batch.is_contiguous() && batch.numel() == values.numel(),
+                "segment_add: batch must be a contiguous CUDA int64 vector of the same length");
+    TORCH_CHECK(out.is_cuda() && out.scalar_type() == at::kFloat && out.is_contiguous(), "segment_add: out");
+    TORCH_CHECK(values.get_device() == batch.get_device() && values.get_device() == out.get_device(), "segment_add: devices differ");
+    if (values.numel() == 0 || out.numel() == 0) return;
+    const c10::cuda::CUDAGuard guard(values.device());
+    TMDN_CALL(tmdn_segment_add_f32(values.data_ptr<float>(), batch.data_ptr<int64_t>(), values.numel(), out.numel(),
+                                   out.data_ptr<float>(), cur_stream()));
+}
+
 int64_t launch_count() { return (int64_t)tmdn_launch_count(); }
 int64_t set_tuning(std::string key, int64_t value) {
     const int old = tmdn_set_tuning(key.c_str(), (int)value);
@@ -1022,6 +1036,7 @@ TORCH_LIBRARY(torchmdnet_b200, m) {
     m.def("node_gemm(Tensor a, Tensor w, Tensor? bias, Tensor? c, bool accumulate) -> Tensor", node_gemm);
     m.def("pair_prior(str kind, Tensor pos, Tensor batch, Tensor weight, float cutoff, float energy_prefactor, "
           "float distance_scale, float alpha, int max_edges, Tensor(a!) energy, Tensor(b!)? forces) -> Tensor", pair_prior);
+    m.def("segment_add(Tensor values, Tensor batch, Tensor(a!) out) -> ()", segment_add);
     m.def("launch_count() -> int", launch_count);
     m.def("set_tuning(str key, int value) -> int", set_tuning);
     m.def("profile_enable(bool on) -> ()", profile_enable);

@@ -129,7 +129,9 @@ class ScriptableTorchMD_Net(nn.Module):
             kind, off, ln = self.prior_kind[ip], self.prior_off[ip], self.prior_len[ip]
             if kind == 0:      # Atomref.pre_reduce + the molecular sum: forces stand as they are
                 w = self.prior_data[off:off + ln]
-                y = y + torch.zeros(n_mol, 1, dtype=y.dtype, device=y.device).index_add_(0, b, w[z].to(y.dtype).unsqueeze(1))
+                add = torch.zeros(n_mol, 1, dtype=torch.float32, device=y.device)
+                torch.ops.torchmdnet_b200.segment_add(w[z].contiguous(), b.contiguous(), add.view(-1))   # fixed summation order
+                y = y + add.to(y.dtype)
             else:              # pair priors: energy and analytic forces in place (csrc/pair_prior.cu)
                 cutoff, pref, dscale, alpha = (self.prior_par[5 * ip], self.prior_par[5 * ip + 1], self.prior_par[5 * ip + 2],
                                                self.prior_par[5 * ip + 3])

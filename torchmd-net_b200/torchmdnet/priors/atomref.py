@@ -56,4 +56,11 @@ class Atomref(BasePrior):
     def molecular_sum(self, z: Tensor, batch: Tensor, n_mol: int) -> Tensor:
         """sum_{i in molecule} atomref[z_i] -> [n_mol, 1]: what pre_reduce + reduce add to y."""
         out = torch.zeros(n_mol, 1, dtype=self.atomref.weight.dtype, device=z.device)
+        if z.is_cuda and out.dtype == torch.float32:
+            # fixed summation order (index_add_ on CUDA adds with atomics): tmdn_segment_add_f32, batch sorted as everywhere
+            from .. import _native
+            _native.load()
+            torch.ops.torchmdnet_b200.segment_add(self.atomref(z).detach().reshape(-1).contiguous(), batch.contiguous(),
+                                                  out.view(-1))
+            return out
         return out.index_add_(0, batch, self.atomref(z))
