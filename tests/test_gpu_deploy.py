@@ -241,3 +241,57 @@ def test_scripted_model_with_priors(name, tmp_path):
     if extra is not None:            # Coulomb without its charges: an assertion inside the scripted module
         with pytest.raises(Exception, match="partial_charges"):
             lm(z, pos, batch, None, None, None)
+
+
+@pytest.mark.parametrize("kind", ["zbl", "coulomb", "d2"])
+def test_pair_prior_kernels_against_the_oracle(kind):
+    """tmdn_pair_prior_f32 against oracle/priors.py (numpy fp64, finite-difference forces; pinned to the reference's fixtures
+    in tests/test_oracle_pinned.py) on random molecules and other parameters than the fixtures use: several molecules of
+    different size, atoms closer than the fixtures' (down to 0.7), Angstrom / eV and nm / kJ-mol-like unit scales.
+    Energies 2e-6 relative, forces 2e-5 of the largest force."""
+    import numpy as np
+    from oracle import priors as P
+    from torchmdnet.priors import D2, ZBL, Coulomb
+    rng = np.random.RandomState({"zbl": 1, "coulomb": 2, "d2": 3}[kind])
+    sizes = [1, 17, 2, 30, 9]
+    batch = np.repeat(np.arange(len(sizes)), sizes)
+    n, nm = batch.size, len(sizes)
+    for trial, (dscale, escale, box) in enumerate([(1e-10, 1.602176634e-19, 4.0), (1e-9, 1.66054e-21, 0.45)]):
+        pos = np.zeros((n, 3))
+        for i in range(n):                      # random positions with a minimum distance of 0.7 (0.07 in nm)
+            while True:
+                p = rng.rand(3) * box * 2
+                same = pos[:i][batch[:i] == batch[i]]
+                if len(same) == 0 or np.linalg.norm(same - p, axis=1).min() > 0.175 * box:
+                    pos[i] = p
+                    break
+        z = rng.randint(1, 10, n)
+        if kind == "zbl":
+            cut = 0.9 * box
+            prior = ZBL(cutoff_distance=cut, max_num_neighbors=40, atomic_number=list(range(10)), distance_scale=dscale,
+                        energy_scale=escale)
+            extra = None
+            fn = lambda p: P.zbl_energy(p, batch, z, nm, list(range(10)), cut, dscale, escale)      # noqa: E731
+        elif kind == "coulomb":
+            q = rng.rand(n) - 0.5
+            alpha = 1.3 / box
+            prior = Coulomb(alpha=alpha, max_num_neighbors=40, distance_scale=dscale, energy_scale=escale)
+            extra = {"partial_charges": torch.from_numpy(q).float().cuda()}
+            fn = lambda p: P.coulomb_energy(p, batch, q.astype(np.float32), nm, alpha, dscale, escale)      # noqa: E731
+        else:
+            cut = 1.5 * box
+            prior = D2(cutoff_distance=cut, max_num_neighbors=40, atomic_number=list(range(10)), distance_scale=dscale,
+                       energy_scale=escale)
+            extra = None
+            fn = lambda p: P.d2_energy(p, batch, z, nm, list(range(10)), cut, dscale, escale)      # noqa: E731
+        prior = prior.cuda()
+        pos32 = pos.astype(np.float32)
+        e = torch.zeros(nm, 1, device="cuda")
+        f = torch.zeros(n, 3, device="cuda")
+        prior.add_energy_forces(e, f, torch.from_numpy(z).cuda(), torch.from_numpy(pos32).cuda(),
+                                torch.from_numpy(batch).cuda(), extra)
+        e_ref = fn(pos32.astype(np.float64))
+        f_ref = P.forces_fd(fn, pos32.astype(np.float64), h=1e-5 * box)
+        assert np.abs(e.cpu().numpy().ravel().astype(np.float64) - e_ref).max() <= 2e-6 * np.abs(e_ref).max(), (kind, trial)
+        assert np.abs(f.cpu().numpy().astype(np.float64) - f_ref).max() <= 2e-5 * np.abs(f_ref).max(), (kind, trial)
+        assert e_ref[0] == 0.0 and float(e[0]) == 0.0 and float(f[0].abs().max()) == 0.0      # the single atom

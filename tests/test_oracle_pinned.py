@@ -82,3 +82,38 @@ def test_oracle_matches_reference_gn_and_t_goldens(arch, tag, fixture):
         y, f = om.energy_forces({k: v.detach() for k, v in sd.items()}, hp, z, pos, batch)
         torch.testing.assert_close(y, y_ref, rtol=RTOL, atol=ATOL)
         torch.testing.assert_close(f, f_ref, rtol=1e-5, atol=ATOL)
+
+
+def test_pair_prior_oracle_against_reference_fixtures():
+    """oracle/priors.py (ZBL, Coulomb, D2 in numpy fp64, forces by central differences) against what the unmodified reference
+    wrote: D2 alone in fp64 (energies to 1e-12, forces to 1e-8), D2 against the Psi4 energies of the reference's
+    tests/test_prior_d2.py (1e-5), ZBL + Coulomb as the difference of the reference's fp32 runs with and without the priors."""
+    from oracle import priors as P
+    g = load_npz("small_tensornet_d2.npz")
+    da = g["hparams"]["prior_model"][0]["D2"]
+    z, pos, batch = g["z"], g["pos"], g["batch"]
+    nm = int(batch.max()) + 1
+    fn = lambda p: P.d2_energy(p, batch, z, nm, da["atomic_number"], da["cutoff_distance"], da["distance_scale"],  # noqa: E731
+                               da["energy_scale"])
+    e = fn(pos)
+    assert np.abs(e - g["y_prior_f64"].ravel()).max() <= 1e-12 * np.abs(e).max()
+    assert np.abs(P.forces_fd(fn, pos) - g["forces_prior_f64"]).max() <= 1e-8
+    psi4 = {"h2": ([1, 1], [[0.0, 0.0, 0.0], [1.0, 0.0, 0.0]], [0, 0], [-2.396695338419219e-06]),
+            "h2o_n2_ch4": ([1, 8, 1, 7, 7, 6, 1, 1, 1],
+                           [[0.0, 0.0, 0.0], [0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [1.0, 2.0, 3.0], [2.0, 1.0, 3.0], [0.0, 0.0, 0.0],
+                            [1.0, 1.0, 0.0], [0.0, 1.0, 1.0], [1.0, 0.0, 1.0]], [0, 0, 0, 1, 1, 2, 2, 2, 2],
+                           [-4.7815923481300465e-06, -3.0071055390390565e-06, -7.100283425158895e-05])}
+    for zz, pp, bb, yy in psi4.values():
+        e = P.d2_energy(np.array(pp), np.array(bb), np.array(zz), max(bb) + 1, list(range(100)), 10.0, 1e-10, 4.35974e-18)
+        np.testing.assert_allclose(e, yy, rtol=1e-5, atol=0)
+    g = load_npz("small_tensornet_pairpriors.npz")
+    za, ca = g["hparams"]["prior_model"][0]["ZBL"], g["hparams"]["prior_model"][1]["Coulomb"]
+    z, pos, batch, q = g["z"], g["pos"], g["batch"], g["partial_charges"]
+    nm = int(batch.max()) + 1
+    fn = lambda p: (P.zbl_energy(p, batch, z, nm, za["atomic_number"], za["cutoff_distance"], za["distance_scale"],  # noqa: E731
+                                 za["energy_scale"])
+                    + P.coulomb_energy(p, batch, q, nm, ca["alpha"], ca["distance_scale"], ca["energy_scale"]))
+    ref = (g["y"].astype(np.float64) - g["y_noprior"]).ravel()          # two fp32 runs of the reference
+    assert np.abs(fn(pos) - ref).max() <= 3e-6 * np.abs(ref).max()
+    fref = g["forces"].astype(np.float64) - g["forces_noprior"]
+    assert np.abs(P.forces_fd(fn, pos) - fref).max() <= 2e-6 * np.abs(fref).max()
