@@ -361,3 +361,111 @@ def test_small_csr_single_kernel_equals_the_four_launch_build(case):
         assert int(out[1][1][0].max()) == max(int(num) // 2, 1)
     finally:
         ops.set_tuning("small_csr", old)
+
+
+@pytest.mark.parametrize("strategy,box_type", [("brute", None), ("brute", "triclinic"), ("shared", "rectangular"),
+                                               ("cell", "rectangular"), ("cell", None)])
+@pytest.mark.parametrize("loop,include_transpose", [(True, True), (False, False)])
+def test_jit_script_compatible(strategy, box_type, loop, include_transpose):
+    """torch.jit.script(OptimizedDistance(...)) -- the reference's tests/test_neighbors.py:471-537: the scripted module gives
+    the pair list of the oracle (and of the eager module, bit for bit), molecules of 3-99 atoms."""
+    from torchmdnet.models.utils import OptimizedDistance
+    rng = np.random.RandomState(4321)
+    sizes = rng.randint(3, 100, 12)
+    batch = np.repeat(np.arange(12, dtype=np.int64), sizes)
+    lbox, cutoff = 10.0, 1.5
+    pos = (rng.rand(batch.size, 3) * lbox).astype(np.float32)
+    pos[0] = pos[1] = 0.0                                  # at least one pair (d = 0: kept by both, as in the reference's test)
+    box = None
+    if box_type == "rectangular":
+        box = np.diag([lbox] * 3).astype(np.float32)
+    elif box_type == "triclinic":
+        box = np.array([[lbox, 0, 0], [0.1 * lbox, lbox, 0], [0.3 * lbox, 0.2 * lbox, lbox]], dtype=np.float32)
+    ref = onb.neighbor_pairs(pos, batch, box, 0.0, cutoff, loop, include_transpose, rect=(strategy == "cell"))
+    n_ref = ref[0].shape[1]
+    nl = OptimizedDistance(cutoff_lower=0.0, loop=loop, cutoff_upper=cutoff, max_num_pairs=n_ref, strategy=strategy,
+                           box=None if box is None else torch.from_numpy(box), return_vecs=True,
+                           include_transpose=include_transpose)
+    tp, tb = torch.from_numpy(pos).cuda().requires_grad_(True), torch.from_numpy(batch).cuda()
+    e0 = nl(tp, tb)
+    snl = torch.jit.script(nl)
+    ei, ew, ev = snl(tp, tb)
+    assert ei.shape == (2, n_ref) and ew.shape == (n_ref,) and ev.shape == (n_ref, 3)
+    a = onb.canonical_order(ei.cpu().numpy().astype(np.int32), ev.detach().cpu().numpy(), ew.detach().cpu().numpy())
+    b = onb.canonical_order(*ref)
+    c = onb.canonical_order(e0[0].cpu().numpy().astype(np.int32), e0[2].detach().cpu().numpy(), e0[1].detach().cpu().numpy())
+    assert np.array_equal(a[0], b[0]) and np.allclose(a[2], b[2], atol=1e-6) and np.allclose(a[1], b[1], atol=1e-6)
+    assert np.array_equal(a[0], c[0]) and np.array_equal(a[1], c[1]) and np.array_equal(a[2], c[2])   # eager == scripted
+    (g,) = torch.autograd.grad(ew.sum() + (ev * ev).sum(), tp)       # the scripted module differentiates like the eager one
+    (g0,) = torch.autograd.grad(e0[1].sum() + (e0[2] * e0[2]).sum(), tp)
+    torch.testing.assert_close(g, g0, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("strategy,box_type", [("brute", None), ("brute", "triclinic"), ("cell", "rectangular")])
+@pytest.mark.parametrize("grad", ["deltas", "distances", "combined"])
+def test_neighbor_autograds(strategy, box_type, grad):
+    """gradcheck + gradgradcheck of the op in fp64 (reference: tests/test_neighbors.py:254-299, same tolerances): first and
+    second derivatives of distances and displacement vectors with respect to the positions."""
+    from torchmdnet.models.utils import OptimizedDistance
+    torch.manual_seed(123)
+    n, cutoff, lbox = 10, 4.999999, 10.0
+    box = None
+    if box_type == "rectangular":
+        box = torch.eye(3, dtype=torch.float64) * lbox
+    elif box_type == "triclinic":
+        box = torch.tensor([[lbox, 0.0, 0.0], [0.1, lbox, 0.0], [0.3, 0.2, lbox]], dtype=torch.float64)
+    nl = OptimizedDistance(cutoff_upper=cutoff, max_num_pairs=n * n, strategy=strategy, loop=False, include_transpose=True,
+                           return_vecs=True, resize_to_fit=True, box=box)
+    pos = (0.25 * lbox * torch.rand(n, 3, dtype=torch.float64)).cuda().requires_grad_(True)
+    batch = torch.zeros(n, dtype=torch.long, device="cuda")
+
+    def fn(p):
+        ei, ew, ev = nl(p, batch)
+        if grad == "deltas":
+            return ev
+        if grad == "distances":
+            return ew
+        return ev.sum(dim=-1) + ew
+
+    assert torch.autograd.gradcheck(fn, pos, eps=1e-4, atol=1e-4, rtol=1e-4, nondet_tol=1e-4)
+    assert torch.autograd.gradgradcheck(fn, pos, eps=1e-4, atol=1e-4, rtol=1e-4, nondet_tol=1e-4)
+
+
+@pytest.mark.parametrize("strategy,box_type", [("brute", None), ("shared", "triclinic"), ("cell", "rectangular")])
+def test_cuda_graph_compatible_backward(strategy, box_type):
+    """The op and its backward inside one CUDA graph (reference: tests/test_neighbors.py:622-693): warm up, capture
+    forward + backward, replay, compare the captured gradient with an eager evaluation."""
+    from torchmdnet.models.utils import OptimizedDistance
+    rng = np.random.RandomState(77)
+    sizes = rng.randint(3, 100, 16)
+    lbox, cutoff = 10.0, 1.5
+    box = None
+    if box_type == "rectangular":
+        box = torch.eye(3) * lbox
+    elif box_type == "triclinic":
+        box = torch.tensor([[lbox, 0.0, 0.0], [1.0, lbox, 0.0], [3.0, 2.0, lbox]])
+    nl = OptimizedDistance(cutoff_lower=0.0, loop=True, cutoff_upper=cutoff, max_num_pairs=-40, strategy=strategy, box=box,
+                           return_vecs=True, include_transpose=True, check_errors=False, resize_to_fit=False)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):          # the leaf lives on the capture stream, so its gradient accumulates there as well
+        batch = torch.from_numpy(np.repeat(np.arange(16, dtype=np.int64), sizes)).cuda()
+        pos = torch.from_numpy((rng.rand(int(sizes.sum()), 3) * lbox).astype(np.float32)).cuda().requires_grad_(True)
+        ei, ew, ev = nl(pos, batch)
+        (g_ref,) = torch.autograd.grad(ew.sum() + (ev * ev).sum(), pos)
+        for _ in range(3):
+            ei, ew, ev = nl(pos, batch)
+            (ew.sum() + (ev * ev).sum()).backward()
+            pos.grad.data.zero_()
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            ei, ew, ev = nl(pos, batch)
+            (ew.sum() + (ev * ev).sum()).backward()
+        pos.grad.data.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        grad = pos.grad.clone()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.testing.assert_close(grad, g_ref, rtol=1e-5, atol=1e-5)
+    assert int((ei[0] >= 0).sum()) > int(sizes.sum())           # self loops + at least some pairs

@@ -16,7 +16,7 @@ import torch.nn.functional as F
 from torch import Tensor, nn
 
 from .. import _native
-from ..neighbors import get_neighbor_pairs_kernel
+from ..neighbors import get_neighbor_pairs_kernel  # noqa: F401  (re-exported, as in the reference)
 
 
 class OptimizedDistance(nn.Module):
@@ -51,19 +51,33 @@ class OptimizedDistance(nn.Module):
         self.check_errors = check_errors
         self.long_edge_index = long_edge_index
 
+    def __prepare_scriptable__(self):
+        """``torch.jit.script(OptimizedDistance(...))`` (reference: tests/test_neighbors.py:471-537) resolves the op while
+        compiling ``forward``: the native library has to be loaded by then."""
+        _native.load()
+        return self
+
     def forward(self, pos: Tensor, batch: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Optional[Tensor]]:
-        _native.require_cuda(pos, "OptimizedDistance")
-        self.box = self.box.to(pos.dtype)
+        if not torch.jit.is_scripting():
+            _native.load()
+        if not pos.is_cuda:
+            raise RuntimeError("OptimizedDistance: this build runs on CUDA (sm_100a) only; got a CPU tensor and there is no "
+                               "CPU fallback")
+        box = self.box
+        assert box is not None
+        box = box.to(pos.dtype)
         max_pairs = self.max_num_pairs
         if max_pairs < 0:
             max_pairs = -max_pairs * pos.shape[0]
         if batch is None:
             batch = torch.zeros(pos.shape[0], dtype=torch.long, device=pos.device)
-        edge_index, edge_vec, edge_weight, num_pairs = get_neighbor_pairs_kernel(
-            self.strategy, pos, batch, self.box, self.use_periodic, self.cutoff_lower, self.cutoff_upper,
-            max_pairs, self.loop, self.include_transpose)
-        if self.check_errors and num_pairs[0] > max_pairs:
-            raise RuntimeError("Found num_pairs({}) > max_num_pairs({})".format(num_pairs[0], max_pairs))
+        edge_index, edge_vec, edge_weight, num_pairs = torch.ops.torchmdnet_neighbors.get_neighbor_pairs(
+            self.strategy, pos, batch, box, self.use_periodic, self.cutoff_lower, self.cutoff_upper, max_pairs, self.loop,
+            self.include_transpose)
+        if self.check_errors:
+            found = int(num_pairs[0].item())
+            if found > max_pairs:
+                raise RuntimeError("Found num_pairs(" + str(found) + ") > max_num_pairs(" + str(max_pairs) + ")")
         if self.resize_to_fit:
             keep = edge_index[0] != -1
             edge_index = edge_index[:, keep]
@@ -71,7 +85,9 @@ class OptimizedDistance(nn.Module):
             edge_vec = edge_vec[keep, :]
         if self.long_edge_index:
             edge_index = edge_index.to(torch.long)
-        return edge_index, edge_weight, (edge_vec if self.return_vecs else None)
+        if self.return_vecs:
+            return edge_index, edge_weight, edge_vec
+        return edge_index, edge_weight, None
 
 
 class CosineCutoff(nn.Module):
