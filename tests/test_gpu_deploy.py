@@ -295,3 +295,41 @@ def test_pair_prior_kernels_against_the_oracle(kind):
         assert np.abs(e.cpu().numpy().ravel().astype(np.float64) - e_ref).max() <= 2e-6 * np.abs(e_ref).max(), (kind, trial)
         assert np.abs(f.cpu().numpy().astype(np.float64) - f_ref).max() <= 2e-5 * np.abs(f_ref).max(), (kind, trial)
         assert e_ref[0] == 0.0 and float(e[0]) == 0.0 and float(f[0].abs().max()) == 0.0      # the single atom
+
+
+def test_zbl_and_coulomb_known_answers():
+    """The reference's own checks of the two priors (tests/test_priors.py:38-93): four atoms, energies against the pair
+    formulas written out in the test (Bohr / kJ-mol for ZBL, nm / kJ-mol for Coulomb).  Tolerance 1e-5 relative: the
+    test's Coulomb constant 138.935 is the six-digit rounding of the 138.935458 that ZBL / Coulomb use (2.30707755e-28 J m
+    converted), a 3.3e-6 difference in itself."""
+    from torchmdnet.priors import ZBL, Coulomb
+    pos = torch.tensor([[1.0, 0.0, 0.0], [2.5, 0.0, 0.0], [1.0, 1.0, 0.0], [0.0, 0.0, -1.0]])
+    types = torch.tensor([0, 1, 2, 1])
+    atomic_number = torch.tensor([1, 6, 8], dtype=torch.int8)
+    zbl = ZBL(10.0, 5, atomic_number, distance_scale=5.29177210903e-11, energy_scale=1000.0 / 6.02214076e23).cuda()
+    energy = zbl.post_reduce(torch.zeros(1, device="cuda"), types.cuda(), pos.cuda(), torch.zeros_like(types).cuda(), {})[0]
+
+    def zbl_pair(p1, p2, z1, z2):
+        r = torch.sqrt(torch.dot(p1 - p2, p1 - p2))
+        x = r / (0.8854 / (z1 ** 0.23 + z2 ** 0.23))
+        phi = (0.1818 * torch.exp(-3.2 * x) + 0.5099 * torch.exp(-0.9423 * x) + 0.2802 * torch.exp(-0.4029 * x)
+               + 0.02817 * torch.exp(-0.2016 * x))
+        return 0.5 * (torch.cos(r * torch.pi / 10.0) + 1.0) * phi * (138.935 / 5.29177210903e-2) * z1 * z2 / r
+
+    expected = sum(zbl_pair(pos[i], pos[j], atomic_number[types[i]].float(), atomic_number[types[j]].float())
+                   for i in range(4) for j in range(i))
+    torch.testing.assert_close(energy.cpu(), expected, rtol=1e-5, atol=1e-5)
+
+    pos = torch.tensor([[0.5, 0.0, 0.0], [1.5, 0.0, 0.0], [0.8, 0.8, 0.0], [0.0, 0.0, -0.4]])
+    charge = torch.tensor([0.2, -0.1, 0.8, -0.9])
+    alpha = 1.8
+    coulomb = Coulomb(alpha, 5, distance_scale=1e-9, energy_scale=1000.0 / 6.02214076e23).cuda()
+    energy = coulomb.post_reduce(torch.zeros(1, device="cuda"), types.cuda(), pos.cuda(), torch.zeros_like(types).cuda(),
+                                 {"partial_charges": charge.cuda()})[0]
+
+    def coulomb_pair(p1, p2, q1, q2):
+        r = torch.sqrt(torch.dot(p1 - p2, p1 - p2))
+        return torch.erf(alpha * r) * 138.935 * q1 * q2 / r
+
+    expected = sum(coulomb_pair(pos[i], pos[j], charge[i], charge[j]) for i in range(4) for j in range(i))
+    torch.testing.assert_close(energy.cpu(), expected, rtol=1e-5, atol=1e-5)
