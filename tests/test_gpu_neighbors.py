@@ -469,3 +469,48 @@ def test_cuda_graph_compatible_backward(strategy, box_type):
     torch.cuda.current_stream().wait_stream(s)
     torch.testing.assert_close(grad, g_ref, rtol=1e-5, atol=1e-5)
     assert int((ei[0] >= 0).sum()) > int(sizes.sum())           # self loops + at least some pairs
+
+
+def test_legacy_distance_module():
+    """``Distance`` (the reference's radius_graph-based module, models/utils.py:393-455) as the reference tests it
+    (tests/test_model_utils.py:9-84): pair counts for two atoms inside / below / above the cutoffs with and without self
+    loops, all pairs of 100 atoms in a unit cube, and the AssertionError when an atom exceeds max_num_neighbors."""
+    from torchmdnet.models.utils import Distance
+    for cutoff_lower in (0, 2):
+        for cutoff_upper in (5, 10):
+            for return_vecs in (False, True):
+                for loop in (False, True):
+                    dist = Distance(cutoff_lower, cutoff_upper, max_num_neighbors=100, return_vecs=return_vecs, loop=loop)
+                    batch = torch.tensor([0, 0]).cuda()
+                    extra = 2 if loop else 0
+                    pos = torch.tensor([[0, 0, 0], [(cutoff_lower + cutoff_upper) / 2, 0, 0]], dtype=torch.float).cuda()
+                    ei, ew, ev = dist(pos, batch)
+                    assert ei.size(1) == 2 + extra and ei.dtype == torch.long
+                    assert (ev is not None) == return_vecs
+                    if return_vecs:
+                        torch.testing.assert_close(ev, pos[ei[0]] - pos[ei[1]])
+                    torch.testing.assert_close(ew, (pos[ei[0]] - pos[ei[1]]).norm(dim=-1))
+                    if cutoff_lower > 0:
+                        pos = torch.tensor([[0, 0, 0], [cutoff_lower / 2, 0, 0]], dtype=torch.float).cuda()
+                        assert dist(pos, batch)[0].size(1) == extra
+                    pos = torch.tensor([[0, 0, 0], [cutoff_upper + 1, 0, 0]], dtype=torch.float).cuda()
+                    assert dist(pos, batch)[0].size(1) == extra
+                    torch.manual_seed(1)
+                    pos = torch.rand(100, 3).cuda()
+                    ei, ew, ev = dist(pos, torch.zeros(100, dtype=torch.long).cuda())
+                    extra = 100 if loop else 0
+                    assert ei.size(1) == (extra if cutoff_lower > 0 else 100 * 99 + extra)
+    dist = Distance(0, 5, max_num_neighbors=32)
+    pos = torch.rand(100, 3).cuda()
+    with pytest.raises(AssertionError, match="max_num_neighbors"):
+        dist(pos, torch.zeros(100, dtype=torch.long).cuda())
+    with pytest.raises(AssertionError, match="max_num_neighbors"):
+        dist(pos, torch.tensor([0] * 20 + [1] * 80).cuda())
+    ei, ew, ev = dist(pos[:30], torch.zeros(30, dtype=torch.long).cuda())        # 29 neighbours each: within the budget
+    assert ei.size(1) == 30 * 29
+    p = pos[:10].clone().requires_grad_(True)                                    # differentiable like OptimizedDistance
+    ei, ew, ev = Distance(0, 5, return_vecs=True)(p, None)
+    (g,) = torch.autograd.grad(ew.sum(), p)
+    u = (p[ei[0]] - p[ei[1]]) / ew.unsqueeze(1)
+    ref = torch.zeros_like(p).index_add_(0, ei[0], u).index_add_(0, ei[1], -u)
+    torch.testing.assert_close(g, ref.detach(), rtol=1e-5, atol=1e-5)

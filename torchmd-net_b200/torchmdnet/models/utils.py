@@ -90,6 +90,45 @@ class OptimizedDistance(nn.Module):
         return edge_index, edge_weight, None
 
 
+class Distance(nn.Module):
+    """The reference's legacy distance module (models/utils.py:393-455; ``torch_cluster.radius_graph`` there, the module its
+    graph network, transformer and pairwise priors are built on): every ordered pair (i, j), i != j, of a molecule with
+    ``cutoff_lower <= d < cutoff_upper``, self pairs when ``loop`` (kept whatever the lower cutoff), and the reference's
+    guard -- an atom with more than ``max_num_neighbors`` neighbours raises the same ``AssertionError``.  Here over the CUDA
+    op of ``OptimizedDistance`` (open boundaries); differentiable in ``pos`` like it."""
+
+    def __init__(self, cutoff_lower, cutoff_upper, max_num_neighbors=32, return_vecs=False, loop=False):
+        super().__init__()
+        self.cutoff_lower = cutoff_lower
+        self.cutoff_upper = cutoff_upper
+        self.max_num_neighbors = max_num_neighbors
+        self.return_vecs = return_vecs
+        self.loop = loop
+
+    def forward(self, pos: Tensor, batch: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Optional[Tensor]]:
+        _native.load()
+        _native.require_cuda(pos, "Distance")
+        n = pos.shape[0]
+        if batch is None:
+            batch = torch.zeros(n, dtype=torch.long, device=pos.device)
+        # room for one neighbour more than allowed per atom (+ the self pair): if the pairs found do not fit, some atom
+        # is over its budget; if they fit, the list is complete and the budget is checked per atom
+        cap = n * (int(self.max_num_neighbors) + 2)
+        ei, ev, ew, num = torch.ops.torchmdnet_neighbors.get_neighbor_pairs(
+            "brute", pos, batch, torch.empty((0, 0), dtype=pos.dtype), False, float(self.cutoff_lower),
+            float(self.cutoff_upper), cap, bool(self.loop), True)
+        msg = ("The neighbor search missed some atoms due to max_num_neighbors being too low. Please increase this "
+               "parameter to include the maximum number of atoms within the cutoff.")
+        assert int(num) <= cap, msg
+        keep = ei[0] != -1
+        ei = ei[:, keep].to(torch.long)
+        ew = ew[keep]
+        ev = ev[keep, :]
+        counts = torch.bincount(ei[0][ei[0] != ei[1]], minlength=n)
+        assert not bool((counts > self.max_num_neighbors).any()), msg
+        return ei, ew, (ev if self.return_vecs else None)
+
+
 class CosineCutoff(nn.Module):
     """models/utils.py:362-390."""
 
