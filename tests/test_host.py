@@ -343,3 +343,28 @@ def test_models_with_priors_script_on_the_cpu(name, kinds, tmp_path):
         torch.testing.assert_close(sm.prior_data[n + 1:2 * n], pr.R_r[pr.Z_map][1:].float())
     with pytest.raises(Exception):          # evaluation still needs the CUDA extension and CUDA tensors
         lm(tt(g["z"]), tt(g["pos"]), tt(g["batch"]))
+
+
+def test_reference_module_paths_resolve():
+    """The import paths a user of the reference has in their scripts (torchmdnet/models/__init__.py, priors/{base,atomref,zbl,
+    coulomb,d2}.py, models/utils.py) exist here under the same names."""
+    import importlib
+    from torchmdnet import models, priors
+    assert models.__all__ == ["graph-network", "transformer", "equivariant-transformer", "tensornet"]
+    assert priors.__all__ == ["Atomref", "D2", "ZBL", "Coulomb"]
+    for mod, names in {"torchmdnet.priors.base": ["BasePrior"], "torchmdnet.priors.atomref": ["Atomref"],
+                       "torchmdnet.priors.zbl": ["ZBL"], "torchmdnet.priors.coulomb": ["Coulomb"],
+                       "torchmdnet.priors.d2": ["D2"],
+                       "torchmdnet.models.utils": ["OptimizedDistance", "Distance", "GaussianSmearing", "ExpNormalSmearing",
+                                                   "ShiftedSoftplus", "CosineCutoff", "NeighborEmbedding",
+                                                   "GatedEquivariantBlock", "rbf_class_mapping", "act_class_mapping",
+                                                   "dtype_mapping"],
+                       "torchmdnet.models.model": ["create_model", "load_model", "create_prior_models", "TorchMD_Net"],
+                       "torchmdnet.models.output_modules": ["Scalar", "EquivariantScalar"],
+                       "torchmdnet.models.tensornet": ["TensorNet"], "torchmdnet.models.torchmd_et": ["TorchMD_ET"],
+                       "torchmdnet.models.torchmd_gn": ["TorchMD_GN"], "torchmdnet.models.torchmd_t": ["TorchMD_T"],
+                       "torchmdnet.calculators": ["External"],
+                       "torchmdnet.neighbors": ["get_neighbor_pairs_kernel"]}.items():
+        m = importlib.import_module(mod)
+        for n in names:
+            assert hasattr(m, n), (mod, n)

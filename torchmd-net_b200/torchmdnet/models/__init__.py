@@ -1,0 +1,2 @@
+"""Model names accepted by ``create_model`` (reference: torchmdnet/models/__init__.py)."""
+__all__ = ["graph-network", "transformer", "equivariant-transformer", "tensornet"]

@@ -4,4 +4,4 @@ call for energy and analytic forces, priors/pairwise.py)."""
 from .atomref import Atomref, BasePrior
 from .pairwise import D2, ZBL, Coulomb
 
-__all__ = ["Atomref", "ZBL", "Coulomb", "D2"]
+__all__ = ["Atomref", "D2", "ZBL", "Coulomb"]
