@@ -480,7 +480,7 @@ def main():
     ap.add_argument("--no-flush", action="store_true",
                     help="experiment only: do not flush L2 between the timed steps of `value` (the line says so; not a bench number)")
     ap.add_argument("--table-intervals", type=int, default=0,
-                    help="intervals of the filter tables (0 = the model's default, 16 * num_rbf); A/B runs only")
+                    help="intervals of the filter tables (0 = the model's default, max(1024, 32 * num_rbf)); A/B runs only")
     ap.add_argument("--no-table-warp", action="store_true",
                     help="A/B runs only: filter tables on a grid uniform in d (round-1 layout; use with --table-intervals 4096)")
     args = ap.parse_args()
