@@ -23,7 +23,7 @@ def main():
                 name += "'"
             kernels[name] = collections.Counter()
             continue
-        m = re.match(r"\s*/\*[0-9a-f]{4}\*/\s+(.*?);", line)
+        m = re.match(r"\s*/\*[0-9a-f]{4,}\*/\s+(.*?);", line)
         if m and name:
             ins = re.sub(r"^@!?U?P(\d+|T)\s+", "", m.group(1))
             kernels[name]["insts"] += 1
