@@ -68,3 +68,21 @@ def test_committed_records_carry_the_contract_keys(path):
         ss = d["strong_scaling"]
         assert ss["atoms_total"] == 1_029_000 and ss["n_gpus"] == d["n_gpus"]
         assert ss["correctness"]["max_abs_dF"] <= 1e-4 and ss["correctness"]["rel_dE"] <= 1e-5
+
+
+def test_reference_arm_under_torchrun_on_the_cpu():
+    """`bench.py --impl reference` launched the way the driver launches N > 1 (torchrun, one process per GPU): rank 0 alone
+    times the CPU restatement and prints ONE JSON line, the other rank exits 0 without work; no GPU is touched."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29577", os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
+           "--warmup", "1"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1, out.stdout
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["steps"] == 1 and d["warmup"] == 1
+    assert d["unit"] == "atom-steps/s" and d["value"] > 0 and d["gpu_launches"] == 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["value"] == d["value"] and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert abs(d["ms_per_step"] * 1e-3 * d["value"] - 166) <= 1e-6 * 166          # value = atoms / seconds per step
